@@ -1,0 +1,410 @@
+// tcgen05 / TMEM implicit-GEMM convolution for sm_100a.
+//
+// GEMM view of a convolution over NHWC bf16 activations:
+//   M = output pixels (tiles of bn x bh x bw <= 128 rows), N = Cout, K = taps * Cin.
+// The A operand of every (tap, 64-channel chunk) is one TMA box of the input
+// tensor, fetched at the tap-shifted coordinate: out-of-bounds elements are
+// zero-filled by the TMA unit, which is exactly the conv padding, so no im2col
+// buffer ever exists.  Stride-2 convs use a 5-D parity-split view of the same
+// NHWC memory, ConvTranspose k4s2 is 4 output-phase launches with 2x2 taps.
+//
+// Roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer
+// (warp 1 also owns the TMEM allocation), warps 2..5 = epilogue (TMEM -> regs
+// -> fused epilogue -> global).  The accumulator is double buffered in TMEM so
+// the epilogue of tile i overlaps the main loop of tile i+1.  Persistent CTAs,
+// static round-robin tile schedule.
+//
+// Reference ops covered: nn.Conv2d / nn.ConvTranspose2d / nn.Linear call sites in
+// network/AEI_Net.py:19-41,101 and network/AADLayer.py:13-18,67-74; the AAD
+// epilogue implements AADLayer.forward (network/AADLayer.py:20-38) + the ReLU
+// that always follows it (network/AADLayer.py:62,70).
+#include "igemm.cuh"
+#include "ptx.cuh"
+
+namespace ghost {
+
+using namespace ptx;
+
+namespace {
+
+struct TileCoord {
+  int tn, th, tw, nt;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile) {
+  TileCoord t;
+  t.nt = tile % p.tiles_n;
+  int m = tile / p.tiles_n;
+  t.tw = m % p.tiles_w;
+  m /= p.tiles_w;
+  t.th = m % p.tiles_h;
+  t.tn = m / p.tiles_h;
+  return t;
+}
+
+__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+
+__device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
+                                                   long long o_pix, long long r_pix) {
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+          if (p.splits > 1) {
+            float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (col0 + i < p.n_valid) atomicAdd(o + i, f[i]);
+            return;
+          }
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + col0 + i);
+          }
+          if (p.act1 == kActLeaky) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * p.slope;
+          } else if (p.act1 == kActPRelu) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * __ldg(p.slope_c + col0 + i);
+          } else if (p.act1 == kActRelu) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          const bool full16 = (col0 + 16 <= p.n_valid);
+          if (p.res) {
+            const __nv_bfloat16* rp = p.res + r_pix + col0;
+            if (full16) {
+              const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
+              const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+              const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                f[2 * i] += bf16lo(qq[i]);
+                f[2 * i + 1] += bf16hi(qq[i]);
+              }
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (col0 + i < p.n_valid) f[i] += __bfloat162float(rp[i]);
+            }
+          }
+          if (p.act2 == kAct2Tanh) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
+          }
+          if (p.out_f32) {
+            float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
+            if (full16) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                reinterpret_cast<float4*>(o)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (col0 + i < p.n_valid) o[i] = f[i];
+            }
+          } else {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + o_pix + col0;
+            if (full16) {
+              uint4 s0, s1;
+              s0.x = pack_bf16(f[0], f[1]);
+              s0.y = pack_bf16(f[2], f[3]);
+              s0.z = pack_bf16(f[4], f[5]);
+              s0.w = pack_bf16(f[6], f[7]);
+              s1.x = pack_bf16(f[8], f[9]);
+              s1.y = pack_bf16(f[10], f[11]);
+              s1.z = pack_bf16(f[12], f[13]);
+              s1.w = pack_bf16(f[14], f[15]);
+              reinterpret_cast<uint4*>(o)[0] = s0;
+              reinterpret_cast<uint4*>(o)[1] = s1;
+            } else {
+              for (int i = 0; i < 16; ++i)
+                if (col0 + i < p.n_valid) o[i] = __float2bfloat16(f[i]);
+            }
+          }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[8];
+  __shared__ uint64_t empty_bar[8];
+  __shared__ uint64_t tfull_bar[2];
+  __shared__ uint64_t tempty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ int abort_flag;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // 1024-byte aligned operand ring (swizzle atoms repeat every 1024 B)
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const int row_bytes = p.kc * 2;
+  const int a_stage_bytes = 128 * row_bytes;
+  const int b_stage_bytes = p.BN * row_bytes;
+  const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
+  const int rows_used = p.bw * p.bh * p.bn;
+  const uint32_t tx_bytes = rows_used * row_bytes + b_stage_bytes;
+
+  const int num_kb = p.ntaps * p.kc_per_tap / p.splits;  // K blocks handled by this CTA
+  const int kb0 = blockIdx.y * num_kb;
+  const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
+
+  if (threadIdx.x == 0) {
+    abort_flag = 0;
+    for (int i = 0; i < p.stages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tmA);
+    prefetch_tmap(&p.tmB);
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  const int acc_stride = p.tmem_cols >> 1;  // columns per accumulator stage
+
+  if (warp == 0) {
+    // ============================== TMA producer ==============================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x) {
+        const TileCoord t = decode_tile(p, tile);
+        const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+        for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
+          const int tap = kb / p.kc_per_tap;
+          const int kci = kb - tap * p.kc_per_tap;
+          if (!mbar_wait(&empty_bar[stage], phase ^ 1u, &abort_flag)) {
+            ok = false;
+            break;
+          }
+          uint8_t* sa = smem + stage * stage_bytes;
+          uint8_t* sb = sa + a_stage_bytes;
+          mbar_expect_tx(&full_bar[stage], tx_bytes);
+          const int c = p.a_c0 + p.tap_c[tap] + kci * p.kc;
+          if (p.a_rank == 4)
+            tma_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
+          else
+            tma_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+          tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ============================== MMA issuer ================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.BN);
+      const uint32_t sbo = 8 * row_bytes;
+      const uint64_t swz_fix = (p.kc == 64) ? 0ull : ((4ull ^ 2ull) << 61);  // SWIZZLE_64B = 4
+      const int mma_per_kb = p.kc / 16;
+      int stage = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        if (!mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag)) break;
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * acc_stride;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          if (!mbar_wait(&full_bar[stage], phase, &abort_flag)) {
+            ok = false;
+            break;
+          }
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint32_t sb = sa + a_stage_bytes;
+          const uint64_t adesc = make_smem_desc_sw128(sa, sbo) ^ swz_fix;
+          const uint64_t bdesc = make_smem_desc_sw128(sb, sbo) ^ swz_fix;
+          for (int k = 0; k < mma_per_kb; ++k)
+            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        if (ok) umma_commit(&tfull_bar[as]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ============================== epilogue ==================================
+    const int lg = warp & 3;            // TMEM lane group this warp may read
+    const int r = lg * 32 + lane;       // GEMM row inside the tile
+    const int rn = r / (p.bh * p.bw);
+    const int rh = (r / p.bw) % p.bh;
+    const int rw = r % p.bw;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it) {
+      const TileCoord t = decode_tile(p, tile);
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
+      const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * acc_stride;
+
+      if (p.mode == kModeLinear) {
+        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
+        tc_fence_after();
+        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+        const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
+        for (int j = 0; j < p.BN; j += 16) {
+          uint32_t v[16];
+          __syncwarp();
+          tmem_ld16(t_addr + j, v);
+          tmem_ld_wait();
+          const int col0 = t.nt * p.BN + j;
+          if (valid && col0 < p.n_valid) linear_epilogue_16(p, v, col0, o_pix, r_pix);
+        }
+      } else {
+        // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
+        const int cn = p.BN >> 1;
+        const int c_base = t.nt * cn;
+        const long long pix = (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow;
+        const __nv_bfloat16* hrow = p.h + pix * p.c_x;
+        float m = 0.f;
+        if (valid) {
+          if (p.mask) {
+            m = __ldg(p.mask + pix);
+          } else {
+            // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh.
+            // Runs while the tensor core is still producing this tile's gamma/beta.
+            const float* wrow = p.wh_fold + static_cast<long long>(n) * p.c_x;
+            float acc = 0.f;
+            for (int c = 0; c < p.c_x; c += 8) {
+              const uint4 q = __ldg(reinterpret_cast<const uint4*>(hrow + c));
+              const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + c));
+              const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + c) + 1);
+              acc += bf16lo(q.x) * w0.x + bf16hi(q.x) * w0.y + bf16lo(q.y) * w0.z + bf16hi(q.y) * w0.w;
+              acc += bf16lo(q.z) * w1.x + bf16hi(q.z) * w1.y + bf16lo(q.w) * w1.z + bf16hi(q.w) * w1.w;
+            }
+            acc += __ldg(p.bh_fold + n);
+            m = 1.f / (1.f + __expf(-acc));
+          }
+        }
+        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
+        tc_fence_after();
+        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+        for (int j = 0; j < cn; j += 16) {
+          uint32_t g[16], b[16];
+          __syncwarp();
+          tmem_ld16(t_addr + j, g);
+          tmem_ld16(t_addr + cn + j, b);
+          tmem_ld_wait();
+          const int c0 = c_base + j;
+          if (!(valid && c0 < p.c_x)) continue;
+          const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(hrow + c0));
+          const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(hrow + c0) + 1);
+          const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+          const float4* par = p.ncpar + static_cast<long long>(n) * p.c_x + c0;
+          const float* bg = p.bias + t.nt * p.BN + j;
+          const float* bb = bg + cn;
+          float o[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float x = (i & 1) ? bf16hi(qq[i >> 1]) : bf16lo(qq[i >> 1]);
+            const float4 pr = __ldg(par + i);
+            const float hn = fmaf(x, pr.x, pr.y);
+            const float A = fmaf(__uint_as_float(g[i]) + __ldg(bg + i), hn, __uint_as_float(b[i]) + __ldg(bb + i));
+            const float I = fmaf(pr.z, hn, pr.w);
+            o[i] = fmaxf(fmaf(m, I - A, A), 0.f);
+          }
+          __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + o_pix + c0;
+          uint4 s0, s1;
+          s0.x = pack_bf16(o[0], o[1]);
+          s0.y = pack_bf16(o[2], o[3]);
+          s0.z = pack_bf16(o[4], o[5]);
+          s0.w = pack_bf16(o[6], o[7]);
+          s1.x = pack_bf16(o[8], o[9]);
+          s1.y = pack_bf16(o[10], o[11]);
+          s1.z = pack_bf16(o[12], o[13]);
+          s1.w = pack_bf16(o[14], o[15]);
+          reinterpret_cast<uint4*>(op)[0] = s0;
+          reinterpret_cast<uint4*>(op)[1] = s1;
+        }
+      }
+      // hand the accumulator stage back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+    }
+  }
+
+  // ------------------------------ teardown ------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (abort_flag && threadIdx.x == 0 && p.err) atomicExch(p.err, 1);
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+int igemm_smem_bytes(const IgemmParams& p) {
+  const int row_bytes = p.kc * 2;
+  return p.stages * (128 * row_bytes + p.BN * row_bytes) + 1024;
+}
+
+const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    attr_set = true;
+  }
+  if (p.BN % 16 || p.BN < 16 || p.BN > 256) return "igemm: BN must be a multiple of 16 in [16,256]";
+  if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";
+  if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm: M box must hold 1..128 rows";
+  if (p.stages < 2 || p.stages > 8) return "igemm: stages must be in [2,8]";
+  if (p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
+    return "igemm: bad tmem_cols";
+  if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
+  if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
+  const int smem = igemm_smem_bytes(p);
+  if (smem > 227 * 1024) return "igemm: shared memory budget exceeded";
+  const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
+  if (tiles <= 0) return "igemm: empty grid";
+  static int num_sms = 0;
+  if (!num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (num_sms <= 0) num_sms = 148;
+  }
+  int gx = tiles < num_sms ? tiles : num_sms;
+  if (p.splits > 1) {
+    gx = num_sms / p.splits;
+    if (gx < 1) gx = 1;
+    if (gx > tiles) gx = tiles;
+  }
+  dim3 grid(gx, p.splits, 1);
+  igemm_kernel<<<grid, kIgemmThreads, smem, stream>>>(p);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+}  // namespace ghost

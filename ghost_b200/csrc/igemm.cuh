@@ -1,0 +1,68 @@
+// Parameter block shared by host and device for the tcgen05 implicit-GEMM
+// convolution kernel (K1/K2/K4/K6/K9 in DESIGN.md).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace ghost {
+
+constexpr int kIgemmMaxTaps = 16;
+constexpr int kIgemmThreads = 192;  // warp0 TMA, warp1 MMA, warps2-5 epilogue
+
+enum IgemmMode : int { kModeLinear = 0, kModeAAD = 1 };
+enum Act1 : int { kActNone = 0, kActLeaky = 1, kActPRelu = 2, kActRelu = 3 };
+enum Act2 : int { kAct2None = 0, kAct2Tanh = 1 };
+
+struct alignas(64) IgemmParams {
+  CUtensorMap tmA;  // activations, NHWC (4-D) or parity-split NHWC (5-D, stride-2 convs)
+  CUtensorMap tmB;  // packed weights [Cout_pad][taps*Cin], K-major
+
+  // ---- M tiling: one tile = bn images x bh rows x bw cols (<= 128 GEMM rows)
+  int a_rank;  // 4 or 5
+  int bw, bh, bn;
+  int tiles_w, tiles_h, tiles_nb, tiles_n;
+  int Nimg, Ho, Wo;
+  // ---- N / K
+  int BN;       // UMMA N (multiple of 16, <= 256)
+  int n_valid;  // real Cout (columns >= n_valid are never stored)
+  int kc;       // K elements per stage: 64 (128B swizzle) or 32 (64B swizzle)
+  int ntaps, kc_per_tap;
+  int a_c0;                       // first input channel inside the inner dimension
+  int b_k0;                       // first K column inside the packed weight matrix
+  int splits;                     // split-K factor (grid.y); >1 => fp32 atomic accumulate
+  short tap_c[kIgemmMaxTaps];     // added to the channel coordinate (parity * C for 5-D maps)
+  short tap_w[kIgemmMaxTaps];     // added to the w coordinate
+  short tap_p[kIgemmMaxTaps];     // h-parity coordinate (5-D maps only)
+  short tap_h[kIgemmMaxTaps];     // added to the h coordinate
+  int stages, tmem_cols;
+
+  // ---- epilogue (linear):  v = act2(act1(acc + bias) + res)
+  int mode;
+  void* out;
+  long long o_sn, o_sh, o_sw, o_off;  // element strides of the output pixel grid
+  int out_f32;                        // 1: fp32 output, else bf16
+  const float* bias;                  // [tiles_n*BN] or null
+  int act1;
+  float slope;
+  const float* slope_c;  // per-channel PReLU slopes
+  const __nv_bfloat16* res;
+  long long r_sn, r_sh, r_sw, r_off;
+  int act2;
+
+  // ---- epilogue (AAD blend): columns [0,cn) = gamma_attr, [cn,2cn) = beta_attr, cn = BN/2
+  const __nv_bfloat16* h;  // raw block input, NHWC, pixel stride c_x
+  int c_x;
+  const float4* ncpar;  // [Nimg][c_x] {rstd, -mu*rstd, gamma_id, beta_id}
+  const float* wh_fold;     // [Nimg][c_x] conv_h weight * rstd
+  const float* bh_fold;     // [Nimg]      conv_h bias - sum(w*mu*rstd)
+  const float* mask;    // optional precomputed sigmoid mask per pixel (else computed in-kernel)
+
+  int* err;  // device word set non-zero when a pipeline wait timed out
+};
+
+// Host side (igemm.cu)
+const char* igemm_launch(const IgemmParams& p, cudaStream_t stream);
+int igemm_smem_bytes(const IgemmParams& p);
+
+}  // namespace ghost

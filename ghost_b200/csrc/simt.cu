@@ -1,0 +1,566 @@
+#include "simt.cuh"
+
+#include "igemm.cuh"  // Act1 / Act2 enums
+
+namespace ghost {
+
+namespace {
+
+template <typename T>
+__device__ __forceinline__ float ldf(const T* p);
+template <>
+__device__ __forceinline__ float ldf<float>(const float* p) {
+  return __ldg(p);
+}
+template <>
+__device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return __bfloat162float(*p);
+}
+template <>
+__device__ __forceinline__ float ldf<__half>(const __half* p) {
+  return __half2float(*p);
+}
+template <typename T>
+__device__ __forceinline__ void stf(T* p, float v);
+template <>
+__device__ __forceinline__ void stf<float>(float* p, float v) {
+  *p = v;
+}
+template <>
+__device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, float v) {
+  *p = __float2bfloat16(v);
+}
+template <>
+__device__ __forceinline__ void stf<__half>(__half* p, float v) {
+  *p = __float2half(v);
+}
+
+inline const char* last_err() {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+// ---------------------------------------------------------------------------
+// Direct convolution as a shared-memory tiled GEMM on CUDA cores.
+// 64 pixels x 64 output channels per block, 256 threads, 4x4 outputs per thread.
+// ---------------------------------------------------------------------------
+constexpr int TM = 64, TN = 64, TK = 16;
+
+template <typename T>
+__global__ void __launch_bounds__(256) simt_conv_kernel(const SimtConvParams p) {
+  __shared__ float As[TK][TM + 4];
+  __shared__ float Bs[TK][TN + 4];
+  const T* in = reinterpret_cast<const T*>(p.in);
+  const int K = p.ntaps * p.Cin;
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  const long long m0 = static_cast<long long>(blockIdx.x) * TM;
+  const int n0 = blockIdx.y * TN;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+
+  // loader mapping: each thread fetches 4 consecutive k for one row
+  const int lrow = threadIdx.x >> 2, lk = (threadIdx.x & 3) * 4;
+  const long long lm = m0 + lrow;
+  int ln = 0, loh = 0, low = 0;
+  const bool lvalid = lm < M;
+  if (lvalid) {
+    low = static_cast<int>(lm % p.Wo);
+    long long t = lm / p.Wo;
+    loh = static_cast<int>(t % p.Ho);
+    ln = static_cast<int>(t / p.Ho);
+  }
+  const int lco = n0 + lrow;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += TK) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = k0 + lk + q;
+      float a = 0.f, b = 0.f;
+      if (k < K) {
+        const int tap = k / p.Cin, c = k - tap * p.Cin;
+        if (lvalid) {
+          const int ih = loh * p.stride + p.dh[tap], iw = low * p.stride + p.dw[tap];
+          if (ih >= 0 && ih < p.H && iw >= 0 && iw < p.W)
+            a = ldf(in + ((static_cast<long long>(ln) * p.H + ih) * p.W + iw) * p.C + p.c0 + c);
+        }
+        if (lco < p.Cout) b = __ldg(p.w + static_cast<long long>(lco) * K + k);
+      }
+      As[lk + q][lrow] = a;
+      Bs[lk + q][lrow] = b;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < TK; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  T* out = reinterpret_cast<T*>(p.out);
+  const T* res = reinterpret_cast<const T*>(p.res);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+    const int ow = static_cast<int>(m % p.Wo);
+    const long long t = m / p.Wo;
+    const int oh = static_cast<int>(t % p.Ho);
+    const int n = static_cast<int>(t / p.Ho);
+    const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+    const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int co = n0 + tx * 4 + j;
+      if (co >= p.Cout) continue;
+      float v = acc[i][j];
+      if (p.bias) v += __ldg(p.bias + co);
+      if (p.act1 == kActLeaky)
+        v = v > 0.f ? v : v * p.slope;
+      else if (p.act1 == kActPRelu)
+        v = v > 0.f ? v : v * __ldg(p.slope_c + co);
+      else if (p.act1 == kActRelu)
+        v = fmaxf(v, 0.f);
+      if (res) v += ldf(res + r_pix + co);
+      if (p.act2 == kAct2Tanh) v = tanhf(v);
+      stf(out + o_pix + co, v);
+    }
+  }
+}
+
+}  // namespace
+
+const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s) {
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  if (M <= 0 || p.Cout <= 0) return "simt_conv: empty problem";
+  dim3 grid(static_cast<unsigned>((M + TM - 1) / TM), (p.Cout + TN - 1) / TN);
+  if (dtype == kF32)
+    simt_conv_kernel<float><<<grid, 256, 0, s>>>(p);
+  else if (dtype == kBF16)
+    simt_conv_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(p);
+  else
+    return "simt_conv: unsupported dtype";
+  return last_err();
+}
+
+// ---------------------------------------------------------------------------
+// Instance-norm statistics (nn.InstanceNorm2d, network/AADLayer.py:17,24):
+// fp32 sum and sum of squares per (n, c).  One thread owns 8 consecutive
+// channels (a 16-byte vector for bf16), a block strides over a slab of pixels,
+// partials are combined in shared memory and flushed with one atomic per
+// (block, channel).
+// ---------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 q;
+  __nv_bfloat162 t;
+  t = __floats2bfloat162_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
+constexpr int kStatThreads = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restrict__ x, int HW, int C,
+                                                                 int pix_per_block, float* __restrict__ sums) {
+  extern __shared__ float sh[];  // [kStatThreads][16]
+  const int n = blockIdx.y;
+  const int vecs = C >> 3;                       // channel vectors per pixel
+  const int ppi = kStatThreads / vecs;           // pixels per iteration (vecs <= 256)
+  const int cv = threadIdx.x % vecs, pl = threadIdx.x / vecs;
+  const int p0 = blockIdx.x * pix_per_block;
+  const int p1 = min(HW, p0 + pix_per_block);
+  float s[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+  if (pl < ppi) {
+    const T* base = x + (static_cast<long long>(n) * HW) * C + cv * 8;
+    for (int p = p0 + pl; p < p1; p += ppi) {
+      float v[8];
+      load8(base + static_cast<long long>(p) * C, v);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += v[i];
+        q[i] = fmaf(v[i], v[i], q[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sh[threadIdx.x * 16 + i] = s[i];
+    sh[threadIdx.x * 16 + 8 + i] = q[i];
+  }
+  __syncthreads();
+  // thread t < vecs*16 reduces one (channel vector, slot) column over the ppi pixel lanes
+  for (int t = threadIdx.x; t < vecs * 16; t += kStatThreads) {
+    const int v = t >> 4, slot = t & 15;
+    float a = 0.f;
+    for (int l = 0; l < ppi; ++l) a += sh[(l * vecs + v) * 16 + slot];
+    const int c = v * 8 + (slot & 7);
+    atomicAdd(sums + (static_cast<long long>(n) * C + c) * 2 + (slot >> 3), a);
+  }
+}
+
+__global__ void aad_fold_kernel(const float* __restrict__ sums, int HW, int C, const float* __restrict__ zfc, int ldz,
+                                int off_gamma, int off_beta, const float* __restrict__ w_h, float b_h,
+                                float4* __restrict__ ncpar, float* __restrict__ wh_fold, float* __restrict__ bh_fold) {
+  __shared__ float red[32];
+  const int n = blockIdx.x;
+  const float inv = 1.f / static_cast<float>(HW);
+  float part = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float su = sums[(static_cast<long long>(n) * C + c) * 2];
+    const float sq = sums[(static_cast<long long>(n) * C + c) * 2 + 1];
+    const float mu = su * inv;
+    const float var = fmaxf(sq * inv - mu * mu, 0.f);
+    const float rstd = rsqrtf(var + 1e-5f);
+    const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
+    const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
+    ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
+    const float w = w_h[c] * rstd;
+    wh_fold[static_cast<long long>(n) * C + c] = w;
+    part += w * mu;
+  }
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) bh_fold[n] = b_h - v;
+  }
+}
+
+// One warp per pixel: pass 1 = mask logit (warp reduce), pass 2 = blend + ReLU.
+template <typename T>
+__global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h, const T* __restrict__ gb,
+                                                         T* __restrict__ out, long long npix, int HW, int C,
+                                                         const float4* __restrict__ ncpar,
+                                                         const float* __restrict__ wh_fold,
+                                                         const float* __restrict__ bh_fold) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long pix = warp0; pix < npix; pix += nwarps) {
+    const int n = static_cast<int>(pix / HW);
+    const T* hrow = h + pix * C;
+    const T* grow = gb + pix * 2 * C;
+    const float* wrow = wh_fold + static_cast<long long>(n) * C;
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc = fmaf(ldf(hrow + c), __ldg(wrow + c), acc);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    const float m = 1.f / (1.f + expf(-(acc + __ldg(bh_fold + n))));
+    for (int c = lane; c < C; c += 32) {
+      const float4 pr = __ldg(ncpar + static_cast<long long>(n) * C + c);
+      const float hn = fmaf(ldf(hrow + c), pr.x, pr.y);
+      const float A = fmaf(ldf(grow + c), hn, ldf(grow + C + c));
+      const float I = fmaf(pr.z, hn, pr.w);
+      stf(out + pix * C + c, fmaxf((1.f - m) * A + m * I, 0.f));
+    }
+  }
+}
+
+}  // namespace
+
+const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* sums, cudaStream_t s) {
+  if (C % 8 || C > 8 * kStatThreads) return "in_stats: C must be a multiple of 8 and <= 2048";
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * N * C, s);
+  if (e != cudaSuccess) return cudaGetErrorString(e);
+  const int vecs = C / 8;
+  const int ppi = kStatThreads / vecs;
+  // aim for >= ~4 waves of 148 SMs worth of blocks, but at least 8 iterations per block
+  int blocks_x = (592 + N - 1) / N;
+  int ppb = (HW + blocks_x - 1) / blocks_x;
+  if (ppb < ppi * 8) ppb = ppi * 8;
+  blocks_x = (HW + ppb - 1) / ppb;
+  dim3 grid(blocks_x, N);
+  const int smem = kStatThreads * 16 * sizeof(float);
+  if (dtype == kF32)
+    in_stats_kernel<float><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x), HW, C, ppb, sums);
+  else if (dtype == kBF16)
+    in_stats_kernel<__nv_bfloat16>
+        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, sums);
+  else
+    return "in_stats: unsupported dtype";
+  return last_err();
+}
+
+const char* aad_fold_launch(const float* sums, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
+                            int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
+                            cudaStream_t s) {
+  aad_fold_kernel<<<N, 256, 0, s>>>(sums, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold, bh_fold);
+  return last_err();
+}
+
+const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype, int N, int HW, int C,
+                             const float4* ncpar, const float* wh_fold, const float* bh_fold, cudaStream_t s) {
+  const long long npix = static_cast<long long>(N) * HW;
+  long long blocks = (npix + 7) / 8;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (dtype == kF32)
+    aad_apply_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, s>>>(
+        reinterpret_cast<const float*>(h), reinterpret_cast<const float*>(gb), reinterpret_cast<float*>(out), npix, HW,
+        C, ncpar, wh_fold, bh_fold);
+  else if (dtype == kBF16)
+    aad_apply_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(h), reinterpret_cast<const __nv_bfloat16*>(gb),
+        reinterpret_cast<__nv_bfloat16*>(out), npix, HW, C, ncpar, wh_fold, bh_fold);
+  else
+    return "aad_apply: unsupported dtype";
+  return last_err();
+}
+
+// ---------------------------------------------------------------------------
+// Bilinear x2 (align_corners=True), layout conversion, small glue kernels.
+// ---------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2x_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H,
+                                                          int W, int C, int oC, int o_c0) {
+  const int Ho = 2 * H, Wo = 2 * W, vecs = C >> 3;
+  const long long total = static_cast<long long>(N) * Ho * Wo * vecs;
+  const float sh = Ho > 1 ? static_cast<float>(H - 1) / static_cast<float>(Ho - 1) : 0.f;
+  const float sw = Wo > 1 ? static_cast<float>(W - 1) / static_cast<float>(Wo - 1) : 0.f;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % vecs);
+    long long t = i / vecs;
+    const int ow = static_cast<int>(t % Wo);
+    t /= Wo;
+    const int oh = static_cast<int>(t % Ho);
+    const int n = static_cast<int>(t / Ho);
+    // ATen upsample_bilinear2d (align_corners): src = dst * (in-1)/(out-1), lambda in fp32
+    const float fh = sh * oh, fw = sw * ow;
+    const int h0 = static_cast<int>(fh), w0 = static_cast<int>(fw);
+    const int h1 = h0 + (h0 < H - 1 ? 1 : 0), w1 = w0 + (w0 < W - 1 ? 1 : 0);
+    const float lh = fh - h0, lw = fw - w0;
+    const T* base = x + static_cast<long long>(n) * H * W * C + cv * 8;
+    float a[8], b[8], c[8], d[8], o[8];
+    load8(base + (static_cast<long long>(h0) * W + w0) * C, a);
+    load8(base + (static_cast<long long>(h0) * W + w1) * C, b);
+    load8(base + (static_cast<long long>(h1) * W + w0) * C, c);
+    load8(base + (static_cast<long long>(h1) * W + w1) * C, d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      o[k] = (1.f - lh) * ((1.f - lw) * a[k] + lw * b[k]) + lh * ((1.f - lw) * c[k] + lw * d[k]);
+    store8(y + ((static_cast<long long>(n) * Ho + oh) * Wo + ow) * oC + o_c0 + cv * 8, o);
+  }
+}
+
+template <typename S, typename D>
+__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const S* __restrict__ src, D* __restrict__ dst, int C,
+                                                            int HW, int dstC, int dst_c0) {
+  // tile transpose: 32 pixels x 32 channels through shared memory, both sides coalesced
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, p = p0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? ldf(src + (static_cast<long long>(n) * C + c) * HW + p) : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int p = p0 + j, c = c0 + tx;
+    if (c < C && p < HW) stf(dst + (static_cast<long long>(n) * HW + p) * dstC + dst_c0 + c, tile[tx][j]);
+  }
+}
+
+template <typename S, typename D>
+__global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const S* __restrict__ src, int srcC, int src_c0,
+                                                            D* __restrict__ dst, int C, int HW) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {
+    const int p = p0 + j, c = c0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? ldf(src + (static_cast<long long>(n) * HW + p) * srcC + src_c0 + c) : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, p = p0 + tx;
+    if (c < C && p < HW) stf(dst + (static_cast<long long>(n) * C + c) * HW + p, tile[tx][j]);
+  }
+}
+
+template <typename T>
+__global__ void zfc_to_act_kernel(const float* __restrict__ zfc, int ldz, int off, int count,
+                                  const float* __restrict__ bias, T* __restrict__ dst, int N) {
+  const long long total = static_cast<long long>(N) * count;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int n = static_cast<int>(i / count), j = static_cast<int>(i % count);
+    stf(dst + i, zfc[static_cast<long long>(n) * ldz + off + j] + (bias ? bias[j] : 0.f));
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) channel_affine_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                              long long npix, int C, const float* __restrict__ scale,
+                                                              const float* __restrict__ shift,
+                                                              const float* __restrict__ prelu) {
+  const int vecs = C >> 3;
+  const long long total = npix * vecs;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(i % vecs) * 8;
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float t = fmaf(v[k], __ldg(scale + c + k), __ldg(shift + c + k));
+      if (prelu) t = t > 0.f ? t : t * __ldg(prelu + c + k);
+      v[k] = t;
+    }
+    store8(y + i * 8, v);
+  }
+}
+
+inline unsigned grid_for(long long total, int threads) {
+  long long b = (total + threads - 1) / threads;
+  const long long cap = 148LL * 32;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<unsigned>(b);
+}
+
+template <typename S>
+const char* nchw_to_nhwc_dst(const S* src, void* dst, int dst_dtype, int N, int C, int H, int W, int dstC, int dst_c0,
+                             cudaStream_t s) {
+  dim3 grid((H * W + 31) / 32, (C + 31) / 32, N);
+  if (dst_dtype == kF32)
+    nchw_to_nhwc_kernel<S, float><<<grid, 256, 0, s>>>(src, reinterpret_cast<float*>(dst), C, H * W, dstC, dst_c0);
+  else if (dst_dtype == kBF16)
+    nchw_to_nhwc_kernel<S, __nv_bfloat16>
+        <<<grid, 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), C, H * W, dstC, dst_c0);
+  else
+    return "nchw_to_nhwc: unsupported destination dtype";
+  return last_err();
+}
+
+template <typename S>
+const char* nhwc_to_nchw_dst(const S* src, int srcC, int src_c0, void* dst, int dst_dtype, int N, int C, int H, int W,
+                             cudaStream_t s) {
+  dim3 grid((H * W + 31) / 32, (C + 31) / 32, N);
+  if (dst_dtype == kF32)
+    nhwc_to_nchw_kernel<S, float><<<grid, 256, 0, s>>>(src, srcC, src_c0, reinterpret_cast<float*>(dst), C, H * W);
+  else if (dst_dtype == kBF16)
+    nhwc_to_nchw_kernel<S, __nv_bfloat16>
+        <<<grid, 256, 0, s>>>(src, srcC, src_c0, reinterpret_cast<__nv_bfloat16*>(dst), C, H * W);
+  else if (dst_dtype == kF16)
+    nhwc_to_nchw_kernel<S, __half><<<grid, 256, 0, s>>>(src, srcC, src_c0, reinterpret_cast<__half*>(dst), C, H * W);
+  else
+    return "nhwc_to_nchw: unsupported destination dtype";
+  return last_err();
+}
+
+}  // namespace
+
+const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, int oC, int o_c0,
+                              cudaStream_t s) {
+  if (C % 8 || oC % 8 || o_c0 % 8) return "upsample2x: channels must be multiples of 8";
+  const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
+  if (dtype == kF32)
+    upsample2x_kernel<float><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const float*>(x),
+                                                                  reinterpret_cast<float*>(y), N, H, W, C, oC, o_c0);
+  else if (dtype == kBF16)
+    upsample2x_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C, oC, o_c0);
+  else
+    return "upsample2x: unsupported dtype";
+  return last_err();
+}
+
+const char* nchw_to_nhwc_launch(const void* src, int src_dtype, void* dst, int dst_dtype, int N, int C, int H, int W,
+                                int dstC, int dst_c0, cudaStream_t s) {
+  if (src_dtype == kF32)
+    return nchw_to_nhwc_dst(reinterpret_cast<const float*>(src), dst, dst_dtype, N, C, H, W, dstC, dst_c0, s);
+  if (src_dtype == kBF16)
+    return nchw_to_nhwc_dst(reinterpret_cast<const __nv_bfloat16*>(src), dst, dst_dtype, N, C, H, W, dstC, dst_c0, s);
+  if (src_dtype == kF16)
+    return nchw_to_nhwc_dst(reinterpret_cast<const __half*>(src), dst, dst_dtype, N, C, H, W, dstC, dst_c0, s);
+  return "nchw_to_nhwc: unsupported source dtype";
+}
+
+const char* nhwc_to_nchw_launch(const void* src, int src_dtype, int srcC, int src_c0, void* dst, int dst_dtype, int N,
+                                int C, int H, int W, cudaStream_t s) {
+  if (src_dtype == kF32)
+    return nhwc_to_nchw_dst(reinterpret_cast<const float*>(src), srcC, src_c0, dst, dst_dtype, N, C, H, W, s);
+  if (src_dtype == kBF16)
+    return nhwc_to_nchw_dst(reinterpret_cast<const __nv_bfloat16*>(src), srcC, src_c0, dst, dst_dtype, N, C, H, W, s);
+  return "nhwc_to_nchw: unsupported source dtype";
+}
+
+const char* zfc_to_act_launch(const float* zfc, int ldz, int off, int count, const float* bias, void* dst, int dtype,
+                              int N, cudaStream_t s) {
+  const long long total = static_cast<long long>(N) * count;
+  if (dtype == kF32)
+    zfc_to_act_kernel<float>
+        <<<grid_for(total, 256), 256, 0, s>>>(zfc, ldz, off, count, bias, reinterpret_cast<float*>(dst), N);
+  else if (dtype == kBF16)
+    zfc_to_act_kernel<__nv_bfloat16>
+        <<<grid_for(total, 256), 256, 0, s>>>(zfc, ldz, off, count, bias, reinterpret_cast<__nv_bfloat16*>(dst), N);
+  else
+    return "zfc_to_act: unsupported dtype";
+  return last_err();
+}
+
+const char* channel_affine_launch(const void* x, void* y, int dtype, long long npix, int C, const float* scale,
+                                  const float* shift, const float* prelu, cudaStream_t s) {
+  if (C % 8) return "channel_affine: C must be a multiple of 8";
+  const long long total = npix * (C / 8);
+  if (dtype == kF32)
+    channel_affine_kernel<float><<<grid_for(total, 256), 256, 0, s>>>(
+        reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), npix, C, scale, shift, prelu);
+  else if (dtype == kBF16)
+    channel_affine_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), npix, C, scale, shift, prelu);
+  else
+    return "channel_affine: unsupported dtype";
+  return last_err();
+}
+
+}  // namespace ghost

@@ -1,0 +1,70 @@
+// CUDA-core kernels: the fp32 "correctness mode" convolution, the thin layers
+// that do not fit a tensor-core tile (Cin = 3), and every bandwidth-bound
+// elementwise / reduction step of the hot path.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ghost {
+
+enum DType : int { kF32 = 0, kBF16 = 1, kF16 = 2, kU8 = 3 };
+
+struct SimtConvParams {
+  const void* in;  // NHWC, element type = act dtype
+  int N, H, W, C;  // C = pixel stride in elements
+  int c0, Cin;     // channel slice read by the conv
+  int stride;      // input pos = stride * o + d
+  int ntaps;
+  short dh[16], dw[16];
+  int Ho, Wo;      // output pixel grid
+  const float* w;  // [Cout][ntaps*Cin]
+  int Cout;
+  void* out;
+  long long o_sn, o_sh, o_sw, o_off;
+  const float* bias;
+  int act1;
+  float slope;
+  const float* slope_c;
+  const void* res;
+  long long r_sn, r_sh, r_sw, r_off;
+  int act2;
+};
+
+// dtype: kF32 or kBF16 activations (weights and accumulation are always fp32)
+const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s);
+
+// Instance-norm statistics, NHWC.  sums: [N][C][2] fp32 (sum, sum of squares), zeroed by the call.
+const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* sums, cudaStream_t s);
+
+// Per-AAD-layer fold of the statistics with the identity FCs and conv_h.
+//   ncpar[n][c] = {rstd, -mu*rstd, gamma_id, beta_id}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
+const char* aad_fold_launch(const float* sums, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
+                            int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
+                            cudaStream_t s);
+
+// Unfused AAD blend (+ReLU) used by the fp32 mode: gb = [N,H,W,2C] (gamma | beta, bias included).
+const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype, int N, int HW, int C,
+                             const float4* ncpar, const float* wh_fold, const float* bh_fold, cudaStream_t s);
+
+// Bilinear x2, align_corners=True, NHWC (F.interpolate call sites network/AEI_Net.py:94,125-137).
+// The output may be a channel slice of a wider tensor (oC = pixel stride, o_c0 = first channel).
+const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, int oC, int o_c0,
+                              cudaStream_t s);
+
+// Layout / dtype conversion at the operator boundary.
+const char* nchw_to_nhwc_launch(const void* src, int src_dtype, void* dst, int dst_dtype, int N, int C, int H, int W,
+                                int dstC, int dst_c0, cudaStream_t s);
+const char* nhwc_to_nchw_launch(const void* src, int src_dtype, int srcC, int src_c0, void* dst, int dst_dtype, int N,
+                                int C, int H, int W, cudaStream_t s);
+
+// up1 (ConvTranspose2d 512->1024 k2 on a 1x1 map) is part of the z_id GEMM; this scatters its
+// fp32 result (+bias) into the NHWC activation m1[N,2,2,1024].
+const char* zfc_to_act_launch(const float* zfc, int ldz, int off, int count, const float* bias, void* dst, int dtype,
+                              int N, cudaStream_t s);
+
+// y[n,p,c] = x[n,p,c]*scale[c] + shift[c]  (iresnet BatchNorm that precedes a zero-padded conv)
+const char* channel_affine_launch(const void* x, void* y, int dtype, long long npix, int C, const float* scale,
+                                  const float* shift, const float* prelu, cudaStream_t s);
+
+}  // namespace ghost
