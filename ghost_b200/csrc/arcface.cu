@@ -1,0 +1,200 @@
+// ArcFace iresnet100 plan.  The reference imports arcface_model/iresnet.py, which is NOT in its
+// tree (download_models.sh:2-3 fetches a copy of insightface recognition/arcface_torch/backbones/
+// iresnet.py); the architecture below restates that public file:
+//   conv3x3(3,64,s1)+BN+PReLU -> layers [3,13,30,3] of IBasicBlock(planes 64,128,256,512; the first
+//   block of each layer has stride 2 and a conv1x1(s2)+BN downsample) -> BN2d -> flatten(NCHW) ->
+//   Linear(25088,512) -> BN1d(512).  IBasicBlock: BN1 -> conv3x3(s1) -> BN2 -> PReLU -> conv3x3(stride)
+//   -> BN3 -> (+identity).  eps = 1e-5 everywhere.  Call sites: inference.py:33-36, core.py:45,54.
+#include <math.h>
+
+#include "net.cuh"
+
+namespace ghost {
+
+namespace {
+const int kLayers[4] = {3, 13, 30, 3};
+const int kPlanes[4] = {64, 128, 256, 512};
+
+void bn_fold_t(const HostTensor& g, const HostTensor& b, const HostTensor& rm, const HostTensor& rv,
+               std::vector<float>* scale, std::vector<float>* shift) {
+  const size_t C = g.data.size();
+  scale->resize(C);
+  shift->resize(C);
+  for (size_t c = 0; c < C; ++c) {
+    const float s = g.data[c] / sqrtf(rv.data[c] + 1e-5f);
+    (*scale)[c] = s;
+    (*shift)[c] = b.data[c] - rm.data[c] * s;
+  }
+}
+}  // namespace
+
+void Net::finalize_arcface() {
+  const bool bf = act_dtype == kBF16;
+  auto bn = [&](const std::string& k, std::vector<float>* sc, std::vector<float>* sh) {
+    bn_fold_t(W(k + ".weight"), W(k + ".bias"), W(k + ".running_mean"), W(k + ".running_var"), sc, sh);
+  };
+  // conv weight [Co,Ci,k,k] -> [Co][tap][Ci] with a per-Cout scale folded in
+  auto pack_conv = [&](const std::string& name, const std::string& key, int Ci, int Co, int k,
+                       const std::vector<float>& sc, const std::vector<float>& sh) {
+    const HostTensor& w = W(key);
+    if (w.shape != std::vector<int64_t>({Co, Ci, k, k})) fail(-2, "unexpected shape for " + key);
+    const int T = k * k;
+    std::vector<float> rows(static_cast<size_t>(Co) * T * Ci);
+    for (int co = 0; co < Co; ++co)
+      for (int ci = 0; ci < Ci; ++ci)
+        for (int t = 0; t < T; ++t)
+          rows[(static_cast<size_t>(co) * T + t) * Ci + ci] = w.data[(static_cast<size_t>(co) * Ci + ci) * T + t] * sc[co];
+    const bool tc = bf && Ci % 32 == 0;
+    packed_[name] = pack(rows, Co, T * Ci, &sh, !tc, tc);
+  };
+  std::vector<float> sc, sh;
+  bn("bn1", &sc, &sh);
+  pack_conv("stem", "conv1.weight", 3, 64, 3, sc, sh);
+  vecs_["stem.prelu"] = wpool_.upload(W("prelu.weight").data);
+  int inpl = 64;
+  for (int l = 0; l < 4; ++l) {
+    const int pl = kPlanes[l];
+    for (int i = 0; i < kLayers[l]; ++i) {
+      char kb[64], nb[64];
+      snprintf(kb, sizeof(kb), "layer%d.%d", l + 1, i);
+      snprintf(nb, sizeof(nb), "l%d.%d", l + 1, i);
+      const std::string k = kb, n = nb;
+      const int ci = i == 0 ? inpl : pl;
+      bn(k + ".bn1", &sc, &sh);
+      vecs_[n + ".bn1.scale"] = wpool_.upload(sc);
+      vecs_[n + ".bn1.shift"] = wpool_.upload(sh);
+      bn(k + ".bn2", &sc, &sh);
+      pack_conv(n + ".conv1", k + ".conv1.weight", ci, pl, 3, sc, sh);
+      {
+        std::vector<float> pr = W(k + ".prelu.weight").data;
+        pr.resize((pl + 255) / 256 * 256, 0.f);
+        vecs_[n + ".prelu"] = wpool_.upload(pr);
+      }
+      bn(k + ".bn3", &sc, &sh);
+      pack_conv(n + ".conv2", k + ".conv2.weight", pl, pl, 3, sc, sh);
+      if (i == 0) {
+        bn(k + ".downsample.1", &sc, &sh);
+        pack_conv(n + ".down", k + ".downsample.0.weight", ci, pl, 1, sc, sh);
+      }
+    }
+    inpl = pl;
+  }
+  // head: BN2d -> flatten (c,h,w) -> fc -> BN1d, all folded into one [512][25088] matrix in (h,w,c) order
+  std::vector<float> s2, t2, sf, tf;
+  bn("bn2", &s2, &t2);
+  bn("features", &sf, &tf);
+  const HostTensor& fw = W("fc.weight");
+  const HostTensor& fb = W("fc.bias");
+  if (fw.shape != std::vector<int64_t>({512, 25088})) fail(-2, "unexpected shape for fc.weight");
+  std::vector<float> rows(static_cast<size_t>(512) * 25088), bias(512);
+  for (int j = 0; j < 512; ++j) {
+    double acc = fb.data[j];
+    for (int c = 0; c < 512; ++c)
+      for (int hw = 0; hw < 49; ++hw) {
+        const float w = fw.data[static_cast<size_t>(j) * 25088 + c * 49 + hw];
+        rows[static_cast<size_t>(j) * 25088 + hw * 512 + c] = w * s2[c] * sf[j];
+        acc += static_cast<double>(w) * t2[c];
+      }
+    bias[j] = static_cast<float>(acc) * sf[j] + tf[j];
+  }
+  packed_["fc"] = pack(rows, 512, 25088, &bias, !bf, bf);
+}
+
+void Net::build_arcface(ExecPlan& p) {
+  const int B = p.B;
+  const int dt = act_dtype;
+  const bool bf = dt == kBF16;
+  int* err = p.err_word;
+  auto new_act = [&](int H, int W, int C) {
+    Act a;
+    a.N = B; a.H = H; a.W = W; a.C = C; a.dtype = dt;
+    a.p = p.pool.alloc(a.bytes());
+    return a;
+  };
+  auto add_conv = [&](const std::string& name, const Act& in, int Cin, const Taps& taps, int Ho, int Wo,
+                      const std::string& wname, const OutView& out, const Epilogue& epi) {
+    auto it = packed_.find(wname);
+    if (it == packed_.end()) fail(-2, "internal: packed weights missing for " + wname);
+    LaunchOp lop;
+    lop.name = name;
+    check_msg(lower_conv(&lop, in, 0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, nullptr), name);
+    Op op;
+    op.name = name;
+    op.flops = lop.flops;
+    op.run = [lop](cudaStream_t s) { return lop.launch(s); };
+    p.ops.push_back(std::move(op));
+  };
+
+  p.emb_in = new_act(112, 112, 3);
+  Act x = new_act(112, 112, 64);
+  {
+    Epilogue e;
+    e.act1 = kActPRelu;
+    e.slope_c = vecs_.at("stem.prelu");
+    add_conv("stem", p.emb_in, 3, Taps::square(3, 1, 1), 112, 112, "stem", OutView::dense(x), e);
+  }
+  int hw = 112;
+  for (int l = 0; l < 4; ++l) {
+    const int pl = kPlanes[l];
+    for (int i = 0; i < kLayers[l]; ++i) {
+      char nb[64];
+      snprintf(nb, sizeof(nb), "l%d.%d", l + 1, i);
+      const std::string n = nb;
+      const int stride = i == 0 ? 2 : 1;
+      const int ho = hw / stride;
+      Act t = new_act(hw, hw, x.C);
+      {
+        const Act xx = x, tt = t;
+        const float* scv = vecs_.at(n + ".bn1.scale");
+        const float* shv = vecs_.at(n + ".bn1.shift");
+        Op op;
+        op.name = n + ".bn1";
+        op.run = [=](cudaStream_t s) {
+          return channel_affine_launch(xx.p, tt.p, dt, static_cast<long long>(B) * xx.H * xx.W, xx.C, scv, shv,
+                                       nullptr, s);
+        };
+        p.ops.push_back(std::move(op));
+      }
+      Act u = new_act(hw, hw, pl);
+      {
+        Epilogue e;
+        e.act1 = kActPRelu;
+        e.slope_c = vecs_.at(n + ".prelu");
+        add_conv(n + ".conv1", t, x.C, Taps::square(3, 1, 1), hw, hw, n + ".conv1", OutView::dense(u), e);
+      }
+      Act idn = x;
+      if (i == 0) {
+        idn = new_act(ho, ho, pl);
+        Taps tp = Taps::point();
+        tp.stride = 2;
+        add_conv(n + ".down", x, x.C, tp, ho, ho, n + ".down", OutView::dense(idn), Epilogue());
+      }
+      Act o = new_act(ho, ho, pl);
+      {
+        Epilogue e;
+        const OutView rv = OutView::dense(idn);
+        e.res = idn.p;
+        e.r_sn = rv.sn; e.r_sh = rv.sh; e.r_sw = rv.sw; e.r_off = rv.off;
+        add_conv(n + ".conv2", u, pl, Taps::square(3, 1, stride), ho, ho, n + ".conv2", OutView::dense(o), e);
+      }
+      x = o;
+      hw = ho;
+    }
+  }
+  // head
+  p.emb_out = p.pool.alloc_n<float>(static_cast<size_t>(B) * 512);
+  Act flat = x;
+  flat.H = flat.W = 1;
+  flat.C = 25088;
+  OutView zo;
+  zo.p = p.emb_out;
+  zo.sn = 512;
+  zo.dtype = kF32;
+  if (bf) {
+    add_conv("fc", flat, 25088, Taps::point(), 1, 1, "fc", zo, Epilogue());
+  } else {
+    add_conv("fc", flat, 25088, Taps::point(), 1, 1, "fc", zo, Epilogue());
+  }
+}
+
+}  // namespace ghost

@@ -1,0 +1,328 @@
+// extern "C" surface declared in include/ghost_b200.h.  No C++ exception crosses the ABI.
+#include <string.h>
+
+#include <mutex>
+
+#include "../../include/ghost_b200.h"
+#include "net.cuh"
+
+using namespace ghost;
+
+struct ghost_net {
+  Net net;
+  std::mutex mu;
+  ghost_net(Net::Kind k, const char* bb, int nb, int cid, int mode) : net(k, bb, nb, cid, mode) {}
+};
+
+namespace {
+
+thread_local std::string g_last_error;
+
+template <typename F>
+int guarded(F&& f) {
+  try {
+    check_device_errors();
+    f();
+    return GHOST_OK;
+  } catch (const GhostError& e) {
+    g_last_error = e.what();
+    return e.code;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return GHOST_ERR_INVALID;
+  } catch (...) {
+    g_last_error = "unknown error";
+    return GHOST_ERR_INVALID;
+  }
+}
+
+inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+void require(bool c, const char* msg) {
+  if (!c) fail(GHOST_ERR_INVALID, msg);
+}
+
+void write_attrs(Net& n, ExecPlan& p, void* const* attr_out, int out_dtype, cudaStream_t s) {
+  if (!attr_out) return;
+  for (int k = 0; k < 8; ++k) {
+    if (!attr_out[k]) continue;
+    const Act& a = p.attr[k];
+    check_msg(nhwc_to_nchw_launch(a.p, a.dtype, a.C, 0, attr_out[k], out_dtype, a.N, a.C, a.H, a.W, s), "attr out");
+  }
+}
+
+struct DeviceTables {
+  short* idx = nullptr;
+  short* a0 = nullptr;
+  short* a1 = nullptr;
+};
+DeviceTables& resize_tables() {
+  static std::map<int, DeviceTables> per_dev;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
+  int dev = 0;
+  check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+  DeviceTables& t = per_dev[dev];
+  if (!t.idx) {
+    short h[3][224];
+    paste_resize_tables(h[0], h[1], h[2]);
+    short* d = nullptr;
+    check_cuda(cudaMalloc(&d, sizeof(h)), "resize tables");
+    check_cuda(cudaMemcpy(d, h, sizeof(h), cudaMemcpyHostToDevice), "resize tables");
+    t.idx = d;
+    t.a0 = d + 224;
+    t.a1 = d + 448;
+  }
+  return t;
+}
+
+// grow-only per-device scratch for the paste-back face table
+struct Scratch {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+void* paste_scratch(size_t bytes) {
+  static std::map<int, Scratch> per_dev;
+  int dev = 0;
+  check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+  Scratch& s = per_dev[dev];
+  if (s.cap < bytes) {
+    if (s.p) {
+      check_cuda(cudaDeviceSynchronize(), "scratch sync");
+      cudaFree(s.p);
+    }
+    s.cap = bytes * 2 + 4096;
+    check_cuda(cudaMalloc(&s.p, s.cap), "paste scratch");
+  }
+  return s.p;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ghost_version(void) { return GHOST_B200_VERSION; }
+const char* ghost_last_error(void) { return g_last_error.c_str(); }
+
+int ghost_check_errors(void) {
+  return guarded([] {});
+}
+
+int ghost_aei_create(ghost_net_t** out, const char* backbone, int num_blocks, int c_id, int mode) {
+  return guarded([&] {
+    require(out && backbone, "null argument");
+    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    if (strcmp(backbone, "resnet") == 0) fail(GHOST_ERR_INVALID, "backbone 'resnet' is not supported by ghost_b200");
+    require(strcmp(backbone, "unet") == 0 || strcmp(backbone, "linknet") == 0, "unknown backbone");
+    require(num_blocks >= 1 && num_blocks <= 4, "num_blocks must be in [1,4]");
+    require(c_id > 0 && c_id % 32 == 0, "c_id must be a positive multiple of 32");
+    *out = new ghost_net(Net::kAEI, backbone, num_blocks, c_id, mode);
+  });
+}
+
+int ghost_arcface_create(ghost_net_t** out, int mode) {
+  return guarded([&] {
+    require(out, "null argument");
+    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    *out = new ghost_net(Net::kArcFace, "iresnet100", 0, 512, mode);
+  });
+}
+
+int ghost_net_set_weight(ghost_net_t* net, const char* key, const float* data, const int64_t* shape, int ndim) {
+  return guarded([&] {
+    require(net && key && data && (shape || ndim == 0) && ndim >= 0 && ndim <= 8, "bad argument");
+    std::lock_guard<std::mutex> lk(net->mu);
+    net->net.set_weight(key, data, shape, ndim);
+  });
+}
+
+int ghost_net_finalize(ghost_net_t* net) {
+  return guarded([&] {
+    require(net, "null net");
+    std::lock_guard<std::mutex> lk(net->mu);
+    net->net.finalize();
+  });
+}
+
+int ghost_net_enable_graph(ghost_net_t* net, int enable) {
+  return guarded([&] {
+    require(net, "null net");
+    net->net.use_graph = enable != 0;
+  });
+}
+
+int ghost_net_stats(ghost_net_t* net, int B, int* launches, double* flops) {
+  return guarded([&] {
+    require(net, "null net");
+    std::lock_guard<std::mutex> lk(net->mu);
+    ExecPlan& p = net->net.plan(B);
+    if (launches) *launches = static_cast<int>(p.ops.size());
+    if (flops) *flops = p.flops;
+  });
+}
+
+int ghost_aei_forward(ghost_net_t* net, const void* Xt, int xt_dtype, const void* z_id, int z_dtype, void* Y,
+                      void* const* attr_out, int out_dtype, int B, void* stream) {
+  return guarded([&] {
+    require(net && Xt && z_id && Y, "null argument");
+    require(net->net.kind == Net::kAEI, "not an AEI_Net handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(nchw_to_nhwc_launch(Xt, xt_dtype, p.x_in.p, p.x_in.dtype, B, 3, 256, 256, 3, 0, s), "Xt in");
+    check_msg(nchw_to_nhwc_launch(z_id, z_dtype, p.zid.p, p.zid.dtype, B, n.c_id, 1, 1, n.c_id, 0, s), "z_id in");
+    n.run_plan(p, s);
+    check_msg(nhwc_to_nchw_launch(p.y.p, p.y.dtype, 3, 0, Y, out_dtype, B, 3, 256, 256, s), "Y out");
+    write_attrs(n, p, attr_out, out_dtype, s);
+  });
+}
+
+int ghost_aei_encode(ghost_net_t* net, const void* X, int x_dtype, void* const* attr_out, int out_dtype, int B,
+                     void* stream) {
+  return guarded([&] {
+    require(net && X && attr_out, "null argument");
+    require(net->net.kind == Net::kAEI, "not an AEI_Net handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(nchw_to_nhwc_launch(X, x_dtype, p.x_in.p, p.x_in.dtype, B, 3, 256, 256, 3, 0, s), "X in");
+    n.run_plan(p, s, 0, n.encoder_ops);
+    write_attrs(n, p, attr_out, out_dtype, s);
+  });
+}
+
+int ghost_aei_swap_u8(ghost_net_t* net, const uint8_t* crops_bgr, const void* z_id, int z_dtype, int z_rows,
+                      uint8_t* out_bgr, int B, void* stream) {
+  return guarded([&] {
+    require(net && crops_bgr && z_id, "null argument");
+    require(net->net.kind == Net::kAEI, "not an AEI_Net handle");
+    require(z_rows == 1 || z_rows == B, "z_id must have 1 or B rows");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    const long long npix = static_cast<long long>(B) * 256 * 256;
+    // bf16 mode rounds once from fp32; the fp32 mode keeps full precision (core.py:13-26)
+    check_msg(preproc_u8_launch(crops_bgr, p.x_in.p, p.x_in.dtype, npix, 0, s), "preproc");
+    const size_t zb = (p.zid.dtype == kF32 ? 4 : 2) * static_cast<size_t>(n.c_id);
+    if (z_rows == B) {
+      check_msg(nchw_to_nhwc_launch(z_id, z_dtype, p.zid.p, p.zid.dtype, B, n.c_id, 1, 1, n.c_id, 0, s), "z_id in");
+    } else {
+      // torch.cat([source_emb]*bs) (faceshifter_run.py:15-16)
+      check_msg(nchw_to_nhwc_launch(z_id, z_dtype, p.zid.p, p.zid.dtype, 1, n.c_id, 1, 1, n.c_id, 0, s), "z_id in");
+      for (int filled = 1; filled < B;) {
+        const int cnt = filled < B - filled ? filled : B - filled;
+        check_cuda(cudaMemcpyAsync(static_cast<char*>(p.zid.p) + zb * filled, p.zid.p, zb * cnt,
+                                   cudaMemcpyDeviceToDevice, s),
+                   "z_id tile");
+        filled += cnt;
+      }
+    }
+    n.run_plan(p, s);
+    if (out_bgr) check_msg(postproc_u8_launch(p.y.p, p.y.dtype, out_bgr, npix, s), "postproc");
+  });
+}
+
+int ghost_net_y_nhwc(ghost_net_t* net, int B, void** ptr, int* dtype) {
+  return guarded([&] {
+    require(net && ptr && dtype, "null argument");
+    std::lock_guard<std::mutex> lk(net->mu);
+    ExecPlan& p = net->net.plan(B);
+    *ptr = p.y.p;
+    *dtype = p.y.dtype;
+  });
+}
+
+int ghost_arcface_forward(ghost_net_t* net, const void* x, int x_dtype, void* z, int z_dtype, int B, void* stream) {
+  return guarded([&] {
+    require(net && x && z, "null argument");
+    require(net->net.kind == Net::kArcFace, "not an iresnet handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(nchw_to_nhwc_launch(x, x_dtype, p.emb_in.p, p.emb_in.dtype, B, 3, 112, 112, 3, 0, s), "x in");
+    n.run_plan(p, s);
+    check_msg(nhwc_to_nchw_launch(p.emb_out, kF32, 512, 0, z, z_dtype, B, 512, 1, 1, s), "z out");
+  });
+}
+
+int ghost_arcface_embed_hwc(ghost_net_t* net, const void* src, int is_u8, void* z, int z_dtype, int B, void* stream) {
+  return guarded([&] {
+    require(net && src && z, "null argument");
+    require(net->net.kind == Net::kArcFace, "not an iresnet handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(arcface_preproc_launch(src, is_u8, p.emb_in.p, p.emb_in.dtype, B, s), "arcface preproc");
+    n.run_plan(p, s);
+    check_msg(nhwc_to_nchw_launch(p.emb_out, kF32, 512, 0, z, z_dtype, B, 512, 1, 1, s), "z out");
+  });
+}
+
+void ghost_net_destroy(ghost_net_t* net) { delete net; }
+
+int ghost_preproc_u8(const uint8_t* crops_bgr, void* dst, int dst_dtype, int B, int half_rounding, void* stream) {
+  return guarded([&] {
+    require(crops_bgr && dst && B > 0, "bad argument");
+    check_msg(preproc_u8_launch(crops_bgr, dst, dst_dtype, static_cast<long long>(B) * 65536, half_rounding, S(stream)),
+              "preproc");
+  });
+}
+
+int ghost_postproc_u8(const void* y, int y_dtype, uint8_t* dst, int B, void* stream) {
+  return guarded([&] {
+    require(y && dst && B > 0, "bad argument");
+    check_msg(postproc_u8_launch(y, y_dtype, dst, static_cast<long long>(B) * 65536, S(stream)), "postproc");
+  });
+}
+
+int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
+  return guarded([&] {
+    require(d, "null descriptor");
+    require(d->frames_in && d->frames_out && d->n_frames > 0 && d->H > 0 && d->W > 0, "bad frame batch");
+    require(d->n_faces >= 0, "bad face count");
+    require(d->n_faces == 0 || (d->crops && d->masks && d->tfm && d->face_frame && d->face_crop && d->face_mask),
+            "null face arrays");
+    require(d->mode == GHOST_PASTE_EXACT || d->mode == GHOST_PASTE_FLOAT, "bad paste mode");
+    cudaStream_t s = S(stream);
+    std::vector<PasteFace> faces(d->n_faces > 0 ? d->n_faces : 1);
+    std::vector<int> start(d->n_frames + 1, 0);
+    int prev = 0;
+    for (int i = 0; i < d->n_faces; ++i) {
+      const int f = d->face_frame[i];
+      require(f >= prev && f < d->n_frames, "face_frame must be non-decreasing and inside the frame batch");
+      require(d->face_crop[i] >= 0 && d->face_crop[i] < d->n_crops, "face_crop out of range");
+      require(d->face_mask[i] >= 0 && d->face_mask[i] < d->n_masks, "face_mask out of range");
+      prev = f;
+      start[f + 1]++;
+      paste_prepare_face(&faces[i], d->tfm + 6 * i, d->H, d->W, d->face_crop[i], d->face_mask[i]);
+    }
+    for (int f = 0; f < d->n_frames; ++f) start[f + 1] += start[f];
+    const size_t fb = faces.size() * sizeof(PasteFace), sb = start.size() * sizeof(int);
+    const size_t fb_al = (fb + 255) / 256 * 256;
+    char* scratch = static_cast<char*>(paste_scratch(fb_al + sb));
+    check_cuda(cudaMemcpyAsync(scratch, faces.data(), fb, cudaMemcpyHostToDevice, s), "faces upload");
+    check_cuda(cudaMemcpyAsync(scratch + fb_al, start.data(), sb, cudaMemcpyHostToDevice, s), "face index upload");
+    DeviceTables& t = resize_tables();
+    PasteParams p;
+    memset(&p, 0, sizeof(p));
+    p.crops = d->crops;
+    p.crop_kind = d->crop_kind;
+    p.masks = d->masks;
+    p.mask_f64 = d->mask_f64;
+    p.frames_in = d->frames_in;
+    p.frames_out = d->frames_out;
+    p.F = d->n_frames; p.H = d->H; p.W = d->W;
+    p.faces = reinterpret_cast<const PasteFace*>(scratch);
+    p.face_start = reinterpret_cast<const int*>(scratch + fb_al);
+    p.rs_idx = t.idx; p.rs_a0 = t.a0; p.rs_a1 = t.a1;
+    p.mode = d->mode;
+    check_msg(paste_back_launch(p, s), "paste_back");
+  });
+}
+
+}  // extern "C"

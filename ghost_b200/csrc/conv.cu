@@ -1,0 +1,260 @@
+#include "conv.cuh"
+
+#include <cudaTypedefs.h>
+#include <string.h>
+
+namespace ghost {
+
+Taps Taps::square(int k, int pad, int stride) {
+  Taps t;
+  t.n = k * k;
+  t.stride = stride;
+  for (int kh = 0; kh < k; ++kh)
+    for (int kw = 0; kw < k; ++kw) {
+      t.dh[kh * k + kw] = static_cast<short>(kh - pad);
+      t.dw[kh * k + kw] = static_cast<short>(kw - pad);
+    }
+  return t;
+}
+
+// ConvTranspose2d(k=4, s=2, p=1): out[2q+r] += in[q+d] * W[kh] with
+//   r=0: (kh=1, d=0), (kh=3, d=-1);   r=1: (kh=0, d=+1), (kh=2, d=0)
+// (from oh = 2*ih - 1 + kh, network/AEI_Net.py:30).  Tap order matches pack.cc::deconv_kidx.
+Taps Taps::deconv_phase(int r, int s) {
+  static const short d_of[2][2] = {{0, -1}, {1, 0}};
+  Taps t;
+  t.n = 4;
+  t.stride = 1;
+  for (int th = 0; th < 2; ++th)
+    for (int tw = 0; tw < 2; ++tw) {
+      t.dh[th * 2 + tw] = d_of[r][th];
+      t.dw[th * 2 + tw] = d_of[s][tw];
+    }
+  return t;
+}
+
+Taps Taps::point() {
+  Taps t;
+  t.n = 1;
+  t.stride = 1;
+  t.dh[0] = t.dw[0] = 0;
+  return t;
+}
+
+const char* encode_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                        const uint32_t* box, int swizzle_bytes) {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+    if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) return "cuTensorMapEncodeTiled entry point not found";
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  cuuint64_t gdims[5];
+  cuuint64_t gstr[4];
+  cuuint32_t gbox[5], estr[5];
+  for (int i = 0; i < rank; ++i) {
+    gdims[i] = dims[i];
+    gbox[i] = box[i];
+    estr[i] = 1;
+    if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
+  }
+  CUtensorMapSwizzle sw = swizzle_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdims, gstr, gbox, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled failed";
+  return nullptr;
+}
+
+namespace {
+
+void choose_box(int N, int Ho, int Wo, int* bw, int* bh, int* bn) {
+  double best = -1.0;
+  const long long total = static_cast<long long>(N) * Ho * Wo;
+  for (int w = 1; w <= Wo && w <= 128; ++w) {
+    for (int h = 1; h <= Ho && w * h <= 128; ++h) {
+      int n = 1;
+      if (w == Wo && h == Ho) {
+        n = 128 / (w * h);
+        if (n > N) n = N;
+        if (n < 1) n = 1;
+      }
+      const long long tiles = static_cast<long long>((Wo + w - 1) / w) * ((Ho + h - 1) / h) * ((N + n - 1) / n);
+      double eff = static_cast<double>(total) / (static_cast<double>(tiles) * 128.0);
+      eff += 1e-6 * w;  // tie-break: longer contiguous runs
+      if (eff > best) {
+        best = eff;
+        *bw = w;
+        *bh = h;
+        *bn = n;
+      }
+    }
+  }
+}
+
+int pow2_at_least(int v) {
+  int p = 32;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+}  // namespace
+
+const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
+                       const PackedW& w, const OutView& out, const Epilogue& epi, bool force_simt, int* err_word,
+                       const AadArgs* aad, int bn_hint) {
+  if (taps.n > kIgemmMaxTaps) return "lower_conv: too many taps";
+  if (w.K != taps.n * Cin) return "lower_conv: weight K does not match taps*Cin";
+  op->flops = 2.0 * in.N * Ho * Wo * static_cast<double>(w.Cout) * w.K;
+  const bool can_igemm = !force_simt && in.dtype == kBF16 && (Cin % 32 == 0) && (in.C % 8 == 0) && (c0 % 8 == 0) &&
+                         w.wb != nullptr && (taps.stride == 1 || (taps.stride == 2 && in.H % 2 == 0 && in.W % 2 == 0));
+  if (!can_igemm) {
+    if (aad) return "lower_conv: the fused AAD epilogue needs the tensor-core path";
+    if (!w.wf) return "lower_conv: fp32 weights missing for the CUDA-core path";
+    op->kind = LaunchOp::kSimt;
+    op->simt_dtype = in.dtype;
+    if (out.dtype != in.dtype) return "lower_conv: CUDA-core path needs matching in/out dtypes";
+    SimtConvParams& p = op->sc;
+    memset(&p, 0, sizeof(p));
+    p.in = in.p;
+    p.N = in.N; p.H = in.H; p.W = in.W; p.C = in.C;
+    p.c0 = c0; p.Cin = Cin;
+    p.stride = taps.stride;
+    p.ntaps = taps.n;
+    for (int i = 0; i < taps.n; ++i) { p.dh[i] = taps.dh[i]; p.dw[i] = taps.dw[i]; }
+    p.Ho = Ho; p.Wo = Wo;
+    p.w = w.wf;
+    p.Cout = w.Cout;
+    p.out = out.p;
+    p.o_sn = out.sn; p.o_sh = out.sh; p.o_sw = out.sw; p.o_off = out.off;
+    p.bias = w.bias;
+    p.act1 = epi.act1; p.slope = epi.slope; p.slope_c = epi.slope_c;
+    p.res = epi.res;
+    p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;
+    p.act2 = epi.act2;
+    return nullptr;
+  }
+
+  op->kind = LaunchOp::kIgemm;
+  IgemmParams& p = op->ig;
+  memset(&p, 0, sizeof(p));
+  p.kc = (Cin % 64 == 0) ? 64 : 32;
+  const int swz = p.kc * 2;
+  p.Nimg = in.N; p.Ho = Ho; p.Wo = Wo;
+  choose_box(in.N, Ho, Wo, &p.bw, &p.bh, &p.bn);
+  p.tiles_w = (Wo + p.bw - 1) / p.bw;
+  p.tiles_h = (Ho + p.bh - 1) / p.bh;
+  p.tiles_nb = (in.N + p.bn - 1) / p.bn;
+  p.ntaps = taps.n;
+  p.kc_per_tap = Cin / p.kc;
+  p.a_c0 = c0;
+  p.b_k0 = 0;
+  p.splits = 1;
+
+  // ---- activation tensor map
+  const uint64_t eb = 2;
+  if (taps.stride == 1) {
+    p.a_rank = 4;
+    const uint64_t dims[4] = {static_cast<uint64_t>(in.C), static_cast<uint64_t>(in.W), static_cast<uint64_t>(in.H),
+                              static_cast<uint64_t>(in.N)};
+    const uint64_t str[3] = {in.C * eb, static_cast<uint64_t>(in.W) * in.C * eb,
+                             static_cast<uint64_t>(in.H) * in.W * in.C * eb};
+    const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh),
+                             static_cast<uint32_t>(p.bn)};
+    if (const char* e = encode_tmap(&p.tmA, in.p, 4, dims, str, box, swz)) return e;
+    for (int i = 0; i < taps.n; ++i) {
+      p.tap_c[i] = 0;
+      p.tap_w[i] = taps.dw[i];
+      p.tap_p[i] = 0;
+      p.tap_h[i] = taps.dh[i];
+    }
+  } else {
+    // parity-split view: (2C | W/2 | 2 | H/2 | N); input pixel (2*hh+ph, 2*ww+pw), channel c lives at
+    // inner index pw*C + c.
+    p.a_rank = 5;
+    const uint64_t dims[5] = {static_cast<uint64_t>(2 * in.C), static_cast<uint64_t>(in.W / 2), 2,
+                              static_cast<uint64_t>(in.H / 2), static_cast<uint64_t>(in.N)};
+    const uint64_t str[4] = {2 * in.C * eb, static_cast<uint64_t>(in.W) * in.C * eb,
+                             2 * static_cast<uint64_t>(in.W) * in.C * eb,
+                             static_cast<uint64_t>(in.H) * in.W * in.C * eb};
+    const uint32_t box[5] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.bw), 1,
+                             static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
+    if (const char* e = encode_tmap(&p.tmA, in.p, 5, dims, str, box, swz)) return e;
+    for (int i = 0; i < taps.n; ++i) {
+      const int dw = taps.dw[i], dh = taps.dh[i];
+      p.tap_c[i] = static_cast<short>((dw & 1) * in.C);
+      p.tap_w[i] = static_cast<short>(dw >> 1);  // arithmetic shift: floor(dw / 2)
+      p.tap_p[i] = static_cast<short>(dh & 1);
+      p.tap_h[i] = static_cast<short>(dh >> 1);
+    }
+  }
+
+  // ---- N tiling
+  if (aad) {
+    const int cn = aad->c_x < 128 ? aad->c_x : 128;
+    if (aad->c_x % cn || cn % 16) return "lower_conv: AAD c_x must be a multiple of 16";
+    p.BN = 2 * cn;
+    p.tiles_n = aad->c_x / cn;
+    p.n_valid = 2 * aad->c_x;
+    if (w.rows_pad < 2 * aad->c_x) return "lower_conv: AAD weights must hold 2*c_x rows";
+  } else {
+    int bn_ = bn_hint;
+    if (!bn_) {
+      const int cpad = (w.Cout + 15) / 16 * 16;
+      bn_ = cpad < 256 ? cpad : 256;
+      const long long tiles_m = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
+      while (bn_ > 64 && bn_ % 32 == 0 && tiles_m * ((w.Cout + bn_ - 1) / bn_) < 148) bn_ /= 2;
+    }
+    p.BN = bn_;
+    p.tiles_n = (w.Cout + p.BN - 1) / p.BN;
+    p.n_valid = w.Cout;
+    if (w.rows_pad < p.tiles_n * p.BN) return "lower_conv: packed weight rows are not padded to the N tile";
+  }
+  {
+    const uint64_t dims[2] = {static_cast<uint64_t>(w.K), static_cast<uint64_t>(w.rows_pad)};
+    const uint64_t str[1] = {static_cast<uint64_t>(w.K) * eb};
+    const uint32_t box[2] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.BN)};
+    if (const char* e = encode_tmap(&p.tmB, w.wb, 2, dims, str, box, swz)) return e;
+  }
+  const int stage_bytes = (128 + p.BN) * p.kc * 2;
+  int stages = (220 * 1024) / stage_bytes;
+  if (stages > 8) stages = 8;
+  const int num_kb = p.ntaps * p.kc_per_tap;
+  if (stages > num_kb + 1 && num_kb >= 2) stages = num_kb + 1;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  p.tmem_cols = pow2_at_least(2 * p.BN);
+
+  // ---- epilogue
+  p.out = out.p;
+  p.o_sn = out.sn; p.o_sh = out.sh; p.o_sw = out.sw; p.o_off = out.off;
+  p.out_f32 = out.dtype == kF32;
+  p.bias = w.bias;
+  p.err = err_word;
+  if (aad) {
+    if (out.dtype != kBF16) return "lower_conv: AAD output must be bf16";
+    p.mode = kModeAAD;
+    p.h = reinterpret_cast<const __nv_bfloat16*>(aad->h);
+    p.c_x = aad->c_x;
+    p.ncpar = aad->ncpar;
+    p.wh_fold = aad->wh_fold;
+    p.bh_fold = aad->bh_fold;
+    p.mask = nullptr;
+    if (!w.bias) return "lower_conv: AAD needs the gamma/beta bias vector";
+  } else {
+    p.mode = kModeLinear;
+    p.act1 = epi.act1; p.slope = epi.slope; p.slope_c = epi.slope_c;
+    p.res = reinterpret_cast<const __nv_bfloat16*>(epi.res);
+    p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;
+    p.act2 = epi.act2;
+    if (out.dtype == kBF16 && w.Cout % 16 == 0 && ((out.off % 8) || (out.sw % 8) || (out.sh % 8) || (out.sn % 8)))
+      return "lower_conv: bf16 output view must be 16-byte aligned";
+  }
+  return nullptr;
+}
+
+}  // namespace ghost

@@ -1,0 +1,107 @@
+// Host-side convolution descriptors: one ConvOp describes a conv / conv-transpose
+// phase / linear layer and is lowered either to the tcgen05 implicit-GEMM kernel
+// (bf16 mode) or to the CUDA-core kernel (fp32 mode, Cin not a multiple of 32).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "igemm.cuh"
+#include "simt.cuh"
+
+namespace ghost {
+
+// Dense NHWC activation tensor (C = pixel stride in elements).
+struct Act {
+  void* p = nullptr;
+  int N = 0, H = 0, W = 0, C = 0;
+  int dtype = kBF16;
+  size_t elems() const { return static_cast<size_t>(N) * H * W * C; }
+  size_t bytes() const { return elems() * (dtype == kF32 ? 4 : 2); }
+};
+
+// Geometry of the sliding window: input position = stride * o + (dh, dw).
+struct Taps {
+  int n = 0;
+  int stride = 1;
+  short dh[kIgemmMaxTaps], dw[kIgemmMaxTaps];
+  static Taps square(int k, int pad, int stride);
+  static Taps deconv_phase(int r, int s);  // ConvTranspose2d k4 s2 p1, output phase (r, s)
+  static Taps point();
+};
+
+// Weights of one op, already in the packed [Cout][tap][Cin] order, resident on the device.
+struct PackedW {
+  const __nv_bfloat16* wb = nullptr;  // [rows_pad][K] bf16 (igemm)
+  const float* wf = nullptr;          // [Cout][K] fp32 (CUDA-core path)
+  const float* bias = nullptr;        // [rows_pad] fp32 or null
+  int Cout = 0, rows_pad = 0, K = 0;
+};
+
+struct Epilogue {
+  int act1 = kActNone;
+  float slope = 0.f;
+  const float* slope_c = nullptr;
+  const void* res = nullptr;  // residual, same dtype as the output
+  long long r_sn = 0, r_sh = 0, r_sw = 0, r_off = 0;
+  int act2 = kAct2None;
+};
+
+struct OutView {
+  void* p = nullptr;
+  long long sn = 0, sh = 0, sw = 0, off = 0;  // element strides over (n, oh, ow) + constant offset
+  int dtype = kBF16;                          // kBF16 / kF32
+  static OutView dense(const Act& a, int c_off = 0) {
+    OutView o;
+    o.p = a.p;
+    o.sn = static_cast<long long>(a.H) * a.W * a.C;
+    o.sh = static_cast<long long>(a.W) * a.C;
+    o.sw = a.C;
+    o.off = c_off;
+    o.dtype = a.dtype;
+    return o;
+  }
+  // ConvTranspose2d output phase (r, s): pixel (2q+r, 2p+s) of a tensor twice the grid size
+  static OutView deconv_phase(const Act& a, int r, int s, int c_off = 0) {
+    OutView o;
+    o.p = a.p;
+    o.sn = static_cast<long long>(a.H) * a.W * a.C;
+    o.sh = 2LL * a.W * a.C;
+    o.sw = 2LL * a.C;
+    o.off = (static_cast<long long>(r) * a.W + s) * a.C + c_off;
+    o.dtype = a.dtype;
+    return o;
+  }
+};
+
+struct AadArgs {  // only for the fused AAD epilogue
+  const void* h = nullptr;
+  int c_x = 0;
+  const float4* ncpar = nullptr;
+  const float* wh_fold = nullptr;
+  const float* bh_fold = nullptr;
+};
+
+// A lowered, launch-ready op.
+struct LaunchOp {
+  enum Kind { kIgemm, kSimt } kind = kIgemm;
+  IgemmParams ig;
+  SimtConvParams sc;
+  int simt_dtype = kBF16;
+  std::string name;
+  double flops = 0.0;
+  const char* launch(cudaStream_t s) const {
+    return kind == kIgemm ? igemm_launch(ig, s) : simt_conv_launch(sc, simt_dtype, s);
+  }
+};
+
+// Lower a convolution.  `in` is read on channels [c0, c0+Cin); the output grid is Ho x Wo per image.
+// force_simt selects the CUDA-core kernel (fp32 mode).  Returns nullptr on success.
+const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
+                       const PackedW& w, const OutView& out, const Epilogue& epi, bool force_simt, int* err_word,
+                       const AadArgs* aad = nullptr, int bn_hint = 0);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
+const char* encode_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                        const uint32_t* box, int swizzle_bytes);
+
+}  // namespace ghost

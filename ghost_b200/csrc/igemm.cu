@@ -357,7 +357,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   // ------------------------------ teardown ------------------------------------
   tc_fence_before();
   __syncthreads();
-  if (abort_flag && threadIdx.x == 0 && p.err) atomicExch(p.err, 1);
+  if (abort_flag && threadIdx.x == 0 && p.err) {
+    *reinterpret_cast<volatile int*>(p.err) = 1;  // pinned, host-mapped word
+    __threadfence_system();
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);

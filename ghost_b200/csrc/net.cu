@@ -1,0 +1,188 @@
+#include "net.cuh"
+
+#include <math.h>
+#include <string.h>
+
+namespace ghost {
+
+void fail(int code, const std::string& msg) { throw GhostError(code, msg); }
+void check_cuda(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) fail(-3, std::string(what) + ": " + cudaGetErrorString(e));
+}
+void check_msg(const char* err, const std::string& where) {
+  if (err) fail(-3, where + ": " + err);
+}
+
+// ------------------------------------------------------------------ DevPool
+DevPool::~DevPool() {
+  for (void* p : ptrs_) cudaFree(p);
+}
+void* DevPool::alloc(size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  bytes = (bytes + 255) / 256 * 256;
+  void* p = nullptr;
+  check_cuda(cudaMalloc(&p, bytes), "cudaMalloc");
+  check_cuda(cudaMemset(p, 0, bytes), "cudaMemset");
+  ptrs_.push_back(p);
+  total_ += bytes;
+  return p;
+}
+float* DevPool::upload(const std::vector<float>& v) {
+  float* d = alloc_n<float>(v.size());
+  check_cuda(cudaMemcpy(d, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice), "upload");
+  return d;
+}
+static inline uint16_t f2bf(float f) {  // round-to-nearest-even, NaN preserved
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return static_cast<uint16_t>(u >> 16);
+}
+__nv_bfloat16* DevPool::upload_bf16(const std::vector<float>& v) {
+  std::vector<uint16_t> h(v.size());
+  for (size_t i = 0; i < v.size(); ++i) h[i] = f2bf(v[i]);
+  __nv_bfloat16* d = alloc_n<__nv_bfloat16>(v.size());
+  check_cuda(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice), "upload_bf16");
+  return d;
+}
+
+ExecPlan::~ExecPlan() {
+  if (graph) cudaGraphExecDestroy(graph);
+}
+
+// ------------------------------------------------------------------ Net basics
+Net::Net(Kind k, std::string bb, int nb, int cid, int mode)
+    : kind(k), backbone(std::move(bb)), num_blocks(nb), c_id(cid), act_dtype(mode == 0 ? kF32 : kBF16) {}
+Net::~Net() {}
+
+void Net::set_weight(const std::string& key, const float* data, const int64_t* shape, int ndim) {
+  HostTensor t;
+  t.shape.assign(shape, shape + ndim);
+  const int64_t n = t.numel();
+  t.data.assign(data, data + n);
+  w_[key] = std::move(t);
+  finalized = false;
+}
+
+const HostTensor& Net::W(const std::string& key) const {
+  auto it = w_.find(key);
+  if (it == w_.end()) fail(-2, "missing state_dict entry: " + key);
+  return it->second;
+}
+
+PackedW Net::pack(const std::vector<float>& rows, int Cout, int K, const std::vector<float>* bias, bool need_f32,
+                  bool need_bf16) {
+  PackedW p;
+  p.Cout = Cout;
+  p.K = K;
+  p.rows_pad = (Cout + 255) / 256 * 256;
+  if (need_f32) p.wf = wpool_.upload(rows);
+  if (need_bf16) {
+    std::vector<float> padded(static_cast<size_t>(p.rows_pad) * K, 0.f);
+    memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
+    p.wb = wpool_.upload_bf16(padded);
+  }
+  if (bias) {
+    std::vector<float> b(p.rows_pad, 0.f);
+    memcpy(b.data(), bias->data(), bias->size() * sizeof(float));
+    p.bias = wpool_.upload(b);
+  }
+  return p;
+}
+
+void Net::finalize() {
+  if (finalized) return;
+  plans_.clear();
+  packed_.clear();
+  vecs_.clear();
+  scalars_.clear();
+  aad_.clear();
+  if (kind == kAEI)
+    finalize_aei();
+  else
+    finalize_arcface();
+  check_cuda(cudaDeviceSynchronize(), "finalize");
+  finalized = true;
+}
+
+ExecPlan& Net::plan(int B) {
+  if (!finalized) fail(-1, "network used before ghost_net_finalize");
+  if (B <= 0) fail(-1, "batch size must be positive");
+  auto it = plans_.find(B);
+  if (it != plans_.end()) return *it->second;
+  std::unique_ptr<ExecPlan> p(new ExecPlan());
+  p->B = B;
+  p->err_word = device_err_word();
+  if (kind == kAEI)
+    build_aei(*p);
+  else
+    build_arcface(*p);
+  for (auto& op : p->ops) p->flops += op.flops;
+  ExecPlan& ref = *p;
+  plans_[B] = std::move(p);
+  return ref;
+}
+
+void Net::run_plan(ExecPlan& p, cudaStream_t s, size_t first, size_t last) {
+  if (last > p.ops.size()) last = p.ops.size();
+  const bool whole = first == 0 && last == p.ops.size();
+  if (use_graph && whole) {
+    if (!p.graph && !p.graph_tried) {
+      p.graph_tried = true;
+      // warm every kernel once (module load, attribute setup) before capturing
+      for (auto& op : p.ops) check_msg(op.run(s), op.name);
+      check_cuda(cudaStreamSynchronize(s), "graph warm-up");
+      cudaStream_t cs;
+      check_cuda(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking), "capture stream");
+      cudaGraph_t g = nullptr;
+      check_cuda(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal), "begin capture");
+      const char* err = nullptr;
+      std::string where;
+      for (auto& op : p.ops) {
+        err = op.run(cs);
+        if (err) {
+          where = op.name;
+          break;
+        }
+      }
+      cudaError_t ce = cudaStreamEndCapture(cs, &g);
+      if (err) {
+        if (g) cudaGraphDestroy(g);
+        cudaStreamDestroy(cs);
+        check_msg(err, where);
+      }
+      check_cuda(ce, "end capture");
+      check_cuda(cudaGraphInstantiate(&p.graph, g, 0), "graph instantiate");
+      cudaGraphDestroy(g);
+      cudaStreamDestroy(cs);
+    }
+    if (p.graph) {
+      check_cuda(cudaGraphLaunch(p.graph, s), "graph launch");
+      return;
+    }
+  }
+  for (size_t i = first; i < last; ++i) check_msg(p.ops[i].run(s), p.ops[i].name);
+}
+
+// One pinned, device-mapped word per process: a kernel whose pipeline wait times out sets it, the
+// host reads it (without synchronising) at the entry of every API call, so a device-side failure
+// is reported by the next call at the latest and by ghost_check_errors() after a synchronize.
+static int* g_err_host = nullptr;
+int* device_err_word() {
+  if (!g_err_host) {
+    check_cuda(cudaHostAlloc(reinterpret_cast<void**>(&g_err_host), sizeof(int), cudaHostAllocMapped), "err word");
+    *g_err_host = 0;
+  }
+  int* d = nullptr;
+  check_cuda(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), g_err_host, 0), "err word map");
+  return d;
+}
+void check_device_errors() {
+  if (g_err_host && *reinterpret_cast<volatile int*>(g_err_host)) {
+    *g_err_host = 0;
+    fail(-4, "device-side pipeline timeout in the tcgen05 conv kernel");
+  }
+}
+
+}  // namespace ghost

@@ -1,0 +1,127 @@
+// Host-side model plans: weight store, packing (BN fold, tap-major repack),
+// activation buffers, the op list of one forward and its CUDA graph.
+#pragma once
+#include <functional>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "conv.cuh"
+#include "paste.cuh"
+
+namespace ghost {
+
+struct GhostError : std::runtime_error {
+  int code;
+  GhostError(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+[[noreturn]] void fail(int code, const std::string& msg);
+void check_cuda(cudaError_t e, const char* what);
+void check_msg(const char* err, const std::string& where);  // nullptr = ok, else throws GHOST_ERR_CUDA
+
+int* device_err_word();
+void check_device_errors();
+
+struct HostTensor {
+  std::vector<float> data;
+  std::vector<int64_t> shape;
+  int64_t numel() const {
+    int64_t n = 1;
+    for (auto s : shape) n *= s;
+    return n;
+  }
+};
+
+// Owns device allocations.
+class DevPool {
+ public:
+  ~DevPool();
+  void* alloc(size_t bytes);
+  template <typename T>
+  T* alloc_n(size_t n) {
+    return reinterpret_cast<T*>(alloc(n * sizeof(T)));
+  }
+  float* upload(const std::vector<float>& v);
+  __nv_bfloat16* upload_bf16(const std::vector<float>& v);
+  size_t total_bytes() const { return total_; }
+
+ private:
+  std::vector<void*> ptrs_;
+  size_t total_ = 0;
+};
+
+struct Op {
+  std::string name;
+  std::function<const char*(cudaStream_t)> run;
+  double flops = 0.0;
+};
+
+// A conv's weights in both packings.
+struct ConvWeights {
+  PackedW pw;
+};
+
+// One executable forward for a fixed batch size.
+struct ExecPlan {
+  int B = 0;
+  DevPool pool;
+  std::vector<Op> ops;
+  cudaGraphExec_t graph = nullptr;
+  bool graph_tried = false;
+  int* err_word = nullptr;
+  // boundary buffers
+  Act x_in;          // NHWC-3 network input
+  Act zid;           // [B,1,1,c_id]
+  Act y;             // NHWC-3 generator output
+  Act attr[8];       // z_attr1..8 (NHWC); for unet they are the concat buffers
+  Act emb_in;        // arcface: [B,112,112,3]
+  float* emb_out = nullptr;  // arcface: [B,512] fp32
+  void* stage = nullptr;     // staging for broadcast z_id
+  double flops = 0.0;
+  ~ExecPlan();
+};
+
+class Net {
+ public:
+  enum Kind { kAEI, kArcFace };
+  Net(Kind kind, std::string backbone, int num_blocks, int c_id, int mode);
+  ~Net();
+
+  void set_weight(const std::string& key, const float* data, const int64_t* shape, int ndim);
+  void finalize();
+  ExecPlan& plan(int B);
+  void run_plan(ExecPlan& p, cudaStream_t s, size_t first_op = 0, size_t last_op = static_cast<size_t>(-1));
+
+  Kind kind;
+  std::string backbone;
+  int num_blocks, c_id;
+  int act_dtype;  // kF32 or kBF16
+  bool use_graph = false;
+  bool finalized = false;
+  size_t encoder_ops = 0;  // ops [0, encoder_ops) compute the attribute maps
+
+ private:
+  const HostTensor& W(const std::string& key) const;
+  bool has(const std::string& key) const { return w_.count(key) != 0; }
+  // packing
+  PackedW pack(const std::vector<float>& w_rows, int Cout, int K, const std::vector<float>* bias, bool need_f32,
+               bool need_bf16);
+  void build_aei(ExecPlan& p);
+  void build_arcface(ExecPlan& p);
+  void finalize_aei();
+  void finalize_arcface();
+
+  std::map<std::string, HostTensor> w_;
+  DevPool wpool_;
+  std::map<std::string, PackedW> packed_;       // by logical layer name
+  std::map<std::string, float*> vecs_;          // small fp32 vectors (conv_h weights, prelu slopes, ...)
+  std::map<std::string, float> scalars_;
+  std::map<int, std::unique_ptr<ExecPlan>> plans_;
+  int zfc_cols_ = 0;
+  struct AadInfo { std::string name; int c_x, c_attr, off_gamma, off_beta; };
+  std::map<std::string, AadInfo> aad_;
+};
+
+}  // namespace ghost

@@ -1,0 +1,150 @@
+/*
+ * ghost_b200 -- C ABI of the B200-native GHOST face-swap inference hot path.
+ *
+ * Every entry point takes plain pointers and sizes; device pointers are raw CUDA
+ * device addresses (tensor.data_ptr()), `stream` is a cudaStream_t passed as void*.
+ * All calls are asynchronous on `stream` unless stated otherwise and return
+ * 0 on success or a negative ghost_status; ghost_last_error() gives the message
+ * of the last failure on the calling thread.  There is no CPU fallback.
+ *
+ * Reference interfaces replaced (paths relative to the postworthy/ghost tree):
+ *   network/AEI_Net.py:143-159               AEI_Net.__init__/forward/get_attr
+ *   arcface_model/iresnet.py (un-vendored)   iresnet100(fp16=False).forward
+ *   utils/inference/core.py:13-26            transform_target_to_torch
+ *   utils/inference/faceshifter_run.py:5-23  faceshifter_batch
+ *   utils/inference/image_processing.py:23-48,51-77   normalize_and_torch(_batch), get_final_image
+ *   utils/inference/video_processing.py:191-243       get_final_video (compositing only)
+ */
+#ifndef GHOST_B200_H_
+#define GHOST_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GHOST_B200_VERSION 100
+
+typedef enum {
+  GHOST_OK = 0,
+  GHOST_ERR_INVALID = -1, /* bad argument / unsupported configuration */
+  GHOST_ERR_WEIGHTS = -2, /* missing or mis-shaped state_dict entry */
+  GHOST_ERR_CUDA = -3,    /* CUDA runtime / driver error */
+  GHOST_ERR_KERNEL = -4   /* device-side pipeline timeout (a kernel bug, never ignored) */
+} ghost_status;
+
+/* element types of buffers crossing the ABI */
+typedef enum { GHOST_F32 = 0, GHOST_BF16 = 1, GHOST_F16 = 2, GHOST_U8 = 3 } ghost_dtype;
+
+/* arithmetic mode of a network: GHOST_F32 = CUDA-core fp32 correctness mode (1e-4 contract),
+ * GHOST_BF16 = tcgen05 bf16 x bf16 -> fp32 production mode (1e-2 contract). */
+
+typedef struct ghost_net ghost_net_t;
+
+int ghost_version(void);
+const char* ghost_last_error(void);
+/* Returns GHOST_ERR_KERNEL if any kernel launched so far reported a device-side pipeline timeout
+ * (meaningful after the caller synchronised the stream); every other entry point performs the same check. */
+int ghost_check_errors(void);
+
+/* ---- AEI_Net(backbone, num_blocks, c_id)  (network/AEI_Net.py:143-151).
+ * backbone: "unet" or "linknet" ("resnet" -> GHOST_ERR_INVALID). */
+int ghost_aei_create(ghost_net_t** out, const char* backbone, int num_blocks, int c_id, int mode);
+
+/* ---- iresnet100(fp16=False) (inference.py:33-36) */
+int ghost_arcface_create(ghost_net_t** out, int mode);
+
+/* Hand over one state_dict entry under the reference's key name (fp32, host memory, contiguous).
+ * The data is copied; unknown keys are rejected at finalize time only if a required key is missing. */
+int ghost_net_set_weight(ghost_net_t* net, const char* ref_key, const float* host_data, const int64_t* shape,
+                         int ndim);
+
+/* Fold BatchNorm, repack into kernel layouts, upload.  Synchronous. */
+int ghost_net_finalize(ghost_net_t* net);
+
+/* Y, attr = G(Xt, z_id)  (network/AEI_Net.py:153-156).
+ *   Xt   [B,3,256,256] NCHW contiguous, xt_dtype in {F32,BF16,F16}, RGB in [-1,1]
+ *   z_id [B,c_id] (or [B,1,c_id]) same set of dtypes
+ *   Y    [B,3,256,256] NCHW out_dtype in {F32,BF16,F16}
+ *   attr_out: NULL, or 8 device pointers (each may be NULL) receiving z_attr1..8 in NCHW out_dtype */
+int ghost_aei_forward(ghost_net_t* net, const void* Xt, int xt_dtype, const void* z_id, int z_dtype, void* Y,
+                      void* const* attr_out, int out_dtype, int B, void* stream);
+
+/* attr = G.get_attr(X)  (network/AEI_Net.py:158-159) */
+int ghost_aei_encode(ghost_net_t* net, const void* X, int x_dtype, void* const* attr_out, int out_dtype, int B,
+                     void* stream);
+
+/* Fused inference entry (core.py:13-26 + faceshifter_run.py:5-23 with the bounce through the host removed):
+ *   crops_bgr [B,256,256,3] uint8 BGR (device) -> normalise -> G -> optional uint8 BGR [B,256,256,3] (device).
+ *   z_id: [1,c_id] (broadcast, as faceshifter_batch tiles source_emb) when z_rows == 1, else [B,c_id].
+ *   out_bgr may be NULL when only the on-device Y (ghost_net_y_nhwc) is wanted by the paste-back. */
+int ghost_aei_swap_u8(ghost_net_t* net, const uint8_t* crops_bgr, const void* z_id, int z_dtype, int z_rows,
+                      uint8_t* out_bgr, int B, void* stream);
+
+/* Device pointer + dtype of the NHWC-3 generator output of the last forward with batch B (valid until the next call). */
+int ghost_net_y_nhwc(ghost_net_t* net, int B, void** ptr, int* dtype);
+
+/* z = netArc(x), x [B,3,112,112] NCHW -> z [B,512], not normalised (core.py:45,54). */
+int ghost_arcface_forward(ghost_net_t* net, const void* x, int x_dtype, void* z, int z_dtype, int B, void* stream);
+
+/* normalize_and_torch(_batch) + F.interpolate(0.5, bilinear, align_corners=True) + netArc in one call:
+ * src [B,224,224,3] RGB HWC, uint8 (is_u8=1, divided by 255) or float32 in [0,1] (device). */
+int ghost_arcface_embed_hwc(ghost_net_t* net, const void* src, int is_u8, void* z, int z_dtype, int B, void* stream);
+
+/* Capture the forward of batch size B into a CUDA graph (optional; replayed by later calls). */
+int ghost_net_enable_graph(ghost_net_t* net, int enable);
+
+/* number of kernel launches one forward of batch B issues, and its dense FLOPs (for bench accounting) */
+int ghost_net_stats(ghost_net_t* net, int B, int* launches, double* flops);
+
+void ghost_net_destroy(ghost_net_t* net);
+
+/* ---- standalone conversions (device buffers) */
+int ghost_preproc_u8(const uint8_t* crops_bgr, void* dst_nhwc3, int dst_dtype, int B, int half_rounding, void* stream);
+int ghost_postproc_u8(const void* y_nhwc3, int y_dtype, uint8_t* dst_bgr, int B, void* stream);
+
+/* ---- paste-back (image_processing.py:51-77 exact mode; video_processing.py:212-233 float mode) */
+typedef enum { GHOST_PASTE_EXACT = 0, GHOST_PASTE_FLOAT = 1 } ghost_paste_mode;
+typedef enum { GHOST_CROP_U8_BGR = 0, GHOST_CROP_Y_BF16 = 1, GHOST_CROP_Y_F32 = 2 } ghost_crop_kind;
+
+typedef struct {
+  const void* crops;        /* device: [n_crops,256,256,3] u8 BGR, or NHWC-3 generator output (RGB, [-1,1]) */
+  int crop_kind;            /* ghost_crop_kind */
+  int n_crops;
+  const void* masks;        /* device: [n_masks,224,224] float64 (mask_f64=1) or float32 */
+  int mask_f64;
+  int n_masks;
+  const uint8_t* frames_in; /* device: [n_frames,H,W,3] u8 BGR */
+  uint8_t* frames_out;      /* device: [n_frames,H,W,3]; may alias frames_in */
+  int n_frames, H, W;
+  int n_faces;
+  const double* tfm;        /* host: [n_faces][2][3] frame->224-crop affines (tfm_arrays) */
+  const int* face_frame;    /* host: [n_faces] frame index of each face, non-decreasing; faces of one frame
+                               compose in list order */
+  const int* face_crop;     /* host: [n_faces] crop index */
+  const int* face_mask;     /* host: [n_faces] mask index */
+  int mode;                 /* ghost_paste_mode */
+} ghost_paste_desc;
+
+int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
+
+/* ---- single-op entry points used by the kernel-level parity tests (tests/test_kernels_gpu.py).
+ * conv: NHWC activations (dtype = mode); weights fp32 on the host in the reference layout:
+ * kind 0 = nn.Conv2d(k,stride,pad) weight [Cout][Cin][k][k], kind 1 = nn.ConvTranspose2d(k=4,s=2,p=1) weight
+ * [Cin][Cout][4][4].  act: 0 none, 1 leaky(slope), 3 relu.  mode GHOST_F32 / GHOST_BF16.  Synchronous. */
+int ghost_test_conv(const void* x_nhwc, int N, int H, int W, int Cin, const float* w_host, const float* bias_host,
+                    int Cout, int kind, int k, int stride, int pad, int act, float slope, void* y_nhwc, int mode,
+                    int bn_hint, void* stream);
+/* AADLayer + ReLU on NHWC tensors (network/AADLayer.py:20-38): weights on the host in reference layout. */
+int ghost_test_aad(const void* h_nhwc, const void* zattr_nhwc, const float* zid_host, int N, int H, int W, int c_x,
+                   int c_attr, int c_id, const float* conv1_w, const float* conv1_b, const float* conv2_w,
+                   const float* conv2_b, const float* fc1_w, const float* fc1_b, const float* fc2_w,
+                   const float* fc2_b, const float* convh_w, float convh_b, void* out_nhwc, int mode, void* stream);
+const char* ghost_test_last_error(void);
+int ghost_test_upsample2x(const void* x_nhwc, void* y_nhwc, int dtype, int N, int H, int W, int C, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GHOST_B200_H_ */
