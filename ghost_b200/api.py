@@ -1,0 +1,552 @@
+"""Host-side mirror of the reference's operator interface for the face-swap hot path.
+
+Same names, argument meaning and error behaviour as the reference (postworthy/ghost):
+
+    AEI_Net(backbone, num_blocks=2, c_id=256).forward(Xt, z_id) -> (Y, attr)   network/AEI_Net.py:143-159
+    iresnet100(fp16=False)(x[B,3,112,112]) -> z_id[B,512]                        arcface_model/iresnet.py (un-vendored)
+    transform_target_to_torch(resized_frs, half=True)                           utils/inference/core.py:13-26
+    faceshifter_batch(source_emb, target, G) -> uint8 BGR [B,256,256,3]         utils/inference/faceshifter_run.py:5-23
+    normalize_and_torch(_batch)                                                 utils/inference/image_processing.py:23-48
+    get_final_image(final_frames, crop_frames, full_frame, tfm_arrays, handler) utils/inference/image_processing.py:51-77
+    get_final_video(final_frames, crop_frames, full_frames, tfm_array, ...)     utils/inference/video_processing.py:191-243
+
+Everything numerical runs in the CUDA library behind include/ghost_b200.h; torch is used for
+device memory, streams and dtype bookkeeping only.  There is no CPU path: tensors must live on
+a CUDA device and the library must be built, otherwise the call raises.
+"""
+import ctypes as C
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import _lib
+from . import weights as _w
+
+_DT = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16, torch.float16: _lib.F16, torch.uint8: _lib.U8}
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _require_cuda(t, name):
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor, got %s" % (name, type(t).__name__))
+    if not t.is_cuda:
+        raise ValueError("%s must be a CUDA tensor (ghost_b200 has no CPU path)" % name)
+
+
+class _Net(object):
+    """Weight store + lazily created device plans (one C handle per (device, arithmetic mode))."""
+
+    _kind = None
+
+    def __init__(self, spec, seed):
+        self._spec = spec
+        self._sd = _w.init_state_dict(spec, seed)
+        self._dtype = torch.float32
+        self._device = None
+        self._handles = {}
+        self._graph = False
+        self.training = False
+
+    # ---- nn.Module-like surface used by the reference's call sites (inference.py:26-36)
+    def eval(self):
+        self.training = False
+        return self
+
+    def train(self, mode=True):
+        if mode:
+            raise NotImplementedError("ghost_b200 implements the inference path only (eval-mode BatchNorm)")
+        return self.eval()
+
+    def requires_grad_(self, flag=False):
+        if flag:
+            raise NotImplementedError("ghost_b200 implements the inference path only")
+        return self
+
+    def half(self):
+        self._dtype = torch.float16
+        return self
+
+    def bfloat16(self):
+        self._dtype = torch.bfloat16
+        return self
+
+    def float(self):
+        self._dtype = torch.float32
+        return self
+
+    def cuda(self, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
+        self._device = torch.device("cuda", torch.cuda.current_device() if device is None else
+                                    (device if isinstance(device, int) else torch.device(device).index or 0))
+        return self
+
+    def to(self, *args, **kwargs):
+        for a in list(args) + list(kwargs.values()):
+            if isinstance(a, torch.dtype):
+                if a not in (torch.float32, torch.float16, torch.bfloat16):
+                    raise TypeError("unsupported dtype %s" % a)
+                self._dtype = a
+            elif isinstance(a, (str, torch.device)):
+                d = torch.device(a)
+                if d.type != "cuda":
+                    raise ValueError("ghost_b200 modules live on CUDA devices only")
+                self.cuda(d.index)
+        return self
+
+    def cpu(self):
+        raise ValueError("ghost_b200 modules live on CUDA devices only (no CPU fallback)")
+
+    @property
+    def dtype(self):
+        return self._dtype
+
+    def state_dict(self):
+        return OrderedDict((k, v.clone()) for k, v in self._sd.items())
+
+    def load_state_dict(self, sd, strict=True):
+        missing = [k for k in self._spec if k not in sd]
+        unexpected = [k for k in sd if k not in self._spec]
+        if strict and (missing or unexpected):
+            raise RuntimeError("Error(s) in loading state_dict: missing keys %s, unexpected keys %s" %
+                               (missing[:8], unexpected[:8]))
+        new = OrderedDict()
+        for k, (shape, _) in self._spec.items():
+            if k not in sd:
+                new[k] = self._sd[k]
+                continue
+            v = sd[k].detach().to("cpu")
+            if tuple(v.shape) != tuple(shape):
+                raise RuntimeError("size mismatch for %s: expected %s, got %s" % (k, tuple(shape), tuple(v.shape)))
+            new[k] = v.to(torch.int64) if k.endswith("num_batches_tracked") else v.to(torch.float32).contiguous()
+        self._sd = new
+        self._drop_handles()
+        return self
+
+    def enable_graph(self, enable=True):
+        """Replay the whole forward as one CUDA graph per batch size."""
+        self._graph = bool(enable)
+        lib = _lib.load()
+        for h in self._handles.values():
+            _lib.check(lib.ghost_net_enable_graph(h, int(self._graph)))
+        return self
+
+    def _drop_handles(self):
+        if self._handles:
+            lib = _lib.load()
+            torch.cuda.synchronize()
+            for h in self._handles.values():
+                lib.ghost_net_destroy(h)
+        self._handles = {}
+
+    def __del__(self):
+        try:
+            self._drop_handles()
+        except Exception:
+            pass
+
+    def _mode(self):
+        return _lib.F32 if self._dtype == torch.float32 else _lib.BF16
+
+    def _create(self, lib, out, mode):
+        raise NotImplementedError
+
+    def _handle(self, device):
+        lib = _lib.load()
+        key = (device.index, self._mode())
+        h = self._handles.get(key)
+        if h is not None:
+            return h
+        with torch.cuda.device(device):
+            out = C.c_void_p()
+            self._create(lib, out, self._mode())
+            try:
+                for k, v in self._sd.items():
+                    if k.endswith("num_batches_tracked"):
+                        continue
+                    shape = (C.c_int64 * max(1, v.dim()))(*v.shape)
+                    _lib.check(lib.ghost_net_set_weight(out, k.encode(), C.c_void_p(v.data_ptr()), shape, v.dim()))
+                _lib.check(lib.ghost_net_finalize(out))
+                _lib.check(lib.ghost_net_enable_graph(out, int(self._graph)))
+            except Exception:
+                lib.ghost_net_destroy(out)
+                raise
+        self._handles[key] = out
+        return out
+
+    def stats(self, B, device=None):
+        """(kernel launches, dense FLOPs) of one forward at batch B."""
+        lib = _lib.load()
+        dev = device or self._device or torch.device("cuda", torch.cuda.current_device())
+        n, f = C.c_int(), C.c_double()
+        with torch.cuda.device(dev):
+            _lib.check(lib.ghost_net_stats(self._handle(dev), B, C.byref(n), C.byref(f)))
+        return n.value, f.value
+
+    def __call__(self, *a, **k):
+        return self.forward(*a, **k)
+
+
+class AEI_Net(_Net):
+    """Drop-in for network.AEI_Net.AEI_Net (network/AEI_Net.py:143-159), inference only.
+
+    The arithmetic mode follows the module dtype like the reference: `.float()` -> fp32 CUDA-core
+    correctness mode (1e-4 contract); `.half()` / `.bfloat16()` -> tcgen05 bf16 x bf16 -> fp32 mode
+    (1e-2 contract) with fp16 / bf16 tensors at the boundary."""
+
+    def __init__(self, backbone, num_blocks=2, c_id=256, seed=0):
+        super().__init__(_w.aei_spec(backbone, num_blocks, c_id), seed)
+        self.backbone, self.num_blocks, self.c_id = backbone, num_blocks, c_id
+        self.return_attr = True  # the reference always returns the 8 attribute maps
+
+    def _create(self, lib, out, mode):
+        _lib.check(lib.ghost_aei_create(C.byref(out), self.backbone.encode(), self.num_blocks, self.c_id, mode))
+
+    def _attr_shapes(self, B):
+        blocks = _w.BLOCKS[self.backbone]
+        return [(B, blocks[k][2], 2 << k, 2 << k) for k in range(8)]
+
+    def _check_x(self, Xt, name):
+        _require_cuda(Xt, name)
+        if Xt.dim() != 4 or tuple(Xt.shape[1:]) != (3, 256, 256):
+            raise ValueError("%s must be [B,3,256,256], got %s" % (name, tuple(Xt.shape)))
+        if Xt.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+            raise TypeError("%s has unsupported dtype %s" % (name, Xt.dtype))
+        return Xt.contiguous()
+
+    def forward(self, Xt, z_id):
+        Xt = self._check_x(Xt, "Xt")
+        _require_cuda(z_id, "z_id")
+        B = Xt.shape[0]
+        if z_id.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+            raise TypeError("z_id has unsupported dtype %s" % z_id.dtype)
+        z = z_id.reshape(z_id.shape[0], -1).contiguous()  # [B,512] or [B,1,512] (export-onnx.py:30)
+        if tuple(z.shape) != (B, self.c_id):
+            raise ValueError("z_id must be [%d,%d], got %s" % (B, self.c_id, tuple(z_id.shape)))
+        if z.device != Xt.device:
+            raise ValueError("Xt and z_id must be on the same device")
+        lib = _lib.load()
+        with torch.cuda.device(Xt.device):
+            h = self._handle(Xt.device)
+            Y = torch.empty((B, 3, 256, 256), dtype=self._dtype, device=Xt.device)
+            attrs, ptrs = None, None
+            if self.return_attr:
+                attrs = tuple(torch.empty(s, dtype=self._dtype, device=Xt.device) for s in self._attr_shapes(B))
+                ptrs = (C.c_void_p * 8)(*[a.data_ptr() for a in attrs])
+            _lib.check(lib.ghost_aei_forward(h, _ptr(Xt), _DT[Xt.dtype], _ptr(z), _DT[z.dtype], _ptr(Y), ptrs,
+                                             _DT[self._dtype], B, _stream()))
+        return Y, attrs
+
+    def get_attr(self, X):
+        X = self._check_x(X, "X")
+        B = X.shape[0]
+        lib = _lib.load()
+        with torch.cuda.device(X.device):
+            h = self._handle(X.device)
+            attrs = tuple(torch.empty(s, dtype=self._dtype, device=X.device) for s in self._attr_shapes(B))
+            ptrs = (C.c_void_p * 8)(*[a.data_ptr() for a in attrs])
+            _lib.check(lib.ghost_aei_encode(h, _ptr(X), _DT[X.dtype], ptrs, _DT[self._dtype], B, _stream()))
+        return attrs
+
+    def swap_u8(self, crops_bgr, z_id, out=None):
+        """Fused transform_target_to_torch + faceshifter_batch (core.py:13-26, faceshifter_run.py:5-23) without
+        the bounce through the host: uint8 BGR crops [B,256,256,3] on the device -> uint8 BGR [B,256,256,3] on
+        the device.  z_id is [1,c_id] (tiled over the batch as faceshifter_batch does) or [B,c_id]."""
+        _require_cuda(crops_bgr, "crops_bgr")
+        _require_cuda(z_id, "z_id")
+        if crops_bgr.dtype != torch.uint8 or crops_bgr.dim() != 4 or tuple(crops_bgr.shape[1:]) != (256, 256, 3):
+            raise ValueError("crops_bgr must be uint8 [B,256,256,3]")
+        B = crops_bgr.shape[0]
+        z = z_id.reshape(z_id.shape[0], -1).contiguous()
+        if z.shape[0] not in (1, B) or z.shape[1] != self.c_id:
+            raise ValueError("z_id must be [1,%d] or [%d,%d]" % (self.c_id, B, self.c_id))
+        crops_bgr = crops_bgr.contiguous()
+        lib = _lib.load()
+        with torch.cuda.device(crops_bgr.device):
+            h = self._handle(crops_bgr.device)
+            if out is None:
+                out = torch.empty_like(crops_bgr)
+            _lib.check(lib.ghost_aei_swap_u8(h, _ptr(crops_bgr), _ptr(z), _DT[z.dtype], z.shape[0], _ptr(out), B,
+                                             _stream()))
+        return out
+
+    def y_nhwc(self, B, device=None):
+        """(device pointer, ghost dtype) of the NHWC generator output of the last forward at batch B."""
+        lib = _lib.load()
+        dev = device or self._device or torch.device("cuda", torch.cuda.current_device())
+        p, dt = C.c_void_p(), C.c_int()
+        with torch.cuda.device(dev):
+            _lib.check(lib.ghost_net_y_nhwc(self._handle(dev), B, C.byref(p), C.byref(dt)))
+        return p.value, dt.value
+
+
+class IResNet100(_Net):
+    """Drop-in for arcface_model.iresnet.iresnet100(fp16=False) as used at inference.py:33-36."""
+
+    def __init__(self, seed=0):
+        super().__init__(_w.iresnet100_spec(), seed)
+
+    def _create(self, lib, out, mode):
+        _lib.check(lib.ghost_arcface_create(C.byref(out), mode))
+
+    def forward(self, x):
+        _require_cuda(x, "x")
+        if x.dim() != 4 or tuple(x.shape[1:]) != (3, 112, 112):
+            raise ValueError("x must be [B,3,112,112], got %s" % (tuple(x.shape),))
+        if x.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+            raise TypeError("x has unsupported dtype %s" % x.dtype)
+        x = x.contiguous()
+        B = x.shape[0]
+        lib = _lib.load()
+        with torch.cuda.device(x.device):
+            h = self._handle(x.device)
+            # the reference's iresnet(fp16=False) returns fp32 whatever the input
+            z = torch.empty((B, 512), dtype=torch.float32 if self._dtype == torch.float32 else self._dtype,
+                            device=x.device)
+            _lib.check(lib.ghost_arcface_forward(h, _ptr(x), _DT[x.dtype], _ptr(z), _DT[z.dtype], B, _stream()))
+        return z
+
+    def embed_hwc(self, images, out_dtype=torch.float32):
+        """normalize_and_torch(_batch) + F.interpolate(scale 0.5, bilinear, align_corners=True) + netArc in one
+        call (image_processing.py:23-48, core.py:44-45,52-54).  images: [B,224,224,3] RGB HWC on the device,
+        uint8 (divided by 255) or float32 already in [0,1]."""
+        _require_cuda(images, "images")
+        if images.dim() != 4 or tuple(images.shape[1:]) != (224, 224, 3):
+            raise ValueError("images must be [B,224,224,3]")
+        if images.dtype not in (torch.uint8, torch.float32):
+            raise TypeError("images must be uint8 or float32")
+        images = images.contiguous()
+        B = images.shape[0]
+        lib = _lib.load()
+        with torch.cuda.device(images.device):
+            h = self._handle(images.device)
+            z = torch.empty((B, 512), dtype=out_dtype, device=images.device)
+            _lib.check(lib.ghost_arcface_embed_hwc(h, _ptr(images), int(images.dtype == torch.uint8), _ptr(z),
+                                                   _DT[out_dtype], B, _stream()))
+        return z
+
+
+def iresnet100(pretrained=False, progress=True, fp16=False, **kwargs):
+    if pretrained:
+        raise ValueError("no pretrained weights are bundled; load_state_dict() a backbone.pth state dict")
+    net = IResNet100()
+    return net.half() if fp16 else net
+
+
+# ------------------------------------------------------------------------------------------------ pre / post
+def transform_target_to_torch(resized_frs, half=True):
+    """utils/inference/core.py:13-26: uint8 BGR [B,256,256,3] -> normalised RGB, returned (like the reference)
+    as the NCHW *view* of an NHWC tensor.  half=True reproduces the fp16 rounding order of the reference."""
+    src = torch.from_numpy(np.ascontiguousarray(resized_frs)) if isinstance(resized_frs, np.ndarray) else resized_frs
+    if src.dtype != torch.uint8 or src.dim() != 4 or tuple(src.shape[1:]) != (256, 256, 3):
+        raise ValueError("resized_frs must be uint8 [B,256,256,3]")
+    if not torch.cuda.is_available():
+        raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
+    src = src.cuda().contiguous()
+    B = src.shape[0]
+    lib = _lib.load()
+    dst = torch.empty((B, 256, 256, 3), dtype=torch.float32, device=src.device)
+    with torch.cuda.device(src.device):
+        _lib.check(lib.ghost_preproc_u8(_ptr(src), _ptr(dst), _lib.F32, B, int(bool(half)), _stream()))
+    if half:
+        dst = dst.half()  # exact: the kernel already rounded every step to fp16
+    return dst.permute(0, 3, 1, 2)
+
+
+def faceshifter_batch(source_emb, target, G):
+    """utils/inference/faceshifter_run.py:5-23."""
+    bs = target.shape[0]
+    assert target.ndim == 4, "target should have 4 dimentions -- B x C x H x W"
+    if bs > 1:
+        source_emb = torch.cat([source_emb] * bs)
+    keep = G.return_attr
+    G.return_attr = False
+    try:
+        Y, _ = G(target, source_emb)
+    finally:
+        G.return_attr = keep
+    lib = _lib.load()
+    out = torch.empty((bs, 256, 256, 3), dtype=torch.uint8, device=Y.device)
+    with torch.cuda.device(Y.device):
+        p, dt = G.y_nhwc(bs, Y.device)
+        _lib.check(lib.ghost_postproc_u8(C.c_void_p(p), dt, _ptr(out), bs, _stream()))
+    return out.cpu().numpy()
+
+
+def normalize_and_torch(image):
+    """utils/inference/image_processing.py:23-34 (layout/scale bookkeeping only; the arithmetic that matters,
+    normalise + resample + embed, is fused in IResNet100.embed_hwc)."""
+    image = torch.tensor(np.array(image, copy=True), dtype=torch.float32).cuda()
+    if image.max() > 1.:
+        image = image / 255.
+    image = image.permute(2, 0, 1).unsqueeze(0)
+    return (image - 0.5) / 0.5
+
+
+def normalize_and_torch_batch(frames):
+    """utils/inference/image_processing.py:37-48."""
+    batch = torch.from_numpy(np.array(frames, copy=True)).cuda()
+    if batch.max() > 1.:
+        batch = batch / 255.
+    batch = batch.permute(0, 3, 1, 2)
+    return (batch - 0.5) / 0.5
+
+
+# ------------------------------------------------------------------------------------------------ paste-back
+def _as_dev(a, dtype, device):
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device=device, dtype=dtype)
+
+
+def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask=None, mode="exact", out=None,
+               crop_kind=None):
+    """Fused inverse-warp + mask composite of swapped crops into full frames (K11).
+
+    frames : uint8 BGR [F,H,W,3] (device tensor or numpy)
+    crops  : uint8 BGR [n,256,256,3], or the generator's NHWC output given as (device_ptr, ghost dtype, n)
+    masks  : [m,224,224] float64 / float32 in [0,1]
+    tfms   : [n_faces,2,3] float64 frame->224-crop affines; face_frame[i] (non-decreasing) is the frame of
+             face i, faces of one frame compose in list order; face_crop / face_mask default to arange.
+    mode   : "exact" = get_final_image arithmetic (bit-exact), "float" = get_final_video arithmetic.
+    Returns the composited frames as a device tensor [F,H,W,3] uint8."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
+    dev = frames.device if isinstance(frames, torch.Tensor) and frames.is_cuda else torch.device(
+        "cuda", torch.cuda.current_device())
+    fr = _as_dev(frames, torch.uint8, dev)
+    if fr.dim() != 4 or fr.shape[3] != 3:
+        raise ValueError("frames must be [F,H,W,3] uint8")
+    F_, H, W = fr.shape[0], fr.shape[1], fr.shape[2]
+    tf = np.ascontiguousarray(np.asarray(tfms, dtype=np.float64).reshape(-1, 2, 3))
+    nf = tf.shape[0]
+    ff = np.ascontiguousarray(np.asarray(face_frame, dtype=np.int32).reshape(-1))
+    fc = np.arange(nf, dtype=np.int32) if face_crop is None else np.ascontiguousarray(np.asarray(face_crop, np.int32))
+    fm = np.arange(nf, dtype=np.int32) if face_mask is None else np.ascontiguousarray(np.asarray(face_mask, np.int32))
+    if not (len(ff) == len(fc) == len(fm) == nf):
+        raise ValueError("tfms, face_frame, face_crop and face_mask must have one entry per face")
+    if isinstance(crops, tuple):
+        cptr, cdt, ncrops = crops
+        ckind = _lib.CROP_Y_BF16 if cdt == _lib.BF16 else _lib.CROP_Y_F32
+        keep = None
+    else:
+        keep = _as_dev(crops, torch.uint8, dev)
+        if keep.dim() != 4 or tuple(keep.shape[1:]) != (256, 256, 3):
+            raise ValueError("crops must be uint8 [n,256,256,3]")
+        cptr, ncrops, ckind = keep.data_ptr(), keep.shape[0], _lib.CROP_U8_BGR
+    if crop_kind is not None:
+        ckind = crop_kind
+    mk = masks if isinstance(masks, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(masks))
+    if mk.dtype not in (torch.float64, torch.float32):
+        mk = mk.to(torch.float64)
+    mk = mk.to(dev).contiguous()
+    if mk.dim() != 3 or tuple(mk.shape[1:]) != (224, 224):
+        raise ValueError("masks must be [m,224,224]")
+    if out is None:
+        out = torch.empty_like(fr)
+    d = _lib.PasteDesc()
+    d.crops, d.crop_kind, d.n_crops = cptr, ckind, ncrops
+    d.masks, d.mask_f64, d.n_masks = mk.data_ptr(), int(mk.dtype == torch.float64), mk.shape[0]
+    d.frames_in, d.frames_out = fr.data_ptr(), out.data_ptr()
+    d.n_frames, d.H, d.W = F_, H, W
+    d.n_faces = nf
+    d.tfm = tf.ctypes.data_as(C.POINTER(C.c_double))
+    d.face_frame = ff.ctypes.data_as(C.POINTER(C.c_int))
+    d.face_crop = fc.ctypes.data_as(C.POINTER(C.c_int))
+    d.face_mask = fm.ctypes.data_as(C.POINTER(C.c_int))
+    d.mode = _lib.PASTE_EXACT if mode == "exact" else _lib.PASTE_FLOAT
+    if mode not in ("exact", "float"):
+        raise ValueError("mode must be 'exact' or 'float'")
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        _lib.check(lib.ghost_paste_back(C.byref(d), _stream()))
+    return out
+
+
+def _masks_from_handler(swaps224, crop_frames, handler, params):
+    from .masks import face_mask_static
+    masks = []
+    for j, (swap, tgt) in enumerate(zip(swaps224, crop_frames)):
+        lm = handler.get_without_detection_without_transform(swap)
+        lm_t = handler.get_without_detection_without_transform(tgt)
+        if params[j] is None:
+            m, params[j] = face_mask_static(tgt, lm, lm_t, None)
+        else:
+            m = face_mask_static(tgt, lm, lm_t, params[j])
+        masks.append(m)
+    return masks
+
+
+def get_final_image(final_frames, crop_frames, full_frame, tfm_arrays, handler=None, masks=None):
+    """utils/inference/image_processing.py:51-77.  Landmark detection is out of scope, so the blend masks can be
+    passed directly (masks[i]: float64 224x224); with a `handler` they are built on the host exactly as the
+    reference does (cv2.resize + handler + face_mask_static).  Returns uint8 [H,W,3]."""
+    n = len(final_frames)
+    if n == 0:
+        return np.array(full_frame, dtype="uint8")
+    if masks is None:
+        if handler is None:
+            raise ValueError("get_final_image needs either a landmark handler or precomputed masks")
+        import cv2
+        swaps = [cv2.resize(final_frames[i][0], (224, 224)) for i in range(n)]
+        masks = _masks_from_handler(swaps, [crop_frames[i][0] for i in range(n)], handler, [None] * n)
+    crops = np.stack([np.asarray(final_frames[i][0], dtype=np.uint8) for i in range(n)])
+    tf = np.stack([np.asarray(tfm_arrays[i][0], dtype=np.float64) for i in range(n)])
+    out = paste_back(np.asarray(full_frame, dtype=np.uint8)[None], crops, np.stack(masks).astype(np.float64), tf,
+                     np.zeros(n, np.int32), mode="exact")
+    return out[0].cpu().numpy()
+
+
+def get_final_video(final_frames, crop_frames, full_frames, tfm_array, OUT_VIDEO_NAME=None, fps=30.0, handler=None,
+                    masks=None, chunk=64):
+    """utils/inference/video_processing.py:191-243 compositing (fp32 arithmetic, faces compose through uint8).
+    masks[j][i] replaces the landmark handler (out of scope).  Returns the list of composited frames; when
+    OUT_VIDEO_NAME is given they are also written with cv2.VideoWriter as the reference does."""
+    nF, nJ = len(full_frames), len(crop_frames)
+    result = []
+    params = [None] * nJ
+    for c0 in range(0, nF, chunk):
+        c1 = min(nF, c0 + chunk)
+        crops, mks, tfs, ffr = [], [], [], []
+        for i in range(c0, c1):
+            for j in range(nJ):
+                if len(crop_frames[j][i]) == 0 or len(final_frames[j][i]) == 0:
+                    params[j] = None
+                    continue
+                if masks is not None:
+                    m = masks[j][i]
+                else:
+                    if handler is None:
+                        raise ValueError("get_final_video needs either a landmark handler or precomputed masks")
+                    import cv2
+                    swap = cv2.resize(final_frames[j][i], (224, 224))
+                    p = [params[j]]
+                    m = _masks_from_handler([swap], [crop_frames[j][i]], handler, p)[0]
+                    params[j] = p[0]
+                crops.append(np.asarray(final_frames[j][i], dtype=np.uint8))
+                mks.append(np.asarray(m, dtype=np.float32))
+                tfs.append(np.asarray(tfm_array[j][i], dtype=np.float64))
+                ffr.append(i - c0)
+        frames = np.stack([np.asarray(f, dtype=np.uint8) for f in full_frames[c0:c1]])
+        if crops:
+            out = paste_back(frames, np.stack(crops), np.stack(mks), np.stack(tfs), np.asarray(ffr, np.int32),
+                             mode="float").cpu().numpy()
+        else:
+            out = frames
+        result.extend(list(out))
+    if OUT_VIDEO_NAME:
+        import cv2
+        vw = cv2.VideoWriter(str(OUT_VIDEO_NAME), cv2.VideoWriter_fourcc(*"mp4v"), fps,
+                             (full_frames[0].shape[1], full_frames[0].shape[0]))
+        for f in result:
+            vw.write(f)
+        vw.release()
+    return result

@@ -1,0 +1,148 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference (run in the build container only).
+
+    PYTHONDONTWRITEBYTECODE=1 python oracle/gen_golden.py
+
+Imports /root/reference (network.AEI_Net.AEI_Net, utils.inference.image_processing.get_final_image,
+utils.inference.masks.face_mask_static) on the CPU and records their outputs on seeded inputs and
+seeded weights, so that the GPU box - where /root/reference does not exist - can still check the
+oracle restatements (oracle/aei_ref.py, oracle/paste_ref.py) and the CUDA path against the reference.
+Inputs and weights are regenerated from the seeds by the tests (ghost_b200/synth.py, ghost_b200/weights.py);
+the files hold only the reference's outputs plus input checksums.
+"""
+import hashlib
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+sys.dont_write_bytecode = True
+sys.path.insert(0, ROOT)
+sys.path.insert(0, REF)
+
+from ghost_b200 import synth, weights as W  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+AEI_CASES = [  # name, backbone, num_blocks, perturbed, batch
+    ("aei_unet2_default", "unet", 2, False, 1),
+    ("aei_unet2_perturbed", "unet", 2, True, 2),
+    ("aei_linknet3_perturbed", "linknet", 3, True, 1),
+    ("aei_unet1_perturbed", "unet", 1, True, 1),
+]
+
+
+def aei_case_inputs(name, backbone, nb, perturbed, B):
+    sd = W.init_state_dict(W.aei_spec(backbone, nb, 512), seed=0)
+    if perturbed:
+        W.perturb_(sd, seed=1)
+    return sd, synth.crops_pm1(B, seed=7), synth.z_ids(B, seed=7)
+
+
+def gen_aei():
+    from network.AEI_Net import AEI_Net
+    for name, bb, nb, pert, B in AEI_CASES:
+        sd, Xt, z = aei_case_inputs(name, bb, nb, pert, B)
+        G = AEI_Net(bb, nb, 512).eval()
+        G.load_state_dict(sd)
+        with torch.no_grad():
+            Y, attr = G(Xt, z)
+        out = {"Y": Y.numpy().astype(np.float32), "xt_sha": sha(Xt.numpy()), "z_sha": sha(z.numpy())}
+        for k, a in enumerate(attr):
+            a = a.numpy()
+            out["attr%d_sample" % (k + 1)] = a.reshape(-1)[:: max(1, a.size // 4096)][:4096].astype(np.float32)
+            out["attr%d_absmean" % (k + 1)] = np.float64(np.abs(a).mean())
+            out["attr%d_shape" % (k + 1)] = np.array(a.shape)
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), **out)
+        print(name, "Y mean|.|", float(np.abs(out["Y"]).mean()))
+
+
+class FakeHandler(object):
+    """Stands in for coordinate_reg.image_infer.Handler (landmark model, out of scope): returns seeded
+    synthetic landmarks; the swap and the target crop get slightly different sets like the real model."""
+
+    def __init__(self, seed, shift):
+        self.seed, self.shift, self.calls = seed, shift, 0
+
+    def get_without_detection_without_transform(self, img):
+        self.calls += 1
+        rng = np.random.default_rng(self.seed + self.calls % 2)
+        return synth.landmarks106(rng, 224, shift=self.shift if self.calls % 2 == 1 else 0.0)
+
+
+PASTE_CASES = [  # name, H, W, n_faces, seed, clipped, landmark shift (selects the erode/sigma preset)
+    ("paste_small_1face", 270, 480, 1, 11, False, 0.0),
+    ("paste_small_clipped", 270, 480, 1, 12, True, 3.0),
+    ("paste_mid_3faces", 540, 960, 3, 13, False, -2.0),
+    ("paste_1080p_1face", 1080, 1920, 1, 14, False, 1.5),
+    ("paste_1080p_4faces_overlap", 1080, 1920, 4, 15, False, 0.0),
+]
+
+
+def paste_case_inputs(name, H, W, nf, seed, clipped, shift):
+    rng = np.random.default_rng(seed)
+    frame = synth.frame_u8(H, W, seed=seed)
+    crops = synth.crops_u8(nf, seed=seed)
+    targets = synth.crops_u8(nf, seed=seed + 100)[:, :224, :224].copy()
+    tfms = []
+    for i in range(nf):
+        t = synth.similarity_tfm(H, W, rng, clipped=clipped)
+        if "overlap" in name and i > 0:      # pile later faces onto the first one
+            t = tfms[0].copy()
+            t[:, 2] += rng.uniform(-40, 40, size=2)
+        tfms.append(t)
+    return frame, crops, targets, np.stack(tfms)
+
+
+def gen_paste():
+    for m in ("matplotlib", "matplotlib.pyplot", "insightface", "insightface.utils", "insightface.utils.face_align"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    sys.modules["insightface"].utils = sys.modules["insightface.utils"]
+    sys.modules["insightface.utils"].face_align = sys.modules["insightface.utils.face_align"]
+    from utils.inference.image_processing import get_final_image
+    from utils.inference import masks as ref_masks
+    import cv2
+    for name, H, W, nf, seed, clipped, shift in PASTE_CASES:
+        frame, crops, targets, tfms = paste_case_inputs(name, H, W, nf, seed, clipped, shift)
+        handler = FakeHandler(seed, shift)
+        final_frames = [[crops[i]] for i in range(nf)]
+        crop_frames = [[targets[i]] for i in range(nf)]
+        tfm_arrays = [[tfms[i]] for i in range(nf)]
+        out = get_final_image(final_frames, crop_frames, frame, tfm_arrays, handler)
+        # the masks the reference built on the way (same handler call sequence)
+        h2 = FakeHandler(seed, shift)
+        masks_u8, params = [], []
+        for i in range(nf):
+            sw = cv2.resize(crops[i], (224, 224))
+            lm = h2.get_without_detection_without_transform(sw)
+            lt = h2.get_without_detection_without_transform(targets[i])
+            m, p = ref_masks.face_mask_static(targets[i], lm, lt, None)
+            masks_u8.append(np.rint(m * 255).astype(np.uint8))
+            assert np.array_equal(masks_u8[-1] / 255, m)
+            params.append(p)
+        diff = np.any(out != frame, axis=2)
+        ys, xs = np.nonzero(diff)
+        y0, y1, x0, x1 = (int(ys.min()), int(ys.max()) + 1, int(xs.min()), int(xs.max()) + 1) if len(ys) else (0, 0, 0, 0)
+        rec = {"masks_u8": np.stack(masks_u8), "params": np.array(params), "roi": np.array([y0, y1, x0, x1]),
+               "out_roi": out[y0:y1, x0:x1].copy(), "out_sha": sha(out), "frame_sha": sha(frame),
+               "crops_sha": sha(crops), "tfm_sha": sha(tfms)}
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), **rec)
+        print(name, "roi", rec["roi"], "params", params, "changed px", int(diff.sum()))
+
+
+if __name__ == "__main__":
+    os.makedirs(GOLD, exist_ok=True)
+    which = sys.argv[1:] or ["aei", "paste"]
+    if "aei" in which:
+        gen_aei()
+    if "paste" in which:
+        gen_paste()
