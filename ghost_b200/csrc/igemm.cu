@@ -373,11 +373,19 @@ int igemm_smem_bytes(const IgemmParams& p) {
 }
 
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) return cudaGetErrorString(e);
-    attr_set = true;
+  static int max_dyn_smem = 0;  // opt-in dynamic shared memory limit (227 KB minus the kernel's static part)
+  if (!max_dyn_smem) {
+    cudaFuncAttributes fa;
+    cudaError_t e = cudaFuncGetAttributes(&fa, igemm_kernel);
+    if (e == cudaSuccess) {
+      const int lim = 227 * 1024 - static_cast<int>(fa.sharedSizeBytes);
+      e = cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+      if (e == cudaSuccess) max_dyn_smem = lim;
+    }
+    if (e != cudaSuccess) {
+      cudaGetLastError();  // do not leave a stale error behind for the next launch check
+      return cudaGetErrorString(e);
+    }
   }
   if (p.BN % 16 || p.BN < 16 || p.BN > 256) return "igemm: BN must be a multiple of 16 in [16,256]";
   if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";
@@ -388,7 +396,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
   if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
   const int smem = igemm_smem_bytes(p);
-  if (smem > 227 * 1024) return "igemm: shared memory budget exceeded";
+  if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
   if (tiles <= 0) return "igemm: empty grid";
   static int num_sms = 0;

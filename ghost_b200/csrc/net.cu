@@ -7,7 +7,10 @@ namespace ghost {
 
 void fail(int code, const std::string& msg) { throw GhostError(code, msg); }
 void check_cuda(cudaError_t e, const char* what) {
-  if (e != cudaSuccess) fail(-3, std::string(what) + ": " + cudaGetErrorString(e));
+  if (e != cudaSuccess) {
+    cudaGetLastError();  // clear, so the next launch check does not report this error again
+    fail(-3, std::string(what) + ": " + cudaGetErrorString(e));
+  }
 }
 void check_msg(const char* err, const std::string& where) {
   if (err) fail(-3, where + ": " + err);
