@@ -59,6 +59,9 @@ SIGNATURES = {
     "ghost_arcface_embed_hwc": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp]),
     "ghost_net_enable_graph": (_i, [_vp, _i]),
     "ghost_net_stats": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_d)]),
+    "ghost_net_profile": (_i, [_vp, _i, _i, _i, _fp, C.POINTER(_d), C.POINTER(_d), C.POINTER(_i), C.c_char_p, _i,
+                               C.POINTER(_i), _vp]),
+    "ghost_net_debug_get": (_i, [_vp, _i, C.c_char_p, _vp, _i, C.POINTER(_i), _vp]),
     "ghost_net_destroy": (None, [_vp]),
     "ghost_preproc_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ghost_postproc_u8": (_i, [_vp, _i, _vp, _i, _vp]),

@@ -191,6 +191,32 @@ class _Net(object):
             _lib.check(lib.ghost_net_stats(self._handle(dev), B, C.byref(n), C.byref(f)))
         return n.value, f.value
 
+    def profile(self, B, reps=5, device=None):
+        """Per-op CUDA-event timing of one forward at batch B: list of dicts (name, cls, ms, flops, bytes)."""
+        lib = _lib.load()
+        dev = device or self._device or torch.device("cuda", torch.cuda.current_device())
+        cap, stride = 1024, 64
+        ms, fl, by = (C.c_float * cap)(), (C.c_double * cap)(), (C.c_double * cap)()
+        cl, names, n = (C.c_int * cap)(), C.create_string_buffer(cap * stride), C.c_int()
+        with torch.cuda.device(dev):
+            _lib.check(lib.ghost_net_profile(self._handle(dev), B, reps, cap, ms, fl, by, cl, names, stride,
+                                             C.byref(n), _stream()))
+        raw = names.raw
+        return [dict(name=raw[i * stride:(i + 1) * stride].split(b"\0", 1)[0].decode(), cls=cl[i], ms=ms[i],
+                     flops=fl[i], bytes=by[i]) for i in range(min(n.value, cap))]
+
+    def intermediate(self, name, B, device=None, dtype=torch.float32):
+        """Named intermediate activation of the last forward at batch B as an NCHW tensor (block-level tests)."""
+        lib = _lib.load()
+        dev = device or self._device or torch.device("cuda", torch.cuda.current_device())
+        shape = (C.c_int * 4)()
+        with torch.cuda.device(dev):
+            h = self._handle(dev)
+            _lib.check(lib.ghost_net_debug_get(h, B, name.encode(), None, _DT[dtype], shape, _stream()))
+            out = torch.empty(tuple(shape), dtype=dtype, device=dev)
+            _lib.check(lib.ghost_net_debug_get(h, B, name.encode(), _ptr(out), _DT[dtype], shape, _stream()))
+        return out
+
     def __call__(self, *a, **k):
         return self.forward(*a, **k)
 
@@ -452,6 +478,9 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
         raise ValueError("masks must be [m,224,224]")
     if out is None:
         out = torch.empty_like(fr)
+    elif not (isinstance(out, torch.Tensor) and out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous()
+              and out.shape == fr.shape and out.device == fr.device):
+        raise ValueError("out must be a contiguous uint8 CUDA tensor shaped like frames")
     d = _lib.PasteDesc()
     d.crops, d.crop_kind, d.n_crops = cptr, ckind, ncrops
     d.masks, d.mask_f64, d.n_masks = mk.data_ptr(), int(mk.dtype == torch.float64), mk.shape[0]

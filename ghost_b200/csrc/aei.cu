@@ -204,15 +204,22 @@ void Net::build_aei(ExecPlan& p) {
     Op op;
     op.name = name;
     op.flops = lop.flops;
+    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : (aad ? kOpAadTC : kOpConvTC);
+    if (aad)  // apply read of h + z_attr read + write (gamma/beta never touch HBM)
+      op.bytes = static_cast<double>(B) * Ho * Wo * (2.0 * aad->c_x + Cin) * 2.0;
     op.run = [lop](cudaStream_t s) { return lop.launch(s); };
     p.ops.push_back(std::move(op));
   };
-  auto add_op = [&](const std::string& name, std::function<const char*(cudaStream_t)> fn) {
+  auto add_op = [&](const std::string& name, std::function<const char*(cudaStream_t)> fn, int cls = kOpMisc,
+                    double bytes = 0.0) {
     Op op;
     op.name = name;
     op.run = std::move(fn);
+    op.cls = cls;
+    op.bytes = bytes;
     p.ops.push_back(std::move(op));
   };
+  const double esz = bf ? 2.0 : 4.0;
 
   // ------------------------------------------------------------------ buffers
   p.x_in = new_act(256, 256, 3);
@@ -279,7 +286,7 @@ void Net::build_aei(ExecPlan& p) {
     const Act src = z[7], dst = z[8];
     add_op("enc.z_attr8.upsample", [=](cudaStream_t s) {
       return upsample2x_launch(src.p, dst.p, dt, B, src.H, src.W, src.C, dst.C, 0, s);
-    });
+    }, kOpUpsample, 5.0 * B * src.H * src.W * src.C * esz);
   }
   encoder_ops = p.ops.size();
 
@@ -293,6 +300,7 @@ void Net::build_aei(ExecPlan& p) {
     add_conv("gen.zid_fc", p.zid, 0, c_id, Taps::point(), 1, 1, "zfc", zo, Epilogue(), nullptr);
   }
   Act m = new_act(2, 2, 1024);
+  p.named["m1"] = m;
   {
     const Act mm = m;
     add_op("gen.up1", [=](cudaStream_t s) { return zfc_to_act_launch(zfc, ldz, 0, 4096, nullptr, mm.p, dt, B, s); });
@@ -303,10 +311,12 @@ void Net::build_aei(ExecPlan& p) {
     const int hw = 2 << (k - 1);
     const int HW = hw * hw;
     const Act& za = z[k];
-    float* sums_m = p.pool.alloc_n<float>(static_cast<size_t>(B) * b.cin * 2);
+    const int parts_in = in_stats_parts(B, HW, b.cin);
+    float* sums_m = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * b.cin);
     {
       const Act mm = m;
-      add_op(S("blk%d.stats_m", k), [=](cudaStream_t s) { return in_stats_launch(mm.p, dt, B, HW, mm.C, sums_m, s); });
+      add_op(S("blk%d.stats_m", k), [=](cudaStream_t s) { return in_stats_launch(mm.p, dt, B, HW, mm.C, sums_m, s); },
+             kOpStats, static_cast<double>(B) * HW * mm.C * esz);
     }
     Act a = new_act(hw, hw, b.cin);
     Act gb;  // fp32 mode only: gamma|beta of the attribute branch
@@ -322,7 +332,7 @@ void Net::build_aei(ExecPlan& p) {
       const float bh = scalars_.at(lname + ".bh");
       const int cx = b.cin, og = info.off_gamma, ob = info.off_beta;
       add_op(lname + ".fold", [=](cudaStream_t s) {
-        return aad_fold_launch(sums, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, s);
+        return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, s);
       });
       if (bf) {
         AadArgs args;
@@ -366,22 +376,26 @@ void Net::build_aei(ExecPlan& p) {
       add_conv(S("blk%d.conv%d", k, i), a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.conv%d", k, i),
                OutView::dense(o), e, nullptr);
       if (!last) {
-        float* sums_o = p.pool.alloc_n<float>(static_cast<size_t>(B) * co * 2);
+        float* sums_o = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * co);  // co == b.cin here
         const Act oo = o;
         add_op(S("blk%d.stats%d", k, i + 1),
-               [=](cudaStream_t s) { return in_stats_launch(oo.p, dt, B, HW, oo.C, sums_o, s); });
+               [=](cudaStream_t s) { return in_stats_launch(oo.p, dt, B, HW, oo.C, sums_o, s); }, kOpStats,
+               static_cast<double>(B) * HW * oo.C * esz);
         sums_x = sums_o;
       }
       x = o;
       y = o;
     }
+    p.named[S("y%d", k)] = y;
+    p.named[S("a%d", k)] = a;  // output of the block's last AADLayer+ReLU
     if (k < 8) {
       Act nm = new_act(2 * hw, 2 * hw, b.cout);
       const Act yy = y, nn = nm;
       add_op(S("blk%d.upsample", k), [=](cudaStream_t s) {
         return upsample2x_launch(yy.p, nn.p, dt, B, yy.H, yy.W, yy.C, nn.C, 0, s);
-      });
+      }, kOpUpsample, 5.0 * B * yy.H * yy.W * yy.C * esz);
       m = nm;
+      p.named[S("m%d", k + 1)] = m;
     } else {
       p.y = y;
     }

@@ -121,6 +121,7 @@ void Net::build_arcface(ExecPlan& p) {
     Op op;
     op.name = name;
     op.flops = lop.flops;
+    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : kOpConvTC;
     op.run = [lop](cudaStream_t s) { return lop.launch(s); };
     p.ops.push_back(std::move(op));
   };

@@ -263,6 +263,46 @@ int ghost_arcface_embed_hwc(ghost_net_t* net, const void* src, int is_u8, void* 
   });
 }
 
+int ghost_net_profile(ghost_net_t* net, int B, int reps, int max_ops, float* ms, double* flops, double* bytes, int* cls,
+                      char* names, int name_stride, int* n_ops, void* stream) {
+  return guarded([&] {
+    require(net && n_ops && reps > 0 && max_ops >= 0, "bad argument");
+    std::lock_guard<std::mutex> lk(net->mu);
+    ExecPlan& p = net->net.plan(B);
+    std::vector<float> t;
+    net->net.profile_plan(p, S(stream), reps, &t);
+    const int n = static_cast<int>(p.ops.size());
+    *n_ops = n;
+    for (int i = 0; i < n && i < max_ops; ++i) {
+      if (ms) ms[i] = t[i];
+      if (flops) flops[i] = p.ops[i].flops;
+      if (bytes) bytes[i] = p.ops[i].bytes;
+      if (cls) cls[i] = p.ops[i].cls;
+      if (names && name_stride > 0) {
+        strncpy(names + static_cast<size_t>(i) * name_stride, p.ops[i].name.c_str(), name_stride - 1);
+        names[static_cast<size_t>(i) * name_stride + name_stride - 1] = 0;
+      }
+    }
+  });
+}
+
+int ghost_net_debug_get(ghost_net_t* net, int B, const char* name, void* dst, int dst_dtype, int* shape4,
+                        void* stream) {
+  return guarded([&] {
+    require(net && name, "null argument");
+    std::lock_guard<std::mutex> lk(net->mu);
+    ExecPlan& p = net->net.plan(B);
+    auto it = p.named.find(name);
+    if (it == p.named.end()) fail(GHOST_ERR_INVALID, std::string("no intermediate named ") + name);
+    const Act& a = it->second;
+    if (shape4) {
+      shape4[0] = a.N; shape4[1] = a.C; shape4[2] = a.H; shape4[3] = a.W;
+    }
+    if (dst)
+      check_msg(nhwc_to_nchw_launch(a.p, a.dtype, a.C, 0, dst, dst_dtype, a.N, a.C, a.H, a.W, S(stream)), "debug get");
+  });
+}
+
 void ghost_net_destroy(ghost_net_t* net) { delete net; }
 
 int ghost_preproc_u8(const uint8_t* crops_bgr, void* dst, int dst_dtype, int B, int half_rounding, void* stream) {

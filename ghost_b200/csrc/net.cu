@@ -168,6 +168,28 @@ void Net::run_plan(ExecPlan& p, cudaStream_t s, size_t first, size_t last) {
   for (size_t i = first; i < last; ++i) check_msg(p.ops[i].run(s), p.ops[i].name);
 }
 
+void Net::profile_plan(ExecPlan& p, cudaStream_t s, int reps, std::vector<float>* ms) {
+  const size_t n = p.ops.size();
+  ms->assign(n, 0.f);
+  std::vector<cudaEvent_t> ev(n + 1);
+  for (auto& e : ev) check_cuda(cudaEventCreate(&e), "event create");
+  for (int r = 0; r < reps + 1; ++r) {  // first round is a warm-up
+    check_cuda(cudaEventRecord(ev[0], s), "event record");
+    for (size_t i = 0; i < n; ++i) {
+      check_msg(p.ops[i].run(s), p.ops[i].name);
+      check_cuda(cudaEventRecord(ev[i + 1], s), "event record");
+    }
+    check_cuda(cudaStreamSynchronize(s), "profile sync");
+    if (r == 0) continue;
+    for (size_t i = 0; i < n; ++i) {
+      float t = 0.f;
+      check_cuda(cudaEventElapsedTime(&t, ev[i], ev[i + 1]), "event elapsed");
+      (*ms)[i] += t / reps;
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+}
+
 // One pinned, device-mapped word per process: a kernel whose pipeline wait times out sets it, the
 // host reads it (without synchronising) at the entry of every API call, so a device-side failure
 // is reported by the next call at the latest and by ghost_check_errors() after a synchronize.

@@ -52,10 +52,22 @@ class DevPool {
   size_t total_ = 0;
 };
 
+// Kernel class of an op, for the per-class roofline accounting of the bench.
+enum OpClass : int {
+  kOpConvTC = 0,   // tcgen05 implicit-GEMM conv / deconv phase / linear (tensor bound)
+  kOpAadTC = 1,    // tcgen05 gamma/beta GEMM with the fused AAD blend epilogue (HBM bound)
+  kOpConvSimt = 2, // CUDA-core conv (fp32 mode, Cin = 3 layers)
+  kOpStats = 3,    // instance-norm statistics (HBM bound)
+  kOpUpsample = 4, // bilinear x2 (HBM bound)
+  kOpMisc = 5      // folds, scatter, per-channel affine, layout conversion
+};
+
 struct Op {
   std::string name;
   std::function<const char*(cudaStream_t)> run;
-  double flops = 0.0;
+  double flops = 0.0;  // dense multiply-add flops (2*MAC) of contraction ops
+  double bytes = 0.0;  // algorithmic HBM bytes of bandwidth-bound ops (SURVEY 8d accounting)
+  int cls = kOpMisc;
 };
 
 // A conv's weights in both packings.
@@ -80,6 +92,7 @@ struct ExecPlan {
   float* emb_out = nullptr;  // arcface: [B,512] fp32
   void* stage = nullptr;     // staging for broadcast z_id
   double flops = 0.0;
+  std::map<std::string, Act> named;  // intermediate activations by name (block-level parity tests, debugging)
   ~ExecPlan();
 };
 
@@ -93,6 +106,8 @@ class Net {
   void finalize();
   ExecPlan& plan(int B);
   void run_plan(ExecPlan& p, cudaStream_t s, size_t first_op = 0, size_t last_op = static_cast<size_t>(-1));
+  // Runs every op `reps` times bracketed by CUDA events on `s`; ms[i] = mean duration of op i.
+  void profile_plan(ExecPlan& p, cudaStream_t s, int reps, std::vector<float>* ms);
 
   Kind kind;
   std::string backbone;

@@ -203,28 +203,38 @@ __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const fl
 
 constexpr int kStatThreads = 256;
 
+// Partial statistics layout for one tensor: per image n a block of (2*P + 1) rows of C floats:
+//   row 2p   = sum_p (x - shift)        over the pixels of part p
+//   row 2p+1 = sum_p (x - shift)^2
+//   row 2P   = shift = x[n, pixel 0, c]  (one common shift per (n,c) keeps the sums linear across parts and
+//              removes the E[x^2]-E[x]^2 cancellation: |mean - shift| is of the order of the std)
+// Every part is written by exactly one block and the fold kernel adds them in a fixed order, so the
+// statistics are deterministic (no atomics, no memset).
 template <typename T>
 __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restrict__ x, int HW, int C,
-                                                                 int pix_per_block, float* __restrict__ sums) {
+                                                                 int pix_per_block, float* __restrict__ parts) {
   extern __shared__ float sh[];  // [kStatThreads][16]
   const int n = blockIdx.y;
+  const int P = gridDim.x;
   const int vecs = C >> 3;                       // channel vectors per pixel
   const int ppi = kStatThreads / vecs;           // pixels per iteration (vecs <= 256)
   const int cv = threadIdx.x % vecs, pl = threadIdx.x / vecs;
   const int p0 = blockIdx.x * pix_per_block;
   const int p1 = min(HW, p0 + pix_per_block);
-  float s[8], q[8];
+  float s[8], q[8], sft[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+  const T* base = x + (static_cast<long long>(n) * HW) * C + cv * 8;
+  load8(base, sft);
   if (pl < ppi) {
-    const T* base = x + (static_cast<long long>(n) * HW) * C + cv * 8;
     for (int p = p0 + pl; p < p1; p += ppi) {
       float v[8];
       load8(base + static_cast<long long>(p) * C, v);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        s[i] += v[i];
-        q[i] = fmaf(v[i], v[i], q[i]);
+        const float d = v[i] - sft[i];
+        s[i] += d;
+        q[i] = fmaf(d, d, q[i]);
       }
     }
   }
@@ -234,29 +244,39 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
     sh[threadIdx.x * 16 + 8 + i] = q[i];
   }
   __syncthreads();
-  // thread t < vecs*16 reduces one (channel vector, slot) column over the ppi pixel lanes
+  float* out = parts + static_cast<long long>(n) * (2 * P + 1) * C;
+  // thread t < vecs*16 reduces one (channel vector, slot) column over the ppi pixel lanes, in a fixed order
   for (int t = threadIdx.x; t < vecs * 16; t += kStatThreads) {
     const int v = t >> 4, slot = t & 15;
     float a = 0.f;
     for (int l = 0; l < ppi; ++l) a += sh[(l * vecs + v) * 16 + slot];
     const int c = v * 8 + (slot & 7);
-    atomicAdd(sums + (static_cast<long long>(n) * C + c) * 2 + (slot >> 3), a);
+    out[(2 * blockIdx.x + (slot >> 3)) * C + c] = a;
+  }
+  if (blockIdx.x == 0 && pl == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) out[2 * P * C + cv * 8 + i] = sft[i];
   }
 }
 
-__global__ void aad_fold_kernel(const float* __restrict__ sums, int HW, int C, const float* __restrict__ zfc, int ldz,
-                                int off_gamma, int off_beta, const float* __restrict__ w_h, float b_h,
+__global__ void aad_fold_kernel(const float* __restrict__ parts, int P, int HW, int C, const float* __restrict__ zfc,
+                                int ldz, int off_gamma, int off_beta, const float* __restrict__ w_h, float b_h,
                                 float4* __restrict__ ncpar, float* __restrict__ wh_fold, float* __restrict__ bh_fold) {
   __shared__ float red[32];
   const int n = blockIdx.x;
-  const float inv = 1.f / static_cast<float>(HW);
+  const double inv = 1.0 / static_cast<double>(HW);
+  const float* pn = parts + static_cast<long long>(n) * (2 * P + 1) * C;
   float part = 0.f;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float su = sums[(static_cast<long long>(n) * C + c) * 2];
-    const float sq = sums[(static_cast<long long>(n) * C + c) * 2 + 1];
-    const float mu = su * inv;
-    const float var = fmaxf(sq * inv - mu * mu, 0.f);
-    const float rstd = rsqrtf(var + 1e-5f);
+    double su = 0.0, sq = 0.0;
+    for (int p = 0; p < P; ++p) {
+      su += static_cast<double>(pn[(2 * p) * C + c]);
+      sq += static_cast<double>(pn[(2 * p + 1) * C + c]);
+    }
+    const double d = su * inv;
+    const float mu = static_cast<float>(static_cast<double>(pn[2 * P * C + c]) + d);
+    const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));  // biased variance (InstanceNorm2d)
+    const float rstd = 1.0f / sqrtf(var + 1e-5f);
     const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
     const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
     ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
@@ -305,33 +325,42 @@ __global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h,
 
 }  // namespace
 
-const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* sums, cudaStream_t s) {
-  if (C % 8 || C > 8 * kStatThreads) return "in_stats: C must be a multiple of 8 and <= 2048";
-  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * N * C, s);
-  if (e != cudaSuccess) return cudaGetErrorString(e);
-  const int vecs = C / 8;
-  const int ppi = kStatThreads / vecs;
-  // aim for >= ~4 waves of 148 SMs worth of blocks, but at least 8 iterations per block
-  int blocks_x = (592 + N - 1) / N;
+namespace {
+// pixels per block of the statistics kernel for a tensor of N images x HW pixels x C channels
+int stats_pix_per_block(int N, int HW, int C) {
+  const int ppi = kStatThreads / (C / 8);
+  // aim for ~4 waves of 148 SMs worth of blocks, but at least 8 iterations per block
+  const int blocks_x = (592 + N - 1) / N;
   int ppb = (HW + blocks_x - 1) / blocks_x;
   if (ppb < ppi * 8) ppb = ppi * 8;
-  blocks_x = (HW + ppb - 1) / ppb;
-  dim3 grid(blocks_x, N);
+  return ppb;
+}
+}  // namespace
+
+int in_stats_parts(int N, int HW, int C) {
+  const int ppb = stats_pix_per_block(N, HW, C);
+  return (HW + ppb - 1) / ppb;
+}
+
+const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* parts, cudaStream_t s) {
+  if (C % 8 || C > 8 * kStatThreads) return "in_stats: C must be a multiple of 8 and <= 2048";
+  const int ppb = stats_pix_per_block(N, HW, C);
+  dim3 grid((HW + ppb - 1) / ppb, N);
   const int smem = kStatThreads * 16 * sizeof(float);
   if (dtype == kF32)
-    in_stats_kernel<float><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x), HW, C, ppb, sums);
+    in_stats_kernel<float><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x), HW, C, ppb, parts);
   else if (dtype == kBF16)
     in_stats_kernel<__nv_bfloat16>
-        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, sums);
+        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, parts);
   else
     return "in_stats: unsupported dtype";
   return last_err();
 }
 
-const char* aad_fold_launch(const float* sums, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
+const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
                             cudaStream_t s) {
-  aad_fold_kernel<<<N, 256, 0, s>>>(sums, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold, bh_fold);
+  aad_fold_kernel<<<N, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold, bh_fold);
   return last_err();
 }
 

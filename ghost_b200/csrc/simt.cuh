@@ -34,12 +34,14 @@ struct SimtConvParams {
 // dtype: kF32 or kBF16 activations (weights and accumulation are always fp32)
 const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s);
 
-// Instance-norm statistics, NHWC.  sums: [N][C][2] fp32 (sum, sum of squares), zeroed by the call.
-const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* sums, cudaStream_t s);
+// Instance-norm statistics, NHWC, as deterministic per-block partial sums about a per-(n,c) shift.
+// parts: [N][2*P + 1][C] fp32 with P = in_stats_parts(N, HW, C) (layout in simt.cu); fully overwritten by the call.
+int in_stats_parts(int N, int HW, int C);
+const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* parts, cudaStream_t s);
 
-// Per-AAD-layer fold of the statistics with the identity FCs and conv_h.
+// Per-AAD-layer fold of the statistics (fixed-order sum of the P parts, in double) with the identity FCs and conv_h.
 //   ncpar[n][c] = {rstd, -mu*rstd, gamma_id, beta_id}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
-const char* aad_fold_launch(const float* sums, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
+const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
                             cudaStream_t s);
 

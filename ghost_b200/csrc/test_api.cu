@@ -128,13 +128,14 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
         zfc[static_cast<size_t>(n) * 2 * c_x + c_x + c] = static_cast<float>(b);
       }
     float* d_zfc = pool.upload(zfc);
-    float* sums = pool.alloc_n<float>(static_cast<size_t>(N) * c_x * 2);
+    const int parts = in_stats_parts(N, HW, c_x);
+    float* sums = pool.alloc_n<float>(static_cast<size_t>(N) * (2 * parts + 1) * c_x);
     float4* ncpar = pool.alloc_n<float4>(static_cast<size_t>(N) * c_x);
     float* whf = pool.alloc_n<float>(static_cast<size_t>(N) * c_x);
     float* bhf = pool.alloc_n<float>(N);
     float* d_wh = pool.upload(std::vector<float>(convh_w, convh_w + c_x));
     check_msg(in_stats_launch(h, dt, N, HW, c_x, sums, s), "stats");
-    check_msg(aad_fold_launch(sums, N, HW, c_x, d_zfc, 2 * c_x, 0, c_x, d_wh, convh_b, ncpar, whf, bhf, s), "fold");
+    check_msg(aad_fold_launch(sums, parts, N, HW, c_x, d_zfc, 2 * c_x, 0, c_x, d_wh, convh_b, ncpar, whf, bhf, s), "fold");
     const int cn = bf ? (c_x < 128 ? c_x : 128) : c_x;
     std::vector<float> rows(static_cast<size_t>(2) * c_x * c_attr), bias(2 * c_x);
     for (int c = 0; c < c_x; ++c) {

@@ -59,7 +59,7 @@ def frame_u8(H, W, seed=0, cell=16):
         y, x = int(rng.integers(0, H)), int(rng.integers(0, W))
         h, w = int(rng.integers(8, max(9, H // 4))), int(rng.integers(8, max(9, W // 4)))
         img[y:y + h, x:x + w] = rng.uniform(0, 255, size=3)
-    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
+    return np.ascontiguousarray(np.clip(np.rint(img), 0, 255).astype(np.uint8))
 
 
 def similarity_tfm(H, W, rng, clipped=False, scale=None):

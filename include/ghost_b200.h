@@ -98,6 +98,20 @@ int ghost_net_enable_graph(ghost_net_t* net, int enable);
 /* number of kernel launches one forward of batch B issues, and its dense FLOPs (for bench accounting) */
 int ghost_net_stats(ghost_net_t* net, int B, int* launches, double* flops);
 
+/* Per-op timing of one forward at batch B (the network must have run at batch B at least once, so that its input
+ * buffers hold data): every op is launched `reps` times bracketed by CUDA events on `stream`.  Synchronous.
+ * For each op i < *n_ops (at most max_ops): ms[i] mean duration, flops[i] dense 2*MAC flops, bytes[i] algorithmic
+ * HBM bytes (bandwidth-bound ops), cls[i] kernel class (0 tcgen05 conv, 1 tcgen05 gamma/beta GEMM + fused AAD blend,
+ * 2 CUDA-core conv, 3 instance-norm statistics, 4 bilinear x2, 5 misc), names + i*name_stride a NUL-terminated name. */
+int ghost_net_profile(ghost_net_t* net, int B, int reps, int max_ops, float* ms, double* flops, double* bytes, int* cls,
+                      char* names, int name_stride, int* n_ops, void* stream);
+
+/* Block-level parity hook: copy a named intermediate activation of the last forward at batch B ("m1".."m8" block
+ * inputs, "y1".."y8" block outputs, "a1".."a8" last AAD+ReLU output of a block) into dst as NCHW dst_dtype.
+ * shape4 (optional) receives {N,C,H,W}; dst may be NULL to query the shape only. */
+int ghost_net_debug_get(ghost_net_t* net, int B, const char* name, void* dst, int dst_dtype, int* shape4,
+                        void* stream);
+
 void ghost_net_destroy(ghost_net_t* net);
 
 /* ---- standalone conversions (device buffers) */

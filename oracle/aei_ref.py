@@ -79,23 +79,28 @@ def aad_resblk(sd, p, h, z_attr, z_id, num_blocks):
     return x + h
 
 
-def generate(sd, attrs, z_id, num_blocks):
-    """AADGenerator.forward (AEI_Net.py:122-139)."""
+def generate(sd, attrs, z_id, num_blocks, trace=None):
+    """AADGenerator.forward (AEI_Net.py:122-139).  trace (optional dict) receives the block inputs m1..m8 and
+    block outputs y1..y8 (y8 after tanh) for the block-level parity tests."""
     z = z_id.reshape(z_id.shape[0], -1)
     m = F.conv_transpose2d(z.reshape(z.shape[0], -1, 1, 1), sd["generator.up1.weight"], sd["generator.up1.bias"])
     for k in range(1, 9):
+        if trace is not None:
+            trace["m%d" % k] = m
         y = aad_resblk(sd, "generator.AADBlk%d" % k, m, attrs[k - 1], z, num_blocks)
+        if trace is not None:
+            trace["y%d" % k] = torch.tanh(y) if k == 8 else y
         if k < 8:
             m = _up2(y)
     return torch.tanh(y)
 
 
-def aei_forward(sd, Xt, z_id, backbone, num_blocks):
+def aei_forward(sd, Xt, z_id, backbone, num_blocks, trace=None):
     """AEI_Net.forward (AEI_Net.py:153-156): returns (Y, attrs)."""
     with torch.no_grad():
         sd = {k: v.float() for k, v in sd.items() if v.dtype.is_floating_point}
         attrs = encode(sd, Xt.float(), backbone)
-        return generate(sd, attrs, z_id.float(), num_blocks), attrs
+        return generate(sd, attrs, z_id.float(), num_blocks, trace), attrs
 
 
 # ------------------------------------------------------------------ boundary conversions

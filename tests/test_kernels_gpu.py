@@ -34,6 +34,12 @@ CONV_CASES = [
     ("a1_1x1s2_128", 1, 128, 28, 28, 256, 0, 1, 2, 0, 0),
     ("a1_3x3_cin3_prelu_like", 1, 3, 56, 56, 64, 0, 3, 1, 1, 3),
     ("k32_3x3_32ch", 1, 32, 16, 16, 32, 0, 3, 1, 1, 0),
+    # more tiles than SMs: persistent CTAs loop over several tiles (TMEM double buffer, smem ring wrap-around)
+    ("multi_tile_3x3_64_256px", 2, 64, 256, 256, 64, 0, 3, 1, 1, 0),
+    ("multi_tile_3x3_128_to_64", 3, 128, 128, 128, 64, 0, 3, 1, 1, 0),
+    ("multi_tile_4x4s2_32_to_64", 4, 32, 128, 128, 64, 0, 4, 2, 1, 1),
+    ("multi_tile_deconv_128_to_32", 3, 128, 64, 64, 32, 1, 4, 2, 1, 1),
+    ("multi_tile_3x3_64_to_3", 2, 64, 256, 256, 3, 0, 3, 1, 1, 0),
 ]
 
 
@@ -74,7 +80,7 @@ def test_conv(case, mode):
 
 AAD_CASES = [  # N, H, c_x, c_attr
     (2, 2, 1024, 1024), (1, 4, 1024, 2048), (2, 16, 1024, 512), (1, 32, 512, 256), (1, 64, 256, 128),
-    (1, 128, 128, 64), (1, 64, 64, 64), (2, 32, 64, 32),
+    (1, 128, 128, 64), (1, 64, 64, 64), (2, 32, 64, 32), (3, 256, 64, 64), (2, 128, 128, 64),
 ]
 
 

@@ -1,0 +1,129 @@
+"""GPU parity of the fused paste-back (K11) through the C ABI.
+exact mode: bit-exact against the golden outputs of the reference's get_final_image and against the CPU oracle;
+float mode: <= 1 LSB on >= 99.9 % of the pixels against the torch restatement of the kornia path;
+plus size-independent properties at full 1080p batch sizes."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import ghost_b200
+from ghost_b200 import _lib, synth
+from oracle import paste_float_ref, paste_ref
+from oracle.gen_golden import PASTE_CASES, paste_case_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", PASTE_CASES, ids=[c[0] for c in PASTE_CASES])
+def test_exact_matches_reference_golden(case, golden_dir):
+    name, H, W, nf, seed, clipped, shift = case
+    gold = np.load(os.path.join(golden_dir, name + ".npz"))
+    frame, crops, targets, tfms = paste_case_inputs(*case)
+    masks = [m / 255 for m in gold["masks_u8"]]
+    out = ghost_b200.get_final_image([[c] for c in crops], [[t] for t in targets], frame, [[t] for t in tfms],
+                                     handler=None, masks=masks)
+    y0, y1, x0, x1 = gold["roi"]
+    assert out.dtype == np.uint8 and out.shape == frame.shape
+    assert np.array_equal(out[y0:y1, x0:x1], gold["out_roi"])
+    ref = frame.copy()
+    ref[y0:y1, x0:x1] = gold["out_roi"]
+    assert np.array_equal(out, ref), "%d pixels differ" % int((out != ref).any(axis=2).sum())
+
+
+def test_exact_batch_of_frames_matches_oracle():
+    """Several frames in one launch: 0, 1 and 2 faces per frame, float32 and float64 masks, an affine whose
+    square leaves the frame, in-place output."""
+    rng = np.random.default_rng(42)
+    H, W, F_ = 360, 640, 4
+    frames = np.stack([synth.frame_u8(H, W, seed=50 + f) for f in range(F_)])
+    crops = synth.crops_u8(3, seed=51)
+    masks = np.stack([synth.soft_mask(rng) for _ in range(2)])
+    tfms = np.stack([synth.similarity_tfm(H, W, rng), synth.similarity_tfm(H, W, rng, clipped=True),
+                     synth.similarity_tfm(H, W, rng)])
+    face_frame = np.array([0, 2, 2], np.int32)      # frame 1 and 3 have no face
+    face_crop = np.array([2, 0, 1], np.int32)
+    face_mask = np.array([1, 0, 1], np.int32)
+    ref = frames.copy()
+    ref[0] = paste_ref.get_final_image_ref([[crops[2]]], [masks[1]], frames[0], [[tfms[0]]])
+    ref[2] = paste_ref.get_final_image_ref([[crops[0]], [crops[1]]], [masks[0], masks[1]], frames[2],
+                                           [[tfms[1]], [tfms[2]]])
+    dev = torch.from_numpy(frames).cuda()
+    out = ghost_b200.paste_back(dev, crops, masks, tfms, face_frame, face_crop, face_mask, mode="exact", out=dev)
+    assert out.data_ptr() == dev.data_ptr()
+    assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_exact_from_generator_output():
+    """crop_kind = Y: the kernel converts the generator's NHWC output itself (faceshifter_run.py:20-21) and
+    gives the same frame as converting first."""
+    rng = np.random.default_rng(7)
+    H, W = 300, 500
+    frame = synth.frame_u8(H, W, seed=3)
+    Y = (synth.crops_pm1(1, seed=5) * 1.02).clamp(-1, 1)
+    u8 = paste_ref.postprocess_ref(Y.numpy())
+    mask = synth.soft_mask(rng)
+    tfm = synth.similarity_tfm(H, W, rng)
+    ref = paste_ref.get_final_image_ref([[u8[0]]], [mask], frame, [[tfm]])
+    y_nhwc = Y.permute(0, 2, 3, 1).contiguous().cuda()
+    out = ghost_b200.paste_back(frame[None], (y_nhwc.data_ptr(), _lib.F32, 1), mask[None], tfm[None],
+                                np.zeros(1, np.int32), mode="exact")
+    assert np.array_equal(out[0].cpu().numpy(), ref)
+    yb = y_nhwc.bfloat16()
+    u8b = paste_ref.postprocess_ref(yb.float().cpu().permute(0, 3, 1, 2).numpy())
+    refb = paste_ref.get_final_image_ref([[u8b[0]]], [mask], frame, [[tfm]])
+    outb = ghost_b200.paste_back(frame[None], (yb.data_ptr(), _lib.BF16, 1), mask[None], tfm[None],
+                                 np.zeros(1, np.int32), mode="exact")
+    assert np.array_equal(outb[0].cpu().numpy(), refb)
+
+
+def test_float_mode_matches_kornia_restatement():
+    rng = np.random.default_rng(9)
+    H, W = 360, 640
+    frame = synth.frame_u8(H, W, seed=9)
+    crops = synth.crops_u8(2, seed=9)
+    masks = [synth.soft_mask(rng), synth.soft_mask(rng)]
+    t0 = synth.similarity_tfm(H, W, rng)
+    t1 = t0.copy()
+    t1[:, 2] += 25.0                                   # overlapping second face: composes through uint8
+    ref = paste_float_ref.composite_frame_ref(frame, [crops[0], crops[1]], masks, [t0, t1])
+    out = ghost_b200.get_final_video([[crops[0]], [crops[1]]], [[crops[0][:224, :224]], [crops[1][:224, :224]]],
+                                     [frame], [[t0], [t1]], None, 30.0, handler=None,
+                                     masks=[[masks[0]], [masks[1]]])[0]
+    d = np.abs(out.astype(int) - ref.astype(int))
+    assert (ref != frame).any(), "the oracle did not change the frame"
+    assert d.max() <= 2 and (d <= 1).mean() >= 0.999 and (d == 0).mean() >= 0.97, (d.max(), (d <= 1).mean(),
+                                                                                   (d == 0).mean())
+
+
+def test_properties_at_1080p_batch():
+    """Size-independent properties on a full batch of 1080p frames: zero mask -> identity; pixels outside every
+    face box untouched; an empty face list copies the batch; the result does not depend on batching."""
+    rng = np.random.default_rng(3)
+    H, W, F_ = 1080, 1920, 16
+    base = synth.frame_u8(H, W, seed=1)
+    frames = torch.from_numpy(base).cuda()[None].repeat(F_, 1, 1, 1)
+    frames += torch.arange(F_, device="cuda", dtype=torch.uint8)[:, None, None, None]
+    crops = synth.crops_u8(F_, seed=2)
+    mask = synth.soft_mask(rng)[None]
+    tfms = np.stack([synth.similarity_tfm(H, W, rng, clipped=(f % 5 == 4)) for f in range(F_)])
+    ff = np.arange(F_, dtype=np.int32)
+    zero = ghost_b200.paste_back(frames, crops, np.zeros_like(mask), tfms, ff, face_mask=np.zeros(F_, np.int32))
+    assert torch.equal(zero, frames)
+    none = ghost_b200.paste_back(frames, crops[:0], mask, tfms[:0], ff[:0])
+    assert torch.equal(none, frames)
+    out = ghost_b200.paste_back(frames, crops, mask, tfms, ff, face_mask=np.zeros(F_, np.int32))
+    changed = (out != frames).any(dim=3)
+    assert changed.any()
+    for f in (0, 4, F_ - 1):
+        inv = paste_ref.invert_affine(tfms[f])
+        c = np.array([[0, 0, 1], [224, 0, 1], [0, 224, 1], [224, 224, 1]], np.float64) @ inv.T
+        ys, xs = torch.nonzero(changed[f], as_tuple=True)
+        assert xs.min().item() >= np.floor(c[:, 0].min()) - 1 and xs.max().item() <= np.ceil(c[:, 0].max()) + 1
+        assert ys.min().item() >= np.floor(c[:, 1].min()) - 1 and ys.max().item() <= np.ceil(c[:, 1].max()) + 1
+        single = ghost_b200.paste_back(frames[f:f + 1], crops[f:f + 1], mask, tfms[f:f + 1], np.zeros(1, np.int32))
+        assert torch.equal(single[0], out[f])
+    # one frame against the CPU oracle at full size
+    ref = paste_ref.get_final_image_ref([[crops[4]]], [mask[0]], frames[4].cpu().numpy(), [[tfms[4]]])
+    assert np.array_equal(out[4].cpu().numpy(), ref)
