@@ -94,6 +94,13 @@ __global__ void __launch_bounds__(256) simt_conv_kernel(const SimtConvParams p) 
       Bs[lk + q][lrow] = b;
     }
     __syncthreads();
+    // two-level (blocked) summation: the 16 products of a K tile are summed on their own and then added to the
+    // running total, which keeps the fp32 rounding error of K = 9216..18432 term sums near that of a pairwise sum
+    float part[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) part[i][j] = 0.f;
 #pragma unroll
     for (int kk = 0; kk < TK; ++kk) {
       float a[4], b[4];
@@ -104,8 +111,12 @@ __global__ void __launch_bounds__(256) simt_conv_kernel(const SimtConvParams p) 
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) part[i][j] = fmaf(a[i], b[j], part[i][j]);
     }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] += part[i][j];
     __syncthreads();
   }
 
