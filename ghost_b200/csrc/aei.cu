@@ -337,6 +337,13 @@ void Net::build_aei(ExecPlan& p) {
       if (bf) {
         AadArgs args;
         args.h = h.p; args.c_x = cx; args.ncpar = ncpar; args.wh_fold = whf; args.bh_fold = bhf;
+        if (cx > 128) {  // several N tiles per pixel: the sigmoid mask is computed once, ahead of the GEMM
+          float* mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
+          const Act hh = h;
+          add_op(lname + ".mask", [=](cudaStream_t s) { return aad_mask_launch(hh.p, B, HW, cx, whf, bhf, mask, s); },
+                 kOpStats, static_cast<double>(B) * HW * cx * esz);
+          args.mask = mask;
+        }
         add_conv(lname + ".gemm_blend", za, 0, za.C, Taps::point(), hw, hw, lname + ".gb", OutView::dense(a),
                  Epilogue(), &args);
       } else {

@@ -221,7 +221,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     if (const char* e = encode_tmap(&p.tmB, w.wb, 2, dims, str, box, swz)) return e;
   }
   const int stage_bytes = (128 + p.BN) * p.kc * 2;
-  int stages = (220 * 1024) / stage_bytes;
+  const int aad_bytes = aad ? 3 * ((p.BN >> 1) >> 6) * 16384 : 0;  // two h tiles + one staging tile
+  int stages = (220 * 1024 - aad_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
   const int num_kb = p.ntaps * p.kc_per_tap;
   if (stages > num_kb + 1 && num_kb >= 2) stages = num_kb + 1;
@@ -243,8 +244,21 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.ncpar = aad->ncpar;
     p.wh_fold = aad->wh_fold;
     p.bh_fold = aad->bh_fold;
-    p.mask = nullptr;
+    p.mask = aad->mask;
     if (!w.bias) return "lower_conv: AAD needs the gamma/beta bias vector";
+    if (aad->c_x % 64) return "lower_conv: AAD c_x must be a multiple of 64";
+    if (p.tiles_n > 1 && !aad->mask) return "lower_conv: AAD with c_x > 128 needs the precomputed mask";
+    if (out.sw != aad->c_x || out.off != 0 || out.sh != static_cast<long long>(Wo) * aad->c_x ||
+        out.sn != static_cast<long long>(Ho) * Wo * aad->c_x)
+      return "lower_conv: AAD output must be a dense NHWC tensor of c_x channels";
+    {
+      const uint64_t cx = static_cast<uint64_t>(aad->c_x);
+      const uint64_t dims[4] = {cx, static_cast<uint64_t>(Wo), static_cast<uint64_t>(Ho), static_cast<uint64_t>(in.N)};
+      const uint64_t str[3] = {cx * eb, static_cast<uint64_t>(Wo) * cx * eb, static_cast<uint64_t>(Ho) * Wo * cx * eb};
+      const uint32_t box[4] = {64u, static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
+      if (const char* e = encode_tmap(&p.tmH, aad->h, 4, dims, str, box, 128)) return e;
+      if (const char* e = encode_tmap(&p.tmO, out.p, 4, dims, str, box, 128)) return e;
+    }
   } else {
     p.mode = kModeLinear;
     p.act1 = epi.act1; p.slope = epi.slope; p.slope_c = epi.slope_c;

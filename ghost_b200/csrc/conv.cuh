@@ -79,6 +79,7 @@ struct AadArgs {  // only for the fused AAD epilogue
   const float4* ncpar = nullptr;
   const float* wh_fold = nullptr;
   const float* bh_fold = nullptr;
+  const float* mask = nullptr;  // precomputed sigmoid mask [N*H*W]; required when c_x > 128
 };
 
 // A lowered, launch-ready op.

@@ -136,6 +136,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __shared__ uint64_t empty_bar[8];
   __shared__ uint64_t tfull_bar[2];
   __shared__ uint64_t tempty_bar[2];
+  __shared__ uint64_t hfull_bar[2];   // AAD mode: h tile landed in shared memory
+  __shared__ uint64_t hempty_bar[2];  // AAD mode: epilogue done with the h tile
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
@@ -152,6 +154,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int rows_used = p.bw * p.bh * p.bn;
   const uint32_t tx_bytes = rows_used * row_bytes + b_stage_bytes;
 
+  // AAD mode: two h tiles and one output tile behind the operand ring, each cn/64 boxes of [128 rows][128 B]
+  const int cn = p.BN >> 1;
+  const int hbox = cn >> 6;
+  const int htile_bytes = hbox * 16384;
+  uint8_t* hbuf = smem + p.stages * stage_bytes;
+  uint8_t* obuf = hbuf + 2 * htile_bytes;
+
   const int num_kb = p.ntaps * p.kc_per_tap / p.splits;  // K blocks handled by this CTA
   const int kb0 = blockIdx.y * num_kb;
   const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
@@ -165,12 +174,18 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 4);
+      mbar_init(&hfull_bar[i], 1);
+      mbar_init(&hempty_bar[i], 4);
     }
     fence_mbar_init();
   }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmA);
     prefetch_tmap(&p.tmB);
+    if (p.mode == kModeAAD) {
+      prefetch_tmap(&p.tmH);
+      prefetch_tmap(&p.tmO);
+    }
   }
   if (warp == 1) tmem_alloc(&tmem_base_smem, p.tmem_cols);
   tc_fence_before();
@@ -185,9 +200,17 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       int stage = 0;
       uint32_t phase = 0;
       bool ok = true;
-      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x) {
+      int hit = 0;
+      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit) {
         const TileCoord t = decode_tile(p, tile);
         const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+        if (p.mode == kModeAAD) {
+          const int hs = hit & 1;
+          if (!mbar_wait(&hempty_bar[hs], ((hit >> 1) & 1) ^ 1u, &abort_flag)) break;
+          mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
+          for (int b = 0; b < hbox; ++b)
+            tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
+        }
         for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
           const int tap = kb / p.kc_per_tap;
           const int kci = kb - tap * p.kc_per_tap;
@@ -282,58 +305,64 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         }
       } else {
         // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
-        const int cn = p.BN >> 1;
+        // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels), the blended tile is staged in
+        // shared memory and leaves by TMA store: no row-by-row global access.
+        const int hs = it & 1;
         const int c_base = t.nt * cn;
-        const long long pix = (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow;
-        const __nv_bfloat16* hrow = p.h + pix * p.c_x;
+        const int nc = min(n, p.Nimg - 1);  // rows outside the tensor still index valid parameters
+        const uint8_t* hrow = hbuf + hs * htile_bytes + r * 128;
+        const int sw = r & 7;
+        if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], (it >> 1) & 1, &abort_flag))) break;
         float m = 0.f;
-        if (valid) {
-          if (p.mask) {
-            m = __ldg(p.mask + pix);
-          } else {
-            // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh.
-            // Runs while the tensor core is still producing this tile's gamma/beta.
-            const float* wrow = p.wh_fold + static_cast<long long>(n) * p.c_x;
-            float acc = 0.f;
-            for (int c = 0; c < p.c_x; c += 8) {
-              const uint4 q = __ldg(reinterpret_cast<const uint4*>(hrow + c));
-              const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + c));
-              const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + c) + 1);
-              acc += bf16lo(q.x) * w0.x + bf16hi(q.x) * w0.y + bf16lo(q.y) * w0.z + bf16hi(q.y) * w0.w;
-              acc += bf16lo(q.z) * w1.x + bf16hi(q.z) * w1.y + bf16lo(q.w) * w1.z + bf16hi(q.w) * w1.w;
+        if (p.mask) {
+          if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
+        } else {
+          // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh (single N tile: cn == c_x).
+          // Runs while the tensor core is still producing this tile's gamma/beta.
+          const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x;
+          float acc = 0.f;
+          for (int bx = 0; bx < hbox; ++bx) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const uint4 v = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q ^ sw) << 4));
+              const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + bx * 64 + q * 8));
+              const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + bx * 64 + q * 8) + 1);
+              acc += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
+              acc += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
             }
-            acc += __ldg(p.bh_fold + n);
-            m = 1.f / (1.f + __expf(-acc));
           }
+          acc += __ldg(p.bh_fold + nc);
+          m = 1.f / (1.f + __expf(-acc));
         }
         if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
         tc_fence_after();
-        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+        // the previous tile's TMA store must have finished reading the staging tile before it is overwritten
+        if (threadIdx.x == 64) bulk_wait_read<0>();
+        named_bar_sync(1, 128);
+        const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
+        const float* bg = p.bias + t.nt * p.BN;
+        const float* bb = bg + cn;
+        uint8_t* orow = obuf + r * 128;
         for (int j = 0; j < cn; j += 16) {
           uint32_t g[16], b[16];
           __syncwarp();
           tmem_ld16(t_addr + j, g);
           tmem_ld16(t_addr + cn + j, b);
+          const int bx = j >> 6, q0 = (j & 63) >> 3;
+          const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q0 ^ sw) << 4));
+          const uint4 h1 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + (((q0 + 1) ^ sw) << 4));
           tmem_ld_wait();
-          const int c0 = c_base + j;
-          if (!(valid && c0 < p.c_x)) continue;
-          const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(hrow + c0));
-          const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(hrow + c0) + 1);
-          const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-          const float4* par = p.ncpar + static_cast<long long>(n) * p.c_x + c0;
-          const float* bg = p.bias + t.nt * p.BN + j;
-          const float* bb = bg + cn;
+          const uint32_t qq[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
           float o[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const float x = (i & 1) ? bf16hi(qq[i >> 1]) : bf16lo(qq[i >> 1]);
-            const float4 pr = __ldg(par + i);
+            const float4 pr = __ldg(par + j + i);
             const float hn = fmaf(x, pr.x, pr.y);
-            const float A = fmaf(__uint_as_float(g[i]) + __ldg(bg + i), hn, __uint_as_float(b[i]) + __ldg(bb + i));
+            const float A = fmaf(__uint_as_float(g[i]) + __ldg(bg + j + i), hn, __uint_as_float(b[i]) + __ldg(bb + j + i));
             const float I = fmaf(pr.z, hn, pr.w);
             o[i] = fmaxf(fmaf(m, I - A, A), 0.f);
           }
-          __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + o_pix + c0;
           uint4 s0, s1;
           s0.x = pack_bf16(o[0], o[1]);
           s0.y = pack_bf16(o[2], o[3]);
@@ -343,9 +372,18 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           s1.y = pack_bf16(o[10], o[11]);
           s1.z = pack_bf16(o[12], o[13]);
           s1.w = pack_bf16(o[14], o[15]);
-          reinterpret_cast<uint4*>(op)[0] = s0;
-          reinterpret_cast<uint4*>(op)[1] = s1;
+          *reinterpret_cast<uint4*>(orow + bx * 16384 + ((q0 ^ sw) << 4)) = s0;
+          *reinterpret_cast<uint4*>(orow + bx * 16384 + (((q0 + 1) ^ sw) << 4)) = s1;
         }
+        fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to the TMA (async proxy)
+        tc_fence_before();
+        named_bar_sync(1, 128);
+        if (threadIdx.x == 64) {
+          for (int bx = 0; bx < hbox; ++bx)
+            tma_store_4d(&p.tmO, obuf + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);
+          bulk_commit();
+        }
+        if (lane == 0) mbar_arrive(&hempty_bar[hs]);
       }
       // hand the accumulator stage back to the MMA warp
       tc_fence_before();
@@ -355,6 +393,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   }
 
   // ------------------------------ teardown ------------------------------------
+  if (threadIdx.x == 64) bulk_wait<0>();  // outstanding TMA stores of the AAD epilogue
   tc_fence_before();
   __syncthreads();
   if (abort_flag && threadIdx.x == 0 && p.err) {
@@ -369,7 +408,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 
 int igemm_smem_bytes(const IgemmParams& p) {
   const int row_bytes = p.kc * 2;
-  return p.stages * (128 * row_bytes + p.BN * row_bytes) + 1024;
+  const int aad = p.mode == kModeAAD ? 3 * ((p.BN >> 1) >> 6) * 16384 : 0;  // 2 h tiles + 1 staging tile
+  return p.stages * (128 * row_bytes + p.BN * row_bytes) + aad + 1024;
 }
 
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {

@@ -17,6 +17,8 @@ enum Act2 : int { kAct2None = 0, kAct2Tanh = 1 };
 struct alignas(64) IgemmParams {
   CUtensorMap tmA;  // activations, NHWC (4-D) or parity-split NHWC (5-D, stride-2 convs)
   CUtensorMap tmB;  // packed weights [Cout_pad][taps*Cin], K-major
+  CUtensorMap tmH;  // AAD mode: block input h, NHWC, boxes of 64 channels x (bw, bh, bn), SWIZZLE_128B
+  CUtensorMap tmO;  // AAD mode: output tensor, same boxes (TMA store)
 
   // ---- M tiling: one tile = bn images x bh rows x bw cols (<= 128 GEMM rows)
   int a_rank;  // 4 or 5
@@ -51,7 +53,9 @@ struct alignas(64) IgemmParams {
   int act2;
 
   // ---- epilogue (AAD blend): columns [0,cn) = gamma_attr, [cn,2cn) = beta_attr, cn = BN/2
-  const __nv_bfloat16* h;  // raw block input, NHWC, pixel stride c_x
+  // The h tile is TMA-loaded into shared memory, blended there and TMA-stored (nothing is read row by row
+  // from global memory); when c_x > 128 (several N tiles per pixel) the sigmoid mask comes precomputed in `mask`.
+  const __nv_bfloat16* h;  // raw block input, NHWC, pixel stride c_x (kept for reference / debugging)
   int c_x;
   const float4* ncpar;  // [Nimg][c_x] {rstd, -mu*rstd, gamma_id, beta_id}
   const float* wh_fold;     // [Nimg][c_x] conv_h weight * rstd

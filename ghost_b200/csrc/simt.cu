@@ -334,7 +334,43 @@ __global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h,
   }
 }
 
+// sigmoid(conv_h(instance_norm(h))) per pixel with the normalisation folded into wh/bh: one warp per pixel,
+// 16-byte loads, warp-shuffle reduction over the channels (used when c_x > 128, i.e. several N tiles per pixel).
+__global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __restrict__ h, long long npix, int HW, int C,
+                                                        const float* __restrict__ wh_fold,
+                                                        const float* __restrict__ bh_fold, float* __restrict__ mask) {
+  const int lane = threadIdx.x & 31;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  for (long long pix = warp0; pix < npix; pix += nwarps) {
+    const int n = static_cast<int>(pix / HW);
+    const __nv_bfloat16* hrow = h + pix * C;
+    const float* wrow = wh_fold + static_cast<long long>(n) * C;
+    float acc = 0.f;
+    for (int c = lane * 8; c < C; c += 256) {
+      float v[8];
+      load8(hrow + c, v);
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + c));
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + c) + 1);
+      acc += v[0] * w0.x + v[1] * w0.y + v[2] * w0.z + v[3] * w0.w + v[4] * w1.x + v[5] * w1.y + v[6] * w1.z + v[7] * w1.w;
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) mask[pix] = 1.f / (1.f + __expf(-(acc + __ldg(bh_fold + n))));
+  }
+}
+
 }  // namespace
+
+const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
+                            cudaStream_t s) {
+  if (C % 8) return "aad_mask: C must be a multiple of 8";
+  const long long npix = static_cast<long long>(N) * HW;
+  long long blocks = (npix + 7) / 8;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  aad_mask_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(h), npix, HW, C,
+                                                               wh_fold, bh_fold, mask);
+  return last_err();
+}
 
 namespace {
 // pixels per block of the statistics kernel for a tensor of N images x HW pixels x C channels

@@ -45,6 +45,10 @@ const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, con
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
                             cudaStream_t s);
 
+// bf16 mode, c_x > 128: the per-pixel sigmoid mask of an AADLayer, mask[N*HW] fp32.
+const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
+                            cudaStream_t s);
+
 // Unfused AAD blend (+ReLU) used by the fp32 mode: gb = [N,H,W,2C] (gamma | beta, bias included).
 const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype, int N, int HW, int C,
                              const float4* ncpar, const float* wh_fold, const float* bh_fold, cudaStream_t s);

@@ -164,6 +164,11 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
       pw.wb = pool.upload_bf16(padded);
       AadArgs args;
       args.h = h; args.c_x = c_x; args.ncpar = ncpar; args.wh_fold = whf; args.bh_fold = bhf;
+      if (c_x > 128) {
+        float* mask = pool.alloc_n<float>(static_cast<size_t>(N) * HW);
+        check_msg(aad_mask_launch(h, N, HW, c_x, whf, bhf, mask, s), "aad mask");
+        args.mask = mask;
+      }
       LaunchOp op;
       check_msg(lower_conv(&op, za, 0, c_attr, Taps::point(), H, W, pw, OutView::dense(o), Epilogue(), false,
                            device_err_word(), &args),
