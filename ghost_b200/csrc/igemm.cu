@@ -173,9 +173,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 4);
+      mbar_init(&tempty_bar[i], kIgemmEpiWarps);
       mbar_init(&hfull_bar[i], 1);
-      mbar_init(&hempty_bar[i], 4);
+      mbar_init(&hempty_bar[i], kIgemmEpiWarps);
     }
     fence_mbar_init();
   }
@@ -277,6 +277,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   } else {
     // ============================== epilogue ==================================
     const int lg = warp & 3;            // TMEM lane group this warp may read
+    const int half = (warp - 2) >> 2;   // which half of the tile's columns this warp handles
     const int r = lg * 32 + lane;       // GEMM row inside the tile
     const int rn = r / (p.bh * p.bw);
     const int rh = (r / p.bw) % p.bh;
@@ -295,7 +296,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         tc_fence_after();
         const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
-        for (int j = 0; j < p.BN; j += 16) {
+        const int nch = p.BN >> 4, ch0 = half ? (nch + 1) >> 1 : 0, ch1 = half ? nch : (nch + 1) >> 1;
+        for (int j = ch0 * 16; j < ch1 * 16; j += 16) {
           uint32_t v[16];
           __syncwarp();
           tmem_ld16(t_addr + j, v);
@@ -338,12 +340,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         tc_fence_after();
         // the previous tile's TMA store must have finished reading the staging tile before it is overwritten
         if (threadIdx.x == 64) bulk_wait_read<0>();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 32 * kIgemmEpiWarps);
         const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
         const float* bg = p.bias + t.nt * p.BN;
         const float* bb = bg + cn;
         uint8_t* orow = obuf + r * 128;
-        for (int j = 0; j < cn; j += 16) {
+        for (int j = half * (cn >> 1); j < (half + 1) * (cn >> 1); j += 16) {
           uint32_t g[16], b[16];
           __syncwarp();
           tmem_ld16(t_addr + j, g);
@@ -377,7 +379,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         }
         fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to the TMA (async proxy)
         tc_fence_before();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 32 * kIgemmEpiWarps);
         if (threadIdx.x == 64) {
           for (int bx = 0; bx < hbox; ++bx)
             tma_store_4d(&p.tmO, obuf + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);

@@ -8,7 +8,8 @@
 namespace ghost {
 
 constexpr int kIgemmMaxTaps = 16;
-constexpr int kIgemmThreads = 192;  // warp0 TMA, warp1 MMA, warps2-5 epilogue
+constexpr int kIgemmEpiWarps = 8;                            // two warps per TMEM lane group, splitting the columns
+constexpr int kIgemmThreads = 64 + 32 * kIgemmEpiWarps;      // warp0 TMA, warp1 MMA, warps2-9 epilogue
 
 enum IgemmMode : int { kModeLinear = 0, kModeAAD = 1 };
 enum Act1 : int { kActNone = 0, kActLeaky = 1, kActPRelu = 2, kActRelu = 3 };

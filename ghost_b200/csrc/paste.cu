@@ -124,65 +124,87 @@ __device__ __forceinline__ void paste_float_px(const PasteParams& p, const CropS
   }
 }
 
-// Each thread owns PX horizontally consecutive pixels of one frame (PX = 4 -> three 32-bit words).
+// Each thread owns PX horizontally consecutive pixels of one frame: PX = 16 -> three 16-byte vectors,
+// PX = 4 -> three 32-bit words.  Spans that no face box touches (almost all of a 1080p frame) are a straight
+// vector copy; only touched spans run the per-pixel compositing.
 template <int PX>
-__global__ void __launch_bounds__(256) paste_kernel(const PasteParams p) {
+__global__ void __launch_bounds__(128) paste_kernel(const PasteParams p) {
   const int f = blockIdx.z;
   const int xg = blockIdx.x * blockDim.x + threadIdx.x;  // pixel group index
   const int y = blockIdx.y;
   const int x_base = xg * PX;
   if (x_base >= p.W) return;
   const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x_base) * 3;
-  uint8_t px[PX * 3];
-  if (PX == 4) {
+  constexpr int NB = PX * 3;
+  union alignas(16) Span {
+    uint4 v[(NB + 15) / 16];
+    uint32_t w[(NB + 3) / 4];
+    uint8_t b[NB];
+  } sp;
+  if (PX == 16) {
+    const uint4* s = reinterpret_cast<const uint4*>(p.frames_in + off);
+    sp.v[0] = __ldg(s);
+    sp.v[1] = __ldg(s + 1);
+    sp.v[2] = __ldg(s + 2);
+  } else if (PX == 4) {
     const uint32_t* s = reinterpret_cast<const uint32_t*>(p.frames_in + off);
-    uint32_t* d = reinterpret_cast<uint32_t*>(px);
-    d[0] = __ldg(s);
-    d[1] = __ldg(s + 1);
-    d[2] = __ldg(s + 2);
+    sp.w[0] = __ldg(s);
+    sp.w[1] = __ldg(s + 1);
+    sp.w[2] = __ldg(s + 2);
   } else {
 #pragma unroll
-    for (int i = 0; i < PX * 3; ++i) px[i] = p.frames_in[off + i];
+    for (int i = 0; i < NB; ++i) sp.b[i] = p.frames_in[off + i];
   }
   const int fs = __ldg(p.face_start + f), fe = __ldg(p.face_start + f + 1);
-  CropSrc cs{p.crops, p.crop_kind};
-  for (int i = 0; i < PX; ++i) {
-    const int x = x_base + i;
-    bool touched = false;
-    double fd[3];
-    float ff[3];
-    for (int j = fs; j < fe; ++j) {
-      const PasteFace& face = p.faces[j];
-      if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
-      if (!touched) {
-        touched = true;
+  bool span_touched = false;
+  for (int j = fs; j < fe; ++j) {
+    const PasteFace& face = p.faces[j];
+    span_touched |= (x_base + PX > face.x0 && x_base < face.x1 && y >= face.y0 && y < face.y1);
+  }
+  if (span_touched) {
+    CropSrc cs{p.crops, p.crop_kind};
+    for (int i = 0; i < PX; ++i) {
+      const int x = x_base + i;
+      bool touched = false;
+      double fd[3];
+      float ff[3];
+      for (int j = fs; j < fe; ++j) {
+        const PasteFace& face = p.faces[j];
+        if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
+        if (!touched) {
+          touched = true;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          fd[c] = static_cast<double>(px[i * 3 + c]);
-          ff[c] = static_cast<float>(px[i * 3 + c]);
+          for (int c = 0; c < 3; ++c) {
+            fd[c] = static_cast<double>(sp.b[i * 3 + c]);
+            ff[c] = static_cast<float>(sp.b[i * 3 + c]);
+          }
         }
+        if (p.mode == kPasteExact)
+          paste_exact_px(p, cs, face, x, y, fd);
+        else
+          paste_float_px(p, cs, face, x, y, ff);
       }
-      if (p.mode == kPasteExact)
-        paste_exact_px(p, cs, face, x, y, fd);
-      else
-        paste_float_px(p, cs, face, x, y, ff);
-    }
-    if (touched) {
+      if (touched) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-        px[i * 3 + c] = p.mode == kPasteExact ? static_cast<uint8_t>(static_cast<int>(fd[c]))
-                                              : static_cast<uint8_t>(static_cast<int>(ff[c]));
+        for (int c = 0; c < 3; ++c)
+          sp.b[i * 3 + c] = p.mode == kPasteExact ? static_cast<uint8_t>(static_cast<int>(fd[c]))
+                                                  : static_cast<uint8_t>(static_cast<int>(ff[c]));
+      }
     }
   }
-  if (PX == 4) {
+  if (PX == 16) {
+    uint4* d = reinterpret_cast<uint4*>(p.frames_out + off);
+    d[0] = sp.v[0];
+    d[1] = sp.v[1];
+    d[2] = sp.v[2];
+  } else if (PX == 4) {
     uint32_t* d = reinterpret_cast<uint32_t*>(p.frames_out + off);
-    const uint32_t* s = reinterpret_cast<const uint32_t*>(px);
-    d[0] = s[0];
-    d[1] = s[1];
-    d[2] = s[2];
+    d[0] = sp.w[0];
+    d[1] = sp.w[1];
+    d[2] = sp.w[2];
   } else {
 #pragma unroll
-    for (int i = 0; i < PX * 3; ++i) p.frames_out[off + i] = px[i];
+    for (int i = 0; i < NB; ++i) p.frames_out[off + i] = sp.b[i];
   }
 }
 
@@ -330,12 +352,16 @@ void paste_prepare_face(PasteFace* f, const double* t, int H, int W, int crop_in
 
 const char* paste_back_launch(const PasteParams& p, cudaStream_t s) {
   if (p.F <= 0 || p.H <= 0 || p.W <= 0) return "paste_back: empty frame batch";
-  if (p.W % 4 == 0) {
-    dim3 grid((p.W / 4 + 255) / 256, p.H, p.F);
-    paste_kernel<4><<<grid, 256, 0, s>>>(p);
+  const bool al16 = (reinterpret_cast<uintptr_t>(p.frames_in) % 16 == 0) && (reinterpret_cast<uintptr_t>(p.frames_out) % 16 == 0);
+  if (p.W % 16 == 0 && al16) {
+    dim3 grid((p.W / 16 + 127) / 128, p.H, p.F);
+    paste_kernel<16><<<grid, 128, 0, s>>>(p);
+  } else if (p.W % 4 == 0 && al16) {
+    dim3 grid((p.W / 4 + 127) / 128, p.H, p.F);
+    paste_kernel<4><<<grid, 128, 0, s>>>(p);
   } else {
-    dim3 grid((p.W + 255) / 256, p.H, p.F);
-    paste_kernel<1><<<grid, 256, 0, s>>>(p);
+    dim3 grid((p.W + 127) / 128, p.H, p.F);
+    paste_kernel<1><<<grid, 128, 0, s>>>(p);
   }
   return last_err();
 }

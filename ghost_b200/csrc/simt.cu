@@ -40,6 +40,43 @@ inline const char* last_err() {
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }
 
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 q;
+  __nv_bfloat162 t;
+  t = __floats2bfloat162_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
 // ---------------------------------------------------------------------------
 // Direct convolution as a shared-memory tiled GEMM on CUDA cores.
 // 64 pixels x 64 output channels per block, 256 threads, 4x4 outputs per thread.
@@ -151,11 +188,95 @@ __global__ void __launch_bounds__(256) simt_conv_kernel(const SimtConvParams p) 
   }
 }
 
+// ---------------------------------------------------------------------------
+// Direct convolution for the 3-channel input layers (encoder conv1, iresnet stem): one thread per output
+// pixel keeps all COUT accumulators in registers, the [taps*3][COUT] weight matrix sits in shared memory and
+// is read as broadcast float4s.  K = taps*3 <= 48, so the layer is FMA-issue bound, not a GEMM-tile problem.
+// ---------------------------------------------------------------------------
+template <typename T, int COUT>
+__global__ void __launch_bounds__(128) rgb_conv_kernel(const SimtConvParams p) {
+  __shared__ __align__(16) float ws[48 * COUT];
+  __shared__ float bs[COUT], ss[COUT];
+  const int K = p.ntaps * 3;
+  for (int i = threadIdx.x; i < K * COUT; i += blockDim.x) {
+    const int k = i / COUT, co = i - k * COUT;
+    ws[i] = __ldg(p.w + static_cast<long long>(co) * K + k);
+  }
+  for (int i = threadIdx.x; i < COUT; i += blockDim.x) {
+    bs[i] = p.bias ? __ldg(p.bias + i) : 0.f;
+    ss[i] = p.act1 == kActPRelu ? __ldg(p.slope_c + i) : p.slope;
+  }
+  __syncthreads();
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  const long long m = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (m >= M) return;
+  const int ow = static_cast<int>(m % p.Wo);
+  const long long t = m / p.Wo;
+  const int oh = static_cast<int>(t % p.Ho);
+  const int n = static_cast<int>(t / p.Ho);
+  const T* in = reinterpret_cast<const T*>(p.in);
+  float acc[COUT];
+#pragma unroll
+  for (int i = 0; i < COUT; ++i) acc[i] = 0.f;
+  for (int tap = 0; tap < p.ntaps; ++tap) {
+    const int ih = oh * p.stride + p.dh[tap], iw = ow * p.stride + p.dw[tap];
+    if (ih < 0 || ih >= p.H || iw < 0 || iw >= p.W) continue;
+    const T* px = in + ((static_cast<long long>(n) * p.H + ih) * p.W + iw) * 3;
+    const float x[3] = {ldf(px), ldf(px + 1), ldf(px + 2)};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float4* wr = reinterpret_cast<const float4*>(ws + (tap * 3 + c) * COUT);
+#pragma unroll
+      for (int q = 0; q < COUT / 4; ++q) {
+        const float4 w = wr[q];
+        acc[4 * q] = fmaf(x[c], w.x, acc[4 * q]);
+        acc[4 * q + 1] = fmaf(x[c], w.y, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(x[c], w.z, acc[4 * q + 2]);
+        acc[4 * q + 3] = fmaf(x[c], w.w, acc[4 * q + 3]);
+      }
+    }
+  }
+  T* out = reinterpret_cast<T*>(p.out) + n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+#pragma unroll
+  for (int q = 0; q < COUT / 8; ++q) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float a = acc[8 * q + i] + bs[8 * q + i];
+      if (p.act1 == kActLeaky || p.act1 == kActPRelu)
+        a = a > 0.f ? a : a * ss[8 * q + i];
+      else if (p.act1 == kActRelu)
+        a = fmaxf(a, 0.f);
+      v[i] = a;
+    }
+    store8(out + 8 * q, v);
+  }
+}
+
+template <typename T>
+const char* rgb_conv_dispatch(const SimtConvParams& p, cudaStream_t s) {
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  const unsigned blocks = static_cast<unsigned>((M + 127) / 128);
+  if (p.Cout == 32)
+    rgb_conv_kernel<T, 32><<<blocks, 128, 0, s>>>(p);
+  else
+    rgb_conv_kernel<T, 64><<<blocks, 128, 0, s>>>(p);
+  return last_err();
+}
+
 }  // namespace
 
 const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s) {
   const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
   if (M <= 0 || p.Cout <= 0) return "simt_conv: empty problem";
+  const int esz = dtype == kF32 ? 4 : 2;
+  const bool out_al16 = (reinterpret_cast<uintptr_t>(p.out) % 16 == 0) && ((p.o_sn * esz) % 16 == 0) &&
+                        ((p.o_sh * esz) % 16 == 0) && ((p.o_sw * esz) % 16 == 0) && ((p.o_off * esz) % 16 == 0);
+  if (p.Cin == 3 && p.C == 3 && p.c0 == 0 && (p.Cout == 32 || p.Cout == 64) && !p.res && p.act2 == kAct2None &&
+      p.ntaps <= 16 && out_al16) {
+    if (dtype == kF32) return rgb_conv_dispatch<float>(p, s);
+    if (dtype == kBF16) return rgb_conv_dispatch<__nv_bfloat16>(p, s);
+  }
   dim3 grid(static_cast<unsigned>((M + TM - 1) / TM), (p.Cout + TN - 1) / TN);
   if (dtype == kF32)
     simt_conv_kernel<float><<<grid, 256, 0, s>>>(p);
@@ -174,43 +295,6 @@ const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s)
 // (block, channel).
 // ---------------------------------------------------------------------------
 namespace {
-
-template <typename T>
-__device__ __forceinline__ void load8(const T* p, float (&v)[8]);
-template <>
-__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
-  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
-  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
-  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-}
-template <>
-__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
-  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
-  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    v[2 * i] = __uint_as_float(w[i] << 16);
-    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
-  }
-}
-template <typename T>
-__device__ __forceinline__ void store8(T* p, const float (&v)[8]);
-template <>
-__device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
-  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
-  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
-}
-template <>
-__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
-  uint4 q;
-  __nv_bfloat162 t;
-  t = __floats2bfloat162_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
-  t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
-  t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
-  t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
-  *reinterpret_cast<uint4*>(p) = q;
-}
 
 constexpr int kStatThreads = 256;
 

@@ -55,6 +55,20 @@ def test_exact_batch_of_frames_matches_oracle():
     assert np.array_equal(out.cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("W", [500, 501, 512])
+def test_exact_odd_widths(W):
+    """Widths that are / are not multiples of 16 and 4 take the 16-, 4- and 1-pixel-per-thread variants."""
+    rng = np.random.default_rng(W)
+    H = 301
+    frame = synth.frame_u8(H, W, seed=W)
+    crops = synth.crops_u8(2, seed=W)
+    masks = np.stack([synth.soft_mask(rng), synth.soft_mask(rng)])
+    tfms = np.stack([synth.similarity_tfm(H, W, rng), synth.similarity_tfm(H, W, rng, clipped=True)])
+    ref = paste_ref.get_final_image_ref([[crops[0]], [crops[1]]], [masks[0], masks[1]], frame, [[tfms[0]], [tfms[1]]])
+    out = ghost_b200.paste_back(frame[None], crops, masks, tfms, np.zeros(2, np.int32), mode="exact")
+    assert np.array_equal(out[0].cpu().numpy(), ref)
+
+
 def test_exact_from_generator_output():
     """crop_kind = Y: the kernel converts the generator's NHWC output itself (faceshifter_run.py:20-21) and
     gives the same frame as converting first."""
