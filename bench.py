@@ -234,12 +234,16 @@ def run_ours(args):
         # paste kernel alone
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         yptr, ydt = G.y_nhwc(B, dev)
+        # queue the paste launches behind a long-running forward so that the events bracket GPU time only
+        # (the call's host-side preparation would otherwise dominate a 0.2 ms kernel)
+        z_warm = arc.embed_hwc(sources_d, out_dtype=torch.bfloat16)
+        G.swap_u8(crops_d, z_warm, out=swapped)
         p0.record()
-        for _ in range(5):
+        for _ in range(3):
             ghost_b200.paste_back(frames_d, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out_d)
         p1.record()
         torch.cuda.synchronize()
-        paste_ms = p0.elapsed_time(p1) / 5
+        paste_ms = p0.elapsed_time(p1) / 3
 
         def agg(prof, cls):
             sel = [o for o in prof if o["cls"] in cls]

@@ -221,8 +221,11 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     if (const char* e = encode_tmap(&p.tmB, w.wb, 2, dims, str, box, swz)) return e;
   }
   const int stage_bytes = (128 + p.BN) * p.kc * 2;
-  const int aad_bytes = aad ? 3 * ((p.BN >> 1) >> 6) * 16384 : 0;  // two h tiles + one staging tile
-  int stages = (220 * 1024 - aad_bytes) / stage_bytes;
+  // AAD mode keeps h tiles in flight deep enough to cover the HBM latency (the epilogue, not the MMA, paces it)
+  p.h_bufs = aad ? ((p.BN >> 1) == 64 ? 4 : 3) : 0;
+  p.o_bufs = aad ? ((p.BN >> 1) == 64 ? 2 : 1) : 0;
+  const int aad_bytes = (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384;
+  int stages = (224 * 1024 - aad_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
   const int num_kb = p.ntaps * p.kc_per_tap;
   if (stages > num_kb + 1 && num_kb >= 2) stages = num_kb + 1;

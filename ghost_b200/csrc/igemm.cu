@@ -136,8 +136,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __shared__ uint64_t empty_bar[8];
   __shared__ uint64_t tfull_bar[2];
   __shared__ uint64_t tempty_bar[2];
-  __shared__ uint64_t hfull_bar[2];   // AAD mode: h tile landed in shared memory
-  __shared__ uint64_t hempty_bar[2];  // AAD mode: epilogue done with the h tile
+  __shared__ uint64_t hfull_bar[4];   // AAD mode: h tile landed in shared memory
+  __shared__ uint64_t hempty_bar[4];  // AAD mode: epilogue done with the h tile
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int hbox = cn >> 6;
   const int htile_bytes = hbox * 16384;
   uint8_t* hbuf = smem + p.stages * stage_bytes;
-  uint8_t* obuf = hbuf + 2 * htile_bytes;
+  uint8_t* obuf = hbuf + p.h_bufs * htile_bytes;  // p.o_bufs staging tiles
 
   const int num_kb = p.ntaps * p.kc_per_tap / p.splits;  // K blocks handled by this CTA
   const int kb0 = blockIdx.y * num_kb;
@@ -174,6 +174,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], kIgemmEpiWarps);
+    }
+    for (int i = 0; i < 4; ++i) {
       mbar_init(&hfull_bar[i], 1);
       mbar_init(&hempty_bar[i], kIgemmEpiWarps);
     }
@@ -205,8 +207,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         const TileCoord t = decode_tile(p, tile);
         const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
         if (p.mode == kModeAAD) {
-          const int hs = hit & 1;
-          if (!mbar_wait(&hempty_bar[hs], ((hit >> 1) & 1) ^ 1u, &abort_flag)) break;
+          const int hs = hit % p.h_bufs;
+          if (!mbar_wait(&hempty_bar[hs], ((hit / p.h_bufs) & 1) ^ 1u, &abort_flag)) break;
           mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
           for (int b = 0; b < hbox; ++b)
             tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
@@ -309,12 +311,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
         // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels), the blended tile is staged in
         // shared memory and leaves by TMA store: no row-by-row global access.
-        const int hs = it & 1;
+        const int hs = it % p.h_bufs;
+        const int ob = it % p.o_bufs;
         const int c_base = t.nt * cn;
         const int nc = min(n, p.Nimg - 1);  // rows outside the tensor still index valid parameters
         const uint8_t* hrow = hbuf + hs * htile_bytes + r * 128;
         const int sw = r & 7;
-        if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], (it >> 1) & 1, &abort_flag))) break;
+        if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], (it / p.h_bufs) & 1, &abort_flag))) break;
         float m = 0.f;
         if (p.mask) {
           if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
@@ -339,12 +342,14 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
         tc_fence_after();
         // the previous tile's TMA store must have finished reading the staging tile before it is overwritten
-        if (threadIdx.x == 64) bulk_wait_read<0>();
+        if (threadIdx.x == 64) {
+          if (p.o_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
+        }
         named_bar_sync(1, 32 * kIgemmEpiWarps);
         const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
         const float* bg = p.bias + t.nt * p.BN;
         const float* bb = bg + cn;
-        uint8_t* orow = obuf + r * 128;
+        uint8_t* orow = obuf + ob * htile_bytes + r * 128;
         for (int j = half * (cn >> 1); j < (half + 1) * (cn >> 1); j += 16) {
           uint32_t g[16], b[16];
           __syncwarp();
@@ -355,13 +360,21 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           const uint4 h1 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + (((q0 + 1) ^ sw) << 4));
           tmem_ld_wait();
           const uint32_t qq[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-          float o[16];
+          float o[16], bgv[16], bbv[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(bg + j) + i);
+            const float4 w = __ldg(reinterpret_cast<const float4*>(bb + j) + i);
+            bgv[4 * i] = u.x; bgv[4 * i + 1] = u.y; bgv[4 * i + 2] = u.z; bgv[4 * i + 3] = u.w;
+            bbv[4 * i] = w.x; bbv[4 * i + 1] = w.y; bbv[4 * i + 2] = w.z; bbv[4 * i + 3] = w.w;
+          }
+          const float4* parj = par + j;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const float x = (i & 1) ? bf16hi(qq[i >> 1]) : bf16lo(qq[i >> 1]);
-            const float4 pr = __ldg(par + j + i);
+            const float4 pr = __ldg(parj + i);
             const float hn = fmaf(x, pr.x, pr.y);
-            const float A = fmaf(__uint_as_float(g[i]) + __ldg(bg + j + i), hn, __uint_as_float(b[i]) + __ldg(bb + j + i));
+            const float A = fmaf(__uint_as_float(g[i]) + bgv[i], hn, __uint_as_float(b[i]) + bbv[i]);
             const float I = fmaf(pr.z, hn, pr.w);
             o[i] = fmaxf(fmaf(m, I - A, A), 0.f);
           }
@@ -382,7 +395,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         named_bar_sync(1, 32 * kIgemmEpiWarps);
         if (threadIdx.x == 64) {
           for (int bx = 0; bx < hbox; ++bx)
-            tma_store_4d(&p.tmO, obuf + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);
+            tma_store_4d(&p.tmO, obuf + ob * htile_bytes + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);
           bulk_commit();
         }
         if (lane == 0) mbar_arrive(&hempty_bar[hs]);
@@ -410,7 +423,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 
 int igemm_smem_bytes(const IgemmParams& p) {
   const int row_bytes = p.kc * 2;
-  const int aad = p.mode == kModeAAD ? 3 * ((p.BN >> 1) >> 6) * 16384 : 0;  // 2 h tiles + 1 staging tile
+  const int aad = p.mode == kModeAAD ? (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384 : 0;
   return p.stages * (128 * row_bytes + p.BN * row_bytes) + aad + 1024;
 }
 
@@ -433,6 +446,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm: M box must hold 1..128 rows";
   if (p.stages < 2 || p.stages > 8) return "igemm: stages must be in [2,8]";
+  if (p.mode == kModeAAD && (p.h_bufs < 2 || p.h_bufs > 4 || p.o_bufs < 1 || p.o_bufs > 2)) return "igemm: bad AAD buffering";
   if (p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm: bad tmem_cols";
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";

@@ -39,6 +39,7 @@ struct alignas(64) IgemmParams {
   short tap_p[kIgemmMaxTaps];     // h-parity coordinate (5-D maps only)
   short tap_h[kIgemmMaxTaps];     // added to the h coordinate
   int stages, tmem_cols;
+  int h_bufs, o_bufs;  // AAD mode: shared-memory h tiles in flight (2..4) and output staging tiles (1..2)
 
   // ---- epilogue (linear):  v = act2(act1(acc + bias) + res)
   int mode;

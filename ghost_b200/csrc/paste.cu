@@ -136,24 +136,20 @@ __global__ void __launch_bounds__(128) paste_kernel(const PasteParams p) {
   if (x_base >= p.W) return;
   const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x_base) * 3;
   constexpr int NB = PX * 3;
-  union alignas(16) Span {
-    uint4 v[(NB + 15) / 16];
-    uint32_t w[(NB + 3) / 4];
-    uint8_t b[NB];
-  } sp;
+  // the span lives in registers (r0..r2); only a span that a face box touches is spilled to a byte array
+  uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0, r2 = r0;
   if (PX == 16) {
     const uint4* s = reinterpret_cast<const uint4*>(p.frames_in + off);
-    sp.v[0] = __ldg(s);
-    sp.v[1] = __ldg(s + 1);
-    sp.v[2] = __ldg(s + 2);
+    r0 = __ldg(s);
+    r1 = __ldg(s + 1);
+    r2 = __ldg(s + 2);
   } else if (PX == 4) {
     const uint32_t* s = reinterpret_cast<const uint32_t*>(p.frames_in + off);
-    sp.w[0] = __ldg(s);
-    sp.w[1] = __ldg(s + 1);
-    sp.w[2] = __ldg(s + 2);
+    r0.x = __ldg(s);
+    r0.y = __ldg(s + 1);
+    r0.z = __ldg(s + 2);
   } else {
-#pragma unroll
-    for (int i = 0; i < NB; ++i) sp.b[i] = p.frames_in[off + i];
+    r0.x = p.frames_in[off] | (p.frames_in[off + 1] << 8) | (p.frames_in[off + 2] << 16);
   }
   const int fs = __ldg(p.face_start + f), fe = __ldg(p.face_start + f + 1);
   bool span_touched = false;
@@ -161,7 +157,33 @@ __global__ void __launch_bounds__(128) paste_kernel(const PasteParams p) {
     const PasteFace& face = p.faces[j];
     span_touched |= (x_base + PX > face.x0 && x_base < face.x1 && y >= face.y0 && y < face.y1);
   }
-  if (span_touched) {
+  if (!span_touched) {
+    if (PX == 16) {
+      uint4* d = reinterpret_cast<uint4*>(p.frames_out + off);
+      d[0] = r0;
+      d[1] = r1;
+      d[2] = r2;
+    } else if (PX == 4) {
+      uint32_t* d = reinterpret_cast<uint32_t*>(p.frames_out + off);
+      d[0] = r0.x;
+      d[1] = r0.y;
+      d[2] = r0.z;
+    } else {
+      p.frames_out[off] = r0.x & 255;
+      p.frames_out[off + 1] = (r0.x >> 8) & 255;
+      p.frames_out[off + 2] = (r0.x >> 16) & 255;
+    }
+    return;
+  }
+  union alignas(16) Span {
+    uint4 v[3];
+    uint32_t w[12];
+    uint8_t b[48];
+  } sp;
+  sp.v[0] = r0;
+  sp.v[1] = r1;
+  sp.v[2] = r2;
+  {
     CropSrc cs{p.crops, p.crop_kind};
     for (int i = 0; i < PX; ++i) {
       const int x = x_base + i;
