@@ -1,6 +1,7 @@
 #include "conv.cuh"
 
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace ghost {
@@ -146,6 +147,20 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   const int swz = p.kc * 2;
   p.Nimg = in.N; p.Ho = Ho; p.Wo = Wo;
   choose_box(in.N, Ho, Wo, &p.bw, &p.bh, &p.bn);
+  // Row-window mode (igemm.cuh): 3x3 / stride 1 / pad 1 over a wide image, tiles are runs of one image row.
+  static const int win_mode = [] {
+    const char* e = getenv("GHOST_AWIN");  // A/B switch for profiling: GHOST_AWIN=0 turns the mode off
+    return e ? (atoi(e) != 0) : 1;
+  }();
+  bool win = win_mode != 0 && !aad && taps.n == 9 && taps.stride == 1 && p.kc == 64 && Wo == in.W && Ho == in.H &&
+             Wo >= 112 && w.Cout <= 128;
+  for (int i = 0; win && i < 9; ++i) win = taps.dh[i] == i / 3 - 1 && taps.dw[i] == i % 3 - 1;
+  if (win) {
+    const int tw = (Wo + 127) / 128;
+    p.bw = (Wo + tw - 1) / tw;
+    p.bh = 1;
+    p.bn = 1;
+  }
   p.tiles_w = (Wo + p.bw - 1) / p.bw;
   p.tiles_h = (Ho + p.bh - 1) / p.bh;
   p.tiles_nb = (in.N + p.bn - 1) / p.bn;
@@ -163,8 +178,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
                               static_cast<uint64_t>(in.N)};
     const uint64_t str[3] = {in.C * eb, static_cast<uint64_t>(in.W) * in.C * eb,
                              static_cast<uint64_t>(in.H) * in.W * in.C * eb};
-    const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh),
-                             static_cast<uint32_t>(p.bn)};
+    const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(win ? p.bw + 2 : p.bw),
+                             static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
     if (const char* e = encode_tmap(&p.tmA, in.p, 4, dims, str, box, swz)) return e;
     for (int i = 0; i < taps.n; ++i) {
       p.tap_c[i] = 0;
@@ -220,14 +235,24 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const uint32_t box[2] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.BN)};
     if (const char* e = encode_tmap(&p.tmB, w.wb, 2, dims, str, box, swz)) return e;
   }
-  const int stage_bytes = (128 + p.BN) * p.kc * 2;
+  int stage_bytes = (128 + p.BN) * p.kc * 2;
+  int resident_bytes = 0;
+  if (win) {
+    const int b_tile = p.BN * 128;
+    const int slab = 9 * p.kc_per_tap * b_tile;
+    p.a_win = win_mode;
+    p.b_res = p.tiles_n == 1 && (224 * 1024 - slab) / (17 * 1024) >= 4;
+    stage_bytes = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
+    resident_bytes = p.b_res ? slab : 0;
+    if ((224 * 1024 - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
+  }
   // AAD mode keeps h tiles in flight deep enough to cover the HBM latency (the epilogue, not the MMA, paces it)
   p.h_bufs = aad ? ((p.BN >> 1) == 64 ? 4 : 3) : 0;
   p.o_bufs = aad ? ((p.BN >> 1) == 64 ? 2 : 1) : 0;
   const int aad_bytes = (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384;
-  int stages = (224 * 1024 - aad_bytes) / stage_bytes;
+  int stages = (224 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
-  const int num_kb = p.ntaps * p.kc_per_tap;
+  const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
   if (stages > num_kb + 1 && num_kb >= 2) stages = num_kb + 1;
   if (stages < 2) stages = 2;
   p.stages = stages;

@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __shared__ uint64_t tempty_bar[2];
   __shared__ uint64_t hfull_bar[4];   // AAD mode: h tile landed in shared memory
   __shared__ uint64_t hempty_bar[4];  // AAD mode: epilogue done with the h tile
+  __shared__ uint64_t bfull_bar;      // resident-weights mode: the packed weight slab landed
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
@@ -148,20 +149,27 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
   const int row_bytes = p.kc * 2;
-  const int a_stage_bytes = 128 * row_bytes;
-  const int b_stage_bytes = p.BN * row_bytes;
+  const bool win = p.a_win != 0;
+  const int b_tile_bytes = p.BN * row_bytes;
+  // row-window mode: the A slot holds bw+2 (<= 130) pixel rows of 128 B, the B slot the three taps of one kernel row
+  const int a_stage_bytes = win ? 17 * 1024 : 128 * row_bytes;
+  const int b_stage_bytes = win ? (p.b_res ? 0 : 3 * b_tile_bytes) : b_tile_bytes;
   const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
   const int rows_used = p.bw * p.bh * p.bn;
-  const uint32_t tx_bytes = rows_used * row_bytes + b_stage_bytes;
+  const uint32_t tx_bytes = (win ? (p.bw + 2) * 128 : rows_used * row_bytes) + b_stage_bytes;
+  const int bres_tiles = p.b_res ? p.ntaps * p.kc_per_tap : 0;
+  uint8_t* bres = smem;                                 // resident weight tiles [tap][chunk][BN rows][128 B]
+  uint8_t* ring = smem + bres_tiles * b_tile_bytes;     // operand ring
 
   // AAD mode: two h tiles and one output tile behind the operand ring, each cn/64 boxes of [128 rows][128 B]
   const int cn = p.BN >> 1;
   const int hbox = cn >> 6;
   const int htile_bytes = hbox * 16384;
-  uint8_t* hbuf = smem + p.stages * stage_bytes;
+  uint8_t* hbuf = ring + p.stages * stage_bytes;
   uint8_t* obuf = hbuf + p.h_bufs * htile_bytes;  // p.o_bufs staging tiles
 
-  const int num_kb = p.ntaps * p.kc_per_tap / p.splits;  // K blocks handled by this CTA
+  // K blocks handled by this CTA (row-window mode: one block = one kernel row x one 64-channel chunk = 3 taps)
+  const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap / p.splits;
   const int kb0 = blockIdx.y * num_kb;
   const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
 
@@ -175,6 +183,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], kIgemmEpiWarps);
     }
+    mbar_init(&bfull_bar, 1);
     for (int i = 0; i < 4; ++i) {
       mbar_init(&hfull_bar[i], 1);
       mbar_init(&hempty_bar[i], kIgemmEpiWarps);
@@ -198,84 +207,121 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      bool ok = true;
-      int hit = 0;
-      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit) {
-        const TileCoord t = decode_tile(p, tile);
-        const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
-        if (p.mode == kModeAAD) {
-          const int hs = hit % p.h_bufs;
-          if (!mbar_wait(&hempty_bar[hs], ((hit / p.h_bufs) & 1) ^ 1u, &abort_flag)) break;
+    // The whole warp runs the loop converged (every exit is voted on); one elected lane issues the copies.
+    int stage = 0;
+    uint32_t phase = 0;
+    bool ok = true;
+    int hit = 0;
+    if (p.b_res && elect_one()) {
+      mbar_expect_tx(&bfull_bar, bres_tiles * b_tile_bytes);
+      for (int i = 0; i < bres_tiles; ++i)
+        tma_load_2d(bres + i * b_tile_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * p.kc, 0);
+    }
+    __syncwarp();
+    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit) {
+      const TileCoord t = decode_tile(p, tile);
+      const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+      if (p.mode == kModeAAD) {
+        const int hs = hit % p.h_bufs;
+        if (!__all_sync(0xffffffffu, mbar_wait(&hempty_bar[hs], ((hit / p.h_bufs) & 1) ^ 1u, &abort_flag))) break;
+        if (elect_one()) {
           mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
           for (int b = 0; b < hbox; ++b)
             tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
         }
-        for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
-          const int tap = kb / p.kc_per_tap;
-          const int kci = kb - tap * p.kc_per_tap;
-          if (!mbar_wait(&empty_bar[stage], phase ^ 1u, &abort_flag)) {
-            ok = false;
-            break;
-          }
-          uint8_t* sa = smem + stage * stage_bytes;
+        __syncwarp();
+      }
+      int tap = kb0 / p.kc_per_tap, kci = kb0 - tap * p.kc_per_tap;
+      for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
+        if (!__all_sync(0xffffffffu, mbar_wait(&empty_bar[stage], phase ^ 1u, &abort_flag))) {
+          ok = false;
+          break;
+        }
+        if (elect_one()) {
+          uint8_t* sa = ring + stage * stage_bytes;
           uint8_t* sb = sa + a_stage_bytes;
           mbar_expect_tx(&full_bar[stage], tx_bytes);
-          const int c = p.a_c0 + p.tap_c[tap] + kci * p.kc;
-          if (p.a_rank == 4)
-            tma_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
-          else
-            tma_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
-          tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1u;
+          if (win) {
+            // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
+            tma_load_4d(sa, &p.tmA, &full_bar[stage], p.a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
+            if (!p.b_res)
+              for (int dwi = 0; dwi < 3; ++dwi)
+                tma_load_2d(sb + dwi * b_tile_bytes, &p.tmB, &full_bar[stage],
+                            p.b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, t.nt * p.BN);
+          } else {
+            const int c = p.a_c0 + p.tap_c[tap] + kci * p.kc;
+            if (p.a_rank == 4)
+              tma_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
+            else
+              tma_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+            tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
           }
+        }
+        __syncwarp();
+        if (++kci == p.kc_per_tap) {
+          kci = 0;
+          ++tap;
+        }
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // ============================== MMA issuer ================================
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, p.BN);
-      const uint32_t sbo = 8 * row_bytes;
-      const uint64_t swz_fix = (p.kc == 64) ? 0ull : ((4ull ^ 2ull) << 61);  // SWIZZLE_64B = 4
-      const int mma_per_kb = p.kc / 16;
-      int stage = 0;
-      uint32_t phase = 0;
-      bool ok = true;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        if (!mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag)) break;
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * acc_stride;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          if (!mbar_wait(&full_bar[stage], phase, &abort_flag)) {
-            ok = false;
-            break;
-          }
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-          const uint32_t sb = sa + a_stage_bytes;
-          const uint64_t adesc = make_smem_desc_sw128(sa, sbo) ^ swz_fix;
-          const uint64_t bdesc = make_smem_desc_sw128(sb, sbo) ^ swz_fix;
-          for (int k = 0; k < mma_per_kb; ++k)
-            umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1u;
-          }
+    // Converged warp, one elected lane issues; descriptors are built from warp-uniform values so the whole batch
+    // of a K block goes out back to back (see umma_bf16_batch).
+    const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t idesc = make_idesc_bf16(128, p.BN);
+    const uint32_t dhi = smem_desc_hi(win ? 1024 : 8 * row_bytes, p.kc != 64);
+    const uint32_t ring_u = smem_u32(ring);
+    const uint32_t bres_u = smem_u32(bres);
+    int stage = 0;
+    uint32_t phase = 0;
+    bool ok = true;
+    int it = 0;
+    if (p.b_res && !__all_sync(0xffffffffu, mbar_wait(&bfull_bar, 0, &abort_flag))) ok = false;
+    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      if (!__all_sync(0xffffffffu, mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag))) break;
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base_u + as * acc_stride;
+      int dhi_row = 0, kci = 0;  // row-window mode: kernel row and channel chunk of this K block
+      for (int kb = 0; kb < num_kb; ++kb) {
+        if (!__all_sync(0xffffffffu, mbar_wait(&full_bar[stage], phase, &abort_flag))) {
+          ok = false;
+          break;
         }
-        if (ok) umma_commit(&tfull_bar[as]);
+        tc_fence_after();
+        const uint32_t sa = ring_u + stage * stage_bytes;
+        const uint32_t sb = sa + a_stage_bytes;
+        if (win) {
+#pragma unroll
+          for (int dwi = 0; dwi < 3; ++dwi) {
+            const uint32_t bt = p.b_res ? bres_u + ((dhi_row * 3 + dwi) * p.kc_per_tap + kci) * b_tile_bytes
+                                        : sb + dwi * b_tile_bytes;
+            // the horizontal tap is a view of the window shifted by dwi pixel rows (128 B each)
+            umma_bf16_batch<4>(d_tmem, smem_desc_lo(sa + dwi * 128), smem_desc_lo(bt), dhi, idesc, (kb | dwi) != 0);
+          }
+          if (++kci == p.kc_per_tap) {
+            kci = 0;
+            ++dhi_row;
+          }
+        } else if (p.kc == 64) {
+          umma_bf16_batch<4>(d_tmem, smem_desc_lo(sa), smem_desc_lo(sb), dhi, idesc, kb != 0);
+        } else {
+          umma_bf16_batch<2>(d_tmem, smem_desc_lo(sa), smem_desc_lo(sb), dhi, idesc, kb != 0);
+        }
+        umma_commit_elect(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1u;
+        }
       }
+      if (ok) umma_commit_elect(&tfull_bar[as]);
     }
-    __syncwarp();
   } else {
     // ============================== epilogue ==================================
     const int lg = warp & 3;            // TMEM lane group this warp may read
@@ -424,7 +470,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 int igemm_smem_bytes(const IgemmParams& p) {
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384 : 0;
-  return p.stages * (128 * row_bytes + p.BN * row_bytes) + aad + 1024;
+  const int b_tile = p.BN * row_bytes;
+  if (p.a_win) {
+    const int stage = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
+    return p.stages * stage + (p.b_res ? p.ntaps * p.kc_per_tap * b_tile : 0) + aad + 1024;
+  }
+  return p.stages * (128 * row_bytes + b_tile) + aad + 1024;
 }
 
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
@@ -451,6 +502,9 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
     return "igemm: bad tmem_cols";
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
   if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
+  if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
+    return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
+  if (p.b_res && (!p.a_win || p.tiles_n != 1)) return "igemm: resident weights need row-window mode and one N tile";
   const int smem = igemm_smem_bytes(p);
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;

@@ -40,6 +40,11 @@ struct alignas(64) IgemmParams {
   short tap_h[kIgemmMaxTaps];     // added to the h coordinate
   int stages, tmem_cols;
   int h_bufs, o_bufs;  // AAD mode: shared-memory h tiles in flight (2..4) and output staging tiles (1..2)
+  // Row-window mode (3x3 stride-1 convs on wide images, bh == bn == 1, kc == 64): one TMA box of bw+2 pixels per
+  // (kernel row, 64-channel chunk) serves the three horizontal taps as row-shifted UMMA views, so the A operand
+  // crosses L2->shared 3x instead of 9x.  b_res: the whole packed weight slab stays resident in shared memory.
+  int a_win;   // 0 off, 1 on (the UMMA descriptor start address carries the row shift)
+  int b_res;
 
   // ---- epilogue (linear):  v = act2(act1(acc + bias) + res)
   int mode;

@@ -173,6 +173,67 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uin
   return d;
 }
 
+// A view that starts `row_shift` (0..7) rows into a 1024-byte swizzle atom: the MMA unit derives the 128B-swizzle
+// phase from the shared-memory address bits, exactly as the TMA unit did when it wrote the tile, so shifting the start
+// address by whole 128-byte rows is all it takes (measured on B200: the descriptor base-offset field must stay 0).
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t smem_addr, uint32_t sbo_bytes,
+                                                                 uint32_t row_shift) {
+  return make_smem_desc_sw128(smem_addr + row_shift * 128u, sbo_bytes);
+}
+
+// Split form of the same descriptor for the MMA issue loop: the low word carries the start address (advanced by
+// 2 per 16-element K step, by 8 per 128-byte row), the high word (SBO, version, swizzle mode) is loop invariant.
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t smem_addr) {
+  return ((smem_addr & 0x3FFFFu) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ uint32_t smem_desc_hi(uint32_t sbo_bytes, bool swizzle64) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | ((swizzle64 ? 4u : 2u) << 29);
+}
+
+// NK consecutive 16-element K steps of one operand pair, issued back to back by one elected lane of a CONVERGED
+// warp (all 32 lanes must call this with identical arguments).  Keeping the batch in one asm block lets ptxas hold
+// the descriptors in uniform registers: the issue loop costs a few instructions per MMA instead of ~30.
+template <int NK>
+__device__ __forceinline__ void umma_bf16_batch(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                                uint32_t idesc, uint32_t accumulate_first) {
+  static_assert(NK == 2 || NK == 4, "K steps per batch");
+  if (NK == 4) {
+    asm volatile(
+        "{\n\t.reg .pred E, Q;\n\t.reg .b64 da, db;\n\t.reg .b32 a, b;\n\t"
+        "elect.sync _|E, 0xffffffff;\n\t"
+        "setp.ne.b32 Q, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, Q;\n\t"
+        "add.u32 a, %1, 2;\n\tadd.u32 b, %2, 2;\n\tmov.b64 da, {a, %3};\n\tmov.b64 db, {b, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, 1;\n\t"
+        "add.u32 a, %1, 4;\n\tadd.u32 b, %2, 4;\n\tmov.b64 da, {a, %3};\n\tmov.b64 db, {b, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, 1;\n\t"
+        "add.u32 a, %1, 6;\n\tadd.u32 b, %2, 6;\n\tmov.b64 da, {a, %3};\n\tmov.b64 db, {b, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, 1;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate_first)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred E, Q;\n\t.reg .b64 da, db;\n\t.reg .b32 a, b;\n\t"
+        "elect.sync _|E, 0xffffffff;\n\t"
+        "setp.ne.b32 Q, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, Q;\n\t"
+        "add.u32 a, %1, 2;\n\tadd.u32 b, %2, 2;\n\tmov.b64 da, {a, %3};\n\tmov.b64 db, {b, %3};\n\t"
+        "@E tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, 1;\n\t}\n" ::"r"(d_tmem),
+        "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate_first)
+        : "memory");
+  }
+}
+// commit by one elected lane of a converged warp
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred E;\n\t"
+      "elect.sync _|E, 0xffffffff;\n\t"
+      "@E tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n" ::"r"(smem_u32(bar))
+      : "memory");
+}
+
 // Instruction descriptor for kind::f16: bf16 x bf16 -> fp32, both K-major.
 __host__ __device__ inline uint32_t make_idesc_bf16(uint32_t M, uint32_t N) {
   uint32_t d = 0;

@@ -40,6 +40,11 @@ CONV_CASES = [
     ("multi_tile_4x4s2_32_to_64", 4, 32, 128, 128, 64, 0, 4, 2, 1, 1),
     ("multi_tile_deconv_128_to_32", 3, 128, 64, 64, 32, 1, 4, 2, 1, 1),
     ("multi_tile_3x3_64_to_3", 2, 64, 256, 256, 3, 0, 3, 1, 1, 0),
+    # row-window mode (wide 3x3 stride-1 convs): streamed weights (128 -> 128), 112-pixel rows, ragged split rows
+    ("window_3x3_128_to_128", 2, 128, 128, 128, 128, 0, 3, 1, 1, 3),
+    ("window_3x3_64_112px", 2, 64, 112, 112, 64, 0, 3, 1, 1, 0),
+    ("window_3x3_64_150px_ragged", 1, 64, 37, 150, 48, 0, 3, 1, 1, 1),
+    ("window_3x3_192_to_96", 1, 192, 40, 128, 96, 0, 3, 1, 1, 0),
 ]
 
 
