@@ -241,21 +241,26 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const int b_tile = p.BN * 128;
     const int slab = 9 * p.kc_per_tap * b_tile;
     p.a_win = win_mode;
-    p.b_res = p.tiles_n == 1 && (224 * 1024 - slab) / (17 * 1024) >= 4;
+    p.b_res = p.tiles_n == 1 && (221 * 1024 - slab) / (17 * 1024) >= 4;
     stage_bytes = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
     resident_bytes = p.b_res ? slab : 0;
-    if ((224 * 1024 - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
+    if ((221 * 1024 - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
   }
   // AAD mode keeps h tiles in flight deep enough to cover the HBM latency (the epilogue, not the MMA, paces it)
   p.h_bufs = aad ? ((p.BN >> 1) == 64 ? 4 : 3) : 0;
   p.o_bufs = aad ? ((p.BN >> 1) == 64 ? 2 : 1) : 0;
-  const int aad_bytes = (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384;
-  int stages = (224 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
+  int aad_bytes = (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384;
+  int stages = (221 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
+  if (aad && stages < 2 && p.h_bufs > 2) {  // wide gamma/beta tiles: trade one h tile for a second operand slot
+    p.h_bufs = 2;
+    stages = (221 * 1024 - (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384) / stage_bytes;
+  }
   if (stages > 8) stages = 8;
-  const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
-  if (stages > num_kb + 1 && num_kb >= 2) stages = num_kb + 1;
   if (stages < 2) stages = 2;
   p.stages = stages;
+  // narrow / short tiles are bound by how fast one warp can issue tcgen05.mma: split the tiles over two issuers
+  // when the ring is deep enough to give each of them three or more slots
+  p.dual = stages >= 6;
   p.tmem_cols = pow2_at_least(2 * p.BN);
 
   // ---- epilogue

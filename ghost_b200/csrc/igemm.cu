@@ -8,11 +8,11 @@
 // buffer ever exists.  Stride-2 convs use a 5-D parity-split view of the same
 // NHWC memory, ConvTranspose k4s2 is 4 output-phase launches with 2x2 taps.
 //
-// Roles (192 threads): warp 0 lane 0 = TMA producer, warp 1 lane 0 = MMA issuer
-// (warp 1 also owns the TMEM allocation), warps 2..5 = epilogue (TMEM -> regs
-// -> fused epilogue -> global).  The accumulator is double buffered in TMEM so
-// the epilogue of tile i overlaps the main loop of tile i+1.  Persistent CTAs,
-// static round-robin tile schedule.
+// Roles (608 threads): warp 0 = TMA producer, warps 1-2 = MMA issuers (even / odd tiles; warp 1 also owns the
+// TMEM allocation), warps 3..18 = epilogue (TMEM -> regs -> fused epilogue -> global or TMA store), four warps
+// per TMEM lane group splitting the columns.  Producer and issuer warps run converged and elect one lane per
+// copy / MMA batch.  The accumulator is double buffered in TMEM so the epilogue of tile i overlaps the main loop
+// of tile i+1.  Persistent CTAs, static round-robin tile schedule.
 //
 // Reference ops covered: nn.Conv2d / nn.ConvTranspose2d / nn.Linear call sites in
 // network/AEI_Net.py:19-41,101 and network/AADLayer.py:13-18,67-74; the AAD
@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __shared__ uint64_t hfull_bar[4];   // AAD mode: h tile landed in shared memory
   __shared__ uint64_t hempty_bar[4];  // AAD mode: epilogue done with the h tile
   __shared__ uint64_t bfull_bar;      // resident-weights mode: the packed weight slab landed
+  __shared__ float mpart[4][128];     // AAD mode: per-quarter partial sums of the mask logit
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
@@ -208,8 +209,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   if (warp == 0) {
     // ============================== TMA producer ==============================
     // The whole warp runs the loop converged (every exit is voted on); one elected lane issues the copies.
-    int stage = 0;
-    uint32_t phase = 0;
+    // dual-issuer mode: even tiles go through ring slots [0, S2), odd tiles through [S2, 2*S2)
+    const int S2 = p.dual ? p.stages >> 1 : p.stages;
+    int st[2] = {0, 0};
+    uint32_t ph[2] = {0, 0};
     bool ok = true;
     int hit = 0;
     if (p.b_res && elect_one()) {
@@ -232,7 +235,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         __syncwarp();
       }
       int tap = kb0 / p.kc_per_tap, kci = kb0 - tap * p.kc_per_tap;
+      const int rg = p.dual ? (hit & 1) : 0;
+      int stage_r = st[rg];
+      uint32_t phase = ph[rg];
       for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
+        const int stage = rg * S2 + stage_r;
         if (!__all_sync(0xffffffffu, mbar_wait(&empty_bar[stage], phase ^ 1u, &abort_flag))) {
           ok = false;
           break;
@@ -262,61 +269,78 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           kci = 0;
           ++tap;
         }
-        if (++stage == p.stages) {
-          stage = 0;
+        if (++stage_r == S2) {
+          stage_r = 0;
           phase ^= 1u;
         }
       }
+      st[rg] = stage_r;
+      ph[rg] = phase;
     }
-  } else if (warp == 1) {
-    // ============================== MMA issuer ================================
-    // Converged warp, one elected lane issues; descriptors are built from warp-uniform values so the whole batch
-    // of a K block goes out back to back (see umma_bf16_batch).
+  } else if (warp <= kIgemmMmaWarps) {
+    // ============================== MMA issuers ===============================
+    // Two converged warps: warp 1 issues the even tiles of this CTA (accumulator stage 0), warp 2 the odd ones
+    // (stage 1).  One warp cannot issue tcgen05.mma fast enough for narrow tiles (a K block of a 64-channel conv
+    // is only a few hundred tensor-pipe cycles); a tile's MMAs all come from one thread, so the accumulation
+    // order - and the result - does not depend on the split.  Both walk the same operand ring.
+    const int par = warp - 1;
     const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint32_t idesc = make_idesc_bf16(128, p.BN);
     const uint32_t dhi = smem_desc_hi(win ? 1024 : 8 * row_bytes, p.kc != 64);
     const uint32_t ring_u = smem_u32(ring);
-    const uint32_t bres_u = smem_u32(bres);
-    int stage = 0;
+    const uint32_t bt16 = static_cast<uint32_t>(b_tile_bytes) >> 4;     // weight tile size in descriptor units
+    const uint32_t bres_lo = smem_desc_lo(smem_u32(bres));
+    const int S2 = p.dual ? p.stages >> 1 : p.stages;
+    const int slot0 = p.dual ? par * S2 : 0;  // this issuer's part of the ring
+    int stage_r = 0;
     uint32_t phase = 0;
-    bool ok = true;
+    bool ok = p.dual || par == 0;  // single-issuer mode: warp 2 idles
     int it = 0;
-    if (p.b_res && !__all_sync(0xffffffffu, mbar_wait(&bfull_bar, 0, &abort_flag))) ok = false;
+    if (ok && p.b_res && !__all_sync(0xffffffffu, mbar_wait(&bfull_bar, 0, &abort_flag))) ok = false;
     for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
       const int as = it & 1;
+      if (p.dual && as != par) continue;  // the other issuer's tile
+      const uint32_t d_tmem = tmem_base_u + as * acc_stride;
       const uint32_t aphase = (it >> 1) & 1;
       if (!__all_sync(0xffffffffu, mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag))) break;
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base_u + as * acc_stride;
-      int dhi_row = 0, kci = 0;  // row-window mode: kernel row and channel chunk of this K block
+      uint32_t bq = bres_lo;  // resident weights: descriptor of tap (row, 0), chunk kci
+      int kci = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
+        const int stage = slot0 + stage_r;
         if (!__all_sync(0xffffffffu, mbar_wait(&full_bar[stage], phase, &abort_flag))) {
           ok = false;
           break;
         }
         tc_fence_after();
         const uint32_t sa = ring_u + stage * stage_bytes;
-        const uint32_t sb = sa + a_stage_bytes;
+        const uint32_t a_lo = smem_desc_lo(sa);
         if (win) {
-#pragma unroll
-          for (int dwi = 0; dwi < 3; ++dwi) {
-            const uint32_t bt = p.b_res ? bres_u + ((dhi_row * 3 + dwi) * p.kc_per_tap + kci) * b_tile_bytes
-                                        : sb + dwi * b_tile_bytes;
-            // the horizontal tap is a view of the window shifted by dwi pixel rows (128 B each)
-            umma_bf16_batch<4>(d_tmem, smem_desc_lo(sa + dwi * 128), smem_desc_lo(bt), dhi, idesc, (kb | dwi) != 0);
-          }
-          if (++kci == p.kc_per_tap) {
-            kci = 0;
-            ++dhi_row;
+          // the horizontal taps are views of the window shifted by whole pixel rows (128 B = 8 descriptor units)
+          if (p.b_res) {
+            const uint32_t bstep = p.kc_per_tap * bt16;
+            umma_bf16_batch<4>(d_tmem, a_lo, bq, dhi, idesc, kb != 0);
+            umma_bf16_batch<4>(d_tmem, a_lo + 8, bq + bstep, dhi, idesc, 1);
+            umma_bf16_batch<4>(d_tmem, a_lo + 16, bq + 2 * bstep, dhi, idesc, 1);
+            bq += bt16;
+            if (++kci == p.kc_per_tap) {
+              kci = 0;
+              bq += 2 * bstep;
+            }
+          } else {
+            const uint32_t b_lo = smem_desc_lo(sa + a_stage_bytes);
+            umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
+            umma_bf16_batch<4>(d_tmem, a_lo + 8, b_lo + bt16, dhi, idesc, 1);
+            umma_bf16_batch<4>(d_tmem, a_lo + 16, b_lo + 2 * bt16, dhi, idesc, 1);
           }
         } else if (p.kc == 64) {
-          umma_bf16_batch<4>(d_tmem, smem_desc_lo(sa), smem_desc_lo(sb), dhi, idesc, kb != 0);
+          umma_bf16_batch<4>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
         } else {
-          umma_bf16_batch<2>(d_tmem, smem_desc_lo(sa), smem_desc_lo(sb), dhi, idesc, kb != 0);
+          umma_bf16_batch<2>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
         }
         umma_commit_elect(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
-        if (++stage == p.stages) {
-          stage = 0;
+        if (++stage_r == S2) {
+          stage_r = 0;
           phase ^= 1u;
         }
       }
@@ -325,7 +349,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   } else {
     // ============================== epilogue ==================================
     const int lg = warp & 3;            // TMEM lane group this warp may read
-    const int half = (warp - 2) >> 2;   // which half of the tile's columns this warp handles
+    const int quarter = (warp - kIgemmEpiWarp0) >> 2;  // which quarter of the tile's columns this warp handles
     const int r = lg * 32 + lane;       // GEMM row inside the tile
     const int rn = r / (p.bh * p.bw);
     const int rh = (r / p.bw) % p.bh;
@@ -344,7 +368,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         tc_fence_after();
         const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
-        const int nch = p.BN >> 4, ch0 = half ? (nch + 1) >> 1 : 0, ch1 = half ? nch : (nch + 1) >> 1;
+        const int nch = p.BN >> 4, ch0 = (nch * quarter) >> 2, ch1 = (nch * (quarter + 1)) >> 2;
         for (int j = ch0 * 16; j < ch1 * 16; j += 16) {
           uint32_t v[16];
           __syncwarp();
@@ -369,54 +393,56 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
         } else {
           // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh (single N tile: cn == c_x).
-          // Runs while the tensor core is still producing this tile's gamma/beta.
+          // Each of the four warps sharing this row sums a quarter of the channels; the partials meet in shared
+          // memory at the barrier below.  Runs while the tensor core is still producing this tile's gamma/beta.
           const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x;
           float acc = 0.f;
-          for (int bx = 0; bx < hbox; ++bx) {
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const uint4 v = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q ^ sw) << 4));
-              const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + bx * 64 + q * 8));
-              const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + bx * 64 + q * 8) + 1);
-              acc += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
-              acc += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
-            }
+          const int nq = hbox * 2;  // 16-byte chunks (8 channels) per quarter
+          for (int qq = quarter * nq; qq < (quarter + 1) * nq; ++qq) {
+            const int bx = qq >> 3, q = qq & 7;
+            const uint4 v = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q ^ sw) << 4));
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + qq * 8));
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + qq * 8) + 1);
+            acc += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
+            acc += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
           }
-          acc += __ldg(p.bh_fold + nc);
-          m = 1.f / (1.f + __expf(-acc));
+          mpart[quarter][r] = acc;
         }
         if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
         tc_fence_after();
         // the previous tile's TMA store must have finished reading the staging tile before it is overwritten
-        if (threadIdx.x == 64) {
+        if (threadIdx.x == 32 * kIgemmEpiWarp0) {
           if (p.o_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
         }
         named_bar_sync(1, 32 * kIgemmEpiWarps);
+        if (!p.mask) {
+          const float acc = ((mpart[0][r] + mpart[1][r]) + (mpart[2][r] + mpart[3][r])) + __ldg(p.bh_fold + nc);
+          m = 1.f / (1.f + __expf(-acc));
+        }
         const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
         const float* bg = p.bias + t.nt * p.BN;
         const float* bb = bg + cn;
         uint8_t* orow = obuf + ob * htile_bytes + r * 128;
-        for (int j = half * (cn >> 1); j < (half + 1) * (cn >> 1); j += 16) {
-          uint32_t g[16], b[16];
+        const int cq = cn >> 2;  // columns per warp
+        for (int j = quarter * cq; j < (quarter + 1) * cq; j += 8) {
+          uint32_t g[8], b[8];
           __syncwarp();
-          tmem_ld16(t_addr + j, g);
-          tmem_ld16(t_addr + cn + j, b);
+          tmem_ld8(t_addr + j, g);
+          tmem_ld8(t_addr + cn + j, b);
           const int bx = j >> 6, q0 = (j & 63) >> 3;
           const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q0 ^ sw) << 4));
-          const uint4 h1 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + (((q0 + 1) ^ sw) << 4));
+          const float4 u0 = __ldg(reinterpret_cast<const float4*>(bg + j));
+          const float4 u1 = __ldg(reinterpret_cast<const float4*>(bg + j) + 1);
+          const float4 v0 = __ldg(reinterpret_cast<const float4*>(bb + j));
+          const float4 v1 = __ldg(reinterpret_cast<const float4*>(bb + j) + 1);
           tmem_ld_wait();
-          const uint32_t qq[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
-          float o[16], bgv[16], bbv[16];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 u = __ldg(reinterpret_cast<const float4*>(bg + j) + i);
-            const float4 w = __ldg(reinterpret_cast<const float4*>(bb + j) + i);
-            bgv[4 * i] = u.x; bgv[4 * i + 1] = u.y; bgv[4 * i + 2] = u.z; bgv[4 * i + 3] = u.w;
-            bbv[4 * i] = w.x; bbv[4 * i + 1] = w.y; bbv[4 * i + 2] = w.z; bbv[4 * i + 3] = w.w;
-          }
+          const uint32_t qq[4] = {h0.x, h0.y, h0.z, h0.w};
+          const float bgv[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+          const float bbv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+          float o[8];
           const float4* parj = par + j;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
+          for (int i = 0; i < 8; ++i) {
             const float x = (i & 1) ? bf16hi(qq[i >> 1]) : bf16lo(qq[i >> 1]);
             const float4 pr = __ldg(parj + i);
             const float hn = fmaf(x, pr.x, pr.y);
@@ -424,22 +450,17 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const float I = fmaf(pr.z, hn, pr.w);
             o[i] = fmaxf(fmaf(m, I - A, A), 0.f);
           }
-          uint4 s0, s1;
+          uint4 s0;
           s0.x = pack_bf16(o[0], o[1]);
           s0.y = pack_bf16(o[2], o[3]);
           s0.z = pack_bf16(o[4], o[5]);
           s0.w = pack_bf16(o[6], o[7]);
-          s1.x = pack_bf16(o[8], o[9]);
-          s1.y = pack_bf16(o[10], o[11]);
-          s1.z = pack_bf16(o[12], o[13]);
-          s1.w = pack_bf16(o[14], o[15]);
           *reinterpret_cast<uint4*>(orow + bx * 16384 + ((q0 ^ sw) << 4)) = s0;
-          *reinterpret_cast<uint4*>(orow + bx * 16384 + (((q0 + 1) ^ sw) << 4)) = s1;
         }
         fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to the TMA (async proxy)
         tc_fence_before();
         named_bar_sync(1, 32 * kIgemmEpiWarps);
-        if (threadIdx.x == 64) {
+        if (threadIdx.x == 32 * kIgemmEpiWarp0) {
           for (int bx = 0; bx < hbox; ++bx)
             tma_store_4d(&p.tmO, obuf + ob * htile_bytes + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);
           bulk_commit();
@@ -454,7 +475,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   }
 
   // ------------------------------ teardown ------------------------------------
-  if (threadIdx.x == 64) bulk_wait<0>();  // outstanding TMA stores of the AAD epilogue
+  if (threadIdx.x == 32 * kIgemmEpiWarp0) bulk_wait<0>();  // outstanding TMA stores of the AAD epilogue
   tc_fence_before();
   __syncthreads();
   if (abort_flag && threadIdx.x == 0 && p.err) {
@@ -497,6 +518,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm: M box must hold 1..128 rows";
   if (p.stages < 2 || p.stages > 8) return "igemm: stages must be in [2,8]";
+  if (p.dual && p.stages < 4) return "igemm: two issuers need at least four ring slots";
   if (p.mode == kModeAAD && (p.h_bufs < 2 || p.h_bufs > 4 || p.o_bufs < 1 || p.o_bufs > 2)) return "igemm: bad AAD buffering";
   if (p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm: bad tmem_cols";

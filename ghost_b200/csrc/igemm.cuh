@@ -8,8 +8,10 @@
 namespace ghost {
 
 constexpr int kIgemmMaxTaps = 16;
-constexpr int kIgemmEpiWarps = 8;                            // two warps per TMEM lane group, splitting the columns
-constexpr int kIgemmThreads = 64 + 32 * kIgemmEpiWarps;      // warp0 TMA, warp1 MMA, warps2-9 epilogue
+constexpr int kIgemmEpiWarps = 16;                           // four warps per TMEM lane group, splitting the columns
+constexpr int kIgemmMmaWarps = 2;                            // MMA issuers: warp 1 takes even tiles, warp 2 odd tiles
+constexpr int kIgemmEpiWarp0 = 1 + kIgemmMmaWarps;           // first epilogue warp
+constexpr int kIgemmThreads = 32 * (kIgemmEpiWarp0 + kIgemmEpiWarps);  // warp0 TMA, warps1-2 MMA, warps3-18 epilogue
 
 enum IgemmMode : int { kModeLinear = 0, kModeAAD = 1 };
 enum Act1 : int { kActNone = 0, kActLeaky = 1, kActPRelu = 2, kActRelu = 3 };
@@ -43,6 +45,7 @@ struct alignas(64) IgemmParams {
   // Row-window mode (3x3 stride-1 convs on wide images, bh == bn == 1, kc == 64): one TMA box of bw+2 pixels per
   // (kernel row, 64-channel chunk) serves the three horizontal taps as row-shifted UMMA views, so the A operand
   // crosses L2->shared 3x instead of 9x.  b_res: the whole packed weight slab stays resident in shared memory.
+  int dual;    // 1: two MMA issuer warps (even / odd tiles), each with its own half of the operand ring
   int a_win;   // 0 off, 1 on (the UMMA descriptor start address carries the row shift)
   int b_res;
 
