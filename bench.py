@@ -170,17 +170,17 @@ def run_ours(args):
     pin = lambda a: torch.from_numpy(a).pin_memory()
     sources_p, crops_p, frames_p = pin(sources_h), pin(crops_h), pin(frames_h)
     out_p = torch.empty_like(frames_p).pin_memory()
-    masks_d = torch.from_numpy(masks_h).to(dev)
+    masks_p = pin(masks_h)
+    masks_d = masks_p.to(dev)
     sources_d, crops_d, frames_d = sources_p.to(dev), crops_p.to(dev), frames_p.to(dev)
     out_d = torch.empty_like(frames_d)
 
     def step_device(src, crp, frm, out):
         z = arc.embed_hwc(src, out_dtype=torch.bfloat16)
-        G.swap_u8(crp, z, out=None if False else swapped)          # generator output stays on the device
+        G.swap_u8(crp, z, write_u8=False)                          # generator output stays on the device
         yptr, ydt = G.y_nhwc(B, dev)
         ghost_b200.paste_back(frm, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out)
 
-    swapped = torch.empty((B, 256, 256, 3), dtype=torch.uint8, device=dev)
 
     def barrier():
         torch.cuda.synchronize()
@@ -204,19 +204,21 @@ def run_ours(args):
     clocks = sampler.summary()
 
     # ---------------------------------------------------------------- end-to-end timing with host buffers (e2e)
+    # The public streaming call: every step uploads its sources, crops, frames and masks from pinned host memory
+    # and downloads the composited frames; SwapPipeline double-buffers the three stages over CUDA streams, the
+    # last download is inside the timed region (flush before the closing event).
+    pipe = ghost_b200.SwapPipeline(G, arc, B, (H, W), depth=2, mode="exact")
     def step_e2e():
-        s = sources_p.to(dev, non_blocking=True)
-        c = crops_p.to(dev, non_blocking=True)
-        f = frames_p.to(dev, non_blocking=True)
-        step_device(s, c, f, out_d)
-        out_p.copy_(out_d, non_blocking=True)
-    for _ in range(2):
+        pipe.submit(sources_p, crops_p, frames_p, masks_p, tfms, face_frame, out_p)
+    for _ in range(3):
         step_e2e()
+    pipe.flush()
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     for _ in range(args.steps):
         step_e2e()
+    pipe.flush()
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
@@ -237,7 +239,7 @@ def run_ours(args):
         # queue the paste launches behind a long-running forward so that the events bracket GPU time only
         # (the call's host-side preparation would otherwise dominate a 0.2 ms kernel)
         z_warm = arc.embed_hwc(sources_d, out_dtype=torch.bfloat16)
-        G.swap_u8(crops_d, z_warm, out=swapped)
+        G.swap_u8(crops_d, z_warm, write_u8=False)
         p0.record()
         for _ in range(3):
             ghost_b200.paste_back(frames_d, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out_d)
@@ -265,15 +267,15 @@ def run_ours(args):
                     "unit": "GB/s", "frac": a / pk["hbm"], "ms_per_step": ms}
         roofline_hbm = [hbm(aad_ms, aad_by, aad_n, "igemm_kernel AAD mode (gamma/beta GEMM + fused IN/mask/blend/ReLU)"),
                         hbm(st_ms, st_by, st_n, "in_stats_kernel"), hbm(up_ms, up_by, up_n, "upsample2x_kernel"),
-                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 1, "paste_kernel (exact mode)")]
+                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 3, "paste-back: frame copy + resize_crops_kernel + paste_faces_kernel (exact mode)")]
 
         n_launch_g, flops_g = G.stats(B)
         n_launch_a, flops_a = arc.stats(B)
-        launches_per_step = n_launch_g + n_launch_a + 2 + 1 + 1   # + preproc, arcface preproc, postproc, paste
+        launches_per_step = n_launch_g + n_launch_a + 2 + 2   # + preproc, arcface preproc, crop resize, face paste (the frame copy is a memcpy)
         cpu_fps, cpu_sec, cores = cpu_baseline_run(2, 2, 1)
         fps = B * world * args.steps / (ms_total * 1e-3)
         fps_e2e = B * world * args.steps / (ms_e2e * 1e-3)
-        h2d = sources_p.numel() + crops_p.numel() + frames_p.numel()
+        h2d = sources_p.numel() + crops_p.numel() + frames_p.numel() + masks_p.numel() * masks_p.element_size()
         line = {
             "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

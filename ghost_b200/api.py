@@ -282,10 +282,11 @@ class AEI_Net(_Net):
             _lib.check(lib.ghost_aei_encode(h, _ptr(X), _DT[X.dtype], ptrs, _DT[self._dtype], B, _stream()))
         return attrs
 
-    def swap_u8(self, crops_bgr, z_id, out=None):
+    def swap_u8(self, crops_bgr, z_id, out=None, write_u8=True):
         """Fused transform_target_to_torch + faceshifter_batch (core.py:13-26, faceshifter_run.py:5-23) without
         the bounce through the host: uint8 BGR crops [B,256,256,3] on the device -> uint8 BGR [B,256,256,3] on
-        the device.  z_id is [1,c_id] (tiled over the batch as faceshifter_batch does) or [B,c_id]."""
+        the device.  z_id is [1,c_id] (tiled over the batch as faceshifter_batch does) or [B,c_id].
+        write_u8=False skips the uint8 conversion (the paste-back reads the generator output through y_nhwc)."""
         _require_cuda(crops_bgr, "crops_bgr")
         _require_cuda(z_id, "z_id")
         if crops_bgr.dtype != torch.uint8 or crops_bgr.dim() != 4 or tuple(crops_bgr.shape[1:]) != (256, 256, 3):
@@ -298,11 +299,12 @@ class AEI_Net(_Net):
         lib = _lib.load()
         with torch.cuda.device(crops_bgr.device):
             h = self._handle(crops_bgr.device)
-            if out is None:
+            if out is None and write_u8:
                 out = torch.empty_like(crops_bgr)
-            _lib.check(lib.ghost_aei_swap_u8(h, _ptr(crops_bgr), _ptr(z), _DT[z.dtype], z.shape[0], _ptr(out), B,
+            optr = _ptr(out) if write_u8 else None
+            _lib.check(lib.ghost_aei_swap_u8(h, _ptr(crops_bgr), _ptr(z), _DT[z.dtype], z.shape[0], optr, B,
                                              _stream()))
-        return out
+        return out if write_u8 else None
 
     def y_nhwc(self, B, device=None):
         """(device pointer, ghost dtype) of the NHWC generator output of the last forward at batch B."""
@@ -498,6 +500,72 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
     with torch.cuda.device(dev):
         _lib.check(lib.ghost_paste_back(C.byref(d), _stream()))
     return out
+
+
+class SwapPipeline(object):
+    """The per-batch video loop of the reference (utils/inference/core.py:model_inference ->
+    faceshifter_batch -> video_processing.py:get_final_video) as one double-buffered device pipeline:
+
+        pinned host batch --H2D--> ArcFace z_id -> AEI_Net swap -> paste-back --D2H--> pinned host frames
+
+    Uploads, compute and downloads run on three CUDA streams over `depth` device slots, so the PCIe copies of
+    neighbouring batches overlap the generator.  Results are bit-identical to calling embed_hwc / swap_u8 /
+    paste_back one after the other.  Call submit() per batch and flush() before reading the last outputs."""
+
+    def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
+        self.G, self.arc, self.B, self.mode, self.depth = G, arc, int(batch), mode, int(depth)
+        self.dev = device or torch.device("cuda", torch.cuda.current_device())
+        H, W = frame_hw
+        u8 = dict(dtype=torch.uint8, device=self.dev)
+        self.slots = []
+        for _ in range(self.depth):
+            self.slots.append({
+                "src": torch.empty((self.B, 224, 224, 3), **u8), "crp": torch.empty((self.B, 256, 256, 3), **u8),
+                "frm": torch.empty((self.B, H, W, 3), **u8), "out": torch.empty((self.B, H, W, 3), **u8),
+                "msk": torch.empty((self.B, 224, 224), dtype=mask_dtype, device=self.dev),
+                "ev_in": torch.cuda.Event(), "ev_done": torch.cuda.Event(), "ev_out": torch.cuda.Event(), "used": False})
+        self.s_in = torch.cuda.Stream(device=self.dev)
+        self.s_out = torch.cuda.Stream(device=self.dev)
+        self.i = 0
+
+    def submit(self, sources, crops, frames, masks, tfms, face_frame, out):
+        """sources uint8 RGB [B,224,224,3], crops uint8 BGR [B,256,256,3], frames uint8 BGR [B,H,W,3], masks
+        [B,224,224]: pinned host tensors of one batch; tfms / face_frame as in paste_back (one face per entry);
+        out: pinned host tensor [B,H,W,3] that receives the composited frames (valid after flush())."""
+        slot = self.slots[self.i % self.depth]
+        self.i += 1
+        main = torch.cuda.current_stream(self.dev)
+        if slot["used"]:
+            self.s_in.wait_event(slot["ev_done"])   # the step that last read this slot's inputs has finished
+        with torch.cuda.stream(self.s_in):
+            slot["src"].copy_(sources, non_blocking=True)
+            slot["crp"].copy_(crops, non_blocking=True)
+            slot["frm"].copy_(frames, non_blocking=True)
+            slot["msk"].copy_(masks, non_blocking=True)
+            slot["ev_in"].record(self.s_in)
+        main.wait_event(slot["ev_in"])
+        if slot["used"]:
+            main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
+        z = self.arc.embed_hwc(slot["src"], out_dtype=torch.bfloat16 if self.G.dtype == torch.bfloat16 else torch.float32)
+        self.G.swap_u8(slot["crp"], z, write_u8=False)
+        yptr, ydt = self.G.y_nhwc(self.B, self.dev)
+        paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=slot["out"])
+        slot["ev_done"].record(main)
+        self.s_out.wait_event(slot["ev_done"])
+        with torch.cuda.stream(self.s_out):
+            out.copy_(slot["out"], non_blocking=True)
+            slot["ev_out"].record(self.s_out)
+        slot["used"] = True
+        return out
+
+    def flush(self):
+        """Make the current stream wait for every outstanding download (then synchronize it to read `out`)."""
+        main = torch.cuda.current_stream(self.dev)
+        for slot in self.slots:
+            if slot["used"]:
+                main.wait_event(slot["ev_out"])
 
 
 def _masks_from_handler(swaps224, crop_frames, handler, params):

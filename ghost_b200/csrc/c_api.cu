@@ -340,11 +340,13 @@ int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
       prev = f;
       start[f + 1]++;
       paste_prepare_face(&faces[i], d->tfm + 6 * i, d->H, d->W, d->face_crop[i], d->face_mask[i]);
+      faces[i].frame = f;
     }
     for (int f = 0; f < d->n_frames; ++f) start[f + 1] += start[f];
     const size_t fb = faces.size() * sizeof(PasteFace), sb = start.size() * sizeof(int);
     const size_t fb_al = (fb + 255) / 256 * 256;
-    char* scratch = static_cast<char*>(paste_scratch(fb_al + sb));
+    const size_t sb_al = (sb + 255) / 256 * 256;
+    char* scratch = static_cast<char*>(paste_scratch(fb_al + sb_al + paste_rz_bytes(d->n_faces > 0 ? d->n_crops : 0)));
     check_cuda(cudaMemcpyAsync(scratch, faces.data(), fb, cudaMemcpyHostToDevice, s), "faces upload");
     check_cuda(cudaMemcpyAsync(scratch + fb_al, start.data(), sb, cudaMemcpyHostToDevice, s), "face index upload");
     DeviceTables& t = resize_tables();
@@ -361,7 +363,10 @@ int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
     p.face_start = reinterpret_cast<const int*>(scratch + fb_al);
     p.rs_idx = t.idx; p.rs_a0 = t.a0; p.rs_a1 = t.a1;
     p.mode = d->mode;
-    check_msg(paste_back_launch(p, s), "paste_back");
+    p.n_faces = d->n_faces;
+    p.n_crops = d->n_crops;
+    p.rz = reinterpret_cast<uint8_t*>(scratch + fb_al + sb_al);
+    check_msg(paste_back_launch(p, faces.data(), s), "paste_back");
   });
 }
 

@@ -41,15 +41,32 @@ struct CropSrc {
   }
 };
 
-// cv2.resize(256->224, INTER_LINEAR, uint8) evaluated at one destination pixel / channel.
-__device__ __forceinline__ int resized_px(const CropSrc& cs, const PasteParams& p, int crop, int y, int x, int c) {
-  const int sy = __ldg(p.rs_idx + y), sx = __ldg(p.rs_idx + x);
-  const int ay0 = __ldg(p.rs_a0 + y), ay1 = __ldg(p.rs_a1 + y);
-  const int ax0 = __ldg(p.rs_a0 + x), ax1 = __ldg(p.rs_a1 + x);
-  const int sy1 = min(sy + 1, 255), sx1 = min(sx + 1, 255);
-  const int r0 = cs.px(crop, sy, sx, c) * ax0 + cs.px(crop, sy, sx1, c) * ax1;
-  const int r1 = cs.px(crop, sy1, sx, c) * ax0 + cs.px(crop, sy1, sx1, c) * ax1;
-  return (((ay0 * (r0 >> 4)) >> 16) + ((ay1 * (r1 >> 4)) >> 16) + 2) >> 2;
+// cv2.resize(256->224, INTER_LINEAR, uint8) of every crop, once per batch: rz[crop][y][x] = {B, G, R, 0}.
+// The compositing kernel then samples 4 resized pixels per destination pixel instead of 16 crop pixels.
+__global__ void __launch_bounds__(256) resize_crops_kernel(const PasteParams p) {
+  const CropSrc cs{p.crops, p.crop_kind};
+  const long long total = static_cast<long long>(p.n_crops) * 224 * 224;
+  for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += gridDim.x * 256LL) {
+    const int x = static_cast<int>(i % 224), y = static_cast<int>((i / 224) % 224), crop = static_cast<int>(i / (224 * 224));
+    const int sy = __ldg(p.rs_idx + y), sx = __ldg(p.rs_idx + x);
+    const int ay0 = __ldg(p.rs_a0 + y), ay1 = __ldg(p.rs_a1 + y);
+    const int ax0 = __ldg(p.rs_a0 + x), ax1 = __ldg(p.rs_a1 + x);
+    const int sy1 = min(sy + 1, 255), sx1 = min(sx + 1, 255);
+    uint32_t out = 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const int r0 = cs.px(crop, sy, sx, c) * ax0 + cs.px(crop, sy, sx1, c) * ax1;
+      const int r1 = cs.px(crop, sy1, sx, c) * ax0 + cs.px(crop, sy1, sx1, c) * ax1;
+      const int v = (((ay0 * (r0 >> 4)) >> 16) + ((ay1 * (r1 >> 4)) >> 16) + 2) >> 2;
+      out |= static_cast<uint32_t>(v & 255) << (8 * c);
+    }
+    reinterpret_cast<uint32_t*>(p.rz)[i] = out;
+  }
+}
+
+// packed BGR0 of resized pixel (y, x) of one crop
+__device__ __forceinline__ uint32_t rz_px(const PasteParams& p, int crop, int y, int x) {
+  return __ldg(reinterpret_cast<const uint32_t*>(p.rz) + (static_cast<long long>(crop) * 224 + y) * 224 + x);
 }
 
 __device__ __forceinline__ double mask_at(const PasteParams& p, int mi, int y, int x) {
@@ -60,8 +77,7 @@ __device__ __forceinline__ double mask_at(const PasteParams& p, int mi, int y, i
 }
 
 // One destination pixel, exact mode.  fin[3] is the float64 running composite.
-__device__ __forceinline__ void paste_exact_px(const PasteParams& p, const CropSrc& cs, const PasteFace& f, int x, int y,
-                                               double (&fin)[3]) {
+__device__ __forceinline__ void paste_exact_px(const PasteParams& p, const PasteFace& f, int x, int y, double (&fin)[3]) {
   // cv2.warpAffine fixed-point coordinates (AB_BITS = 10, INTER_BITS = 5)
   const long long adelta = __double2ll_rn(__dmul_rn(__dmul_rn(f.M[0], static_cast<double>(x)), 1024.0));
   const long long bdelta = __double2ll_rn(__dmul_rn(__dmul_rn(f.M[3], static_cast<double>(x)), 1024.0));
@@ -85,19 +101,21 @@ __device__ __forceinline__ void paste_exact_px(const PasteParams& p, const CropS
   if (m == 0.0) return;  // 0*swap + (1-0)*final == final exactly
   const int x0 = min(max(sx, 0), 223), x1 = min(max(sx + 1, 0), 223);
   const int y0 = min(max(sy, 0), 223), y1 = min(max(sy + 1, 0), 223);
+  const uint32_t q00 = rz_px(p, f.crop_index, y0, x0), q01 = rz_px(p, f.crop_index, y0, x1);
+  const uint32_t q10 = rz_px(p, f.crop_index, y1, x0), q11 = rz_px(p, f.crop_index, y1, x1);
   const double om = __dsub_rn(1.0, m);
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const int acc = resized_px(cs, p, f.crop_index, y0, x0, c) * w00 + resized_px(cs, p, f.crop_index, y0, x1, c) * w01 +
-                    resized_px(cs, p, f.crop_index, y1, x0, c) * w10 + resized_px(cs, p, f.crop_index, y1, x1, c) * w11;
+    const int sh = 8 * c;
+    const int acc = static_cast<int>((q00 >> sh) & 255) * w00 + static_cast<int>((q01 >> sh) & 255) * w01 +
+                    static_cast<int>((q10 >> sh) & 255) * w10 + static_cast<int>((q11 >> sh) & 255) * w11;
     const int sw = (acc + 512) >> 10;  // == (sum(src * 32*w) + 16384) >> 15
     fin[c] = __dadd_rn(__dmul_rn(m, static_cast<double>(sw)), __dmul_rn(om, fin[c]));
   }
 }
 
 // Float mode: one destination pixel; fin[] holds the uint8 composite as float.
-__device__ __forceinline__ void paste_float_px(const PasteParams& p, const CropSrc& cs, const PasteFace& f, int x, int y,
-                                               float (&fin)[3]) {
+__device__ __forceinline__ void paste_float_px(const PasteParams& p, const PasteFace& f, int x, int y, float (&fin)[3]) {
   const float fx = __fadd_rn(__fadd_rn(__fmul_rn(f.A[0], x), __fmul_rn(f.A[1], y)), f.A[2]);
   const float fy = __fadd_rn(__fadd_rn(__fmul_rn(f.A[3], x), __fmul_rn(f.A[4], y)), f.A[5]);
   const float x0f = floorf(fx), y0f = floorf(fy);
@@ -107,126 +125,61 @@ __device__ __forceinline__ void paste_float_px(const PasteParams& p, const CropS
   const float w00 = (1.f - ty) * (1.f - tx), w01 = (1.f - ty) * tx, w10 = ty * (1.f - tx), w11 = ty * tx;
   const bool vx0 = sx >= 0, vx1 = sx + 1 < 224, vy0 = sy >= 0, vy1 = sy + 1 < 224;
   float m = 0.f;
-  if (vy0 && vx0) m += static_cast<float>(mask_at(p, f.mask_index, sy, sx)) * w00;
-  if (vy0 && vx1) m += static_cast<float>(mask_at(p, f.mask_index, sy, sx + 1)) * w01;
-  if (vy1 && vx0) m += static_cast<float>(mask_at(p, f.mask_index, sy + 1, sx)) * w10;
-  if (vy1 && vx1) m += static_cast<float>(mask_at(p, f.mask_index, sy + 1, sx + 1)) * w11;
+  uint32_t q00 = 0, q01 = 0, q10 = 0, q11 = 0;
+  if (vy0 && vx0) { m += static_cast<float>(mask_at(p, f.mask_index, sy, sx)) * w00; q00 = rz_px(p, f.crop_index, sy, sx); }
+  if (vy0 && vx1) { m += static_cast<float>(mask_at(p, f.mask_index, sy, sx + 1)) * w01; q01 = rz_px(p, f.crop_index, sy, sx + 1); }
+  if (vy1 && vx0) { m += static_cast<float>(mask_at(p, f.mask_index, sy + 1, sx)) * w10; q10 = rz_px(p, f.crop_index, sy + 1, sx); }
+  if (vy1 && vx1) { m += static_cast<float>(mask_at(p, f.mask_index, sy + 1, sx + 1)) * w11; q11 = rz_px(p, f.crop_index, sy + 1, sx + 1); }
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
+    const int sh = 8 * c;
     float sw = 0.f;
-    if (vy0 && vx0) sw += static_cast<float>(resized_px(cs, p, f.crop_index, sy, sx, c)) * w00;
-    if (vy0 && vx1) sw += static_cast<float>(resized_px(cs, p, f.crop_index, sy, sx + 1, c)) * w01;
-    if (vy1 && vx0) sw += static_cast<float>(resized_px(cs, p, f.crop_index, sy + 1, sx, c)) * w10;
-    if (vy1 && vx1) sw += static_cast<float>(resized_px(cs, p, f.crop_index, sy + 1, sx + 1, c)) * w11;
+    if (vy0 && vx0) sw += static_cast<float>((q00 >> sh) & 255) * w00;
+    if (vy0 && vx1) sw += static_cast<float>((q01 >> sh) & 255) * w01;
+    if (vy1 && vx0) sw += static_cast<float>((q10 >> sh) & 255) * w10;
+    if (vy1 && vx1) sw += static_cast<float>((q11 >> sh) & 255) * w11;
     const float v = __fadd_rn(__fmul_rn(m, sw), __fmul_rn(__fsub_rn(1.f, m), fin[c]));
     // faces compose through uint8 (video_processing.py:233,235)
     fin[c] = static_cast<float>(static_cast<int>(fminf(fmaxf(v, 0.f), 255.f)));
   }
 }
 
-// Each thread owns PX horizontally consecutive pixels of one frame: PX = 16 -> three 16-byte vectors,
-// PX = 4 -> three 32-bit words.  Spans that no face box touches (almost all of a 1080p frame) are a straight
-// vector copy; only touched spans run the per-pixel compositing.
-template <int PX>
-__global__ void __launch_bounds__(128) paste_kernel(const PasteParams p) {
-  const int f = blockIdx.z;
-  const int xg = blockIdx.x * blockDim.x + threadIdx.x;  // pixel group index
-  const int y = blockIdx.y;
-  const int x_base = xg * PX;
-  if (x_base >= p.W) return;
-  const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x_base) * 3;
-  constexpr int NB = PX * 3;
-  // the span lives in registers (r0..r2); only a span that a face box touches is spilled to a byte array
-  uint4 r0 = make_uint4(0, 0, 0, 0), r1 = r0, r2 = r0;
-  if (PX == 16) {
-    const uint4* s = reinterpret_cast<const uint4*>(p.frames_in + off);
-    r0 = __ldg(s);
-    r1 = __ldg(s + 1);
-    r2 = __ldg(s + 2);
-  } else if (PX == 4) {
-    const uint32_t* s = reinterpret_cast<const uint32_t*>(p.frames_in + off);
-    r0.x = __ldg(s);
-    r0.y = __ldg(s + 1);
-    r0.z = __ldg(s + 2);
-  } else {
-    r0.x = p.frames_in[off] | (p.frames_in[off + 1] << 8) | (p.frames_in[off + 2] << 16);
-  }
+// One thread per destination pixel of one face box (blockIdx.z = face).  Frames are copied in -> out beforehand;
+// this kernel rewrites only the pixels inside face boxes.  A pixel covered by several boxes of its frame is owned
+// by the first of them, and its owner composites every face of the frame in order, so the float64 running blend
+// matches the reference's per-frame loop exactly.
+__global__ void __launch_bounds__(256) paste_faces_kernel(const PasteParams p) {
+  const int j = blockIdx.z;
+  const PasteFace& me = p.faces[j];
+  const int x = me.x0 + blockIdx.x * 32 + (threadIdx.x & 31);
+  const int y = me.y0 + blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= me.x1 || y >= me.y1) return;
+  const int f = me.frame;
   const int fs = __ldg(p.face_start + f), fe = __ldg(p.face_start + f + 1);
-  bool span_touched = false;
-  for (int j = fs; j < fe; ++j) {
-    const PasteFace& face = p.faces[j];
-    span_touched |= (x_base + PX > face.x0 && x_base < face.x1 && y >= face.y0 && y < face.y1);
+  for (int k = fs; k < j; ++k) {
+    const PasteFace& o = p.faces[k];
+    if (x >= o.x0 && x < o.x1 && y >= o.y0 && y < o.y1) return;  // an earlier box owns this pixel
   }
-  if (!span_touched) {
-    if (PX == 16) {
-      uint4* d = reinterpret_cast<uint4*>(p.frames_out + off);
-      d[0] = r0;
-      d[1] = r1;
-      d[2] = r2;
-    } else if (PX == 4) {
-      uint32_t* d = reinterpret_cast<uint32_t*>(p.frames_out + off);
-      d[0] = r0.x;
-      d[1] = r0.y;
-      d[2] = r0.z;
-    } else {
-      p.frames_out[off] = r0.x & 255;
-      p.frames_out[off + 1] = (r0.x >> 8) & 255;
-      p.frames_out[off + 2] = (r0.x >> 16) & 255;
+  const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x) * 3;
+  const int b0 = p.frames_in[off], b1 = p.frames_in[off + 1], b2 = p.frames_in[off + 2];
+  if (p.mode == kPasteExact) {
+    double fd[3] = {static_cast<double>(b0), static_cast<double>(b1), static_cast<double>(b2)};
+    for (int k = j; k < fe; ++k) {
+      const PasteFace& face = p.faces[k];
+      if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
+      paste_exact_px(p, face, x, y, fd);
     }
-    return;
-  }
-  union alignas(16) Span {
-    uint4 v[3];
-    uint32_t w[12];
-    uint8_t b[48];
-  } sp;
-  sp.v[0] = r0;
-  sp.v[1] = r1;
-  sp.v[2] = r2;
-  {
-    CropSrc cs{p.crops, p.crop_kind};
-    for (int i = 0; i < PX; ++i) {
-      const int x = x_base + i;
-      bool touched = false;
-      double fd[3];
-      float ff[3];
-      for (int j = fs; j < fe; ++j) {
-        const PasteFace& face = p.faces[j];
-        if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
-        if (!touched) {
-          touched = true;
 #pragma unroll
-          for (int c = 0; c < 3; ++c) {
-            fd[c] = static_cast<double>(sp.b[i * 3 + c]);
-            ff[c] = static_cast<float>(sp.b[i * 3 + c]);
-          }
-        }
-        if (p.mode == kPasteExact)
-          paste_exact_px(p, cs, face, x, y, fd);
-        else
-          paste_float_px(p, cs, face, x, y, ff);
-      }
-      if (touched) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-          sp.b[i * 3 + c] = p.mode == kPasteExact ? static_cast<uint8_t>(static_cast<int>(fd[c]))
-                                                  : static_cast<uint8_t>(static_cast<int>(ff[c]));
-      }
-    }
-  }
-  if (PX == 16) {
-    uint4* d = reinterpret_cast<uint4*>(p.frames_out + off);
-    d[0] = sp.v[0];
-    d[1] = sp.v[1];
-    d[2] = sp.v[2];
-  } else if (PX == 4) {
-    uint32_t* d = reinterpret_cast<uint32_t*>(p.frames_out + off);
-    d[0] = sp.w[0];
-    d[1] = sp.w[1];
-    d[2] = sp.w[2];
+    for (int c = 0; c < 3; ++c) p.frames_out[off + c] = static_cast<uint8_t>(static_cast<int>(fd[c]));
   } else {
+    float ff[3] = {static_cast<float>(b0), static_cast<float>(b1), static_cast<float>(b2)};
+    for (int k = j; k < fe; ++k) {
+      const PasteFace& face = p.faces[k];
+      if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
+      paste_float_px(p, face, x, y, ff);
+    }
 #pragma unroll
-    for (int i = 0; i < NB; ++i) p.frames_out[off + i] = sp.b[i];
+    for (int c = 0; c < 3; ++c) p.frames_out[off + c] = static_cast<uint8_t>(static_cast<int>(ff[c]));
   }
 }
 
@@ -372,19 +325,24 @@ void paste_prepare_face(PasteFace* f, const double* t, int H, int W, int crop_in
   f->mask_index = mask_index;
 }
 
-const char* paste_back_launch(const PasteParams& p, cudaStream_t s) {
+const char* paste_back_launch(PasteParams p, const PasteFace* host_faces, cudaStream_t s) {
   if (p.F <= 0 || p.H <= 0 || p.W <= 0) return "paste_back: empty frame batch";
-  const bool al16 = (reinterpret_cast<uintptr_t>(p.frames_in) % 16 == 0) && (reinterpret_cast<uintptr_t>(p.frames_out) % 16 == 0);
-  if (p.W % 16 == 0 && al16) {
-    dim3 grid((p.W / 16 + 127) / 128, p.H, p.F);
-    paste_kernel<16><<<grid, 128, 0, s>>>(p);
-  } else if (p.W % 4 == 0 && al16) {
-    dim3 grid((p.W / 4 + 127) / 128, p.H, p.F);
-    paste_kernel<4><<<grid, 128, 0, s>>>(p);
-  } else {
-    dim3 grid((p.W + 127) / 128, p.H, p.F);
-    paste_kernel<1><<<grid, 128, 0, s>>>(p);
+  if (p.frames_out != p.frames_in) {
+    const size_t bytes = static_cast<size_t>(p.F) * p.H * p.W * 3;
+    cudaError_t e = cudaMemcpyAsync(p.frames_out, p.frames_in, bytes, cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
   }
+  if (p.n_faces <= 0) return last_err();
+  p.max_bw = p.max_bh = 0;
+  for (int i = 0; i < p.n_faces; ++i) {
+    const int bw = host_faces[i].x1 - host_faces[i].x0, bh = host_faces[i].y1 - host_faces[i].y0;
+    p.max_bw = bw > p.max_bw ? bw : p.max_bw;
+    p.max_bh = bh > p.max_bh ? bh : p.max_bh;
+  }
+  if (p.max_bw <= 0 || p.max_bh <= 0) return last_err();  // every face lies outside its frame
+  resize_crops_kernel<<<grid_for(static_cast<long long>(p.n_crops) * 224 * 224, 256), 256, 0, s>>>(p);
+  dim3 grid((p.max_bw + 31) / 32, (p.max_bh + 7) / 8, p.n_faces);
+  paste_faces_kernel<<<grid, 256, 0, s>>>(p);
   return last_err();
 }
 

@@ -17,6 +17,8 @@ struct PasteFace {
   int x0, y0, x1, y1;  // destination bounding box of the 224x224 crop square (exclusive upper bounds)
   int crop_index;  // which 256x256 crop of the batch
   int mask_index;  // which 224x224 mask
+  int frame;       // destination frame
+  int pad_;
 };
 
 struct PasteParams {
@@ -33,6 +35,10 @@ struct PasteParams {
   const short* rs_a0;           // [224] 11-bit coefficient of the left/top sample
   const short* rs_a1;           // [224] 11-bit coefficient of the right/bottom sample
   int mode;
+  // filled by the launcher
+  int n_faces, n_crops;
+  int max_bw, max_bh;  // largest face box of the batch (grid extent of the compositing kernel)
+  uint8_t* rz;         // scratch [n_crops][224][224][4]: crops after cv2.resize 256->224, BGR0 per pixel
 };
 
 // tfm: 2x3 float64 frame->crop(224) affine (row-major).  Computes M / A and the bounding box.
@@ -40,7 +46,10 @@ void paste_prepare_face(PasteFace* f, const double* tfm, int H, int W, int crop_
 // 224-entry cv2.resize tables (host): idx, a0, a1
 void paste_resize_tables(short* idx, short* a0, short* a1);
 
-const char* paste_back_launch(const PasteParams& p, cudaStream_t s);
+// bytes of scratch paste_back_launch needs behind p.rz
+inline size_t paste_rz_bytes(int n_crops) { return static_cast<size_t>(n_crops) * 224 * 224 * 4; }
+// host_faces: the same PasteFace records p.faces points at (device), for the launch geometry
+const char* paste_back_launch(PasteParams p, const PasteFace* host_faces, cudaStream_t s);
 
 // F1: uint8 BGR NHWC 256x256 crops -> normalised RGB NHWC-3 activations (utils/inference/core.py:13-26)
 const char* preproc_u8_launch(const uint8_t* src, void* dst, int dst_dtype, long long npix, int half_rounding,
