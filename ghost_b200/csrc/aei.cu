@@ -306,14 +306,16 @@ void Net::build_aei(ExecPlan& p) {
     add_op("gen.up1", [=](cudaStream_t s) { return zfc_to_act_launch(zfc, ldz, 0, 4096, nullptr, mm.p, dt, B, s); });
   }
 
+  float* sums_next = nullptr;  // statistics of m written by the previous block's fused upsample
   for (int k = 1; k <= 8; ++k) {
     const BlockSpec& b = blocks[k - 1];
     const int hw = 2 << (k - 1);
     const int HW = hw * hw;
     const Act& za = z[k];
     const int parts_in = in_stats_parts(B, HW, b.cin);
-    float* sums_m = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * b.cin);
-    {
+    float* sums_m = sums_next;
+    if (!sums_m) {
+      sums_m = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * b.cin);
       const Act mm = m;
       add_op(S("blk%d.stats_m", k), [=](cudaStream_t s) { return in_stats_launch(mm.p, dt, B, HW, mm.C, sums_m, s); },
              kOpStats, static_cast<double>(B) * HW * mm.C * esz);
@@ -396,11 +398,15 @@ void Net::build_aei(ExecPlan& p) {
     p.named[S("y%d", k)] = y;
     p.named[S("a%d", k)] = a;  // output of the block's last AADLayer+ReLU
     if (k < 8) {
+      // bilinear x2 (AEI_Net.py:124-138) fused with the InstanceNorm statistics of the next block's input
       Act nm = new_act(2 * hw, 2 * hw, b.cout);
       const Act yy = y, nn = nm;
-      add_op(S("blk%d.upsample", k), [=](cudaStream_t s) {
-        return upsample2x_launch(yy.p, nn.p, dt, B, yy.H, yy.W, yy.C, nn.C, 0, s);
+      const int parts_nx = in_stats_parts(B, 4 * HW, b.cout);
+      float* sums_nx = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_nx + 1) * b.cout);
+      add_op(S("blk%d.upsample_stats", k), [=](cudaStream_t s) {
+        return upsample2x_stats_launch(yy.p, nn.p, dt, B, yy.H, yy.W, yy.C, sums_nx, s);
       }, kOpUpsample, 5.0 * B * yy.H * yy.W * yy.C * esz);
+      sums_next = sums_nx;
       m = nm;
       p.named[S("m%d", k + 1)] = m;
     } else {

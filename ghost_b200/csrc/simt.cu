@@ -322,14 +322,22 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
   const T* base = x + (static_cast<long long>(n) * HW) * C + cv * 8;
   load8(base, sft);
   if (pl < ppi) {
-    for (int p = p0 + pl; p < p1; p += ppi) {
-      float v[8];
-      load8(base + static_cast<long long>(p) * C, v);
+    // four independent 16-byte loads in flight per thread: the kernel is a pure HBM stream
+    for (int p = p0 + pl; p < p1; p += 4 * ppi) {
+      float v[4][8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float d = v[i] - sft[i];
-        s[i] += d;
-        q[i] = fmaf(d, d, q[i]);
+      for (int u = 0; u < 4; ++u)
+        if (p + u * ppi < p1) load8(base + static_cast<long long>(p + u * ppi) * C, v[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (p + u * ppi < p1) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float d = v[u][i] - sft[i];
+            s[i] += d;
+            q[i] = fmaf(d, d, q[i]);
+          }
+        }
       }
     }
   }
@@ -358,26 +366,50 @@ __global__ void aad_fold_kernel(const float* __restrict__ parts, int P, int HW, 
                                 int ldz, int off_gamma, int off_beta, const float* __restrict__ w_h, float b_h,
                                 float4* __restrict__ ncpar, float* __restrict__ wh_fold, float* __restrict__ bh_fold) {
   __shared__ float red[32];
+  __shared__ double shs[256], shq[256];
   const int n = blockIdx.x;
   const double inv = 1.0 / static_cast<double>(HW);
   const float* pn = parts + static_cast<long long>(n) * (2 * P + 1) * C;
   float part = 0.f;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    double su = 0.0, sq = 0.0;
-    for (int p = 0; p < P; ++p) {
-      su += static_cast<double>(pn[(2 * p) * C + c]);
-      sq += static_cast<double>(pn[(2 * p + 1) * C + c]);
+  // 256 threads = CW channels x L part-lanes; every lane adds its parts in a fixed order, lane 0 adds the lanes in
+  // a fixed order: the statistics stay deterministic however many parts the producers wrote
+  const int CW = C < 256 ? C : 256;
+  const int L = 256 / CW;
+  const int cl = threadIdx.x % CW, lane = threadIdx.x / CW;
+  for (int c0 = 0; c0 < C; c0 += CW) {
+    const int c = c0 + cl;
+    double su0 = 0.0, su1 = 0.0, sq0 = 0.0, sq1 = 0.0;
+    if (lane < L && c < C) {
+      for (int p = lane; p < P; p += 2 * L) {
+        su0 += static_cast<double>(pn[(2 * p) * C + c]);
+        sq0 += static_cast<double>(pn[(2 * p + 1) * C + c]);
+        if (p + L < P) {
+          su1 += static_cast<double>(pn[(2 * (p + L)) * C + c]);
+          sq1 += static_cast<double>(pn[(2 * (p + L) + 1) * C + c]);
+        }
+      }
     }
-    const double d = su * inv;
-    const float mu = static_cast<float>(static_cast<double>(pn[2 * P * C + c]) + d);
-    const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));  // biased variance (InstanceNorm2d)
-    const float rstd = 1.0f / sqrtf(var + 1e-5f);
-    const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
-    const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
-    ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
-    const float w = w_h[c] * rstd;
-    wh_fold[static_cast<long long>(n) * C + c] = w;
-    part += w * mu;
+    shs[threadIdx.x] = su0 + su1;
+    shq[threadIdx.x] = sq0 + sq1;
+    __syncthreads();
+    if (lane == 0 && c < C) {
+      double su = 0.0, sq = 0.0;
+      for (int l = 0; l < L; ++l) {
+        su += shs[l * CW + cl];
+        sq += shq[l * CW + cl];
+      }
+      const double d = su * inv;
+      const float mu = static_cast<float>(static_cast<double>(pn[2 * P * C + c]) + d);
+      const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));  // biased variance (InstanceNorm2d)
+      const float rstd = 1.0f / sqrtf(var + 1e-5f);
+      const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
+      const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
+      ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
+      const float w = w_h[c] * rstd;
+      wh_fold[static_cast<long long>(n) * C + c] = w;
+      part += w * mu;
+    }
+    __syncthreads();
   }
   for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
@@ -460,8 +492,9 @@ namespace {
 // pixels per block of the statistics kernel for a tensor of N images x HW pixels x C channels
 int stats_pix_per_block(int N, int HW, int C) {
   const int ppi = kStatThreads / (C / 8);
-  // aim for ~4 waves of 148 SMs worth of blocks, but at least 8 iterations per block
-  const int blocks_x = (592 + N - 1) / N;
+  // aim for ~16 blocks per SM (four waves at four resident blocks): a grid of barely more than one wave loses up
+  // to half its time in the tail; but at least 8 iterations per block
+  const int blocks_x = (148 * 16 + N - 1) / N;
   int ppb = (HW + blocks_x - 1) / blocks_x;
   if (ppb < ppi * 8) ppb = ppi * 8;
   return ppb;
@@ -521,33 +554,110 @@ namespace {
 template <typename T>
 __global__ void __launch_bounds__(256) upsample2x_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H,
                                                           int W, int C, int oC, int o_c0) {
+  // grid: x = chunks of one output row (pixels x channel vectors), y = output row, z = image
   const int Ho = 2 * H, Wo = 2 * W, vecs = C >> 3;
-  const long long total = static_cast<long long>(N) * Ho * Wo * vecs;
+  const int oh = blockIdx.y, n = blockIdx.z;
   const float sh = Ho > 1 ? static_cast<float>(H - 1) / static_cast<float>(Ho - 1) : 0.f;
   const float sw = Wo > 1 ? static_cast<float>(W - 1) / static_cast<float>(Wo - 1) : 0.f;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cv = static_cast<int>(i % vecs);
-    long long t = i / vecs;
-    const int ow = static_cast<int>(t % Wo);
-    t /= Wo;
-    const int oh = static_cast<int>(t % Ho);
-    const int n = static_cast<int>(t / Ho);
-    // ATen upsample_bilinear2d (align_corners): src = dst * (in-1)/(out-1), lambda in fp32
-    const float fh = sh * oh, fw = sw * ow;
-    const int h0 = static_cast<int>(fh), w0 = static_cast<int>(fw);
-    const int h1 = h0 + (h0 < H - 1 ? 1 : 0), w1 = w0 + (w0 < W - 1 ? 1 : 0);
-    const float lh = fh - h0, lw = fw - w0;
-    const T* base = x + static_cast<long long>(n) * H * W * C + cv * 8;
+  // ATen upsample_bilinear2d (align_corners): src = dst * (in-1)/(out-1), lambda in fp32
+  const float fh = sh * oh;
+  const int h0 = static_cast<int>(fh);
+  const int h1 = h0 + (h0 < H - 1 ? 1 : 0);
+  const float lh = fh - h0;
+  const T* base = x + static_cast<long long>(n) * H * W * C;
+  T* orow = y + (static_cast<long long>(n) * Ho + oh) * Wo * oC + o_c0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < Wo * vecs; i += gridDim.x * blockDim.x) {
+    const int ow = i / vecs, cv = i - ow * vecs;
+    const float fw = sw * ow;
+    const int w0 = static_cast<int>(fw);
+    const int w1 = w0 + (w0 < W - 1 ? 1 : 0);
+    const float lw = fw - w0;
     float a[8], b[8], c[8], d[8], o[8];
-    load8(base + (static_cast<long long>(h0) * W + w0) * C, a);
-    load8(base + (static_cast<long long>(h0) * W + w1) * C, b);
-    load8(base + (static_cast<long long>(h1) * W + w0) * C, c);
-    load8(base + (static_cast<long long>(h1) * W + w1) * C, d);
+    load8(base + (h0 * W + w0) * C + cv * 8, a);
+    load8(base + (h0 * W + w1) * C + cv * 8, b);
+    load8(base + (h1 * W + w0) * C + cv * 8, c);
+    load8(base + (h1 * W + w1) * C + cv * 8, d);
 #pragma unroll
     for (int k = 0; k < 8; ++k)
       o[k] = (1.f - lh) * ((1.f - lw) * a[k] + lw * b[k]) + lh * ((1.f - lw) * c[k] + lw * d[k]);
-    store8(y + ((static_cast<long long>(n) * Ho + oh) * Wo + ow) * oC + o_c0 + cv * 8, o);
+    store8(orow + static_cast<long long>(ow) * oC + cv * 8, o);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ float round_as(float v);
+template <>
+__device__ __forceinline__ float round_as<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float round_as<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16(v)); }
+
+// Bilinear x2 fused with the InstanceNorm statistics of its own output (the next AAD block normalises exactly
+// this tensor, network/AADLayer.py:21): same block / part decomposition and partial-sum layout as
+// in_stats_kernel, the sums run over the values as stored (after rounding to T).  The shift row is source
+// pixel (0,0), which align_corners copies unchanged to output pixel 0.
+template <typename T>
+__global__ void __launch_bounds__(kStatThreads) upsample2x_stats_kernel(const T* __restrict__ x, T* __restrict__ y, int H,
+                                                                         int W, int C, int pix_per_block,
+                                                                         float* __restrict__ parts) {
+  extern __shared__ float sh[];  // [kStatThreads][16]
+  const int n = blockIdx.y;
+  const int P = gridDim.x;
+  const int Ho = 2 * H, Wo = 2 * W, HWo = Ho * Wo;
+  const int vecs = C >> 3;
+  const int ppi = kStatThreads / vecs;
+  const int cv = threadIdx.x % vecs, pl = threadIdx.x / vecs;
+  const int p0 = blockIdx.x * pix_per_block;
+  const int p1 = min(HWo, p0 + pix_per_block);
+  const float shh = static_cast<float>(H - 1) / static_cast<float>(Ho - 1);
+  const float sww = static_cast<float>(W - 1) / static_cast<float>(Wo - 1);
+  float s[8], q[8], sft[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+  const T* base = x + static_cast<long long>(n) * H * W * C + cv * 8;
+  T* obase = y + static_cast<long long>(n) * HWo * C + cv * 8;
+  load8(base, sft);
+  if (pl < ppi) {
+    for (int p = p0 + pl; p < p1; p += ppi) {
+      const int oh = p / Wo, ow = p - oh * Wo;
+      // ATen upsample_bilinear2d (align_corners): src = dst * (in-1)/(out-1), lambda in fp32
+      const float fh = shh * oh, fw = sww * ow;
+      const int h0 = static_cast<int>(fh), w0 = static_cast<int>(fw);
+      const int h1 = h0 + (h0 < H - 1 ? 1 : 0), w1 = w0 + (w0 < W - 1 ? 1 : 0);
+      const float lh = fh - h0, lw = fw - w0;
+      float a[8], b[8], c[8], d[8], o[8];
+      load8(base + (h0 * W + w0) * C, a);
+      load8(base + (h0 * W + w1) * C, b);
+      load8(base + (h1 * W + w0) * C, c);
+      load8(base + (h1 * W + w1) * C, d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        o[k] = (1.f - lh) * ((1.f - lw) * a[k] + lw * b[k]) + lh * ((1.f - lw) * c[k] + lw * d[k]);
+      store8(obase + static_cast<long long>(p) * C, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float dv = round_as<T>(o[k]) - sft[k];
+        s[k] += dv;
+        q[k] = fmaf(dv, dv, q[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sh[threadIdx.x * 16 + i] = s[i];
+    sh[threadIdx.x * 16 + 8 + i] = q[i];
+  }
+  __syncthreads();
+  float* out = parts + static_cast<long long>(n) * (2 * P + 1) * C;
+  for (int t = threadIdx.x; t < vecs * 16; t += kStatThreads) {
+    const int v = t >> 4, slot = t & 15;
+    float acc = 0.f;
+    for (int l = 0; l < ppi; ++l) acc += sh[(l * vecs + v) * 16 + slot];
+    const int c = v * 8 + (slot & 7);
+    out[(2 * blockIdx.x + (slot >> 3)) * C + c] = acc;
+  }
+  if (blockIdx.x == 0 && pl == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) out[2 * P * C + cv * 8 + i] = sft[i];
   }
 }
 
@@ -662,15 +772,37 @@ const char* nhwc_to_nchw_dst(const S* src, int srcC, int src_c0, void* dst, int 
 const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, int oC, int o_c0,
                               cudaStream_t s) {
   if (C % 8 || oC % 8 || o_c0 % 8) return "upsample2x: channels must be multiples of 8";
-  const long long total = static_cast<long long>(N) * 4 * H * W * (C / 8);
+  if (static_cast<long long>(H) * W * C >= (1LL << 31)) return "upsample2x: image too large";
+  const int row_items = 2 * W * (C / 8);
+  dim3 grid((row_items + 255) / 256, 2 * H, N);
+  if (grid.x > 64) grid.x = 64;
   if (dtype == kF32)
-    upsample2x_kernel<float><<<grid_for(total, 256), 256, 0, s>>>(reinterpret_cast<const float*>(x),
-                                                                  reinterpret_cast<float*>(y), N, H, W, C, oC, o_c0);
+    upsample2x_kernel<float><<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y), N, H,
+                                                  W, C, oC, o_c0);
   else if (dtype == kBF16)
-    upsample2x_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
-        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C, oC, o_c0);
+    upsample2x_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                          reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C, oC, o_c0);
   else
     return "upsample2x: unsupported dtype";
+  return last_err();
+}
+
+const char* upsample2x_stats_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, float* parts,
+                                    cudaStream_t s) {
+  if (C % 8 || C > 8 * kStatThreads) return "upsample2x_stats: C must be a multiple of 8 and <= 2048";
+  if (static_cast<long long>(H) * W * C >= (1LL << 31)) return "upsample2x_stats: image too large";
+  const int HWo = 4 * H * W;
+  const int ppb = stats_pix_per_block(N, HWo, C);
+  dim3 grid((HWo + ppb - 1) / ppb, N);
+  const int smem = kStatThreads * 16 * sizeof(float);
+  if (dtype == kF32)
+    upsample2x_stats_kernel<float><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x),
+                                                                    reinterpret_cast<float*>(y), H, W, C, ppb, parts);
+  else if (dtype == kBF16)
+    upsample2x_stats_kernel<__nv_bfloat16><<<grid, kStatThreads, smem, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), H, W, C, ppb, parts);
+  else
+    return "upsample2x_stats: unsupported dtype";
   return last_err();
 }
 
