@@ -330,11 +330,12 @@ void Net::build_aei(ExecPlan& p) {
       float4* ncpar = p.pool.alloc_n<float4>(static_cast<size_t>(B) * b.cin);
       float* whf = p.pool.alloc_n<float>(static_cast<size_t>(B) * b.cin);
       float* bhf = p.pool.alloc_n<float>(B);
+      float* fsc = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, b.cin));  // zeroed by the pool
       const float* wh = vecs_.at(lname + ".wh");
       const float bh = scalars_.at(lname + ".bh");
       const int cx = b.cin, og = info.off_gamma, ob = info.off_beta;
       add_op(lname + ".fold", [=](cudaStream_t s) {
-        return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, s);
+        return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, fsc, s);
       });
       if (bf) {
         AadArgs args;

@@ -42,6 +42,28 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
   return t;
 }
 
+// Walks the persistent CTA's tile sequence (blockIdx.x, + gridDim.x, ...) without per-tile divisions: the stride is
+// decomposed once into mixed-radix digits and added with carries.
+struct TileWalk {
+  TileCoord t, d;
+  __device__ __forceinline__ void init(const IgemmParams& p, int first, int stride) {
+    t = decode_tile(p, first);
+    d = decode_tile(p, stride);  // d.tn may exceed its radix: it is only ever added
+  }
+  __device__ __forceinline__ void next(const IgemmParams& p) {
+    t.nt += d.nt;
+    int c = t.nt >= p.tiles_n;
+    t.nt -= c ? p.tiles_n : 0;
+    t.tw += d.tw + c;
+    c = t.tw >= p.tiles_w;
+    t.tw -= c ? p.tiles_w : 0;
+    t.th += d.th + c;
+    c = t.th >= p.tiles_h;
+    t.th -= c ? p.tiles_h : 0;
+    t.tn += d.tn + c;
+  }
+};
+
 __device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -221,20 +243,28 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         tma_load_2d(bres + i * b_tile_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * p.kc, 0);
     }
     __syncwarp();
-    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit) {
-      const TileCoord t = decode_tile(p, tile);
+    TileWalk walk;
+    walk.init(p, blockIdx.x, gridDim.x);
+    int hs = 0;
+    uint32_t hphase = 0;
+    const int tap0 = kb0 / p.kc_per_tap, kci0 = kb0 - tap0 * p.kc_per_tap;
+    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit, walk.next(p)) {
+      const TileCoord t = walk.t;
       const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
       if (p.mode == kModeAAD) {
-        const int hs = hit % p.h_bufs;
-        if (!__all_sync(0xffffffffu, mbar_wait(&hempty_bar[hs], ((hit / p.h_bufs) & 1) ^ 1u, &abort_flag))) break;
+        if (!__all_sync(0xffffffffu, mbar_wait(&hempty_bar[hs], hphase ^ 1u, &abort_flag))) break;
         if (elect_one()) {
           mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
           for (int b = 0; b < hbox; ++b)
             tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
         }
         __syncwarp();
+        if (++hs == p.h_bufs) {
+          hs = 0;
+          hphase ^= 1u;
+        }
       }
-      int tap = kb0 / p.kc_per_tap, kci = kb0 - tap * p.kc_per_tap;
+      int tap = tap0, kci = kci0;
       const int rg = p.dual ? (hit & 1) : 0;
       int stage_r = st[rg];
       uint32_t phase = ph[rg];
@@ -355,8 +385,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     const int rh = (r / p.bw) % p.bh;
     const int rw = r % p.bw;
     int it = 0;
-    for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it) {
-      const TileCoord t = decode_tile(p, tile);
+    TileWalk walk;
+    walk.init(p, blockIdx.x, gridDim.x);
+    int hs = 0, ob = 0;
+    uint32_t hphase = 0;
+    for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it, walk.next(p)) {
+      const TileCoord t = walk.t;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
@@ -381,13 +415,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
         // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels), the blended tile is staged in
         // shared memory and leaves by TMA store: no row-by-row global access.
-        const int hs = it % p.h_bufs;
-        const int ob = it % p.o_bufs;
         const int c_base = t.nt * cn;
         const int nc = min(n, p.Nimg - 1);  // rows outside the tensor still index valid parameters
         const uint8_t* hrow = hbuf + hs * htile_bytes + r * 128;
         const int sw = r & 7;
-        if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], (it / p.h_bufs) & 1, &abort_flag))) break;
+        if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], hphase, &abort_flag))) break;
         float m = 0.f;
         if (p.mask) {
           if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
@@ -466,6 +498,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           bulk_commit();
         }
         if (lane == 0) mbar_arrive(&hempty_bar[hs]);
+        if (++hs == p.h_bufs) {
+          hs = 0;
+          hphase ^= 1u;
+        }
+        if (++ob == p.o_bufs) ob = 0;
       }
       // hand the accumulator stage back to the MMA warp
       tc_fence_before();

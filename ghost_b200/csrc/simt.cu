@@ -362,62 +362,73 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
   }
 }
 
-__global__ void aad_fold_kernel(const float* __restrict__ parts, int P, int HW, int C, const float* __restrict__ zfc,
-                                int ldz, int off_gamma, int off_beta, const float* __restrict__ w_h, float b_h,
-                                float4* __restrict__ ncpar, float* __restrict__ wh_fold, float* __restrict__ bh_fold) {
-  __shared__ float red[32];
+// grid (N, C/64): block (n, by) folds 64 channels with 4 part-lanes each.  Every lane adds its parts in a fixed
+// order and lane 0 adds the lanes in a fixed order, so the statistics stay deterministic however many parts the
+// producers wrote.  The conv_h bias needs a sum over all channels: each block leaves its partial in
+// scratch[n][by], the last block of image n to finish (self-resetting counter) adds them in index order.
+__global__ void __launch_bounds__(256) aad_fold_kernel(const float* __restrict__ parts, int P, int HW, int C,
+                                                        const float* __restrict__ zfc, int ldz, int off_gamma,
+                                                        int off_beta, const float* __restrict__ w_h, float b_h,
+                                                        float4* __restrict__ ncpar, float* __restrict__ wh_fold,
+                                                        float* __restrict__ bh_fold, float* scratch) {
   __shared__ double shs[256], shq[256];
-  const int n = blockIdx.x;
+  __shared__ float red[2];
+  __shared__ int is_last;
+  const int n = blockIdx.x, by = blockIdx.y, gy = gridDim.y;
   const double inv = 1.0 / static_cast<double>(HW);
   const float* pn = parts + static_cast<long long>(n) * (2 * P + 1) * C;
-  float part = 0.f;
-  // 256 threads = CW channels x L part-lanes; every lane adds its parts in a fixed order, lane 0 adds the lanes in
-  // a fixed order: the statistics stay deterministic however many parts the producers wrote
-  const int CW = C < 256 ? C : 256;
-  const int L = 256 / CW;
-  const int cl = threadIdx.x % CW, lane = threadIdx.x / CW;
-  for (int c0 = 0; c0 < C; c0 += CW) {
-    const int c = c0 + cl;
-    double su0 = 0.0, su1 = 0.0, sq0 = 0.0, sq1 = 0.0;
-    if (lane < L && c < C) {
-      for (int p = lane; p < P; p += 2 * L) {
-        su0 += static_cast<double>(pn[(2 * p) * C + c]);
-        sq0 += static_cast<double>(pn[(2 * p + 1) * C + c]);
-        if (p + L < P) {
-          su1 += static_cast<double>(pn[(2 * (p + L)) * C + c]);
-          sq1 += static_cast<double>(pn[(2 * (p + L) + 1) * C + c]);
-        }
+  const int cl = threadIdx.x & 63, lane = threadIdx.x >> 6;
+  const int c = by * 64 + cl;
+  double su0 = 0.0, su1 = 0.0, sq0 = 0.0, sq1 = 0.0;
+  if (c < C) {
+    for (int p = lane; p < P; p += 8) {
+      su0 += static_cast<double>(pn[(2 * p) * C + c]);
+      sq0 += static_cast<double>(pn[(2 * p + 1) * C + c]);
+      if (p + 4 < P) {
+        su1 += static_cast<double>(pn[(2 * (p + 4)) * C + c]);
+        sq1 += static_cast<double>(pn[(2 * (p + 4) + 1) * C + c]);
       }
     }
-    shs[threadIdx.x] = su0 + su1;
-    shq[threadIdx.x] = sq0 + sq1;
-    __syncthreads();
-    if (lane == 0 && c < C) {
-      double su = 0.0, sq = 0.0;
-      for (int l = 0; l < L; ++l) {
-        su += shs[l * CW + cl];
-        sq += shq[l * CW + cl];
-      }
-      const double d = su * inv;
-      const float mu = static_cast<float>(static_cast<double>(pn[2 * P * C + c]) + d);
-      const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));  // biased variance (InstanceNorm2d)
-      const float rstd = 1.0f / sqrtf(var + 1e-5f);
-      const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
-      const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
-      ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
-      const float w = w_h[c] * rstd;
-      wh_fold[static_cast<long long>(n) * C + c] = w;
-      part += w * mu;
-    }
-    __syncthreads();
   }
-  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  shs[threadIdx.x] = su0 + su1;
+  shq[threadIdx.x] = sq0 + sq1;
   __syncthreads();
-  if (threadIdx.x < 32) {
-    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (threadIdx.x == 0) bh_fold[n] = b_h - v;
+  float part = 0.f;
+  if (lane == 0 && c < C) {
+    double su = 0.0, sq = 0.0;
+    for (int l = 0; l < 4; ++l) {
+      su += shs[l * 64 + cl];
+      sq += shq[l * 64 + cl];
+    }
+    const double d = su * inv;
+    const float mu = static_cast<float>(static_cast<double>(pn[2 * P * C + c]) + d);
+    const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));  // biased variance (InstanceNorm2d)
+    const float rstd = 1.0f / sqrtf(var + 1e-5f);
+    const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
+    const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
+    ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
+    const float w = w_h[c] * rstd;
+    wh_fold[static_cast<long long>(n) * C + c] = w;
+    part = w * mu;
+  }
+  if (threadIdx.x < 64) {  // warps 0 and 1 hold the 64 channel terms
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  }
+  __syncthreads();
+  float* sc = scratch + static_cast<long long>(n) * (gy + 1);
+  if (threadIdx.x == 0) {
+    sc[1 + by] = red[0] + red[1];
+    __threadfence();
+    const unsigned done = atomicAdd(reinterpret_cast<unsigned*>(sc), 1u);
+    is_last = done == static_cast<unsigned>(gy - 1);
+    if (is_last) {
+      __threadfence();
+      float v = 0.f;
+      for (int i = 0; i < gy; ++i) v += *reinterpret_cast<volatile float*>(sc + 1 + i);
+      bh_fold[n] = b_h - v;
+      *reinterpret_cast<unsigned*>(sc) = 0u;  // ready for the next launch (graph replays included)
+    }
   }
 }
 
@@ -521,10 +532,14 @@ const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, floa
   return last_err();
 }
 
+size_t aad_fold_scratch_floats(int N, int C) { return static_cast<size_t>(N) * ((C + 63) / 64 + 1); }
+
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
-                            cudaStream_t s) {
-  aad_fold_kernel<<<N, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold, bh_fold);
+                            float* scratch, cudaStream_t s) {
+  dim3 grid(N, (C + 63) / 64);
+  aad_fold_kernel<<<grid, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold,
+                                       bh_fold, scratch);
   return last_err();
 }
 

@@ -41,9 +41,11 @@ const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, floa
 
 // Per-AAD-layer fold of the statistics (fixed-order sum of the P parts, in double) with the identity FCs and conv_h.
 //   ncpar[n][c] = {rstd, -mu*rstd, gamma_id, beta_id}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
+// scratch: aad_fold_scratch_floats(N, C) floats, zero before the first launch (the kernel leaves it zeroed)
+size_t aad_fold_scratch_floats(int N, int C);
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
-                            cudaStream_t s);
+                            float* scratch, cudaStream_t s);
 
 // bf16 mode, c_x > 128: the per-pixel sigmoid mask of an AADLayer, mask[N*HW] fp32.
 const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,

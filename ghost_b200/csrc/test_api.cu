@@ -135,7 +135,8 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
     float* bhf = pool.alloc_n<float>(N);
     float* d_wh = pool.upload(std::vector<float>(convh_w, convh_w + c_x));
     check_msg(in_stats_launch(h, dt, N, HW, c_x, sums, s), "stats");
-    check_msg(aad_fold_launch(sums, parts, N, HW, c_x, d_zfc, 2 * c_x, 0, c_x, d_wh, convh_b, ncpar, whf, bhf, s), "fold");
+    float* fsc = pool.alloc_n<float>(aad_fold_scratch_floats(N, c_x));
+    check_msg(aad_fold_launch(sums, parts, N, HW, c_x, d_zfc, 2 * c_x, 0, c_x, d_wh, convh_b, ncpar, whf, bhf, fsc, s), "fold");
     const int cn = bf ? (c_x < 128 ? c_x : 128) : c_x;
     std::vector<float> rows(static_cast<size_t>(2) * c_x * c_attr), bias(2 * c_x);
     for (int c = 0; c < c_x; ++c) {
