@@ -246,22 +246,40 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     resident_bytes = p.b_res ? slab : 0;
     if ((221 * 1024 - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
   }
-  // AAD mode keeps h tiles in flight deep enough to cover the HBM latency (the epilogue, not the MMA, paces it)
-  p.h_bufs = aad ? ((p.BN >> 1) == 64 ? 4 : 3) : 0;
-  p.o_bufs = aad ? ((p.BN >> 1) == 64 ? 2 : 1) : 0;
-  int aad_bytes = (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384;
-  int stages = (221 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
-  if (aad && stages < 2 && p.h_bufs > 2) {  // wide gamma/beta tiles: trade one h tile for a second operand slot
-    p.h_bufs = 2;
-    stages = (221 * 1024 - (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384) / stage_bytes;
+  p.sets = 2;
+  int aad_bytes = 0;
+  if (aad) {
+    // 128-column tiles (c_x = 64): four accumulator stages / warp groups; 256-column tiles: two
+    const int hbox = (p.BN >> 1) >> 6;
+    p.sets = 4 / hbox;
+    // one N tile and 64-channel K chunks: the gamma/beta weights stay resident, only z_attr streams
+    const int slab = p.kc_per_tap * p.BN * p.kc * 2;
+    p.b_res = p.tiles_n == 1 && p.kc == 64 && slab <= 64 * 1024;
+    if (p.b_res) {
+      stage_bytes = 128 * p.kc * 2;
+      resident_bytes = slab;
+    }
+    // two h slots per warp group when they still leave three operand slots
+    p.h_bufs = 2 * p.sets;
+    aad_bytes = p.h_bufs * hbox * 16384;
+    if ((221 * 1024 - aad_bytes - resident_bytes) / stage_bytes < 3) {
+      p.h_bufs = p.sets;
+      aad_bytes = p.h_bufs * hbox * 16384;
+    }
   }
+  int stages = (221 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) stages = 2;
   p.stages = stages;
-  // narrow / short tiles are bound by how fast one warp can issue tcgen05.mma: split the tiles over two issuers
-  // when the ring is deep enough to give each of them three or more slots
-  p.dual = stages >= 6;
-  p.tmem_cols = pow2_at_least(2 * p.BN);
+  // Short tiles are bound by how fast one warp can issue tcgen05.mma and hand tiles over: split the tiles over
+  // two issuers, each with half of the ring - but only when a whole tile fits in its half.  The producer fills
+  // the ring in tile order, so a long tile would see just half of the prefetch depth (the fill is latency
+  // bound: bytes in flight / ~1.8 us).
+  {
+    const int nkb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
+    p.dual = !aad && stages >= 4 && 2 * nkb <= stages;
+  }
+  p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
 
   // ---- epilogue
   p.out = out.p;
@@ -290,7 +308,25 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       const uint64_t str[3] = {cx * eb, static_cast<uint64_t>(Wo) * cx * eb, static_cast<uint64_t>(Ho) * Wo * cx * eb};
       const uint32_t box[4] = {64u, static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
       if (const char* e = encode_tmap(&p.tmH, aad->h, 4, dims, str, box, 128)) return e;
-      if (const char* e = encode_tmap(&p.tmO, out.p, 4, dims, str, box, 128)) return e;
+      // store box = the 32 consecutive tile rows (order n, h, w) one epilogue warp owns
+      uint32_t ob[4] = {64u, 0, 1, 1};
+      const int bw = p.bw, bh = p.bh, bn = p.bn;
+      if (bw >= 32) {
+        if (bw % 32) return "lower_conv: AAD tiles need a row length that is a multiple of 32 (or a divisor of it)";
+        ob[1] = 32;
+      } else if (bw * bh >= 32) {
+        if (32 % bw || bh % (32 / bw)) return "lower_conv: AAD tile rows do not split into 32-row boxes";
+        ob[1] = bw;
+        ob[2] = 32 / bw;
+      } else {
+        if (32 % (bw * bh)) return "lower_conv: AAD tile images do not split into 32-row boxes";
+        ob[1] = bw;
+        ob[2] = bh;
+        ob[3] = 32 / (bw * bh);
+        if (static_cast<int>(ob[3]) > bn && bn * bw * bh < 32) ob[3] = bn;  // fewer than 32 rows in the whole tile
+      }
+      if (const char* e = encode_tmap(&p.tmO, out.p, 4, dims, str, ob, 128)) return e;
+
     }
   } else {
     p.mode = kModeLinear;

@@ -70,6 +70,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&t);
 }
+// max(., 0) and the bf16x2 pack in one instruction (lo -> bits [0,16), hi -> bits [16,32))
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 
 
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
@@ -156,12 +162,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
   __shared__ uint64_t empty_bar[8];
-  __shared__ uint64_t tfull_bar[2];
-  __shared__ uint64_t tempty_bar[2];
-  __shared__ uint64_t hfull_bar[4];   // AAD mode: h tile landed in shared memory
-  __shared__ uint64_t hempty_bar[4];  // AAD mode: epilogue done with the h tile
+  __shared__ uint64_t tfull_bar[4];
+  __shared__ uint64_t tempty_bar[4];
+  __shared__ uint64_t hfull_bar[8];   // AAD mode: h tile landed in shared memory
+  __shared__ uint64_t hempty_bar[8];  // AAD mode: blended tile stored, h slot free again
   __shared__ uint64_t bfull_bar;      // resident-weights mode: the packed weight slab landed
-  __shared__ float mpart[4][128];     // AAD mode: per-quarter partial sums of the mask logit
+  __shared__ float mexch[2][4][128];  // AAD mode, 128-channel tiles: mask-logit halves of the two warps sharing a row
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
@@ -176,7 +182,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int b_tile_bytes = p.BN * row_bytes;
   // row-window mode: the A slot holds bw+2 (<= 130) pixel rows of 128 B, the B slot the three taps of one kernel row
   const int a_stage_bytes = win ? 17 * 1024 : 128 * row_bytes;
-  const int b_stage_bytes = win ? (p.b_res ? 0 : 3 * b_tile_bytes) : b_tile_bytes;
+  const int b_stage_bytes = p.b_res ? 0 : (win ? 3 * b_tile_bytes : b_tile_bytes);
   const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
   const int rows_used = p.bw * p.bh * p.bn;
   const uint32_t tx_bytes = (win ? (p.bw + 2) * 128 : rows_used * row_bytes) + b_stage_bytes;
@@ -184,12 +190,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   uint8_t* bres = smem;                                 // resident weight tiles [tap][chunk][BN rows][128 B]
   uint8_t* ring = smem + bres_tiles * b_tile_bytes;     // operand ring
 
-  // AAD mode: two h tiles and one output tile behind the operand ring, each cn/64 boxes of [128 rows][128 B]
+  // AAD mode: h tiles behind the operand ring, each cn/64 boxes of [128 rows][128 B]
   const int cn = p.BN >> 1;
   const int hbox = cn >> 6;
   const int htile_bytes = hbox * 16384;
   uint8_t* hbuf = ring + p.stages * stage_bytes;
-  uint8_t* obuf = hbuf + p.h_bufs * htile_bytes;  // p.o_bufs staging tiles
 
   // K blocks handled by this CTA (row-window mode: one block = one kernel row x one 64-channel chunk = 3 taps)
   const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap / p.splits;
@@ -202,14 +207,16 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    // linear mode: all 16 epilogue warps share every tile; AAD mode: 4 warps per 64-channel box of a tile
+    const int epi_arrivals = p.mode == kModeAAD ? 4 * hbox : kIgemmEpiWarps;
+    for (int i = 0; i < 4; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], kIgemmEpiWarps);
+      mbar_init(&tempty_bar[i], epi_arrivals);
     }
     mbar_init(&bfull_bar, 1);
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
       mbar_init(&hfull_bar[i], 1);
-      mbar_init(&hempty_bar[i], kIgemmEpiWarps);
+      mbar_init(&hempty_bar[i], epi_arrivals);
     }
     fence_mbar_init();
   }
@@ -226,7 +233,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
-  const int acc_stride = p.tmem_cols >> 1;  // columns per accumulator stage
+  const int acc_stride = p.tmem_cols / p.sets;  // columns per accumulator stage
 
   if (warp == 0) {
     // ============================== TMA producer ==============================
@@ -291,7 +298,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
               tma_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
             else
               tma_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
-            tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
+            if (!p.b_res) tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
           }
         }
         __syncwarp();
@@ -327,11 +334,15 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     bool ok = p.dual || par == 0;  // single-issuer mode: warp 2 idles
     int it = 0;
     if (ok && p.b_res && !__all_sync(0xffffffffu, mbar_wait(&bfull_bar, 0, &abort_flag))) ok = false;
+    int as = 0;           // accumulator stage of tile `it` = it % sets
+    uint32_t aphase = 0;  // (it / sets) & 1
     for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
-      const int as = it & 1;
-      if (p.dual && as != par) continue;  // the other issuer's tile
+      if (it != 0 && ++as == p.sets) {
+        as = 0;
+        aphase ^= 1u;
+      }
+      if (p.dual && (it & 1) != par) continue;  // the other issuer's tile (two accumulator stages in this mode)
       const uint32_t d_tmem = tmem_base_u + as * acc_stride;
-      const uint32_t aphase = (it >> 1) & 1;
       if (!__all_sync(0xffffffffu, mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag))) break;
       tc_fence_after();
       uint32_t bq = bres_lo;  // resident weights: descriptor of tap (row, 0), chunk kci
@@ -364,7 +375,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             umma_bf16_batch<4>(d_tmem, a_lo + 16, b_lo + 2 * bt16, dhi, idesc, 1);
           }
         } else if (p.kc == 64) {
-          umma_bf16_batch<4>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
+          const uint32_t b_lo = p.b_res ? bres_lo + kb * bt16 : smem_desc_lo(sa + a_stage_bytes);
+          umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
         } else {
           umma_bf16_batch<2>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
         }
@@ -378,31 +390,29 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     }
   } else {
     // ============================== epilogue ==================================
-    const int lg = warp & 3;            // TMEM lane group this warp may read
-    const int quarter = (warp - kIgemmEpiWarp0) >> 2;  // which quarter of the tile's columns this warp handles
-    const int r = lg * 32 + lane;       // GEMM row inside the tile
+    const int lg = warp & 3;                       // TMEM lane group this warp may read
+    const int ew = (warp - kIgemmEpiWarp0) >> 2;   // 0..3: which of the four warps of that lane group
+    const int r = lg * 32 + lane;                  // GEMM row inside the tile
     const int rn = r / (p.bh * p.bw);
     const int rh = (r / p.bw) % p.bh;
     const int rw = r % p.bw;
-    int it = 0;
-    TileWalk walk;
-    walk.init(p, blockIdx.x, gridDim.x);
-    int hs = 0, ob = 0;
-    uint32_t hphase = 0;
-    for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it, walk.next(p)) {
-      const TileCoord t = walk.t;
-      const int as = it & 1;
-      const uint32_t aphase = (it >> 1) & 1;
-      const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
-      const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
-      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * acc_stride;
-
-      if (p.mode == kModeLinear) {
+    if (p.mode == kModeLinear) {
+      // all 16 warps share every tile: warp ew takes a quarter of its columns
+      int it = 0;
+      TileWalk walk;
+      walk.init(p, blockIdx.x, gridDim.x);
+      for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it, walk.next(p)) {
+        const TileCoord t = walk.t;
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
+        const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * acc_stride;
         if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
         tc_fence_after();
         const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
-        const int nch = p.BN >> 4, ch0 = (nch * quarter) >> 2, ch1 = (nch * (quarter + 1)) >> 2;
+        const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
         for (int j = ch0 * 16; j < ch1 * 16; j += 16) {
           uint32_t v[16];
           __syncwarp();
@@ -411,108 +421,122 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           const int col0 = t.nt * p.BN + j;
           if (valid && col0 < p.n_valid) linear_epilogue_16(p, v, col0, o_pix, r_pix);
         }
-      } else {
-        // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
-        // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels), the blended tile is staged in
-        // shared memory and leaves by TMA store: no row-by-row global access.
-        const int c_base = t.nt * cn;
+        // hand the accumulator stage back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      }
+    } else {
+      // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
+      // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels); each warp blends its own 32 rows x
+      // 64 channels in place and sends them out with its own TMA store, so no warp ever waits for another one
+      // (except the pair sharing a row of a 128-channel tile, for the mask logit).  The 16 warps form `sets`
+      // groups; group s serves the tiles with it % sets == s, i.e. always accumulator stage s.
+      const int set = hbox == 1 ? ew : ew >> 1;
+      const int box = hbox == 1 ? 0 : ew & 1;
+      const int sets = p.sets;
+      const bool h2 = p.h_bufs == 2 * sets;  // two h slots per group
+      const int sw = r & 7;
+      const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + set * acc_stride + box * 64;
+      TileWalk walk;
+      walk.init(p, blockIdx.x + set * gridDim.x, gridDim.x * sets);
+      int k = 0;  // tiles this group has served
+      for (int tile = blockIdx.x + set * gridDim.x; tile < tiles_total; tile += gridDim.x * sets, ++k, walk.next(p)) {
+        const TileCoord t = walk.t;
+        const int hs = h2 ? set + (k & 1) * sets : set;
+        const uint32_t hphase = h2 ? (k >> 1) & 1 : k & 1;
+        const uint32_t aphase = k & 1;
+        const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
+        const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
+        const int c_base = t.nt * cn + box * 64;
         const int nc = min(n, p.Nimg - 1);  // rows outside the tensor still index valid parameters
-        const uint8_t* hrow = hbuf + hs * htile_bytes + r * 128;
-        const int sw = r & 7;
+        uint8_t* hrow = hbuf + hs * htile_bytes + box * 16384 + r * 128;
         if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], hphase, &abort_flag))) break;
         float m = 0.f;
         if (p.mask) {
           if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
         } else {
           // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh (single N tile: cn == c_x).
-          // Each of the four warps sharing this row sums a quarter of the channels; the partials meet in shared
-          // memory at the barrier below.  Runs while the tensor core is still producing this tile's gamma/beta.
-          const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x;
-          float acc = 0.f;
-          const int nq = hbox * 2;  // 16-byte chunks (8 channels) per quarter
-          for (int qq = quarter * nq; qq < (quarter + 1) * nq; ++qq) {
-            const int bx = qq >> 3, q = qq & 7;
-            const uint4 v = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q ^ sw) << 4));
-            const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + qq * 8));
-            const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + qq * 8) + 1);
-            acc += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
-            acc += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
+          // Runs while the tensor core is still producing this tile's gamma/beta.
+          const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x + box * 64;
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const uint4 v = *reinterpret_cast<const uint4*>(hrow + ((q ^ sw) << 4));
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + q * 8));
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + q * 8) + 1);
+            acc0 += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
+            acc1 += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
           }
-          mpart[quarter][r] = acc;
+          float acc = acc0 + acc1;
+          if (hbox == 2) {
+            // the other 64 channels of this row belong to the partner warp: swap halves, add in box order
+            float(*ex)[128] = mexch[k & 1];
+            ex[set * 2 + box][r] = acc;
+            named_bar_sync(1 + set * 4 + lg, 64);
+            const float other = ex[set * 2 + (box ^ 1)][r];
+            acc = box == 0 ? acc + other : other + acc;
+          }
+          m = 1.f / (1.f + __expf(-(acc + __ldg(p.bh_fold + nc))));
         }
-        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
+        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[set], aphase, &abort_flag))) break;
         tc_fence_after();
-        // the previous tile's TMA store must have finished reading the staging tile before it is overwritten
-        if (threadIdx.x == 32 * kIgemmEpiWarp0) {
-          if (p.o_bufs == 2) bulk_wait_read<1>(); else bulk_wait_read<0>();
-        }
-        named_bar_sync(1, 32 * kIgemmEpiWarps);
-        if (!p.mask) {
-          const float acc = ((mpart[0][r] + mpart[1][r]) + (mpart[2][r] + mpart[3][r])) + __ldg(p.bh_fold + nc);
-          m = 1.f / (1.f + __expf(-acc));
-        }
         const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
-        const float* bg = p.bias + t.nt * p.BN;
+        const float* bg = p.bias + t.nt * p.BN + box * 64;
         const float* bb = bg + cn;
-        uint8_t* orow = obuf + ob * htile_bytes + r * 128;
-        const int cq = cn >> 2;  // columns per warp
-        for (int j = quarter * cq; j < (quarter + 1) * cq; j += 8) {
+        const float2 mm = make_float2(m, m);
+#pragma unroll 2
+        for (int j = 0; j < 64; j += 8) {
           uint32_t g[8], b[8];
           __syncwarp();
           tmem_ld8(t_addr + j, g);
           tmem_ld8(t_addr + cn + j, b);
-          const int bx = j >> 6, q0 = (j & 63) >> 3;
-          const uint4 h0 = *reinterpret_cast<const uint4*>(hrow + bx * 16384 + ((q0 ^ sw) << 4));
+          uint4* hp = reinterpret_cast<uint4*>(hrow + (((j >> 3) ^ sw) << 4));
+          const uint4 h0 = *hp;
           const float4 u0 = __ldg(reinterpret_cast<const float4*>(bg + j));
           const float4 u1 = __ldg(reinterpret_cast<const float4*>(bg + j) + 1);
           const float4 v0 = __ldg(reinterpret_cast<const float4*>(bb + j));
           const float4 v1 = __ldg(reinterpret_cast<const float4*>(bb + j) + 1);
           tmem_ld_wait();
           const uint32_t qq[4] = {h0.x, h0.y, h0.z, h0.w};
-          const float bgv[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
-          const float bbv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-          float o[8];
+          const float2 bgv[4] = {{u0.x, u0.y}, {u0.z, u0.w}, {u1.x, u1.y}, {u1.z, u1.w}};
+          const float2 bbv[4] = {{v0.x, v0.y}, {v0.z, v0.w}, {v1.x, v1.y}, {v1.z, v1.w}};
+          uint32_t o[4];
           const float4* parj = par + j;
+          // two adjacent channels per packed fp32 instruction; the parameter table is laid out per channel pair
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float x = (i & 1) ? bf16hi(qq[i >> 1]) : bf16lo(qq[i >> 1]);
-            const float4 pr = __ldg(parj + i);
-            const float hn = fmaf(x, pr.x, pr.y);
-            const float A = fmaf(__uint_as_float(g[i]) + bgv[i], hn, __uint_as_float(b[i]) + bbv[i]);
-            const float I = fmaf(pr.z, hn, pr.w);
-            o[i] = fmaxf(fmaf(m, I - A, A), 0.f);
+          for (int i = 0; i < 4; ++i) {
+            const float2 x = make_float2(bf16lo(qq[i]), bf16hi(qq[i]));
+            const float4 p0 = __ldg(parj + 2 * i);      // {rstd0, rstd1, shift0, shift1}
+            const float4 p1 = __ldg(parj + 2 * i + 1);  // {gamma_id0, gamma_id1, beta_id0, beta_id1}
+            const float2 hn = fma2(x, make_float2(p0.x, p0.y), make_float2(p0.z, p0.w));
+            const float2 ga = add2(make_float2(__uint_as_float(g[2 * i]), __uint_as_float(g[2 * i + 1])), bgv[i]);
+            const float2 be = add2(make_float2(__uint_as_float(b[2 * i]), __uint_as_float(b[2 * i + 1])), bbv[i]);
+            const float2 A = fma2(ga, hn, be);
+            const float2 I = fma2(make_float2(p1.x, p1.y), hn, make_float2(p1.z, p1.w));
+            const float2 r2 = fma2(mm, sub2(I, A), A);
+            o[i] = pack_bf16_relu(r2.x, r2.y);  // the ReLU that always follows the layer (AADLayer.py:62,70)
           }
-          uint4 s0;
-          s0.x = pack_bf16(o[0], o[1]);
-          s0.y = pack_bf16(o[2], o[3]);
-          s0.z = pack_bf16(o[4], o[5]);
-          s0.w = pack_bf16(o[6], o[7]);
-          *reinterpret_cast<uint4*>(orow + bx * 16384 + ((q0 ^ sw) << 4)) = s0;
+          *hp = make_uint4(o[0], o[1], o[2], o[3]);  // in place: this thread alone reads and writes this chunk
         }
-        fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to the TMA (async proxy)
+        fence_proxy_async();  // generic-proxy writes of the blended rows -> visible to the TMA (async proxy)
         tc_fence_before();
-        named_bar_sync(1, 32 * kIgemmEpiWarps);
-        if (threadIdx.x == 32 * kIgemmEpiWarp0) {
-          for (int bx = 0; bx < hbox; ++bx)
-            tma_store_4d(&p.tmO, obuf + ob * htile_bytes + bx * 16384, c_base + bx * 64, t.tw * p.bw, t.th * p.bh, t.tn * p.bn);
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&tempty_bar[set]);  // accumulator stage back to the MMA warp
+          // lane 0 holds the first of this warp's 32 rows: its pixel is the origin of the store box
+          if (r < rows_used) tma_store_4d(&p.tmO, hrow, c_base, ow, oh, n);
           bulk_commit();
+          bulk_wait_read<0>();            // the store has read the rows: the h slot may be refilled
+          mbar_arrive(&hempty_bar[hs]);
         }
-        if (lane == 0) mbar_arrive(&hempty_bar[hs]);
-        if (++hs == p.h_bufs) {
-          hs = 0;
-          hphase ^= 1u;
-        }
-        if (++ob == p.o_bufs) ob = 0;
+        __syncwarp();
       }
-      // hand the accumulator stage back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[as]);
+      if (lane == 0) bulk_wait<0>();  // outstanding TMA stores
     }
   }
 
   // ------------------------------ teardown ------------------------------------
-  if (threadIdx.x == 32 * kIgemmEpiWarp0) bulk_wait<0>();  // outstanding TMA stores of the AAD epilogue
   tc_fence_before();
   __syncthreads();
   if (abort_flag && threadIdx.x == 0 && p.err) {
@@ -527,13 +551,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 
 int igemm_smem_bytes(const IgemmParams& p) {
   const int row_bytes = p.kc * 2;
-  const int aad = p.mode == kModeAAD ? (p.h_bufs + p.o_bufs) * ((p.BN >> 1) >> 6) * 16384 : 0;
+  const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
   const int b_tile = p.BN * row_bytes;
-  if (p.a_win) {
-    const int stage = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
-    return p.stages * stage + (p.b_res ? p.ntaps * p.kc_per_tap * b_tile : 0) + aad + 1024;
-  }
-  return p.stages * (128 * row_bytes + b_tile) + aad + 1024;
+  const int resident = p.b_res ? p.ntaps * p.kc_per_tap * b_tile : 0;
+  const int stage = p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_tile) : 128 * row_bytes + (p.b_res ? 0 : b_tile);
+  return p.stages * stage + resident + aad + 1024;
 }
 
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
@@ -556,14 +578,18 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm: M box must hold 1..128 rows";
   if (p.stages < 2 || p.stages > 8) return "igemm: stages must be in [2,8]";
   if (p.dual && p.stages < 4) return "igemm: two issuers need at least four ring slots";
-  if (p.mode == kModeAAD && (p.h_bufs < 2 || p.h_bufs > 4 || p.o_bufs < 1 || p.o_bufs > 2)) return "igemm: bad AAD buffering";
-  if (p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
+  if (p.sets != 2 && p.sets != 4) return "igemm: 2 or 4 accumulator stages";
+  if (p.mode == kModeLinear && p.sets != 2) return "igemm: the linear epilogue works on two accumulator stages";
+  if (p.mode == kModeAAD &&
+      (p.sets * (p.BN >> 7) != 4 || (p.h_bufs != p.sets && p.h_bufs != 2 * p.sets) || p.dual || p.BN % 128))
+    return "igemm: bad AAD staging";
+  if (p.tmem_cols < p.sets * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm: bad tmem_cols";
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
   if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
-  if (p.b_res && (!p.a_win || p.tiles_n != 1)) return "igemm: resident weights need row-window mode and one N tile";
+  if (p.b_res && (p.tiles_n != 1 || p.kc != 64 || p.splits != 1)) return "igemm: resident weights need one N tile";
   const int smem = igemm_smem_bytes(p);
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;

@@ -21,7 +21,7 @@ struct alignas(64) IgemmParams {
   CUtensorMap tmA;  // activations, NHWC (4-D) or parity-split NHWC (5-D, stride-2 convs)
   CUtensorMap tmB;  // packed weights [Cout_pad][taps*Cin], K-major
   CUtensorMap tmH;  // AAD mode: block input h, NHWC, boxes of 64 channels x (bw, bh, bn), SWIZZLE_128B
-  CUtensorMap tmO;  // AAD mode: output tensor, same boxes (TMA store)
+  CUtensorMap tmO;  // AAD mode: output tensor, boxes of 64 channels x the 32 tile rows one epilogue warp owns (TMA store)
 
   // ---- M tiling: one tile = bn images x bh rows x bw cols (<= 128 GEMM rows)
   int a_rank;  // 4 or 5
@@ -41,7 +41,8 @@ struct alignas(64) IgemmParams {
   short tap_p[kIgemmMaxTaps];     // h-parity coordinate (5-D maps only)
   short tap_h[kIgemmMaxTaps];     // added to the h coordinate
   int stages, tmem_cols;
-  int h_bufs, o_bufs;  // AAD mode: shared-memory h tiles in flight (2..4) and output staging tiles (1..2)
+  int sets;    // TMEM accumulator stages (tmem_cols / sets columns each): 2, or 4 for AAD tiles of 128 columns
+  int h_bufs;  // AAD mode: shared-memory h tiles (sets or 2*sets); the blended tile overwrites its h tile in place
   // Row-window mode (3x3 stride-1 convs on wide images, bh == bn == 1, kc == 64): one TMA box of bw+2 pixels per
   // (kernel row, 64-channel chunk) serves the three horizontal taps as row-shifted UMMA views, so the A operand
   // crosses L2->shared 3x instead of 9x.  b_res: the whole packed weight slab stays resident in shared memory.
@@ -63,11 +64,13 @@ struct alignas(64) IgemmParams {
   int act2;
 
   // ---- epilogue (AAD blend): columns [0,cn) = gamma_attr, [cn,2cn) = beta_attr, cn = BN/2
-  // The h tile is TMA-loaded into shared memory, blended there and TMA-stored (nothing is read row by row
-  // from global memory); when c_x > 128 (several N tiles per pixel) the sigmoid mask comes precomputed in `mask`.
+  // The h tile is TMA-loaded into shared memory, blended there in place and TMA-stored (nothing is read row by
+  // row from global memory).  Every epilogue warp owns a 32-row x 64-channel piece of a tile and never syncs with
+  // the others; the 16 warps form `sets` groups that work on different tiles at the same time.  When c_x > 128
+  // (several N tiles per pixel) the sigmoid mask comes precomputed in `mask`.
   const __nv_bfloat16* h;  // raw block input, NHWC, pixel stride c_x (kept for reference / debugging)
   int c_x;
-  const float4* ncpar;  // [Nimg][c_x] {rstd, -mu*rstd, gamma_id, beta_id}
+  const float4* ncpar;  // [Nimg][c_x] per channel pair: {rstd0, rstd1, -mu0*rstd0, -mu1*rstd1}, {gamma_id0, gamma_id1, beta_id0, beta_id1}
   const float* wh_fold;     // [Nimg][c_x] conv_h weight * rstd
   const float* bh_fold;     // [Nimg]      conv_h bias - sum(w*mu*rstd)
   const float* mask;    // optional precomputed sigmoid mask per pixel (else computed in-kernel)

@@ -406,7 +406,13 @@ __global__ void __launch_bounds__(256) aad_fold_kernel(const float* __restrict__
     const float rstd = 1.0f / sqrtf(var + 1e-5f);
     const float g = zfc[static_cast<long long>(n) * ldz + off_gamma + c];
     const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
-    ncpar[static_cast<long long>(n) * C + c] = make_float4(rstd, -mu * rstd, g, b);
+    // laid out per channel pair for the packed-fp32 epilogue: entry c&~1 = {rstd0, rstd1, shift0, shift1},
+    // entry (c&~1)+1 = {gamma_id0, gamma_id1, beta_id0, beta_id1}
+    float* pp = reinterpret_cast<float*>(ncpar + static_cast<long long>(n) * C + (c & ~1)) + (c & 1);
+    pp[0] = rstd;
+    pp[2] = -mu * rstd;
+    pp[4] = g;
+    pp[6] = b;
     const float w = w_h[c] * rstd;
     wh_fold[static_cast<long long>(n) * C + c] = w;
     part = w * mu;
@@ -452,7 +458,8 @@ __global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h,
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     const float m = 1.f / (1.f + expf(-(acc + __ldg(bh_fold + n))));
     for (int c = lane; c < C; c += 32) {
-      const float4 pr = __ldg(ncpar + static_cast<long long>(n) * C + c);
+      const float* pp = reinterpret_cast<const float*>(ncpar + static_cast<long long>(n) * C + (c & ~1)) + (c & 1);
+      const float4 pr = make_float4(__ldg(pp), __ldg(pp + 2), __ldg(pp + 4), __ldg(pp + 6));
       const float hn = fmaf(ldf(hrow + c), pr.x, pr.y);
       const float A = fmaf(ldf(grow + c), hn, ldf(grow + C + c));
       const float I = fmaf(pr.z, hn, pr.w);

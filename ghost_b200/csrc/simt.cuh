@@ -40,7 +40,7 @@ int in_stats_parts(int N, int HW, int C);
 const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* parts, cudaStream_t s);
 
 // Per-AAD-layer fold of the statistics (fixed-order sum of the P parts, in double) with the identity FCs and conv_h.
-//   ncpar[n][c] = {rstd, -mu*rstd, gamma_id, beta_id}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
+//   ncpar[n][c] = per channel pair: {rstd0, rstd1, -mu0*rstd0, -mu1*rstd1}, {gamma_id0, gamma_id1, beta_id0, beta_id1}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
 // scratch: aad_fold_scratch_floats(N, C) floats, zero before the first launch (the kernel leaves it zeroed)
 size_t aad_fold_scratch_floats(int N, int C);
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
