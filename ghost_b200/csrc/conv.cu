@@ -269,6 +269,11 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   }
   int stages = (221 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
+  static const int max_stages = [] {
+    const char* e = getenv("GHOST_MAX_STAGES");  // profiling switch: cap the operand ring depth
+    return e ? atoi(e) : 8;
+  }();
+  if (stages > max_stages) stages = max_stages;
   if (stages < 2) stages = 2;
   p.stages = stages;
   // Short tiles are bound by how fast one warp can issue tcgen05.mma and hand tiles over: split the tiles over

@@ -8,11 +8,12 @@
 // buffer ever exists.  Stride-2 convs use a 5-D parity-split view of the same
 // NHWC memory, ConvTranspose k4s2 is 4 output-phase launches with 2x2 taps.
 //
-// Roles (608 threads): warp 0 = TMA producer, warps 1-2 = MMA issuers (even / odd tiles; warp 1 also owns the
-// TMEM allocation), warps 3..18 = epilogue (TMEM -> regs -> fused epilogue -> global or TMA store), four warps
-// per TMEM lane group splitting the columns.  Producer and issuer warps run converged and elect one lane per
-// copy / MMA batch.  The accumulator is double buffered in TMEM so the epilogue of tile i overlaps the main loop
-// of tile i+1.  Persistent CTAs, static round-robin tile schedule.
+// Roles (640 threads): warp 0 = TMA producer of the activation operand (+ AAD h tiles, resident weights), warp 3 =
+// TMA producer of the weight operand, warps 1-2 = MMA issuers (even / odd tiles; warp 1 also owns the TMEM
+// allocation), warps 4..19 = epilogue (TMEM -> regs -> fused epilogue -> global or TMA store).  Producer and
+// issuer warps run converged and elect one lane per copy / MMA batch.  The accumulator is multi-buffered in TMEM
+// so the epilogue of tile i overlaps the main loop of the next tiles.  Persistent CTAs, static round-robin tile
+// schedule.
 //
 // Reference ops covered: nn.Conv2d / nn.ConvTranspose2d / nn.Linear call sites in
 // network/AEI_Net.py:19-41,101 and network/AADLayer.py:13-18,67-74; the AAD
@@ -158,6 +159,85 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
 
 }  // namespace
 
+// One MMA issuer warp (converged; one elected lane issues).  `par` is a literal at both call sites so that every
+// ring position and barrier address derives from kernel parameters and blockIdx only: ptxas then keeps the
+// loop state in uniform registers instead of broadcasting it from vector registers before every tcgen05.mma.
+__device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, const uint32_t tmem_base,
+                                           uint64_t* full_bar, uint64_t* empty_bar, uint64_t* tfull_bar,
+                                           uint64_t* tempty_bar, uint64_t* bfull_bar_p, int* abort_flag_p, uint8_t* ring,
+                                           uint8_t* bres, const bool win, const int row_bytes, const int b_tile_bytes,
+                                           const int a_stage_bytes, const int stage_bytes, const int num_kb,
+                                           const int tiles_total, const int acc_stride) {
+  volatile int& abort_flag = *abort_flag_p;
+  uint64_t& bfull_bar = *bfull_bar_p;
+    const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t idesc = make_idesc_bf16(128, p.BN);
+    const uint32_t dhi = smem_desc_hi(win ? 1024 : 8 * row_bytes, p.kc != 64);
+    const uint32_t ring_u = smem_u32(ring);
+    const uint32_t bt16 = static_cast<uint32_t>(b_tile_bytes) >> 4;  // weight tile size in descriptor units
+    const uint32_t bres_lo = smem_desc_lo(smem_u32(bres));
+    const uint32_t bstep = p.kc_per_tap * bt16;
+    const int S2 = p.dual ? p.stages >> 1 : p.stages;
+    const uint32_t slot0 = ring_u + (p.dual ? par * S2 : 0) * stage_bytes;  // this issuer's part of the ring
+    const uint32_t full0 = smem_u32(&full_bar[p.dual ? par * S2 : 0]);
+    const uint32_t empty0 = smem_u32(&empty_bar[p.dual ? par * S2 : 0]);
+    const int my_tiles = blockIdx.x < tiles_total ? (tiles_total - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+    int stage_r = 0;
+    uint32_t phase = 0;
+    int as = 0;           // accumulator stage of tile `it` = it % sets
+    uint32_t aphase = 0;  // (it / sets) & 1
+    if (p.b_res) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
+    for (int it = 0; it < my_tiles; ++it) {
+      if (it != 0 && ++as == p.sets) {
+        as = 0;
+        aphase ^= 1u;
+      }
+      if (p.dual && (it & 1) != par) continue;  // the other issuer's tile (two accumulator stages in this mode)
+      const uint32_t d_tmem = tmem_base_u + as * acc_stride;
+      mbar_wait_nofail(&tempty_bar[as], aphase ^ 1u, &abort_flag);
+      tc_fence_after();
+      uint32_t bq = bres_lo;  // resident weights: descriptor of the current K chunk (tap (row, 0) in window mode)
+      int kci = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_nofail(reinterpret_cast<uint64_t*>(__cvta_shared_to_generic(full0 + 8 * stage_r)), phase, &abort_flag);
+        tc_fence_after();
+        const uint32_t sa = slot0 + stage_r * stage_bytes;
+        const uint32_t a_lo = smem_desc_lo(sa);
+        if (win) {
+          // the horizontal taps are views of the window shifted by whole pixel rows (128 B = 8 descriptor units)
+          if (p.b_res) {
+            umma_bf16_batch<4>(d_tmem, a_lo, bq, dhi, idesc, kb != 0);
+            umma_bf16_batch<4>(d_tmem, a_lo + 8, bq + bstep, dhi, idesc, 1);
+            umma_bf16_batch<4>(d_tmem, a_lo + 16, bq + 2 * bstep, dhi, idesc, 1);
+            bq += bt16;
+            if (++kci == p.kc_per_tap) {
+              kci = 0;
+              bq += 2 * bstep;
+            }
+          } else {
+            const uint32_t b_lo = smem_desc_lo(sa + a_stage_bytes);
+            umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
+            umma_bf16_batch<4>(d_tmem, a_lo + 8, b_lo + bt16, dhi, idesc, 1);
+            umma_bf16_batch<4>(d_tmem, a_lo + 16, b_lo + 2 * bt16, dhi, idesc, 1);
+          }
+        } else if (p.kc == 64) {
+          const uint32_t b_lo = p.b_res ? bq : smem_desc_lo(sa + a_stage_bytes);
+          umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
+          bq += bt16;
+        } else {
+          umma_bf16_batch<2>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
+        }
+        // frees the smem slot when these MMAs retire
+        umma_commit_elect(reinterpret_cast<uint64_t*>(__cvta_shared_to_generic(empty0 + 8 * stage_r)));
+        if (++stage_r == S2) {
+          stage_r = 0;
+          phase ^= 1u;
+        }
+      }
+      umma_commit_elect(&tfull_bar[as]);
+    }
+}
+
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
@@ -185,7 +265,6 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int b_stage_bytes = p.b_res ? 0 : (win ? 3 * b_tile_bytes : b_tile_bytes);
   const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
   const int rows_used = p.bw * p.bh * p.bn;
-  const uint32_t tx_bytes = (win ? (p.bw + 2) * 128 : rows_used * row_bytes) + b_stage_bytes;
   const int bres_tiles = p.b_res ? p.ntaps * p.kc_per_tap : 0;
   uint8_t* bres = smem;                                 // resident weight tiles [tap][chunk][BN rows][128 B]
   uint8_t* ring = smem + bres_tiles * b_tile_bytes;     // operand ring
@@ -204,7 +283,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   if (threadIdx.x == 0) {
     abort_flag = 0;
     for (int i = 0; i < p.stages; ++i) {
-      mbar_init(&full_bar[i], 1);
+      mbar_init(&full_bar[i], p.b_res ? 1 : 2);  // one arrive.expect_tx per operand producer
       mbar_init(&empty_bar[i], 1);
     }
     // linear mode: all 16 epilogue warps share every tile; AAD mode: 4 warps per 64-channel box of a tile
@@ -236,14 +315,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int acc_stride = p.tmem_cols / p.sets;  // columns per accumulator stage
 
   if (warp == 0) {
-    // ============================== TMA producer ==============================
-    // The whole warp runs the loop converged (every exit is voted on); one elected lane issues the copies.
-    // dual-issuer mode: even tiles go through ring slots [0, S2), odd tiles through [S2, 2*S2)
+    // ============================== TMA producer: activations =================
+    // Converged warp, one elected lane issues the copies; no data-dependent exits (mbar_wait_nofail).  The weight
+    // operand has its own producer (warp 3): a single thread cannot feed both operands of short K blocks fast
+    // enough.  dual-issuer mode: even tiles go through ring slots [0, S2), odd tiles through [S2, 2*S2).
     const int S2 = p.dual ? p.stages >> 1 : p.stages;
     int st[2] = {0, 0};
     uint32_t ph[2] = {0, 0};
-    bool ok = true;
-    int hit = 0;
     if (p.b_res && elect_one()) {
       mbar_expect_tx(&bfull_bar, bres_tiles * b_tile_bytes);
       for (int i = 0; i < bres_tiles; ++i)
@@ -255,11 +333,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     int hs = 0;
     uint32_t hphase = 0;
     const int tap0 = kb0 / p.kc_per_tap, kci0 = kb0 - tap0 * p.kc_per_tap;
-    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++hit, walk.next(p)) {
+    const uint32_t a_tx = win ? (p.bw + 2) * 128 : rows_used * row_bytes;
+    int hit = 0;
+    for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++hit, walk.next(p)) {
       const TileCoord t = walk.t;
       const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
       if (p.mode == kModeAAD) {
-        if (!__all_sync(0xffffffffu, mbar_wait(&hempty_bar[hs], hphase ^ 1u, &abort_flag))) break;
+        mbar_wait_nofail(&hempty_bar[hs], hphase ^ 1u, &abort_flag);
         if (elect_one()) {
           mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
           for (int b = 0; b < hbox; ++b)
@@ -275,30 +355,21 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       const int rg = p.dual ? (hit & 1) : 0;
       int stage_r = st[rg];
       uint32_t phase = ph[rg];
-      for (int kb = kb0; kb < kb0 + num_kb; ++kb) {
+      for (int kb = 0; kb < num_kb; ++kb) {
         const int stage = rg * S2 + stage_r;
-        if (!__all_sync(0xffffffffu, mbar_wait(&empty_bar[stage], phase ^ 1u, &abort_flag))) {
-          ok = false;
-          break;
-        }
+        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
         if (elect_one()) {
           uint8_t* sa = ring + stage * stage_bytes;
-          uint8_t* sb = sa + a_stage_bytes;
-          mbar_expect_tx(&full_bar[stage], tx_bytes);
+          mbar_expect_tx(&full_bar[stage], a_tx);
           if (win) {
             // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
             tma_load_4d(sa, &p.tmA, &full_bar[stage], p.a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
-            if (!p.b_res)
-              for (int dwi = 0; dwi < 3; ++dwi)
-                tma_load_2d(sb + dwi * b_tile_bytes, &p.tmB, &full_bar[stage],
-                            p.b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, t.nt * p.BN);
           } else {
             const int c = p.a_c0 + p.tap_c[tap] + kci * p.kc;
             if (p.a_rank == 4)
               tma_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
             else
               tma_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
-            if (!p.b_res) tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * p.kc, t.nt * p.BN);
           }
         }
         __syncwarp();
@@ -314,80 +385,63 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       st[rg] = stage_r;
       ph[rg] = phase;
     }
-  } else if (warp <= kIgemmMmaWarps) {
-    // ============================== MMA issuers ===============================
-    // Two converged warps: warp 1 issues the even tiles of this CTA (accumulator stage 0), warp 2 the odd ones
-    // (stage 1).  One warp cannot issue tcgen05.mma fast enough for narrow tiles (a K block of a 64-channel conv
-    // is only a few hundred tensor-pipe cycles); a tile's MMAs all come from one thread, so the accumulation
-    // order - and the result - does not depend on the split.  Both walk the same operand ring.
-    const int par = warp - 1;
-    const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t idesc = make_idesc_bf16(128, p.BN);
-    const uint32_t dhi = smem_desc_hi(win ? 1024 : 8 * row_bytes, p.kc != 64);
-    const uint32_t ring_u = smem_u32(ring);
-    const uint32_t bt16 = static_cast<uint32_t>(b_tile_bytes) >> 4;     // weight tile size in descriptor units
-    const uint32_t bres_lo = smem_desc_lo(smem_u32(bres));
-    const int S2 = p.dual ? p.stages >> 1 : p.stages;
-    const int slot0 = p.dual ? par * S2 : 0;  // this issuer's part of the ring
-    int stage_r = 0;
-    uint32_t phase = 0;
-    bool ok = p.dual || par == 0;  // single-issuer mode: warp 2 idles
-    int it = 0;
-    if (ok && p.b_res && !__all_sync(0xffffffffu, mbar_wait(&bfull_bar, 0, &abort_flag))) ok = false;
-    int as = 0;           // accumulator stage of tile `it` = it % sets
-    uint32_t aphase = 0;  // (it / sets) & 1
-    for (int tile = blockIdx.x; tile < tiles_total && ok; tile += gridDim.x, ++it) {
-      if (it != 0 && ++as == p.sets) {
-        as = 0;
-        aphase ^= 1u;
-      }
-      if (p.dual && (it & 1) != par) continue;  // the other issuer's tile (two accumulator stages in this mode)
-      const uint32_t d_tmem = tmem_base_u + as * acc_stride;
-      if (!__all_sync(0xffffffffu, mbar_wait(&tempty_bar[as], aphase ^ 1u, &abort_flag))) break;
-      tc_fence_after();
-      uint32_t bq = bres_lo;  // resident weights: descriptor of tap (row, 0), chunk kci
-      int kci = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int stage = slot0 + stage_r;
-        if (!__all_sync(0xffffffffu, mbar_wait(&full_bar[stage], phase, &abort_flag))) {
-          ok = false;
-          break;
-        }
-        tc_fence_after();
-        const uint32_t sa = ring_u + stage * stage_bytes;
-        const uint32_t a_lo = smem_desc_lo(sa);
-        if (win) {
-          // the horizontal taps are views of the window shifted by whole pixel rows (128 B = 8 descriptor units)
-          if (p.b_res) {
-            const uint32_t bstep = p.kc_per_tap * bt16;
-            umma_bf16_batch<4>(d_tmem, a_lo, bq, dhi, idesc, kb != 0);
-            umma_bf16_batch<4>(d_tmem, a_lo + 8, bq + bstep, dhi, idesc, 1);
-            umma_bf16_batch<4>(d_tmem, a_lo + 16, bq + 2 * bstep, dhi, idesc, 1);
-            bq += bt16;
-            if (++kci == p.kc_per_tap) {
-              kci = 0;
-              bq += 2 * bstep;
+  } else if (warp == 3) {
+    // ============================== TMA producer: weights =====================
+    if (!p.b_res) {
+      const int S2 = p.dual ? p.stages >> 1 : p.stages;
+      int st[2] = {0, 0};
+      uint32_t ph[2] = {0, 0};
+      const int tap0 = kb0 / p.kc_per_tap, kci0 = kb0 - tap0 * p.kc_per_tap;
+      int nt = blockIdx.x % p.tiles_n;           // N tile of the current tile (tiles walk nt fastest)
+      const int dnt = gridDim.x % p.tiles_n;
+      int hit = 0;
+      for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++hit) {
+        int tap = tap0, kci = kci0;
+        const int rg = p.dual ? (hit & 1) : 0;
+        int stage_r = st[rg];
+        uint32_t phase = ph[rg];
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int stage = rg * S2 + stage_r;
+          mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+          if (elect_one()) {
+            uint8_t* sb = ring + stage * stage_bytes + a_stage_bytes;
+            mbar_expect_tx(&full_bar[stage], b_stage_bytes);
+            if (win) {
+              for (int dwi = 0; dwi < 3; ++dwi)
+                tma_load_2d(sb + dwi * b_tile_bytes, &p.tmB, &full_bar[stage],
+                            p.b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, nt * p.BN);
+            } else {
+              tma_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + (kb0 + kb) * p.kc, nt * p.BN);
             }
-          } else {
-            const uint32_t b_lo = smem_desc_lo(sa + a_stage_bytes);
-            umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
-            umma_bf16_batch<4>(d_tmem, a_lo + 8, b_lo + bt16, dhi, idesc, 1);
-            umma_bf16_batch<4>(d_tmem, a_lo + 16, b_lo + 2 * bt16, dhi, idesc, 1);
           }
-        } else if (p.kc == 64) {
-          const uint32_t b_lo = p.b_res ? bres_lo + kb * bt16 : smem_desc_lo(sa + a_stage_bytes);
-          umma_bf16_batch<4>(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
-        } else {
-          umma_bf16_batch<2>(d_tmem, a_lo, smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
+          __syncwarp();
+          if (++kci == p.kc_per_tap) {
+            kci = 0;
+            ++tap;
+          }
+          if (++stage_r == S2) {
+            stage_r = 0;
+            phase ^= 1u;
+          }
         }
-        umma_commit_elect(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
-        if (++stage_r == S2) {
-          stage_r = 0;
-          phase ^= 1u;
-        }
+        st[rg] = stage_r;
+        ph[rg] = phase;
+        nt += dnt;
+        if (nt >= p.tiles_n) nt -= p.tiles_n;
       }
-      if (ok) umma_commit_elect(&tfull_bar[as]);
     }
+  } else if (warp == 1) {
+    // ============================== MMA issuers ===============================
+    // Warp 1 issues the even tiles of this CTA (accumulator stage 0) and warp 2 the odd ones (stage 1) when
+    // p.dual is set, else warp 1 issues everything.  One warp cannot issue tcgen05.mma fast enough for short
+    // tiles; a tile's MMAs all come from one thread, so the accumulation order - and the result - does not
+    // depend on the split.  The loops have no data-dependent exits (see mbar_wait_nofail).
+    mma_issuer(p, 0, tmem_base, full_bar, empty_bar, tfull_bar, tempty_bar, &bfull_bar, &abort_flag, ring, bres, win,
+               row_bytes, b_tile_bytes, a_stage_bytes, stage_bytes, num_kb, tiles_total, acc_stride);
+  } else if (warp == 2) {
+    if (p.dual)
+      mma_issuer(p, 1, tmem_base, full_bar, empty_bar, tfull_bar, tempty_bar, &bfull_bar, &abort_flag, ring, bres, win,
+                 row_bytes, b_tile_bytes, a_stage_bytes, stage_bytes, num_kb, tiles_total, acc_stride);
   } else {
     // ============================== epilogue ==================================
     const int lg = warp & 3;                       // TMEM lane group this warp may read

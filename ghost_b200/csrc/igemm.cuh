@@ -10,8 +10,10 @@ namespace ghost {
 constexpr int kIgemmMaxTaps = 16;
 constexpr int kIgemmEpiWarps = 16;                           // four warps per TMEM lane group, splitting the columns
 constexpr int kIgemmMmaWarps = 2;                            // MMA issuers: warp 1 takes even tiles, warp 2 odd tiles
-constexpr int kIgemmEpiWarp0 = 1 + kIgemmMmaWarps;           // first epilogue warp
-constexpr int kIgemmThreads = 32 * (kIgemmEpiWarp0 + kIgemmEpiWarps);  // warp0 TMA, warps1-2 MMA, warps3-18 epilogue
+constexpr int kIgemmEpiWarp0 = 4;                            // first epilogue warp (a multiple of 4: TMEM lane groups)
+// warp 0: TMA producer of the activation operand (+ AAD h tiles, resident weights), warps 1-2: MMA issuers,
+// warp 3: TMA producer of the weight operand, warps 4-19: epilogue
+constexpr int kIgemmThreads = 32 * (kIgemmEpiWarp0 + kIgemmEpiWarps);
 
 enum IgemmMode : int { kModeLinear = 0, kModeAAD = 1 };
 enum Act1 : int { kActNone = 0, kActLeaky = 1, kActPRelu = 2, kActRelu = 3 };

@@ -69,6 +69,21 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volati
   return false;
 }
 
+// Same bound, but never changes the caller's control flow: after a timeout (or once another role has flagged one)
+// it simply returns and the caller carries on with stale data; the kernel then finishes and reports the error
+// word.  Keeping the issue loops free of data-dependent exits lets ptxas hold their state in uniform registers.
+__device__ __forceinline__ void mbar_wait_nofail(uint64_t* bar, uint32_t parity, volatile int* abort_flag) {
+  if (mbar_try_wait(bar, parity)) return;
+  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
+    if (mbar_try_wait(bar, parity)) return;
+    if ((spin & 63u) == 63u) {
+      if (*abort_flag) return;
+      __nanosleep(64);
+    }
+  }
+  *abort_flag = 1;
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
