@@ -219,10 +219,25 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   } else {
     int bn_ = bn_hint;
     if (!bn_) {
+      // Measured on B200 (tools/conv_sweep.py): with one CTA per SM a K block costs ~0.40 us whatever the N tile
+      // (issue-bound: four tcgen05.mma + two TMA boxes per block), ~0.43 us at N = 256.  So pick the N tile that
+      // minimises (rounds of the persistent grid) x (cost of a K block); ties go to the narrower tile, which
+      // spreads the work over more SMs.
       const int cpad = (w.Cout + 15) / 16 * 16;
-      bn_ = cpad < 256 ? cpad : 256;
       const long long tiles_m = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
-      while (bn_ > 64 && bn_ % 32 == 0 && tiles_m * ((w.Cout + bn_ - 1) / bn_) < 148) bn_ /= 2;
+      double best = 1e30;
+      bn_ = cpad < 256 ? cpad : 256;
+      const int cands[4] = {256, 128, 64, cpad < 256 ? cpad : 256};
+      for (int i = 0; i < 4; ++i) {
+        const int bn_c = cands[i];
+        if (bn_c > cpad && bn_c != cands[3]) continue;
+        const long long tiles = tiles_m * ((w.Cout + bn_c - 1) / bn_c);
+        const double cost = static_cast<double>((tiles + 147) / 148) * (bn_c > 128 ? 0.43 : 0.40);
+        if (cost < best || (cost == best && bn_c < bn_)) {
+          best = cost;
+          bn_ = bn_c;
+        }
+      }
     }
     p.BN = bn_;
     p.tiles_n = (w.Cout + p.BN - 1) / p.BN;
