@@ -71,6 +71,7 @@ SIGNATURES = {
                             _vp, _i, _vp]),
     "ghost_test_last_error": (C.c_char_p, []),
     "ghost_test_upsample2x": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "ghost_test_upsample2x_stats": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _fp, _fp, _vp]),
 }
 
 _lib = None

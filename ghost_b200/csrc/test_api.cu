@@ -199,4 +199,34 @@ int ghost_test_upsample2x(const void* x, void* y, int dtype, int N, int H, int W
   });
 }
 
+// Fused upsample + InstanceNorm statistics (K5b): also folds the per-part sums on the host (in double, part order)
+// into mean[N*C] / biased var[N*C] so that the caller can compare them with the statistics of y itself.
+int ghost_test_upsample2x_stats(const void* x, void* y, int dtype, int N, int H, int W, int C, float* mean_host,
+                                float* var_host, void* stream) {
+  return guarded_t([&] {
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    DevPool pool;
+    const int HWo = 4 * H * W;
+    const int P = in_stats_parts(N, HWo, C);
+    const size_t nparts = static_cast<size_t>(N) * (2 * P + 1) * C;
+    float* parts = pool.alloc_n<float>(nparts);
+    check_msg(upsample2x_stats_launch(x, y, dtype == GHOST_F32 ? kF32 : kBF16, N, H, W, C, parts, s), "upsample2x_stats");
+    check_cuda(cudaStreamSynchronize(s), "upsample sync");
+    std::vector<float> hp(nparts);
+    check_cuda(cudaMemcpy(hp.data(), parts, nparts * sizeof(float), cudaMemcpyDeviceToHost), "parts download");
+    for (int n = 0; n < N; ++n)
+      for (int c = 0; c < C; ++c) {
+        const float* pn = hp.data() + static_cast<size_t>(n) * (2 * P + 1) * C;
+        double su = 0.0, sq = 0.0;
+        for (int q = 0; q < P; ++q) {
+          su += pn[(2 * q) * C + c];
+          sq += pn[(2 * q + 1) * C + c];
+        }
+        const double d = su / HWo;
+        mean_host[static_cast<size_t>(n) * C + c] = static_cast<float>(pn[2 * P * C + c] + d);
+        var_host[static_cast<size_t>(n) * C + c] = static_cast<float>(sq / HWo - d * d);
+      }
+  });
+}
+
 }  // extern "C"

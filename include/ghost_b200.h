@@ -157,6 +157,10 @@ int ghost_test_aad(const void* h_nhwc, const void* zattr_nhwc, const float* zid_
                    const float* fc2_b, const float* convh_w, float convh_b, void* out_nhwc, int mode, void* stream);
 const char* ghost_test_last_error(void);
 int ghost_test_upsample2x(const void* x_nhwc, void* y_nhwc, int dtype, int N, int H, int W, int C, void* stream);
+/* Bilinear x2 fused with the InstanceNorm statistics of its output (the next AAD block's input,
+ * network/AEI_Net.py:124-138 + network/AADLayer.py:21); mean / biased variance per (n, c) come back on the host. */
+int ghost_test_upsample2x_stats(const void* x_nhwc, void* y_nhwc, int dtype, int N, int H, int W, int C,
+                                float* mean_host, float* var_host, void* stream);
 
 #ifdef __cplusplus
 }

@@ -158,3 +158,32 @@ def test_upsample2x(shape, mode):
     got = y.float().permute(0, 3, 1, 2)
     tol = 1e-5 if mode == _lib.F32 else 2e-2
     assert (got - ref).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("mode", [_lib.BF16, _lib.F32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("shape", [(2, 64, 16, 16), (1, 1024, 2, 2), (3, 128, 32, 32), (2, 64, 128, 128)])
+def test_upsample2x_fused_stats(shape, mode):
+    """The fused kernel writes the same pixels as the plain upsample and the InstanceNorm statistics of exactly
+    those (rounded) pixels."""
+    N, Cc, H, W = shape
+    dt = torch.float32 if mode == _lib.F32 else torch.bfloat16
+    g = torch.Generator().manual_seed(11)
+    x = (torch.randn(N, Cc, H, W, generator=g) * 2.0 + 0.7).cuda()
+    xn = nhwc(x, dt)
+    lib = _lib.load()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    y0 = torch.empty((N, 2 * H, 2 * W, Cc), dtype=dt, device="cuda")
+    _lib.check(lib.ghost_test_upsample2x(C.c_void_p(xn.data_ptr()), C.c_void_p(y0.data_ptr()), mode, N, H, W, Cc, st),
+               test_api=True)
+    y1 = torch.full_like(y0, float("nan"))
+    mean = np.zeros((N, Cc), np.float32)
+    var = np.zeros((N, Cc), np.float32)
+    _lib.check(lib.ghost_test_upsample2x_stats(C.c_void_p(xn.data_ptr()), C.c_void_p(y1.data_ptr()), mode, N, H, W, Cc,
+                                               mean.ctypes.data_as(C.POINTER(C.c_float)),
+                                               var.ctypes.data_as(C.POINTER(C.c_float)), st), test_api=True)
+    assert torch.equal(y0, y1)
+    yd = y1.double()
+    ref_mean = yd.mean(dim=(1, 2)).cpu().numpy()
+    ref_var = yd.var(dim=(1, 2), unbiased=False).cpu().numpy()
+    assert np.abs(mean - ref_mean).max() <= 1e-5 * max(1.0, np.abs(ref_mean).max())
+    assert np.abs(var - ref_var).max() <= 2e-5 * max(1.0, ref_var.max())

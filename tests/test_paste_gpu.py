@@ -141,3 +141,53 @@ def test_properties_at_1080p_batch():
     # one frame against the CPU oracle at full size
     ref = paste_ref.get_final_image_ref([[crops[4]]], [mask[0]], frames[4].cpu().numpy(), [[tfms[4]]])
     assert np.array_equal(out[4].cpu().numpy(), ref)
+
+
+def test_overlapping_faces_compose_in_order():
+    """Two faces whose boxes overlap in one frame: every pixel is composited once, by the first box that holds it,
+    over all faces in list order (float64 running blend) - bit-exact against the reference loop."""
+    rng = np.random.default_rng(7)
+    H, W = 400, 600
+    frame = synth.frame_u8(H, W, seed=71)
+    crops = synth.crops_u8(3, seed=72)
+    masks = np.stack([synth.soft_mask(rng) for _ in range(3)])
+    base = synth.similarity_tfm(H, W, rng, scale=0.55)
+    tf2 = base.copy()
+    tf2[:, 2] += np.array([-60.0, 25.0])      # same face shifted: boxes overlap heavily
+    tf3 = base.copy()
+    tf3[:, 2] += np.array([40.0, -50.0])
+    tfms = np.stack([base, tf2, tf3])
+    ref = paste_ref.get_final_image_ref([[crops[0]], [crops[1]], [crops[2]]], [masks[0], masks[1], masks[2]], frame,
+                                        [[tfms[0]], [tfms[1]], [tfms[2]]])
+    out = ghost_b200.paste_back(frame[None], crops, masks, tfms, np.zeros(3, np.int32), mode="exact")
+    assert np.array_equal(out[0].cpu().numpy(), ref)
+
+
+def test_swap_pipeline_matches_sequential_calls():
+    """SwapPipeline (three streams, double-buffered slots) returns exactly what embed_hwc -> swap_u8 -> paste_back
+    return when called one after the other, batch after batch."""
+    B, H, W = 2, 240, 320
+    G = ghost_b200.AEI_Net("unet", 1, 512, seed=3).eval().bfloat16().cuda()
+    arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
+    rng = np.random.default_rng(5)
+    pipe = ghost_b200.SwapPipeline(G, arc, B, (H, W), depth=2, mode="exact")
+    face_frame = np.arange(B, dtype=np.int32)
+    batches, outs = [], []
+    for step in range(5):
+        src = torch.from_numpy(synth.sources_u8(B, seed=step)).pin_memory()
+        crp = torch.from_numpy(synth.crops_u8(B, seed=10 + step)).pin_memory()
+        frm = torch.from_numpy(np.stack([synth.frame_u8(H, W, seed=100 * step + f) for f in range(B)])).pin_memory()
+        msk = torch.from_numpy(np.stack([synth.soft_mask(rng) for _ in range(B)])).pin_memory()
+        tf = np.stack([synth.similarity_tfm(H, W, rng, scale=0.9) for _ in range(B)])
+        out = torch.empty_like(frm).pin_memory()
+        pipe.submit(src, crp, frm, msk, tf, face_frame, out)
+        batches.append((src, crp, frm, msk, tf))
+        outs.append(out)
+    pipe.flush()
+    torch.cuda.synchronize()
+    for (src, crp, frm, msk, tf), out in zip(batches, outs):
+        z = arc.embed_hwc(src.cuda(), out_dtype=torch.bfloat16)
+        G.swap_u8(crp.cuda(), z, write_u8=False)
+        yptr, ydt = G.y_nhwc(B)
+        ref = ghost_b200.paste_back(frm.cuda(), (yptr, ydt, B), msk.cuda(), tf, face_frame, mode="exact")
+        assert torch.equal(out, ref.cpu())
