@@ -126,12 +126,33 @@ void Net::build_arcface(ExecPlan& p) {
     p.ops.push_back(std::move(op));
   };
 
+  // Block names in execution order: in bf16 mode the conv that produces a block's input also writes bn1(input)
+  // as a second output (IBasicBlock.forward applies bn1 before conv1 and keeps x for the shortcut), which saves
+  // one read + write pass per block; the fp32 (CUDA-core) mode keeps the separate per-channel affine.
+  std::vector<std::string> names;
+  for (int l = 0; l < 4; ++l)
+    for (int i = 0; i < kLayers[l]; ++i) {
+      char nb[64];
+      snprintf(nb, sizeof(nb), "l%d.%d", l + 1, i);
+      names.push_back(nb);
+    }
+  size_t blk = 0;
   p.emb_in = new_act(112, 112, 3);
   Act x = new_act(112, 112, 64);
+  Act t_fused;  // bn1(x) of the block about to run, when the producer conv wrote it
+  auto fuse_bn1 = [&](Epilogue* e, const Act& like, size_t next_blk) {
+    t_fused = Act();
+    if (!bf || next_blk >= names.size() || like.C % 16) return;
+    t_fused = new_act(like.H, like.W, like.C);
+    e->out2 = t_fused.p;
+    e->scale2 = vecs_.at(names[next_blk] + ".bn1.scale");
+    e->shift2 = vecs_.at(names[next_blk] + ".bn1.shift");
+  };
   {
     Epilogue e;
     e.act1 = kActPRelu;
     e.slope_c = vecs_.at("stem.prelu");
+    // the stem runs on CUDA cores (Cin = 3): no second output there
     add_conv("stem", p.emb_in, 3, Taps::square(3, 1, 1), 112, 112, "stem", OutView::dense(x), e);
   }
   int hw = 112;
@@ -143,8 +164,9 @@ void Net::build_arcface(ExecPlan& p) {
       const std::string n = nb;
       const int stride = i == 0 ? 2 : 1;
       const int ho = hw / stride;
-      Act t = new_act(hw, hw, x.C);
-      {
+      Act t = t_fused;
+      if (!t.p) {
+        t = new_act(hw, hw, x.C);
         const Act xx = x, tt = t;
         const float* scv = vecs_.at(n + ".bn1.scale");
         const float* shv = vecs_.at(n + ".bn1.shift");
@@ -176,8 +198,10 @@ void Net::build_arcface(ExecPlan& p) {
         const OutView rv = OutView::dense(idn);
         e.res = idn.p;
         e.r_sn = rv.sn; e.r_sh = rv.sh; e.r_sw = rv.sw; e.r_off = rv.off;
+        fuse_bn1(&e, o, blk + 1);
         add_conv(n + ".conv2", u, pl, Taps::square(3, 1, stride), ho, ho, n + ".conv2", OutView::dense(o), e);
       }
+      ++blk;
       x = o;
       hw = ho;
     }

@@ -137,6 +137,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.res = epi.res;
     p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;
     p.act2 = epi.act2;
+    if (epi.out2) return "lower_conv: the second output needs the tensor-core path";
     return nullptr;
   }
 
@@ -354,6 +355,10 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.res = reinterpret_cast<const __nv_bfloat16*>(epi.res);
     p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;
     p.act2 = epi.act2;
+    p.out2 = epi.out2;
+    p.scale2 = epi.scale2;
+    p.shift2 = epi.shift2;
+    if (epi.out2 && (out.dtype != kBF16 || w.Cout % 16)) return "lower_conv: the second output needs bf16 and Cout % 16 == 0";
     if (out.dtype == kBF16 && w.Cout % 16 == 0 && ((out.off % 8) || (out.sw % 8) || (out.sh % 8) || (out.sn % 8)))
       return "lower_conv: bf16 output view must be 16-byte aligned";
   }

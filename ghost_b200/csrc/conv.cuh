@@ -44,6 +44,11 @@ struct Epilogue {
   const void* res = nullptr;  // residual, same dtype as the output
   long long r_sn = 0, r_sh = 0, r_sw = 0, r_off = 0;
   int act2 = kAct2None;
+  // optional second output (tensor-core path, bf16, same strides as the first): out2 = out * scale2[c] + shift2[c]
+  // computed from the value as stored - iresnet's bn1 of the next block (arcface iresnet.py IBasicBlock.forward)
+  void* out2 = nullptr;
+  const float* scale2 = nullptr;
+  const float* shift2 = nullptr;
 };
 
 struct OutView {

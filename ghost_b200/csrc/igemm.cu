@@ -138,6 +138,31 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
             }
           } else {
             __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + o_pix + col0;
+            if (full16 && p.out2) {
+              // second output from the value as stored (rounded to bf16), e.g. the next block's bn1
+              __nv_bfloat16* o2 = reinterpret_cast<__nv_bfloat16*>(p.out2) + o_pix + col0;
+              float t[16];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 sc = __ldg(reinterpret_cast<const float4*>(p.scale2 + col0) + i);
+                const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift2 + col0) + i);
+                t[4 * i] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i])), sc.x, sh.x);
+                t[4 * i + 1] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 1])), sc.y, sh.y);
+                t[4 * i + 2] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 2])), sc.z, sh.z);
+                t[4 * i + 3] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 3])), sc.w, sh.w);
+              }
+              uint4 s0, s1;
+              s0.x = pack_bf16(t[0], t[1]);
+              s0.y = pack_bf16(t[2], t[3]);
+              s0.z = pack_bf16(t[4], t[5]);
+              s0.w = pack_bf16(t[6], t[7]);
+              s1.x = pack_bf16(t[8], t[9]);
+              s1.y = pack_bf16(t[10], t[11]);
+              s1.z = pack_bf16(t[12], t[13]);
+              s1.w = pack_bf16(t[14], t[15]);
+              reinterpret_cast<uint4*>(o2)[0] = s0;
+              reinterpret_cast<uint4*>(o2)[1] = s1;
+            }
             if (full16) {
               uint4 s0, s1;
               s0.x = pack_bf16(f[0], f[1]);

@@ -64,6 +64,9 @@ struct alignas(64) IgemmParams {
   const __nv_bfloat16* res;
   long long r_sn, r_sh, r_sw, r_off;
   int act2;
+  void* out2;            // optional second bf16 output, same strides: bf16(out) * scale2[c] + shift2[c]
+  const float* scale2;
+  const float* shift2;
 
   // ---- epilogue (AAD blend): columns [0,cn) = gamma_attr, [cn,2cn) = beta_attr, cn = BN/2
   // The h tile is TMA-loaded into shared memory, blended there in place and TMA-stored (nothing is read row by
