@@ -1,6 +1,7 @@
 #include "simt.cuh"
 
 #include "igemm.cuh"  // Act1 / Act2 enums
+#include "ptx.cuh"    // packed fp32 helpers (fma2 / add2 / sub2 / mul2)
 
 namespace ghost {
 
@@ -305,6 +306,19 @@ constexpr int kStatThreads = 256;
 //              removes the E[x^2]-E[x]^2 cancellation: |mean - shift| is of the order of the std)
 // Every part is written by exactly one block and the fold kernel adds them in a fixed order, so the
 // statistics are deterministic (no atomics, no memset).
+//
+// s += (v - shift), q += (v - shift)^2 for eight channels, two per packed fp32 instruction.
+__device__ __forceinline__ void stats_accumulate8(const float (&v)[8], const float (&sft)[8], float (&s)[8],
+                                                  float (&q)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) {
+    const float2 d = ptx::sub2(make_float2(v[i], v[i + 1]), make_float2(sft[i], sft[i + 1]));
+    const float2 sn = ptx::add2(make_float2(s[i], s[i + 1]), d);
+    const float2 qn = ptx::fma2(d, d, make_float2(q[i], q[i + 1]));
+    s[i] = sn.x; s[i + 1] = sn.y;
+    q[i] = qn.x; q[i + 1] = qn.y;
+  }
+}
 template <typename T>
 __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restrict__ x, int HW, int C,
                                                                  int pix_per_block, float* __restrict__ parts) {
@@ -330,14 +344,7 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
         if (p + u * ppi < p1) load8(base + static_cast<long long>(p + u * ppi) * C, v[u]);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        if (p + u * ppi < p1) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float d = v[u][i] - sft[i];
-            s[i] += d;
-            q[i] = fmaf(d, d, q[i]);
-          }
-        }
+        if (p + u * ppi < p1) stats_accumulate8(v[u], sft, s, q);
       }
     }
   }
@@ -573,6 +580,44 @@ const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype
 // ---------------------------------------------------------------------------
 namespace {
 
+// ATen upsample_bilinear2d blend of the four neighbours of eight channels (packed fp32):
+//   o = (1-lh) * ((1-lw)*a + lw*b) + lh * ((1-lw)*c + lw*d)
+__device__ __forceinline__ void bilerp8(const float (&a)[8], const float (&b)[8], const float (&c)[8],
+                                        const float (&d)[8], float lw, float lh, float (&o)[8]) {
+  const float2 w0 = make_float2(1.f - lw, 1.f - lw), w1 = make_float2(lw, lw);
+  const float2 h0 = make_float2(1.f - lh, 1.f - lh), h1 = make_float2(lh, lh);
+#pragma unroll
+  for (int k = 0; k < 8; k += 2) {
+    const float2 t0 = ptx::fma2(w1, make_float2(b[k], b[k + 1]), ptx::mul2(w0, make_float2(a[k], a[k + 1])));
+    const float2 t1 = ptx::fma2(w1, make_float2(d[k], d[k + 1]), ptx::mul2(w0, make_float2(c[k], c[k + 1])));
+    const float2 r = ptx::fma2(h1, t1, ptx::mul2(h0, t0));
+    o[k] = r.x;
+    o[k + 1] = r.y;
+  }
+}
+
+// store eight channels and hand back the values as stored (after rounding to T)
+__device__ __forceinline__ void store8_rounded(float* p, const float (&v)[8], float (&r)[8]) {
+  store8(p, v);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r[i] = v[i];
+}
+__device__ __forceinline__ void store8_rounded(__nv_bfloat16* p, const float (&v)[8], float (&r)[8]) {
+  uint4 q;
+  __nv_bfloat162 t;
+  t = __floats2bfloat162_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    r[2 * i] = __uint_as_float(w[i] << 16);
+    r[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) upsample2x_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H,
                                                           int W, int C, int oC, int o_c0) {
@@ -599,26 +644,17 @@ __global__ void __launch_bounds__(256) upsample2x_kernel(const T* __restrict__ x
     load8(base + (h0 * W + w1) * C + cv * 8, b);
     load8(base + (h1 * W + w0) * C + cv * 8, c);
     load8(base + (h1 * W + w1) * C + cv * 8, d);
-#pragma unroll
-    for (int k = 0; k < 8; ++k)
-      o[k] = (1.f - lh) * ((1.f - lw) * a[k] + lw * b[k]) + lh * ((1.f - lw) * c[k] + lw * d[k]);
+    bilerp8(a, b, c, d, lw, lh, o);
     store8(orow + static_cast<long long>(ow) * oC + cv * 8, o);
   }
 }
-
-template <typename T>
-__device__ __forceinline__ float round_as(float v);
-template <>
-__device__ __forceinline__ float round_as<float>(float v) { return v; }
-template <>
-__device__ __forceinline__ float round_as<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16(v)); }
 
 // Bilinear x2 fused with the InstanceNorm statistics of its own output (the next AAD block normalises exactly
 // this tensor, network/AADLayer.py:21): same block / part decomposition and partial-sum layout as
 // in_stats_kernel, the sums run over the values as stored (after rounding to T).  The shift row is source
 // pixel (0,0), which align_corners copies unchanged to output pixel 0.
 template <typename T>
-__global__ void __launch_bounds__(kStatThreads) upsample2x_stats_kernel(const T* __restrict__ x, T* __restrict__ y, int H,
+__global__ void __launch_bounds__(kStatThreads, 4) upsample2x_stats_kernel(const T* __restrict__ x, T* __restrict__ y, int H,
                                                                          int W, int C, int pix_per_block,
                                                                          float* __restrict__ parts) {
   extern __shared__ float sh[];  // [kStatThreads][16]
@@ -651,16 +687,10 @@ __global__ void __launch_bounds__(kStatThreads) upsample2x_stats_kernel(const T*
       load8(base + (h0 * W + w1) * C, b);
       load8(base + (h1 * W + w0) * C, c);
       load8(base + (h1 * W + w1) * C, d);
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        o[k] = (1.f - lh) * ((1.f - lw) * a[k] + lw * b[k]) + lh * ((1.f - lw) * c[k] + lw * d[k]);
-      store8(obase + static_cast<long long>(p) * C, o);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float dv = round_as<T>(o[k]) - sft[k];
-        s[k] += dv;
-        q[k] = fmaf(dv, dv, q[k]);
-      }
+      bilerp8(a, b, c, d, lw, lh, o);
+      float stored[8];
+      store8_rounded(obase + static_cast<long long>(p) * C, o, stored);
+      stats_accumulate8(stored, sft, s, q);
     }
   }
 #pragma unroll
