@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libghost_b200.so")
+# GHOST_B200_LIB: another build of the same library (the profiling build of tools/igemm_prof.py), never a fallback
+LIB_PATH = os.environ.get("GHOST_B200_LIB") or os.path.join(_HERE, "libghost_b200.so")
 
 # ghost_status
 OK, ERR_INVALID, ERR_WEIGHTS, ERR_CUDA, ERR_KERNEL = 0, -1, -2, -3, -4

@@ -26,6 +26,27 @@ namespace ghost {
 
 using namespace ptx;
 
+// Stall accounting for tools/igemm_prof.py (make PROF=1): cycles each role spends waiting on its barriers.
+#ifdef GHOST_IGEMM_PROF
+__device__ unsigned long long g_igemm_prof[160][12];
+// launch timeline (tools/igemm_timeline.py): first CTA entry / last CTA exit of every igemm launch, by %globaltimer
+constexpr int kTlSlots = 8192;
+__device__ unsigned long long g_tl_t0[kTlSlots], g_tl_t1[kTlSlots];
+__device__ int g_tl_meta[kTlSlots][4];
+__device__ unsigned int g_tl_seq, g_tl_done;
+#define PROF_BEGIN() long long pw0_ = 0, pw1_ = 0; const long long pt0_ = clock64()
+#define PROF_WAIT0(stmt) do { const long long a_ = clock64(); stmt; pw0_ += clock64() - a_; } while (0)
+#define PROF_WAIT1(stmt) do { const long long a_ = clock64(); stmt; pw1_ += clock64() - a_; } while (0)
+#define PROF_END(slot, lane_) do { if ((lane_) == 0 && blockIdx.x < 160 && blockIdx.y == 0) { \
+    g_igemm_prof[blockIdx.x][slot] = pw0_; g_igemm_prof[blockIdx.x][slot + 1] = pw1_; \
+    g_igemm_prof[blockIdx.x][slot + 2] = clock64() - pt0_; } } while (0)
+#else
+#define PROF_BEGIN() do {} while (0)
+#define PROF_WAIT0(stmt) stmt
+#define PROF_WAIT1(stmt) stmt
+#define PROF_END(slot, lane_) do {} while (0)
+#endif
+
 namespace {
 
 struct TileCoord {
@@ -79,8 +100,11 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 }
 
 
+// `sp` != nullptr: per-channel parameters of this CTA's N tile staged in shared memory ([bias | slope | scale2 |
+// shift2] x 256 floats, column j of the tile at sp[j]); `rpre`: the residual row was fetched ahead into rq0/rq1.
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
-                                                   long long o_pix, long long r_pix) {
+                                                   long long o_pix, long long r_pix, const float* sp, int j,
+                                                   bool rpre, const uint4& rq0, const uint4& rq1) {
           float f[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
@@ -92,15 +116,34 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
             return;
           }
           if (p.bias) {
+            if (sp) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + col0 + i);
+              for (int i = 0; i < 4; ++i) {
+                const float4 b = *reinterpret_cast<const float4*>(sp + j + 4 * i);
+                f[4 * i] += b.x, f[4 * i + 1] += b.y, f[4 * i + 2] += b.z, f[4 * i + 3] += b.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] += __ldg(p.bias + col0 + i);
+            }
           }
           if (p.act1 == kActLeaky) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * p.slope;
           } else if (p.act1 == kActPRelu) {
+            if (sp) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * __ldg(p.slope_c + col0 + i);
+              for (int i = 0; i < 4; ++i) {
+                const float4 a = *reinterpret_cast<const float4*>(sp + 256 + j + 4 * i);
+                f[4 * i] = f[4 * i] > 0.f ? f[4 * i] : f[4 * i] * a.x;
+                f[4 * i + 1] = f[4 * i + 1] > 0.f ? f[4 * i + 1] : f[4 * i + 1] * a.y;
+                f[4 * i + 2] = f[4 * i + 2] > 0.f ? f[4 * i + 2] : f[4 * i + 2] * a.z;
+                f[4 * i + 3] = f[4 * i + 3] > 0.f ? f[4 * i + 3] : f[4 * i + 3] * a.w;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : f[i] * __ldg(p.slope_c + col0 + i);
+            }
           } else if (p.act1 == kActRelu) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
@@ -109,8 +152,8 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
           if (p.res) {
             const __nv_bfloat16* rp = p.res + r_pix + col0;
             if (full16) {
-              const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
-              const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+              const uint4 q0 = rpre ? rq0 : __ldg(reinterpret_cast<const uint4*>(rp));
+              const uint4 q1 = rpre ? rq1 : __ldg(reinterpret_cast<const uint4*>(rp) + 1);
               const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -144,8 +187,10 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
               float t[16];
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const float4 sc = __ldg(reinterpret_cast<const float4*>(p.scale2 + col0) + i);
-                const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift2 + col0) + i);
+                const float4 sc = sp ? *reinterpret_cast<const float4*>(sp + 512 + j + 4 * i)
+                                     : __ldg(reinterpret_cast<const float4*>(p.scale2 + col0) + i);
+                const float4 sh = sp ? *reinterpret_cast<const float4*>(sp + 768 + j + 4 * i)
+                                     : __ldg(reinterpret_cast<const float4*>(p.shift2 + col0) + i);
                 t[4 * i] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i])), sc.x, sh.x);
                 t[4 * i + 1] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 1])), sc.y, sh.y);
                 t[4 * i + 2] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 2])), sc.z, sh.z);
@@ -212,6 +257,7 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
     int as = 0;           // accumulator stage of tile `it` = it % sets
     uint32_t aphase = 0;  // (it / sets) & 1
     if (p.b_res) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
+    PROF_BEGIN();
     for (int it = 0; it < my_tiles; ++it) {
       if (it != 0 && ++as == p.sets) {
         as = 0;
@@ -219,12 +265,13 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
       }
       if (p.dual && (it & 1) != par) continue;  // the other issuer's tile (two accumulator stages in this mode)
       const uint32_t d_tmem = tmem_base_u + as * acc_stride;
-      mbar_wait_nofail(&tempty_bar[as], aphase ^ 1u, &abort_flag);
+      PROF_WAIT1(mbar_wait_nofail(&tempty_bar[as], aphase ^ 1u, &abort_flag));
       tc_fence_after();
       uint32_t bq = bres_lo;  // resident weights: descriptor of the current K chunk (tap (row, 0) in window mode)
       int kci = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait_nofail(reinterpret_cast<uint64_t*>(__cvta_shared_to_generic(full0 + 8 * stage_r)), phase, &abort_flag);
+        PROF_WAIT0(mbar_wait_nofail(reinterpret_cast<uint64_t*>(__cvta_shared_to_generic(full0 + 8 * stage_r)), phase,
+                                    &abort_flag));
         tc_fence_after();
         const uint32_t sa = slot0 + stage_r * stage_bytes;
         const uint32_t a_lo = smem_desc_lo(sa);
@@ -261,6 +308,13 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
       }
       umma_commit_elect(&tfull_bar[as]);
     }
+    if (par == 0) PROF_END(0, threadIdx.x & 31);
+#ifdef GHOST_IGEMM_PROF
+    if (par == 0 && blockIdx.x == 0 && blockIdx.y == 0 && (threadIdx.x & 31) == 0) {
+      const int cfg[8] = {p.BN, p.stages, p.dual, num_kb, my_tiles, p.a_win, p.b_res, static_cast<int>(gridDim.x)};
+      for (int i = 0; i < 8; ++i) g_igemm_prof[159][i] = cfg[i];
+    }
+#endif
 }
 
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
@@ -272,12 +326,19 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   __shared__ uint64_t hfull_bar[8];   // AAD mode: h tile landed in shared memory
   __shared__ uint64_t hempty_bar[8];  // AAD mode: blended tile stored, h slot free again
   __shared__ uint64_t bfull_bar;      // resident-weights mode: the packed weight slab landed
-  __shared__ float mexch[2][4][128];  // AAD mode, 128-channel tiles: mask-logit halves of the two warps sharing a row
+  __shared__ __align__(16) float mexch[2][4][128];  // AAD mode, 128-channel tiles: mask-logit halves of the two warps sharing a row
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+#ifdef GHOST_IGEMM_PROF
+  const long long cta_t0 = clock64();
+  unsigned long long cta_ns0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cta_ns0));
+  const unsigned tl_seq = *reinterpret_cast<volatile unsigned*>(&g_tl_seq) & (kTlSlots - 1);
+  if (threadIdx.x == 0) atomicMin(&g_tl_t0[tl_seq], cta_ns0);
+#endif
 
   // 1024-byte aligned operand ring (swizzle atoms repeat every 1024 B)
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -333,11 +394,27 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     }
   }
   if (warp == 1) tmem_alloc(&tmem_base_smem, p.tmem_cols);
+  // linear mode, one N tile: the per-channel epilogue parameters go to shared memory once (mexch is free in this
+  // mode), so the epilogue of a tile never waits on global memory for them
+  float* eparm = &mexch[0][0][0];
+  const bool staged = p.mode == kModeLinear && p.tiles_n == 1 && p.splits == 1;
+  if (staged && warp >= kIgemmEpiWarp0) {
+    for (int i = threadIdx.x - kIgemmEpiWarp0 * 32; i < p.BN; i += kIgemmEpiWarps * 32) {
+      const bool in = i < p.n_valid;
+      eparm[i] = (in && p.bias) ? __ldg(p.bias + i) : 0.f;
+      eparm[256 + i] = (in && p.act1 == kActPRelu) ? __ldg(p.slope_c + i) : 0.f;
+      eparm[512 + i] = (in && p.out2) ? __ldg(p.scale2 + i) : 0.f;
+      eparm[768 + i] = (in && p.out2) ? __ldg(p.shift2 + i) : 0.f;
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
   const int acc_stride = p.tmem_cols / p.sets;  // columns per accumulator stage
+#ifdef GHOST_IGEMM_PROF
+  if (threadIdx.x == 0 && blockIdx.x < 160 && blockIdx.y == 0) g_igemm_prof[blockIdx.x][9] = clock64() - cta_t0;
+#endif
 
   if (warp == 0) {
     // ============================== TMA producer: activations =================
@@ -360,11 +437,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     const int tap0 = kb0 / p.kc_per_tap, kci0 = kb0 - tap0 * p.kc_per_tap;
     const uint32_t a_tx = win ? (p.bw + 2) * 128 : rows_used * row_bytes;
     int hit = 0;
+    PROF_BEGIN();
     for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++hit, walk.next(p)) {
       const TileCoord t = walk.t;
       const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
       if (p.mode == kModeAAD) {
-        mbar_wait_nofail(&hempty_bar[hs], hphase ^ 1u, &abort_flag);
+        PROF_WAIT1(mbar_wait_nofail(&hempty_bar[hs], hphase ^ 1u, &abort_flag));
         if (elect_one()) {
           mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
           for (int b = 0; b < hbox; ++b)
@@ -382,7 +460,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       uint32_t phase = ph[rg];
       for (int kb = 0; kb < num_kb; ++kb) {
         const int stage = rg * S2 + stage_r;
-        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+        PROF_WAIT0(mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag));
         if (elect_one()) {
           uint8_t* sa = ring + stage * stage_bytes;
           mbar_expect_tx(&full_bar[stage], a_tx);
@@ -410,6 +488,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       st[rg] = stage_r;
       ph[rg] = phase;
     }
+    PROF_END(3, lane);
   } else if (warp == 3) {
     // ============================== TMA producer: weights =====================
     if (!p.b_res) {
@@ -487,18 +566,53 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
         const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * acc_stride;
-        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
-        tc_fence_after();
         const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
         const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
-        for (int j = ch0 * 16; j < ch1 * 16; j += 16) {
-          uint32_t v[16];
-          __syncwarp();
-          tmem_ld16(t_addr + j, v);
-          tmem_ld_wait();
-          const int col0 = t.nt * p.BN + j;
-          if (valid && col0 < p.n_valid) linear_epilogue_16(p, v, col0, o_pix, r_pix);
+        // the residual rows of this warp's columns are fetched before the accumulator is ready
+        // (two 16-column chunks ahead, the later ones while the earlier are being processed)
+        uint4 rq[4];
+        const bool rpre = p.res != nullptr && p.splits == 1;
+        if (rpre) {
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const int col0 = t.nt * p.BN + (ch0 + c) * 16;
+            if (ch0 + c < ch1 && valid && col0 + 16 <= p.n_valid) {
+              const uint4* rp = reinterpret_cast<const uint4*>(p.res + r_pix + col0);
+              rq[2 * c] = __ldg(rp);
+              rq[2 * c + 1] = __ldg(rp + 1);
+            }
+          }
+        }
+#ifdef GHOST_IGEMM_PROF
+        const long long ew0_ = clock64();
+#endif
+        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
+#ifdef GHOST_IGEMM_PROF
+        if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x < 160) {
+          g_igemm_prof[blockIdx.x][6] = (it ? g_igemm_prof[blockIdx.x][6] : 0ull) + (clock64() - ew0_);
+          g_igemm_prof[blockIdx.x][7] = it + 1;
+        }
+#endif
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (ch0 + c < ch1) {  // warp-uniform
+            const int j = (ch0 + c) * 16;
+            uint32_t v[16];
+            __syncwarp();
+            tmem_ld16(t_addr + j, v);
+            tmem_ld_wait();
+            const int col0 = t.nt * p.BN + j;
+            if (valid && col0 < p.n_valid)
+              linear_epilogue_16(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j, rpre, rq[2 * (c & 1)],
+                                 rq[2 * (c & 1) + 1]);
+            if (c < 2 && rpre && ch0 + c + 2 < ch1 && valid && col0 + 48 <= p.n_valid) {
+              const uint4* rp = reinterpret_cast<const uint4*>(p.res + r_pix + col0 + 32);
+              rq[2 * c] = __ldg(rp);
+              rq[2 * c + 1] = __ldg(rp + 1);
+            }
+          }
         }
         // hand the accumulator stage back to the MMA warp
         tc_fence_before();
@@ -616,8 +730,37 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   }
 
   // ------------------------------ teardown ------------------------------------
+#ifdef GHOST_IGEMM_PROF
+  if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x < 160 && blockIdx.y == 0)
+    g_igemm_prof[blockIdx.x][10] = clock64() - cta_t0;  // epilogue done
+#endif
   tc_fence_before();
   __syncthreads();
+#ifdef GHOST_IGEMM_PROF
+  if (threadIdx.x == 0 && blockIdx.x < 160 && blockIdx.y == 0) {
+    unsigned long long ns1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+    g_igemm_prof[blockIdx.x][8] = clock64() - cta_t0;
+    g_igemm_prof[blockIdx.x][11] = ns1 - cta_ns0;
+  }
+  if (threadIdx.x == 0) {
+    unsigned long long ns1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+    atomicMax(&g_tl_t1[tl_seq], ns1);
+    if (blockIdx.x == 0 && blockIdx.y == 0) {
+      g_tl_meta[tl_seq][0] = p.mode * 1000 + p.BN;
+      g_tl_meta[tl_seq][1] = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
+      g_tl_meta[tl_seq][2] = (p.a_win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap / p.splits) * (p.kc == 64 ? 1 : -1);
+      g_tl_meta[tl_seq][3] = gridDim.x * 10 + p.a_win;
+    }
+    __threadfence();
+    if (atomicAdd(&g_tl_done, 1u) == gridDim.x * gridDim.y - 1) {
+      g_tl_done = 0;
+      __threadfence();
+      atomicAdd(&g_tl_seq, 1u);
+    }
+  }
+#endif
   if (abort_flag && threadIdx.x == 0 && p.err) {
     *reinterpret_cast<volatile int*>(p.err) = 1;  // pinned, host-mapped word
     __threadfence_system();
@@ -691,5 +834,33 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }
+
+#ifdef GHOST_IGEMM_PROF
+extern "C" int ghost_prof_timeline_reset() {
+  cudaDeviceSynchronize();
+  unsigned int z = 0;
+  cudaMemcpyToSymbol(g_tl_seq, &z, sizeof(z));
+  cudaMemcpyToSymbol(g_tl_done, &z, sizeof(z));
+  void *t0 = nullptr, *t1 = nullptr;
+  cudaGetSymbolAddress(&t0, g_tl_t0);
+  cudaGetSymbolAddress(&t1, g_tl_t1);
+  cudaMemset(t0, 0xff, sizeof(g_tl_t0));
+  cudaMemset(t1, 0, sizeof(g_tl_t1));
+  return static_cast<int>(cudaDeviceSynchronize());
+}
+extern "C" int ghost_prof_timeline_read(unsigned long long* t0, unsigned long long* t1, int* meta) {
+  cudaDeviceSynchronize();
+  unsigned int n = 0;
+  cudaMemcpyFromSymbol(&n, g_tl_seq, sizeof(n));
+  cudaMemcpyFromSymbol(t0, g_tl_t0, sizeof(g_tl_t0));
+  cudaMemcpyFromSymbol(t1, g_tl_t1, sizeof(g_tl_t1));
+  cudaMemcpyFromSymbol(meta, g_tl_meta, sizeof(g_tl_meta));
+  return static_cast<int>(n);
+}
+extern "C" int ghost_prof_igemm_read(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  return static_cast<int>(cudaMemcpyFromSymbol(out, g_igemm_prof, sizeof(g_igemm_prof)));
+}
+#endif
 
 }  // namespace ghost
