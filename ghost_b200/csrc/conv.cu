@@ -301,6 +301,17 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.dual = !aad && stages >= 4 && 2 * nkb <= stages;
   }
   p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
+  // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring
+  if (!aad && out.dtype == kBF16 && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
+      !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&
+      (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8))) &&
+      256 * p.BN <= stages * stage_bytes) {
+    static const int stg_mode = [] {
+      const char* e = getenv("GHOST_STG");  // A/B switch for profiling: GHOST_STG=0 turns the staged epilogue off
+      return e ? (atoi(e) != 0) : 1;
+    }();
+    p.stg = stg_mode;
+  }
 
   // ---- epilogue
   p.out = out.p;

@@ -32,7 +32,8 @@ __device__ unsigned long long g_igemm_prof[160][12];
 // launch timeline (tools/igemm_timeline.py): first CTA entry / last CTA exit of every igemm launch, by %globaltimer
 constexpr int kTlSlots = 8192;
 __device__ unsigned long long g_tl_t0[kTlSlots], g_tl_t1[kTlSlots];
-__device__ int g_tl_meta[kTlSlots][4];
+__device__ int g_tl_meta[kTlSlots][12];
+__device__ long long g_tl_cta0[8];  // CTA 0 of the running launch: entry clock, prologue end, issuer end, epilogue end
 __device__ unsigned int g_tl_seq, g_tl_done;
 #define PROF_BEGIN() long long pw0_ = 0, pw1_ = 0; const long long pt0_ = clock64()
 #define PROF_WAIT0(stmt) do { const long long a_ = clock64(); stmt; pw0_ += clock64() - a_; } while (0)
@@ -100,21 +101,10 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 }
 
 
-// `sp` != nullptr: per-channel parameters of this CTA's N tile staged in shared memory ([bias | slope | scale2 |
-// shift2] x 256 floats, column j of the tile at sp[j]); `rpre`: the residual row was fetched ahead into rq0/rq1.
-__device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
-                                                   long long o_pix, long long r_pix, const float* sp, int j,
-                                                   bool rpre, const uint4& rq0, const uint4& rq1) {
-          float f[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.splits > 1) {
-            float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (col0 + i < p.n_valid) atomicAdd(o + i, f[i]);
-            return;
-          }
+// acc + bias, first activation.  `sp` != nullptr: per-channel parameters of this CTA's N tile staged in shared
+// memory ([bias | slope | scale2 | shift2] x 256 floats, column j of the tile at sp[j]).
+__device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (&f)[16], int col0, const float* sp,
+                                                   int j) {
           if (p.bias) {
             if (sp) {
 #pragma unroll
@@ -148,12 +138,27 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
 #pragma unroll
             for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.f);
           }
+}
+
+__device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
+                                                   long long o_pix, long long r_pix, const float* sp, int j) {
+          float f[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+          if (p.splits > 1) {
+            float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (col0 + i < p.n_valid) atomicAdd(o + i, f[i]);
+            return;
+          }
+          linear_bias_act_16(p, f, col0, sp, j);
           const bool full16 = (col0 + 16 <= p.n_valid);
           if (p.res) {
             const __nv_bfloat16* rp = p.res + r_pix + col0;
             if (full16) {
-              const uint4 q0 = rpre ? rq0 : __ldg(reinterpret_cast<const uint4*>(rp));
-              const uint4 q1 = rpre ? rq1 : __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+              const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
+              const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
               const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -310,6 +315,7 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
     }
     if (par == 0) PROF_END(0, threadIdx.x & 31);
 #ifdef GHOST_IGEMM_PROF
+    if (par == 0 && blockIdx.x == 0 && blockIdx.y == 0 && (threadIdx.x & 31) == 0) g_tl_cta0[2] = clock64();
     if (par == 0 && blockIdx.x == 0 && blockIdx.y == 0 && (threadIdx.x & 31) == 0) {
       const int cfg[8] = {p.BN, p.stages, p.dual, num_kb, my_tiles, p.a_win, p.b_res, static_cast<int>(gridDim.x)};
       for (int i = 0; i < 8; ++i) g_igemm_prof[159][i] = cfg[i];
@@ -338,6 +344,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cta_ns0));
   const unsigned tl_seq = *reinterpret_cast<volatile unsigned*>(&g_tl_seq) & (kTlSlots - 1);
   if (threadIdx.x == 0) atomicMin(&g_tl_t0[tl_seq], cta_ns0);
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[0] = cta_t0;
 #endif
 
   // 1024-byte aligned operand ring (swizzle atoms repeat every 1024 B)
@@ -414,6 +421,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int acc_stride = p.tmem_cols / p.sets;  // columns per accumulator stage
 #ifdef GHOST_IGEMM_PROF
   if (threadIdx.x == 0 && blockIdx.x < 160 && blockIdx.y == 0) g_igemm_prof[blockIdx.x][9] = clock64() - cta_t0;
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[1] = clock64();
 #endif
 
   if (warp == 0) {
@@ -556,6 +564,14 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     const int rw = r % p.bw;
     if (p.mode == kModeLinear) {
       // all 16 warps share every tile: warp ew takes a quarter of its columns
+      // Staged output (p.stg) for the LAST tile of the CTA, whose epilogue nothing overlaps: once that tile's
+      // accumulator is complete the operand ring is idle, so every warp parks its 32 rows x wcols there (rows of
+      // P 16-byte pieces, piece q of row r at slot q ^ stg_key(r): bank-conflict free) and moves whole row
+      // segments to / from global memory - 4-8 cache lines per instruction instead of 32.
+      const int wcols = p.BN >> 2, rowb = wcols * 2, P = rowb >> 4, lgP = 31 - __clz(P);
+      uint8_t* wst = ring + (warp - kIgemmEpiWarp0) * (32 * rowb);
+      const int rb_row0 = lane >> lgP, rb_piece = lane & (P - 1), rb_step = 32 >> lgP;
+      auto stg_key = [&](int row) { return ((row * rowb) >> 7) & (P - 1); };
       int it = 0;
       TileWalk walk;
       walk.init(p, blockIdx.x, gridDim.x);
@@ -569,21 +585,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
         const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
-        // the residual rows of this warp's columns are fetched before the accumulator is ready
-        // (two 16-column chunks ahead, the later ones while the earlier are being processed)
-        uint4 rq[4];
-        const bool rpre = p.res != nullptr && p.splits == 1;
-        if (rpre) {
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            const int col0 = t.nt * p.BN + (ch0 + c) * 16;
-            if (ch0 + c < ch1 && valid && col0 + 16 <= p.n_valid) {
-              const uint4* rp = reinterpret_cast<const uint4*>(p.res + r_pix + col0);
-              rq[2 * c] = __ldg(rp);
-              rq[2 * c + 1] = __ldg(rp + 1);
-            }
-          }
-        }
+        const int colw = t.nt * p.BN + ew * wcols;  // staged path: first column of this warp
+        const bool cols_on = colw < p.n_valid;      // (n_valid is a multiple of wcols there)
+        const bool use_stg = p.stg && tile + static_cast<int>(gridDim.x) >= tiles_total;
 #ifdef GHOST_IGEMM_PROF
         const long long ew0_ = clock64();
 #endif
@@ -595,6 +599,112 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         }
 #endif
         tc_fence_after();
+#ifdef GHOST_IGEMM_PROF
+        if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[4] = clock64();
+#endif
+        if (use_stg) {
+          if (p.res != nullptr) {
+            // residual rows of this warp's piece of the tile, as whole row segments
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (i < P) {  // warp-uniform
+                const int row = i * rb_step + rb_row0;
+                const long long rp_row = __shfl_sync(0xffffffffu, r_pix, row);
+                const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
+                if (v_row && cols_on)
+                  *reinterpret_cast<uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4)) =
+                      __ldg(reinterpret_cast<const uint4*>(p.res + rp_row + colw + rb_piece * 8));
+              }
+            }
+            __syncwarp();
+          }
+          uint8_t* my_row = wst + lane * rowb;
+          const int my_key = stg_key(lane);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (c * 16 < wcols) {  // warp-uniform
+              const int j = ew * wcols + c * 16;
+              uint32_t v[16];
+              __syncwarp();
+              tmem_ld16(t_addr + j, v);
+              tmem_ld_wait();
+              if (valid && cols_on) {
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
+                uint4* s0 = reinterpret_cast<uint4*>(my_row + (((2 * c) ^ my_key) << 4));
+                uint4* s1 = reinterpret_cast<uint4*>(my_row + (((2 * c + 1) ^ my_key) << 4));
+                if (p.res) {
+                  const uint4 q0 = *s0, q1 = *s1;
+                  const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    f[2 * i] += bf16lo(qq[i]);
+                    f[2 * i + 1] += bf16hi(qq[i]);
+                  }
+                }
+                if (p.act2 == kAct2Tanh) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
+                }
+                uint4 o0, o1;
+                o0.x = pack_bf16(f[0], f[1]);
+                o0.y = pack_bf16(f[2], f[3]);
+                o0.z = pack_bf16(f[4], f[5]);
+                o0.w = pack_bf16(f[6], f[7]);
+                o1.x = pack_bf16(f[8], f[9]);
+                o1.y = pack_bf16(f[10], f[11]);
+                o1.z = pack_bf16(f[12], f[13]);
+                o1.w = pack_bf16(f[14], f[15]);
+                *s0 = o0;
+                *s1 = o1;
+              }
+            }
+          }
+          // the accumulator stage goes back to the MMA warp before the global stores
+          tc_fence_before();
+          __syncwarp();
+#ifdef GHOST_IGEMM_PROF
+          if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[5] = clock64();
+#endif
+          if (lane == 0) mbar_arrive(&tempty_bar[as]);
+          const int jt = ew * wcols + rb_piece * 8;  // tile column of this lane's 8 channels
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (i >= P) break;  // warp-uniform
+            const int row = i * rb_step + rb_row0;
+            const long long op_row = __shfl_sync(0xffffffffu, o_pix, row);
+            const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
+            if (v_row && cols_on) {
+              const uint4 q = *reinterpret_cast<const uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4));
+              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + op_row + colw + rb_piece * 8) = q;
+              if (p.out2) {
+                // second output from the value as stored (rounded to bf16), e.g. the next block's bn1
+                float4 sc0, sc1, sh0, sh1;
+                if (staged) {
+                  sc0 = *reinterpret_cast<const float4*>(eparm + 512 + jt);
+                  sc1 = *reinterpret_cast<const float4*>(eparm + 512 + jt + 4);
+                  sh0 = *reinterpret_cast<const float4*>(eparm + 768 + jt);
+                  sh1 = *reinterpret_cast<const float4*>(eparm + 768 + jt + 4);
+                } else {
+                  const int cg = colw + rb_piece * 8;
+                  sc0 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg));
+                  sc1 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg) + 1);
+                  sh0 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg));
+                  sh1 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg) + 1);
+                }
+                uint4 o2;
+                o2.x = pack_bf16(fmaf(bf16lo(q.x), sc0.x, sh0.x), fmaf(bf16hi(q.x), sc0.y, sh0.y));
+                o2.y = pack_bf16(fmaf(bf16lo(q.y), sc0.z, sh0.z), fmaf(bf16hi(q.y), sc0.w, sh0.w));
+                o2.z = pack_bf16(fmaf(bf16lo(q.z), sc1.x, sh1.x), fmaf(bf16hi(q.z), sc1.y, sh1.y));
+                o2.w = pack_bf16(fmaf(bf16lo(q.w), sc1.z, sh1.z), fmaf(bf16hi(q.w), sc1.w, sh1.w));
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out2) + op_row + colw + rb_piece * 8) = o2;
+              }
+            }
+          }
+          continue;
+        }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           if (ch0 + c < ch1) {  // warp-uniform
@@ -604,14 +714,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             tmem_ld16(t_addr + j, v);
             tmem_ld_wait();
             const int col0 = t.nt * p.BN + j;
-            if (valid && col0 < p.n_valid)
-              linear_epilogue_16(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j, rpre, rq[2 * (c & 1)],
-                                 rq[2 * (c & 1) + 1]);
-            if (c < 2 && rpre && ch0 + c + 2 < ch1 && valid && col0 + 48 <= p.n_valid) {
-              const uint4* rp = reinterpret_cast<const uint4*>(p.res + r_pix + col0 + 32);
-              rq[2 * c] = __ldg(rp);
-              rq[2 * c + 1] = __ldg(rp + 1);
-            }
+            if (valid && col0 < p.n_valid) linear_epilogue_16(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
           }
         }
         // hand the accumulator stage back to the MMA warp
@@ -733,6 +836,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 #ifdef GHOST_IGEMM_PROF
   if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x < 160 && blockIdx.y == 0)
     g_igemm_prof[blockIdx.x][10] = clock64() - cta_t0;  // epilogue done
+  if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[3] = clock64();
 #endif
   tc_fence_before();
   __syncthreads();
@@ -752,6 +856,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       g_tl_meta[tl_seq][1] = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
       g_tl_meta[tl_seq][2] = (p.a_win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap / p.splits) * (p.kc == 64 ? 1 : -1);
       g_tl_meta[tl_seq][3] = gridDim.x * 10 + p.a_win;
+      g_tl_meta[tl_seq][4] = static_cast<int>(g_tl_cta0[1] - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][5] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[2]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][6] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[3]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][7] = static_cast<int>(clock64() - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][8] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[4]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][9] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[5]) - g_tl_cta0[0]);
     }
     __threadfence();
     if (atomicAdd(&g_tl_done, 1u) == gridDim.x * gridDim.y - 1) {
@@ -812,6 +922,9 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
   if (p.b_res && (p.tiles_n != 1 || p.kc != 64 || p.splits != 1)) return "igemm: resident weights need one N tile";
+  if (p.stg && (p.mode != kModeLinear || p.out_f32 || p.splits != 1 || (p.BN != 128 && p.BN != 256) ||
+                p.n_valid % (p.BN >> 2)))
+    return "igemm: staged output needs a bf16 linear epilogue and N tiles of 128 or 256 whole warp quarters";
   const int smem = igemm_smem_bytes(p);
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;

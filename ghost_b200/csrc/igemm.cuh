@@ -51,6 +51,10 @@ struct alignas(64) IgemmParams {
   int dual;    // 1: two MMA issuer warps (even / odd tiles), each with its own half of the operand ring
   int a_win;   // 0 off, 1 on (the UMMA descriptor start address carries the row shift)
   int b_res;
+  // Linear mode, bf16 output, BN 128 / 256: 1 = for the last tile of a CTA every epilogue warp stages its 32 rows x
+  // BN/4 columns in the (then idle) operand ring and moves whole row segments to / from global memory (residual in,
+  // out and out2 out): the one epilogue that no main loop hides.
+  int stg;
 
   // ---- epilogue (linear):  v = act2(act1(acc + bias) + res)
   int mode;

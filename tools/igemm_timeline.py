@@ -35,7 +35,7 @@ def timeline(label, fn):
     torch.cuda.synchronize()
     t0 = np.zeros(SLOTS, dtype=np.uint64)
     t1 = np.zeros(SLOTS, dtype=np.uint64)
-    meta = np.zeros((SLOTS, 4), dtype=np.int32)
+    meta = np.zeros((SLOTS, 12), dtype=np.int32)
     n = lib.ghost_prof_timeline_read(C.c_void_p(t0.ctypes.data), C.c_void_p(t1.ctypes.data), C.c_void_p(meta.ctypes.data))
     t0 = t0[:n].astype(np.int64)
     t1 = t1[:n].astype(np.int64)
@@ -44,11 +44,12 @@ def timeline(label, fn):
     print("== %s: %d igemm launches, forward %.3f ms by events, first entry -> last exit %.3f ms, sum of igemm durations "
           "%.3f ms, sum of gaps %.3f ms" % (label, n, e0.elapsed_time(e1), (t1[-1] - t0[0]) / 1e6, dur.sum() / 1e3,
                                              gap.sum() / 1e3))
-    print("   idx  mode  BN  tiles  num_kb  grid win   dur_us  gap_after_us")
+    print("   idx  mode  BN  tiles  num_kb  grid win   dur_us  gap_after_us | CTA 0 cycles: prologue, issuer done, epilogue done, exit; last tile: accumulator ready, staged")
     for i in range(n):
         m = meta[i]
-        print("   %3d  %4d %3d %6d %6d %5d %3d %8.2f %8.2f" % (i, m[0] // 1000, m[0] % 1000, m[1], m[2], m[3] // 10,
-                                                               m[3] % 10, dur[i], gap[i]))
+        print("   %3d  %4d %3d %6d %6d %5d %3d %8.2f %8.2f | %6d %7d %7d %7d ; %7d %7d" % (
+            i, m[0] // 1000, m[0] % 1000, m[1], m[2], m[3] // 10, m[3] % 10, dur[i], gap[i], m[4], m[5], m[6], m[7], m[8],
+            m[9]))
 
 
 arc = gb.iresnet100().cuda().bfloat16().eval()
