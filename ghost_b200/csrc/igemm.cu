@@ -19,6 +19,8 @@
 // network/AEI_Net.py:19-41,101 and network/AADLayer.py:13-18,67-74; the AAD
 // epilogue implements AADLayer.forward (network/AADLayer.py:20-38) + the ReLU
 // that always follows it (network/AADLayer.py:62,70).
+#include <cstdlib>
+
 #include "igemm.cuh"
 #include "ptx.cuh"
 
@@ -373,23 +375,24 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   const int kb0 = blockIdx.y * num_kb;
   const int tiles_total = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
 
-  if (threadIdx.x == 0) {
-    abort_flag = 0;
-    for (int i = 0; i < p.stages; ++i) {
-      mbar_init(&full_bar[i], p.b_res ? 1 : 2);  // one arrive.expect_tx per operand producer
-      mbar_init(&empty_bar[i], 1);
-    }
-    // linear mode: all 16 epilogue warps share every tile; AAD mode: 4 warps per 64-channel box of a tile
-    const int epi_arrivals = p.mode == kModeAAD ? 4 * hbox : kIgemmEpiWarps;
-    for (int i = 0; i < 4; ++i) {
-      mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], epi_arrivals);
-    }
-    mbar_init(&bfull_bar, 1);
-    for (int i = 0; i < 8; ++i) {
-      mbar_init(&hfull_bar[i], 1);
-      mbar_init(&hempty_bar[i], epi_arrivals);
-    }
+  // Prologue in two steps, so that the TMA producers do not wait for the TMEM allocation and the parameter staging:
+  // warp 1 initialises the mbarriers and releases the producers (named barrier 9), then allocates TMEM while the
+  // epilogue warps stage their parameters; issuers and epilogue meet on named barrier 10.
+  if (warp == 1) {
+    // one mbarrier per lane and instruction (linear mode: all 16 epilogue warps share every tile; AAD mode: 4 warps
+    // per 64-channel box of a tile)
+    const uint32_t epi_arrivals = p.mode == kModeAAD ? 4 * hbox : kIgemmEpiWarps;
+    if (lane == 0) abort_flag = 0;
+    uint64_t* bar = nullptr;
+    uint32_t cnt = 1;
+    if (lane < 8) bar = &full_bar[lane], cnt = p.b_res ? 1 : 2;  // one arrive.expect_tx per operand producer
+    else if (lane < 16) bar = &empty_bar[lane - 8];
+    else if (lane < 20) bar = &tfull_bar[lane - 16];
+    else if (lane < 24) bar = &tempty_bar[lane - 20], cnt = epi_arrivals;
+    else if (lane == 24) bar = &bfull_bar;
+    if (bar) mbar_init(bar, cnt);
+    if (lane < 8) mbar_init(&hfull_bar[lane], 1);
+    else if (lane < 16) mbar_init(&hempty_bar[lane - 8], epi_arrivals);
     fence_mbar_init();
   }
   if (warp == 0 && lane == 0) {
@@ -400,7 +403,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       prefetch_tmap(&p.tmO);
     }
   }
-  if (warp == 1) tmem_alloc(&tmem_base_smem, p.tmem_cols);
+  if (warp == 1) {
+    __syncwarp();
+    named_bar_arrive(9, 96);
+    tmem_alloc(&tmem_base_smem, p.tmem_cols);
+  }
   // linear mode, one N tile: the per-channel epilogue parameters go to shared memory once (mexch is free in this
   // mode), so the epilogue of a tile never waits on global memory for them
   float* eparm = &mexch[0][0][0];
@@ -414,11 +421,21 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       eparm[768 + i] = (in && p.out2) ? __ldg(p.shift2 + i) : 0.f;
     }
   }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
+  uint32_t tmem_base = 0;
+  if (warp == 0 || warp == 3) {
+    named_bar_sync(9, 96);
+  } else {
+    tc_fence_before();
+    named_bar_sync(10, kIgemmThreads - 64);
+    tc_fence_after();
+    tmem_base = tmem_base_smem;
+  }
   const int acc_stride = p.tmem_cols / p.sets;  // columns per accumulator stage
+  // Programmatic dependent launch: everything above touched only kernel parameters and static weights, so it may
+  // overlap the tail of the previous kernel in the stream; the next kernel may start its own prologue from here on.
+  // Every role that reads activations or writes outputs waits for the previous grid first (the weight producer and
+  // the MMA issuers touch neither).
+  grid_dep_launch();
 #ifdef GHOST_IGEMM_PROF
   if (threadIdx.x == 0 && blockIdx.x < 160 && blockIdx.y == 0) g_igemm_prof[blockIdx.x][9] = clock64() - cta_t0;
   if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[1] = clock64();
@@ -438,6 +455,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         tma_load_2d(bres + i * b_tile_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * p.kc, 0);
     }
     __syncwarp();
+    grid_dep_wait();
     TileWalk walk;
     walk.init(p, blockIdx.x, gridDim.x);
     int hs = 0;
@@ -556,6 +574,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
                  row_bytes, b_tile_bytes, a_stage_bytes, stage_bytes, num_kb, tiles_total, acc_stride);
   } else {
     // ============================== epilogue ==================================
+    grid_dep_wait();
     const int lg = warp & 3;                       // TMEM lane group this warp may read
     const int ew = (warp - kIgemmEpiWarp0) >> 2;   // 0..3: which of the four warps of that lane group
     const int r = lg * 32 + lane;                  // GEMM row inside the tile
@@ -943,8 +962,24 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
     if (gx > tiles) gx = tiles;
   }
   dim3 grid(gx, p.splits, 1);
-  igemm_kernel<<<grid, kIgemmThreads, smem, stream>>>(p);
-  cudaError_t e = cudaGetLastError();
+  // programmatic dependent launch: the prologue of this launch may overlap the tail of the previous kernel in the
+  // stream (the kernel waits for it before touching activations); GHOST_PDL=0 falls back to plain serialisation
+  static const int pdl = [] {
+    const char* ev = getenv("GHOST_PDL");
+    return ev ? (atoi(ev) != 0) : 1;
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kIgemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = static_cast<size_t>(smem);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, igemm_kernel, p);
+  if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }
 
