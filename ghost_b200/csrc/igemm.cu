@@ -31,6 +31,7 @@ using namespace ptx;
 // Stall accounting for tools/igemm_prof.py (make PROF=1): cycles each role spends waiting on its barriers.
 #ifdef GHOST_IGEMM_PROF
 __device__ unsigned long long g_igemm_prof[160][12];
+__device__ unsigned long long g_aad_prof[160][8];  // AAD epilogue, first warp: waits h / pair / acc, blend, store, total, tiles
 // launch timeline (tools/igemm_timeline.py): first CTA entry / last CTA exit of every igemm launch, by %globaltimer
 constexpr int kTlSlots = 8192;
 __device__ unsigned long long g_tl_t0[kTlSlots], g_tl_t1[kTlSlots];
@@ -753,9 +754,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       const bool h2 = p.h_bufs == 2 * sets;  // two h slots per group
       const int sw = r & 7;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + set * acc_stride + box * 64;
+      const bool quad = p.bn == 1;              // all rows of a tile in one image: parameters are per thread
+      const int rq = lane >> 2, cq = lane & 3;  // quad mapping: rows rq + 8k of the piece, channel pairs 8i + 2cq
       TileWalk walk;
       walk.init(p, blockIdx.x + set * gridDim.x, gridDim.x * sets);
       int k = 0;  // tiles this group has served
+      int pend = -1;  // h slot whose TMA store has been issued but not yet waited for
       for (int tile = blockIdx.x + set * gridDim.x; tile < tiles_total; tile += gridDim.x * sets, ++k, walk.next(p)) {
         const TileCoord t = walk.t;
         const int hs = h2 ? set + (k & 1) * sets : set;
@@ -766,8 +770,67 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         const int c_base = t.nt * cn + box * 64;
         const int nc = min(n, p.Nimg - 1);  // rows outside the tensor still index valid parameters
         uint8_t* hrow = hbuf + hs * htile_bytes + box * 16384 + r * 128;
+        uint8_t* hq = hbuf + hs * htile_bytes + box * 16384 + (lg * 32 + rq) * 128 + 4 * cq;  // + 1024k: row rq + 8k
+        const int nq = min(t.tn, p.Nimg - 1);  // quad mapping: the image of the whole tile
+#ifdef GHOST_IGEMM_PROF
+        const long long q0_ = clock64();
+#endif
         if (!__all_sync(0xffffffffu, mbar_wait(&hfull_bar[hs], hphase, &abort_flag))) break;
+#ifdef GHOST_IGEMM_PROF
+        const long long q1_ = clock64();
+        long long qb_ = 0;
+#endif
         float m = 0.f;
+        float m4[4] = {0.f, 0.f, 0.f, 0.f};  // quad mapping: mask of rows rq, rq+8, rq+16, rq+24 of this warp's piece
+        if (quad) {
+          if (p.mask) {
+            if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) m4[kk] = __shfl_sync(0xffffffffu, m, rq + 8 * kk);
+          } else {
+            // every thread sums its 16 channels of its four rows, the four threads of a row add up by shuffle
+            const float* wrow = p.wh_fold + static_cast<long long>(nq) * p.c_x + box * 64 + 2 * cq;
+            float a4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float2 w = __ldg(reinterpret_cast<const float2*>(wrow + 8 * i));
+              const uint8_t* hp = hq + ((i ^ rq) << 4);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {
+                const uint32_t hv = *reinterpret_cast<const uint32_t*>(hp + kk * 1024);
+                a4[kk] += bf16lo(hv) * w.x + bf16hi(hv) * w.y;
+              }
+            }
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              a4[kk] += __shfl_xor_sync(0xffffffffu, a4[kk], 1);
+              a4[kk] += __shfl_xor_sync(0xffffffffu, a4[kk], 2);
+            }
+            if (hbox == 2) {
+              // the other 64 channels of these rows belong to the partner warp: swap halves, add in box order
+              float(*ex)[128] = mexch[k & 1];
+              if (cq == 0) {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) ex[set * 2 + box][lg * 32 + rq + 8 * kk] = a4[kk];
+              }
+#ifdef GHOST_IGEMM_PROF
+              const long long b0_ = clock64();
+#endif
+              named_bar_sync(1 + set * 4 + lg, 64);
+#ifdef GHOST_IGEMM_PROF
+              qb_ = clock64() - b0_;
+#endif
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {
+                const float other = ex[set * 2 + (box ^ 1)][lg * 32 + rq + 8 * kk];
+                a4[kk] = box == 0 ? a4[kk] + other : other + a4[kk];
+              }
+            }
+            const float bhf = __ldg(p.bh_fold + nq);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) m4[kk] = 1.f / (1.f + __expf(-(a4[kk] + bhf)));
+          }
+        } else
         if (p.mask) {
           if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
         } else {
@@ -788,14 +851,74 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             // the other 64 channels of this row belong to the partner warp: swap halves, add in box order
             float(*ex)[128] = mexch[k & 1];
             ex[set * 2 + box][r] = acc;
+#ifdef GHOST_IGEMM_PROF
+            const long long b0_ = clock64();
+#endif
             named_bar_sync(1 + set * 4 + lg, 64);
+#ifdef GHOST_IGEMM_PROF
+            qb_ = clock64() - b0_;
+#endif
             const float other = ex[set * 2 + (box ^ 1)][r];
             acc = box == 0 ? acc + other : other + acc;
           }
           m = 1.f / (1.f + __expf(-(acc + __ldg(p.bh_fold + nc))));
         }
+        if (pend >= 0) {
+          if (lane == 0) {
+            bulk_wait_read<0>();
+            mbar_arrive(&hempty_bar[pend]);
+          }
+          pend = -1;
+        }
+#ifdef GHOST_IGEMM_PROF
+        const long long q2_ = clock64();
+#endif
         if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[set], aphase, &abort_flag))) break;
+#ifdef GHOST_IGEMM_PROF
+        const long long q3_ = clock64();
+#endif
         tc_fence_after();
+        if (quad) {
+          // Quad mapping (tiles of one image): tcgen05.ld.16x256b hands thread t the channel pairs 8i + 2(t%4) of
+          // rows t/4 + {0, 8, 16, 24}, so the per-channel parameters are loaded once per thread for four rows and
+          // spread over the lanes - the row-per-lane mapping below re-reads every parameter in all 32 lanes, which
+          // saturates the load/store writeback path.
+          const float4* parq = p.ncpar + static_cast<long long>(nq) * p.c_x + c_base + 2 * cq;
+          const float* bgq = p.bias + t.nt * p.BN + box * 64 + 2 * cq;
+          const float* bbq = bgq + cn;
+#pragma unroll 2
+          for (int i = 0; i < 8; ++i) {
+            uint32_t g0[4], g1[4], b0[4], b1[4];
+            __syncwarp();
+            tmem_ld_16x256b(t_addr + 8 * i, g0);
+            tmem_ld_16x256b(t_addr + (16u << 16) + 8 * i, g1);
+            tmem_ld_16x256b(t_addr + cn + 8 * i, b0);
+            tmem_ld_16x256b(t_addr + (16u << 16) + cn + 8 * i, b1);
+            uint8_t* hp = hq + ((i ^ rq) << 4);
+            uint32_t hv[4];
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) hv[kk] = *reinterpret_cast<const uint32_t*>(hp + kk * 1024);
+            const float4 p0 = __ldg(parq + 8 * i);      // {rstd0, rstd1, shift0, shift1}
+            const float4 p1 = __ldg(parq + 8 * i + 1);  // {gamma_id0, gamma_id1, beta_id0, beta_id1}
+            const float2 bgv = __ldg(reinterpret_cast<const float2*>(bgq + 8 * i));
+            const float2 bbv = __ldg(reinterpret_cast<const float2*>(bbq + 8 * i));
+            tmem_ld_wait();
+            const uint32_t gg[4][2] = {{g0[0], g0[1]}, {g0[2], g0[3]}, {g1[0], g1[1]}, {g1[2], g1[3]}};
+            const uint32_t bq[4][2] = {{b0[0], b0[1]}, {b0[2], b0[3]}, {b1[0], b1[1]}, {b1[2], b1[3]}};
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              const float2 x = make_float2(bf16lo(hv[kk]), bf16hi(hv[kk]));
+              const float2 hn = fma2(x, make_float2(p0.x, p0.y), make_float2(p0.z, p0.w));
+              const float2 ga = add2(make_float2(__uint_as_float(gg[kk][0]), __uint_as_float(gg[kk][1])), bgv);
+              const float2 be = add2(make_float2(__uint_as_float(bq[kk][0]), __uint_as_float(bq[kk][1])), bbv);
+              const float2 A = fma2(ga, hn, be);
+              const float2 I = fma2(make_float2(p1.x, p1.y), hn, make_float2(p1.z, p1.w));
+              const float2 r2 = fma2(make_float2(m4[kk], m4[kk]), sub2(I, A), A);
+              // in place, with the ReLU that always follows the layer (AADLayer.py:62,70)
+              *reinterpret_cast<uint32_t*>(hp + kk * 1024) = pack_bf16_relu(r2.x, r2.y);
+            }
+          }
+        } else {
         const float4* par = p.ncpar + static_cast<long long>(nc) * p.c_x + c_base;
         const float* bg = p.bias + t.nt * p.BN + box * 64;
         const float* bb = bg + cn;
@@ -834,18 +957,44 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           }
           *hp = make_uint4(o[0], o[1], o[2], o[3]);  // in place: this thread alone reads and writes this chunk
         }
+        }
         fence_proxy_async();  // generic-proxy writes of the blended rows -> visible to the TMA (async proxy)
         tc_fence_before();
         __syncwarp();
+#ifdef GHOST_IGEMM_PROF
+        const long long q4_ = clock64();
+#endif
         if (lane == 0) {
           mbar_arrive(&tempty_bar[set]);  // accumulator stage back to the MMA warp
           // lane 0 holds the first of this warp's 32 rows: its pixel is the origin of the store box
           if (r < rows_used) tma_store_4d(&p.tmO, hrow, c_base, ow, oh, n);
           bulk_commit();
-          bulk_wait_read<0>();            // the store has read the rows: the h slot may be refilled
-          mbar_arrive(&hempty_bar[hs]);
+          if (!h2) {
+            bulk_wait_read<0>();  // the store has read the rows: the h slot may be refilled
+            mbar_arrive(&hempty_bar[hs]);
+          }
         }
+        // two h slots per group: the slot is handed back while the next tile's mask is computed, so nobody waits
+        // for the store to drain
+        pend = h2 ? hs : -1;
         __syncwarp();
+#ifdef GHOST_IGEMM_PROF
+        if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x < 160) {
+          unsigned long long* a = g_aad_prof[blockIdx.x];
+          if (k == 0) a[0] = a[1] = a[2] = a[3] = a[4] = 0ull, a[7] = q0_;
+          a[0] += q1_ - q0_;
+          a[1] += qb_;
+          a[2] += q3_ - q2_;
+          a[3] += (q4_ - q3_) + (q2_ - q1_) - qb_;
+          a[4] += clock64() - q4_;
+          a[5] = clock64() - a[7];
+          a[6] = k + 1;
+        }
+#endif
+      }
+      if (pend >= 0 && lane == 0) {
+        bulk_wait_read<0>();
+        mbar_arrive(&hempty_bar[pend]);
       }
       if (lane == 0) bulk_wait<0>();  // outstanding TMA stores
     }
@@ -1004,6 +1153,10 @@ extern "C" int ghost_prof_timeline_read(unsigned long long* t0, unsigned long lo
   cudaMemcpyFromSymbol(t1, g_tl_t1, sizeof(g_tl_t1));
   cudaMemcpyFromSymbol(meta, g_tl_meta, sizeof(g_tl_meta));
   return static_cast<int>(n);
+}
+extern "C" int ghost_prof_aad_read(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  return static_cast<int>(cudaMemcpyFromSymbol(out, g_aad_prof, sizeof(g_aad_prof)));
 }
 extern "C" int ghost_prof_igemm_read(unsigned long long* out) {
   cudaDeviceSynchronize();

@@ -189,6 +189,14 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[8]) {
                : "r"(taddr)
                : "memory");
 }
+// 16 lanes x 8 consecutive fp32 columns: thread t gets columns 2(t%4), 2(t%4)+1 of lane base + t/4 (v[0], v[1]) and of
+// lane base + t/4 + 8 (v[2], v[3]) - the layout of an m16n8 accumulator fragment (checked by tools/tmem_layout.cu).
+__device__ __forceinline__ void tmem_ld_16x256b(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr)
+               : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------- packed fp32 (Blackwell FFMA2 / FADD2)
