@@ -136,6 +136,12 @@ def init_tensor(shape, kind, gen):
         return torch.full(shape, 0.25)
     if kind == "fc":
         return torch.randn(shape, generator=gen) * math.sqrt(1.0 / shape[1])
+    if kind == "kaiming_uniform":  # nn.Conv2d default (kaiming_uniform_, a=sqrt(5)) = U(+-1/sqrt(fan_in))
+        fi, _ = _fans(shape)
+        return (torch.rand(shape, generator=gen) * 2 - 1) / math.sqrt(fi)
+    if kind == "unit":  # torch spectral_norm: normalize(randn)
+        v = torch.randn(shape, generator=gen)
+        return v / v.norm().clamp_min(1e-12)
     raise ValueError(kind)
 
 
@@ -160,4 +166,77 @@ def perturb_(sd, seed=1):
                 v.copy_(torch.randn(v.shape, generator=gen) * 0.05)
             else:
                 v.copy_(torch.randn(v.shape, generator=gen) * 0.1)
+    return sd
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# pix2pix super-resolution generator: LIPSPADEGenerator with TestOptions (models/config_sr.py:3-29: ngf=48,
+# norm_G='spectralspadesyncbatch3x3', num_upsampling_layers='normal', semantic_nc=3).  Key names follow
+# models/networks/generator.py:27-63 (SPADEGenerator), :353-400 (LIPEncoder, LIPSPADEGenerator),
+# models/networks/architecture.py:21-50 (SPADEResnetBlock, torch spectral_norm -> weight_orig / weight_u / weight_v),
+# models/networks/normalization.py:63-92 (SPADE).
+SR_NGF = 48
+SR_ENC_C = [48, 96, 192, 384, 768, 768]           # LIPEncoder widths: ngf * min(2^i, 16)
+# name, fin, fout of the seven SPADEResnetBlocks in forward order (generator.py:40-55)
+SR_BLOCKS = [("head_0", 768, 768), ("G_middle_0", 768, 768), ("G_middle_1", 768, 768),
+             ("ups.0", 768, 384), ("ups.1", 384, 192), ("ups.2", 192, 96), ("ups.3", 96, 48)]
+
+
+def sr_spec():
+    """OrderedDict key -> (shape, init kind) of LIPSPADEGenerator(TestOptions) in the reference's state_dict order."""
+    spec = OrderedDict()
+    nf = SR_NGF
+    spec["fc.weight"] = ((16 * nf, 3, 3, 3), "xavier_conv")       # unused by LIPSPADEGenerator.forward (encode is overridden)
+    spec["fc.bias"] = ((16 * nf,), "bias:27")
+
+    def spade(prefix, norm_nc):
+        nh = 128 if norm_nc > 128 else norm_nc
+        spec[prefix + ".param_free_norm.running_mean"] = ((norm_nc,), "zeros")
+        spec[prefix + ".param_free_norm.running_var"] = ((norm_nc,), "ones")
+        spec[prefix + ".param_free_norm.num_batches_tracked"] = ((), "count")
+        spec[prefix + ".mlp_shared.0.weight"] = ((nh, 3, 3, 3), "xavier_conv")
+        spec[prefix + ".mlp_shared.0.bias"] = ((nh,), "bias:27")
+        spec[prefix + ".mlp_gamma.weight"] = ((norm_nc, nh, 3, 3), "xavier_conv")
+        spec[prefix + ".mlp_beta.weight"] = ((norm_nc, nh, 3, 3), "xavier_conv")
+
+    def sn_conv(prefix, co, ci, k, bias):
+        if bias:
+            spec[prefix + ".bias"] = ((co,), "bias:%d" % (ci * k * k))
+        spec[prefix + ".weight_orig"] = ((co, ci, k, k), "kaiming_uniform")
+        spec[prefix + ".weight_u"] = ((co,), "unit")
+        spec[prefix + ".weight_v"] = ((ci * k * k,), "unit")
+
+    for name, fin, fout in SR_BLOCKS:
+        fmid = min(fin, fout)
+        sn_conv(name + ".conv_0", fmid, fin, 3, True)
+        sn_conv(name + ".conv_1", fout, fmid, 3, True)
+        if fin != fout:
+            sn_conv(name + ".conv_s", fout, fin, 1, False)
+        spade(name + ".norm_0", fin)
+        spade(name + ".norm_1", fmid)
+        if fin != fout:
+            spade(name + ".norm_s", fin)
+    for i, c in enumerate([8 * nf, 4 * nf, 2 * nf, nf]):
+        spec["to_rgbs.%d.weight" % i] = ((3, c, 3, 3), "xavier_conv")
+        spec["to_rgbs.%d.bias" % i] = ((3,), "bias:%d" % (9 * c))
+    spec["lip_encoder.model.0.weight"] = ((nf, 3, 3, 3), "xavier_conv")
+    for i in range(5):
+        c, cn = SR_ENC_C[i], SR_ENC_C[i + 1]
+        spec["lip_encoder.model.%d.logit.0.weight" % (3 + 4 * i)] = ((c, c, 3, 3), "xavier_conv")
+        spec["lip_encoder.model.%d.logit.1.weight" % (3 + 4 * i)] = ((c,), "ones")
+        spec["lip_encoder.model.%d.logit.1.bias" % (3 + 4 * i)] = ((c,), "zeros")
+        spec["lip_encoder.model.%d.weight" % (4 + 4 * i)] = ((cn, c, 3, 3), "xavier_conv")
+        spec["lip_encoder.model.%d.bias" % (4 + 4 * i)] = ((cn,), "bias:%d" % (9 * c))
+    return spec
+
+
+def perturb_sr_(sd, seed=1):
+    """Parity-test weight set for the SR generator: non-trivial InstanceNorm affine parameters of the LIP gates
+    (identity at init, so the gate would otherwise be numerically invisible)."""
+    gen = torch.Generator().manual_seed(seed)
+    for k, v in sd.items():
+        if ".logit.1.weight" in k:
+            v.copy_(torch.rand(v.shape, generator=gen) + 0.5)
+        elif ".logit.1.bias" in k:
+            v.copy_(torch.randn(v.shape, generator=gen) * 0.3)
     return sd

@@ -139,9 +139,46 @@ def gen_paste():
         print(name, "roi", rec["roi"], "params", params, "changed px", int(diff.sum()))
 
 
+SR_CASES = [  # name, batch, perturbed LIP gates, number of consecutive forwards (spectral-norm state advances)
+    ("sr_b2_default", 2, False, 1),
+    ("sr_b3_perturbed_2calls", 3, True, 2),
+]
+
+
+def sr_case_inputs(name, B, perturbed):
+    sd = W.init_state_dict(W.sr_spec(), seed=0)
+    if perturbed:
+        W.perturb_sr_(sd, seed=1)
+    return sd, synth.crops_u8(B, seed=21)
+
+
+def gen_sr():
+    """LIPSPADEGenerator(TestOptions) of the reference, .train() as inference.py:48, fed like face_enhancement."""
+    from models.config_sr import TestOptions
+    from models.networks.generator import LIPSPADEGenerator
+    for name, B, pert, calls in SR_CASES:
+        sd, crops = sr_case_inputs(name, B, pert)
+        G = LIPSPADEGenerator(TestOptions())
+        G.load_state_dict(sd)
+        G.train()
+        x = torch.from_numpy(np.ascontiguousarray(crops[..., ::-1])).permute(0, 3, 1, 2).float().div(255)
+        with torch.no_grad():
+            for _ in range(calls):
+                y = G(x)
+        u8 = torch.clamp(y * 255, 0, 255).type(torch.uint8).permute(0, 2, 3, 1).numpy()[..., ::-1]
+        out = {"Y": y.numpy().astype(np.float16), "Y_absmean": np.float64(y.abs().mean()),
+               "Y_sample": y.numpy().reshape(-1)[::97][:8192].astype(np.float32), "u8_sha": sha(u8),
+               "crops_sha": sha(crops), "u_head0_conv0": G.head_0.conv_0.weight_u.numpy().copy(),
+               "u_ups3_convs": G.ups[3].conv_s.weight_u.numpy().copy()}
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), **out)
+        print(name, "Y mean|.|", float(out["Y_absmean"]))
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["aei", "paste"]
+    which = sys.argv[1:] or ["aei", "paste", "sr"]
+    if "sr" in which:
+        gen_sr()
     if "aei" in which:
         gen_aei()
     if "paste" in which:
