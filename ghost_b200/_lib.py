@@ -63,6 +63,10 @@ SIGNATURES = {
     "ghost_net_profile": (_i, [_vp, _i, _i, _i, _fp, C.POINTER(_d), C.POINTER(_d), C.POINTER(_i), C.c_char_p, _i,
                                C.POINTER(_i), _vp]),
     "ghost_net_debug_get": (_i, [_vp, _i, C.c_char_p, _vp, _i, C.POINTER(_i), _vp]),
+    "ghost_sr_create": (_i, [C.POINTER(_vp), _i]),
+    "ghost_sr_forward": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp]),
+    "ghost_sr_enhance_u8": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "ghost_sr_read_buffer": (_i, [_vp, C.c_char_p, _fp, _i, C.POINTER(_i), _vp]),
     "ghost_net_destroy": (None, [_vp]),
     "ghost_preproc_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ghost_postproc_u8": (_i, [_vp, _i, _vp, _i, _vp]),

@@ -647,3 +647,124 @@ def get_final_video(final_frames, crop_frames, full_frames, tfm_array, OUT_VIDEO
             vw.write(f)
         vw.release()
     return result
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# pix2pix super-resolution
+class LIPSPADEGenerator(_Net):
+    """Drop-in for models.networks.generator.LIPSPADEGenerator(TestOptions) (generator.py:390-400; options
+    models/config_sr.py:3-29) in the state the reference runs it in: `model.netG.train()` (inference.py:48), i.e.
+    batch statistics in every SPADE and one spectral-norm power iteration per forward.  `.float()` = fp32 CUDA-core
+    mode (the reference's own dtype for this network), `.bfloat16()` / `.half()` = tcgen05 mode."""
+
+    def __init__(self, opt=None, seed=0):
+        super().__init__(_w.sr_spec(), seed)
+        self.opt = opt
+        self.training = True
+
+    def train(self, mode=True):
+        if not mode:
+            return self.eval()
+        self.training = True
+        return self
+
+    def eval(self):
+        raise NotImplementedError(
+            "ghost_b200.LIPSPADEGenerator runs with train() semantics only, as the reference does (inference.py:48); "
+            "the running-statistics mode is not built")
+
+    def _create(self, lib, out, mode):
+        _lib.check(lib.ghost_sr_create(C.byref(out), mode))
+
+    def forward(self, input, seg=None):
+        if seg is not None and seg is not input:
+            raise NotImplementedError("separate segmentation input is not supported (the reference passes seg = input)")
+        _require_cuda(input, "input")
+        if input.dim() != 4 or tuple(input.shape[1:]) != (3, 256, 256):
+            raise ValueError("input must be [B,3,256,256], got %s" % (tuple(input.shape),))
+        if input.dtype not in (torch.float32, torch.float16, torch.bfloat16):
+            raise TypeError("input has unsupported dtype %s" % input.dtype)
+        x = input.contiguous()
+        B = x.shape[0]
+        lib = _lib.load()
+        with torch.cuda.device(x.device):
+            h = self._handle(x.device)
+            y = torch.empty((B, 3, 256, 256), dtype=self._dtype, device=x.device)
+            _lib.check(lib.ghost_sr_forward(h, _ptr(x), _DT[x.dtype], _ptr(y), _DT[self._dtype], B, _stream()))
+        return y
+
+    def enhance_u8(self, crops_bgr, out=None):
+        """One DataLoader batch of face_enhancement (video_processing.py:263-285) on the device:
+        uint8 BGR [B,256,256,3] -> uint8 BGR [B,256,256,3]."""
+        _require_cuda(crops_bgr, "crops_bgr")
+        if crops_bgr.dtype != torch.uint8 or crops_bgr.dim() != 4 or tuple(crops_bgr.shape[1:]) != (256, 256, 3):
+            raise ValueError("crops_bgr must be uint8 [B,256,256,3]")
+        crops_bgr = crops_bgr.contiguous()
+        B = crops_bgr.shape[0]
+        lib = _lib.load()
+        with torch.cuda.device(crops_bgr.device):
+            h = self._handle(crops_bgr.device)
+            if out is None:
+                out = torch.empty_like(crops_bgr)
+            _lib.check(lib.ghost_sr_enhance_u8(h, _ptr(crops_bgr), _ptr(out), B, _stream()))
+        return out
+
+    def state_dict(self):
+        """As the reference module: weight_u / weight_v hold the state after the forwards run so far."""
+        sd = super().state_dict()
+        if self._handles:
+            lib = _lib.load()
+            (dev_index, _), h = next(iter(self._handles.items()))
+            with torch.cuda.device(dev_index):
+                for k in sd:
+                    if k.endswith(".weight_u") or k.endswith(".weight_v"):
+                        buf = np.empty(sd[k].numel(), np.float32)
+                        n = C.c_int()
+                        _lib.check(lib.ghost_sr_read_buffer(h, k.encode(), buf.ctypes.data_as(C.POINTER(C.c_float)),
+                                                            buf.size, C.byref(n), _stream()))
+                        sd[k] = torch.from_numpy(buf.copy())
+        return sd
+
+
+class Pix2PixModel(object):
+    """Inference surface of models.pix2pix_model.Pix2PixModel (pix2pix_model.py:16-62): `.netG` and
+    `model(data, mode='inference2')`."""
+
+    def __init__(self, opt=None, seed=0):
+        self.opt = opt
+        self.netG = LIPSPADEGenerator(opt, seed=seed)
+
+    def load_state_dict(self, sd, strict=True):
+        self.netG.load_state_dict(sd, strict)
+        return self
+
+    def __call__(self, data, mode):
+        return self.forward(data, mode)
+
+    def forward(self, data, mode):
+        if mode != "inference2":
+            raise ValueError("|mode| is invalid")      # pix2pix_model.py:62 (only the inference branch is built)
+        x = data["label"]
+        if not x.is_cuda:
+            x = x.cuda()                               # preprocess_input (pix2pix_model.py:64-69)
+        return self.netG(x)
+
+
+def face_enhancement(final_frames, model, device=None):
+    """utils/inference/video_processing.py:263-285: every non-empty 256x256 BGR crop of each target's frame list goes
+    through the super-resolution generator in DataLoader order, batches of 20 (the crops of a batch share their
+    SPADE batch statistics, so the batching is part of the result)."""
+    netG = model.netG if hasattr(model, "netG") else model
+    dev = device or netG._device or torch.device("cuda", torch.cuda.current_device())
+    out_all = []
+    for frames in final_frames:
+        enhanced = list(frames)
+        idx = [i for i, x in enumerate(frames) if not isinstance(x, list)]
+        for b0 in range(0, len(idx), 20):
+            sel = idx[b0:b0 + 20]
+            batch = torch.from_numpy(np.stack([np.ascontiguousarray(frames[i]) for i in sel])).to(dev)
+            res = netG.enhance_u8(batch).cpu().numpy()
+            for j, i in enumerate(sel):
+                enhanced[i] = res[j]
+        out_all.append(enhanced)
+    return out_all

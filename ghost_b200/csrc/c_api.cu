@@ -5,6 +5,7 @@
 
 #include "../../include/ghost_b200.h"
 #include "net.cuh"
+#include "sr_kernels.cuh"
 
 using namespace ghost;
 
@@ -300,6 +301,53 @@ int ghost_net_debug_get(ghost_net_t* net, int B, const char* name, void* dst, in
     }
     if (dst)
       check_msg(nhwc_to_nchw_launch(a.p, a.dtype, a.C, 0, dst, dst_dtype, a.N, a.C, a.H, a.W, S(stream)), "debug get");
+  });
+}
+
+int ghost_sr_create(ghost_net_t** out, int mode) {
+  return guarded([&] {
+    require(out, "null argument");
+    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    *out = new ghost_net(Net::kSR, "lipspade", 0, 0, mode);
+  });
+}
+
+int ghost_sr_forward(ghost_net_t* net, const void* x, int x_dtype, void* y, int y_dtype, int B, void* stream) {
+  return guarded([&] {
+    require(net && x && y, "null argument");
+    require(net->net.kind == Net::kSR, "not a super-resolution generator handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(nchw_to_nhwc_launch(x, x_dtype, p.x_in.p, p.x_in.dtype, B, 3, 256, 256, 3, 0, s), "x in");
+    n.run_plan(p, s);
+    check_msg(nhwc_to_nchw_launch(p.y.p, p.y.dtype, 3, 0, y, y_dtype, B, 3, 256, 256, s), "y out");
+  });
+}
+
+int ghost_sr_enhance_u8(ghost_net_t* net, const uint8_t* crops_bgr, uint8_t* out_bgr, int B, void* stream) {
+  return guarded([&] {
+    require(net && crops_bgr && out_bgr, "null argument");
+    require(net->net.kind == Net::kSR, "not a super-resolution generator handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(sr_preproc_launch(crops_bgr, p.x_in.p, p.x_in.dtype, B, 65536, s), "sr preproc");
+    n.run_plan(p, s);
+    check_msg(sr_postproc_launch(p.y.p, p.y.dtype, out_bgr, B, 65536, s), "sr postproc");
+  });
+}
+
+int ghost_sr_read_buffer(ghost_net_t* net, const char* key, float* dst_host, int cap, int* n_out, void* stream) {
+  return guarded([&] {
+    require(net && key, "null argument");
+    require(net->net.kind == Net::kSR, "not a super-resolution generator handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    if (!net->net.finalized) fail(GHOST_ERR_INVALID, "network used before ghost_net_finalize");
+    const int n = net->net.read_sn_buffer(key, dst_host, cap, S(stream));
+    if (n_out) *n_out = n;
   });
 }
 

@@ -103,6 +103,8 @@ void Net::finalize() {
   aad_.clear();
   if (kind == kAEI)
     finalize_aei();
+  else if (kind == kSR)
+    finalize_sr();
   else
     finalize_arcface();
   check_cuda(cudaDeviceSynchronize(), "finalize");
@@ -119,6 +121,8 @@ ExecPlan& Net::plan(int B) {
   p->err_word = device_err_word();
   if (kind == kAEI)
     build_aei(*p);
+  else if (kind == kSR)
+    build_sr(*p);
   else
     build_arcface(*p);
   for (auto& op : p->ops) p->flops += op.flops;
@@ -133,8 +137,22 @@ void Net::run_plan(ExecPlan& p, cudaStream_t s, size_t first, size_t last) {
   if (use_graph && whole) {
     if (!p.graph && !p.graph_tried) {
       p.graph_tried = true;
-      // warm every kernel once (module load, attribute setup) before capturing
+      // warm every kernel once (module load, attribute setup) before capturing; the warm-up pass must not count
+      // as a forward for the spectral-norm power iteration, so u is put back afterwards
+      std::vector<std::vector<float>> u_saved;
+      for (auto& kv : sr_sn_) {
+        u_saved.emplace_back(kv.second.R);
+        check_cuda(cudaMemcpyAsync(u_saved.back().data(), kv.second.u, kv.second.R * sizeof(float),
+                                   cudaMemcpyDeviceToHost, s), "save u");
+      }
+      check_cuda(cudaStreamSynchronize(s), "save u sync");
       for (auto& op : p.ops) check_msg(op.run(s), op.name);
+      {
+        size_t i = 0;
+        for (auto& kv : sr_sn_)
+          check_cuda(cudaMemcpyAsync(kv.second.u, u_saved[i++].data(), kv.second.R * sizeof(float),
+                                     cudaMemcpyHostToDevice, s), "restore u");
+      }
       check_cuda(cudaStreamSynchronize(s), "graph warm-up");
       cudaStream_t cs;
       check_cuda(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking), "capture stream");
@@ -166,6 +184,23 @@ void Net::run_plan(ExecPlan& p, cudaStream_t s, size_t first, size_t last) {
     }
   }
   for (size_t i = first; i < last; ++i) check_msg(p.ops[i].run(s), p.ops[i].name);
+}
+
+int Net::read_sn_buffer(const std::string& key, float* dst, int cap, cudaStream_t s) {
+  const size_t dot = key.rfind('.');
+  if (dot == std::string::npos) fail(-1, "bad spectral-norm buffer name: " + key);
+  auto it = sr_sn_.find(key.substr(0, dot));
+  if (it == sr_sn_.end()) fail(-1, "no spectral-norm conv named " + key.substr(0, dot));
+  const std::string leaf = key.substr(dot + 1);
+  const float* src = leaf == "weight_u" ? it->second.u : leaf == "weight_v" ? it->second.v : nullptr;
+  if (!src) fail(-1, "spectral-norm buffer must be weight_u or weight_v");
+  const int n = leaf == "weight_u" ? it->second.R : it->second.K;
+  if (dst) {
+    if (cap < n) fail(-1, "destination too small for " + key);
+    check_cuda(cudaMemcpyAsync(dst, src, n * sizeof(float), cudaMemcpyDeviceToHost, s), "read_sn_buffer");
+    check_cuda(cudaStreamSynchronize(s), "read_sn_buffer sync");
+  }
+  return n;
 }
 
 void Net::profile_plan(ExecPlan& p, cudaStream_t s, int reps, std::vector<float>* ms) {

@@ -98,7 +98,7 @@ struct ExecPlan {
 
 class Net {
  public:
-  enum Kind { kAEI, kArcFace };
+  enum Kind { kAEI, kArcFace, kSR };
   Net(Kind kind, std::string backbone, int num_blocks, int c_id, int mode);
   ~Net();
 
@@ -127,6 +127,8 @@ class Net {
   void build_arcface(ExecPlan& p);
   void finalize_aei();
   void finalize_arcface();
+  void build_sr(ExecPlan& p);
+  void finalize_sr();
 
   std::map<std::string, HostTensor> w_;
   DevPool wpool_;
@@ -137,6 +139,17 @@ class Net {
   int zfc_cols_ = 0;
   struct AadInfo { std::string name; int c_x, c_attr, off_gamma, off_beta; };
   std::map<std::string, AadInfo> aad_;
+  // super-resolution generator (sr.cu): spectral-norm state per conv (device; u advances with every forward, like
+  // the reference's weight_u buffer in train() mode), channel slice of each SPADE's hidden activation
+  struct SnState { int R = 0, K = 0; const float* W = nullptr; float *u = nullptr, *v = nullptr, *inv_sigma = nullptr, *scratch = nullptr; };
+  struct SrSlice { int ri, c0, nhp; };
+  std::map<std::string, SnState> sr_sn_;
+  std::map<std::string, SrSlice> sr_slices_;
+  int sr_actv_c_[6] = {0, 0, 0, 0, 0, 0};
+
+ public:
+  // copies a spectral-norm buffer ("<conv>.weight_u" / "<conv>.weight_v") to the host; returns its length
+  int read_sn_buffer(const std::string& key, float* dst, int cap, cudaStream_t s);
 };
 
 }  // namespace ghost

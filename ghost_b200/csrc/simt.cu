@@ -1,5 +1,7 @@
 #include "simt.cuh"
 
+#include "sr_kernels.cuh"  // in_stats_launch_ex
+
 #include "igemm.cuh"  // Act1 / Act2 enums
 #include "ptx.cuh"    // packed fp32 helpers (fma2 / add2 / sub2 / mul2)
 
@@ -321,7 +323,8 @@ __device__ __forceinline__ void stats_accumulate8(const float (&v)[8], const flo
 }
 template <typename T>
 __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restrict__ x, int HW, int C,
-                                                                 int pix_per_block, float* __restrict__ parts) {
+                                                                 int pix_per_block, float* __restrict__ parts,
+                                                                 int common_shift) {
   extern __shared__ float sh[];  // [kStatThreads][16]
   const int n = blockIdx.y;
   const int P = gridDim.x;
@@ -334,7 +337,8 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
 #pragma unroll
   for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
   const T* base = x + (static_cast<long long>(n) * HW) * C + cv * 8;
-  load8(base, sft);
+  // common_shift: image 0's first pixel for every image, so that the sums add up over the batch (BatchNorm)
+  load8(common_shift ? x + cv * 8 : base, sft);
   if (pl < ppi) {
     // four independent 16-byte loads in flight per thread: the kernel is a pure HBM stream
     for (int p = p0 + pl; p < p1; p += 4 * ppi) {
@@ -532,15 +536,21 @@ int in_stats_parts(int N, int HW, int C) {
 }
 
 const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, float* parts, cudaStream_t s) {
+  return in_stats_launch_ex(x, dtype, N, HW, C, parts, 0, s);
+}
+
+const char* in_stats_launch_ex(const void* x, int dtype, int N, int HW, int C, float* parts, int common_shift,
+                               cudaStream_t s) {
   if (C % 8 || C > 8 * kStatThreads) return "in_stats: C must be a multiple of 8 and <= 2048";
   const int ppb = stats_pix_per_block(N, HW, C);
   dim3 grid((HW + ppb - 1) / ppb, N);
   const int smem = kStatThreads * 16 * sizeof(float);
   if (dtype == kF32)
-    in_stats_kernel<float><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x), HW, C, ppb, parts);
+    in_stats_kernel<float>
+        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const float*>(x), HW, C, ppb, parts, common_shift);
   else if (dtype == kBF16)
     in_stats_kernel<__nv_bfloat16>
-        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, parts);
+        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, parts, common_shift);
   else
     return "in_stats: unsupported dtype";
   return last_err();

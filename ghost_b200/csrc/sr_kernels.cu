@@ -1,0 +1,526 @@
+#include "sr_kernels.cuh"
+
+#include <math.h>
+
+namespace ghost {
+
+namespace {
+
+inline const char* last_err() {
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+template <typename T>
+__device__ __forceinline__ float ldf(const T* p);
+template <>
+__device__ __forceinline__ float ldf<float>(const float* p) {
+  return __ldg(p);
+}
+template <>
+__device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return __bfloat162float(*p);
+}
+template <typename T>
+__device__ __forceinline__ T cvt(float v);
+template <>
+__device__ __forceinline__ float cvt<float>(float v) {
+  return v;
+}
+template <>
+__device__ __forceinline__ __nv_bfloat16 cvt<__nv_bfloat16>(float v) {
+  return __float2bfloat16(v);
+}
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+  v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  uint4 q;
+  __nv_bfloat162 t;
+  t = __floats2bfloat162_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  if (act == kSrRelu) return fmaxf(v, 0.f);
+  if (act == kSrLeaky02) return v > 0.f ? v : v * 0.2f;
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------- seg patches
+template <typename T>
+__global__ void __launch_bounds__(256) seg_patches_kernel(const T* __restrict__ img, T* __restrict__ out, int N, int S,
+                                                           int f) {
+  // one thread per (pixel, 8-channel group of the 32): 4 threads per pixel
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = static_cast<long long>(N) * S * S * 4;
+  if (t >= total) return;
+  const int g = static_cast<int>(t & 3);
+  const long long pix = t >> 2;
+  const int j = static_cast<int>(pix % S);
+  const int i = static_cast<int>((pix / S) % S);
+  const int n = static_cast<int>(pix / (static_cast<long long>(S) * S));
+  float v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int k = g * 8 + e;
+    float val = 0.f;
+    if (k < 27) {
+      const int tap = k / 3, c = k - tap * 3;
+      const int ii = i + tap / 3 - 1, jj = j + tap % 3 - 1;
+      if (ii >= 0 && ii < S && jj >= 0 && jj < S)
+        val = ldf(img + ((static_cast<long long>(n) * 256 + ii * f) * 256 + jj * f) * 3 + c);
+    }
+    v[e] = val;
+  }
+  store8(out + pix * 32 + g * 8, v);
+}
+
+// ---------------------------------------------------------------------------------------------- norm fold
+// block = 16 channels x 64 part-lanes; every lane adds its parts in a fixed order (double), the lanes are added in
+// index order: deterministic.  grid (ceil(C/16), pool_n ? 1 : N).
+__global__ void __launch_bounds__(1024) norm_fold_kernel(const float* __restrict__ parts, int P, int N, int HW, int C,
+                                                          int pool_n, const float* __restrict__ weight,
+                                                          const float* __restrict__ bias, float eps,
+                                                          float2* __restrict__ ss) {
+  __shared__ double shs[64][16], shq[64][16];
+  const int cl = threadIdx.x & 15, lane = threadIdx.x >> 4;
+  const int c = blockIdx.x * 16 + cl;
+  const int n0 = pool_n ? 0 : blockIdx.y, n1 = pool_n ? N : blockIdx.y + 1;
+  double su = 0.0, sq = 0.0;
+  if (c < C) {
+    const long long rows = static_cast<long long>(n1 - n0) * P;
+    for (long long q = lane; q < rows; q += 64) {
+      const int n = n0 + static_cast<int>(q / P), p = static_cast<int>(q % P);
+      const float* pn = parts + (static_cast<long long>(n) * (2 * P + 1) + 2 * p) * C + c;
+      su += static_cast<double>(pn[0]);
+      sq += static_cast<double>(pn[C]);
+    }
+  }
+  shs[lane][cl] = su;
+  shq[lane][cl] = sq;
+  __syncthreads();
+  if (lane == 0 && c < C) {
+    su = 0.0;
+    sq = 0.0;
+    for (int l = 0; l < 64; ++l) {
+      su += shs[l][cl];
+      sq += shq[l][cl];
+    }
+    const double inv = 1.0 / (static_cast<double>(HW) * (n1 - n0));
+    const double d = su * inv;
+    const float sft = parts[(static_cast<long long>(n0) * (2 * P + 1) + 2 * P) * C + c];
+    const float mu = static_cast<float>(static_cast<double>(sft) + d);
+    const float var = static_cast<float>(fmax(sq * inv - d * d, 0.0));
+    const float rstd = 1.0f / sqrtf(var + eps);
+    const float sc = (weight ? weight[c] : 1.f) * rstd;
+    const float sh = (bias ? bias[c] : 0.f) - mu * sc;
+    if (pool_n) {
+      ss[c] = make_float2(sc, sh);
+    } else {
+      ss[static_cast<long long>(n0) * C + c] = make_float2(sc, sh);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- norm + act
+template <typename T>
+__global__ void __launch_bounds__(256) norm_act_kernel(const T* __restrict__ x, T* __restrict__ y, long long total8,
+                                                        int HW, int C, const float2* __restrict__ ss, int ss_stride_n,
+                                                        int act) {
+  const int vecs = C >> 3;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(t % vecs);
+    const long long pix = t / vecs;
+    float v[8];
+    load8(x + t * 8, v);
+    if (ss) {
+      const int n = static_cast<int>(pix / HW);
+      const float2* sp = ss + static_cast<long long>(n) * ss_stride_n + cv * 8;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 a = __ldg(sp + i);
+        v[i] = fmaf(v[i], a.x, a.y);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = apply_act(v[i], act);
+    store8(y + t * 8, v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- LIP pooling
+template <typename T>
+__global__ void __launch_bounds__(256) lip_pool_kernel(const T* __restrict__ x, const T* __restrict__ lg,
+                                                        T* __restrict__ out, int N, int H, int W, int C,
+                                                        const float2* __restrict__ ss) {
+  const int vecs = C >> 3;
+  const int Ho = H >> 1, Wo = W >> 1;
+  const long long total = static_cast<long long>(N) * Ho * Wo * vecs;
+  const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int cv = static_cast<int>(t % vecs);
+  long long pix = t / vecs;
+  const int ow = static_cast<int>(pix % Wo);
+  pix /= Wo;
+  const int oh = static_cast<int>(pix % Ho);
+  const int n = static_cast<int>(pix / Ho);
+  float sc[8], sh[8], num[8], den[8];
+  const float2* sp = ss + static_cast<long long>(n) * C + cv * 8;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float2 a = __ldg(sp + i);
+    sc[i] = a.x;
+    sh[i] = a.y;
+    num[i] = den[i] = 0.f;
+  }
+  for (int kh = 0; kh < 3; ++kh) {
+    const int ih = 2 * oh - 1 + kh;
+    if (ih < 0 || ih >= H) continue;
+    for (int kw = 0; kw < 3; ++kw) {
+      const int iw = 2 * ow - 1 + kw;
+      if (iw < 0 || iw >= W) continue;
+      const long long off = ((static_cast<long long>(n) * H + ih) * W + iw) * C + cv * 8;
+      float xv[8], lv[8];
+      load8(x + off, xv);
+      load8(lg + off, lv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float z = fmaf(lv[i], sc[i], sh[i]);
+        const float g = 12.0f / (1.0f + expf(-z));  // SoftGate: sigmoid * 12
+        const float w = expf(g);
+        num[i] = fmaf(xv[i], w, num[i]);
+        den[i] += w;
+      }
+    }
+  }
+  float o[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = num[i] / den[i];
+  store8(out + t * 8, o);
+}
+
+// ---------------------------------------------------------------------------------------------- SPADE apply
+template <typename T>
+__global__ void __launch_bounds__(256) spade_apply_kernel(const T* __restrict__ x, const T* __restrict__ gb,
+                                                           T* __restrict__ out, long long total8, int H, int W, int C,
+                                                           int up, const float2* __restrict__ ss, int act,
+                                                           const float* __restrict__ post) {
+  const int vecs = C >> 3;
+  const float ps = post ? __ldg(post) : 1.f;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(t % vecs);
+    const long long pix = t / vecs;
+    long long xoff;
+    if (up) {
+      const int w = static_cast<int>(pix % W);
+      const long long r = pix / W;
+      const int h = static_cast<int>(r % H);
+      const long long n = r / H;
+      xoff = ((n * (H >> 1) + (h >> 1)) * (W >> 1) + (w >> 1)) * C + cv * 8;
+    } else {
+      xoff = pix * C + cv * 8;
+    }
+    float xv[8], g[8], b[8];
+    load8(x + xoff, xv);
+    load8(gb + pix * 2 * C + cv * 8, g);
+    load8(gb + pix * 2 * C + C + cv * 8, b);
+    const float2* sp = ss + cv * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float2 a = __ldg(sp + i);
+      const float xn = fmaf(xv[i], a.x, a.y);
+      xv[i] = apply_act(fmaf(xn, g[i], b[i]), act) * ps;
+    }
+    store8(out + t * 8, xv);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) nearest_up2x_kernel(const T* __restrict__ x, T* __restrict__ y, long long total8,
+                                                            int H, int W, int C) {
+  const int vecs = C >> 3;
+  const int Ho = 2 * H, Wo = 2 * W;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8;
+       t += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(t % vecs);
+    const long long pix = t / vecs;
+    const int w = static_cast<int>(pix % Wo);
+    const long long r = pix / Wo;
+    const int h = static_cast<int>(r % Ho);
+    const long long n = r / Ho;
+    float v[8];
+    load8(x + ((n * H + (h >> 1)) * W + (w >> 1)) * C + cv * 8, v);
+    store8(y + t * 8, v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- spectral norm
+constexpr int kSnRowChunks = 16;
+
+// partial[y][k] = sum over the rows of chunk y of W[r][k] * u[r]
+__global__ void __launch_bounds__(256) sn_wtu_kernel(const float* __restrict__ W, int R, int K,
+                                                      const float* __restrict__ u, float* __restrict__ partial) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  const int rows = (R + kSnRowChunks - 1) / kSnRowChunks;
+  const int r0 = blockIdx.y * rows, r1 = min(R, r0 + rows);
+  float a = 0.f;
+  for (int r = r0; r < r1; ++r) a = fmaf(__ldg(W + static_cast<long long>(r) * K + k), __ldg(u + r), a);
+  partial[static_cast<long long>(blockIdx.y) * K + k] = a;
+}
+
+// block-wide sum in a fixed order (warp shuffles, then the warp totals in index order)
+__device__ __forceinline__ float block_sum_1024(float v, float* red) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  for (int i = 0; i < 32; ++i) t += red[i];
+  return t;
+}
+
+// v = normalize(sum_y partial[y])
+__global__ void __launch_bounds__(1024) sn_v_kernel(const float* __restrict__ partial, int K, float* __restrict__ v) {
+  __shared__ float red[32];
+  float loc = 0.f;
+  for (int k = threadIdx.x; k < K; k += 1024) {
+    float t = 0.f;
+    for (int y = 0; y < kSnRowChunks; ++y) t += partial[static_cast<long long>(y) * K + k];
+    v[k] = t;
+    loc = fmaf(t, t, loc);
+  }
+  const float nrm = sqrtf(block_sum_1024(loc, red));
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+  for (int k = threadIdx.x; k < K; k += 1024) v[k] *= inv;
+}
+
+// wv[r] = W[r] . v   (one warp per row)
+__global__ void __launch_bounds__(256) sn_wv_kernel(const float* __restrict__ W, int R, int K,
+                                                     const float* __restrict__ v, float* __restrict__ wv) {
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= R) return;
+  const int lane = threadIdx.x & 31;
+  float a = 0.f;
+  for (int k = lane; k < K; k += 32) a = fmaf(__ldg(W + static_cast<long long>(r) * K + k), __ldg(v + k), a);
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) wv[r] = a;
+}
+
+// u = normalize(wv); sigma = u . wv; inv_sigma = 1 / sigma
+__global__ void __launch_bounds__(1024) sn_u_kernel(const float* __restrict__ wv, int R, float* __restrict__ u,
+                                                     float* __restrict__ inv_sigma) {
+  __shared__ float red[32];
+  float loc = 0.f;
+  for (int r = threadIdx.x; r < R; r += 1024) loc = fmaf(wv[r], wv[r], loc);
+  const float nrm = sqrtf(block_sum_1024(loc, red));
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+  float dot = 0.f;
+  for (int r = threadIdx.x; r < R; r += 1024) {
+    const float un = wv[r] * inv;
+    u[r] = un;
+    dot = fmaf(un, wv[r], dot);
+  }
+  const float sigma = block_sum_1024(dot, red);
+  if (threadIdx.x == 0) inv_sigma[0] = 1.0f / sigma;
+}
+
+// ---------------------------------------------------------------------------------------------- u8 conversions
+template <typename T>
+__global__ void __launch_bounds__(256) sr_preproc_kernel(const uint8_t* __restrict__ src, T* __restrict__ dst,
+                                                          long long npix) {
+  const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (p >= npix) return;
+  const uint8_t* s = src + p * 3;
+  T* d = dst + p * 3;
+  // Frames.__getitem__: BGR -> RGB, ToTensor = uint8 / 255 (fp32 division)
+  d[0] = cvt<T>(static_cast<float>(s[2]) / 255.0f);
+  d[1] = cvt<T>(static_cast<float>(s[1]) / 255.0f);
+  d[2] = cvt<T>(static_cast<float>(s[0]) / 255.0f);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) sr_postproc_kernel(const T* __restrict__ y, uint8_t* __restrict__ dst,
+                                                           long long npix) {
+  const long long p = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (p >= npix) return;
+  const T* s = y + p * 3;
+  uint8_t* d = dst + p * 3;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    // clamp(g * 255, 0, 255).type(uint8): truncation; RGB -> BGR
+    const float v = fminf(fmaxf(ldf(s + c) * 255.0f, 0.f), 255.f);
+    d[2 - c] = static_cast<uint8_t>(static_cast<int>(v));
+  }
+}
+
+inline unsigned grid_for(long long total, int threads, int cap = 148 * 32) {
+  long long b = (total + threads - 1) / threads;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<unsigned>(b);
+}
+
+}  // namespace
+
+const char* seg_patches_launch(const void* img, void* patches, int dtype, int N, int S, cudaStream_t s) {
+  if (S < 1 || 256 % S) return "seg_patches: S must divide 256";
+  const long long total = static_cast<long long>(N) * S * S * 4;
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  if (dtype == kF32)
+    seg_patches_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(img),
+                                                     reinterpret_cast<float*>(patches), N, S, 256 / S);
+  else if (dtype == kBF16)
+    seg_patches_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(img),
+                                                             reinterpret_cast<__nv_bfloat16*>(patches), N, S, 256 / S);
+  else
+    return "seg_patches: unsupported dtype";
+  return last_err();
+}
+
+const char* norm_fold_launch(const float* parts, int P, int N, int HW, int C, int pool_n, const float* weight,
+                             const float* bias, float eps, float2* ss, cudaStream_t s) {
+  dim3 grid((C + 15) / 16, pool_n ? 1 : N);
+  norm_fold_kernel<<<grid, 1024, 0, s>>>(parts, P, N, HW, C, pool_n, weight, bias, eps, ss);
+  return last_err();
+}
+
+const char* norm_act_launch(const void* x, void* y, int dtype, int N, int HW, int C, const float2* ss, int ss_stride_n,
+                            int act, cudaStream_t s) {
+  if (C % 8) return "norm_act: C must be a multiple of 8";
+  const long long total8 = static_cast<long long>(N) * HW * (C / 8);
+  const unsigned blocks = grid_for(total8, 256);
+  if (dtype == kF32)
+    norm_act_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y),
+                                                  total8, HW, C, ss, ss_stride_n, act);
+  else if (dtype == kBF16)
+    norm_act_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                          reinterpret_cast<__nv_bfloat16*>(y), total8, HW, C, ss,
+                                                          ss_stride_n, act);
+  else
+    return "norm_act: unsupported dtype";
+  return last_err();
+}
+
+const char* lip_pool_launch(const void* x, const void* logit, void* out, int dtype, int N, int H, int W, int C,
+                            const float2* ss, cudaStream_t s) {
+  if (C % 8 || (H & 1) || (W & 1)) return "lip_pool: C % 8 and even H, W required";
+  const long long total = static_cast<long long>(N) * (H / 2) * (W / 2) * (C / 8);
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  if (dtype == kF32)
+    lip_pool_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(x),
+                                                  reinterpret_cast<const float*>(logit),
+                                                  reinterpret_cast<float*>(out), N, H, W, C, ss);
+  else if (dtype == kBF16)
+    lip_pool_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                          reinterpret_cast<const __nv_bfloat16*>(logit),
+                                                          reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, ss);
+  else
+    return "lip_pool: unsupported dtype";
+  return last_err();
+}
+
+const char* spade_apply_launch(const void* x, const void* gb, void* out, int dtype, int N, int H, int W, int C, int up,
+                               const float2* ss, int act, const float* post, cudaStream_t s) {
+  if (C % 8) return "spade_apply: C must be a multiple of 8";
+  if (up && ((H & 1) || (W & 1))) return "spade_apply: upsampled grid must be even";
+  const long long total8 = static_cast<long long>(N) * H * W * (C / 8);
+  const unsigned blocks = grid_for(total8, 256);
+  if (dtype == kF32)
+    spade_apply_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(x),
+                                                     reinterpret_cast<const float*>(gb), reinterpret_cast<float*>(out),
+                                                     total8, H, W, C, up, ss, act, post);
+  else if (dtype == kBF16)
+    spade_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(gb),
+        reinterpret_cast<__nv_bfloat16*>(out), total8, H, W, C, up, ss, act, post);
+  else
+    return "spade_apply: unsupported dtype";
+  return last_err();
+}
+
+const char* nearest_up2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, cudaStream_t s) {
+  if (C % 8) return "nearest_up2x: C must be a multiple of 8";
+  const long long total8 = static_cast<long long>(N) * 4 * H * W * (C / 8);
+  const unsigned blocks = grid_for(total8, 256);
+  if (dtype == kF32)
+    nearest_up2x_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(x), reinterpret_cast<float*>(y),
+                                                      total8, H, W, C);
+  else if (dtype == kBF16)
+    nearest_up2x_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                              reinterpret_cast<__nv_bfloat16*>(y), total8, H, W, C);
+  else
+    return "nearest_up2x: unsupported dtype";
+  return last_err();
+}
+
+size_t sn_scratch_floats(int R, int K) { return static_cast<size_t>(kSnRowChunks) * K + R; }
+
+const char* sn_power_iter_launch(const float* W, int R, int K, float* u, float* v, float* inv_sigma, float* scratch,
+                                 cudaStream_t s) {
+  float* partial = scratch;
+  float* wv = scratch + static_cast<size_t>(kSnRowChunks) * K;
+  dim3 g1((K + 255) / 256, kSnRowChunks);
+  sn_wtu_kernel<<<g1, 256, 0, s>>>(W, R, K, u, partial);
+  sn_v_kernel<<<1, 1024, 0, s>>>(partial, K, v);
+  sn_wv_kernel<<<(R + 7) / 8, 256, 0, s>>>(W, R, K, v, wv);
+  sn_u_kernel<<<1, 1024, 0, s>>>(wv, R, u, inv_sigma);
+  return last_err();
+}
+
+const char* sr_preproc_launch(const uint8_t* crops_bgr, void* dst, int dtype, int N, int HW, cudaStream_t s) {
+  const long long npix = static_cast<long long>(N) * HW;
+  const unsigned blocks = static_cast<unsigned>((npix + 255) / 256);
+  if (dtype == kF32)
+    sr_preproc_kernel<float><<<blocks, 256, 0, s>>>(crops_bgr, reinterpret_cast<float*>(dst), npix);
+  else if (dtype == kBF16)
+    sr_preproc_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(crops_bgr, reinterpret_cast<__nv_bfloat16*>(dst), npix);
+  else
+    return "sr_preproc: unsupported dtype";
+  return last_err();
+}
+
+const char* sr_postproc_launch(const void* y, int dtype, uint8_t* dst_bgr, int N, int HW, cudaStream_t s) {
+  const long long npix = static_cast<long long>(N) * HW;
+  const unsigned blocks = static_cast<unsigned>((npix + 255) / 256);
+  if (dtype == kF32)
+    sr_postproc_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(y), dst_bgr, npix);
+  else if (dtype == kBF16)
+    sr_postproc_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(y), dst_bgr, npix);
+  else
+    return "sr_postproc: unsupported dtype";
+  return last_err();
+}
+
+}  // namespace ghost

@@ -14,6 +14,8 @@
  *   utils/inference/faceshifter_run.py:5-23  faceshifter_batch
  *   utils/inference/image_processing.py:23-48,51-77   normalize_and_torch(_batch), get_final_image
  *   utils/inference/video_processing.py:191-243       get_final_video (compositing only)
+ *   utils/inference/video_processing.py:246-285       Frames / face_enhancement
+ *   models/pix2pix_model.py:42-62, models/networks/generator.py:93-137,390-400   Pix2PixModel 'inference2' -> LIPSPADEGenerator
  */
 #ifndef GHOST_B200_H_
 #define GHOST_B200_H_
@@ -111,6 +113,28 @@ int ghost_net_profile(ghost_net_t* net, int B, int reps, int max_ops, float* ms,
  * shape4 (optional) receives {N,C,H,W}; dst may be NULL to query the shape only. */
 int ghost_net_debug_get(ghost_net_t* net, int B, const char* name, void* dst, int dst_dtype, int* shape4,
                         void* stream);
+
+/* ---- pix2pix super-resolution generator: LIPSPADEGenerator(TestOptions) as inference.py:42-48 builds it
+ * (models/pix2pix_model.py:16-25 -> models/networks/generator.py:390-400, config models/config_sr.py:3-29), in the
+ * `.train()` state of inference.py:48: every SPADE normalises with the statistics of the current batch and every
+ * spectral-normalised conv performs one power iteration per forward (its weight_u / weight_v buffers advance).
+ * Weights go in through ghost_net_set_weight under the reference's state_dict keys (head_0.conv_0.weight_orig,
+ * head_0.conv_0.weight_u, ups.3.norm_s.mlp_gamma.weight, lip_encoder.model.3.logit.1.bias, ...). */
+int ghost_sr_create(ghost_net_t** out, int mode);
+
+/* generated = netG(x)  (Pix2PixModel.forward(data, 'inference2'), models/pix2pix_model.py:58-61;
+ * SPADEGenerator.forward, models/networks/generator.py:93-137 with seg = input).
+ *   x [B,3,256,256] NCHW RGB in [0,1], y [B,3,256,256] NCHW in [-1,1] (tanh).  The B crops share their batch statistics. */
+int ghost_sr_forward(ghost_net_t* net, const void* x, int x_dtype, void* y, int y_dtype, int B, void* stream);
+
+/* One DataLoader batch of face_enhancement (utils/inference/video_processing.py:263-285, batch_size = 20):
+ *   crops_bgr [B,256,256,3] uint8 BGR (device) -> RGB / 255 -> netG -> clamp(g*255, 0, 255) -> uint8 -> BGR. */
+int ghost_sr_enhance_u8(ghost_net_t* net, const uint8_t* crops_bgr, uint8_t* out_bgr, int B, void* stream);
+
+/* Reads a spectral-norm buffer of the finalized network ("head_0.conv_0.weight_u", "...weight_v") into host memory
+ * (what state_dict() of the reference module would hold after the forwards run so far).  Synchronous.
+ * dst_host may be NULL to query the length (*n_out). */
+int ghost_sr_read_buffer(ghost_net_t* net, const char* key, float* dst_host, int cap, int* n_out, void* stream);
 
 void ghost_net_destroy(ghost_net_t* net);
 
