@@ -269,7 +269,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const int hbox = (p.BN >> 1) >> 6;
     p.sets = 4 / hbox;
     // one N tile and 64-channel K chunks: the gamma/beta weights stay resident, only z_attr streams
-    const int slab = p.kc_per_tap * p.BN * p.kc * 2;
+    const int slab = p.ntaps * p.kc_per_tap * p.BN * p.kc * 2;
     p.b_res = p.tiles_n == 1 && p.kc == 64 && slab <= 64 * 1024;
     if (p.b_res) {
       stage_bytes = 128 * p.kc * 2;
@@ -330,7 +330,12 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.mask = aad->mask;
     if (!w.bias) return "lower_conv: AAD needs the gamma/beta bias vector";
     if (aad->c_x % 64) return "lower_conv: AAD c_x must be a multiple of 64";
-    if (p.tiles_n > 1 && !aad->mask) return "lower_conv: AAD with c_x > 128 needs the precomputed mask";
+    if (p.tiles_n > 1 && !aad->mask && !aad->spade) return "lower_conv: AAD with c_x > 128 needs the precomputed mask";
+    p.aad_spade = aad->spade;
+    p.aad_slope = aad->slope;
+    p.aad_post = aad->post;
+    p.aad_no_h = aad->no_h;
+    if (aad->no_h && !aad->spade) return "lower_conv: no_h needs the SPADE variant of the epilogue";
     if (out.sw != aad->c_x || out.off != 0 || out.sh != static_cast<long long>(Wo) * aad->c_x ||
         out.sn != static_cast<long long>(Ho) * Wo * aad->c_x)
       return "lower_conv: AAD output must be a dense NHWC tensor of c_x channels";
@@ -339,7 +344,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       const uint64_t dims[4] = {cx, static_cast<uint64_t>(Wo), static_cast<uint64_t>(Ho), static_cast<uint64_t>(in.N)};
       const uint64_t str[3] = {cx * eb, static_cast<uint64_t>(Wo) * cx * eb, static_cast<uint64_t>(Ho) * Wo * cx * eb};
       const uint32_t box[4] = {64u, static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
-      if (const char* e = encode_tmap(&p.tmH, aad->h, 4, dims, str, box, 128)) return e;
+      // no_h: the map is never used by the kernel; it is encoded over the output tensor to stay valid
+      if (const char* e = encode_tmap(&p.tmH, aad->no_h ? out.p : aad->h, 4, dims, str, box, 128)) return e;
       // store box = the 32 consecutive tile rows (order n, h, w) one epilogue warp owns
       uint32_t ob[4] = {64u, 0, 1, 1};
       const int bw = p.bw, bh = p.bh, bn = p.bn;

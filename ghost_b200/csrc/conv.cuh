@@ -85,6 +85,11 @@ struct AadArgs {  // only for the fused AAD epilogue
   const float* wh_fold = nullptr;
   const float* bh_fold = nullptr;
   const float* mask = nullptr;  // precomputed sigmoid mask [N*H*W]; required when c_x > 128
+  // SPADE variant (igemm.cuh): no mask, out = max(v, v*slope) * post[0]
+  int spade = 0;
+  float slope = 0.f;
+  const float* post = nullptr;
+  int no_h = 0;  // SPADE variant without an h tensor (h = nullptr): out = act(beta half + bias) * post
 };
 
 // A lowered, launch-ready op.

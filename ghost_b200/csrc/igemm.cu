@@ -102,6 +102,14 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
   asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
   return d;
 }
+// SPADE variant: max(v, v*slope) * post (slope 0 = ReLU, 0.2 = LeakyReLU(0.2), 1 = identity)
+__device__ __forceinline__ uint32_t pack_bf16_slope(float lo, float hi, float slope, float post) {
+  uint32_t d;
+  lo = fmaxf(lo, lo * slope) * post;
+  hi = fmaxf(hi, hi * slope) * post;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 
 
 // acc + bias, first activation.  `sp` != nullptr: per-channel parameters of this CTA's N tile staged in shared
@@ -471,9 +479,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       if (p.mode == kModeAAD) {
         PROF_WAIT1(mbar_wait_nofail(&hempty_bar[hs], hphase ^ 1u, &abort_flag));
         if (elect_one()) {
-          mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
-          for (int b = 0; b < hbox; ++b)
-            tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
+          if (p.aad_no_h) {
+            mbar_arrive(&hfull_bar[hs]);  // nothing to load: the slot is only the staging of the TMA store
+          } else {
+            mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
+            for (int b = 0; b < hbox; ++b)
+              tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
+          }
         }
         __syncwarp();
         if (++hs == p.h_bufs) {
@@ -755,6 +767,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       const int sw = r & 7;
       const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + set * acc_stride + box * 64;
       const bool quad = p.bn == 1;              // all rows of a tile in one image: parameters are per thread
+      const bool spade = p.aad_spade != 0;
+      const bool no_h = spade && p.aad_no_h != 0;
+      const float sp_slope = p.aad_slope;
+      const float sp_post = (spade && p.aad_post) ? __ldg(p.aad_post) : 1.f;
       const int rq = lane >> 2, cq = lane & 3;  // quad mapping: rows rq + 8k of the piece, channel pairs 8i + 2cq
       TileWalk walk;
       walk.init(p, blockIdx.x + set * gridDim.x, gridDim.x * sets);
@@ -782,7 +798,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 #endif
         float m = 0.f;
         float m4[4] = {0.f, 0.f, 0.f, 0.f};  // quad mapping: mask of rows rq, rq+8, rq+16, rq+24 of this warp's piece
-        if (quad) {
+        if (spade) {
+          // SPADE: no attention mask, the blend reduces to gamma * hn + beta
+        } else if (quad) {
           if (p.mask) {
             if (valid) m = __ldg(p.mask + (static_cast<long long>(n) * p.Ho + oh) * p.Wo + ow);
 #pragma unroll
@@ -897,7 +915,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             uint8_t* hp = hq + ((i ^ rq) << 4);
             uint32_t hv[4];
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) hv[kk] = *reinterpret_cast<const uint32_t*>(hp + kk * 1024);
+            for (int kk = 0; kk < 4; ++kk) hv[kk] = no_h ? 0u : *reinterpret_cast<const uint32_t*>(hp + kk * 1024);
             const float4 p0 = __ldg(parq + 8 * i);      // {rstd0, rstd1, shift0, shift1}
             const float4 p1 = __ldg(parq + 8 * i + 1);  // {gamma_id0, gamma_id1, beta_id0, beta_id1}
             const float2 bgv = __ldg(reinterpret_cast<const float2*>(bgq + 8 * i));
@@ -915,7 +933,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
               const float2 I = fma2(make_float2(p1.x, p1.y), hn, make_float2(p1.z, p1.w));
               const float2 r2 = fma2(make_float2(m4[kk], m4[kk]), sub2(I, A), A);
               // in place, with the ReLU that always follows the layer (AADLayer.py:62,70)
-              *reinterpret_cast<uint32_t*>(hp + kk * 1024) = pack_bf16_relu(r2.x, r2.y);
+              *reinterpret_cast<uint32_t*>(hp + kk * 1024) =
+                  spade ? pack_bf16_slope(r2.x, r2.y, sp_slope, sp_post) : pack_bf16_relu(r2.x, r2.y);
             }
           }
         } else {
@@ -930,7 +949,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           tmem_ld8(t_addr + j, g);
           tmem_ld8(t_addr + cn + j, b);
           uint4* hp = reinterpret_cast<uint4*>(hrow + (((j >> 3) ^ sw) << 4));
-          const uint4 h0 = *hp;
+          const uint4 h0 = no_h ? make_uint4(0u, 0u, 0u, 0u) : *hp;
           const float4 u0 = __ldg(reinterpret_cast<const float4*>(bg + j));
           const float4 u1 = __ldg(reinterpret_cast<const float4*>(bg + j) + 1);
           const float4 v0 = __ldg(reinterpret_cast<const float4*>(bb + j));
@@ -953,7 +972,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const float2 A = fma2(ga, hn, be);
             const float2 I = fma2(make_float2(p1.x, p1.y), hn, make_float2(p1.z, p1.w));
             const float2 r2 = fma2(mm, sub2(I, A), A);
-            o[i] = pack_bf16_relu(r2.x, r2.y);  // the ReLU that always follows the layer (AADLayer.py:62,70)
+            // the ReLU that always follows the layer (AADLayer.py:62,70)
+            o[i] = spade ? pack_bf16_slope(r2.x, r2.y, sp_slope, sp_post) : pack_bf16_relu(r2.x, r2.y);
           }
           *hp = make_uint4(o[0], o[1], o[2], o[3]);  // in place: this thread alone reads and writes this chunk
         }

@@ -83,6 +83,18 @@ struct alignas(64) IgemmParams {
   const float* wh_fold;     // [Nimg][c_x] conv_h weight * rstd
   const float* bh_fold;     // [Nimg]      conv_h bias - sum(w*mu*rstd)
   const float* mask;    // optional precomputed sigmoid mask per pixel (else computed in-kernel)
+  // SPADE variant of the same epilogue (sr.cu; models/networks/normalization.py:94-107 + architecture.py:69-70):
+  // no attention mask (M = 0, the identity half of ncpar is ignored), out = max(v, v*slope) * post[0] with
+  // v = gamma * (h*scale + shift) + beta: slope 0 = ReLU, 0.2 = LeakyReLU(0.2), 1 = no activation; post (device
+  // scalar, may be null) is 1/sigma of the spectral-normalised conv that reads the result.
+  int aad_spade;
+  float aad_slope;
+  const float* aad_post;
+  // aad_no_h (SPADE variant only): there is no h tensor - nothing is loaded, h counts as 0, so with a zero ncpar
+  // table the epilogue is out = act(beta-half of the accumulator + bias) * post, written through the same
+  // shared-memory staging + TMA store.  This is how the thin-K convs of sr.cu (K = 32 .. 128 per pixel, where the
+  // row-per-thread stores of the linear epilogue are the whole cost) leave the SM.
+  int aad_no_h;
 
   int* err;  // device word set non-zero when a pipeline wait timed out
 };

@@ -36,6 +36,9 @@ const SrBlock kSrBlocks[7] = {{"head_0", 768, 768, 8, 0},   {"G_middle_0", 768, 
 const int kSrEncC[6] = {48, 96, 192, 384, 768, 768};
 
 inline int cp(int c) { return (c + 63) / 64 * 64; }
+// SPADE generator tensors: 64, or a multiple of 128 (the fused tcgen05 epilogue works on N tiles of 64 or 128
+// channels: 48 -> 64, 96 -> 128, 192 -> 256)
+inline int cpg(int c) { return c <= 64 ? 64 : (c + 127) / 128 * 128; }
 inline int nhid(int norm_nc) { return norm_nc > 128 ? 128 : norm_nc; }
 
 void expect(const HostTensor& t, std::initializer_list<int64_t> shape, const std::string& key) {
@@ -74,11 +77,27 @@ void Net::finalize_sr() {
   sr_slices_.clear();
   for (int i = 0; i < 6; ++i) sr_actv_c_[i] = 0;
 
+  // bf16 mode, thin-K convs (K = 32..768 per pixel with N <= 384): they leave the SM through the shared-memory
+  // staging + TMA store of the fused epilogue (igemm.cuh aad_no_h).  That epilogue works on [gamma | beta] N tiles,
+  // so the real rows go into the beta half of each tile and the gamma half stays zero (the extra MMA columns cost
+  // nothing next to the stores these layers are bound by).
+  auto pack_ts = [&](const std::vector<float>& rows, int Cp, int K, const std::vector<float>* bias) {
+    const int cn = Cp < 128 ? Cp : 128;
+    std::vector<float> r2(static_cast<size_t>(2) * Cp * K, 0.f), b2(2 * Cp, 0.f);
+    for (int c = 0; c < Cp; ++c) {
+      const int t = c / cn, j = c % cn;
+      const size_t rb = static_cast<size_t>(t) * 2 * cn + cn + j;
+      memcpy(&r2[rb * K], &rows[static_cast<size_t>(c) * K], sizeof(float) * K);
+      if (bias) b2[rb] = (*bias)[c];
+    }
+    return pack(r2, 2 * Cp, K, &b2, false, true);
+  };
+
   // ---- SPADE layers: mlp_shared rows grouped per resolution, gamma|beta matrices
   struct Pending { std::string key; int nh, nhp, row0; };
   std::vector<Pending> per_res[6];  // index = log2(S) - 3
   auto add_spade = [&](const std::string& key, int norm_nc, int S) {
-    const int nh = nhid(norm_nc), nhp = cp(nh), Cp = cp(norm_nc);
+    const int nh = nhid(norm_nc), nhp = cp(nh), Cp = cpg(norm_nc);
     int ri = 0;
     while ((8 << ri) != S) ++ri;
     Pending pd{key, nh, nhp, sr_actv_c_[ri]};
@@ -90,8 +109,24 @@ void Net::finalize_sr() {
     expect(wg, {norm_nc, nh, 3, 3}, key + ".mlp_gamma.weight");
     expect(wb, {norm_nc, nh, 3, 3}, key + ".mlp_beta.weight");
     std::vector<float> g = repack(wg, norm_nc, nh, 3, Cp, nhp), b = repack(wb, norm_nc, nh, 3, Cp, nhp);
-    g.insert(g.end(), b.begin(), b.end());
-    packed_[key + ".gb"] = pack(g, 2 * Cp, 9 * nhp, nullptr, !bf, bf);
+    if (bf) {
+      // fused epilogue: rows interleaved per N tile of cn channels, [gamma(cn) | beta(cn)], so that one TMEM
+      // accumulator tile holds both halves of the same channels (as the AAD layers, aei.cu); zero bias
+      const int cn = Cp < 128 ? Cp : 128;
+      const size_t K = static_cast<size_t>(9) * nhp;
+      std::vector<float> rows(static_cast<size_t>(2) * Cp * K);
+      for (int c = 0; c < Cp; ++c) {
+        const int t = c / cn, j = c % cn;
+        const size_t rg = static_cast<size_t>(t) * 2 * cn + j, rb = rg + cn;
+        memcpy(&rows[rg * K], &g[static_cast<size_t>(c) * K], sizeof(float) * K);
+        memcpy(&rows[rb * K], &b[static_cast<size_t>(c) * K], sizeof(float) * K);
+      }
+      std::vector<float> zero(2 * Cp, 0.f);
+      packed_[key + ".gb"] = pack(rows, 2 * Cp, 9 * nhp, &zero, false, true);
+    } else {
+      g.insert(g.end(), b.begin(), b.end());
+      packed_[key + ".gb"] = pack(g, 2 * Cp, 9 * nhp, nullptr, true, false);
+    }
   };
   // spectral-normalised conv: packed (unscaled) weight_orig + resident fp32 copy, u, v, 1/sigma
   auto add_sn_conv = [&](const std::string& key, int Co, int Ci, int k, bool bias) {
@@ -99,10 +134,13 @@ void Net::finalize_sr() {
     expect(w, {Co, Ci, k, k}, key + ".weight_orig");
     const int K = Ci * k * k;
     expect(W(key + ".weight_u"), {Co}, key + ".weight_u");
-    std::vector<float> rows = repack(w, Co, Ci, k, cp(Co), cp(Ci));
+    std::vector<float> rows = repack(w, Co, Ci, k, cpg(Co), cpg(Ci));
     std::vector<float> b;
-    if (bias) b = padded(W(key + ".bias").data, cp(Co));
-    packed_[key] = pack(rows, cp(Co), k * k * cp(Ci), bias ? &b : nullptr, !bf, bf);
+    if (bias) b = padded(W(key + ".bias").data, cpg(Co));
+    if (bf && k == 1)
+      packed_[key] = pack_ts(rows, cpg(Co), cpg(Ci), nullptr);  // conv_s: 1x1, no bias
+    else
+      packed_[key] = pack(rows, cpg(Co), k * k * cpg(Ci), bias ? &b : nullptr, !bf, bf);
     SnState st;
     st.R = Co;
     st.K = K;
@@ -124,8 +162,9 @@ void Net::finalize_sr() {
     if (b.fin != b.fout) add_spade(n + ".norm_s", b.fin, b.S);
   }
   for (int ri = 0; ri < 6; ++ri) {
+    if (!sr_actv_c_[ri]) continue;
+    if (bf) sr_actv_c_[ri] = cpg(sr_actv_c_[ri]);  // whole N tiles of the TMA-store epilogue (256^2: 320 -> 384)
     const int rows_n = sr_actv_c_[ri];
-    if (!rows_n) continue;
     std::vector<float> rows(static_cast<size_t>(rows_n) * 32, 0.f), bias(rows_n, 0.f);
     for (const Pending& pd : per_res[ri]) {
       const HostTensor& w = W(pd.key + ".mlp_shared.0.weight");
@@ -136,7 +175,7 @@ void Net::finalize_sr() {
     }
     char nm[32];
     snprintf(nm, sizeof(nm), "actv%d", 8 << ri);
-    packed_[nm] = pack(rows, rows_n, 32, &bias, !bf, bf);
+    packed_[nm] = bf ? pack_ts(rows, rows_n, 32, &bias) : pack(rows, rows_n, 32, &bias, true, false);
   }
 
   // ---- LIP encoder (generator.py:353-388)
@@ -145,7 +184,7 @@ void Net::finalize_sr() {
     expect(w, {48, 3, 3, 3}, "lip_encoder.model.0.weight");
     std::vector<float> rows(static_cast<size_t>(64) * 32, 0.f);
     patch_rows(w, 48, &rows, 0);
-    packed_["enc0"] = pack(rows, 64, 32, nullptr, !bf, bf);
+    packed_["enc0"] = bf ? pack_ts(rows, 64, 32, nullptr) : pack(rows, 64, 32, nullptr, true, false);
   }
   for (int i = 0; i < 5; ++i) {
     const int C = kSrEncC[i], Cn = kSrEncC[i + 1];
@@ -214,16 +253,18 @@ void Net::build_sr(ExecPlan& p) {
   };
   // real_flops: dense FLOPs of the unpadded layer (the padded channels are zeros, not work)
   auto add_conv = [&](const std::string& name, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
-                      const std::string& wname, const OutView& out, const Epilogue& epi, double real_flops) {
+                      const std::string& wname, const OutView& out, const Epilogue& epi, double real_flops,
+                      const AadArgs* aad = nullptr, double bytes = 0.0) {
     auto it = packed_.find(wname);
     if (it == packed_.end()) fail(-2, "internal: packed weights missing for " + wname);
     LaunchOp lop;
     lop.name = name;
-    check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, nullptr), name);
+    check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad), name);
     Op op;
     op.name = name;
     op.flops = real_flops;
-    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : kOpConvTC;
+    op.bytes = bytes;
+    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : (aad ? kOpAadTC : kOpConvTC);
     op.run = [lop](cudaStream_t s) { return lop.launch(s); };
     p.ops.push_back(std::move(op));
   };
@@ -242,14 +283,55 @@ void Net::build_sr(ExecPlan& p) {
     });
     return ss;
   };
+  // BatchNorm (training) statistics folded straight into the parameter table of the fused SPADE epilogue
+  auto add_norm_ncpar = [&](const std::string& name, const Act& x) -> float4* {
+    const int HW = x.H * x.W;
+    const int P = in_stats_parts(B, HW, x.C);
+    float* parts = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * P + 1) * x.C);
+    float4* nc = p.pool.alloc_n<float4>(static_cast<size_t>(B) * x.C);  // zeroed: the identity entries stay 0
+    const Act xx = x;
+    add_op(name + ".stats", [=](cudaStream_t s) {
+      return in_stats_launch_ex(xx.p, dt, B, HW, xx.C, parts, 1, s);
+    }, kOpStats, static_cast<double>(B) * HW * x.C * esz);
+    add_op(name + ".fold", [=](cudaStream_t s) {
+      return norm_fold_ncpar_launch(parts, P, B, HW, xx.C, 1e-5f, nc, s);
+    });
+    return nc;
+  };
+  // bf16 mode: out = act(conv + bias) through the TMA-store epilogue (weights packed by pack_ts)
+  float4* zero_nc = bf ? p.pool.alloc_n<float4>(static_cast<size_t>(B) * 512) : nullptr;  // stays zero
+  auto add_conv_ts = [&](const std::string& name, const Act& in, int Cin, const Taps& taps, const std::string& wname,
+                         const Act& out, float slope, double real_flops) {
+    AadArgs args;
+    args.c_x = out.C;
+    args.ncpar = zero_nc;
+    args.spade = 1;
+    args.no_h = 1;
+    args.slope = slope;
+    if (out.C > 512) fail(-1, "internal: add_conv_ts supports up to 512 output channels");
+    add_conv(name, in, 0, Cin, taps, out.H, out.W, wname, OutView::dense(out), Epilogue(), real_flops, &args,
+             static_cast<double>(B) * out.H * out.W * (out.C + Cin) * esz);
+  };
   const Taps t3 = Taps::square(3, 1, 1);
 
   // ------------------------------------------------------------------ spectral-norm power iterations
-  for (auto& kv : sr_sn_) {
-    const SnState st = kv.second;
-    add_op("sn." + kv.first, [=](cudaStream_t s) {
-      return sn_power_iter_launch(st.W, st.R, st.K, st.u, st.v, st.inv_sigma, st.scratch, s);
-    }, kOpMisc, 2.0 * st.R * st.K * 4.0);
+  {
+    std::vector<SnDesc> descs;
+    int max_R = 0, max_K = 0;
+    double bytes = 0.0;
+    for (auto& kv : sr_sn_) {
+      const SnState& st = kv.second;
+      descs.push_back(SnDesc{st.W, st.u, st.v, st.inv_sigma, st.scratch, st.R, st.K});
+      max_R = st.R > max_R ? st.R : max_R;
+      max_K = st.K > max_K ? st.K : max_K;
+      bytes += 2.0 * st.R * st.K * 4.0;
+    }
+    SnDesc* dd = reinterpret_cast<SnDesc*>(p.pool.alloc(descs.size() * sizeof(SnDesc)));
+    check_cuda(cudaMemcpy(dd, descs.data(), descs.size() * sizeof(SnDesc), cudaMemcpyHostToDevice), "sn table");
+    const int n = static_cast<int>(descs.size());
+    add_op("sn.power_iteration", [=](cudaStream_t s) {
+      return sn_power_iter_batched_launch(dd, n, max_R, max_K, s);
+    }, kOpMisc, bytes);
   }
 
   // ------------------------------------------------------------------ conditioning image
@@ -268,16 +350,22 @@ void Net::build_sr(ExecPlan& p) {
     Epilogue relu;
     relu.act1 = kActRelu;
     const std::string nm = "actv" + std::to_string(S);
-    add_conv("seg." + nm, pt, 0, 32, Taps::point(), S, S, nm, OutView::dense(actv[ri]), relu,
-             2.0 * B * S * S * 27.0 * packed_.at(nm).Cout);
+    const double fl = 2.0 * B * S * S * 27.0 * sr_actv_c_[ri];
+    if (bf && sr_actv_c_[ri] <= 512)
+      add_conv_ts("seg." + nm, pt, 32, Taps::point(), nm, actv[ri], 0.f, fl);
+    else
+      add_conv("seg." + nm, pt, 0, 32, Taps::point(), S, S, nm, OutView::dense(actv[ri]), relu, fl);
   }
 
   // ------------------------------------------------------------------ LIP encoder
   Act x;
   {
     Act e0 = new_act(256, 256, 64);
-    add_conv("enc.conv0", patches256, 0, 32, Taps::point(), 256, 256, "enc0", OutView::dense(e0), Epilogue(),
-             2.0 * B * 65536.0 * 27 * 48);
+    if (bf)
+      add_conv_ts("enc.conv0", patches256, 32, Taps::point(), "enc0", e0, 1.f, 2.0 * B * 65536.0 * 27 * 48);
+    else
+      add_conv("enc.conv0", patches256, 0, 32, Taps::point(), 256, 256, "enc0", OutView::dense(e0), Epilogue(),
+               2.0 * B * 65536.0 * 27 * 48);
     float2* ss = add_norm("enc.norm0", e0, false, nullptr, nullptr);
     x = new_act(256, 256, 64);
     const Act xx = x;
@@ -316,22 +404,52 @@ void Net::build_sr(ExecPlan& p) {
     const std::string n = b.name;
     const int S = b.S, HW = S * S;
     const int fmid = b.fin < b.fout ? b.fin : b.fout;
-    const int Ci = cp(b.fin), Cm = cp(fmid), Co = cp(b.fout);
+    const int Ci = cpg(b.fin), Cm = cpg(fmid), Co = cpg(b.fout);
     const bool learned = b.fin != b.fout;
     const Act xs = x;  // block input, at S/2 when b.up
     // batch statistics of x (identical for the nearest-upsampled tensor)
-    float2* ss_x = add_norm(n + ".bn_x", xs, true, nullptr, nullptr);
+    float4* nc_x = nullptr;
+    float2* ss_x = nullptr;
+    Act xfull = xs;  // bf16 mode: x at the block's resolution (the fused epilogue reads it by TMA)
+    if (bf) {
+      nc_x = add_norm_ncpar(n + ".bn_x", xs);
+      if (b.up) {
+        xfull = new_act(S, S, Ci);
+        const Act dst = xfull;
+        add_op(n + ".upsample", [=](cudaStream_t s) {
+          return nearest_up2x_launch(xs.p, dst.p, dt, B, xs.H, xs.W, xs.C, s);
+        }, kOpUpsample, 5.0 * B * xs.H * xs.W * xs.C * esz);
+      }
+    } else {
+      ss_x = add_norm(n + ".bn_x", xs, true, nullptr, nullptr);
+    }
 
     // one SPADE + activation: src (read through nearest x2 when up) -> dst, scaled by 1/sigma of the consumer conv
-    auto spade = [&](const std::string& nkey, const Act& src, int up, const float2* ss, int norm_nc, int act,
-                     const std::string& consumer) -> Act {
+    auto spade = [&](const std::string& nkey, const Act& src, int up, const float2* ss, const float4* ncpar,
+                     int norm_nc, int act, const std::string& consumer) -> Act {
       const SrSlice sl = sr_slices_.at(nkey);
-      const int Cp = cp(norm_nc), nh = nhid(norm_nc);
+      const int Cp = cpg(norm_nc), nh = nhid(norm_nc);
+      const float* post = sr_sn_.at(consumer).inv_sigma;
+      if (bf) {
+        // gamma/beta conv on the tensor cores with the modulation as its epilogue: x arrives by TMA, the result
+        // leaves by TMA store; gamma and beta never touch HBM
+        Act a = shared_act("mod", S, S, Cp);
+        AadArgs args;
+        args.h = src.p;
+        args.c_x = Cp;
+        args.ncpar = ncpar;
+        args.spade = 1;
+        args.slope = act == kSrLeaky02 ? 0.2f : act == kSrRelu ? 0.f : 1.f;
+        args.post = post;
+        add_conv(nkey + ".gemm_modulate", actv[sl.ri], sl.c0, sl.nhp, t3, S, S, nkey + ".gb", OutView::dense(a),
+                 Epilogue(), 2.0 * B * HW * 9.0 * nh * 2.0 * norm_nc, &args,
+                 static_cast<double>(B) * HW * (2.0 * Cp + sl.nhp) * esz);
+        return a;
+      }
       Act gb = shared_act("gb", S, S, 2 * Cp);
       add_conv(nkey + ".gamma_beta", actv[sl.ri], sl.c0, sl.nhp, t3, S, S, nkey + ".gb", OutView::dense(gb), Epilogue(),
                2.0 * B * HW * 9.0 * nh * 2.0 * norm_nc);
       Act a = shared_act("mod", S, S, Cp);
-      const float* post = sr_sn_.at(consumer).inv_sigma;
       const Act ss_src = src;
       add_op(nkey + ".modulate", [=](cudaStream_t s) {
         return spade_apply_launch(ss_src.p, gb.p, a.p, dt, B, S, S, Cp, up, ss, act, post, s);
@@ -339,27 +457,38 @@ void Net::build_sr(ExecPlan& p) {
       return a;
     };
 
+    const Act hsrc = bf ? xfull : xs;
+    const int hup = bf ? 0 : b.up;
     Act x_s;
     if (learned) {
-      Act a = spade(n + ".norm_s", xs, b.up, ss_x, b.fin, kSrNone, n + ".conv_s");
+      Act a = spade(n + ".norm_s", hsrc, hup, ss_x, nc_x, b.fin, kSrNone, n + ".conv_s");
       x_s = new_act(S, S, Co);
-      add_conv(n + ".conv_s", a, 0, Ci, Taps::point(), S, S, n + ".conv_s", OutView::dense(x_s), Epilogue(),
-               2.0 * B * HW * static_cast<double>(b.fin) * b.fout);
-    } else if (b.up) {
+      if (bf)
+        add_conv_ts(n + ".conv_s", a, Ci, Taps::point(), n + ".conv_s", x_s, 1.f,
+                    2.0 * B * HW * static_cast<double>(b.fin) * b.fout);
+      else
+        add_conv(n + ".conv_s", a, 0, Ci, Taps::point(), S, S, n + ".conv_s", OutView::dense(x_s), Epilogue(),
+                 2.0 * B * HW * static_cast<double>(b.fin) * b.fout);
+    } else if (b.up && !bf) {
       x_s = new_act(S, S, Ci);
       const Act dst = x_s;
       add_op(n + ".upsample", [=](cudaStream_t s) {
         return nearest_up2x_launch(xs.p, dst.p, dt, B, xs.H, xs.W, xs.C, s);
       }, kOpUpsample, 5.0 * B * xs.H * xs.W * xs.C * esz);
     } else {
-      x_s = xs;
+      x_s = xfull;
     }
-    Act a0 = spade(n + ".norm_0", xs, b.up, ss_x, b.fin, kSrLeaky02, n + ".conv_0");
+    Act a0 = spade(n + ".norm_0", hsrc, hup, ss_x, nc_x, b.fin, kSrLeaky02, n + ".conv_0");
     Act dx = new_act(S, S, Cm);
     add_conv(n + ".conv_0", a0, 0, Ci, t3, S, S, n + ".conv_0", OutView::dense(dx), Epilogue(),
              2.0 * B * HW * 9.0 * b.fin * fmid);
-    float2* ss_d = add_norm(n + ".bn_dx", dx, true, nullptr, nullptr);
-    Act a1 = spade(n + ".norm_1", dx, 0, ss_d, fmid, kSrLeaky02, n + ".conv_1");
+    float2* ss_d = nullptr;
+    float4* nc_d = nullptr;
+    if (bf)
+      nc_d = add_norm_ncpar(n + ".bn_dx", dx);
+    else
+      ss_d = add_norm(n + ".bn_dx", dx, true, nullptr, nullptr);
+    Act a1 = spade(n + ".norm_1", dx, 0, ss_d, nc_d, fmid, kSrLeaky02, n + ".conv_1");
     Act out = new_act(S, S, Co);
     Epilogue e;
     {

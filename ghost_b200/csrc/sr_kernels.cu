@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256) seg_patches_kernel(const T* __restrict__ 
 __global__ void __launch_bounds__(1024) norm_fold_kernel(const float* __restrict__ parts, int P, int N, int HW, int C,
                                                           int pool_n, const float* __restrict__ weight,
                                                           const float* __restrict__ bias, float eps,
-                                                          float2* __restrict__ ss) {
+                                                          float2* __restrict__ ss, float4* __restrict__ ncpar) {
   __shared__ double shs[64][16], shq[64][16];
   const int cl = threadIdx.x & 15, lane = threadIdx.x >> 4;
   const int c = blockIdx.x * 16 + cl;
@@ -143,7 +143,15 @@ __global__ void __launch_bounds__(1024) norm_fold_kernel(const float* __restrict
     const float rstd = 1.0f / sqrtf(var + eps);
     const float sc = (weight ? weight[c] : 1.f) * rstd;
     const float sh = (bias ? bias[c] : 0.f) - mu * sc;
-    if (pool_n) {
+    if (ncpar) {
+      // parameter table of the fused tcgen05 epilogue (igemm.cuh): per channel pair {scale0, scale1, shift0, shift1}
+      // followed by the (unused, zero) identity entry; the same batch statistics for every image
+      for (int n = 0; n < N; ++n) {
+        float* pp = reinterpret_cast<float*>(ncpar + static_cast<long long>(n) * C + (c & ~1)) + (c & 1);
+        pp[0] = sc;
+        pp[2] = sh;
+      }
+    } else if (pool_n) {
       ss[c] = make_float2(sc, sh);
     } else {
       ss[static_cast<long long>(n0) * C + c] = make_float2(sc, sh);
@@ -216,8 +224,13 @@ __global__ void __launch_bounds__(256) lip_pool_kernel(const T* __restrict__ x, 
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float z = fmaf(lv[i], sc[i], sh[i]);
-        const float g = 12.0f / (1.0f + expf(-z));  // SoftGate: sigmoid * 12
-        const float w = expf(g);
+        float w;
+        if (sizeof(T) == 2) {  // bf16 storage: the hardware ex2 path is far inside the storage precision
+          w = __expf(__fdividef(12.0f, 1.0f + __expf(-z)));
+        } else {
+          const float g = 12.0f / (1.0f + expf(-z));  // SoftGate: sigmoid * 12
+          w = expf(g);
+        }
         num[i] = fmaf(xv[i], w, num[i]);
         den[i] += w;
       }
@@ -412,7 +425,14 @@ const char* seg_patches_launch(const void* img, void* patches, int dtype, int N,
 const char* norm_fold_launch(const float* parts, int P, int N, int HW, int C, int pool_n, const float* weight,
                              const float* bias, float eps, float2* ss, cudaStream_t s) {
   dim3 grid((C + 15) / 16, pool_n ? 1 : N);
-  norm_fold_kernel<<<grid, 1024, 0, s>>>(parts, P, N, HW, C, pool_n, weight, bias, eps, ss);
+  norm_fold_kernel<<<grid, 1024, 0, s>>>(parts, P, N, HW, C, pool_n, weight, bias, eps, ss, nullptr);
+  return last_err();
+}
+
+const char* norm_fold_ncpar_launch(const float* parts, int P, int N, int HW, int C, float eps, float4* ncpar,
+                                   cudaStream_t s) {
+  dim3 grid((C + 15) / 16, 1);
+  norm_fold_kernel<<<grid, 1024, 0, s>>>(parts, P, N, HW, C, 1, nullptr, nullptr, eps, nullptr, ncpar);
   return last_err();
 }
 
@@ -482,6 +502,69 @@ const char* nearest_up2x_launch(const void* x, void* y, int dtype, int N, int H,
                                                               reinterpret_cast<__nv_bfloat16*>(y), total8, H, W, C);
   else
     return "nearest_up2x: unsupported dtype";
+  return last_err();
+}
+
+// ---- the same four steps for a whole table of convs at once (blockIdx.z = conv): the per-conv launches are
+// latency bound (18 convs x 4 launches of a few microseconds each)
+__global__ void __launch_bounds__(256) sn_wtu_batched(const SnDesc* __restrict__ d) {
+  const SnDesc c = d[blockIdx.z];
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= c.K) return;
+  const int rows = (c.R + kSnRowChunks - 1) / kSnRowChunks;
+  const int r0 = blockIdx.y * rows, r1 = min(c.R, r0 + rows);
+  float a = 0.f;
+  for (int r = r0; r < r1; ++r) a = fmaf(__ldg(c.W + static_cast<long long>(r) * c.K + k), c.u[r], a);
+  c.scratch[static_cast<long long>(blockIdx.y) * c.K + k] = a;
+}
+__global__ void __launch_bounds__(1024) sn_v_batched(const SnDesc* __restrict__ d) {
+  __shared__ float red[32];
+  const SnDesc c = d[blockIdx.z];
+  float loc = 0.f;
+  for (int k = threadIdx.x; k < c.K; k += 1024) {
+    float t = 0.f;
+    for (int y = 0; y < kSnRowChunks; ++y) t += c.scratch[static_cast<long long>(y) * c.K + k];
+    c.v[k] = t;
+    loc = fmaf(t, t, loc);
+  }
+  const float nrm = sqrtf(block_sum_1024(loc, red));
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+  for (int k = threadIdx.x; k < c.K; k += 1024) c.v[k] *= inv;
+}
+__global__ void __launch_bounds__(256) sn_wv_batched(const SnDesc* __restrict__ d) {
+  const SnDesc c = d[blockIdx.z];
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (r >= c.R) return;
+  const int lane = threadIdx.x & 31;
+  float a = 0.f;
+  for (int k = lane; k < c.K; k += 32) a = fmaf(__ldg(c.W + static_cast<long long>(r) * c.K + k), c.v[k], a);
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) c.scratch[static_cast<long long>(kSnRowChunks) * c.K + r] = a;
+}
+__global__ void __launch_bounds__(1024) sn_u_batched(const SnDesc* __restrict__ d) {
+  __shared__ float red[32];
+  const SnDesc c = d[blockIdx.z];
+  const float* wv = c.scratch + static_cast<long long>(kSnRowChunks) * c.K;
+  float loc = 0.f;
+  for (int r = threadIdx.x; r < c.R; r += 1024) loc = fmaf(wv[r], wv[r], loc);
+  const float nrm = sqrtf(block_sum_1024(loc, red));
+  const float inv = 1.0f / fmaxf(nrm, 1e-12f);
+  float dot = 0.f;
+  for (int r = threadIdx.x; r < c.R; r += 1024) {
+    const float un = wv[r] * inv;
+    c.u[r] = un;
+    dot = fmaf(un, wv[r], dot);
+  }
+  const float sigma = block_sum_1024(dot, red);
+  if (threadIdx.x == 0) c.inv_sigma[0] = 1.0f / sigma;
+}
+
+const char* sn_power_iter_batched_launch(const SnDesc* descs_dev, int n, int max_R, int max_K, cudaStream_t s) {
+  if (n <= 0) return nullptr;
+  sn_wtu_batched<<<dim3((max_K + 255) / 256, kSnRowChunks, n), 256, 0, s>>>(descs_dev);
+  sn_v_batched<<<dim3(1, 1, n), 1024, 0, s>>>(descs_dev);
+  sn_wv_batched<<<dim3((max_R + 7) / 8, 1, n), 256, 0, s>>>(descs_dev);
+  sn_u_batched<<<dim3(1, 1, n), 1024, 0, s>>>(descs_dev);
   return last_err();
 }
 

@@ -25,6 +25,10 @@ const char* seg_patches_launch(const void* img_nhwc3, void* patches, int dtype, 
 // shift = bias[c] - mean * scale (weight / bias may be null = 1 / 0); biased variance, eps inside the sqrt.
 const char* norm_fold_launch(const float* parts, int P, int N, int HW, int C, int pool_n, const float* weight,
                              const float* bias, float eps, float2* ss, cudaStream_t s);
+// BatchNorm (training) fold written as the parameter table of the fused tcgen05 SPADE epilogue (igemm.cuh `ncpar`):
+// [N][C] float4, per channel pair {scale0, scale1, shift0, shift1}, {0, 0, 0, 0}; the table must start zeroed.
+const char* norm_fold_ncpar_launch(const float* parts, int P, int N, int HW, int C, float eps, float4* ncpar,
+                                   cudaStream_t s);
 // in_stats_launch with one shift per channel shared by all images (sums become additive over the batch)
 const char* in_stats_launch_ex(const void* x, int dtype, int N, int HW, int C, float* parts, int common_shift,
                                cudaStream_t s);
@@ -53,6 +57,14 @@ const char* nearest_up2x_launch(const void* x, void* y, int dtype, int N, int H,
 size_t sn_scratch_floats(int R, int K);
 const char* sn_power_iter_launch(const float* W, int R, int K, float* u, float* v, float* inv_sigma, float* scratch,
                                  cudaStream_t s);
+
+// The same iteration for a table of convs in four launches (blockIdx.z = conv); descs_dev is a device array.
+struct SnDesc {
+  const float* W;
+  float *u, *v, *inv_sigma, *scratch;
+  int R, K;
+};
+const char* sn_power_iter_batched_launch(const SnDesc* descs_dev, int n, int max_R, int max_K, cudaStream_t s);
 
 // face_enhancement pre/post (video_processing.py:253-256, 277-282)
 const char* sr_preproc_launch(const uint8_t* crops_bgr, void* dst_nhwc3, int dtype, int N, int HW, cudaStream_t s);
