@@ -267,7 +267,7 @@ def run_ours(args):
                     "unit": "GB/s", "frac": a / pk["hbm"], "ms_per_step": ms}
         roofline_hbm = [hbm(aad_ms, aad_by, aad_n, "igemm_kernel AAD mode (gamma/beta GEMM + fused IN/mask/blend/ReLU)"),
                         hbm(st_ms, st_by, st_n, "in_stats_kernel"), hbm(up_ms, up_by, up_n, "upsample2x_kernel"),
-                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 3, "paste-back: frame copy + resize_crops_kernel + paste_faces_kernel (exact mode)")]
+                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 2, "paste-back: resize_crops_kernel + paste_frames_kernel (copy + composite in one pass, exact mode)")]
 
         n_launch_g, flops_g = G.stats(B)
         n_launch_a, flops_a = arc.stats(B)
@@ -299,15 +299,138 @@ def run_ours(args):
     return 0
 
 
+def run_config5(args):
+    """BASELINE.json configs[4]: AEI_Net('linknet', 3) bf16 -> pix2pix super-resolution generator
+    (LIPSPADEGenerator, train-mode semantics, DataLoader batches of 20 as face_enhancement) -> paste-back of the
+    enhanced crops into 1080p frames.  Reference-faithful variant: the SR generator is size-preserving (256 -> 256,
+    SURVEY 8d config 5 (i)).  One step = 60 faces per GPU (three SR batches)."""
+    import torch.distributed as dist
+    import ghost_b200
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    pk = peaks()
+    B5, SRB = 60, 20
+    G = ghost_b200.AEI_Net("linknet", 3, 512, seed=0).eval().bfloat16().cuda().enable_graph(True)
+    arc = ghost_b200.iresnet100().eval().bfloat16().cuda().enable_graph(True)
+    SR = ghost_b200.LIPSPADEGenerator().bfloat16().cuda().enable_graph(True)
+    sources_h, crops_h, frames_h, masks_h, tfms = make_inputs(rank)
+    sl = slice(0, B5)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    sources_p, crops_p, frames_p, masks_p = pin(sources_h[sl]), pin(crops_h[sl]), pin(frames_h[sl]), pin(masks_h[sl])
+    out_p = torch.empty_like(frames_p).pin_memory()
+    tf = tfms[sl]
+    face_frame = np.arange(B5, dtype=np.int32)
+    sources_d, crops_d, frames_d, masks_d = sources_p.to(dev), crops_p.to(dev), frames_p.to(dev), masks_p.to(dev)
+    out_d = torch.empty_like(frames_d)
+    swapped = torch.empty_like(crops_d)
+    enhanced = torch.empty_like(crops_d)
+
+    def step(src, crp, frm, msk, out):
+        z = arc.embed_hwc(src, out_dtype=torch.bfloat16)
+        G.swap_u8(crp, z, out=swapped)
+        for b0 in range(0, B5, SRB):
+            SR.enhance_u8(swapped[b0:b0 + SRB], out=enhanced[b0:b0 + SRB])
+        ghost_b200.paste_back(frm, enhanced, msk, tf, face_frame, mode="exact", out=out)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(sources_d, crops_d, frames_d, masks_d, out_d)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step(sources_d, crops_d, frames_d, masks_d, out_d)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.summary()
+    # end to end: pinned host buffers in, composited frames back to the host, every step (one stream)
+    def step_e2e():
+        s_, c_, f_, m_ = (t.to(dev, non_blocking=True) for t in (sources_p, crops_p, frames_p, masks_p))
+        step(s_, c_, f_, m_, out_d)
+        out_p.copy_(out_d, non_blocking=True)
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    line = None
+    if rank == 0:
+        prof = SR.profile(SRB, reps=3)
+        conv = [o for o in prof if o["cls"] in (0, 1)]
+        conv_ms, conv_fl = sum(o["ms"] for o in conv), sum(o["flops"] for o in conv)
+        conv_tf = conv_fl / (conv_ms * 1e-3) / 1e12
+        n_g, fl_g = G.stats(B5)
+        n_a, fl_a = arc.stats(B5)
+        n_s, fl_s = SR.stats(SRB)
+        h2d = sum(x.numel() * x.element_size() for x in (sources_p, crops_p, frames_p, masks_p))
+        line = {
+            "metric": METRIC, "value": B5 * world * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "configs[4]: AEI_Net(linknet, num_blocks=3) bf16 + ArcFace z_id -> pix2pix SR generator "
+                                   "(LIPSPADEGenerator, train-mode batch statistics, batches of 20, 256->256 as the reference) "
+                                   "-> exact paste-back into 1080p frames, 60 faces per step per GPU",
+                       "faces_per_step_per_gpu": B5, "sr_batch": SRB, "frame": "%dx%d" % (W, H),
+                       "parallelism": "frames sharded over %d GPU(s) on SR-batch boundaries, no collective in the step" % world,
+                       "l2": "inputs larger than L2 (weights ~0.8 GB + frames 0.75 GB per step)"},
+            "e2e": {"value": B5 * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(out_p.numel()), "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int((n_g + n_a + 3 * n_s + 3 * 2 + 4) * args.steps),
+            "clocks": clocks,
+            "roofline": {"kernel": "igemm_kernel in the SR generator (tcgen05 convs incl. fused SPADE modulation, %d launches per batch of 20)" % len(conv),
+                         "bound": "tensor", "achieved": conv_tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                         "frac": conv_tf / pk["tf_sustained"], "traffic": None,
+                         "peak_source": pk["source"] + ", sustained",
+                         "note": "algorithmic FLOPs of the unpadded layers (48/96/192-channel layers run padded to 64/128/256)"},
+            "sr_ms_per_batch20": sum(o["ms"] for o in prof),
+            "flops_per_step": fl_g + fl_a + 3 * fl_s,
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="default", choices=["default", "config5"],
+                    help="default = BASELINE.json configs[1] + paste-back (the headline line); config5 = linknet/3 + SR")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "config5":
+        return run_config5(args)
     return run_ours(args)
 
 
