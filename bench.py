@@ -267,7 +267,7 @@ def run_ours(args):
                     "unit": "GB/s", "frac": a / pk["hbm"], "ms_per_step": ms}
         roofline_hbm = [hbm(aad_ms, aad_by, aad_n, "igemm_kernel AAD mode (gamma/beta GEMM + fused IN/mask/blend/ReLU)"),
                         hbm(st_ms, st_by, st_n, "in_stats_kernel"), hbm(up_ms, up_by, up_n, "upsample2x_kernel"),
-                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 2, "paste-back: resize_crops_kernel + paste_frames_kernel (copy + composite in one pass, exact mode)")]
+                        hbm(paste_ms, PASTE_BYTES_PER_FACE * B, 3, "paste-back: frame copy + resize_crops_kernel + paste_faces_kernel (exact mode)")]
 
         n_launch_g, flops_g = G.stats(B)
         n_launch_a, flops_a = arc.stats(B)

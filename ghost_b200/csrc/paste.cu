@@ -183,88 +183,6 @@ __global__ void __launch_bounds__(256) paste_faces_kernel(const PasteParams p) {
   }
 }
 
-// Single pass over whole frames (frames_out != frames_in): frames in -> out and the composite in one kernel, so
-// every frame byte crosses HBM once in each direction.  A thread owns a span of 4 pixels of one row (12 bytes =
-// three aligned 32-bit words when kWords); spans that touch no face box of their frame are a plain copy, the others
-// composite every face of the frame in list order per pixel - the same arithmetic, pixel by pixel, as
-// paste_faces_kernel (no ownership rule needed: each pixel belongs to exactly one thread).
-template <bool kWords>
-__global__ void __launch_bounds__(256) paste_frames_kernel(const PasteParams p) {
-  const int spans = (p.W + 3) >> 2;
-  const long long total = static_cast<long long>(p.F) * p.H * spans;
-  const long long t = blockIdx.x * 256LL + threadIdx.x;
-  if (t >= total) return;
-  const int sx = static_cast<int>(t % spans);
-  const long long r = t / spans;
-  const int y = static_cast<int>(r % p.H), f = static_cast<int>(r / p.H);
-  const int x0 = sx * 4;
-  const int npx = min(4, p.W - x0);
-  const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x0) * 3;
-  uint32_t w[3] = {0u, 0u, 0u};
-  if (kWords) {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(p.frames_in + off);
-    w[0] = __ldg(src);
-    w[1] = __ldg(src + 1);
-    w[2] = __ldg(src + 2);
-  } else {
-    for (int i = 0; i < 3 * npx; ++i) w[i >> 2] |= static_cast<uint32_t>(p.frames_in[off + i]) << (8 * (i & 3));
-  }
-  const int fs = __ldg(p.face_start + f), fe = __ldg(p.face_start + f + 1);
-  bool hit = false;
-  for (int k = fs; k < fe; ++k) {
-    const PasteFace& o = p.faces[k];
-    hit = hit || (y >= o.y0 && y < o.y1 && x0 < o.x1 && x0 + npx > o.x0);
-  }
-  if (hit) {
-    for (int i = 0; i < npx; ++i) {
-      const int x = x0 + i;
-      int b[3];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const int bi = 3 * i + c;
-        b[c] = static_cast<int>((w[bi >> 2] >> (8 * (bi & 3))) & 255u);
-      }
-      bool any = false;
-      if (p.mode == kPasteExact) {
-        double fd[3] = {static_cast<double>(b[0]), static_cast<double>(b[1]), static_cast<double>(b[2])};
-        for (int k = fs; k < fe; ++k) {
-          const PasteFace& face = p.faces[k];
-          if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
-          paste_exact_px(p, face, x, y, fd);
-          any = true;
-        }
-#pragma unroll
-        for (int c = 0; c < 3; ++c) b[c] = static_cast<int>(static_cast<uint8_t>(static_cast<int>(fd[c])));
-      } else {
-        float ff[3] = {static_cast<float>(b[0]), static_cast<float>(b[1]), static_cast<float>(b[2])};
-        for (int k = fs; k < fe; ++k) {
-          const PasteFace& face = p.faces[k];
-          if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
-          paste_float_px(p, face, x, y, ff);
-          any = true;
-        }
-#pragma unroll
-        for (int c = 0; c < 3; ++c) b[c] = static_cast<int>(static_cast<uint8_t>(static_cast<int>(ff[c])));
-      }
-      if (any) {
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const int bi = 3 * i + c, sh = 8 * (bi & 3);
-          w[bi >> 2] = (w[bi >> 2] & ~(255u << sh)) | (static_cast<uint32_t>(b[c]) << sh);
-        }
-      }
-    }
-  }
-  if (kWords) {
-    uint32_t* dst = reinterpret_cast<uint32_t*>(p.frames_out + off);
-    dst[0] = w[0];
-    dst[1] = w[1];
-    dst[2] = w[2];
-  } else {
-    for (int i = 0; i < 3 * npx; ++i) p.frames_out[off + i] = static_cast<uint8_t>((w[i >> 2] >> (8 * (i & 3))) & 255u);
-  }
-}
-
 template <typename T>
 __device__ __forceinline__ void st_act(T* p, float v);
 template <>
@@ -409,26 +327,12 @@ void paste_prepare_face(PasteFace* f, const double* t, int H, int W, int crop_in
 
 const char* paste_back_launch(PasteParams p, const PasteFace* host_faces, cudaStream_t s) {
   if (p.F <= 0 || p.H <= 0 || p.W <= 0) return "paste_back: empty frame batch";
-  const bool in_place = p.frames_out == p.frames_in;
-  if (!in_place && p.n_faces <= 0) {
+  if (p.frames_out != p.frames_in) {
     const size_t bytes = static_cast<size_t>(p.F) * p.H * p.W * 3;
     cudaError_t e = cudaMemcpyAsync(p.frames_out, p.frames_in, bytes, cudaMemcpyDeviceToDevice, s);
     if (e != cudaSuccess) return cudaGetErrorString(e);
   }
   if (p.n_faces <= 0) return last_err();
-  if (!in_place) {
-    // out of place: one fused pass (copy + composite), every frame byte is read once and written once
-    resize_crops_kernel<<<grid_for(static_cast<long long>(p.n_crops) * 224 * 224, 256), 256, 0, s>>>(p);
-    const long long total = static_cast<long long>(p.F) * p.H * ((p.W + 3) >> 2);
-    const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
-    const bool words = (p.W % 4 == 0) && (reinterpret_cast<uintptr_t>(p.frames_in) % 4 == 0) &&
-                       (reinterpret_cast<uintptr_t>(p.frames_out) % 4 == 0);
-    if (words)
-      paste_frames_kernel<true><<<blocks, 256, 0, s>>>(p);
-    else
-      paste_frames_kernel<false><<<blocks, 256, 0, s>>>(p);
-    return last_err();
-  }
   p.max_bw = p.max_bh = 0;
   for (int i = 0; i < p.n_faces; ++i) {
     const int bw = host_faces[i].x1 - host_faces[i].x0, bh = host_faces[i].y1 - host_faces[i].y0;
