@@ -71,10 +71,13 @@ SIGNATURES = {
     "ghost_preproc_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ghost_postproc_u8": (_i, [_vp, _i, _vp, _i, _vp]),
     "ghost_paste_back": (_i, [C.POINTER(PasteDesc), _vp]),
+    "ghost_face_masks": (_i, [_fp, C.POINTER(_i), _i, _vp, _i, _vp]),
     "ghost_test_conv": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _i, _vp]),
     "ghost_test_aad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f,
                             _vp, _i, _vp]),
     "ghost_test_last_error": (C.c_char_p, []),
+    "ghost_test_mask_job": (_i, [_fp, _i, _i, _i, C.POINTER(C.c_uint32), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16),
+                                C.POINTER(_i)]),
     "ghost_test_upsample2x": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "ghost_test_upsample2x_stats": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _fp, _fp, _vp]),
 }

@@ -568,18 +568,19 @@ class SwapPipeline(object):
                 main.wait_event(slot["ev_out"])
 
 
-def _masks_from_handler(swaps224, crop_frames, handler, params):
-    from .masks import face_mask_static
-    masks = []
+def _masks_from_handler(swaps224, crop_frames, handler, params, dtype=torch.float64):
+    """Landmarks from the caller's handler (the landmark model is out of scope), masks on the device: the preset
+    choice of face_mask_static (masks.py:43-69) per face, then one batched ghost_face_masks call.
+    Returns a device tensor [n,224,224]; params[j] is filled in where it was None."""
+    from .masks import choose_params, face_masks
+    lms = []
     for j, (swap, tgt) in enumerate(zip(swaps224, crop_frames)):
         lm = handler.get_without_detection_without_transform(swap)
         lm_t = handler.get_without_detection_without_transform(tgt)
         if params[j] is None:
-            m, params[j] = face_mask_static(tgt, lm, lm_t, None)
-        else:
-            m = face_mask_static(tgt, lm, lm_t, params[j])
-        masks.append(m)
-    return masks
+            params[j] = choose_params(lm, lm_t)
+        lms.append(np.asarray(lm, dtype=np.float32))
+    return face_masks(np.stack(lms), [list(p) for p in params], dtype=dtype)
 
 
 def get_final_image(final_frames, crop_frames, full_frame, tfm_arrays, handler=None, masks=None):
@@ -597,8 +598,10 @@ def get_final_image(final_frames, crop_frames, full_frame, tfm_arrays, handler=N
         masks = _masks_from_handler(swaps, [crop_frames[i][0] for i in range(n)], handler, [None] * n)
     crops = np.stack([np.asarray(final_frames[i][0], dtype=np.uint8) for i in range(n)])
     tf = np.stack([np.asarray(tfm_arrays[i][0], dtype=np.float64) for i in range(n)])
-    out = paste_back(np.asarray(full_frame, dtype=np.uint8)[None], crops, np.stack(masks).astype(np.float64), tf,
-                     np.zeros(n, np.int32), mode="exact")
+    if not isinstance(masks, torch.Tensor):
+        masks = np.stack(masks).astype(np.float64)
+    out = paste_back(np.asarray(full_frame, dtype=np.uint8)[None], crops, masks, tf, np.zeros(n, np.int32),
+                     mode="exact")
     return out[0].cpu().numpy()
 
 
@@ -626,16 +629,17 @@ def get_final_video(final_frames, crop_frames, full_frames, tfm_array, OUT_VIDEO
                     import cv2
                     swap = cv2.resize(final_frames[j][i], (224, 224))
                     p = [params[j]]
-                    m = _masks_from_handler([swap], [crop_frames[j][i]], handler, p)[0]
+                    m = _masks_from_handler([swap], [crop_frames[j][i]], handler, p, dtype=torch.float32)[0]
                     params[j] = p[0]
                 crops.append(np.asarray(final_frames[j][i], dtype=np.uint8))
-                mks.append(np.asarray(m, dtype=np.float32))
+                mks.append(m if isinstance(m, torch.Tensor) else torch.from_numpy(np.asarray(m, dtype=np.float32)))
                 tfs.append(np.asarray(tfm_array[j][i], dtype=np.float64))
                 ffr.append(i - c0)
         frames = np.stack([np.asarray(f, dtype=np.uint8) for f in full_frames[c0:c1]])
         if crops:
-            out = paste_back(frames, np.stack(crops), np.stack(mks), np.stack(tfs), np.asarray(ffr, np.int32),
-                             mode="float").cpu().numpy()
+            dev = torch.device("cuda", torch.cuda.current_device())
+            out = paste_back(frames, np.stack(crops), torch.stack([m.to(dev) for m in mks]), np.stack(tfs),
+                             np.asarray(ffr, np.int32), mode="float").cpu().numpy()
         else:
             out = frames
         result.extend(list(out))

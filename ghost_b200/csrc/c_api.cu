@@ -6,6 +6,7 @@
 #include "../../include/ghost_b200.h"
 #include "net.cuh"
 #include "sr_kernels.cuh"
+#include "mask.cuh"
 
 using namespace ghost;
 
@@ -365,6 +366,25 @@ int ghost_postproc_u8(const void* y, int y_dtype, uint8_t* dst, int B, void* str
   return guarded([&] {
     require(y && dst && B > 0, "bad argument");
     check_msg(postproc_u8_launch(y, y_dtype, dst, static_cast<long long>(B) * 65536, S(stream)), "postproc");
+  });
+}
+
+int ghost_face_masks(const float* landmarks, const int* params, int n, void* masks_out, int mask_f64, void* stream) {
+  return guarded([&] {
+    require(landmarks && params && masks_out && n > 0, "bad argument");
+    cudaStream_t s = S(stream);
+    std::vector<MaskJob> jobs(n);
+    for (int i = 0; i < n; ++i)
+      check_msg(mask_prepare_job(&jobs[i], landmarks + static_cast<size_t>(i) * 212, params[3 * i], params[3 * i + 1],
+                                 params[3 * i + 2]), "face mask");
+    // own allocation (stream-ordered), so the call stays re-entrant next to ghost_paste_back's scratch
+    MaskJob* dev = nullptr;
+    check_cuda(cudaMallocAsync(reinterpret_cast<void**>(&dev), jobs.size() * sizeof(MaskJob), s), "mask jobs alloc");
+    check_cuda(cudaMemcpyAsync(dev, jobs.data(), jobs.size() * sizeof(MaskJob), cudaMemcpyHostToDevice, s), "mask jobs upload");
+    // pageable source: the copy has been staged by the time cudaMemcpyAsync returns, `jobs` may go out of scope
+    const char* err = face_masks_launch(dev, n, masks_out, mask_f64, s);
+    cudaFreeAsync(dev, s);
+    check_msg(err, "face masks");
   });
 }
 

@@ -4,6 +4,7 @@
 
 #include "../../include/ghost_b200.h"
 #include "net.cuh"
+#include "mask.cuh"
 
 using namespace ghost;
 
@@ -227,6 +228,29 @@ int ghost_test_upsample2x_stats(const void* x, void* y, int dtype, int N, int H,
         var_host[static_cast<size_t>(n) * C + c] = static_cast<float>(sq / HWo - d * d);
       }
   });
+}
+
+// Host half of the mask synthesis (no device work): the rasterised hull bitmap [224*7] and the two fixed-point
+// Gaussian kernels of one face; nxny receives {nx, ny}.
+int ghost_test_mask_job(const float* landmarks, int erode, int sigma_x, int sigma_y, uint32_t* bitmap, uint16_t* kx,
+                        uint16_t* ky, int* nxny) {
+  try {
+    std::vector<MaskJob> job(1);
+    const char* err = mask_prepare_job(&job[0], landmarks, erode, sigma_x, sigma_y);
+    if (err) {
+      g_err = err;
+      return -1;
+    }
+    memcpy(bitmap, job[0].bitmap, sizeof(job[0].bitmap));
+    memcpy(kx, job[0].kx, sizeof(job[0].kx));
+    memcpy(ky, job[0].ky, sizeof(job[0].ky));
+    nxny[0] = job[0].nx;
+    nxny[1] = job[0].ny;
+    return 0;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1;
+  }
 }
 
 }  // extern "C"

@@ -15,6 +15,7 @@
  *   utils/inference/image_processing.py:23-48,51-77   normalize_and_torch(_batch), get_final_image
  *   utils/inference/video_processing.py:191-243       get_final_video (compositing only)
  *   utils/inference/video_processing.py:246-285       Frames / face_enhancement
+ *   utils/inference/masks.py:39-108                   face_mask_static / erode_and_blur
  *   models/pix2pix_model.py:42-62, models/networks/generator.py:93-137,390-400   Pix2PixModel 'inference2' -> LIPSPADEGenerator
  */
 #ifndef GHOST_B200_H_
@@ -167,6 +168,18 @@ typedef struct {
 
 int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
 
+/* ---- blend-mask synthesis (utils/inference/masks.py:39-108 face_mask_static + erode_and_blur, called at
+ * image_processing.py:68 and video_processing.py:221-223), bit-exact against the reference's OpenCV calls:
+ *   landmarks [n][106][2] float32 (host): the 106-point landmarks of the swapped 224x224 crop, as
+ *             Handler.get_without_detection_without_transform returns them;
+ *   params    [n][3] int (host): erode, sigmaX, sigmaY - the preset face_mask_static picked (masks.py:43-69) or the
+ *             caller's `params`; erode < 0 dilates;
+ *   masks_out [n][224][224] on the device, float64 (mask_f64 = 1, get_final_image) or float32 (get_final_video),
+ *             the layout ghost_paste_desc.masks reads.
+ * Eyebrow lift, convex hull and polygon rasterisation run on the host (integer work on 106 points), erode / dilate,
+ * border clip and the fixed-point Gaussian blur on the device, one CTA per face. */
+int ghost_face_masks(const float* landmarks, const int* params, int n, void* masks_out, int mask_f64, void* stream);
+
 /* ---- single-op entry points used by the kernel-level parity tests (tests/test_kernels_gpu.py).
  * conv: NHWC activations (dtype = mode); weights fp32 on the host in the reference layout:
  * kind 0 = nn.Conv2d(k,stride,pad) weight [Cout][Cin][k][k], kind 1 = nn.ConvTranspose2d(k=4,s=2,p=1) weight
@@ -185,6 +198,11 @@ int ghost_test_upsample2x(const void* x_nhwc, void* y_nhwc, int dtype, int N, in
  * network/AEI_Net.py:124-138 + network/AADLayer.py:21); mean / biased variance per (n, c) come back on the host. */
 int ghost_test_upsample2x_stats(const void* x_nhwc, void* y_nhwc, int dtype, int N, int H, int W, int C,
                                 float* mean_host, float* var_host, void* stream);
+
+/* Host half of ghost_face_masks for one face (no device work): hull bitmap (224 rows x 7 words, bit x of row y =
+ * pixel (y, x)) and the fixed-point Gaussian kernels (128 entries each, nxny = {nx, ny} taps used). */
+int ghost_test_mask_job(const float* landmarks, int erode, int sigma_x, int sigma_y, uint32_t* bitmap, uint16_t* kx,
+                        uint16_t* ky, int* nxny);
 
 #ifdef __cplusplus
 }
