@@ -33,6 +33,29 @@ BACKBONE, NUM_BLOCKS = "unet", 2
 PASTE_BYTES_PER_FACE = 13.2e6  # frame r+w 12.44 MB + Y 0.39 MB + mask <= 0.4 MB
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on fd 1),
+    so everything else is sent to stderr for the duration of the run and the line goes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -129,7 +152,7 @@ def run_reference(args):
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -223,10 +246,29 @@ def run_ours(args):
     barrier()
     ms_e2e = f0.elapsed_time(f1)
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
+    # ---------------------------------------------------------------- with the final frame gather, N > 1
+    # The only exchange of the path: every rank's finished uint8 frames go to rank 0 in frame order (NCCL send /
+    # recv over NVLink, ghost_b200.FrameSharder.gather); device-resident like `value`, one gather per step.
+    ms_gather = 0.0
+    if world > 1:
+        sharder = ghost_b200.FrameSharder(B * world, rank, world)
+        for _ in range(2):
+            step_device(sources_d, crops_d, frames_d, out_d)
+            sharder.gather(out_d, dst=0)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(args.steps):
+            step_device(sources_d, crops_d, frames_d, out_d)
+            sharder.gather(out_d, dst=0)
+        g1.record()
+        barrier()
+        ms_gather = g0.elapsed_time(g1)
+
+    t = torch.tensor([ms_total, ms_e2e, ms_gather], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
+    ms_total, ms_e2e, ms_gather = float(t[0]), float(t[1]), float(t[2])
 
     # ---------------------------------------------------------------- per-kernel-class roofline (rank 0)
     line = None
@@ -291,11 +333,17 @@ def run_ours(args):
                                       "paste_back": paste_ms, "note": "un-graphed per-op CUDA-event timing"},
             "flops_per_step": flops_g + flops_a,
         }
+        if world > 1:
+            line["with_gather"] = {"value": B * world * args.steps / (ms_gather * 1e-3), "unit": UNIT,
+                                   "ms_per_step": ms_gather / args.steps,
+                                   "bytes_into_rank0_per_step": int((world - 1) * out_d.numel()),
+                                   "note": "device-resident step + gather of every rank's finished frames on rank 0 "
+                                           "(NCCL send/recv, frame order)"}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line))
+        emit(line)
     return 0
 
 
@@ -414,7 +462,7 @@ def run_config5(args):
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
-        print(json.dumps(line))
+        emit(line)
     return 0
 
 
@@ -427,6 +475,7 @@ def main():
     ap.add_argument("--workload", default="default", choices=["default", "config5"],
                     help="default = BASELINE.json configs[1] + paste-back (the headline line); config5 = linknet/3 + SR")
     args = ap.parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         return run_reference(args)
     if args.workload == "config5":
