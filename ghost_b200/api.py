@@ -502,6 +502,41 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
     return out
 
 
+def crop_faces(frames, tfms, face_frame, want224=True, want256=True):
+    """The crop extraction in front of the generator (utils/inference/video_processing.py:159-168 + resize_frames
+    :174-188), on the device and bit-exact against the reference's OpenCV calls:
+
+        crops224[i] = cv2.warpAffine(frames[face_frame[i]], tfms[i], (224, 224), borderValue=0.0)
+        crops256[i] = cv2.resize(crops224[i], (256, 256))
+
+    frames: uint8 BGR [F,H,W,3] (device tensor or numpy); tfms [n,2,3] float64 frame->crop affines.
+    Returns (crops224, crops256) device tensors (None for the one not asked for)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
+    dev = frames.device if isinstance(frames, torch.Tensor) and frames.is_cuda else torch.device(
+        "cuda", torch.cuda.current_device())
+    fr = _as_dev(frames, torch.uint8, dev)
+    if fr.dim() != 4 or fr.shape[3] != 3:
+        raise ValueError("frames must be [F,H,W,3] uint8")
+    tf = np.ascontiguousarray(np.asarray(tfms, dtype=np.float64).reshape(-1, 2, 3))
+    ff = np.ascontiguousarray(np.asarray(face_frame, dtype=np.int32).reshape(-1))
+    n = tf.shape[0]
+    if len(ff) != n:
+        raise ValueError("one frame index per affine")
+    if not (want224 or want256):
+        raise ValueError("nothing to compute")
+    c224 = torch.empty((n, 224, 224, 3), dtype=torch.uint8, device=dev) if want224 else None
+    c256 = torch.empty((n, 256, 256, 3), dtype=torch.uint8, device=dev) if want256 else None
+    if n == 0:
+        return c224, c256
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        _lib.check(lib.ghost_crop_faces(_ptr(fr), fr.shape[0], fr.shape[1], fr.shape[2],
+                                        tf.ctypes.data_as(C.POINTER(C.c_double)), ff.ctypes.data_as(C.POINTER(C.c_int)), n,
+                                        _ptr(c224) if want224 else None, _ptr(c256) if want256 else None, _stream()))
+    return c224, c256
+
+
 class SwapPipeline(object):
     """The per-batch video loop of the reference (utils/inference/core.py:model_inference ->
     faceshifter_batch -> video_processing.py:get_final_video) as one double-buffered device pipeline:

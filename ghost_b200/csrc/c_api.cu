@@ -7,6 +7,7 @@
 #include "net.cuh"
 #include "sr_kernels.cuh"
 #include "mask.cuh"
+#include "crop.cuh"
 
 using namespace ghost;
 
@@ -366,6 +367,33 @@ int ghost_postproc_u8(const void* y, int y_dtype, uint8_t* dst, int B, void* str
   return guarded([&] {
     require(y && dst && B > 0, "bad argument");
     check_msg(postproc_u8_launch(y, y_dtype, dst, static_cast<long long>(B) * 65536, S(stream)), "postproc");
+  });
+}
+
+int ghost_crop_faces(const uint8_t* frames, int n_frames, int H, int W, const double* tfm, const int* face_frame, int n,
+                     uint8_t* crops224, uint8_t* crops256, void* stream) {
+  return guarded([&] {
+    require(frames && tfm && face_frame && n > 0 && n_frames > 0 && H > 0 && W > 0, "bad argument");
+    require(crops224 || crops256, "no output buffer");
+    cudaStream_t s = S(stream);
+    std::vector<CropFace> faces(n);
+    for (int i = 0; i < n; ++i) {
+      require(face_frame[i] >= 0 && face_frame[i] < n_frames, "face_frame out of range");
+      crop_prepare_face(&faces[i], tfm + 6 * i, face_frame[i]);
+    }
+    short tables[7 * 256];
+    crop_resize_tables(tables);
+    const size_t fb = (faces.size() * sizeof(CropFace) + 255) / 256 * 256, tb = sizeof(tables);
+    const size_t scratch224 = crops224 ? 0 : static_cast<size_t>(n) * 224 * 224 * 3;
+    char* dev = nullptr;
+    check_cuda(cudaMallocAsync(reinterpret_cast<void**>(&dev), fb + 4096 + scratch224, s), "crop scratch");
+    check_cuda(cudaMemcpyAsync(dev, faces.data(), faces.size() * sizeof(CropFace), cudaMemcpyHostToDevice, s), "crop faces upload");
+    check_cuda(cudaMemcpyAsync(dev + fb, tables, tb, cudaMemcpyHostToDevice, s), "crop tables upload");
+    uint8_t* c224 = crops224 ? crops224 : reinterpret_cast<uint8_t*>(dev + fb + 4096);
+    const char* err = crop_faces_launch(frames, H, W, reinterpret_cast<const CropFace*>(dev),
+                                        n, reinterpret_cast<const short*>(dev + fb), c224, crops256, s);
+    cudaFreeAsync(dev, s);
+    check_msg(err, "crop faces");
   });
 }
 

@@ -16,6 +16,7 @@
  *   utils/inference/video_processing.py:191-243       get_final_video (compositing only)
  *   utils/inference/video_processing.py:246-285       Frames / face_enhancement
  *   utils/inference/masks.py:39-108                   face_mask_static / erode_and_blur
+ *   utils/inference/video_processing.py:159-188       crop extraction (warpAffine + resize_frames)
  *   models/pix2pix_model.py:42-62, models/networks/generator.py:93-137,390-400   Pix2PixModel 'inference2' -> LIPSPADEGenerator
  */
 #ifndef GHOST_B200_H_
@@ -167,6 +168,15 @@ typedef struct {
 } ghost_paste_desc;
 
 int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
+
+/* ---- crop extraction in front of the generator (utils/inference/video_processing.py:159-168 + resize_frames
+ * :174-188; image_processing.py:13-20), bit-exact against the reference's OpenCV calls:
+ *   crops224[i] = cv2.warpAffine(frames[face_frame[i]], tfm[i], (224, 224), borderValue=0.0)
+ *   crops256[i] = cv2.resize(crops224[i], (256, 256))
+ * frames [n_frames,H,W,3] u8 BGR (device); tfm [n][2][3] float64 frame->crop affines (host, tfm_array entries);
+ * face_frame [n] (host); crops224 [n,224,224,3] / crops256 [n,256,256,3] u8 on the device, either may be NULL. */
+int ghost_crop_faces(const uint8_t* frames, int n_frames, int H, int W, const double* tfm, const int* face_frame, int n,
+                     uint8_t* crops224, uint8_t* crops256, void* stream);
 
 /* ---- blend-mask synthesis (utils/inference/masks.py:39-108 face_mask_static + erode_and_blur, called at
  * image_processing.py:68 and video_processing.py:221-223), bit-exact against the reference's OpenCV calls:
