@@ -537,6 +537,28 @@ def crop_faces(frames, tfms, face_frame, want224=True, want256=True):
     return c224, c256
 
 
+def match_identities(face_embeds, target_embeds, similarity_th):
+    """utils/inference/video_processing.py:141-148: which detected face of a frame belongs to which target identity.
+    face_embeds [n_faces,512], target_embeds [n_targets,512]: un-normalised ArcFace outputs on the device.
+    Returns (best_idxs [n_targets] int64, matched [n_targets] bool, similarity [n_targets] float32) as numpy -
+    matched[j] is the reference's `similarity[best_idx][j] > similarity_th`."""
+    _require_cuda(face_embeds, "face_embeds")
+    _require_cuda(target_embeds, "target_embeds")
+    f = face_embeds.to(torch.float32).contiguous()
+    t = target_embeds.to(torch.float32).contiguous()
+    if f.dim() != 2 or t.dim() != 2 or f.shape[1] != t.shape[1]:
+        raise ValueError("face_embeds [n,d] and target_embeds [t,d] expected")
+    nt = t.shape[0]
+    idx = torch.empty(nt, dtype=torch.int32, device=f.device)
+    sim = torch.empty(nt, dtype=torch.float32, device=f.device)
+    ok = torch.empty(nt, dtype=torch.int32, device=f.device)
+    lib = _lib.load()
+    with torch.cuda.device(f.device):
+        _lib.check(lib.ghost_match_identities(_ptr(f), f.shape[0], _ptr(t), nt, f.shape[1], float(similarity_th),
+                                              _ptr(idx), _ptr(sim), _ptr(ok), _stream()))
+    return idx.cpu().numpy().astype(np.int64), ok.cpu().numpy().astype(bool), sim.cpu().numpy()
+
+
 class SwapPipeline(object):
     """The per-batch video loop of the reference (utils/inference/core.py:model_inference ->
     faceshifter_batch -> video_processing.py:get_final_video) as one double-buffered device pipeline:

@@ -8,6 +8,7 @@
 #include "sr_kernels.cuh"
 #include "mask.cuh"
 #include "crop.cuh"
+#include "match.cuh"
 
 using namespace ghost;
 
@@ -367,6 +368,16 @@ int ghost_postproc_u8(const void* y, int y_dtype, uint8_t* dst, int B, void* str
   return guarded([&] {
     require(y && dst && B > 0, "bad argument");
     check_msg(postproc_u8_launch(y, y_dtype, dst, static_cast<long long>(B) * 65536, S(stream)), "postproc");
+  });
+}
+
+int ghost_match_identities(const float* face_embeds, int n_faces, const float* target_embeds, int n_targets, int dim,
+                           float similarity_th, int* best_idx, float* best_sim, int* matched, void* stream) {
+  return guarded([&] {
+    require(face_embeds && target_embeds && best_idx && best_sim && matched, "null argument");
+    require(n_faces >= 0 && n_targets > 0 && dim > 0, "bad sizes");
+    check_msg(match_identities_launch(face_embeds, n_faces, target_embeds, n_targets, dim, similarity_th, best_idx,
+                                      best_sim, matched, S(stream)), "match identities");
   });
 }
 

@@ -169,6 +169,14 @@ typedef struct {
 
 int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
 
+/* ---- identity matching for multi-face video (utils/inference/video_processing.py:126-148):
+ *   similarity = F.normalize(face_embeds) @ F.normalize(target_embeds).T;  best_idx = similarity.argmax(0);
+ *   matched[j] = similarity[best_idx[j]][j] > similarity_th.
+ * face_embeds [n_faces][dim], target_embeds [n_targets][dim] fp32 un-normalised ArcFace outputs (device);
+ * best_idx / best_sim / matched [n_targets] (device). */
+int ghost_match_identities(const float* face_embeds, int n_faces, const float* target_embeds, int n_targets, int dim,
+                           float similarity_th, int* best_idx, float* best_sim, int* matched, void* stream);
+
 /* ---- crop extraction in front of the generator (utils/inference/video_processing.py:159-168 + resize_frames
  * :174-188; image_processing.py:13-20), bit-exact against the reference's OpenCV calls:
  *   crops224[i] = cv2.warpAffine(frames[face_frame[i]], tfm[i], (224, 224), borderValue=0.0)
