@@ -182,6 +182,9 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     pk = peaks()
+    # everything runs on an explicit stream: the legacy default stream serialises against every other blocking
+    # stream, which would undo the overlap of the copy / encoder side streams
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))
 
     G = ghost_b200.AEI_Net(BACKBONE, NUM_BLOCKS, 512, seed=0).eval().bfloat16().cuda()
     arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
@@ -198,9 +201,12 @@ def run_ours(args):
     sources_d, crops_d, frames_d = sources_p.to(dev), crops_p.to(dev), frames_p.to(dev)
     out_d = torch.empty_like(frames_d)
 
+    side, side_ev = torch.cuda.Stream(device=dev), torch.cuda.Event()
+
     def step_device(src, crp, frm, out):
-        z = arc.embed_hwc(src, out_dtype=torch.bfloat16)
-        G.swap_u8(crp, z, write_u8=False)                          # generator output stays on the device
+        # ArcFace on the current stream, the attribute encoder (independent of z_id) beside it on `side`, then the
+        # AAD generator; the generator output stays on the device
+        ghost_b200.embed_and_swap(G, arc, src, crp, side=side, event=side_ev, write_u8=False)
         yptr, ydt = G.y_nhwc(B, dev)
         ghost_b200.paste_back(frm, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out)
 

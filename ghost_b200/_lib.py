@@ -55,6 +55,8 @@ SIGNATURES = {
     "ghost_aei_forward": (_i, [_vp, _vp, _i, _vp, _i, _vp, C.POINTER(_vp), _i, _i, _vp]),
     "ghost_aei_encode": (_i, [_vp, _vp, _i, C.POINTER(_vp), _i, _i, _vp]),
     "ghost_aei_swap_u8": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i, _vp]),
+    "ghost_aei_encode_u8": (_i, [_vp, _vp, _i, _vp]),
+    "ghost_aei_generate_u8": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "ghost_net_y_nhwc": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_i)]),
     "ghost_arcface_forward": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp]),
     "ghost_arcface_embed_hwc": (_i, [_vp, _vp, _i, _vp, _i, _i, _vp]),

@@ -306,6 +306,33 @@ class AEI_Net(_Net):
                                              _stream()))
         return out if write_u8 else None
 
+    def encode_u8(self, crops_bgr):
+        """First half of swap_u8: normalise + attribute encoder (network/AEI_Net.py:72-95) on the current stream.
+        The encoder does not depend on z_id, so it can run on a side stream beside the ArcFace network
+        (embed_and_swap does that); generate_u8 must be ordered after it."""
+        _require_cuda(crops_bgr, "crops_bgr")
+        if crops_bgr.dtype != torch.uint8 or crops_bgr.dim() != 4 or tuple(crops_bgr.shape[1:]) != (256, 256, 3):
+            raise ValueError("crops_bgr must be uint8 [B,256,256,3]")
+        crops_bgr = crops_bgr.contiguous()
+        lib = _lib.load()
+        with torch.cuda.device(crops_bgr.device):
+            _lib.check(lib.ghost_aei_encode_u8(self._handle(crops_bgr.device), _ptr(crops_bgr), crops_bgr.shape[0],
+                                               _stream()))
+
+    def generate_u8(self, z_id, B, out=None, write_u8=True):
+        """Second half of swap_u8: the AAD generator on the attribute maps encode_u8 left in the plan of batch B."""
+        _require_cuda(z_id, "z_id")
+        z = z_id.reshape(z_id.shape[0], -1).contiguous()
+        if z.shape[0] not in (1, B) or z.shape[1] != self.c_id:
+            raise ValueError("z_id must be [1,%d] or [%d,%d]" % (self.c_id, B, self.c_id))
+        lib = _lib.load()
+        with torch.cuda.device(z.device):
+            if out is None and write_u8:
+                out = torch.empty((B, 256, 256, 3), dtype=torch.uint8, device=z.device)
+            _lib.check(lib.ghost_aei_generate_u8(self._handle(z.device), _ptr(z), _DT[z.dtype], z.shape[0],
+                                                 _ptr(out) if write_u8 else None, B, _stream()))
+        return out if write_u8 else None
+
     def y_nhwc(self, B, device=None):
         """(device pointer, ghost dtype) of the NHWC generator output of the last forward at batch B."""
         lib = _lib.load()
@@ -559,6 +586,25 @@ def match_identities(face_embeds, target_embeds, similarity_th):
     return idx.cpu().numpy().astype(np.int64), ok.cpu().numpy().astype(bool), sim.cpu().numpy()
 
 
+def embed_and_swap(G, arc, sources_rgb224, crops_bgr, side=None, event=None, out=None, write_u8=True):
+    """z_id = netArc(sources) and the swap of `crops_bgr` with it (core.py:44-45 + faceshifter_batch), with the two
+    independent halves overlapped: the attribute encoder of G runs on the stream `side` while the ArcFace network runs
+    on the current stream; the AAD generator follows on the current stream.  Same results as
+    `G.swap_u8(crops, arc.embed_hwc(sources))`; side=None runs exactly that."""
+    zdt = torch.bfloat16 if G.dtype == torch.bfloat16 else (torch.float16 if G.dtype == torch.float16 else torch.float32)
+    if side is None:
+        return G.swap_u8(crops_bgr, arc.embed_hwc(sources_rgb224, out_dtype=zdt), out=out, write_u8=write_u8)
+    main = torch.cuda.current_stream(crops_bgr.device)
+    side.wait_stream(main)                       # inputs ready, previous users of the plan's buffers done
+    with torch.cuda.stream(side):
+        G.encode_u8(crops_bgr)
+        event = event or torch.cuda.Event()
+        event.record(side)
+    z = arc.embed_hwc(sources_rgb224, out_dtype=zdt)
+    main.wait_event(event)
+    return G.generate_u8(z, crops_bgr.shape[0], out=out, write_u8=write_u8)
+
+
 class SwapPipeline(object):
     """The per-batch video loop of the reference (utils/inference/core.py:model_inference ->
     faceshifter_batch -> video_processing.py:get_final_video) as one double-buffered device pipeline:
@@ -585,6 +631,8 @@ class SwapPipeline(object):
                 "ev_in": torch.cuda.Event(), "ev_done": torch.cuda.Event(), "ev_out": torch.cuda.Event(), "used": False})
         self.s_in = torch.cuda.Stream(device=self.dev)
         self.s_out = torch.cuda.Stream(device=self.dev)
+        self.s_enc = torch.cuda.Stream(device=self.dev)   # attribute encoder beside the ArcFace network
+        self.ev_enc = torch.cuda.Event()
         self.i = 0
 
     def submit(self, sources, crops, frames, masks, tfms, face_frame, out):
@@ -605,8 +653,7 @@ class SwapPipeline(object):
         main.wait_event(slot["ev_in"])
         if slot["used"]:
             main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
-        z = self.arc.embed_hwc(slot["src"], out_dtype=torch.bfloat16 if self.G.dtype == torch.bfloat16 else torch.float32)
-        self.G.swap_u8(slot["crp"], z, write_u8=False)
+        embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
         yptr, ydt = self.G.y_nhwc(self.B, self.dev)
         paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=slot["out"])
         slot["ev_done"].record(main)

@@ -229,6 +229,43 @@ int ghost_aei_swap_u8(ghost_net_t* net, const uint8_t* crops_bgr, const void* z_
   });
 }
 
+int ghost_aei_encode_u8(ghost_net_t* net, const uint8_t* crops_bgr, int B, void* stream) {
+  return guarded([&] {
+    require(net && crops_bgr, "null argument");
+    require(net->net.kind == Net::kAEI, "not an AEI_Net handle");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    check_msg(preproc_u8_launch(crops_bgr, p.x_in.p, p.x_in.dtype, static_cast<long long>(B) * 65536, 0, s), "preproc");
+    n.run_plan(p, s, 0, n.encoder_ops);
+  });
+}
+
+int ghost_aei_generate_u8(ghost_net_t* net, const void* z_id, int z_dtype, int z_rows, uint8_t* out_bgr, int B,
+                          void* stream) {
+  return guarded([&] {
+    require(net && z_id, "null argument");
+    require(net->net.kind == Net::kAEI, "not an AEI_Net handle");
+    require(z_rows == 1 || z_rows == B, "z_id must have 1 or B rows");
+    std::lock_guard<std::mutex> lk(net->mu);
+    Net& n = net->net;
+    ExecPlan& p = n.plan(B);
+    cudaStream_t s = S(stream);
+    const size_t zb = (p.zid.dtype == kF32 ? 4 : 2) * static_cast<size_t>(n.c_id);
+    check_msg(nchw_to_nhwc_launch(z_id, z_dtype, p.zid.p, p.zid.dtype, z_rows == B ? B : 1, n.c_id, 1, 1, n.c_id, 0, s),
+              "z_id in");
+    for (int filled = 1; z_rows == 1 && filled < B;) {
+      const int cnt = filled < B - filled ? filled : B - filled;
+      check_cuda(cudaMemcpyAsync(static_cast<char*>(p.zid.p) + zb * filled, p.zid.p, zb * cnt, cudaMemcpyDeviceToDevice, s),
+                 "z_id tile");
+      filled += cnt;
+    }
+    n.run_plan(p, s, n.encoder_ops);
+    if (out_bgr) check_msg(postproc_u8_launch(p.y.p, p.y.dtype, out_bgr, static_cast<long long>(B) * 65536, s), "postproc");
+  });
+}
+
 int ghost_net_y_nhwc(ghost_net_t* net, int B, void** ptr, int* dtype) {
   return guarded([&] {
     require(net && ptr && dtype, "null argument");

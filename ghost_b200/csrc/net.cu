@@ -52,6 +52,8 @@ __nv_bfloat16* DevPool::upload_bf16(const std::vector<float>& v) {
 
 ExecPlan::~ExecPlan() {
   if (graph) cudaGraphExecDestroy(graph);
+  if (graph_enc) cudaGraphExecDestroy(graph_enc);
+  if (graph_gen) cudaGraphExecDestroy(graph_gen);
 }
 
 // ------------------------------------------------------------------ Net basics
@@ -131,56 +133,76 @@ ExecPlan& Net::plan(int B) {
   return ref;
 }
 
+// Captures ops [first, last) of a plan into one CUDA graph.
+void Net::capture_range(ExecPlan& p, cudaStream_t s, size_t first, size_t last, cudaGraphExec_t* out) {
+  // warm every kernel once (module load, attribute setup) before capturing; the warm-up pass must not count
+  // as a forward for the spectral-norm power iteration, so u is put back afterwards
+  std::vector<std::vector<float>> u_saved;
+  for (auto& kv : sr_sn_) {
+    u_saved.emplace_back(kv.second.R);
+    check_cuda(cudaMemcpyAsync(u_saved.back().data(), kv.second.u, kv.second.R * sizeof(float),
+                               cudaMemcpyDeviceToHost, s), "save u");
+  }
+  check_cuda(cudaStreamSynchronize(s), "save u sync");
+  for (size_t i = first; i < last; ++i) check_msg(p.ops[i].run(s), p.ops[i].name);
+  {
+    size_t i = 0;
+    for (auto& kv : sr_sn_)
+      check_cuda(cudaMemcpyAsync(kv.second.u, u_saved[i++].data(), kv.second.R * sizeof(float),
+                                 cudaMemcpyHostToDevice, s), "restore u");
+  }
+  check_cuda(cudaStreamSynchronize(s), "graph warm-up");
+  cudaStream_t cs;
+  check_cuda(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking), "capture stream");
+  cudaGraph_t g = nullptr;
+  check_cuda(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal), "begin capture");
+  const char* err = nullptr;
+  std::string where;
+  for (size_t i = first; i < last; ++i) {
+    err = p.ops[i].run(cs);
+    if (err) {
+      where = p.ops[i].name;
+      break;
+    }
+  }
+  cudaError_t ce = cudaStreamEndCapture(cs, &g);
+  if (err) {
+    if (g) cudaGraphDestroy(g);
+    cudaStreamDestroy(cs);
+    check_msg(err, where);
+  }
+  check_cuda(ce, "end capture");
+  check_cuda(cudaGraphInstantiate(out, g, 0), "graph instantiate");
+  cudaGraphDestroy(g);
+  cudaStreamDestroy(cs);
+}
+
 void Net::run_plan(ExecPlan& p, cudaStream_t s, size_t first, size_t last) {
   if (last > p.ops.size()) last = p.ops.size();
-  const bool whole = first == 0 && last == p.ops.size();
-  if (use_graph && whole) {
-    if (!p.graph && !p.graph_tried) {
-      p.graph_tried = true;
-      // warm every kernel once (module load, attribute setup) before capturing; the warm-up pass must not count
-      // as a forward for the spectral-norm power iteration, so u is put back afterwards
-      std::vector<std::vector<float>> u_saved;
-      for (auto& kv : sr_sn_) {
-        u_saved.emplace_back(kv.second.R);
-        check_cuda(cudaMemcpyAsync(u_saved.back().data(), kv.second.u, kv.second.R * sizeof(float),
-                                   cudaMemcpyDeviceToHost, s), "save u");
-      }
-      check_cuda(cudaStreamSynchronize(s), "save u sync");
-      for (auto& op : p.ops) check_msg(op.run(s), op.name);
-      {
-        size_t i = 0;
-        for (auto& kv : sr_sn_)
-          check_cuda(cudaMemcpyAsync(kv.second.u, u_saved[i++].data(), kv.second.R * sizeof(float),
-                                     cudaMemcpyHostToDevice, s), "restore u");
-      }
-      check_cuda(cudaStreamSynchronize(s), "graph warm-up");
-      cudaStream_t cs;
-      check_cuda(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking), "capture stream");
-      cudaGraph_t g = nullptr;
-      check_cuda(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal), "begin capture");
-      const char* err = nullptr;
-      std::string where;
-      for (auto& op : p.ops) {
-        err = op.run(cs);
-        if (err) {
-          where = op.name;
-          break;
-        }
-      }
-      cudaError_t ce = cudaStreamEndCapture(cs, &g);
-      if (err) {
-        if (g) cudaGraphDestroy(g);
-        cudaStreamDestroy(cs);
-        check_msg(err, where);
-      }
-      check_cuda(ce, "end capture");
-      check_cuda(cudaGraphInstantiate(&p.graph, g, 0), "graph instantiate");
-      cudaGraphDestroy(g);
-      cudaStreamDestroy(cs);
+  if (use_graph) {
+    // three replayable ranges: the whole forward, and - for AEI_Net - the attribute encoder and the generator on
+    // their own (the encoder does not depend on z_id, so a caller may run it beside the ArcFace network)
+    cudaGraphExec_t* slot = nullptr;
+    bool* tried = nullptr;
+    if (first == 0 && last == p.ops.size()) {
+      slot = &p.graph;
+      tried = &p.graph_tried;
+    } else if (encoder_ops > 0 && first == 0 && last == encoder_ops) {
+      slot = &p.graph_enc;
+      tried = &p.enc_tried;
+    } else if (encoder_ops > 0 && first == encoder_ops && last == p.ops.size()) {
+      slot = &p.graph_gen;
+      tried = &p.gen_tried;
     }
-    if (p.graph) {
-      check_cuda(cudaGraphLaunch(p.graph, s), "graph launch");
-      return;
+    if (slot) {
+      if (!*slot && !*tried) {
+        *tried = true;
+        capture_range(p, s, first, last, slot);
+      }
+      if (*slot) {
+        check_cuda(cudaGraphLaunch(*slot, s), "graph launch");
+        return;
+      }
     }
   }
   for (size_t i = first; i < last; ++i) check_msg(p.ops[i].run(s), p.ops[i].name);

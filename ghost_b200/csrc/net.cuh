@@ -82,6 +82,8 @@ struct ExecPlan {
   std::vector<Op> ops;
   cudaGraphExec_t graph = nullptr;
   bool graph_tried = false;
+  cudaGraphExec_t graph_enc = nullptr, graph_gen = nullptr;  // AEI_Net: attribute encoder / generator on their own
+  bool enc_tried = false, gen_tried = false;
   int* err_word = nullptr;
   // boundary buffers
   Act x_in;          // NHWC-3 network input
@@ -106,6 +108,7 @@ class Net {
   void finalize();
   ExecPlan& plan(int B);
   void run_plan(ExecPlan& p, cudaStream_t s, size_t first_op = 0, size_t last_op = static_cast<size_t>(-1));
+  void capture_range(ExecPlan& p, cudaStream_t s, size_t first, size_t last, cudaGraphExec_t* out);
   // Runs every op `reps` times bracketed by CUDA events on `s`; ms[i] = mean duration of op i.
   void profile_plan(ExecPlan& p, cudaStream_t s, int reps, std::vector<float>* ms);
 

@@ -86,6 +86,14 @@ int ghost_aei_encode(ghost_net_t* net, const void* X, int x_dtype, void* const* 
 int ghost_aei_swap_u8(ghost_net_t* net, const uint8_t* crops_bgr, const void* z_id, int z_dtype, int z_rows,
                       uint8_t* out_bgr, int B, void* stream);
 
+/* ghost_aei_swap_u8 in two halves, for callers that overlap the attribute encoder with the ArcFace network (the
+ * encoder, network/AEI_Net.py:72-95, does not depend on z_id): encode_u8 = normalise + MLAttrEncoder on `stream`;
+ * generate_u8 = AADGenerator (+ optional uint8 conversion) on `stream`, which must be ordered after encode_u8 of
+ * the same batch size (an event between the two streams).  Results are identical to ghost_aei_swap_u8. */
+int ghost_aei_encode_u8(ghost_net_t* net, const uint8_t* crops_bgr, int B, void* stream);
+int ghost_aei_generate_u8(ghost_net_t* net, const void* z_id, int z_dtype, int z_rows, uint8_t* out_bgr, int B,
+                          void* stream);
+
 /* Device pointer + dtype of the NHWC-3 generator output of the last forward with batch B (valid until the next call). */
 int ghost_net_y_nhwc(ghost_net_t* net, int B, void** ptr, int* dtype);
 

@@ -60,3 +60,25 @@ def test_state_dict_round_trip_and_errors():
     bad["generator.up1.bias"] = torch.zeros(7)
     with pytest.raises(RuntimeError):
         G.load_state_dict(bad)
+
+
+def test_embed_and_swap_overlapped_matches_sequential():
+    """Attribute encoder on a side stream beside the ArcFace network (graphs for the two halves of the forward):
+    bit-identical to the one-call swap_u8, graph replay included."""
+    import ghost_b200
+    from ghost_b200 import synth
+    B = 4
+    G = ghost_b200.AEI_Net("unet", 1, 512, seed=0).eval().bfloat16().cuda()
+    arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
+    src = torch.from_numpy(synth.sources_u8(B, seed=3)).cuda()
+    crops = torch.from_numpy(synth.crops_u8(B, seed=3)).cuda()
+    ref = G.swap_u8(crops, arc.embed_hwc(src, out_dtype=torch.bfloat16)).clone()
+    side = torch.cuda.Stream()
+    for graph in (False, True):
+        G.enable_graph(graph)
+        arc.enable_graph(graph)
+        for _ in range(3):
+            got = ghost_b200.embed_and_swap(G, arc, src, crops, side=side)
+            torch.cuda.synchronize()
+            assert torch.equal(got, ref)
+    assert torch.equal(ghost_b200.embed_and_swap(G, arc, src, crops, side=None), ref)

@@ -122,6 +122,24 @@ def test_face_enhancement_list_api():
         assert d.max() <= 1 and (d != 0).mean() <= 2e-3
 
 
+def test_ragged_last_batch_matches_oracle():
+    """22 crops = one full DataLoader batch of 20 and a ragged one of 2 (drop_last=False, video_processing.py:272):
+    each batch has its own statistics and the spectral-norm state advances once per batch."""
+    sd = W.init_state_dict(W.sr_spec(), seed=6)
+    crops = synth.crops_u8(22, seed=12)
+    model = ghost_b200.Pix2PixModel()
+    model.load_state_dict(sd)
+    model.netG.float().cuda()
+    out = ghost_b200.face_enhancement([list(crops)], model)[0]
+    state = {}
+    ref = sr_ref.face_enhancement_ref(sd, crops, state)
+    got = np.stack(out)
+    diff = np.abs(got.astype(int) - ref.astype(int))
+    assert diff.max() <= 1 and (diff != 0).mean() <= 2e-3, "%d px differ, max %d" % ((diff != 0).sum(), diff.max())
+    u = model.netG.state_dict()["head_0.conv_1.weight_u"].numpy()
+    assert np.abs(u - state["head_0.conv_1.weight_u"].numpy()).max() <= 1e-5      # two power iterations
+
+
 def test_bf16_tracks_fp32():
     sd = W.init_state_dict(W.sr_spec(), seed=0)
     x = sr_ref.preprocess_ref(synth.crops_u8(4, seed=11)).cuda()
