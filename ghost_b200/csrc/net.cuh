@@ -149,6 +149,7 @@ class Net {
   std::map<std::string, SnState> sr_sn_;
   std::map<std::string, SrSlice> sr_slices_;
   int sr_actv_c_[6] = {0, 0, 0, 0, 0, 0};
+  int sr_actv_need_[6] = {0, 0, 0, 0, 0, 0};  // end of the widest read window per resolution
 
  public:
   // copies a spectral-norm buffer ("<conv>.weight_u" / "<conv>.weight_v") to the host; returns its length

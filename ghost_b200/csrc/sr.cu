@@ -16,6 +16,8 @@
 //  * spectral norm: weight_orig stays resident in fp32, one power iteration per forward runs on the device, and
 //    1/sigma multiplies the *input* of the conv (conv(x, W/sigma) = conv(x/sigma, W)) inside the modulation kernel.
 #include <math.h>
+
+#include <algorithm>
 #include <string.h>
 
 #include "net.cuh"
@@ -75,7 +77,7 @@ void Net::finalize_sr() {
   const bool bf = act_dtype == kBF16;
   sr_sn_.clear();
   sr_slices_.clear();
-  for (int i = 0; i < 6; ++i) sr_actv_c_[i] = 0;
+  for (int i = 0; i < 6; ++i) sr_actv_c_[i] = sr_actv_need_[i] = 0;
 
   // bf16 mode, thin-K convs (K = 32..768 per pixel with N <= 384): they leave the SM through the shared-memory
   // staging + TMA store of the fused epilogue (igemm.cuh aad_no_h).  That epilogue works on [gamma | beta] N tiles,
@@ -97,13 +99,17 @@ void Net::finalize_sr() {
   struct Pending { std::string key; int nh, nhp, row0; };
   std::vector<Pending> per_res[6];  // index = log2(S) - 3
   auto add_spade = [&](const std::string& key, int norm_nc, int S) {
+    // The hidden activations of one resolution are packed back to back (stride nh), but every gamma/beta conv reads
+    // a window of cp(nh) channels (whole 64-channel K chunks - 32-channel chunks measured slower, the K-block rate
+    // is the limit); the window's tail overlaps the next slice or the padding, where this conv's weights are zero.
     const int nh = nhid(norm_nc), nhp = cp(nh), Cp = cpg(norm_nc);
     int ri = 0;
     while ((8 << ri) != S) ++ri;
     Pending pd{key, nh, nhp, sr_actv_c_[ri]};
     per_res[ri].push_back(pd);
     sr_slices_[key] = {ri, sr_actv_c_[ri], nhp};
-    sr_actv_c_[ri] += nhp;
+    sr_actv_need_[ri] = std::max(sr_actv_need_[ri], sr_actv_c_[ri] + nhp);
+    sr_actv_c_[ri] += nh;
     const HostTensor& wg = W(key + ".mlp_gamma.weight");
     const HostTensor& wb = W(key + ".mlp_beta.weight");
     expect(wg, {norm_nc, nh, 3, 3}, key + ".mlp_gamma.weight");
@@ -158,12 +164,13 @@ void Net::finalize_sr() {
     add_sn_conv(n + ".conv_1", b.fout, fmid, 3, true);
     if (b.fin != b.fout) add_sn_conv(n + ".conv_s", b.fout, b.fin, 1, false);
     add_spade(n + ".norm_0", b.fin, b.S);
-    add_spade(n + ".norm_1", fmid, b.S);
     if (b.fin != b.fout) add_spade(n + ".norm_s", b.fin, b.S);
+    add_spade(n + ".norm_1", fmid, b.S);  // the narrowest slice last: its window overhang is the smallest
   }
   for (int ri = 0; ri < 6; ++ri) {
     if (!sr_actv_c_[ri]) continue;
-    if (bf) sr_actv_c_[ri] = cpg(sr_actv_c_[ri]);  // whole N tiles of the TMA-store epilogue (256^2: 320 -> 384)
+    sr_actv_c_[ri] = cp(sr_actv_need_[ri]);        // every read window lies inside the tensor
+    if (bf) sr_actv_c_[ri] = cpg(sr_actv_c_[ri]);  // whole N tiles of the TMA-store epilogue
     const int rows_n = sr_actv_c_[ri];
     std::vector<float> rows(static_cast<size_t>(rows_n) * 32, 0.f), bias(rows_n, 0.f);
     for (const Pending& pd : per_res[ri]) {
