@@ -6,13 +6,17 @@
 //   models/networks/normalization.py:63-107 SPADE (param-free BatchNorm with batch statistics)
 //
 // Layout decisions:
-//  * every channel count is padded to a multiple of 64 (48 -> 64, 96 -> 128): padded weight rows / columns are zero,
-//    so the padded channels carry exact zeros through every layer and every K chunk is a full 128-byte swizzle row;
+//  * channel counts are padded to what the tensor-core tiles want - 64-multiples in the LIP encoder (cp), 64 or a
+//    128-multiple in the SPADE part (cpg: 48 -> 64, 96 -> 128, 192 -> 256): padded weight rows / columns are zero, so
+//    the padded channels carry exact zeros through every layer and every K chunk is a full 128-byte swizzle row;
 //  * the conditioning image enters each SPADE through a 3x3 conv on its nearest-downsampled copy: per resolution
 //    the 3x3x3 neighbourhoods are gathered once (K = 27 -> 32) and all mlp_shared convs of that resolution run as
-//    ONE 1x1 tensor-core GEMM; each SPADE's gamma/beta conv then reads its channel slice of that tensor;
-//  * nn.Upsample(nearest x2) is never materialised for the blocks with a learned shortcut: batch statistics of the
-//    upsampled tensor equal those of its source, and the SPADE modulation reads x at (h>>1, w>>1);
+//    ONE thin-K tensor-core GEMM; the hidden activations of the SPADEs of a resolution lie back to back in that
+//    tensor and each gamma/beta conv reads a 64-multiple window over its own slice (zero weights on the overhang);
+//  * SPADE itself (bf16 mode) is the epilogue of its gamma/beta conv (igemm AAD mode, `aad_spade`): batch-norm of
+//    x, x * gamma + beta, LeakyReLU, 1/sigma of the consuming conv; gamma / beta never reach HBM;
+//  * nn.Upsample(nearest x2): batch statistics are taken on the source tensor (identical); the upsampled tensor is
+//    written once per block because the fused epilogue reads x by TMA (the fp32 mode reads x at (h>>1, w>>1));
 //  * spectral norm: weight_orig stays resident in fp32, one power iteration per forward runs on the device, and
 //    1/sigma multiplies the *input* of the conv (conv(x, W/sigma) = conv(x/sigma, W)) inside the modulation kernel.
 #include <math.h>
