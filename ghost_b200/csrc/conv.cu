@@ -141,6 +141,50 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     return nullptr;
   }
 
+  // ---- 3x3 / stride 1 / pad 1 with <= 3 output channels: the nine taps ride in N (tapn.cuh)
+  static const int tapn_mode = [] {
+    const char* e = getenv("GHOST_TAPN");  // A/B switch for profiling: GHOST_TAPN=0 keeps these convs on igemm_kernel
+    return e ? (atoi(e) != 0) : 1;
+  }();
+  bool tapn = tapn_mode != 0 && !aad && w.wt != nullptr && taps.n == 9 && taps.stride == 1 && Wo == in.W &&
+              Ho == in.H && w.Cout <= 3 && Cin % 64 == 0 && Cin / 64 <= kTapnMaxChunks && in.H >= kTapnTileH &&
+              in.W >= kTapnTileW && epi.act1 == kActNone && !epi.out2 && out.sw >= w.Cout;
+  for (int i = 0; tapn && i < 9; ++i) tapn = taps.dh[i] == i / 3 - 1 && taps.dw[i] == i % 3 - 1;
+  if (tapn) {
+    op->kind = LaunchOp::kTapn;
+    TapnParams& t = op->tp;
+    memset(&t, 0, sizeof(t));
+    t.chunks = Cin / 64;
+    t.c0 = c0;
+    t.cout = w.Cout;
+    t.N = in.N; t.H = in.H; t.W = in.W;
+    t.tiles_x = (in.W + kTapnTileW - 3) / (kTapnTileW - 2);
+    t.tiles_y = (in.H + kTapnTileH - 3) / (kTapnTileH - 2);
+    const long long tiles = static_cast<long long>(t.tiles_x) * t.tiles_y * in.N;
+    if (tiles > 0x7fffffffLL) return "lower_conv: too many tiles";
+    t.tiles = static_cast<int>(tiles);
+    t.bias = w.bias;
+    t.out = out.p;
+    t.out_f32 = out.dtype == kF32;
+    t.o_sn = out.sn; t.o_sh = out.sh; t.o_sw = out.sw; t.o_off = out.off;
+    t.res = epi.res;
+    t.r_sn = epi.r_sn; t.r_sh = epi.r_sh; t.r_sw = epi.r_sw; t.r_off = epi.r_off;
+    t.act2 = epi.act2;
+    t.err = err_word;
+    const uint64_t eb = 2;
+    const uint64_t dims[4] = {static_cast<uint64_t>(in.C), static_cast<uint64_t>(in.W), static_cast<uint64_t>(in.H),
+                              static_cast<uint64_t>(in.N)};
+    const uint64_t str[3] = {in.C * eb, static_cast<uint64_t>(in.W) * in.C * eb,
+                             static_cast<uint64_t>(in.H) * in.W * in.C * eb};
+    const uint32_t box[4] = {64, kTapnTileW, kTapnTileH, 1};
+    if (const char* e = encode_tmap(&t.tmA, in.p, 4, dims, str, box, 128)) return e;
+    const uint64_t wdims[2] = {64, static_cast<uint64_t>(t.chunks) * 32};
+    const uint64_t wstr[1] = {64 * eb};
+    const uint32_t wbox[2] = {64, 32};
+    if (const char* e = encode_tmap(&t.tmW, w.wt, 2, wdims, wstr, wbox, 128)) return e;
+    return nullptr;
+  }
+
   op->kind = LaunchOp::kIgemm;
   IgemmParams& p = op->ig;
   memset(&p, 0, sizeof(p));

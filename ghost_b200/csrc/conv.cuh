@@ -7,6 +7,7 @@
 
 #include "igemm.cuh"
 #include "simt.cuh"
+#include "tapn.cuh"
 
 namespace ghost {
 
@@ -34,6 +35,7 @@ struct PackedW {
   const __nv_bfloat16* wb = nullptr;  // [rows_pad][K] bf16 (igemm)
   const float* wf = nullptr;          // [Cout][K] fp32 (CUDA-core path)
   const float* bias = nullptr;        // [rows_pad] fp32 or null
+  const __nv_bfloat16* wt = nullptr;  // Cout <= 3, K = 9*Cin: the "taps in N" rows of tapn.cuh, or null
   int Cout = 0, rows_pad = 0, K = 0;
 };
 
@@ -94,14 +96,15 @@ struct AadArgs {  // only for the fused AAD epilogue
 
 // A lowered, launch-ready op.
 struct LaunchOp {
-  enum Kind { kIgemm, kSimt } kind = kIgemm;
+  enum Kind { kIgemm, kSimt, kTapn } kind = kIgemm;
   IgemmParams ig;
+  TapnParams tp;
   SimtConvParams sc;
   int simt_dtype = kBF16;
   std::string name;
   double flops = 0.0;
   const char* launch(cudaStream_t s) const {
-    return kind == kIgemm ? igemm_launch(ig, s) : simt_conv_launch(sc, simt_dtype, s);
+    return kind == kIgemm ? igemm_launch(ig, s) : kind == kTapn ? tapn_launch(tp, s) : simt_conv_launch(sc, simt_dtype, s);
   }
 };
 

@@ -87,6 +87,9 @@ PackedW Net::pack(const std::vector<float>& rows, int Cout, int K, const std::ve
     std::vector<float> padded(static_cast<size_t>(p.rows_pad) * K, 0.f);
     memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
     p.wb = wpool_.upload_bf16(padded);
+    // a 3x3 conv onto <= 3 channels (rows [co][tap][ci]): also keep the tapn.cuh layout; lower_conv picks the kernel
+    if (Cout <= 3 && K % (9 * 64) == 0 && K / (9 * 64) <= kTapnMaxChunks)
+      p.wt = wpool_.upload_bf16(tapn_pack_rows(rows.data(), Cout, K / 9));
   }
   if (bias) {
     std::vector<float> b(p.rows_pad, 0.f);

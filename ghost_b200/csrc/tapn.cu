@@ -1,0 +1,203 @@
+// See tapn.cuh.  One persistent CTA pair per SM (192 threads each): warp 0 = TMA producer, warp 1 = MMA issuer and
+// TMEM owner, warps 2-5 = epilogue.  Per tile: one 16 KB TMA box per 64 input channels -> four tcgen05.mma
+// (M = 128 pixels, N = 32 = 9 taps x 3 channels padded, K = 16 each) -> the accumulator goes through shared memory,
+// where every interior pixel collects its nine neighbours' partial sums.
+#include "tapn.cuh"
+
+#include <string.h>
+
+#include "ptx.cuh"
+
+namespace ghost {
+
+namespace {
+
+using namespace ptx;
+
+constexpr int kStages = 3;
+constexpr int kTStride = 29;  // odd: lane-strided rows of T hit 32 different banks
+constexpr int kThreads = 192;
+constexpr int kTileW = kTapnTileW, kTileH = kTapnTileH;  // pixels per tile incl. the halo ring
+constexpr int kInW = kTileW - 2, kInH = kTileH - 2;  // interior = outputs per tile
+
+struct __align__(1024) TapnSmem {
+  uint8_t a[kStages][16384];
+  uint8_t w[kTapnMaxChunks][4096];
+  float t[2][128 * kTStride];
+  uint64_t full[kStages], empty[kStages], wfull, tfull[2], tempty[2];
+  uint32_t tmem_base;
+  int abort_flag;
+};
+
+__device__ __forceinline__ void decode(const TapnParams& p, int tile, int* n, int* gy0, int* gx0) {
+  const int per = p.tiles_x * p.tiles_y;
+  const int nn = tile / per, r = tile - nn * per;
+  const int by = r / p.tiles_x, bx = r - by * p.tiles_x;
+  *n = nn;
+  *gy0 = by * kInH;
+  *gx0 = bx * kInW;
+}
+
+__global__ void __launch_bounds__(kThreads, 2) tapn_kernel(const __grid_constant__ TapnParams p) {
+  extern __shared__ uint8_t tapn_raw[];
+  TapnSmem& sm = *reinterpret_cast<TapnSmem*>((reinterpret_cast<uintptr_t>(tapn_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  volatile int* abortp = &sm.abort_flag;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.empty[s], 1);
+    }
+    mbar_init(&sm.wfull, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&sm.tfull[a], 1);
+      mbar_init(&sm.tempty[a], 4);
+    }
+    sm.abort_flag = 0;
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&sm.tmem_base, 64);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = sm.tmem_base;
+  const int first = blockIdx.x, step = gridDim.x;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      prefetch_tmap(&p.tmA);
+      prefetch_tmap(&p.tmW);
+      mbar_expect_tx(&sm.wfull, p.chunks * 4096);
+      for (int c = 0; c < p.chunks; ++c) tma_load_2d(sm.w[c], &p.tmW, &sm.wfull, 0, c * 32);
+      int it = 0;
+      bool ok = true;
+      for (int t = first; t < p.tiles && ok; t += step) {
+        int n, gy0, gx0;
+        decode(p, t, &n, &gy0, &gx0);
+        for (int c = 0; c < p.chunks; ++c, ++it) {
+          const int s = it % kStages, ph = (it / kStages) & 1;
+          if (!mbar_wait(&sm.empty[s], ph ^ 1, abortp)) {
+            ok = false;
+            break;
+          }
+          mbar_expect_tx(&sm.full[s], 16384);
+          tma_load_4d(sm.a[s], &p.tmA, &sm.full[s], p.c0 + c * 64, gx0 - 1, gy0 - 1, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    mbar_wait_nofail(&sm.wfull, 0, abortp);
+    const uint32_t idesc = make_idesc_bf16(128, 32);
+    const uint32_t hi = smem_desc_hi(1024, false);
+    int it = 0, tl = 0;
+    for (int t = first; t < p.tiles; t += step, ++tl) {
+      const int acc = tl & 1;
+      mbar_wait_nofail(&sm.tempty[acc], ((tl >> 1) & 1) ^ 1, abortp);
+      tc_fence_after();
+      for (int c = 0; c < p.chunks; ++c, ++it) {
+        const int s = it % kStages, ph = (it / kStages) & 1;
+        mbar_wait_nofail(&sm.full[s], ph, abortp);
+        tc_fence_after();
+        umma_bf16_batch<4>(tmem + acc * 32, smem_desc_lo(smem_u32(sm.a[s])), smem_desc_lo(smem_u32(sm.w[c])), hi, idesc,
+                           c > 0 ? 1u : 0u);
+        umma_commit_elect(&sm.empty[s]);
+      }
+      umma_commit_elect(&sm.tfull[acc]);
+    }
+  } else {
+    const int e = threadIdx.x - 64;  // 0..127
+    const int lg = warp & 3;         // the TMEM lane group this warp may read
+    const int m = lg * 32 + lane;    // tile pixel (row-major over 8 x 16) held by this thread
+    float bias[3] = {0.f, 0.f, 0.f};
+    if (p.bias)
+      for (int c = 0; c < p.cout; ++c) bias[c] = __ldg(p.bias + c);
+    int tl = 0;
+    for (int t = first; t < p.tiles; t += step, ++tl) {
+      const int acc = tl & 1;
+      mbar_wait_nofail(&sm.tfull[acc], (tl >> 1) & 1, abortp);
+      tc_fence_after();
+      uint32_t v0[16], v1[16];
+      const uint32_t taddr = tmem + (static_cast<uint32_t>(lg * 32) << 16) + acc * 32;
+      tmem_ld16(taddr, v0);
+      tmem_ld16(taddr + 16, v1);
+      tmem_ld_wait();
+      tc_fence_before();
+      if (lane == 0) mbar_arrive(&sm.tempty[acc]);
+      float* T = sm.t[tl & 1];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) T[m * kTStride + j] = __uint_as_float(v0[j]);
+#pragma unroll
+      for (int j = 0; j < 11; ++j) T[m * kTStride + 16 + j] = __uint_as_float(v1[j]);
+      // T[tl & 1] is rewritten two tiles from now; every thread passes the next tile's barrier in between, and it
+      // only gets there after its reads below - one barrier per tile is enough
+      named_bar_sync(1, 128);
+      int n, gy0, gx0;
+      decode(p, t, &n, &gy0, &gx0);
+      for (int idx = e; idx < kInW * kInH * 3; idx += 128) {
+        const int px = idx / 3, co = idx - px * 3;
+        const int oy = px / kInW, ox = px - oy * kInW;
+        const int gy = gy0 + oy, gx = gx0 + ox;
+        if (gy >= p.H || gx >= p.W || co >= p.cout) continue;
+        const float* tp = T + (oy * kTileW + ox) * kTStride + co;
+        float s = 0.f;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) s += tp[(kh * kTileW + kw) * kTStride + (kh * 3 + kw) * 3];
+        s += co == 0 ? bias[0] : (co == 1 ? bias[1] : bias[2]);
+        const long long o = p.o_off + n * p.o_sn + gy * p.o_sh + gx * p.o_sw + co;
+        if (p.res) {
+          const long long r = p.r_off + n * p.r_sn + gy * p.r_sh + gx * p.r_sw + co;
+          s += p.out_f32 ? __ldg(reinterpret_cast<const float*>(p.res) + r)
+                         : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.res)[r]);
+        }
+        if (p.act2 == kAct2Tanh) s = tanhf(s);
+        if (p.out_f32)
+          reinterpret_cast<float*>(p.out)[o] = s;
+        else
+          reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16(s);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 64);
+  }
+  if (sm.abort_flag && threadIdx.x == 0 && p.err) *reinterpret_cast<volatile int*>(p.err) = 1;
+}
+
+}  // namespace
+
+std::vector<float> tapn_pack_rows(const float* rows_in, int Co, int Ci) {
+  const int chunks = (Ci + 63) / 64;
+  std::vector<float> rows(static_cast<size_t>(chunks) * 32 * 64, 0.f);
+  for (int co = 0; co < Co; ++co)
+    for (int t = 0; t < 9; ++t)
+      for (int ci = 0; ci < Ci; ++ci)
+        rows[(static_cast<size_t>(ci / 64) * 32 + t * 3 + co) * 64 + (ci % 64)] =
+            rows_in[(static_cast<size_t>(co) * 9 + t) * Ci + ci];
+  return rows;
+}
+
+const char* tapn_launch(const TapnParams& p, cudaStream_t s) {
+  static bool configured = false;
+  const int smem = static_cast<int>(sizeof(TapnSmem)) + 1024;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(tapn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return cudaGetErrorString(e);
+    }
+    configured = true;
+  }
+  const int grid = p.tiles < 2 * 148 ? p.tiles : 2 * 148;
+  tapn_kernel<<<grid, kThreads, smem, s>>>(p);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
+}  // namespace ghost

@@ -57,6 +57,8 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
         std::vector<float> padded(static_cast<size_t>(pw.rows_pad) * K, 0.f);
         memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
         pw.wb = pool.upload_bf16(padded);
+        if (kind == 0 && k == 3 && Cout <= 3 && Cin % 64 == 0 && Cin / 64 <= kTapnMaxChunks)
+          pw.wt = pool.upload_bf16(tapn_pack_rows(rows.data(), Cout, Cin));
       }
       if (bias_host) {
         std::vector<float> b(pw.rows_pad, 0.f);
