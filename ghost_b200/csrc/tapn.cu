@@ -1,5 +1,5 @@
 // See tapn.cuh.  One persistent CTA pair per SM (192 threads each): warp 0 = TMA producer, warp 1 = MMA issuer and
-// TMEM owner, warps 2-5 = epilogue.  Per tile: one 16 KB TMA box per 64 input channels -> four tcgen05.mma
+// TMEM owner, warps 2-5 and 6-9 = two epilogue groups on alternate tiles.  Per tile: one 16 KB TMA box per 64 input channels -> four tcgen05.mma
 // (M = 128 pixels, N = 32 = 9 taps x 3 channels padded, K = 16 each) -> the accumulator goes through shared memory,
 // where every interior pixel collects its nine neighbours' partial sums.
 #include "tapn.cuh"
@@ -14,9 +14,9 @@ namespace {
 
 using namespace ptx;
 
-constexpr int kStages = 3;
+constexpr int kStages = 4;
 constexpr int kTStride = 29;  // odd: lane-strided rows of T hit 32 different banks
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;
 constexpr int kTileW = kTapnTileW, kTileH = kTapnTileH;  // pixels per tile incl. the halo ring
 constexpr int kInW = kTileW - 2, kInH = kTileH - 2;  // interior = outputs per tile
 
@@ -28,6 +28,18 @@ struct __align__(1024) TapnSmem {
   uint32_t tmem_base;
   int abort_flag;
 };
+
+// bar.sync with a literal barrier id (a register id makes ptxas reserve all 16 barriers of the CTA)
+template <int ID>
+__device__ __forceinline__ void group_sync() {
+  asm volatile("bar.sync %0, 128;" ::"n"(ID) : "memory");
+}
+__device__ __forceinline__ void group_sync(int g) {
+  if (g == 0)
+    group_sync<1>();
+  else
+    group_sync<2>();
+}
 
 __device__ __forceinline__ void decode(const TapnParams& p, int tile, int* n, int* gy0, int* gx0) {
   const int per = p.tiles_x * p.tiles_y;
@@ -106,57 +118,77 @@ __global__ void __launch_bounds__(kThreads, 2) tapn_kernel(const __grid_constant
       umma_commit_elect(&sm.tfull[acc]);
     }
   } else {
-    const int e = threadIdx.x - 64;  // 0..127
-    const int lg = warp & 3;         // the TMEM lane group this warp may read
-    const int m = lg * 32 + lane;    // tile pixel (row-major over 8 x 16) held by this thread
+    // two epilogue groups of four warps; group g owns accumulator stage g and every second tile of this CTA
+    const int g = (warp - 2) >> 2;
+    const int e = (threadIdx.x - 64) & 127;  // 0..127 within the group
+    const int lg = warp & 3;                 // the TMEM lane group this warp may read
+    const int m = lg * 32 + lane;            // tile pixel (row-major over 8 x 16) held by this thread
     float bias[3] = {0.f, 0.f, 0.f};
-    if (p.bias)
-      for (int c = 0; c < p.cout; ++c) bias[c] = __ldg(p.bias + c);
-    int tl = 0;
-    for (int t = first; t < p.tiles; t += step, ++tl) {
-      const int acc = tl & 1;
-      mbar_wait_nofail(&sm.tfull[acc], (tl >> 1) & 1, abortp);
+    if (p.bias) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        if (c < p.cout) bias[c] = __ldg(p.bias + c);
+    }
+    float* T = sm.t[g];
+    // the (at most two) outputs of this thread inside a tile: pixel-major, channel-minor
+    int oy[2], ox[2], co[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int idx = e + 128 * k;
+      const int px = idx / 3;
+      co[k] = idx - px * 3;
+      oy[k] = px / kInW;
+      ox[k] = px - oy[k] * kInW;
+      if (idx >= kInW * kInH * 3 || co[k] >= p.cout) oy[k] = -1;
+    }
+    for (int t = first + g * step, tl = g; t < p.tiles; t += 2 * step, tl += 2) {
+      int n, gy0, gx0;
+      decode(p, t, &n, &gy0, &gx0);
+      long long o[2];
+      float r[2] = {0.f, 0.f};
+      bool on[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {  // addresses and the residual first: their latency hides behind the MMA wait
+        const int gy = gy0 + oy[k], gx = gx0 + ox[k];
+        on[k] = oy[k] >= 0 && gy < p.H && gx < p.W;
+        o[k] = p.o_off + n * p.o_sn + gy * p.o_sh + gx * p.o_sw + co[k];
+        if (on[k] && p.res) {
+          const long long ro = p.r_off + n * p.r_sn + gy * p.r_sh + gx * p.r_sw + co[k];
+          r[k] = p.out_f32 ? __ldg(reinterpret_cast<const float*>(p.res) + ro)
+                           : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.res)[ro]);
+        }
+      }
+      mbar_wait_nofail(&sm.tfull[g], (tl >> 1) & 1, abortp);
       tc_fence_after();
       uint32_t v0[16], v1[16];
-      const uint32_t taddr = tmem + (static_cast<uint32_t>(lg * 32) << 16) + acc * 32;
+      const uint32_t taddr = tmem + (static_cast<uint32_t>(lg * 32) << 16) + g * 32;
       tmem_ld16(taddr, v0);
       tmem_ld16(taddr + 16, v1);
       tmem_ld_wait();
       tc_fence_before();
-      if (lane == 0) mbar_arrive(&sm.tempty[acc]);
-      float* T = sm.t[tl & 1];
+      if (lane == 0) mbar_arrive(&sm.tempty[g]);
+      group_sync(g);  // the group has finished reading the previous tile's T
 #pragma unroll
       for (int j = 0; j < 16; ++j) T[m * kTStride + j] = __uint_as_float(v0[j]);
 #pragma unroll
       for (int j = 0; j < 11; ++j) T[m * kTStride + 16 + j] = __uint_as_float(v1[j]);
-      // T[tl & 1] is rewritten two tiles from now; every thread passes the next tile's barrier in between, and it
-      // only gets there after its reads below - one barrier per tile is enough
-      named_bar_sync(1, 128);
-      int n, gy0, gx0;
-      decode(p, t, &n, &gy0, &gx0);
-      for (int idx = e; idx < kInW * kInH * 3; idx += 128) {
-        const int px = idx / 3, co = idx - px * 3;
-        const int oy = px / kInW, ox = px - oy * kInW;
-        const int gy = gy0 + oy, gx = gx0 + ox;
-        if (gy >= p.H || gx >= p.W || co >= p.cout) continue;
-        const float* tp = T + (oy * kTileW + ox) * kTStride + co;
+      group_sync(g);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (!on[k]) continue;
+        const float* tp = T + (oy[k] * kTileW + ox[k]) * kTStride + co[k];
         float s = 0.f;
 #pragma unroll
         for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
           for (int kw = 0; kw < 3; ++kw) s += tp[(kh * kTileW + kw) * kTStride + (kh * 3 + kw) * 3];
-        s += co == 0 ? bias[0] : (co == 1 ? bias[1] : bias[2]);
-        const long long o = p.o_off + n * p.o_sn + gy * p.o_sh + gx * p.o_sw + co;
-        if (p.res) {
-          const long long r = p.r_off + n * p.r_sn + gy * p.r_sh + gx * p.r_sw + co;
-          s += p.out_f32 ? __ldg(reinterpret_cast<const float*>(p.res) + r)
-                         : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.res)[r]);
-        }
+        s += co[k] == 0 ? bias[0] : (co[k] == 1 ? bias[1] : bias[2]);
+        s += r[k];
         if (p.act2 == kAct2Tanh) s = tanhf(s);
         if (p.out_f32)
-          reinterpret_cast<float*>(p.out)[o] = s;
+          reinterpret_cast<float*>(p.out)[o[k]] = s;
         else
-          reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16(s);
+          reinterpret_cast<__nv_bfloat16*>(p.out)[o[k]] = __float2bfloat16(s);
       }
     }
   }

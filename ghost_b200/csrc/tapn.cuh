@@ -20,7 +20,7 @@
 
 namespace ghost {
 
-constexpr int kTapnMaxChunks = 4;  // Cin <= 256
+constexpr int kTapnMaxChunks = 2;  // Cin <= 128
 
 struct TapnParams {
   CUtensorMap tmA;  // input NHWC bf16, box {64 channels, 16, 8, 1}, SWIZZLE_128B

@@ -47,7 +47,8 @@ CONV_CASES = [
     ("window_3x3_192_to_96", 1, 192, 40, 128, 96, 0, 3, 1, 1, 0),
     # <= 3 output channels: the nine taps ride in N (tapn.cu); ragged tiles, several K chunks, the smallest image
     ("tapn_3x3_128_to_2_ragged", 2, 128, 23, 45, 2, 0, 3, 1, 1, 0),
-    ("tapn_3x3_256_to_1", 1, 256, 16, 16, 1, 0, 3, 1, 1, 0),
+    ("tapn_3x3_128_to_1", 1, 128, 16, 16, 1, 0, 3, 1, 1, 0),
+    ("tapn_3x3_256_to_1_igemm", 1, 256, 16, 16, 1, 0, 3, 1, 1, 0),
     ("tapn_3x3_64_to_3_8x16", 3, 64, 8, 16, 3, 0, 3, 1, 1, 0),
 ]
 
