@@ -2,6 +2,9 @@
 // Reference: network/AEI_Net.py:44-156 (MLAttrEncoder, AADGenerator, AEI_Net),
 // network/AADLayer.py:5-80 (AADLayer, AAD_ResBlk).
 #include <math.h>
+#include <stdlib.h>
+
+#include <map>
 
 #include "net.cuh"
 
@@ -16,6 +19,15 @@ const BlockSpec kUnetBlocks[8] = {{1024, 1024, 1024}, {1024, 1024, 2048}, {1024,
                                   {512, 256, 256},    {256, 128, 128},    {128, 64, 64},      {64, 3, 64}};
 const BlockSpec kLinkBlocks[8] = {{1024, 1024, 1024}, {1024, 1024, 1024}, {1024, 1024, 512}, {1024, 512, 256},
                                   {512, 256, 128},    {256, 128, 64},     {128, 64, 32},     {64, 3, 32}};
+// AAD blocks whose shortcut layer and first main layer run as one paired launch (igemm.cuh aad_pair): tensor-core
+// mode, masks computed inside the epilogue (c_x <= 128).  GHOST_AAD_PAIR=0 keeps the two launches (A/B switch).
+bool aad_pairable(bool bf, int c_x) {
+  static const int on = [] {
+    const char* e = getenv("GHOST_AAD_PAIR");
+    return e ? (atoi(e) != 0) : 1;
+  }();
+  return on && bf && (c_x == 64 || c_x == 128);
+}
 const int kEncC[8] = {3, 32, 64, 128, 256, 512, 1024, 1024};
 // deconv i (1-based): Cin / Cout
 const int kUnetDecIn[6] = {1024, 2048, 1024, 512, 256, 128};
@@ -117,6 +129,7 @@ void Net::finalize_aei() {
         zbias[pos * 1024 + co] = b.data[co];
       }
   }
+  std::map<std::string, std::vector<float>> gb_rows, gb_bias;  // per layer, for the paired launches below
   auto add_aad = [&](const std::string& name, const std::string& key, int c_x, int c_attr) {
     AadInfo info;
     info.name = name;
@@ -148,6 +161,8 @@ void Net::finalize_aei() {
     const bool tc = bf && c_attr % 32 == 0;
     if (bf && !tc) fail(-1, "AAD attribute channels must be a multiple of 32");
     packed_[name + ".gb"] = pack(rows, 2 * c_x, c_attr, &bias, !bf, bf);
+    gb_rows[name] = rows;
+    gb_bias[name] = bias;
     const HostTensor& wh = W(key + ".conv_h.weight");
     expect_shape(wh, {1, c_x, 1, 1}, key + ".conv_h.weight");
     vecs_[name + ".wh"] = wpool_.upload(wh.data);
@@ -173,6 +188,14 @@ void Net::finalize_aei() {
     if (b.cin != b.cout) {
       add_aad(S("blk%d.aadsc", k), S("generator.AADBlk%d.last_add_block.0", k), b.cin, b.cattr);
       add_conv3(S("blk%d.convsc", k), S("generator.AADBlk%d.last_add_block.2.weight", k), b.cin, b.cout);
+      if (aad_pairable(bf, b.cin)) {
+        // the shortcut layer and the first main layer read the same h and z_attr: one launch, two N tiles
+        std::vector<float> rows = gb_rows.at(S("blk%d.aadsc", k)), bias = gb_bias.at(S("blk%d.aadsc", k));
+        const std::vector<float>&r0 = gb_rows.at(S("blk%d.aad0", k)), &b0 = gb_bias.at(S("blk%d.aad0", k));
+        rows.insert(rows.end(), r0.begin(), r0.end());
+        bias.insert(bias.end(), b0.begin(), b0.end());
+        packed_[S("blk%d.aadpair.gb", k)] = pack(rows, 4 * b.cin, b.cattr, &bias, false, true);
+      }
     }
   }
   zfc_cols_ = static_cast<int>(zbias.size());
@@ -205,8 +228,8 @@ void Net::build_aei(ExecPlan& p) {
     op.name = name;
     op.flops = lop.flops;
     op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : (aad ? kOpAadTC : kOpConvTC);
-    if (aad)  // apply read of h + z_attr read + write (gamma/beta never touch HBM)
-      op.bytes = static_cast<double>(B) * Ho * Wo * (2.0 * aad->c_x + Cin) * 2.0;
+    if (aad)  // apply read of h + z_attr read + write (gamma/beta never touch HBM); a pair reads h once
+      op.bytes = static_cast<double>(B) * Ho * Wo * ((aad->pair ? 1.5 : 2.0) * aad->c_x + Cin) * 2.0;
     op.run = [lop](cudaStream_t s) { return lop.launch(s); };
     p.ops.push_back(std::move(op));
   };
@@ -361,10 +384,40 @@ void Net::build_aei(ExecPlan& p) {
 
     // shortcut branch first so the residual add can ride in the epilogue of the last main conv
     Act sc;
+    const bool pair = b.cin != b.cout && packed_.count(S("blk%d.aadpair.gb", k)) != 0;
+    Act a2;  // pair: [aadsc output | aad0 output], 2 * cin channels
+    if (pair) {
+      // the shortcut AADLayer and the first main AADLayer both read (m, z_attr): one launch, two N tiles
+      a2 = new_act(hw, hw, 2 * b.cin);
+      const int cx = b.cin;
+      float4* ncpar2 = p.pool.alloc_n<float4>(static_cast<size_t>(B) * 2 * cx);
+      float* whf2 = p.pool.alloc_n<float>(static_cast<size_t>(B) * 2 * cx);
+      float* bhf2 = p.pool.alloc_n<float>(2 * static_cast<size_t>(B));
+      for (int L = 0; L < 2; ++L) {
+        const std::string lname = L == 0 ? S("blk%d.aadsc", k) : S("blk%d.aad0", k);
+        const AadInfo& info = aad_.at(lname);
+        float* fsc = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, cx));  // zeroed by the pool
+        const float* wh = vecs_.at(lname + ".wh");
+        const float bh = scalars_.at(lname + ".bh");
+        const int og = info.off_gamma, ob = info.off_beta;
+        float4* ncp = ncpar2 + L * cx;
+        float* whp = whf2 + L * cx;
+        float* bhp = bhf2 + L * B;
+        const float* sums = sums_m;
+        add_op(lname + ".fold", [=](cudaStream_t s) {
+          return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncp, whp, bhp, fsc, s, 2 * cx);
+        });
+      }
+      AadArgs args;
+      args.h = m.p; args.c_x = 2 * cx; args.pair = 1;
+      args.ncpar = ncpar2; args.wh_fold = whf2; args.bh_fold = bhf2;
+      add_conv(S("blk%d.aadpair.gemm_blend", k), za, 0, za.C, Taps::point(), hw, hw, S("blk%d.aadpair.gb", k),
+               OutView::dense(a2), Epilogue(), &args);
+    }
     if (b.cin != b.cout) {
       sc = new_act(hw, hw, b.cout);
-      aad_layer(S("blk%d.aadsc", k), m, sums_m);
-      add_conv(S("blk%d.convsc", k), a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
+      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m);
+      add_conv(S("blk%d.convsc", k), pair ? a2 : a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
                OutView::dense(sc), Epilogue(), nullptr);
     }
     Act x = m;
@@ -372,7 +425,8 @@ void Net::build_aei(ExecPlan& p) {
     Act y;
     for (int i = 0; i < num_blocks; ++i) {
       const bool last = i == num_blocks - 1;
-      aad_layer(S("blk%d.aad%d", k, i), x, sums_x);
+      const bool from_pair = pair && i == 0;
+      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x);
       const int co = last ? b.cout : b.cin;
       Act o = new_act(hw, hw, co);
       Epilogue e;
@@ -383,8 +437,8 @@ void Net::build_aei(ExecPlan& p) {
         e.r_sn = rv.sn; e.r_sh = rv.sh; e.r_sw = rv.sw; e.r_off = rv.off;
         if (k == 8) e.act2 = kAct2Tanh;
       }
-      add_conv(S("blk%d.conv%d", k, i), a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.conv%d", k, i),
-               OutView::dense(o), e, nullptr);
+      add_conv(S("blk%d.conv%d", k, i), from_pair ? a2 : a, from_pair ? b.cin : 0, b.cin, Taps::square(3, 1, 1), hw, hw,
+               S("blk%d.conv%d", k, i), OutView::dense(o), e, nullptr);
       if (!last) {
         float* sums_o = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * co);  // co == b.cin here
         const Act oo = o;

@@ -255,7 +255,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
 
   // ---- N tiling
   if (aad) {
-    const int cn = aad->c_x < 128 ? aad->c_x : 128;
+    const int cn = aad->pair ? aad->c_x / 2 : (aad->c_x < 128 ? aad->c_x : 128);
+    if (aad->pair && cn != 64 && cn != 128) return "lower_conv: paired AAD layers need 64 or 128 channels each";
     if (aad->c_x % cn || cn % 16) return "lower_conv: AAD c_x must be a multiple of 16";
     p.BN = 2 * cn;
     p.tiles_n = aad->c_x / cn;
@@ -314,7 +315,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.sets = 4 / hbox;
     // one N tile and 64-channel K chunks: the gamma/beta weights stay resident, only z_attr streams
     const int slab = p.ntaps * p.kc_per_tap * p.BN * p.kc * 2;
-    p.b_res = p.tiles_n == 1 && p.kc == 64 && slab <= 64 * 1024;
+    p.b_res = (p.tiles_n == 1 || aad->pair) && p.kc == 64 && slab <= 64 * 1024;
     if (p.b_res) {
       stage_bytes = 128 * p.kc * 2;
       resident_bytes = slab;
@@ -374,7 +375,9 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.mask = aad->mask;
     if (!w.bias) return "lower_conv: AAD needs the gamma/beta bias vector";
     if (aad->c_x % 64) return "lower_conv: AAD c_x must be a multiple of 64";
-    if (p.tiles_n > 1 && !aad->mask && !aad->spade) return "lower_conv: AAD with c_x > 128 needs the precomputed mask";
+    p.aad_pair = aad->pair;
+    if (aad->pair && (aad->mask || aad->spade || p.tiles_n != 2)) return "lower_conv: paired AAD layers compute their own masks";
+    if (p.tiles_n > 1 && !aad->mask && !aad->spade && !aad->pair) return "lower_conv: AAD with c_x > 128 needs the precomputed mask";
     p.aad_spade = aad->spade;
     p.aad_slope = aad->slope;
     p.aad_post = aad->post;
@@ -387,9 +390,13 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       const uint64_t cx = static_cast<uint64_t>(aad->c_x);
       const uint64_t dims[4] = {cx, static_cast<uint64_t>(Wo), static_cast<uint64_t>(Ho), static_cast<uint64_t>(in.N)};
       const uint64_t str[3] = {cx * eb, static_cast<uint64_t>(Wo) * cx * eb, static_cast<uint64_t>(Ho) * Wo * cx * eb};
+      const uint64_t ch = aad->pair ? cx / 2 : cx;  // channels of h
+      const uint64_t hdims[4] = {ch, dims[1], dims[2], dims[3]};
+      const uint64_t hstr[3] = {ch * eb, static_cast<uint64_t>(Wo) * ch * eb, static_cast<uint64_t>(Ho) * Wo * ch * eb};
       const uint32_t box[4] = {64u, static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
       // no_h: the map is never used by the kernel; it is encoded over the output tensor to stay valid
-      if (const char* e = encode_tmap(&p.tmH, aad->no_h ? out.p : aad->h, 4, dims, str, box, 128)) return e;
+      if (const char* e = encode_tmap(&p.tmH, aad->no_h ? out.p : aad->h, 4, aad->no_h ? dims : hdims, aad->no_h ? str : hstr, box, 128))
+        return e;
       // store box = the 32 consecutive tile rows (order n, h, w) one epilogue warp owns
       uint32_t ob[4] = {64u, 0, 1, 1};
       const int bw = p.bw, bh = p.bh, bn = p.bn;

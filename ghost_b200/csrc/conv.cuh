@@ -92,6 +92,7 @@ struct AadArgs {  // only for the fused AAD epilogue
   float slope = 0.f;
   const float* post = nullptr;
   int no_h = 0;  // SPADE variant without an h tensor (h = nullptr): out = act(beta half + bias) * post
+  int pair = 0;  // two layers on the same h / z_attr as the two N tiles (igemm.cuh aad_pair); c_x = 2 * channels of h
 };
 
 // A lowered, launch-ready op.

@@ -461,7 +461,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     if (p.b_res && elect_one()) {
       mbar_expect_tx(&bfull_bar, bres_tiles * b_tile_bytes);
       for (int i = 0; i < bres_tiles; ++i)
-        tma_load_2d(bres + i * b_tile_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * p.kc, 0);
+        tma_load_2d(bres + i * b_tile_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * p.kc,
+                    p.aad_pair ? static_cast<int>(blockIdx.x & 1) * p.BN : 0);
     }
     __syncwarp();
     grid_dep_wait();
@@ -484,7 +485,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           } else {
             mbar_expect_tx(&hfull_bar[hs], rows_used * cn * 2);
             for (int b = 0; b < hbox; ++b)
-              tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs], t.nt * cn + b * 64, w0, h0, n0);
+              tma_load_4d(hbuf + hs * htile_bytes + b * 16384, &p.tmH, &hfull_bar[hs],
+                          (p.aad_pair ? 0 : t.nt * cn) + b * 64, w0, h0, n0);
           }
         }
         __syncwarp();
@@ -788,6 +790,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         uint8_t* hrow = hbuf + hs * htile_bytes + box * 16384 + r * 128;
         uint8_t* hq = hbuf + hs * htile_bytes + box * 16384 + (lg * 32 + rq) * 128 + 4 * cq;  // + 1024k: row rq + 8k
         const int nq = min(t.tn, p.Nimg - 1);  // quad mapping: the image of the whole tile
+        // paired layers: this tile's layer = its N tile; rows of that layer in wh_fold / bh_fold
+        const int pair_c = p.aad_pair ? t.nt * cn : 0, pair_n = p.aad_pair ? t.nt * p.Nimg : 0;
 #ifdef GHOST_IGEMM_PROF
         const long long q0_ = clock64();
 #endif
@@ -807,7 +811,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             for (int kk = 0; kk < 4; ++kk) m4[kk] = __shfl_sync(0xffffffffu, m, rq + 8 * kk);
           } else {
             // every thread sums its 16 channels of its four rows, the four threads of a row add up by shuffle
-            const float* wrow = p.wh_fold + static_cast<long long>(nq) * p.c_x + box * 64 + 2 * cq;
+            const float* wrow = p.wh_fold + static_cast<long long>(nq) * p.c_x + pair_c + box * 64 + 2 * cq;
             float a4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -844,7 +848,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
                 a4[kk] = box == 0 ? a4[kk] + other : other + a4[kk];
               }
             }
-            const float bhf = __ldg(p.bh_fold + nq);
+            const float bhf = __ldg(p.bh_fold + pair_n + nq);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) m4[kk] = 1.f / (1.f + __expf(-(a4[kk] + bhf)));
           }
@@ -854,7 +858,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         } else {
           // sigmoid(conv_h(instance_norm(h))) with the normalisation folded into wh/bh (single N tile: cn == c_x).
           // Runs while the tensor core is still producing this tile's gamma/beta.
-          const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x + box * 64;
+          const float* wrow = p.wh_fold + static_cast<long long>(nc) * p.c_x + pair_c + box * 64;
           float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -879,7 +883,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const float other = ex[set * 2 + (box ^ 1)][r];
             acc = box == 0 ? acc + other : other + acc;
           }
-          m = 1.f / (1.f + __expf(-(acc + __ldg(p.bh_fold + nc))));
+          m = 1.f / (1.f + __expf(-(acc + __ldg(p.bh_fold + pair_n + nc))));
         }
         if (pend >= 0) {
           if (lane == 0) {
@@ -1109,7 +1113,8 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
-  if (p.b_res && (p.tiles_n != 1 || p.kc != 64 || p.splits != 1)) return "igemm: resident weights need one N tile";
+  if (p.b_res && ((p.tiles_n != 1 && !p.aad_pair) || p.kc != 64 || p.splits != 1))
+    return "igemm: resident weights need one N tile";
   if (p.stg && (p.mode != kModeLinear || p.out_f32 || p.splits != 1 || (p.BN != 128 && p.BN != 256) ||
                 p.n_valid % (p.BN >> 2)))
     return "igemm: staged output needs a bf16 linear epilogue and N tiles of 128 or 256 whole warp quarters";
@@ -1130,6 +1135,8 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
     if (gx < 1) gx = 1;
     if (gx > tiles) gx = tiles;
   }
+  if (p.aad_pair) gx &= ~1;  // CTA b serves layer b & 1 for its whole life
+  if (gx < 1) return "igemm: paired AAD layers need an even grid";
   dim3 grid(gx, p.splits, 1);
   // programmatic dependent launch: the prologue of this launch may overlap the tail of the previous kernel in the
   // stream (the kernel waits for it before touching activations); GHOST_PDL=0 falls back to plain serialisation

@@ -95,6 +95,13 @@ struct alignas(64) IgemmParams {
   // shared-memory staging + TMA store.  This is how the thin-K convs of sr.cu (K = 32 .. 128 per pixel, where the
   // row-per-thread stores of the linear epilogue are the whole cost) leave the SM.
   int aad_no_h;
+  // aad_pair: two AAD layers that read the SAME h and z_attr (the shortcut layer and the first main layer of an
+  // AAD block, AADLayer.py / AEI_Net.py AAD_ResBlk) as the two N tiles of one launch: weights / bias / ncpar /
+  // wh_fold rows of layer L at offset L * cn, bh_fold at L * Nimg, output channels [L*cn, (L+1)*cn) of a tensor of
+  // c_x = 2*cn channels; h has cn channels and each layer's mask comes from its own tile.  Tiles walk the N index
+  // fastest and the grid is even, so CTA pairs (2i, 2i+1) work on the same pixels at the same time: h and z_attr
+  // cross HBM once for both layers (the second reader hits L2), and every CTA keeps one layer's weights resident.
+  int aad_pair;
 
   int* err;  // device word set non-zero when a pipeline wait timed out
 };

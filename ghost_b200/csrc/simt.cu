@@ -381,7 +381,7 @@ __global__ void __launch_bounds__(256) aad_fold_kernel(const float* __restrict__
                                                         const float* __restrict__ zfc, int ldz, int off_gamma,
                                                         int off_beta, const float* __restrict__ w_h, float b_h,
                                                         float4* __restrict__ ncpar, float* __restrict__ wh_fold,
-                                                        float* __restrict__ bh_fold, float* scratch) {
+                                                        float* __restrict__ bh_fold, float* scratch, int ld_out) {
   __shared__ double shs[256], shq[256];
   __shared__ float red[2];
   __shared__ int is_last;
@@ -419,13 +419,13 @@ __global__ void __launch_bounds__(256) aad_fold_kernel(const float* __restrict__
     const float b = zfc[static_cast<long long>(n) * ldz + off_beta + c];
     // laid out per channel pair for the packed-fp32 epilogue: entry c&~1 = {rstd0, rstd1, shift0, shift1},
     // entry (c&~1)+1 = {gamma_id0, gamma_id1, beta_id0, beta_id1}
-    float* pp = reinterpret_cast<float*>(ncpar + static_cast<long long>(n) * C + (c & ~1)) + (c & 1);
+    float* pp = reinterpret_cast<float*>(ncpar + static_cast<long long>(n) * ld_out + (c & ~1)) + (c & 1);
     pp[0] = rstd;
     pp[2] = -mu * rstd;
     pp[4] = g;
     pp[6] = b;
     const float w = w_h[c] * rstd;
-    wh_fold[static_cast<long long>(n) * C + c] = w;
+    wh_fold[static_cast<long long>(n) * ld_out + c] = w;
     part = w * mu;
   }
   if (threadIdx.x < 64) {  // warps 0 and 1 hold the 64 channel terms
@@ -560,10 +560,10 @@ size_t aad_fold_scratch_floats(int N, int C) { return static_cast<size_t>(N) * (
 
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
-                            float* scratch, cudaStream_t s) {
+                            float* scratch, cudaStream_t s, int ld_out) {
   dim3 grid(N, (C + 63) / 64);
   aad_fold_kernel<<<grid, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold,
-                                       bh_fold, scratch);
+                                       bh_fold, scratch, ld_out > 0 ? ld_out : C);
   return last_err();
 }
 

@@ -45,7 +45,7 @@ const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, floa
 size_t aad_fold_scratch_floats(int N, int C);
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
-                            float* scratch, cudaStream_t s);
+                            float* scratch, cudaStream_t s, int ld_out = 0);  // ld_out: row stride of ncpar / wh_fold (0 = C)
 
 // bf16 mode, c_x > 128: the per-pixel sigmoid mask of an AADLayer, mask[N*HW] fp32.
 const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,

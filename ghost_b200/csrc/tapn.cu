@@ -15,7 +15,8 @@ namespace {
 using namespace ptx;
 
 constexpr int kStages = 4;
-constexpr int kTStride = 29;  // odd: lane-strided rows of T hit 32 different banks
+constexpr int kTStride = 35;  // odd (lane-strided row writes hit 32 banks) and = 3 mod 32 (the gather reads
+                              // pixel-major, channel-minor: consecutive lanes -> consecutive banks)
 constexpr int kThreads = 320;
 constexpr int kTileW = kTapnTileW, kTileH = kTapnTileH;  // pixels per tile incl. the halo ring
 constexpr int kInW = kTileW - 2, kInH = kTileH - 2;  // interior = outputs per tile
