@@ -326,12 +326,14 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
                                                                  int pix_per_block, float* __restrict__ parts,
                                                                  int common_shift) {
   extern __shared__ float sh[];  // [kStatThreads][16]
-  const int n = blockIdx.y;
+  // blocks walk the tensor backwards: its producer wrote it front to back, so the tail is what L2 still holds
+  const int n = gridDim.y - 1 - blockIdx.y;
+  const int bx = gridDim.x - 1 - blockIdx.x;
   const int P = gridDim.x;
   const int vecs = C >> 3;                       // channel vectors per pixel
   const int ppi = kStatThreads / vecs;           // pixels per iteration (vecs <= 256)
   const int cv = threadIdx.x % vecs, pl = threadIdx.x / vecs;
-  const int p0 = blockIdx.x * pix_per_block;
+  const int p0 = bx * pix_per_block;
   const int p1 = min(HW, p0 + pix_per_block);
   float s[8], q[8], sft[8];
 #pragma unroll
@@ -365,9 +367,9 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
     float a = 0.f;
     for (int l = 0; l < ppi; ++l) a += sh[(l * vecs + v) * 16 + slot];
     const int c = v * 8 + (slot & 7);
-    out[(2 * blockIdx.x + (slot >> 3)) * C + c] = a;
+    out[(2 * bx + (slot >> 3)) * C + c] = a;
   }
-  if (blockIdx.x == 0 && pl == 0) {
+  if (bx == 0 && pl == 0) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) out[2 * P * C + cv * 8 + i] = sft[i];
   }

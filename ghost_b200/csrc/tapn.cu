@@ -1,5 +1,6 @@
-// See tapn.cuh.  One persistent CTA pair per SM (192 threads each): warp 0 = TMA producer, warp 1 = MMA issuer and
-// TMEM owner, warps 2-5 and 6-9 = two epilogue groups on alternate tiles.  Per tile: one 16 KB TMA box per 64 input channels -> four tcgen05.mma
+// See tapn.cuh.  Two persistent CTAs per SM (320 threads each): warp 0 = TMA producer, warp 1 = MMA issuer and
+// TMEM owner, warps 2-5 and 6-9 = two epilogue groups on alternate tiles.  Per tile: one 16 KB TMA box per 64
+// input channels -> four tcgen05.mma
 // (M = 128 pixels, N = 32 = 9 taps x 3 channels padded, K = 16 each) -> the accumulator goes through shared memory,
 // where every interior pixel collects its nine neighbours' partial sums.
 #include "tapn.cuh"
@@ -43,6 +44,8 @@ __device__ __forceinline__ void group_sync(int g) {
 }
 
 __device__ __forceinline__ void decode(const TapnParams& p, int tile, int* n, int* gy0, int* gx0) {
+  // tiles are walked back to front: the producer of the input wrote it front to back, its tail is still in L2
+  tile = p.tiles - 1 - tile;
   const int per = p.tiles_x * p.tiles_y;
   const int nn = tile / per, r = tile - nn * per;
   const int by = r / p.tiles_x, bx = r - by * p.tiles_x;
