@@ -350,26 +350,44 @@ void Net::build_aei(ExecPlan& p) {
     if (!bf) gb = new_act(hw, hw, 2 * b.cin);
 
     // one AADLayer + ReLU: input h (with its statistics) -> a
-    auto aad_layer = [&](const std::string& lname, const Act& h, const float* sums) {
+    struct AadPre {  // per-layer tables written by the fold (+ the mask when it was computed ahead)
+      float4* ncpar;
+      float *whf, *bhf, *mask;
+    };
+    auto aad_fold = [&](const std::string& lname, const float* sums) {
       const AadInfo& info = aad_.at(lname);
-      float4* ncpar = p.pool.alloc_n<float4>(static_cast<size_t>(B) * b.cin);
-      float* whf = p.pool.alloc_n<float>(static_cast<size_t>(B) * b.cin);
-      float* bhf = p.pool.alloc_n<float>(B);
+      AadPre q;
+      q.ncpar = p.pool.alloc_n<float4>(static_cast<size_t>(B) * b.cin);
+      q.whf = p.pool.alloc_n<float>(static_cast<size_t>(B) * b.cin);
+      q.bhf = p.pool.alloc_n<float>(B);
+      q.mask = nullptr;
       float* fsc = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, b.cin));  // zeroed by the pool
       const float* wh = vecs_.at(lname + ".wh");
       const float bh = scalars_.at(lname + ".bh");
       const int cx = b.cin, og = info.off_gamma, ob = info.off_beta;
+      float4* ncpar = q.ncpar;
+      float *whf = q.whf, *bhf = q.bhf;
       add_op(lname + ".fold", [=](cudaStream_t s) {
         return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, fsc, s);
       });
+      return q;
+    };
+    auto aad_layer = [&](const std::string& lname, const Act& h, const float* sums, const AadPre* pre = nullptr) {
+      const AadPre q = pre ? *pre : aad_fold(lname, sums);
+      float4* ncpar = q.ncpar;
+      float *whf = q.whf, *bhf = q.bhf;
+      const int cx = b.cin;
       if (bf) {
         AadArgs args;
         args.h = h.p; args.c_x = cx; args.ncpar = ncpar; args.wh_fold = whf; args.bh_fold = bhf;
         if (cx > 128) {  // several N tiles per pixel: the sigmoid mask is computed once, ahead of the GEMM
-          float* mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
-          const Act hh = h;
-          add_op(lname + ".mask", [=](cudaStream_t s) { return aad_mask_launch(hh.p, B, HW, cx, whf, bhf, mask, s); },
-                 kOpStats, static_cast<double>(B) * HW * cx * esz);
+          float* mask = q.mask;
+          if (!mask) {
+            mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
+            const Act hh = h;
+            add_op(lname + ".mask", [=](cudaStream_t s) { return aad_mask_launch(hh.p, B, HW, cx, whf, bhf, mask, s); },
+                   kOpStats, static_cast<double>(B) * HW * cx * esz);
+          }
           args.mask = mask;
         }
         add_conv(lname + ".gemm_blend", za, 0, za.C, Taps::point(), hw, hw, lname + ".gb", OutView::dense(a),
@@ -416,9 +434,24 @@ void Net::build_aei(ExecPlan& p) {
       add_conv(S("blk%d.aadpair.gemm_blend", k), za, 0, za.C, Taps::point(), hw, hw, S("blk%d.aadpair.gb", k),
                OutView::dense(a2), Epilogue(), &args);
     }
+    // c_x > 128: the masks of the shortcut layer and of the first main layer in one pass over m
+    AadPre pre_sc{}, pre_0{};
+    const bool mask2 = bf && !pair && b.cin != b.cout && b.cin > 128;
+    if (mask2) {
+      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m);
+      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m);
+      pre_sc.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
+      pre_0.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
+      const Act mm = m;
+      const AadPre qs = pre_sc, q0 = pre_0;
+      const int cx = b.cin;
+      add_op(S("blk%d.aadsc+aad0.mask", k), [=](cudaStream_t s) {
+        return aad_mask2_launch(mm.p, B, HW, cx, qs.whf, qs.bhf, qs.mask, q0.whf, q0.bhf, q0.mask, s);
+      }, kOpStats, static_cast<double>(B) * HW * cx * esz);
+    }
     if (b.cin != b.cout) {
       sc = new_act(hw, hw, b.cout);
-      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m);
+      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, mask2 ? &pre_sc : nullptr);
       add_conv(S("blk%d.convsc", k), pair ? a2 : a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
                OutView::dense(sc), Epilogue(), nullptr);
     }
@@ -428,7 +461,7 @@ void Net::build_aei(ExecPlan& p) {
     for (int i = 0; i < num_blocks; ++i) {
       const bool last = i == num_blocks - 1;
       const bool from_pair = pair && i == 0;
-      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x);
+      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x, (mask2 && i == 0) ? &pre_0 : nullptr);
       const int co = last ? b.cout : b.cin;
       Act o = new_act(hw, hw, co);
       Epilogue e;

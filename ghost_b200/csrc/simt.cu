@@ -483,39 +483,116 @@ __global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h,
 
 // sigmoid(conv_h(instance_norm(h))) per pixel with the normalisation folded into wh/bh: one warp per pixel,
 // 16-byte loads, warp-shuffle reduction over the channels (used when c_x > 128, i.e. several N tiles per pixel).
+// The folded weights depend on the image only: every lane keeps its NIT x 8 of them in registers and reloads them
+// when its pixel sequence crosses into the next image, so the inner loop is one 16-byte load of h per 8 channels.
+// DUAL: a second layer on the same h (the shortcut layer and the first main layer of a block) in the same pass.
+template <int NIT, bool DUAL>
 __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __restrict__ h, long long npix, int HW, int C,
                                                         const float* __restrict__ wh_fold,
-                                                        const float* __restrict__ bh_fold, float* __restrict__ mask) {
+                                                        const float* __restrict__ bh_fold, float* __restrict__ mask,
+                                                        const float* __restrict__ wh_fold2,
+                                                        const float* __restrict__ bh_fold2, float* __restrict__ mask2) {
   const int lane = threadIdx.x & 31;
   const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
-  for (long long pix = warp0; pix < npix; pix += nwarps) {
+  float w[NIT][8], u[DUAL ? NIT : 1][8];
+  float bh = 0.f, bh2 = 0.f;
+  int cur_n = -1;
+  // every warp owns a run of consecutive pixels, so it crosses an image boundary at most once or twice
+  const long long chunk = (npix + nwarps - 1) / nwarps;
+  const long long pend = min(npix, (warp0 + 1) * chunk);
+  for (long long pix = warp0 * chunk; pix < pend; ++pix) {
     const int n = static_cast<int>(pix / HW);
+    if (n != cur_n) {
+      cur_n = n;
+      const float* wrow = wh_fold + static_cast<long long>(n) * C;
+      bh = __ldg(bh_fold + n);
+      if (DUAL) bh2 = __ldg(bh_fold2 + n);
+#pragma unroll
+      for (int it = 0; it < NIT; ++it) {
+        const int c = it * 256 + lane * 8;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, b0 = a0, b1 = a0;
+        if (c < C) {
+          a0 = __ldg(reinterpret_cast<const float4*>(wrow + c));
+          a1 = __ldg(reinterpret_cast<const float4*>(wrow + c) + 1);
+          if (DUAL) {
+            const float* urow = wh_fold2 + static_cast<long long>(n) * C;
+            b0 = __ldg(reinterpret_cast<const float4*>(urow + c));
+            b1 = __ldg(reinterpret_cast<const float4*>(urow + c) + 1);
+          }
+        }
+        w[it][0] = a0.x; w[it][1] = a0.y; w[it][2] = a0.z; w[it][3] = a0.w;
+        w[it][4] = a1.x; w[it][5] = a1.y; w[it][6] = a1.z; w[it][7] = a1.w;
+        if (DUAL) {
+          u[it][0] = b0.x; u[it][1] = b0.y; u[it][2] = b0.z; u[it][3] = b0.w;
+          u[it][4] = b1.x; u[it][5] = b1.y; u[it][6] = b1.z; u[it][7] = b1.w;
+        }
+      }
+    }
     const __nv_bfloat16* hrow = h + pix * C;
-    const float* wrow = wh_fold + static_cast<long long>(n) * C;
-    float acc = 0.f;
-    for (int c = lane * 8; c < C; c += 256) {
-      float v[8];
-      load8(hrow + c, v);
-      const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + c));
-      const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + c) + 1);
-      acc += v[0] * w0.x + v[1] * w0.y + v[2] * w0.z + v[3] * w0.w + v[4] * w1.x + v[5] * w1.y + v[6] * w1.z + v[7] * w1.w;
+    float v[NIT][8];
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int c = it * 256 + lane * 8;
+      if (c < C) {
+        load8(hrow + c, v[it]);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) v[it][q] = 0.f;
+      }
+    }
+    float acc = 0.f, acc2 = 0.f;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      // same association as one expression per 8 channels: products summed left to right, then added to acc
+      acc += v[it][0] * w[it][0] + v[it][1] * w[it][1] + v[it][2] * w[it][2] + v[it][3] * w[it][3] +
+             v[it][4] * w[it][4] + v[it][5] * w[it][5] + v[it][6] * w[it][6] + v[it][7] * w[it][7];
+      if (DUAL)
+        acc2 += v[it][0] * u[it][0] + v[it][1] * u[it][1] + v[it][2] * u[it][2] + v[it][3] * u[it][3] +
+                v[it][4] * u[it][4] + v[it][5] * u[it][5] + v[it][6] * u[it][6] + v[it][7] * u[it][7];
     }
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) mask[pix] = 1.f / (1.f + __expf(-(acc + __ldg(bh_fold + n))));
+    if (lane == 0) mask[pix] = 1.f / (1.f + __expf(-(acc + bh)));
+    if (DUAL) {
+      for (int o = 16; o > 0; o >>= 1) acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+      if (lane == 0) mask2[pix] = 1.f / (1.f + __expf(-(acc2 + bh2)));
+    }
   }
+}
+
+template <int NIT>
+void aad_mask_dispatch(unsigned blocks, cudaStream_t s, const __nv_bfloat16* h, long long npix, int HW, int C,
+                       const float* wh_fold, const float* bh_fold, float* mask, const float* wh_fold2,
+                       const float* bh_fold2, float* mask2) {
+  if (wh_fold2)
+    aad_mask_kernel<NIT, true><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else
+    aad_mask_kernel<NIT, false><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr);
 }
 
 }  // namespace
 
 const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
                             cudaStream_t s) {
+  return aad_mask2_launch(h, N, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr, s);
+}
+
+const char* aad_mask2_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
+                             const float* wh_fold2, const float* bh_fold2, float* mask2, cudaStream_t s) {
   if (C % 8) return "aad_mask: C must be a multiple of 8";
   const long long npix = static_cast<long long>(N) * HW;
   long long blocks = (npix + 7) / 8;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  aad_mask_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(h), npix, HW, C,
-                                                               wh_fold, bh_fold, mask);
+  const __nv_bfloat16* hp = reinterpret_cast<const __nv_bfloat16*>(h);
+  const unsigned nb = static_cast<unsigned>(blocks);
+  if (C <= 256)
+    aad_mask_dispatch<1>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else if (C <= 512)
+    aad_mask_dispatch<2>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else if (C <= 1024)
+    aad_mask_dispatch<4>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else
+    return "aad_mask: C must be <= 1024";
   return last_err();
 }
 
