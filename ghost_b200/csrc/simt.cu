@@ -211,8 +211,9 @@ __global__ void __launch_bounds__(128) rgb_conv_kernel(const SimtConvParams p) {
   }
   __syncthreads();
   const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
-  const long long m = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (m >= M) return;
+  // a block walks many groups of 128 pixels: the weight matrix is staged once per block, not once per 128 pixels
+  for (long long m = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; m < M;
+       m += static_cast<long long>(gridDim.x) * blockDim.x) {
   const int ow = static_cast<int>(m % p.Wo);
   const long long t = m / p.Wo;
   const int oh = static_cast<int>(t % p.Ho);
@@ -254,12 +255,15 @@ __global__ void __launch_bounds__(128) rgb_conv_kernel(const SimtConvParams p) {
     }
     store8(out + 8 * q, v);
   }
+  }
 }
 
 template <typename T>
 const char* rgb_conv_dispatch(const SimtConvParams& p, cudaStream_t s) {
   const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
-  const unsigned blocks = static_cast<unsigned>((M + 127) / 128);
+  long long nb = (M + 127) / 128;
+  if (nb > 148 * 8) nb = 148 * 8;
+  const unsigned blocks = static_cast<unsigned>(nb);
   if (p.Cout == 32)
     rgb_conv_kernel<T, 32><<<blocks, 128, 0, s>>>(p);
   else
