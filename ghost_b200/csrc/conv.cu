@@ -138,6 +138,10 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;
     p.act2 = epi.act2;
     if (epi.out2) return "lower_conv: the second output needs the tensor-core path";
+    if (rgb_const_supported(p, in.dtype)) {
+      op->rgb = std::make_shared<RgbConvConst>();
+      if (const char* e = rgb_const_prepare(p, op->rgb.get())) return e;
+    }
     return nullptr;
   }
 

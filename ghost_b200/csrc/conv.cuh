@@ -2,6 +2,7 @@
 // phase / linear layer and is lowered either to the tcgen05 implicit-GEMM kernel
 // (bf16 mode) or to the CUDA-core kernel (fp32 mode, Cin not a multiple of 32).
 #pragma once
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -102,9 +103,11 @@ struct LaunchOp {
   TapnParams tp;
   SimtConvParams sc;
   int simt_dtype = kBF16;
+  std::shared_ptr<RgbConvConst> rgb;  // Cin = 3 stems: weights by value in the kernel parameters (simt.cuh)
   std::string name;
   double flops = 0.0;
   const char* launch(cudaStream_t s) const {
+    if (kind == kSimt && rgb) return rgb_const_launch(sc, *rgb, simt_dtype, s);
     return kind == kIgemm ? igemm_launch(ig, s) : kind == kTapn ? tapn_launch(tp, s) : simt_conv_launch(sc, simt_dtype, s);
   }
 };

@@ -1,4 +1,8 @@
 #include "simt.cuh"
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
 
 #include "sr_kernels.cuh"  // in_stats_launch_ex
 
@@ -258,6 +262,57 @@ __global__ void __launch_bounds__(128) rgb_conv_kernel(const SimtConvParams p) {
   }
 }
 
+// Same layer with the weights in the kernel-parameter constant bank (simt.cuh RgbConvConst).  K x K taps, stride S,
+// pad 1; every loop is unrolled so each FFMA reads its weight as c[0][imm].
+template <typename T, int COUT, int K, int S>
+__global__ void __launch_bounds__(128) rgb_const_kernel(const SimtConvParams p, const __grid_constant__ RgbConvConst cw) {
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  const T* in = reinterpret_cast<const T*>(p.in);
+  for (long long m = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; m < M;
+       m += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int ow = static_cast<int>(m % p.Wo);
+    const long long t = m / p.Wo;
+    const int oh = static_cast<int>(t % p.Ho);
+    const int n = static_cast<int>(t / p.Ho);
+    float acc[COUT];
+#pragma unroll
+    for (int i = 0; i < COUT; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < K; ++kh) {
+      const int ih = oh * S + kh - 1;
+      const bool vh = ih >= 0 && ih < p.H;
+#pragma unroll
+      for (int kw = 0; kw < K; ++kw) {
+        const int iw = ow * S + kw - 1;
+        const bool v = vh && iw >= 0 && iw < p.W;
+        const T* px = in + ((static_cast<long long>(n) * p.H + (v ? ih : 0)) * p.W + (v ? iw : 0)) * 3;
+        float x[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) x[c] = v ? ldf(px + c) : 0.f;
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int co = 0; co < COUT; ++co) acc[co] = fmaf(x[c], cw.w[((kh * K + kw) * 3 + c) * COUT + co], acc[co]);
+      }
+    }
+    T* out = reinterpret_cast<T*>(p.out) + n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+#pragma unroll
+    for (int q = 0; q < COUT / 8; ++q) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float a = acc[8 * q + i] + cw.bias[8 * q + i];
+        if (p.act1 == kActLeaky || p.act1 == kActPRelu)
+          a = a > 0.f ? a : a * cw.slope[8 * q + i];
+        else if (p.act1 == kActRelu)
+          a = fmaxf(a, 0.f);
+        v[i] = a;
+      }
+      store8(out + 8 * q, v);
+    }
+  }
+}
+
 template <typename T>
 const char* rgb_conv_dispatch(const SimtConvParams& p, cudaStream_t s) {
   const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
@@ -272,6 +327,68 @@ const char* rgb_conv_dispatch(const SimtConvParams& p, cudaStream_t s) {
 }
 
 }  // namespace
+
+namespace {
+// 0: not a stem shape; 1: 4x4 s2 p1 -> 32; 2: 3x3 s1 p1 -> 64
+int rgb_const_shape(const SimtConvParams& p) {
+  const uintptr_t al = reinterpret_cast<uintptr_t>(p.out);
+  if (p.Cin != 3 || p.C != 3 || p.c0 != 0 || p.res || p.act2 != kAct2None || (al % 16) || (p.o_sw % 8) ||
+      (p.o_sh % 8) || (p.o_sn % 8) || (p.o_off % 8))
+    return 0;
+  int k = 0, shape = 0;
+  if (p.ntaps == 16 && p.stride == 2 && p.Cout == 32) k = 4, shape = 1;
+  if (p.ntaps == 9 && p.stride == 1 && p.Cout == 64) k = 3, shape = 2;
+  if (!shape) return 0;
+  for (int i = 0; i < p.ntaps; ++i)
+    if (p.dh[i] != i / k - 1 || p.dw[i] != i % k - 1) return 0;
+  return shape;
+}
+}  // namespace
+
+bool rgb_const_supported(const SimtConvParams& p, int dtype) {
+  static const int on = [] {
+    const char* e = getenv("GHOST_RGB_CONST");  // A/B switch for profiling: 0 keeps the shared-memory kernel
+    return e ? (atoi(e) != 0) : 1;
+  }();
+  return on && (dtype == kF32 || dtype == kBF16) && rgb_const_shape(p) != 0;
+}
+
+const char* rgb_const_prepare(const SimtConvParams& p, RgbConvConst* c) {
+  const int K = p.ntaps * 3;
+  std::vector<float> w(static_cast<size_t>(p.Cout) * K);
+  memset(c, 0, sizeof(*c));
+  if (cudaMemcpy(w.data(), p.w, w.size() * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess) return "rgb_const: weight copy failed";
+  for (int co = 0; co < p.Cout; ++co)
+    for (int k = 0; k < K; ++k) c->w[k * p.Cout + co] = w[static_cast<size_t>(co) * K + k];
+  if (p.bias && cudaMemcpy(c->bias, p.bias, p.Cout * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+    return "rgb_const: bias copy failed";
+  if (p.act1 == kActPRelu) {
+    if (cudaMemcpy(c->slope, p.slope_c, p.Cout * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+      return "rgb_const: slope copy failed";
+  } else {
+    for (int i = 0; i < p.Cout; ++i) c->slope[i] = p.slope;
+  }
+  return nullptr;
+}
+
+const char* rgb_const_launch(const SimtConvParams& p, const RgbConvConst& c, int dtype, cudaStream_t s) {
+  const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;
+  long long nb = (M + 127) / 128;
+  if (nb > 148 * 16) nb = 148 * 16;
+  const unsigned blocks = static_cast<unsigned>(nb);
+  const int shape = rgb_const_shape(p);
+  if (shape == 1 && dtype == kBF16)
+    rgb_const_kernel<__nv_bfloat16, 32, 4, 2><<<blocks, 128, 0, s>>>(p, c);
+  else if (shape == 1 && dtype == kF32)
+    rgb_const_kernel<float, 32, 4, 2><<<blocks, 128, 0, s>>>(p, c);
+  else if (shape == 2 && dtype == kBF16)
+    rgb_const_kernel<__nv_bfloat16, 64, 3, 1><<<blocks, 128, 0, s>>>(p, c);
+  else if (shape == 2 && dtype == kF32)
+    rgb_const_kernel<float, 64, 3, 1><<<blocks, 128, 0, s>>>(p, c);
+  else
+    return "rgb_const: unsupported shape";
+  return last_err();
+}
 
 const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s) {
   const long long M = static_cast<long long>(p.N) * p.Ho * p.Wo;

@@ -34,6 +34,22 @@ struct SimtConvParams {
 // dtype: kF32 or kBF16 activations (weights and accumulation are always fp32)
 const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s);
 
+// The Cin = 3 stems (AEI_Net encoder conv1: 4x4 s2 p1 -> 32; iresnet conv1: 3x3 s1 p1 -> 64) with the whole weight
+// matrix, bias and slopes passed BY VALUE as a kernel parameter (13 KB; CUDA >= 12.1 allows 32 KB): the FFMAs take
+// their weight operand straight from the constant bank, so the loop is pure FMA issue.  (Weights in shared memory
+// cost one LDS.128 per four FFMA, and a broadcast LDS.128 still occupies the SM's shared-memory pipe for four cycles
+// - the layer ran at 29 % of the FMA rate.)
+struct RgbConvConst {
+  float w[48 * 64];  // [tap*3 + c][Cout]
+  float bias[64];
+  float slope[64];   // LeakyReLU / PReLU slope per channel (act1), unused otherwise
+};
+// true when (p, taps) is one of the two stem shapes rgb_const_launch handles
+bool rgb_const_supported(const SimtConvParams& p, int dtype);
+// fills `c` from the device-side weights / bias / slopes of p (synchronous copies: plan-build time only)
+const char* rgb_const_prepare(const SimtConvParams& p, RgbConvConst* c);
+const char* rgb_const_launch(const SimtConvParams& p, const RgbConvConst& c, int dtype, cudaStream_t s);
+
 // Instance-norm statistics, NHWC, as deterministic per-block partial sums about a per-(n,c) shift.
 // parts: [N][2*P + 1][C] fp32 with P = in_stats_parts(N, HW, C) (layout in simt.cu); fully overwritten by the call.
 int in_stats_parts(int N, int HW, int C);
