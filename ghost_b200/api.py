@@ -628,7 +628,7 @@ class SwapPipeline(object):
                 "src": torch.empty((self.B, 224, 224, 3), **u8), "crp": torch.empty((self.B, 256, 256, 3), **u8),
                 "frm": torch.empty((self.B, H, W, 3), **u8), "out": torch.empty((self.B, H, W, 3), **u8),
                 "msk": torch.empty((self.B, 224, 224), dtype=mask_dtype, device=self.dev),
-                "ev_in": torch.cuda.Event(), "ev_done": torch.cuda.Event(), "ev_out": torch.cuda.Event(), "used": False})
+                "ev_in": torch.cuda.Event(), "ev_frm": torch.cuda.Event(), "ev_done": torch.cuda.Event(), "ev_out": torch.cuda.Event(), "used": False})
         self.s_in = torch.cuda.Stream(device=self.dev)
         self.s_out = torch.cuda.Stream(device=self.dev)
         self.s_enc = torch.cuda.Stream(device=self.dev)   # attribute encoder beside the ArcFace network
@@ -645,16 +645,20 @@ class SwapPipeline(object):
         if slot["used"]:
             self.s_in.wait_event(slot["ev_done"])   # the step that last read this slot's inputs has finished
         with torch.cuda.stream(self.s_in):
+            # the networks need only the small tensors (22 MB): they start while the frames (398 MB at 1080p) are
+            # still crossing PCIe; only the paste-back waits for those
             slot["src"].copy_(sources, non_blocking=True)
             slot["crp"].copy_(crops, non_blocking=True)
+            slot["ev_in"].record(self.s_in)
             slot["frm"].copy_(frames, non_blocking=True)
             slot["msk"].copy_(masks, non_blocking=True)
-            slot["ev_in"].record(self.s_in)
+            slot["ev_frm"].record(self.s_in)
         main.wait_event(slot["ev_in"])
-        if slot["used"]:
-            main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
         embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
         yptr, ydt = self.G.y_nhwc(self.B, self.dev)
+        main.wait_event(slot["ev_frm"])
+        if slot["used"]:
+            main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
         paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=slot["out"])
         slot["ev_done"].record(main)
         self.s_out.wait_event(slot["ev_done"])
