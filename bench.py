@@ -178,6 +178,9 @@ def run_ours(args):
         raise RuntimeError("bench.py needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # one process per GPU: sit on the CPUs / memory of the GPU's NUMA node before any pinned buffer is allocated
+    from ghost_b200.shard import bind_to_gpu_numa
+    numa = bind_to_gpu_numa(local) if os.environ.get("GHOST_NUMA_BIND", "1") != "0" else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -327,7 +330,7 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic", "config": workload_config(world),
+            "dtype": "bf16", "data": "synthetic", "config": dict(workload_config(world), host_numa_node=numa),
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(out_p.numel()),
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches_per_step * args.steps),
@@ -367,6 +370,9 @@ def run_config5(args):
         raise RuntimeError("bench.py needs a CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # one process per GPU: sit on the CPUs / memory of the GPU's NUMA node before any pinned buffer is allocated
+    from ghost_b200.shard import bind_to_gpu_numa
+    numa = bind_to_gpu_numa(local) if os.environ.get("GHOST_NUMA_BIND", "1") != "0" else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)

@@ -3,6 +3,8 @@ weights are replicated; there is no collective inside the forward.  The only exc
 gather of finished uint8 frames on the consumer rank.
 
 One process per GPU under torch.distributed (NCCL on the GPUs, gloo in the CPU tests)."""
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -66,4 +68,32 @@ class FrameSharder(object):
             return out
         if self.local_count > 0:
             dist.send(local_frames.contiguous(), dst=dst, group=self.group)
+        return None
+
+
+def bind_to_gpu_numa(device_index):
+    """Pin this process (one per GPU) to the CPUs of the NUMA node its GPU hangs off, so that the pinned host buffers
+    allocated afterwards (first touch) and the copy threads sit next to the GPU's PCIe root port.  Reads the PCI
+    bus id from torch and the node from sysfs; returns the node, or None when the platform does not say (single
+    socket, container without sysfs) - then nothing is changed."""
+    import torch
+    try:
+        bdf = torch.cuda.get_device_properties(device_index).pci_bus_id
+        dom = torch.cuda.get_device_properties(device_index).pci_domain_id
+        dev = torch.cuda.get_device_properties(device_index).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bdf, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.extend(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError, RuntimeError):
         return None
