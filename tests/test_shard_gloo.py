@@ -50,3 +50,13 @@ def test_gather_in_frame_order_world2(n_frames):
         p.join(timeout=120)
         assert p.exitcode == 0
     assert q.get(timeout=5) is True
+
+
+def test_numa_binding_is_a_noop_without_topology():
+    """bind_to_gpu_numa: no CUDA device / no NUMA information -> None, CPU affinity untouched."""
+    from ghost_b200.shard import bind_to_gpu_numa
+
+    before = os.sched_getaffinity(0)
+    assert bind_to_gpu_numa(0) is None or isinstance(bind_to_gpu_numa(0), int)
+    if not torch.cuda.is_available():
+        assert os.sched_getaffinity(0) == before
