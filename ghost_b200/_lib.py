@@ -73,6 +73,8 @@ SIGNATURES = {
     "ghost_preproc_u8": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "ghost_postproc_u8": (_i, [_vp, _i, _vp, _i, _vp]),
     "ghost_paste_back": (_i, [C.POINTER(PasteDesc), _vp]),
+    "ghost_paste_boxes": (_i, [C.POINTER(_d), _i, _i, _i, C.POINTER(_i)]),
+    "ghost_copy_boxes": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), _i, _i, _vp]),
     "ghost_match_identities": (_i, [_vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp, _vp]),
     "ghost_crop_faces": (_i, [_vp, _i, _i, _i, C.POINTER(_d), C.POINTER(_i), _i, _vp, _vp, _vp]),
     "ghost_face_masks": (_i, [_fp, C.POINTER(_i), _i, _vp, _i, _vp]),

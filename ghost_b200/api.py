@@ -605,6 +605,33 @@ def embed_and_swap(G, arc, sources_rgb224, crops_bgr, side=None, event=None, out
     return G.generate_u8(z, crops_bgr.shape[0], out=out, write_u8=write_u8)
 
 
+def paste_boxes(tfms, frame_hw):
+    """Bounding boxes the paste-back rewrites, one per face: int32 [n,4] = (x0, y0, x1, y1), x1 / y1 exclusive, all
+    zero for a face outside its frame.  Everything outside these boxes leaves get_final_image / get_final_video
+    unchanged (image_processing.py:66-75: the warped mask is 0 there)."""
+    tf = np.ascontiguousarray(np.asarray(tfms, dtype=np.float64).reshape(-1, 2, 3))
+    boxes = np.zeros((tf.shape[0], 4), dtype=np.int32)
+    lib = _lib.load()
+    _lib.check(lib.ghost_paste_boxes(tf.ctypes.data_as(C.POINTER(C.c_double)), tf.shape[0], int(frame_hw[0]),
+                                     int(frame_hw[1]), boxes.ctypes.data_as(C.POINTER(C.c_int))))
+    return boxes
+
+
+def _copy_boxes(dst, src, face_frame, boxes, to_device):
+    """Box pixels of [F,H,W,3] uint8 frames between a pinned host tensor and a device tensor of the same shape,
+    asynchronously on the current stream (cudaMemcpy2DAsync per box).  Returns the bytes moved."""
+    F, H, W = int(dst.shape[0]), int(dst.shape[1]), int(dst.shape[2])
+    ff = np.ascontiguousarray(np.asarray(face_frame, dtype=np.int32).reshape(-1))
+    bx = np.ascontiguousarray(np.asarray(boxes, dtype=np.int32).reshape(-1, 4))
+    lib = _lib.load()
+    devt = dst if to_device else src
+    with torch.cuda.device(devt.device):
+        _lib.check(lib.ghost_copy_boxes(dst.data_ptr(), src.data_ptr(), F, H, W, ff.ctypes.data_as(C.POINTER(C.c_int)),
+                                        bx.ctypes.data_as(C.POINTER(C.c_int)), len(ff), 1 if to_device else 0,
+                                        _stream()))
+    return int(((bx[:, 2] - bx[:, 0]) * (bx[:, 3] - bx[:, 1])).sum()) * 3
+
+
 class SwapPipeline(object):
     """The per-batch video loop of the reference (utils/inference/core.py:model_inference ->
     faceshifter_batch -> video_processing.py:get_final_video) as one double-buffered device pipeline:
@@ -615,10 +642,16 @@ class SwapPipeline(object):
     neighbouring batches overlap the generator.  Results are bit-identical to calling embed_hwc / swap_u8 /
     paste_back one after the other.  Call submit() per batch and flush() before reading the last outputs."""
 
-    def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None):
+    def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None,
+                 boxes_only=False):
         if not torch.cuda.is_available():
             raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
         self.G, self.arc, self.B, self.mode, self.depth = G, arc, int(batch), mode, int(depth)
+        # boxes_only: the frames stay in the caller's pinned host buffer and are composited IN PLACE - only the face
+        # boxes cross PCIe (up, composited on the device, down into the same host frames); `out` must be `frames`
+        self.boxes_only = bool(boxes_only)
+        self.frame_hw = (int(frame_hw[0]), int(frame_hw[1]))
+        self.h2d_bytes = self.d2h_bytes = 0       # bytes of the last submit()
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         H, W = frame_hw
         u8 = dict(dtype=torch.uint8, device=self.dev)
@@ -644,26 +677,41 @@ class SwapPipeline(object):
         main = torch.cuda.current_stream(self.dev)
         if slot["used"]:
             self.s_in.wait_event(slot["ev_done"])   # the step that last read this slot's inputs has finished
+            if self.boxes_only:
+                self.s_in.wait_event(slot["ev_out"])  # ... and its boxes have been read back out of slot["frm"]
         with torch.cuda.stream(self.s_in):
             # the networks need only the small tensors (22 MB): they start while the frames (398 MB at 1080p) are
             # still crossing PCIe; only the paste-back waits for those
             slot["src"].copy_(sources, non_blocking=True)
             slot["crp"].copy_(crops, non_blocking=True)
             slot["ev_in"].record(self.s_in)
-            slot["frm"].copy_(frames, non_blocking=True)
+            if self.boxes_only:
+                if out is not frames:
+                    raise ValueError("boxes_only composites in place: pass out=frames")
+                boxes = paste_boxes(tfms, self.frame_hw)
+                nb = _copy_boxes(slot["frm"], frames, face_frame, boxes, to_device=True)
+            else:
+                slot["frm"].copy_(frames, non_blocking=True)
+                nb = frames.numel()
             slot["msk"].copy_(masks, non_blocking=True)
             slot["ev_frm"].record(self.s_in)
+            self.h2d_bytes = (nb + sources.numel() + crops.numel() + masks.numel() * masks.element_size())
         main.wait_event(slot["ev_in"])
         embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
         yptr, ydt = self.G.y_nhwc(self.B, self.dev)
         main.wait_event(slot["ev_frm"])
         if slot["used"]:
             main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
-        paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=slot["out"])
+        dst = slot["frm"] if self.boxes_only else slot["out"]     # in place on the device too: no frame copy
+        paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=dst)
         slot["ev_done"].record(main)
         self.s_out.wait_event(slot["ev_done"])
         with torch.cuda.stream(self.s_out):
-            out.copy_(slot["out"], non_blocking=True)
+            if self.boxes_only:
+                self.d2h_bytes = _copy_boxes(out, slot["frm"], face_frame, boxes, to_device=False)
+            else:
+                out.copy_(slot["out"], non_blocking=True)
+                self.d2h_bytes = out.numel()
             slot["ev_out"].record(self.s_out)
         slot["used"] = True
         return out

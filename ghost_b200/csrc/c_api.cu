@@ -514,4 +514,42 @@ int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
   });
 }
 
+/* Face boxes of a paste-back and box-only transfers of the frames (the compositing touches nothing else). */
+int ghost_paste_boxes(const double* tfm, int n_faces, int H, int W, int* boxes) {
+  return guarded([&] {
+    require(n_faces >= 0 && H > 0 && W > 0, "bad arguments");
+    require(n_faces == 0 || (tfm && boxes), "null arrays");
+    for (int i = 0; i < n_faces; ++i) {
+      PasteFace f;
+      paste_prepare_face(&f, tfm + 6 * i, H, W, 0, 0);
+      const bool empty = f.x1 <= f.x0 || f.y1 <= f.y0;
+      boxes[4 * i + 0] = empty ? 0 : f.x0;
+      boxes[4 * i + 1] = empty ? 0 : f.y0;
+      boxes[4 * i + 2] = empty ? 0 : f.x1;
+      boxes[4 * i + 3] = empty ? 0 : f.y1;
+    }
+  });
+}
+
+int ghost_copy_boxes(void* dst, const void* src, int n_frames, int H, int W, const int* face_frame, const int* boxes,
+                     int n_faces, int to_device, void* stream) {
+  return guarded([&] {
+    require(dst && src && n_frames > 0 && H > 0 && W > 0 && n_faces >= 0, "bad arguments");
+    require(n_faces == 0 || (face_frame && boxes), "null arrays");
+    cudaStream_t s = S(stream);
+    const size_t pitch = static_cast<size_t>(W) * 3;
+    for (int i = 0; i < n_faces; ++i) {
+      const int f = face_frame[i], x0 = boxes[4 * i], y0 = boxes[4 * i + 1], x1 = boxes[4 * i + 2], y1 = boxes[4 * i + 3];
+      require(f >= 0 && f < n_frames, "face_frame out of range");
+      if (x1 <= x0 || y1 <= y0) continue;
+      require(x0 >= 0 && y0 >= 0 && x1 <= W && y1 <= H, "box outside the frame");
+      const size_t off = (static_cast<size_t>(f) * H + y0) * pitch + static_cast<size_t>(x0) * 3;
+      check_cuda(cudaMemcpy2DAsync(static_cast<uint8_t*>(dst) + off, pitch, static_cast<const uint8_t*>(src) + off, pitch,
+                                   static_cast<size_t>(x1 - x0) * 3, y1 - y0,
+                                   to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost, s),
+                 "box copy");
+    }
+  });
+}
+
 }  // extern "C"

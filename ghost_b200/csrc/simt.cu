@@ -622,7 +622,24 @@ __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __re
   // every warp owns a run of consecutive pixels, so it crosses an image boundary at most once or twice
   const long long chunk = (npix + nwarps - 1) / nwarps;
   const long long pend = min(npix, (warp0 + 1) * chunk);
+  // the next pixel's channels are requested before the current pixel is reduced: two loads in flight per lane
+  uint4 cur[NIT];
+  {
+    const long long pix = warp0 * chunk;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int c = it * 256 + lane * 8;
+      cur[it] = (pix < pend && c < C) ? __ldg(reinterpret_cast<const uint4*>(h + pix * C + c)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
   for (long long pix = warp0 * chunk; pix < pend; ++pix) {
+    uint4 nxt[NIT];
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+      const int c = it * 256 + lane * 8;
+      nxt[it] = (pix + 1 < pend && c < C) ? __ldg(reinterpret_cast<const uint4*>(h + (pix + 1) * C + c))
+                                          : make_uint4(0u, 0u, 0u, 0u);
+    }
     const int n = static_cast<int>(pix / HW);
     if (n != cur_n) {
       cur_n = n;
@@ -650,17 +667,16 @@ __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __re
         }
       }
     }
-    const __nv_bfloat16* hrow = h + pix * C;
     float v[NIT][8];
 #pragma unroll
     for (int it = 0; it < NIT; ++it) {
-      const int c = it * 256 + lane * 8;
-      if (c < C) {
-        load8(hrow + c, v[it]);
-      } else {
+      const uint32_t q4[4] = {cur[it].x, cur[it].y, cur[it].z, cur[it].w};
 #pragma unroll
-        for (int q = 0; q < 8; ++q) v[it][q] = 0.f;
+      for (int i = 0; i < 4; ++i) {
+        v[it][2 * i] = __uint_as_float(q4[i] << 16);
+        v[it][2 * i + 1] = __uint_as_float(q4[i] & 0xffff0000u);
       }
+      cur[it] = nxt[it];
     }
     float acc = 0.f, acc2 = 0.f;
 #pragma unroll

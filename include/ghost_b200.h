@@ -177,6 +177,16 @@ typedef struct {
 
 int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
 
+/* The paste-back rewrites only the bounding box of each face (the image of the 224 x 224 crop under the inverse of
+ * its affine, clipped to the frame; image_processing.py:66-75 composites `mask*swap + (1-mask)*frame`, which is the
+ * frame itself wherever the warped mask is 0).  ghost_paste_boxes returns those boxes, boxes[i] = {x0, y0, x1, y1}
+ * (x1, y1 exclusive; all 0 for a face outside its frame), so that a caller who keeps the frames in pinned host
+ * memory can move just the boxes: ghost_copy_boxes copies the box pixels of [n_frames,H,W,3] u8 frames between a
+ * host and a device buffer of the same layout (to_device != 0: host -> device), asynchronously on `stream`. */
+int ghost_paste_boxes(const double* tfm, int n_faces, int H, int W, int* boxes);
+int ghost_copy_boxes(void* dst, const void* src, int n_frames, int H, int W, const int* face_frame, const int* boxes,
+                     int n_faces, int to_device, void* stream);
+
 /* ---- identity matching for multi-face video (utils/inference/video_processing.py:126-148):
  *   similarity = F.normalize(face_embeds) @ F.normalize(target_embeds).T;  best_idx = similarity.argmax(0);
  *   matched[j] = similarity[best_idx[j]][j] > similarity_th.

@@ -191,3 +191,44 @@ def test_swap_pipeline_matches_sequential_calls():
         yptr, ydt = G.y_nhwc(B)
         ref = ghost_b200.paste_back(frm.cuda(), (yptr, ydt, B), msk.cuda(), tf, face_frame, mode="exact")
         assert torch.equal(out, ref.cpu())
+
+
+def test_swap_pipeline_boxes_only_matches_full_frames():
+    """SwapPipeline(boxes_only=True): only the face boxes cross PCIe and the frames are composited in place in the
+    caller's pinned buffer - bit-identical to the sequential full-frame calls, also with two faces in one frame,
+    overlapping boxes and a box clipped by the frame border; the boxes cover every pixel the paste-back changes."""
+    B, H, W = 3, 240, 320
+    G = ghost_b200.AEI_Net("unet", 1, 512, seed=3).eval().bfloat16().cuda()
+    arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
+    rng = np.random.default_rng(9)
+    pipe = ghost_b200.SwapPipeline(G, arc, B, (H, W), depth=2, mode="exact", boxes_only=True)
+    face_frame = np.array([0, 0, 2], dtype=np.int32)          # two faces in frame 0, none in frame 1
+    batches = []
+    for step in range(5):
+        src = torch.from_numpy(synth.sources_u8(B, seed=step)).pin_memory()
+        crp = torch.from_numpy(synth.crops_u8(B, seed=10 + step)).pin_memory()
+        frm0 = np.stack([synth.frame_u8(H, W, seed=100 * step + f) for f in range(B)])
+        frm = torch.from_numpy(frm0.copy()).pin_memory()
+        msk = torch.from_numpy(np.stack([synth.soft_mask(rng) for _ in range(B)])).pin_memory()
+        tf = np.stack([synth.similarity_tfm(H, W, rng, scale=0.9, clipped=(i == 2)) for i in range(B)])
+        tf[1] = tf[0]
+        tf[1, :, 2] += 20.0                                    # second face of frame 0 overlaps the first
+        with pytest.raises(ValueError):
+            pipe.submit(src, crp, frm, msk, tf, face_frame, torch.empty_like(frm).pin_memory())
+        pipe.submit(src, crp, frm, msk, tf, face_frame, frm)
+        batches.append((src, crp, frm0, frm, msk, tf))
+    pipe.flush()
+    torch.cuda.synchronize()
+    for src, crp, frm0, frm, msk, tf in batches:
+        z = arc.embed_hwc(src.cuda(), out_dtype=torch.bfloat16)
+        G.swap_u8(crp.cuda(), z, write_u8=False)
+        yptr, ydt = G.y_nhwc(B)
+        ref = ghost_b200.paste_back(torch.from_numpy(frm0).cuda(), (yptr, ydt, B), msk.cuda(), tf, face_frame,
+                                    mode="exact").cpu()
+        assert torch.equal(frm, ref)
+        changed = (ref.numpy() != frm0).any(axis=3)
+        cover = np.zeros_like(changed)
+        for f, (x0, y0, x1, y1) in zip(face_frame, ghost_b200.paste_boxes(tf, (H, W))):
+            cover[f, y0:y1, x0:x1] = True
+        assert changed.any() and not (changed & ~cover).any()
+    assert pipe.d2h_bytes < frm.numel() and pipe.h2d_bytes < frm.numel() + src.numel() + crp.numel() + msk.numel() * 8
