@@ -643,7 +643,7 @@ class SwapPipeline(object):
     paste_back one after the other.  Call submit() per batch and flush() before reading the last outputs."""
 
     def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None,
-                 boxes_only=False):
+                 boxes_only=False, sr=None, sr_batch=20):
         if not torch.cuda.is_available():
             raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
         self.G, self.arc, self.B, self.mode, self.depth = G, arc, int(batch), mode, int(depth)
@@ -652,8 +652,14 @@ class SwapPipeline(object):
         self.boxes_only = bool(boxes_only)
         self.frame_hw = (int(frame_hw[0]), int(frame_hw[1]))
         self.h2d_bytes = self.d2h_bytes = 0       # bytes of the last submit()
+        # sr: the --use_sr pass (face_enhancement, batches of sr_batch crops like the reference's DataLoader) between the
+        # swap and the paste-back
+        self.sr, self.sr_batch = sr, int(sr_batch)
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         H, W = frame_hw
+        if sr is not None:
+            self.swapped = torch.empty((self.B, 256, 256, 3), dtype=torch.uint8, device=self.dev)
+            self.enhanced = torch.empty_like(self.swapped)
         u8 = dict(dtype=torch.uint8, device=self.dev)
         self.slots = []
         for _ in range(self.depth):
@@ -697,13 +703,21 @@ class SwapPipeline(object):
             slot["ev_frm"].record(self.s_in)
             self.h2d_bytes = (nb + sources.numel() + crops.numel() + masks.numel() * masks.element_size())
         main.wait_event(slot["ev_in"])
-        embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
-        yptr, ydt = self.G.y_nhwc(self.B, self.dev)
+        if self.sr is None:
+            embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
+            yptr, ydt = self.G.y_nhwc(self.B, self.dev)
+            swap_arg = (yptr, ydt, self.B)
+        else:
+            embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc,
+                           out=self.swapped, write_u8=True)
+            for b0 in range(0, self.B, self.sr_batch):
+                self.sr.enhance_u8(self.swapped[b0:b0 + self.sr_batch], out=self.enhanced[b0:b0 + self.sr_batch])
+            swap_arg = self.enhanced
         main.wait_event(slot["ev_frm"])
         if slot["used"]:
             main.wait_event(slot["ev_out"])         # this slot's previous result has left the device
         dst = slot["frm"] if self.boxes_only else slot["out"]     # in place on the device too: no frame copy
-        paste_back(slot["frm"], (yptr, ydt, self.B), slot["msk"], tfms, face_frame, mode=self.mode, out=dst)
+        paste_back(slot["frm"], swap_arg, slot["msk"], tfms, face_frame, mode=self.mode, out=dst)
         slot["ev_done"].record(main)
         self.s_out.wait_event(slot["ev_done"])
         with torch.cuda.stream(self.s_out):

@@ -232,3 +232,37 @@ def test_swap_pipeline_boxes_only_matches_full_frames():
             cover[f, y0:y1, x0:x1] = True
         assert changed.any() and not (changed & ~cover).any()
     assert pipe.d2h_bytes < frm.numel() and pipe.h2d_bytes < frm.numel() + src.numel() + crp.numel() + msk.numel() * 8
+
+
+def test_swap_pipeline_with_sr_stage_matches_sequential_calls():
+    """SwapPipeline(sr=...): swap -> face_enhancement batches -> paste-back inside the streaming loop gives the frames
+    of the calls made one after the other (the SR generator is stateful: a twin with the same seed replays them)."""
+    B, H, W = 3, 240, 320
+    G = ghost_b200.AEI_Net("unet", 1, 512, seed=3).eval().bfloat16().cuda()
+    arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
+    sr_a = ghost_b200.LIPSPADEGenerator(seed=1).bfloat16().cuda()
+    sr_b = ghost_b200.LIPSPADEGenerator(seed=1).bfloat16().cuda()
+    rng = np.random.default_rng(11)
+    pipe = ghost_b200.SwapPipeline(G, arc, B, (H, W), depth=2, mode="exact", sr=sr_a, sr_batch=2)
+    face_frame = np.arange(B, dtype=np.int32)
+    batches, outs = [], []
+    for step in range(3):
+        src = torch.from_numpy(synth.sources_u8(B, seed=step)).pin_memory()
+        crp = torch.from_numpy(synth.crops_u8(B, seed=10 + step)).pin_memory()
+        frm = torch.from_numpy(np.stack([synth.frame_u8(H, W, seed=100 * step + f) for f in range(B)])).pin_memory()
+        msk = torch.from_numpy(np.stack([synth.soft_mask(rng) for _ in range(B)])).pin_memory()
+        tf = np.stack([synth.similarity_tfm(H, W, rng, scale=0.9) for _ in range(B)])
+        out = torch.empty_like(frm).pin_memory()
+        pipe.submit(src, crp, frm, msk, tf, face_frame, out)
+        batches.append((src, crp, frm, msk, tf))
+        outs.append(out)
+    pipe.flush()
+    torch.cuda.synchronize()
+    for (src, crp, frm, msk, tf), out in zip(batches, outs):
+        z = arc.embed_hwc(src.cuda(), out_dtype=torch.bfloat16)
+        swapped = G.swap_u8(crp.cuda(), z)
+        enh = torch.empty_like(swapped)
+        for b0 in range(0, B, 2):
+            sr_b.enhance_u8(swapped[b0:b0 + 2], out=enh[b0:b0 + 2])
+        ref = ghost_b200.paste_back(frm.cuda(), enh, msk.cuda(), tf, face_frame, mode="exact")
+        assert torch.equal(out, ref.cpu())
