@@ -640,7 +640,12 @@ class SwapPipeline(object):
 
     Uploads, compute and downloads run on three CUDA streams over `depth` device slots, so the PCIe copies of
     neighbouring batches overlap the generator.  Results are bit-identical to calling embed_hwc / swap_u8 /
-    paste_back one after the other.  Call submit() per batch and flush() before reading the last outputs."""
+    paste_back one after the other.  Call submit() per batch and flush() before reading the last outputs.
+
+    The networks start as soon as the crops and sources (22 MB per 64 faces) are on the device; the frames follow on
+    the upload stream and only the paste-back waits for them.  boxes_only=True composites in place in the caller's
+    pinned frame buffer and moves just the face boxes over PCIe (pass out=frames); sr=<LIPSPADEGenerator> inserts
+    the --use_sr pass (face_enhancement, batches of sr_batch crops) between the swap and the paste-back."""
 
     def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None,
                  boxes_only=False, sr=None, sr_batch=20):
