@@ -17,7 +17,7 @@ OK, ERR_INVALID, ERR_WEIGHTS, ERR_CUDA, ERR_KERNEL = 0, -1, -2, -3, -4
 F32, BF16, F16, U8 = 0, 1, 2, 3
 # ghost_paste_mode / ghost_crop_kind
 PASTE_EXACT, PASTE_FLOAT = 0, 1
-CROP_U8_BGR, CROP_Y_BF16, CROP_Y_F32 = 0, 1, 2
+CROP_U8_BGR, CROP_Y_BF16, CROP_Y_F32, CROP_Y_F16 = 0, 1, 2, 3
 
 
 class GhostError(RuntimeError):

@@ -154,7 +154,9 @@ class _Net(object):
             pass
 
     def _mode(self):
-        return _lib.F32 if self._dtype == torch.float32 else _lib.BF16
+        # the module dtype IS the arithmetic mode, as for the reference module: .float() -> fp32 CUDA cores,
+        # .half() -> fp16 storage on tcgen05 (inference.py:30 `G.half()`), .bfloat16() -> bf16 storage on tcgen05
+        return {torch.float32: _lib.F32, torch.float16: _lib.F16, torch.bfloat16: _lib.BF16}[self._dtype]
 
     def _create(self, lib, out, mode):
         raise NotImplementedError
@@ -225,8 +227,9 @@ class AEI_Net(_Net):
     """Drop-in for network.AEI_Net.AEI_Net (network/AEI_Net.py:143-159), inference only.
 
     The arithmetic mode follows the module dtype like the reference: `.float()` -> fp32 CUDA-core
-    correctness mode (1e-4 contract); `.half()` / `.bfloat16()` -> tcgen05 bf16 x bf16 -> fp32 mode
-    (1e-2 contract) with fp16 / bf16 tensors at the boundary."""
+    correctness mode (1e-4 contract); `.half()` -> tcgen05 fp16 x fp16 -> fp32 with fp16 activations and
+    weights, the dtype the reference deploys (inference.py:30) and the mode that meets the 1e-2 / 1e-3
+    contract; `.bfloat16()` -> the same kernels on bf16 storage (same speed, 8 mantissa bits)."""
 
     def __init__(self, backbone, num_blocks=2, c_id=256, seed=0):
         super().__init__(_w.aei_spec(backbone, num_blocks, c_id), seed)
@@ -490,7 +493,7 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
         raise ValueError("tfms, face_frame, face_crop and face_mask must have one entry per face")
     if isinstance(crops, tuple):
         cptr, cdt, ncrops = crops
-        ckind = _lib.CROP_Y_BF16 if cdt == _lib.BF16 else _lib.CROP_Y_F32
+        ckind = {_lib.BF16: _lib.CROP_Y_BF16, _lib.F16: _lib.CROP_Y_F16}.get(cdt, _lib.CROP_Y_F32)
         keep = None
     else:
         keep = _as_dev(crops, torch.uint8, dev)
@@ -834,7 +837,8 @@ class LIPSPADEGenerator(_Net):
     """Drop-in for models.networks.generator.LIPSPADEGenerator(TestOptions) (generator.py:390-400; options
     models/config_sr.py:3-29) in the state the reference runs it in: `model.netG.train()` (inference.py:48), i.e.
     batch statistics in every SPADE and one spectral-norm power iteration per forward.  `.float()` = fp32 CUDA-core
-    mode (the reference's own dtype for this network), `.bfloat16()` / `.half()` = tcgen05 mode."""
+    mode (the reference's own dtype for this network), `.half()` / `.bfloat16()` = tcgen05 mode on fp16 / bf16
+    storage."""
 
     def __init__(self, opt=None, seed=0):
         super().__init__(_w.sr_spec(), seed)

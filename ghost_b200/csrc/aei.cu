@@ -67,7 +67,7 @@ void Net::finalize_aei() {
   if (backbone != "unet" && backbone != "linknet") fail(-1, "backbone must be 'unet' or 'linknet'");
   if (num_blocks < 1 || num_blocks > 4) fail(-1, "num_blocks must be in [1,4]");
   if (c_id % 32) fail(-1, "c_id must be a multiple of 32");
-  const bool bf = act_dtype == kBF16;
+  const bool bf = is16(act_dtype);  // tensor-core mode: bf16 or fp16 storage
   const bool unet = backbone == "unet";
   const BlockSpec* blocks = unet ? kUnetBlocks : kLinkBlocks;
 
@@ -208,7 +208,7 @@ void Net::finalize_aei() {
 void Net::build_aei(ExecPlan& p) {
   const int B = p.B;
   const int dt = act_dtype;
-  const bool bf = dt == kBF16;
+  const bool bf = is16(dt);  // tensor-core mode: bf16 or fp16 storage
   const bool unet = backbone == "unet";
   const BlockSpec* blocks = unet ? kUnetBlocks : kLinkBlocks;
   int* err = p.err_word;
@@ -385,7 +385,7 @@ void Net::build_aei(ExecPlan& p) {
           if (!mask) {
             mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
             const Act hh = h;
-            add_op(lname + ".mask", [=](cudaStream_t s) { return aad_mask_launch(hh.p, B, HW, cx, whf, bhf, mask, s); },
+            add_op(lname + ".mask", [=](cudaStream_t s) { return aad_mask_launch(hh.p, B, HW, cx, whf, bhf, mask, s, dt); },
                    kOpStats, static_cast<double>(B) * HW * cx * esz);
           }
           args.mask = mask;
@@ -446,7 +446,7 @@ void Net::build_aei(ExecPlan& p) {
       const AadPre qs = pre_sc, q0 = pre_0;
       const int cx = b.cin;
       add_op(S("blk%d.aadsc+aad0.mask", k), [=](cudaStream_t s) {
-        return aad_mask2_launch(mm.p, B, HW, cx, qs.whf, qs.bhf, qs.mask, q0.whf, q0.bhf, q0.mask, s);
+        return aad_mask2_launch(mm.p, B, HW, cx, qs.whf, qs.bhf, qs.mask, q0.whf, q0.bhf, q0.mask, s, dt);
       }, kOpStats, static_cast<double>(B) * HW * cx * esz);
     }
     if (b.cin != b.cout) {

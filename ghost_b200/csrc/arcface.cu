@@ -29,7 +29,7 @@ void bn_fold_t(const HostTensor& g, const HostTensor& b, const HostTensor& rm, c
 }  // namespace
 
 void Net::finalize_arcface() {
-  const bool bf = act_dtype == kBF16;
+  const bool bf = is16(act_dtype);  // tensor-core mode: bf16 or fp16 storage
   auto bn = [&](const std::string& k, std::vector<float>* sc, std::vector<float>* sh) {
     bn_fold_t(W(k + ".weight"), W(k + ".bias"), W(k + ".running_mean"), W(k + ".running_var"), sc, sh);
   };
@@ -103,7 +103,7 @@ void Net::finalize_arcface() {
 void Net::build_arcface(ExecPlan& p) {
   const int B = p.B;
   const int dt = act_dtype;
-  const bool bf = dt == kBF16;
+  const bool bf = is16(dt);  // tensor-core mode: bf16 or fp16 storage
   int* err = p.err_word;
   auto new_act = [&](int H, int W, int C) {
     Act a;

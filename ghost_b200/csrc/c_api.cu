@@ -115,7 +115,7 @@ int ghost_check_errors(void) {
 int ghost_aei_create(ghost_net_t** out, const char* backbone, int num_blocks, int c_id, int mode) {
   return guarded([&] {
     require(out && backbone, "null argument");
-    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    require(mode == GHOST_F32 || mode == GHOST_BF16 || mode == GHOST_F16, "mode must be GHOST_F32, GHOST_BF16 or GHOST_F16");
     if (strcmp(backbone, "resnet") == 0) fail(GHOST_ERR_INVALID, "backbone 'resnet' is not supported by ghost_b200");
     require(strcmp(backbone, "unet") == 0 || strcmp(backbone, "linknet") == 0, "unknown backbone");
     require(num_blocks >= 1 && num_blocks <= 4, "num_blocks must be in [1,4]");
@@ -127,7 +127,7 @@ int ghost_aei_create(ghost_net_t** out, const char* backbone, int num_blocks, in
 int ghost_arcface_create(ghost_net_t** out, int mode) {
   return guarded([&] {
     require(out, "null argument");
-    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    require(mode == GHOST_F32 || mode == GHOST_BF16 || mode == GHOST_F16, "mode must be GHOST_F32, GHOST_BF16 or GHOST_F16");
     *out = new ghost_net(Net::kArcFace, "iresnet100", 0, 512, mode);
   });
 }
@@ -347,7 +347,7 @@ int ghost_net_debug_get(ghost_net_t* net, int B, const char* name, void* dst, in
 int ghost_sr_create(ghost_net_t** out, int mode) {
   return guarded([&] {
     require(out, "null argument");
-    require(mode == GHOST_F32 || mode == GHOST_BF16, "mode must be GHOST_F32 or GHOST_BF16");
+    require(mode == GHOST_F32 || mode == GHOST_BF16 || mode == GHOST_F16, "mode must be GHOST_F32, GHOST_BF16 or GHOST_F16");
     *out = new ghost_net(Net::kSR, "lipspade", 0, 0, mode);
   });
 }

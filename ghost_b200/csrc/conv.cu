@@ -111,7 +111,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   if (taps.n > kIgemmMaxTaps) return "lower_conv: too many taps";
   if (w.K != taps.n * Cin) return "lower_conv: weight K does not match taps*Cin";
   op->flops = 2.0 * in.N * Ho * Wo * static_cast<double>(w.Cout) * w.K;
-  const bool can_igemm = !force_simt && in.dtype == kBF16 && (Cin % 32 == 0) && (in.C % 8 == 0) && (c0 % 8 == 0) &&
+  const bool can_igemm = !force_simt && is16(in.dtype) && (Cin % 32 == 0) && (in.C % 8 == 0) && (c0 % 8 == 0) &&
                          w.wb != nullptr && (taps.stride == 1 || (taps.stride == 2 && in.H % 2 == 0 && in.W % 2 == 0));
   if (!can_igemm) {
     if (aad) return "lower_conv: the fused AAD epilogue needs the tensor-core path";
@@ -170,6 +170,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     t.bias = w.bias;
     t.out = out.p;
     t.out_f32 = out.dtype == kF32;
+    t.f16 = in.dtype == kF16;
+    if (!t.out_f32 && out.dtype != in.dtype) return "lower_conv: 16-bit output type must match the input";
     t.o_sn = out.sn; t.o_sh = out.sh; t.o_sw = out.sw; t.o_off = out.off;
     t.res = epi.res;
     t.r_sn = epi.r_sn; t.r_sh = epi.r_sh; t.r_sw = epi.r_sw; t.r_off = epi.r_off;
@@ -351,7 +353,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   }
   p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
   // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring
-  if (!aad && out.dtype == kBF16 && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
+  if (!aad && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
       !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&
       (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8))) &&
       256 * p.BN <= stages * stage_bytes) {
@@ -366,10 +368,12 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   p.out = out.p;
   p.o_sn = out.sn; p.o_sh = out.sh; p.o_sw = out.sw; p.o_off = out.off;
   p.out_f32 = out.dtype == kF32;
+  p.f16 = in.dtype == kF16;
+  if (!p.out_f32 && out.dtype != in.dtype) return "lower_conv: 16-bit output type must match the input";
   p.bias = w.bias;
   p.err = err_word;
   if (aad) {
-    if (out.dtype != kBF16) return "lower_conv: AAD output must be bf16";
+    if (!is16(out.dtype)) return "lower_conv: AAD output must be a 16-bit tensor";
     p.mode = kModeAAD;
     p.h = reinterpret_cast<const __nv_bfloat16*>(aad->h);
     p.c_x = aad->c_x;
@@ -430,8 +434,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.out2 = epi.out2;
     p.scale2 = epi.scale2;
     p.shift2 = epi.shift2;
-    if (epi.out2 && (out.dtype != kBF16 || w.Cout % 16)) return "lower_conv: the second output needs bf16 and Cout % 16 == 0";
-    if (out.dtype == kBF16 && w.Cout % 16 == 0 && ((out.off % 8) || (out.sw % 8) || (out.sh % 8) || (out.sn % 8)))
+    if (epi.out2 && (!is16(out.dtype) || w.Cout % 16)) return "lower_conv: the second output needs a 16-bit tensor and Cout % 16 == 0";
+    if (is16(out.dtype) && w.Cout % 16 == 0 && ((out.off % 8) || (out.sw % 8) || (out.sh % 8) || (out.sn % 8)))
       return "lower_conv: bf16 output view must be 16-byte aligned";
   }
   return nullptr;

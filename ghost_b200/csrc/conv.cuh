@@ -12,6 +12,9 @@
 
 namespace ghost {
 
+// 16-bit storage types of the tensor-core path: bf16, or IEEE fp16 (the reference's own inference dtype, inference.py:30)
+inline bool is16(int dtype) { return dtype == kBF16 || dtype == kF16; }
+
 // Dense NHWC activation tensor (C = pixel stride in elements).
 struct Act {
   void* p = nullptr;
@@ -33,7 +36,7 @@ struct Taps {
 
 // Weights of one op, already in the packed [Cout][tap][Cin] order, resident on the device.
 struct PackedW {
-  const __nv_bfloat16* wb = nullptr;  // [rows_pad][K] bf16 (igemm)
+  const __nv_bfloat16* wb = nullptr;  // [rows_pad][K] bf16 or fp16 bits, the net's 16-bit storage type (igemm)
   const float* wf = nullptr;          // [Cout][K] fp32 (CUDA-core path)
   const float* bias = nullptr;        // [rows_pad] fp32 or null
   const __nv_bfloat16* wt = nullptr;  // Cout <= 3, K = 9*Cin: the "taps in N" rows of tapn.cuh, or null

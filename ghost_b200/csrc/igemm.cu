@@ -20,6 +20,9 @@
 // epilogue implements AADLayer.forward (network/AADLayer.py:20-38) + the ReLU
 // that always follows it (network/AADLayer.py:62,70).
 #include <cstdlib>
+#include <mutex>
+
+#include <cuda_fp16.h>
 
 #include "igemm.cuh"
 #include "ptx.cuh"
@@ -90,25 +93,56 @@ struct TileWalk {
   }
 };
 
-__device__ __forceinline__ float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
-__device__ __forceinline__ float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&t);
+// 16-bit storage element: bf16 (F16 = false) or IEEE fp16 (F16 = true, the reference's own inference dtype,
+// inference.py:30 `G.half()`); the arithmetic is fp32 either way, tcgen05 kind::f16 takes both at the same rate.
+template <bool F16>
+__device__ __forceinline__ float lo16(uint32_t v) {
+  if (F16) return __half2float(__ushort_as_half(static_cast<unsigned short>(v & 0xffffu)));
+  return __uint_as_float(v << 16);
 }
-// max(., 0) and the bf16x2 pack in one instruction (lo -> bits [0,16), hi -> bits [16,32))
-__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+template <bool F16>
+__device__ __forceinline__ float hi16(uint32_t v) {
+  if (F16) return __half2float(__ushort_as_half(static_cast<unsigned short>(v >> 16)));
+  return __uint_as_float(v & 0xffff0000u);
+}
+template <bool F16>
+__device__ __forceinline__ float ld16(const __nv_bfloat16* p) {
+  if (F16) return __half2float(*reinterpret_cast<const __half*>(p));
+  return __bfloat162float(*p);
+}
+template <bool F16>
+__device__ __forceinline__ void st16(__nv_bfloat16* p, float v) {
+  if (F16) *reinterpret_cast<__half*>(p) = __float2half_rn(v);
+  else *p = __float2bfloat16(v);
+}
+// the value as it reads back after a 16-bit store
+template <bool F16>
+__device__ __forceinline__ float round16(float v) {
+  if (F16) return __half2float(__float2half_rn(v));
+  return __bfloat162float(__float2bfloat16(v));
+}
+// lo -> bits [0,16), hi -> bits [16,32)
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16(float lo, float hi) {
   uint32_t d;
-  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  if (F16) asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+// max(., 0) and the pack in one instruction
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16_relu(float lo, float hi) {
+  uint32_t d;
+  if (F16) asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
   return d;
 }
 // SPADE variant: max(v, v*slope) * post (slope 0 = ReLU, 0.2 = LeakyReLU(0.2), 1 = identity)
-__device__ __forceinline__ uint32_t pack_bf16_slope(float lo, float hi, float slope, float post) {
-  uint32_t d;
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16_slope(float lo, float hi, float slope, float post) {
   lo = fmaxf(lo, lo * slope) * post;
   hi = fmaxf(hi, hi * slope) * post;
-  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  return d;
+  return pack16<F16>(lo, hi);
 }
 
 
@@ -151,6 +185,7 @@ __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (
           }
 }
 
+template <bool F16>
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
                                                    long long o_pix, long long r_pix, const float* sp, int j) {
           float f[16];
@@ -173,12 +208,12 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
               const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
-                f[2 * i] += bf16lo(qq[i]);
-                f[2 * i + 1] += bf16hi(qq[i]);
+                f[2 * i] += lo16<F16>(qq[i]);
+                f[2 * i + 1] += hi16<F16>(qq[i]);
               }
             } else {
               for (int i = 0; i < 16; ++i)
-                if (col0 + i < p.n_valid) f[i] += __bfloat162float(rp[i]);
+                if (col0 + i < p.n_valid) f[i] += ld16<F16>(rp + i);
             }
           }
           if (p.act2 == kAct2Tanh) {
@@ -207,38 +242,38 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
                                      : __ldg(reinterpret_cast<const float4*>(p.scale2 + col0) + i);
                 const float4 sh = sp ? *reinterpret_cast<const float4*>(sp + 768 + j + 4 * i)
                                      : __ldg(reinterpret_cast<const float4*>(p.shift2 + col0) + i);
-                t[4 * i] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i])), sc.x, sh.x);
-                t[4 * i + 1] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 1])), sc.y, sh.y);
-                t[4 * i + 2] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 2])), sc.z, sh.z);
-                t[4 * i + 3] = fmaf(__bfloat162float(__float2bfloat16(f[4 * i + 3])), sc.w, sh.w);
+                t[4 * i] = fmaf(round16<F16>(f[4 * i]), sc.x, sh.x);
+                t[4 * i + 1] = fmaf(round16<F16>(f[4 * i + 1]), sc.y, sh.y);
+                t[4 * i + 2] = fmaf(round16<F16>(f[4 * i + 2]), sc.z, sh.z);
+                t[4 * i + 3] = fmaf(round16<F16>(f[4 * i + 3]), sc.w, sh.w);
               }
               uint4 s0, s1;
-              s0.x = pack_bf16(t[0], t[1]);
-              s0.y = pack_bf16(t[2], t[3]);
-              s0.z = pack_bf16(t[4], t[5]);
-              s0.w = pack_bf16(t[6], t[7]);
-              s1.x = pack_bf16(t[8], t[9]);
-              s1.y = pack_bf16(t[10], t[11]);
-              s1.z = pack_bf16(t[12], t[13]);
-              s1.w = pack_bf16(t[14], t[15]);
+              s0.x = pack16<F16>(t[0], t[1]);
+              s0.y = pack16<F16>(t[2], t[3]);
+              s0.z = pack16<F16>(t[4], t[5]);
+              s0.w = pack16<F16>(t[6], t[7]);
+              s1.x = pack16<F16>(t[8], t[9]);
+              s1.y = pack16<F16>(t[10], t[11]);
+              s1.z = pack16<F16>(t[12], t[13]);
+              s1.w = pack16<F16>(t[14], t[15]);
               reinterpret_cast<uint4*>(o2)[0] = s0;
               reinterpret_cast<uint4*>(o2)[1] = s1;
             }
             if (full16) {
               uint4 s0, s1;
-              s0.x = pack_bf16(f[0], f[1]);
-              s0.y = pack_bf16(f[2], f[3]);
-              s0.z = pack_bf16(f[4], f[5]);
-              s0.w = pack_bf16(f[6], f[7]);
-              s1.x = pack_bf16(f[8], f[9]);
-              s1.y = pack_bf16(f[10], f[11]);
-              s1.z = pack_bf16(f[12], f[13]);
-              s1.w = pack_bf16(f[14], f[15]);
+              s0.x = pack16<F16>(f[0], f[1]);
+              s0.y = pack16<F16>(f[2], f[3]);
+              s0.z = pack16<F16>(f[4], f[5]);
+              s0.w = pack16<F16>(f[6], f[7]);
+              s1.x = pack16<F16>(f[8], f[9]);
+              s1.y = pack16<F16>(f[10], f[11]);
+              s1.z = pack16<F16>(f[12], f[13]);
+              s1.w = pack16<F16>(f[14], f[15]);
               reinterpret_cast<uint4*>(o)[0] = s0;
               reinterpret_cast<uint4*>(o)[1] = s1;
             } else {
               for (int i = 0; i < 16; ++i)
-                if (col0 + i < p.n_valid) o[i] = __float2bfloat16(f[i]);
+                if (col0 + i < p.n_valid) st16<F16>(o + i, f[i]);
             }
           }
 }
@@ -257,7 +292,7 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
   volatile int& abort_flag = *abort_flag_p;
   uint64_t& bfull_bar = *bfull_bar_p;
     const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
-    const uint32_t idesc = make_idesc_bf16(128, p.BN);
+    const uint32_t idesc = make_idesc_f16(128, p.BN, p.f16 != 0);
     const uint32_t dhi = smem_desc_hi(win ? 1024 : 8 * row_bytes, p.kc != 64);
     const uint32_t ring_u = smem_u32(ring);
     const uint32_t bt16 = static_cast<uint32_t>(b_tile_bytes) >> 4;  // weight tile size in descriptor units
@@ -334,6 +369,7 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
 #endif
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
@@ -674,8 +710,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
                   const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
                   for (int i = 0; i < 8; ++i) {
-                    f[2 * i] += bf16lo(qq[i]);
-                    f[2 * i + 1] += bf16hi(qq[i]);
+                    f[2 * i] += lo16<F16>(qq[i]);
+                    f[2 * i + 1] += hi16<F16>(qq[i]);
                   }
                 }
                 if (p.act2 == kAct2Tanh) {
@@ -683,14 +719,14 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
                   for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
                 }
                 uint4 o0, o1;
-                o0.x = pack_bf16(f[0], f[1]);
-                o0.y = pack_bf16(f[2], f[3]);
-                o0.z = pack_bf16(f[4], f[5]);
-                o0.w = pack_bf16(f[6], f[7]);
-                o1.x = pack_bf16(f[8], f[9]);
-                o1.y = pack_bf16(f[10], f[11]);
-                o1.z = pack_bf16(f[12], f[13]);
-                o1.w = pack_bf16(f[14], f[15]);
+                o0.x = pack16<F16>(f[0], f[1]);
+                o0.y = pack16<F16>(f[2], f[3]);
+                o0.z = pack16<F16>(f[4], f[5]);
+                o0.w = pack16<F16>(f[6], f[7]);
+                o1.x = pack16<F16>(f[8], f[9]);
+                o1.y = pack16<F16>(f[10], f[11]);
+                o1.z = pack16<F16>(f[12], f[13]);
+                o1.w = pack16<F16>(f[14], f[15]);
                 *s0 = o0;
                 *s1 = o1;
               }
@@ -729,10 +765,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
                   sh1 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg) + 1);
                 }
                 uint4 o2;
-                o2.x = pack_bf16(fmaf(bf16lo(q.x), sc0.x, sh0.x), fmaf(bf16hi(q.x), sc0.y, sh0.y));
-                o2.y = pack_bf16(fmaf(bf16lo(q.y), sc0.z, sh0.z), fmaf(bf16hi(q.y), sc0.w, sh0.w));
-                o2.z = pack_bf16(fmaf(bf16lo(q.z), sc1.x, sh1.x), fmaf(bf16hi(q.z), sc1.y, sh1.y));
-                o2.w = pack_bf16(fmaf(bf16lo(q.w), sc1.z, sh1.z), fmaf(bf16hi(q.w), sc1.w, sh1.w));
+                o2.x = pack16<F16>(fmaf(lo16<F16>(q.x), sc0.x, sh0.x), fmaf(hi16<F16>(q.x), sc0.y, sh0.y));
+                o2.y = pack16<F16>(fmaf(lo16<F16>(q.y), sc0.z, sh0.z), fmaf(hi16<F16>(q.y), sc0.w, sh0.w));
+                o2.z = pack16<F16>(fmaf(lo16<F16>(q.z), sc1.x, sh1.x), fmaf(hi16<F16>(q.z), sc1.y, sh1.y));
+                o2.w = pack16<F16>(fmaf(lo16<F16>(q.w), sc1.z, sh1.z), fmaf(hi16<F16>(q.w), sc1.w, sh1.w));
                 *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out2) + op_row + colw + rb_piece * 8) = o2;
               }
             }
@@ -748,7 +784,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             tmem_ld16(t_addr + j, v);
             tmem_ld_wait();
             const int col0 = t.nt * p.BN + j;
-            if (valid && col0 < p.n_valid) linear_epilogue_16(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
+            if (valid && col0 < p.n_valid) linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
           }
         }
         // hand the accumulator stage back to the MMA warp
@@ -820,7 +856,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk) {
                 const uint32_t hv = *reinterpret_cast<const uint32_t*>(hp + kk * 1024);
-                a4[kk] += bf16lo(hv) * w.x + bf16hi(hv) * w.y;
+                a4[kk] += lo16<F16>(hv) * w.x + hi16<F16>(hv) * w.y;
               }
             }
 #pragma unroll
@@ -865,8 +901,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const uint4 v = *reinterpret_cast<const uint4*>(hrow + ((q ^ sw) << 4));
             const float4 w0 = __ldg(reinterpret_cast<const float4*>(wrow + q * 8));
             const float4 w1 = __ldg(reinterpret_cast<const float4*>(wrow + q * 8) + 1);
-            acc0 += bf16lo(v.x) * w0.x + bf16hi(v.x) * w0.y + bf16lo(v.y) * w0.z + bf16hi(v.y) * w0.w;
-            acc1 += bf16lo(v.z) * w1.x + bf16hi(v.z) * w1.y + bf16lo(v.w) * w1.z + bf16hi(v.w) * w1.w;
+            acc0 += lo16<F16>(v.x) * w0.x + hi16<F16>(v.x) * w0.y + lo16<F16>(v.y) * w0.z + hi16<F16>(v.y) * w0.w;
+            acc1 += lo16<F16>(v.z) * w1.x + hi16<F16>(v.z) * w1.y + lo16<F16>(v.w) * w1.z + hi16<F16>(v.w) * w1.w;
           }
           float acc = acc0 + acc1;
           if (hbox == 2) {
@@ -929,7 +965,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const uint32_t bq[4][2] = {{b0[0], b0[1]}, {b0[2], b0[3]}, {b1[0], b1[1]}, {b1[2], b1[3]}};
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
-              const float2 x = make_float2(bf16lo(hv[kk]), bf16hi(hv[kk]));
+              const float2 x = make_float2(lo16<F16>(hv[kk]), hi16<F16>(hv[kk]));
               const float2 hn = fma2(x, make_float2(p0.x, p0.y), make_float2(p0.z, p0.w));
               const float2 ga = add2(make_float2(__uint_as_float(gg[kk][0]), __uint_as_float(gg[kk][1])), bgv);
               const float2 be = add2(make_float2(__uint_as_float(bq[kk][0]), __uint_as_float(bq[kk][1])), bbv);
@@ -938,7 +974,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
               const float2 r2 = fma2(make_float2(m4[kk], m4[kk]), sub2(I, A), A);
               // in place, with the ReLU that always follows the layer (AADLayer.py:62,70)
               *reinterpret_cast<uint32_t*>(hp + kk * 1024) =
-                  spade ? pack_bf16_slope(r2.x, r2.y, sp_slope, sp_post) : pack_bf16_relu(r2.x, r2.y);
+                  spade ? pack16_slope<F16>(r2.x, r2.y, sp_slope, sp_post) : pack16_relu<F16>(r2.x, r2.y);
             }
           }
         } else {
@@ -967,7 +1003,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           // two adjacent channels per packed fp32 instruction; the parameter table is laid out per channel pair
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float2 x = make_float2(bf16lo(qq[i]), bf16hi(qq[i]));
+            const float2 x = make_float2(lo16<F16>(qq[i]), hi16<F16>(qq[i]));
             const float4 p0 = __ldg(parj + 2 * i);      // {rstd0, rstd1, shift0, shift1}
             const float4 p1 = __ldg(parj + 2 * i + 1);  // {gamma_id0, gamma_id1, beta_id0, beta_id1}
             const float2 hn = fma2(x, make_float2(p0.x, p0.y), make_float2(p0.z, p0.w));
@@ -977,7 +1013,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
             const float2 I = fma2(make_float2(p1.x, p1.y), hn, make_float2(p1.z, p1.w));
             const float2 r2 = fma2(mm, sub2(I, A), A);
             // the ReLU that always follows the layer (AADLayer.py:62,70)
-            o[i] = spade ? pack_bf16_slope(r2.x, r2.y, sp_slope, sp_post) : pack_bf16_relu(r2.x, r2.y);
+            o[i] = spade ? pack16_slope<F16>(r2.x, r2.y, sp_slope, sp_post) : pack16_relu<F16>(r2.x, r2.y);
           }
           *hp = make_uint4(o[0], o[1], o[2], o[3]);  // in place: this thread alone reads and writes this chunk
         }
@@ -1082,21 +1118,51 @@ int igemm_smem_bytes(const IgemmParams& p) {
   return p.stages * stage + resident + aad + 1024;
 }
 
-const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
-  static int max_dyn_smem = 0;  // opt-in dynamic shared memory limit (227 KB minus the kernel's static part)
-  if (!max_dyn_smem) {
+namespace {
+// Per-device launch state: the dynamic shared-memory opt-in is a per-device function attribute and the SM count is
+// a device property, so both are cached per device ordinal (one process may drive several GPUs).
+struct IgemmDevState {
+  int max_dyn_smem = 0;  // opt-in dynamic shared memory limit (227 KB minus the kernel's static part)
+  int num_sms = 0;
+};
+constexpr int kMaxDevices = 64;
+IgemmDevState g_dev_state[kMaxDevices];
+std::mutex g_dev_mutex;
+
+const char* igemm_dev_state(IgemmDevState* out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cudaGetErrorString(e);
+  if (dev < 0 || dev >= kMaxDevices) return "igemm: device ordinal out of range";
+  std::lock_guard<std::mutex> lock(g_dev_mutex);
+  IgemmDevState& st = g_dev_state[dev];
+  if (!st.max_dyn_smem) {
     cudaFuncAttributes fa;
-    cudaError_t e = cudaFuncGetAttributes(&fa, igemm_kernel);
+    e = cudaFuncGetAttributes(&fa, igemm_kernel<false>);
+    int lim = 0;
     if (e == cudaSuccess) {
-      const int lim = 227 * 1024 - static_cast<int>(fa.sharedSizeBytes);
-      e = cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
-      if (e == cudaSuccess) max_dyn_smem = lim;
+      lim = 227 * 1024 - static_cast<int>(fa.sharedSizeBytes);
+      e = cudaFuncSetAttribute(igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     }
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    int sms = 0;
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) {
       cudaGetLastError();  // do not leave a stale error behind for the next launch check
       return cudaGetErrorString(e);
     }
+    st.num_sms = sms > 0 ? sms : 148;
+    st.max_dyn_smem = lim;
   }
+  *out = st;
+  return nullptr;
+}
+}  // namespace
+
+const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
+  IgemmDevState dev_state;
+  if (const char* e = igemm_dev_state(&dev_state)) return e;
+  const int max_dyn_smem = dev_state.max_dyn_smem;
   if (p.BN % 16 || p.BN < 16 || p.BN > 256) return "igemm: BN must be a multiple of 16 in [16,256]";
   if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm: M box must hold 1..128 rows";
@@ -1122,13 +1188,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
   if (tiles <= 0) return "igemm: empty grid";
-  static int num_sms = 0;
-  if (!num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (num_sms <= 0) num_sms = 148;
-  }
+  const int num_sms = dev_state.num_sms;
   int gx = tiles < num_sms ? tiles : num_sms;
   if (p.splits > 1) {
     gx = num_sms / p.splits;
@@ -1154,7 +1214,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, igemm_kernel, p);
+  cudaError_t e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm_kernel<true>, p) : cudaLaunchKernelEx(&cfg, igemm_kernel<false>, p);
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }

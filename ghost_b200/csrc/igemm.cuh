@@ -103,6 +103,8 @@ struct alignas(64) IgemmParams {
   // cross HBM once for both layers (the second reader hits L2), and every CTA keeps one layer's weights resident.
   int aad_pair;
 
+  int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
+
   int* err;  // device word set non-zero when a pipeline wait timed out
 };
 

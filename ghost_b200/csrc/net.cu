@@ -42,11 +42,36 @@ static inline uint16_t f2bf(float f) {  // round-to-nearest-even, NaN preserved
   u += 0x7fffu + ((u >> 16) & 1u);
   return static_cast<uint16_t>(u >> 16);
 }
-__nv_bfloat16* DevPool::upload_bf16(const std::vector<float>& v) {
+// fp32 -> IEEE fp16 bits, round-to-nearest-even, overflow to infinity, subnormals kept (what __float2half_rn does)
+static inline uint16_t f2h(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  const uint32_t sign = (u >> 16) & 0x8000u;
+  const uint32_t a = u & 0x7fffffffu;
+  if (a > 0x7f800000u) return static_cast<uint16_t>(sign | 0x7e00u);          // NaN
+  if (a >= 0x477ff000u) return static_cast<uint16_t>(sign | 0x7c00u);         // rounds to >= 65520: infinity
+  if (a < 0x33000001u) return static_cast<uint16_t>(sign);                    // <= 2^-25: rounds to zero
+  if (a < 0x38800000u) {                                                      // subnormal half
+    const int e = static_cast<int>(a >> 23);                                  // biased exponent, 102..112
+    const uint32_t m = (a & 0x7fffffu) | 0x800000u;                           // 24-bit significand
+    const int sh = 126 - e;                                                   // 14..24: value = m * 2^-sh half ulps
+    uint32_t r = m >> sh;
+    const uint32_t rem = m & ((1u << sh) - 1u), half = 1u << (sh - 1);
+    if (rem > half || (rem == half && (r & 1u))) ++r;
+    return static_cast<uint16_t>(sign | r);
+  }
+  uint32_t r = a - 0x38000000u;                                               // rebias 127 -> 15
+  r += 0xfffu + ((r >> 13) & 1u);
+  return static_cast<uint16_t>(sign | (r >> 13));
+}
+__nv_bfloat16* DevPool::upload_16(const std::vector<float>& v, bool f16) {
   std::vector<uint16_t> h(v.size());
-  for (size_t i = 0; i < v.size(); ++i) h[i] = f2bf(v[i]);
+  if (f16)
+    for (size_t i = 0; i < v.size(); ++i) h[i] = f2h(v[i]);
+  else
+    for (size_t i = 0; i < v.size(); ++i) h[i] = f2bf(v[i]);
   __nv_bfloat16* d = alloc_n<__nv_bfloat16>(v.size());
-  check_cuda(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice), "upload_bf16");
+  check_cuda(cudaMemcpy(d, h.data(), h.size() * 2, cudaMemcpyHostToDevice), "upload_16");
   return d;
 }
 
@@ -58,7 +83,7 @@ ExecPlan::~ExecPlan() {
 
 // ------------------------------------------------------------------ Net basics
 Net::Net(Kind k, std::string bb, int nb, int cid, int mode)
-    : kind(k), backbone(std::move(bb)), num_blocks(nb), c_id(cid), act_dtype(mode == 0 ? kF32 : kBF16) {}
+    : kind(k), backbone(std::move(bb)), num_blocks(nb), c_id(cid), act_dtype(mode == 0 ? kF32 : (mode == 2 ? kF16 : kBF16)) {}
 Net::~Net() {}
 
 void Net::set_weight(const std::string& key, const float* data, const int64_t* shape, int ndim) {
@@ -86,10 +111,10 @@ PackedW Net::pack(const std::vector<float>& rows, int Cout, int K, const std::ve
   if (need_bf16) {
     std::vector<float> padded(static_cast<size_t>(p.rows_pad) * K, 0.f);
     memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
-    p.wb = wpool_.upload_bf16(padded);
+    p.wb = wpool_.upload_16(padded, act_dtype == kF16);
     // a 3x3 conv onto <= 3 channels (rows [co][tap][ci]): also keep the tapn.cuh layout; lower_conv picks the kernel
     if (Cout <= 3 && K % (9 * 64) == 0 && K / (9 * 64) <= kTapnMaxChunks)
-      p.wt = wpool_.upload_bf16(tapn_pack_rows(rows.data(), Cout, K / 9));
+      p.wt = wpool_.upload_16(tapn_pack_rows(rows.data(), Cout, K / 9), act_dtype == kF16);
   }
   if (bias) {
     std::vector<float> b(p.rows_pad, 0.f);

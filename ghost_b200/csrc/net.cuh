@@ -44,7 +44,9 @@ class DevPool {
     return reinterpret_cast<T*>(alloc(n * sizeof(T)));
   }
   float* upload(const std::vector<float>& v);
-  __nv_bfloat16* upload_bf16(const std::vector<float>& v);
+  // 16-bit copy of v in the net's storage type: bf16, or IEEE fp16 bits behind the same pointer type
+  __nv_bfloat16* upload_16(const std::vector<float>& v, bool f16);
+  __nv_bfloat16* upload_bf16(const std::vector<float>& v) { return upload_16(v, false); }
   size_t total_bytes() const { return total_; }
 
  private:
@@ -115,7 +117,7 @@ class Net {
   Kind kind;
   std::string backbone;
   int num_blocks, c_id;
-  int act_dtype;  // kF32 or kBF16
+  int act_dtype;  // kF32, or the 16-bit storage type of the tensor-core path: kBF16 / kF16
   bool use_graph = false;
   bool finalized = false;
   size_t encoder_ops = 0;  // ops [0, encoder_ops) compute the attribute maps

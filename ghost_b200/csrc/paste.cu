@@ -11,6 +11,7 @@
 #include "paste.cuh"
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <math.h>
 
 namespace ghost {
@@ -30,6 +31,14 @@ struct CropSrc {
     const long long pix = (static_cast<long long>(crop) * 256 + y) * 256 + x;
     if (kind == kCropU8BGR) return reinterpret_cast<const uint8_t*>(base)[pix * 3 + c];
     float v;
+    if (kind == kCropYF16) {
+      // fp16 generator (inference.py:30 `G.half()`): the reference evaluates (Y*0.5 + 0.5)*255 in fp16, one rounding
+      // per operation (faceshifter_run.py:20), then truncates
+      const __half h = reinterpret_cast<const __half*>(base)[pix * 3 + (2 - c)];
+      const __half t = __hmul(__hadd(__hmul(h, __float2half_rn(0.5f)), __float2half_rn(0.5f)), __float2half_rn(255.f));
+      v = fminf(fmaxf(__half2float(t), 0.f), 255.f);
+      return static_cast<int>(v);
+    }
     if (kind == kCropYBF16)
       v = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[pix * 3 + (2 - c)]);
     else
@@ -193,6 +202,16 @@ template <>
 __device__ __forceinline__ void st_act<__nv_bfloat16>(__nv_bfloat16* p, float v) {
   *p = __float2bfloat16(v);
 }
+template <>
+__device__ __forceinline__ void st_act<__half>(__half* p, float v) {
+  *p = __float2half_rn(v);
+}
+template <typename T>
+struct YKind { static constexpr int value = kCropYF32; };
+template <>
+struct YKind<__nv_bfloat16> { static constexpr int value = kCropYBF16; };
+template <>
+struct YKind<__half> { static constexpr int value = kCropYF16; };
 
 template <typename T>
 __global__ void preproc_u8_kernel(const uint8_t* __restrict__ src, T* __restrict__ dst, long long npix,
@@ -217,7 +236,7 @@ __global__ void preproc_u8_kernel(const uint8_t* __restrict__ src, T* __restrict
 
 template <typename T>
 __global__ void postproc_u8_kernel(const T* __restrict__ y, uint8_t* __restrict__ dst, long long npix) {
-  CropSrc cs{y, sizeof(T) == 2 ? kCropYBF16 : kCropYF32};
+  CropSrc cs{y, YKind<T>::value};
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < npix;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int crop = static_cast<int>(i >> 16), rem = static_cast<int>(i & 65535);
@@ -353,6 +372,8 @@ const char* preproc_u8_launch(const uint8_t* src, void* dst, int dst_dtype, long
   else if (dst_dtype == kBF16)
     preproc_u8_kernel<__nv_bfloat16>
         <<<grid_for(npix, 256), 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), npix, half_rounding);
+  else if (dst_dtype == kF16)  // fp16 net: the reference's own rounding order (core.py:20-23), whatever half_rounding says
+    preproc_u8_kernel<__half><<<grid_for(npix, 256), 256, 0, s>>>(src, reinterpret_cast<__half*>(dst), npix, 1);
   else
     return "preproc_u8: unsupported dtype";
   return last_err();
@@ -364,6 +385,8 @@ const char* postproc_u8_launch(const void* y, int y_dtype, uint8_t* dst, long lo
   else if (y_dtype == kBF16)
     postproc_u8_kernel<__nv_bfloat16>
         <<<grid_for(npix, 256), 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(y), dst, npix);
+  else if (y_dtype == kF16)
+    postproc_u8_kernel<__half><<<grid_for(npix, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(y), dst, npix);
   else
     return "postproc_u8: unsupported dtype";
   return last_err();
@@ -376,6 +399,8 @@ const char* arcface_preproc_launch(const void* src, int is_u8, void* dst, int ds
   else if (dst_dtype == kBF16)
     arcface_preproc_kernel<__nv_bfloat16>
         <<<grid_for(total, 256), 256, 0, s>>>(src, is_u8, reinterpret_cast<__nv_bfloat16*>(dst), N);
+  else if (dst_dtype == kF16)
+    arcface_preproc_kernel<__half><<<grid_for(total, 256), 256, 0, s>>>(src, is_u8, reinterpret_cast<__half*>(dst), N);
   else
     return "arcface_preproc: unsupported dtype";
   return last_err();

@@ -8,7 +8,7 @@
 namespace ghost {
 
 enum PasteMode : int { kPasteExact = 0, kPasteFloat = 1 };
-enum CropKind : int { kCropU8BGR = 0, kCropYBF16 = 1, kCropYF32 = 2 };
+enum CropKind : int { kCropU8BGR = 0, kCropYBF16 = 1, kCropYF32 = 2, kCropYF16 = 3 };
 
 // One (frame, face) pair.  Filled on the host by paste_prepare_face().
 struct PasteFace {
@@ -22,7 +22,7 @@ struct PasteFace {
 };
 
 struct PasteParams {
-  const void* crops;  // u8 BGR [n,256,256,3], or generator output Y NHWC-3 (RGB, [-1,1]) bf16 / fp32
+  const void* crops;  // u8 BGR [n,256,256,3], or generator output Y NHWC-3 (RGB, [-1,1]) bf16 / fp32 / fp16
   int crop_kind;
   const void* masks;  // [n,224,224] float64 or float32
   int mask_f64;

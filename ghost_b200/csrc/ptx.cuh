@@ -316,16 +316,19 @@ __device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
       : "memory");
 }
 
-// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32, both K-major.
-__host__ __device__ inline uint32_t make_idesc_bf16(uint32_t M, uint32_t N) {
+// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32 or fp16 x fp16 -> fp32, both operands K-major.
+__host__ __device__ inline uint32_t make_idesc_f16(uint32_t M, uint32_t N, bool fp16) {
   uint32_t d = 0;
   d |= 1u << 4;            // D format: f32
-  d |= 1u << 7;            // A format: bf16
-  d |= 1u << 10;           // B format: bf16
+  if (!fp16) {
+    d |= 1u << 7;          // A format: 1 = bf16 (0 = fp16)
+    d |= 1u << 10;         // B format: 1 = bf16 (0 = fp16)
+  }
   d |= (N >> 3) << 17;     // N / 8
   d |= (M >> 4) << 24;     // M / 16
   return d;
 }
+__host__ __device__ inline uint32_t make_idesc_bf16(uint32_t M, uint32_t N) { return make_idesc_f16(M, N, false); }
 
 }  // namespace ptx
 }  // namespace ghost

@@ -1,4 +1,6 @@
 #include "simt.cuh"
+
+#include <cuda_fp16.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -66,6 +68,17 @@ __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, flo
     v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
   }
 }
+template <>
+__device__ __forceinline__ void load8<__half>(const __half* p, float (&v)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
 template <typename T>
 __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
 template <>
@@ -81,6 +94,17 @@ __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const fl
   t = __floats2bfloat162_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
   t = __floats2bfloat162_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
   t = __floats2bfloat162_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
+template <>
+__device__ __forceinline__ void store8<__half>(__half* p, const float (&v)[8]) {
+  uint4 q;
+  __half2 t;
+  t = __floats2half2_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
   *reinterpret_cast<uint4*>(p) = q;
 }
 
@@ -350,7 +374,7 @@ bool rgb_const_supported(const SimtConvParams& p, int dtype) {
     const char* e = getenv("GHOST_RGB_CONST");  // A/B switch for profiling: 0 keeps the shared-memory kernel
     return e ? (atoi(e) != 0) : 1;
   }();
-  return on && (dtype == kF32 || dtype == kBF16) && rgb_const_shape(p) != 0;
+  return on && (dtype == kF32 || dtype == kBF16 || dtype == kF16) && rgb_const_shape(p) != 0;
 }
 
 const char* rgb_const_prepare(const SimtConvParams& p, RgbConvConst* c) {
@@ -385,6 +409,10 @@ const char* rgb_const_launch(const SimtConvParams& p, const RgbConvConst& c, int
     rgb_const_kernel<__nv_bfloat16, 64, 3, 1><<<blocks, 128, 0, s>>>(p, c);
   else if (shape == 2 && dtype == kF32)
     rgb_const_kernel<float, 64, 3, 1><<<blocks, 128, 0, s>>>(p, c);
+  else if (shape == 1 && dtype == kF16)
+    rgb_const_kernel<__half, 32, 4, 2><<<blocks, 128, 0, s>>>(p, c);
+  else if (shape == 2 && dtype == kF16)
+    rgb_const_kernel<__half, 64, 3, 1><<<blocks, 128, 0, s>>>(p, c);
   else
     return "rgb_const: unsupported shape";
   return last_err();
@@ -400,12 +428,15 @@ const char* simt_conv_launch(const SimtConvParams& p, int dtype, cudaStream_t s)
       p.ntaps <= 16 && out_al16) {
     if (dtype == kF32) return rgb_conv_dispatch<float>(p, s);
     if (dtype == kBF16) return rgb_conv_dispatch<__nv_bfloat16>(p, s);
+    if (dtype == kF16) return rgb_conv_dispatch<__half>(p, s);
   }
   dim3 grid(static_cast<unsigned>((M + TM - 1) / TM), (p.Cout + TN - 1) / TN);
   if (dtype == kF32)
     simt_conv_kernel<float><<<grid, 256, 0, s>>>(p);
   else if (dtype == kBF16)
     simt_conv_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(p);
+  else if (dtype == kF16)
+    simt_conv_kernel<__half><<<grid, 256, 0, s>>>(p);
   else
     return "simt_conv: unsupported dtype";
   return last_err();
@@ -607,7 +638,7 @@ __global__ void __launch_bounds__(256) aad_apply_kernel(const T* __restrict__ h,
 // The folded weights depend on the image only: every lane keeps its NIT x 8 of them in registers and reloads them
 // when its pixel sequence crosses into the next image, so the inner loop is one 16-byte load of h per 8 channels.
 // DUAL: a second layer on the same h (the shortcut layer and the first main layer of a block) in the same pass.
-template <int NIT, bool DUAL>
+template <int NIT, bool DUAL, bool F16>
 __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __restrict__ h, long long npix, int HW, int C,
                                                         const float* __restrict__ wh_fold,
                                                         const float* __restrict__ bh_fold, float* __restrict__ mask,
@@ -673,8 +704,14 @@ __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __re
       const uint32_t q4[4] = {cur[it].x, cur[it].y, cur[it].z, cur[it].w};
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        v[it][2 * i] = __uint_as_float(q4[i] << 16);
-        v[it][2 * i + 1] = __uint_as_float(q4[i] & 0xffff0000u);
+        if (F16) {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&q4[i]));
+          v[it][2 * i] = f.x;
+          v[it][2 * i + 1] = f.y;
+        } else {
+          v[it][2 * i] = __uint_as_float(q4[i] << 16);
+          v[it][2 * i + 1] = __uint_as_float(q4[i] & 0xffff0000u);
+        }
       }
       cur[it] = nxt[it];
     }
@@ -697,37 +734,47 @@ __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __re
   }
 }
 
-template <int NIT>
+template <int NIT, bool F16>
 void aad_mask_dispatch(unsigned blocks, cudaStream_t s, const __nv_bfloat16* h, long long npix, int HW, int C,
                        const float* wh_fold, const float* bh_fold, float* mask, const float* wh_fold2,
                        const float* bh_fold2, float* mask2) {
   if (wh_fold2)
-    aad_mask_kernel<NIT, true><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    aad_mask_kernel<NIT, true, F16><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
   else
-    aad_mask_kernel<NIT, false><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr);
+    aad_mask_kernel<NIT, false, F16><<<blocks, 256, 0, s>>>(h, npix, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr);
+}
+template <int NIT>
+void aad_mask_dispatch(unsigned blocks, cudaStream_t s, int dtype, const __nv_bfloat16* h, long long npix, int HW, int C,
+                       const float* wh_fold, const float* bh_fold, float* mask, const float* wh_fold2,
+                       const float* bh_fold2, float* mask2) {
+  if (dtype == kF16)
+    aad_mask_dispatch<NIT, true>(blocks, s, h, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else
+    aad_mask_dispatch<NIT, false>(blocks, s, h, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
 }
 
 }  // namespace
 
 const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
-                            cudaStream_t s) {
-  return aad_mask2_launch(h, N, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr, s);
+                            cudaStream_t s, int dtype) {
+  return aad_mask2_launch(h, N, HW, C, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr, s, dtype);
 }
 
 const char* aad_mask2_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
-                             const float* wh_fold2, const float* bh_fold2, float* mask2, cudaStream_t s) {
+                             const float* wh_fold2, const float* bh_fold2, float* mask2, cudaStream_t s, int dtype) {
   if (C % 8) return "aad_mask: C must be a multiple of 8";
+  if (dtype != kBF16 && dtype != kF16) return "aad_mask: h must be a 16-bit tensor";
   const long long npix = static_cast<long long>(N) * HW;
   long long blocks = (npix + 7) / 8;
   if (blocks > 148 * 16) blocks = 148 * 16;
   const __nv_bfloat16* hp = reinterpret_cast<const __nv_bfloat16*>(h);
   const unsigned nb = static_cast<unsigned>(blocks);
   if (C <= 256)
-    aad_mask_dispatch<1>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    aad_mask_dispatch<1>(nb, s, dtype, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
   else if (C <= 512)
-    aad_mask_dispatch<2>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    aad_mask_dispatch<2>(nb, s, dtype, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
   else if (C <= 1024)
-    aad_mask_dispatch<4>(nb, s, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    aad_mask_dispatch<4>(nb, s, dtype, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
   else
     return "aad_mask: C must be <= 1024";
   return last_err();
@@ -767,6 +814,9 @@ const char* in_stats_launch_ex(const void* x, int dtype, int N, int HW, int C, f
   else if (dtype == kBF16)
     in_stats_kernel<__nv_bfloat16>
         <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __nv_bfloat16*>(x), HW, C, ppb, parts, common_shift);
+  else if (dtype == kF16)
+    in_stats_kernel<__half>
+        <<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const __half*>(x), HW, C, ppb, parts, common_shift);
   else
     return "in_stats: unsupported dtype";
   return last_err();
@@ -796,6 +846,10 @@ const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype
     aad_apply_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, s>>>(
         reinterpret_cast<const __nv_bfloat16*>(h), reinterpret_cast<const __nv_bfloat16*>(gb),
         reinterpret_cast<__nv_bfloat16*>(out), npix, HW, C, ncpar, wh_fold, bh_fold);
+  else if (dtype == kF16)
+    aad_apply_kernel<__half><<<static_cast<unsigned>(blocks), 256, 0, s>>>(
+        reinterpret_cast<const __half*>(h), reinterpret_cast<const __half*>(gb),
+        reinterpret_cast<__half*>(out), npix, HW, C, ncpar, wh_fold, bh_fold);
   else
     return "aad_apply: unsupported dtype";
   return last_err();
@@ -841,6 +895,23 @@ __device__ __forceinline__ void store8_rounded(__nv_bfloat16* p, const float (&v
   for (int i = 0; i < 4; ++i) {
     r[2 * i] = __uint_as_float(w[i] << 16);
     r[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+
+__device__ __forceinline__ void store8_rounded(__half* p, const float (&v)[8], float (&r)[8]) {
+  uint4 q;
+  __half2 t;
+  t = __floats2half2_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    r[2 * i] = f.x;
+    r[2 * i + 1] = f.y;
   }
 }
 
@@ -1024,6 +1095,9 @@ const char* nchw_to_nhwc_dst(const S* src, void* dst, int dst_dtype, int N, int 
   else if (dst_dtype == kBF16)
     nchw_to_nhwc_kernel<S, __nv_bfloat16>
         <<<grid, 256, 0, s>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), C, H * W, dstC, dst_c0);
+  else if (dst_dtype == kF16)
+    nchw_to_nhwc_kernel<S, __half>
+        <<<grid, 256, 0, s>>>(src, reinterpret_cast<__half*>(dst), C, H * W, dstC, dst_c0);
   else
     return "nchw_to_nhwc: unsupported destination dtype";
   return last_err();
@@ -1060,6 +1134,9 @@ const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, i
   else if (dtype == kBF16)
     upsample2x_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                           reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C, oC, o_c0);
+  else if (dtype == kF16)
+    upsample2x_kernel<__half><<<grid, 256, 0, s>>>(reinterpret_cast<const __half*>(x),
+                                                          reinterpret_cast<__half*>(y), N, H, W, C, oC, o_c0);
   else
     return "upsample2x: unsupported dtype";
   return last_err();
@@ -1079,6 +1156,9 @@ const char* upsample2x_stats_launch(const void* x, void* y, int dtype, int N, in
   else if (dtype == kBF16)
     upsample2x_stats_kernel<__nv_bfloat16><<<grid, kStatThreads, smem, s>>>(
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), H, W, C, ppb, parts);
+  else if (dtype == kF16)
+    upsample2x_stats_kernel<__half><<<grid, kStatThreads, smem, s>>>(
+        reinterpret_cast<const __half*>(x), reinterpret_cast<__half*>(y), H, W, C, ppb, parts);
   else
     return "upsample2x_stats: unsupported dtype";
   return last_err();
@@ -1101,6 +1181,8 @@ const char* nhwc_to_nchw_launch(const void* src, int src_dtype, int srcC, int sr
     return nhwc_to_nchw_dst(reinterpret_cast<const float*>(src), srcC, src_c0, dst, dst_dtype, N, C, H, W, s);
   if (src_dtype == kBF16)
     return nhwc_to_nchw_dst(reinterpret_cast<const __nv_bfloat16*>(src), srcC, src_c0, dst, dst_dtype, N, C, H, W, s);
+  if (src_dtype == kF16)
+    return nhwc_to_nchw_dst(reinterpret_cast<const __half*>(src), srcC, src_c0, dst, dst_dtype, N, C, H, W, s);
   return "nhwc_to_nchw: unsupported source dtype";
 }
 
@@ -1113,6 +1195,9 @@ const char* zfc_to_act_launch(const float* zfc, int ldz, int off, int count, con
   else if (dtype == kBF16)
     zfc_to_act_kernel<__nv_bfloat16>
         <<<grid_for(total, 256), 256, 0, s>>>(zfc, ldz, off, count, bias, reinterpret_cast<__nv_bfloat16*>(dst), N);
+  else if (dtype == kF16)
+    zfc_to_act_kernel<__half>
+        <<<grid_for(total, 256), 256, 0, s>>>(zfc, ldz, off, count, bias, reinterpret_cast<__half*>(dst), N);
   else
     return "zfc_to_act: unsupported dtype";
   return last_err();
@@ -1128,6 +1213,9 @@ const char* channel_affine_launch(const void* x, void* y, int dtype, long long n
   else if (dtype == kBF16)
     channel_affine_kernel<__nv_bfloat16><<<grid_for(total, 256), 256, 0, s>>>(
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), npix, C, scale, shift, prelu);
+  else if (dtype == kF16)
+    channel_affine_kernel<__half><<<grid_for(total, 256), 256, 0, s>>>(
+        reinterpret_cast<const __half*>(x), reinterpret_cast<__half*>(y), npix, C, scale, shift, prelu);
   else
     return "channel_affine: unsupported dtype";
   return last_err();

@@ -3,6 +3,7 @@
 // elementwise / reduction step of the hot path.
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -65,10 +66,11 @@ const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, con
 
 // bf16 mode, c_x > 128: the per-pixel sigmoid mask of an AADLayer, mask[N*HW] fp32.
 const char* aad_mask_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
-                            cudaStream_t s);
+                            cudaStream_t s, int dtype = kBF16);  // dtype of h: kBF16 or kF16
 // the masks of two AADLayers that read the same h (shortcut layer + first main layer of a block) in one pass over h
 const char* aad_mask2_launch(const void* h, int N, int HW, int C, const float* wh_fold, const float* bh_fold, float* mask,
-                             const float* wh_fold2, const float* bh_fold2, float* mask2, cudaStream_t s);
+                             const float* wh_fold2, const float* bh_fold2, float* mask2, cudaStream_t s,
+                             int dtype = kBF16);
 
 // Unfused AAD blend (+ReLU) used by the fp32 mode: gb = [N,H,W,2C] (gamma | beta, bias included).
 const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype, int N, int HW, int C,

@@ -78,7 +78,7 @@ std::vector<float> padded(const std::vector<float>& v, int n, float fill = 0.f) 
 }  // namespace
 
 void Net::finalize_sr() {
-  const bool bf = act_dtype == kBF16;
+  const bool bf = is16(act_dtype);  // tensor-core mode: bf16 or fp16 storage
   sr_sn_.clear();
   sr_slices_.clear();
   for (int i = 0; i < 6; ++i) sr_actv_c_[i] = sr_actv_need_[i] = 0;
@@ -232,7 +232,7 @@ void Net::finalize_sr() {
 void Net::build_sr(ExecPlan& p) {
   const int B = p.B;
   const int dt = act_dtype;
-  const bool bf = dt == kBF16;
+  const bool bf = is16(dt);  // tensor-core mode: bf16 or fp16 storage
   const double esz = bf ? 2.0 : 4.0;
   int* err = p.err_word;
 

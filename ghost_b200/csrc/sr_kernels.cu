@@ -1,5 +1,7 @@
 #include "sr_kernels.cuh"
 
+#include <cuda_fp16.h>
+
 #include <math.h>
 
 namespace ghost {
@@ -21,8 +23,16 @@ template <>
 __device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p) {
   return __bfloat162float(*p);
 }
+template <>
+__device__ __forceinline__ float ldf<__half>(const __half* p) {
+  return __half2float(*p);
+}
 template <typename T>
 __device__ __forceinline__ T cvt(float v);
+template <>
+__device__ __forceinline__ __half cvt<__half>(float v) {
+  return __float2half_rn(v);
+}
 template <>
 __device__ __forceinline__ float cvt<float>(float v) {
   return v;
@@ -51,8 +61,29 @@ __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, flo
     v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
   }
 }
+template <>
+__device__ __forceinline__ void load8<__half>(const __half* p, float (&v)[8]) {
+  const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
 template <typename T>
 __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void store8<__half>(__half* p, const float (&v)[8]) {
+  uint4 q;
+  __half2 t;
+  t = __floats2half2_rn(v[0], v[1]); q.x = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[2], v[3]); q.y = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[4], v[5]); q.z = *reinterpret_cast<uint32_t*>(&t);
+  t = __floats2half2_rn(v[6], v[7]); q.w = *reinterpret_cast<uint32_t*>(&t);
+  *reinterpret_cast<uint4*>(p) = q;
+}
 template <>
 __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
   reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
@@ -417,6 +448,9 @@ const char* seg_patches_launch(const void* img, void* patches, int dtype, int N,
   else if (dtype == kBF16)
     seg_patches_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(img),
                                                              reinterpret_cast<__nv_bfloat16*>(patches), N, S, 256 / S);
+  else if (dtype == kF16)
+    seg_patches_kernel<__half><<<blocks, 256, 0, s>>>(reinterpret_cast<const __half*>(img),
+                                                             reinterpret_cast<__half*>(patches), N, S, 256 / S);
   else
     return "seg_patches: unsupported dtype";
   return last_err();
@@ -448,6 +482,10 @@ const char* norm_act_launch(const void* x, void* y, int dtype, int N, int HW, in
     norm_act_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                           reinterpret_cast<__nv_bfloat16*>(y), total8, HW, C, ss,
                                                           ss_stride_n, act);
+  else if (dtype == kF16)
+    norm_act_kernel<__half><<<blocks, 256, 0, s>>>(reinterpret_cast<const __half*>(x),
+                                                          reinterpret_cast<__half*>(y), total8, HW, C, ss,
+                                                          ss_stride_n, act);
   else
     return "norm_act: unsupported dtype";
   return last_err();
@@ -466,6 +504,10 @@ const char* lip_pool_launch(const void* x, const void* logit, void* out, int dty
     lip_pool_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                           reinterpret_cast<const __nv_bfloat16*>(logit),
                                                           reinterpret_cast<__nv_bfloat16*>(out), N, H, W, C, ss);
+  else if (dtype == kF16)
+    lip_pool_kernel<__half><<<blocks, 256, 0, s>>>(reinterpret_cast<const __half*>(x),
+                                                          reinterpret_cast<const __half*>(logit),
+                                                          reinterpret_cast<__half*>(out), N, H, W, C, ss);
   else
     return "lip_pool: unsupported dtype";
   return last_err();
@@ -485,6 +527,10 @@ const char* spade_apply_launch(const void* x, const void* gb, void* out, int dty
     spade_apply_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(gb),
         reinterpret_cast<__nv_bfloat16*>(out), total8, H, W, C, up, ss, act, post);
+  else if (dtype == kF16)
+    spade_apply_kernel<__half><<<blocks, 256, 0, s>>>(
+        reinterpret_cast<const __half*>(x), reinterpret_cast<const __half*>(gb),
+        reinterpret_cast<__half*>(out), total8, H, W, C, up, ss, act, post);
   else
     return "spade_apply: unsupported dtype";
   return last_err();
@@ -500,6 +546,9 @@ const char* nearest_up2x_launch(const void* x, void* y, int dtype, int N, int H,
   else if (dtype == kBF16)
     nearest_up2x_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                               reinterpret_cast<__nv_bfloat16*>(y), total8, H, W, C);
+  else if (dtype == kF16)
+    nearest_up2x_kernel<__half><<<blocks, 256, 0, s>>>(reinterpret_cast<const __half*>(x),
+                                                              reinterpret_cast<__half*>(y), total8, H, W, C);
   else
     return "nearest_up2x: unsupported dtype";
   return last_err();
@@ -589,6 +638,8 @@ const char* sr_preproc_launch(const uint8_t* crops_bgr, void* dst, int dtype, in
     sr_preproc_kernel<float><<<blocks, 256, 0, s>>>(crops_bgr, reinterpret_cast<float*>(dst), npix);
   else if (dtype == kBF16)
     sr_preproc_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(crops_bgr, reinterpret_cast<__nv_bfloat16*>(dst), npix);
+  else if (dtype == kF16)
+    sr_preproc_kernel<__half><<<blocks, 256, 0, s>>>(crops_bgr, reinterpret_cast<__half*>(dst), npix);
   else
     return "sr_preproc: unsupported dtype";
   return last_err();
@@ -601,6 +652,8 @@ const char* sr_postproc_launch(const void* y, int dtype, uint8_t* dst_bgr, int N
     sr_postproc_kernel<float><<<blocks, 256, 0, s>>>(reinterpret_cast<const float*>(y), dst_bgr, npix);
   else if (dtype == kBF16)
     sr_postproc_kernel<__nv_bfloat16><<<blocks, 256, 0, s>>>(reinterpret_cast<const __nv_bfloat16*>(y), dst_bgr, npix);
+  else if (dtype == kF16)
+    sr_postproc_kernel<__half><<<blocks, 256, 0, s>>>(reinterpret_cast<const __half*>(y), dst_bgr, npix);
   else
     return "sr_postproc: unsupported dtype";
   return last_err();

@@ -5,7 +5,10 @@
 // where every interior pixel collects its nine neighbours' partial sums.
 #include "tapn.cuh"
 
+#include <cuda_fp16.h>
 #include <string.h>
+
+#include <mutex>
 
 #include "ptx.cuh"
 
@@ -104,7 +107,7 @@ __global__ void __launch_bounds__(kThreads, 2) tapn_kernel(const __grid_constant
     }
   } else if (warp == 1) {
     mbar_wait_nofail(&sm.wfull, 0, abortp);
-    const uint32_t idesc = make_idesc_bf16(128, 32);
+    const uint32_t idesc = make_idesc_f16(128, 32, p.f16 != 0);
     const uint32_t hi = smem_desc_hi(1024, false);
     int it = 0, tl = 0;
     for (int t = first; t < p.tiles; t += step, ++tl) {
@@ -159,7 +162,8 @@ __global__ void __launch_bounds__(kThreads, 2) tapn_kernel(const __grid_constant
         if (on[k] && p.res) {
           const long long ro = p.r_off + n * p.r_sn + gy * p.r_sh + gx * p.r_sw + co[k];
           r[k] = p.out_f32 ? __ldg(reinterpret_cast<const float*>(p.res) + ro)
-                           : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.res)[ro]);
+                 : p.f16    ? __half2float(reinterpret_cast<const __half*>(p.res)[ro])
+                            : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.res)[ro]);
         }
       }
       mbar_wait_nofail(&sm.tfull[g], (tl >> 1) & 1, abortp);
@@ -191,6 +195,8 @@ __global__ void __launch_bounds__(kThreads, 2) tapn_kernel(const __grid_constant
         if (p.act2 == kAct2Tanh) s = tanhf(s);
         if (p.out_f32)
           reinterpret_cast<float*>(p.out)[o[k]] = s;
+        else if (p.f16)
+          reinterpret_cast<__half*>(p.out)[o[k]] = __float2half_rn(s);
         else
           reinterpret_cast<__nv_bfloat16*>(p.out)[o[k]] = __float2bfloat16(s);
       }
@@ -220,17 +226,28 @@ std::vector<float> tapn_pack_rows(const float* rows_in, int Co, int Ci) {
 }
 
 const char* tapn_launch(const TapnParams& p, cudaStream_t s) {
-  static bool configured = false;
+  // the dynamic shared-memory opt-in and the SM count are per device (one process may drive several GPUs)
+  static std::mutex mu;
+  static int sms_of[64] = {0};
   const int smem = static_cast<int>(sizeof(TapnSmem)) + 1024;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tapn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      cudaGetLastError();
-      return cudaGetErrorString(e);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return "tapn: bad device ordinal";
+  int sms;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!sms_of[dev]) {
+      cudaError_t e = cudaFuncSetAttribute(tapn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      int n = 0;
+      if (e == cudaSuccess) e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        return cudaGetErrorString(e);
+      }
+      sms_of[dev] = n > 0 ? n : 148;
     }
-    configured = true;
+    sms = sms_of[dev];
   }
-  const int grid = p.tiles < 2 * 148 ? p.tiles : 2 * 148;
+  const int grid = p.tiles < 2 * sms ? p.tiles : 2 * sms;
   tapn_kernel<<<grid, kThreads, smem, s>>>(p);
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);

@@ -31,6 +31,7 @@ struct TapnParams {
   int tiles_x, tiles_y, tiles;
   void* out;
   int out_f32;
+  int f16;  // 16-bit storage type: 0 = bf16, 1 = fp16 (input, weights, residual and a 16-bit output)
   long long o_sn, o_sh, o_sw, o_off;
   const void* res;  // residual in the output's dtype, or null
   long long r_sn, r_sh, r_sw, r_off;

@@ -36,7 +36,7 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
                     void* stream) {
   return guarded_t([&] {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    const int dt = mode == GHOST_F32 ? kF32 : kBF16;
+    const int dt = mode == GHOST_F32 ? kF32 : (mode == GHOST_F16 ? kF16 : kBF16);
     DevPool pool;
     Act in;
     in.p = const_cast<void*>(x);
@@ -56,9 +56,9 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
       } else {
         std::vector<float> padded(static_cast<size_t>(pw.rows_pad) * K, 0.f);
         memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
-        pw.wb = pool.upload_bf16(padded);
+        pw.wb = pool.upload_16(padded, dt == kF16);
         if (kind == 0 && k == 3 && Cout <= 3 && Cin % 64 == 0 && Cin / 64 <= kTapnMaxChunks)
-          pw.wt = pool.upload_bf16(tapn_pack_rows(rows.data(), Cout, Cin));
+          pw.wt = pool.upload_16(tapn_pack_rows(rows.data(), Cout, Cin), dt == kF16);
       }
       if (bias_host) {
         std::vector<float> b(pw.rows_pad, 0.f);
@@ -114,8 +114,8 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
                    const float* convh_w, float convh_b, void* out, int mode, void* stream) {
   return guarded_t([&] {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    const int dt = mode == GHOST_F32 ? kF32 : kBF16;
-    const bool bf = dt == kBF16;
+    const int dt = mode == GHOST_F32 ? kF32 : (mode == GHOST_F16 ? kF16 : kBF16);
+    const bool bf = is16(dt);
     DevPool pool;
     const int HW = H * W;
     // identity branch on the host (fp32): gamma_id / beta_id = fc(z_id)
@@ -165,12 +165,12 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
     if (bf) {
       std::vector<float> padded(static_cast<size_t>(pw.rows_pad) * c_attr, 0.f);
       memcpy(padded.data(), rows.data(), rows.size() * sizeof(float));
-      pw.wb = pool.upload_bf16(padded);
+      pw.wb = pool.upload_16(padded, dt == kF16);
       AadArgs args;
       args.h = h; args.c_x = c_x; args.ncpar = ncpar; args.wh_fold = whf; args.bh_fold = bhf;
       if (c_x > 128) {
         float* mask = pool.alloc_n<float>(static_cast<size_t>(N) * HW);
-        check_msg(aad_mask_launch(h, N, HW, c_x, whf, bhf, mask, s), "aad mask");
+        check_msg(aad_mask_launch(h, N, HW, c_x, whf, bhf, mask, s, dt), "aad mask");
         args.mask = mask;
       }
       LaunchOp op;
@@ -197,7 +197,7 @@ int ghost_test_aad(const void* h, const void* zattr, const float* zid_host, int 
 int ghost_test_upsample2x(const void* x, void* y, int dtype, int N, int H, int W, int C, void* stream) {
   return guarded_t([&] {
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    check_msg(upsample2x_launch(x, y, dtype == GHOST_F32 ? kF32 : kBF16, N, H, W, C, C, 0, s), "upsample2x");
+    check_msg(upsample2x_launch(x, y, dtype == GHOST_F32 ? kF32 : (dtype == GHOST_F16 ? kF16 : kBF16), N, H, W, C, C, 0, s), "upsample2x");
     check_cuda(cudaStreamSynchronize(s), "upsample sync");
   });
 }
@@ -213,7 +213,7 @@ int ghost_test_upsample2x_stats(const void* x, void* y, int dtype, int N, int H,
     const int P = in_stats_parts(N, HWo, C);
     const size_t nparts = static_cast<size_t>(N) * (2 * P + 1) * C;
     float* parts = pool.alloc_n<float>(nparts);
-    check_msg(upsample2x_stats_launch(x, y, dtype == GHOST_F32 ? kF32 : kBF16, N, H, W, C, parts, s), "upsample2x_stats");
+    check_msg(upsample2x_stats_launch(x, y, dtype == GHOST_F32 ? kF32 : (dtype == GHOST_F16 ? kF16 : kBF16), N, H, W, C, parts, s), "upsample2x_stats");
     check_cuda(cudaStreamSynchronize(s), "upsample sync");
     std::vector<float> hp(nparts);
     check_cuda(cudaMemcpy(hp.data(), parts, nparts * sizeof(float), cudaMemcpyDeviceToHost), "parts download");

@@ -41,8 +41,12 @@ typedef enum {
 /* element types of buffers crossing the ABI */
 typedef enum { GHOST_F32 = 0, GHOST_BF16 = 1, GHOST_F16 = 2, GHOST_U8 = 3 } ghost_dtype;
 
-/* arithmetic mode of a network: GHOST_F32 = CUDA-core fp32 correctness mode (1e-4 contract),
- * GHOST_BF16 = tcgen05 bf16 x bf16 -> fp32 production mode (1e-2 contract). */
+/* arithmetic mode of a network (= storage type of its activations and weights on the device):
+ *   GHOST_F32  = CUDA-core fp32 correctness mode (1e-4 contract);
+ *   GHOST_F16  = tcgen05 fp16 x fp16 -> fp32 production mode: the reference's own deployment dtype
+ *                (inference.py:30 `G.half()`), meets the 1e-2 max-abs / 1e-3 mean-abs contract on Y;
+ *   GHOST_BF16 = tcgen05 bf16 x bf16 -> fp32, same speed, wider range, 8 mantissa bits (outside that contract for
+ *                random-init weights). */
 
 typedef struct ghost_net ghost_net_t;
 
@@ -154,7 +158,7 @@ int ghost_postproc_u8(const void* y_nhwc3, int y_dtype, uint8_t* dst_bgr, int B,
 
 /* ---- paste-back (image_processing.py:51-77 exact mode; video_processing.py:212-233 float mode) */
 typedef enum { GHOST_PASTE_EXACT = 0, GHOST_PASTE_FLOAT = 1 } ghost_paste_mode;
-typedef enum { GHOST_CROP_U8_BGR = 0, GHOST_CROP_Y_BF16 = 1, GHOST_CROP_Y_F32 = 2 } ghost_crop_kind;
+typedef enum { GHOST_CROP_U8_BGR = 0, GHOST_CROP_Y_BF16 = 1, GHOST_CROP_Y_F32 = 2, GHOST_CROP_Y_F16 = 3 } ghost_crop_kind;
 
 typedef struct {
   const void* crops;        /* device: [n_crops,256,256,3] u8 BGR, or NHWC-3 generator output (RGB, [-1,1]) */
@@ -219,7 +223,7 @@ int ghost_face_masks(const float* landmarks, const int* params, int n, void* mas
 /* ---- single-op entry points used by the kernel-level parity tests (tests/test_kernels_gpu.py).
  * conv: NHWC activations (dtype = mode); weights fp32 on the host in the reference layout:
  * kind 0 = nn.Conv2d(k,stride,pad) weight [Cout][Cin][k][k], kind 1 = nn.ConvTranspose2d(k=4,s=2,p=1) weight
- * [Cin][Cout][4][4].  act: 0 none, 1 leaky(slope), 3 relu.  mode GHOST_F32 / GHOST_BF16.  Synchronous. */
+ * [Cin][Cout][4][4].  act: 0 none, 1 leaky(slope), 3 relu.  mode GHOST_F32 / GHOST_BF16 / GHOST_F16.  Synchronous. */
 int ghost_test_conv(const void* x_nhwc, int N, int H, int W, int Cin, const float* w_host, const float* bias_host,
                     int Cout, int kind, int k, int stride, int pad, int act, float slope, void* y_nhwc, int mode,
                     int bn_hint, void* stream);

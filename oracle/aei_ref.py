@@ -118,3 +118,12 @@ def postprocess_ref(Y):
     """utils/inference/faceshifter_run.py:20-22 in fp32: Y [B,3,H,W] -> uint8 BGR [B,H,W,3] (truncating cast)."""
     y = (Y.float().permute(0, 2, 3, 1) * 0.5 + 0.5) * 255
     return y[:, :, :, [2, 1, 0]].type(torch.uint8).numpy()
+
+
+def postprocess_ref_half(Y_half):
+    """utils/inference/faceshifter_run.py:20-22 as the reference evaluates it with G.half() (inference.py:30): Y is
+    an fp16 tensor, so (Y*0.5 + 0.5)*255 runs in fp16 with one rounding per operation, then the truncating uint8 cast.
+    torch's CPU half kernels compute each elementwise op in fp32 and round the result to fp16 = the same roundings."""
+    assert Y_half.dtype == torch.float16
+    y = (Y_half.permute(0, 2, 3, 1) * 0.5 + 0.5) * 255
+    return y[:, :, :, [2, 1, 0]].type(torch.uint8).numpy()

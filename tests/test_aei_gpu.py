@@ -5,7 +5,10 @@ Tolerances.  fp32 mode: max-abs <= 1e-4 on Y in [-1,1] (BASELINE.json north_star
 For the "perturbed" weight sets the reference's own fp32 forward sits 3e-5 .. 4.5e-4 (max-abs) away from the same
 arithmetic in fp64 (tools/fp64_noise.py, FP32_NOISE below), so 1e-4 is inside its rounding noise there; those cases
 assert max-abs <= max(1e-4, 5 x that noise floor) and mean-abs <= 2e-5.
-bf16 mode: north_star asks for max-abs <= 1e-2 / mean-abs <= 1e-3 against the fp32 forward.  With random-init
+fp16 mode (`.half()`, the dtype the reference deploys, inference.py:30; fp16 operands on tcgen05 kind::f16, fp32
+accumulation and statistics): the north_star bound itself, max-abs <= 1e-2 / mean-abs <= 1e-3 against the fp32
+forward, on ALL golden cases (default and perturbed weights), with no emulation-relative escape hatch.
+bf16 mode (`.bfloat16()`): OUTSIDE north_star's bound, documented.  With random-init
 weights that is below what bf16 *storage* allows for this network whatever the kernels do: rounding only the
 weights, or only one block's activations, of the reference's own fp32 forward to bf16 already moves Y by
 1e-3..5e-3 mean-abs (tools/sens.py, DESIGN.md "bf16 error budget").  The bf16 tests therefore assert
@@ -28,6 +31,8 @@ from oracle.gen_golden import AEI_CASES, aei_case_inputs
 pytestmark = pytest.mark.gpu
 
 BF16_DEFAULT_MAX, BF16_DEFAULT_MEAN, F32_MAX = 1e-1, 3e-3, 1e-4
+F16_MAX, F16_MEAN = 1e-2, 1e-3          # BASELINE.json north_star, asserted as written
+DT = {"fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}
 # max |fp32 reference - fp64 reference| on Y per golden case (tools/fp64_noise.py, run in the build container)
 FP32_NOISE = {"aei_unet2_default": 1.0e-5, "aei_unet2_perturbed": 1.42e-4, "aei_linknet3_perturbed": 4.52e-4,
               "aei_unet1_perturbed": 3.1e-5}
@@ -39,19 +44,23 @@ def build(bb, nb, sd, dtype):
     return G.to(dtype).cuda()
 
 
-@pytest.mark.parametrize("mode", ["bf16", "fp32"])
+@pytest.mark.parametrize("mode", ["fp16", "bf16", "fp32"])
 @pytest.mark.parametrize("case", AEI_CASES, ids=[c[0] for c in AEI_CASES])
 def test_forward_matches_reference_golden(case, mode, golden_dir):
     name, bb, nb, pert, B = case
     gold = np.load(os.path.join(golden_dir, name + ".npz"))
     sd, Xt, z = aei_case_inputs(*case)
-    dt = torch.bfloat16 if mode == "bf16" else torch.float32
+    dt = DT[mode]
     G = build(bb, nb, sd, dt)
     Y, attrs = G(Xt.cuda().to(dt), z.cuda().to(dt))
     torch.cuda.synchronize()
     assert Y.dtype == dt and tuple(Y.shape) == (B, 3, 256, 256) and len(attrs) == 8
+    assert torch.isfinite(Y.float()).all()
     d = np.abs(Y.float().cpu().numpy() - gold["Y"])
-    if mode == "bf16":
+    if mode == "fp16":
+        print("%s fp16: cuda-ref max %.3e mean %.3e" % (name, d.max(), d.mean()))
+        assert d.max() <= F16_MAX and d.mean() <= F16_MEAN, "max %.3e mean %.3e" % (d.max(), d.mean())
+    elif mode == "bf16":  # outside north_star, documented: bounded by the storage-rounding emulation instead
         Ye, _ = aei_emul.aei_forward_emul(sd, Xt, z, bb, nb)
         de = np.abs(Ye.numpy() - gold["Y"])
         print("%s bf16: cuda-ref max %.3e mean %.3e | emul-ref max %.3e mean %.3e" % (name, d.max(), d.mean(), de.max(),
@@ -68,36 +77,39 @@ def test_forward_matches_reference_golden(case, mode, golden_dir):
         assert tuple(a.shape) == tuple(gold["attr%d_shape" % k])
         s = a.reshape(-1)[:: max(1, a.size // 4096)][:4096]
         ref = gold["attr%d_sample" % k]
-        tol = (3e-2 if mode == "bf16" else 2e-4) * max(1.0, np.abs(ref).max())
+        tol = {"bf16": 3e-2, "fp16": 4e-3, "fp32": 2e-4}[mode] * max(1.0, np.abs(ref).max())
         assert np.abs(s - ref).max() <= tol, "attr%d: %.3e" % (k, np.abs(s - ref).max())
 
 
-@pytest.mark.parametrize("mode", ["bf16", "fp32"])
+@pytest.mark.parametrize("mode", ["fp16", "bf16", "fp32"])
 def test_forward_matches_oracle_odd_batch(mode):
-    """B=3 (not a tile multiple), distinct z_id per crop, z_id given as [B,1,512], fp16 boundary tensors."""
+    """B=3 (not a tile multiple), distinct z_id per crop, z_id given as [B,1,512]."""
     bb, nb, B = "unet", 2, 3
     sd = W.perturb_(W.init_state_dict(W.aei_spec(bb, nb, 512), seed=5), seed=6)
     Xt, z = synth.crops_pm1(B, seed=21), synth.z_ids(B, seed=21)
     Yr, ar = aei_ref.aei_forward(sd, Xt, z, bb, nb)
-    dt = torch.float16 if mode == "bf16" else torch.float32
+    dt = DT[mode]
     G = build(bb, nb, sd, dt)
     Y, attrs = G(Xt.cuda().to(dt), z.cuda().to(dt).reshape(B, 1, 512))
     d = (Y.float().cpu() - Yr).abs()
-    if mode == "bf16":
-        Ye, _ = aei_emul.aei_forward_emul(sd, Xt.half().float(), z.half().float(), bb, nb)
+    if mode == "fp16":
+        assert d.max().item() <= F16_MAX and d.mean().item() <= F16_MEAN, (d.max().item(), d.mean().item())
+    elif mode == "bf16":
+        Ye, _ = aei_emul.aei_forward_emul(sd, Xt.bfloat16().float(), z.bfloat16().float(), bb, nb)
         de = (Ye - Yr).abs()
         assert d.mean().item() <= 1.3 * de.mean().item() + 2e-4, (d.mean().item(), de.mean().item())
     else:   # perturbed weights: same noise-floor argument as the unet2_perturbed golden case
         assert d.max().item() <= 5 * FP32_NOISE["aei_unet2_perturbed"] and d.mean().item() <= 2e-5, (d.max().item(),
                                                                                                    d.mean().item())
     for a, r in zip(attrs, ar):
-        tol = (3e-2 if mode == "bf16" else 2e-4) * max(1.0, r.abs().max().item())
+        tol = {"bf16": 3e-2, "fp16": 4e-3, "fp32": 2e-4}[mode] * max(1.0, r.abs().max().item())
         assert (a.float().cpu() - r).abs().max().item() <= tol
     # per-sample independence: crop 1 alone gives the same result as inside the batch
     # (tile shapes differ with the batch size, so accumulation order - not the function - may differ)
     Y1, _ = G(Xt[1:2].cuda().to(dt), z[1:2].cuda().to(dt))
     d1 = (Y1.float() - Y[1:2].float()).abs()
-    assert d1.mean().item() <= (3e-3 if mode == "bf16" else 1e-6) and d1.max().item() <= (1.0 if mode == "bf16" else 2e-5)
+    assert d1.mean().item() <= {"bf16": 3e-3, "fp16": 4e-4, "fp32": 1e-6}[mode]
+    assert d1.max().item() <= {"bf16": 1.0, "fp16": 1e-2, "fp32": 2e-5}[mode]
 
 
 def test_blocks_match_bf16_emulation():

@@ -34,12 +34,25 @@ def test_faceshifter_batch_and_fused_swap():
                                 bb, nb)
     ref = aei_ref.postprocess_ref(Yr)
     d = np.abs(out.astype(int) - ref.astype(int))
-    # bf16 storage moves Y by ~1e-2 mean-abs with these (perturbed) weights = ~1.3 grey levels (tests/test_aei_gpu.py)
-    assert d.mean() <= 3.0 and np.percentile(d, 90) <= 8, (d.max(), d.mean())
+    # G.half() is the fp16 tensor-core mode (the reference's own deployment dtype): Y within 1e-2 / 1e-3 of the fp32
+    # forward = at most ~1.3 grey levels, ~0.13 on average, plus the fp16 evaluation of the uint8 conversion
+    print("faceshifter_batch vs fp32 oracle: mean %.3f max %d grey levels" % (d.mean(), d.max()))
+    assert d.mean() <= 0.5 and np.percentile(d, 99) <= 2 and d.max() <= 3, (d.max(), d.mean())
+    # the uint8 conversion itself, bit-exact against the reference's fp16 arithmetic on the same Y
+    G.return_attr = False
+    Y, _ = G(target, z.cuda().half().repeat(B, 1))
+    assert Y.dtype == torch.float16
+    assert np.array_equal(out, aei_ref.postprocess_ref_half(Y.cpu()))
+    # fused path: same rounding order as transform_target_to_torch(half=True) + faceshifter_batch -> identical bytes
     fused = G.swap_u8(torch.from_numpy(u8).cuda(), z.cuda().half()).cpu().numpy()
-    d2 = np.abs(fused.astype(int) - out.astype(int))
-    # same network, inputs rounded through fp16 (reference order) vs once to bf16: small, not bit-identical
-    assert d2.mean() <= 2.0 and (d2 <= 2).mean() > 0.8, (d2.mean(), (d2 <= 2).mean())
+    assert np.array_equal(fused, out)
+    # bf16 storage (outside north_star, documented): ~1e-2 mean-abs on Y with these perturbed weights
+    Gb = ghost_b200.AEI_Net(bb, nb, 512).eval()
+    Gb.load_state_dict(sd)
+    Gb = Gb.cuda().bfloat16()
+    fb = Gb.swap_u8(torch.from_numpy(u8).cuda(), z.cuda().bfloat16()).cpu().numpy()
+    db = np.abs(fb.astype(int) - ref.astype(int))
+    assert db.mean() <= 3.0 and np.percentile(db, 90) <= 8, (db.max(), db.mean())
 
 
 def test_state_dict_round_trip_and_errors():

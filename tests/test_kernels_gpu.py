@@ -9,7 +9,7 @@ import torch
 import torch.nn.functional as F
 
 from ghost_b200 import _lib
-from util import bf16_round, fptr, nhwc, run_conv
+from util import fptr, nhwc, round16, run_conv, torch_dtype
 
 pytestmark = pytest.mark.gpu
 
@@ -65,7 +65,7 @@ def torch_conv(x, w, b, kind, k, stride, pad, act, slope):
     return y
 
 
-@pytest.mark.parametrize("mode", [_lib.BF16, _lib.F32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("mode", [_lib.F16, _lib.BF16, _lib.F32], ids=["fp16", "bf16", "fp32"])
 @pytest.mark.parametrize("case", CONV_CASES, ids=[c[0] for c in CONV_CASES])
 def test_conv(case, mode):
     name, N, Cin, H, W, Cout, kind, k, stride, pad, act = case
@@ -76,15 +76,14 @@ def test_conv(case, mode):
     wshape = (Cout, Cin, k, k) if kind == 0 else (Cin, Cout, 4, 4)
     w = (torch.randn(wshape, generator=g) / (Cin * k * k / (4 if kind else 1)) ** 0.5).cuda()
     b = (torch.randn(Cout, generator=g) * 0.1).cuda()
-    if mode == _lib.BF16:
-        x, w = bf16_round(x), bf16_round(w)
+    x, w = round16(x, mode), round16(w, mode)
     y = run_conv(x, w, b, kind, k, stride, pad, act, 0.1, mode)
     ref = torch_conv(x.double(), w.double(), b.double(), kind, k, stride, pad, act, 0.1).float()
     assert y.shape == ref.shape
     assert torch.isfinite(y).all(), "output has NaN/Inf (unwritten pixels?)"
     err = (y - ref).abs().max().item()
     scale = ref.abs().max().item()
-    tol = (2e-5 if mode == _lib.F32 else 6e-3) * max(scale, 1.0)
+    tol = {_lib.F32: 2e-5, _lib.BF16: 6e-3, _lib.F16: 8e-4}[mode] * max(scale, 1.0)
     assert err <= tol, "%s: max err %.3e (scale %.3f)" % (name, err, scale)
 
 
@@ -104,13 +103,13 @@ def torch_aad(h, za, zid, p):
     return F.relu((1 - M) * (ga * hn + ba) + M * (gi * hn + bi))
 
 
-@pytest.mark.parametrize("mode", [_lib.BF16, _lib.F32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("mode", [_lib.F16, _lib.BF16, _lib.F32], ids=["fp16", "bf16", "fp32"])
 @pytest.mark.parametrize("case", AAD_CASES, ids=["n%d_hw%d_cx%d_ca%d" % c for c in AAD_CASES])
 def test_aad_layer(case, mode):
     N, H, c_x, c_attr = case
     c_id = 512
     g = torch.Generator().manual_seed(c_x * 7 + H)
-    dt = torch.float32 if mode == _lib.F32 else torch.bfloat16
+    dt = torch_dtype(mode)
     h = (torch.randn(N, c_x, H, H, generator=g) * 1.5 + 0.3).cuda()
     za = torch.randn(N, c_attr, H, H, generator=g).cuda()
     zid = torch.randn(N, c_id, generator=g)
@@ -121,9 +120,8 @@ def test_aad_layer(case, mode):
         "f2w": torch.randn(c_x, c_id, generator=g) * 0.04, "f2b": torch.randn(c_x, generator=g) * 0.1,
         "chw": torch.randn(1, c_x, 1, 1, generator=g) / c_x ** 0.5, "chb": torch.randn(1, generator=g) * 0.1,
     }
-    if mode == _lib.BF16:
-        h, za = bf16_round(h), bf16_round(za)
-        p["c1w"], p["c2w"] = bf16_round(p["c1w"]), bf16_round(p["c2w"])
+    h, za = round16(h, mode), round16(za, mode)
+    p["c1w"], p["c2w"] = round16(p["c1w"], mode), round16(p["c2w"], mode)
     hn, zan = nhwc(h, dt), nhwc(za, dt)
     out = torch.full((N, H, H, c_x), float("nan"), dtype=dt, device="cuda")
     hp = {k: np.ascontiguousarray(v.numpy().astype(np.float32)) for k, v in p.items()}
@@ -140,19 +138,18 @@ def test_aad_layer(case, mode):
     assert torch.isfinite(got).all()
     err = (got - ref).abs().max().item()
     scale = ref.abs().max().item()
-    tol = (5e-5 if mode == _lib.F32 else 1.2e-2) * max(scale, 1.0)
+    tol = {_lib.F32: 5e-5, _lib.BF16: 1.2e-2, _lib.F16: 1.6e-3}[mode] * max(scale, 1.0)
     assert err <= tol, "max err %.3e (scale %.3f)" % (err, scale)
 
 
-@pytest.mark.parametrize("mode", [_lib.BF16, _lib.F32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("mode", [_lib.F16, _lib.BF16, _lib.F32], ids=["fp16", "bf16", "fp32"])
 @pytest.mark.parametrize("shape", [(2, 1024, 2, 2), (1, 64, 128, 128), (3, 128, 7, 5)], ids=str)
 def test_upsample2x(shape, mode):
     N, Cc, H, W = shape
-    dt = torch.float32 if mode == _lib.F32 else torch.bfloat16
+    dt = torch_dtype(mode)
     g = torch.Generator().manual_seed(3)
     x = torch.randn(N, Cc, H, W, generator=g).cuda()
-    if mode == _lib.BF16:
-        x = bf16_round(x)
+    x = round16(x, mode)
     xn = nhwc(x, dt)
     y = torch.full((N, 2 * H, 2 * W, Cc), float("nan"), dtype=dt, device="cuda")
     lib = _lib.load()
@@ -161,17 +158,17 @@ def test_upsample2x(shape, mode):
     _lib.check(rc, test_api=True)
     ref = F.interpolate(x, scale_factor=2, mode="bilinear", align_corners=True)
     got = y.float().permute(0, 3, 1, 2)
-    tol = 1e-5 if mode == _lib.F32 else 2e-2
+    tol = {_lib.F32: 1e-5, _lib.BF16: 2e-2, _lib.F16: 2.5e-3}[mode]
     assert (got - ref).abs().max().item() <= tol
 
 
-@pytest.mark.parametrize("mode", [_lib.BF16, _lib.F32], ids=["bf16", "fp32"])
+@pytest.mark.parametrize("mode", [_lib.F16, _lib.BF16, _lib.F32], ids=["fp16", "bf16", "fp32"])
 @pytest.mark.parametrize("shape", [(2, 64, 16, 16), (1, 1024, 2, 2), (3, 128, 32, 32), (2, 64, 128, 128)])
 def test_upsample2x_fused_stats(shape, mode):
     """The fused kernel writes the same pixels as the plain upsample and the InstanceNorm statistics of exactly
     those (rounded) pixels."""
     N, Cc, H, W = shape
-    dt = torch.float32 if mode == _lib.F32 else torch.bfloat16
+    dt = torch_dtype(mode)
     g = torch.Generator().manual_seed(11)
     x = (torch.randn(N, Cc, H, W, generator=g) * 2.0 + 0.7).cuda()
     xn = nhwc(x, dt)

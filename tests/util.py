@@ -15,6 +15,19 @@ def bf16_round(t):
     return t.to(torch.bfloat16).to(torch.float32)
 
 
+def f16_round(t):
+    return t.to(torch.float16).to(torch.float32)
+
+
+def round16(t, mode):
+    """t rounded through the 16-bit storage type of a tensor-core mode (unchanged in fp32 mode)"""
+    return bf16_round(t) if mode == _lib.BF16 else f16_round(t) if mode == _lib.F16 else t
+
+
+def torch_dtype(mode):
+    return {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16, _lib.F16: torch.float16}[mode]
+
+
 def fptr(a):
     """host float32 numpy array -> void*"""
     assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
@@ -24,7 +37,7 @@ def fptr(a):
 def run_conv(x_nchw, w, bias, kind, k, stride, pad, act, slope, mode, bn_hint=0):
     """ghost_test_conv on a [N,C,H,W] fp32 cuda tensor; returns the NCHW fp32 result."""
     lib = _lib.load()
-    dt = torch.float32 if mode == _lib.F32 else torch.bfloat16
+    dt = torch_dtype(mode)
     N, Cin, H, W = x_nchw.shape
     x = nhwc(x_nchw, dt)
     wh = np.ascontiguousarray(w.detach().cpu().numpy().astype(np.float32))
