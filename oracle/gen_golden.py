@@ -37,6 +37,8 @@ AEI_CASES = [  # name, backbone, num_blocks, perturbed, batch
     ("aei_unet2_perturbed", "unet", 2, True, 2),
     ("aei_linknet3_perturbed", "linknet", 3, True, 1),
     ("aei_unet1_perturbed", "unet", 1, True, 1),
+    ("aei_linknet3_default", "linknet", 3, False, 1),
+    ("aei_unet1_default", "unet", 1, False, 2),
 ]
 
 
@@ -47,9 +49,11 @@ def aei_case_inputs(name, backbone, nb, perturbed, B):
     return sd, synth.crops_pm1(B, seed=7), synth.z_ids(B, seed=7)
 
 
-def gen_aei():
+def gen_aei(only_missing=True):
     from network.AEI_Net import AEI_Net
     for name, bb, nb, pert, B in AEI_CASES:
+        if only_missing and os.path.exists(os.path.join(GOLD, name + ".npz")):
+            continue   # recorded in an earlier round: left byte-identical
         sd, Xt, z = aei_case_inputs(name, bb, nb, pert, B)
         G = AEI_Net(bb, nb, 512).eval()
         G.load_state_dict(sd)
@@ -63,6 +67,26 @@ def gen_aei():
             out["attr%d_shape" % (k + 1)] = np.array(a.shape)
         np.savez_compressed(os.path.join(GOLD, name + ".npz"), **out)
         print(name, "Y mean|.|", float(np.abs(out["Y"]).mean()))
+
+
+def gen_aei_half():
+    """The reference as it is DEPLOYED (inference.py:26-30: G.eval() ... .half()): the unmodified module in fp16 on
+    the same inputs and weights, and how far its Y lies from its own fp32 forward.  That distance is the yardstick
+    for the 16-bit tensor-core modes on the ill-conditioned ("perturbed") weight sets, where no 16-bit operand
+    format can hold 1e-2 (tools/sens16.py): tests/golden/aei_half_ref.npz = per case [max-abs, mean-abs]."""
+    from network.AEI_Net import AEI_Net
+    out = {}
+    for name, bb, nb, pert, B in AEI_CASES:
+        sd, Xt, z = aei_case_inputs(name, bb, nb, pert, B)
+        G = AEI_Net(bb, nb, 512).eval()
+        G.load_state_dict(sd)
+        with torch.no_grad():
+            Y32, _ = G(Xt, z)
+            Y16, _ = G.half()(Xt.half(), z.half())
+        d = (Y16.float() - Y32).abs()
+        out[name] = np.array([d.max().item(), d.mean().item()], dtype=np.float64)
+        print(name, "reference .half() vs its fp32 forward: max %.3e mean %.3e" % (out[name][0], out[name][1]))
+    np.savez_compressed(os.path.join(GOLD, "aei_half_ref.npz"), **out)
 
 
 class FakeHandler(object):
@@ -181,5 +205,6 @@ if __name__ == "__main__":
         gen_sr()
     if "aei" in which:
         gen_aei()
+        gen_aei_half()
     if "paste" in which:
         gen_paste()

@@ -66,3 +66,30 @@ def test_pre_post_conversions():
     y = aei_ref.postprocess_ref(x.float())
     assert y.dtype == np.uint8 and y.shape == (2, 256, 256, 3)
     assert np.abs(y.astype(int) - u8.astype(int)).max() <= 1      # truncation after the fp16 round trip
+
+
+def test_half_yardstick_matches_live_reference(have_reference, golden_dir):
+    """tests/golden/aei_half_ref.npz (how far the reference's own G.half() forward lies from its fp32 forward) is
+    recomputed from the unmodified module where /root/reference is mounted; everywhere: it covers every case."""
+    rec = np.load(os.path.join(golden_dir, "aei_half_ref.npz"))
+    assert sorted(rec.files) == sorted(c[0] for c in AEI_CASES)
+    if not have_reference:
+        pytest.skip("/root/reference is not mounted on this box (the recorded file covers it)")
+    sys.path.insert(0, "/root/reference")
+    try:
+        from network.AEI_Net import AEI_Net
+    finally:
+        sys.path.remove("/root/reference")
+    name, bb, nb, pert, B = AEI_CASES[0]
+    sd, Xt, z = aei_case_inputs(*AEI_CASES[0])
+    G = AEI_Net(bb, nb, 512).eval()
+    G.load_state_dict(sd)
+    with torch.no_grad():
+        Y32, _ = G(Xt, z)
+        Y16, _ = G.half()(Xt.half(), z.half())
+    d = (Y16.float() - Y32).abs()
+    assert abs(d.max().item() - rec[name][0]) <= 0.05 * rec[name][0] + 1e-4
+    assert abs(d.mean().item() - rec[name][1]) <= 0.05 * rec[name][1] + 1e-6
+    # the fp16 evaluation of the uint8 conversion (faceshifter_run.py:20-22 with a half Y) against the restatement
+    ref_u8 = ((Y16.permute(0, 2, 3, 1) * 0.5 + 0.5) * 255)[:, :, :, [2, 1, 0]].type(torch.uint8).numpy()
+    assert np.array_equal(aei_ref.postprocess_ref_half(Y16), ref_u8)
