@@ -476,6 +476,8 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
              face i, faces of one frame compose in list order; face_crop / face_mask default to arange.
     mode   : "exact" = get_final_image arithmetic (bit-exact), "float" = get_final_video arithmetic.
     Returns the composited frames as a device tensor [F,H,W,3] uint8."""
+    if mode not in ("exact", "float"):
+        raise ValueError("mode must be 'exact' or 'float'")
     if not torch.cuda.is_available():
         raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
     dev = frames.device if isinstance(frames, torch.Tensor) and frames.is_cuda else torch.device(
@@ -524,8 +526,6 @@ def paste_back(frames, crops, masks, tfms, face_frame, face_crop=None, face_mask
     d.face_crop = fc.ctypes.data_as(C.POINTER(C.c_int))
     d.face_mask = fm.ctypes.data_as(C.POINTER(C.c_int))
     d.mode = _lib.PASTE_EXACT if mode == "exact" else _lib.PASTE_FLOAT
-    if mode not in ("exact", "float"):
-        raise ValueError("mode must be 'exact' or 'float'")
     lib = _lib.load()
     with torch.cuda.device(dev):
         _lib.check(lib.ghost_paste_back(C.byref(d), _stream()))
@@ -589,14 +589,20 @@ def match_identities(face_embeds, target_embeds, similarity_th):
     return idx.cpu().numpy().astype(np.int64), ok.cpu().numpy().astype(bool), sim.cpu().numpy()
 
 
-def embed_and_swap(G, arc, sources_rgb224, crops_bgr, side=None, event=None, out=None, write_u8=True):
+def embed_and_swap(G, arc, sources_rgb224, crops_bgr, side=None, event=None, out=None, write_u8=True,
+                   face_source=None):
     """z_id = netArc(sources) and the swap of `crops_bgr` with it (core.py:44-45 + faceshifter_batch), with the two
     independent halves overlapped: the attribute encoder of G runs on the stream `side` while the ArcFace network runs
     on the current stream; the AAD generator follows on the current stream.  Same results as
-    `G.swap_u8(crops, arc.embed_hwc(sources))`; side=None runs exactly that."""
+    `G.swap_u8(crops, arc.embed_hwc(sources))`; side=None runs exactly that.
+    face_source (int64 device tensor [B], optional): crop i is swapped with the identity of source face_source[i] -
+    the reference embeds every source once (core.py:52-54) and reuses it for all the crops of its target."""
     zdt = torch.bfloat16 if G.dtype == torch.bfloat16 else (torch.float16 if G.dtype == torch.float16 else torch.float32)
     if side is None:
-        return G.swap_u8(crops_bgr, arc.embed_hwc(sources_rgb224, out_dtype=zdt), out=out, write_u8=write_u8)
+        z = arc.embed_hwc(sources_rgb224, out_dtype=zdt)
+        if face_source is not None:
+            z = z.index_select(0, face_source)
+        return G.swap_u8(crops_bgr, z, out=out, write_u8=write_u8)
     main = torch.cuda.current_stream(crops_bgr.device)
     side.wait_stream(main)                       # inputs ready, previous users of the plan's buffers done
     with torch.cuda.stream(side):
@@ -604,6 +610,8 @@ def embed_and_swap(G, arc, sources_rgb224, crops_bgr, side=None, event=None, out
         event = event or torch.cuda.Event()
         event.record(side)
     z = arc.embed_hwc(sources_rgb224, out_dtype=zdt)
+    if face_source is not None:
+        z = z.index_select(0, face_source)
     main.wait_event(event)
     return G.generate_u8(z, crops_bgr.shape[0], out=out, write_u8=write_u8)
 
@@ -651,10 +659,14 @@ class SwapPipeline(object):
     the --use_sr pass (face_enhancement, batches of sr_batch crops) between the swap and the paste-back."""
 
     def __init__(self, G, arc, batch, frame_hw, depth=2, mode="exact", mask_dtype=torch.float64, device=None,
-                 boxes_only=False, sr=None, sr_batch=20):
+                 boxes_only=False, sr=None, sr_batch=20, n_frames=None, n_sources=None):
         if not torch.cuda.is_available():
             raise RuntimeError("ghost_b200 needs a CUDA device (no CPU fallback)")
         self.G, self.arc, self.B, self.mode, self.depth = G, arc, int(batch), mode, int(depth)
+        # several faces per frame / several crops per source (BASELINE configs[3]): n_frames frames and n_sources
+        # source images per batch of `batch` crops; submit() then takes face_frame / face_source index lists
+        self.F = int(batch if n_frames is None else n_frames)
+        self.S = int(batch if n_sources is None else n_sources)
         # boxes_only: the frames stay in the caller's pinned host buffer and are composited IN PLACE - only the face
         # boxes cross PCIe (up, composited on the device, down into the same host frames); `out` must be `frames`
         self.boxes_only = bool(boxes_only)
@@ -663,6 +675,11 @@ class SwapPipeline(object):
         # sr: the --use_sr pass (face_enhancement, batches of sr_batch crops like the reference's DataLoader) between the
         # swap and the paste-back
         self.sr, self.sr_batch = sr, int(sr_batch)
+        if sr is not None and self.B % self.sr_batch:
+            # the SR generator runs on batch statistics (inference.py:48), so the batch boundaries are part of the
+            # result: the reference batches 20 continuously over a target's frame list (video_processing.py:263-285)
+            raise ValueError("SwapPipeline(sr=...): batch (%d) must be a multiple of sr_batch (%d) so that the SR "
+                             "batches fall where face_enhancement puts them" % (self.B, self.sr_batch))
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         H, W = frame_hw
         if sr is not None:
@@ -672,8 +689,8 @@ class SwapPipeline(object):
         self.slots = []
         for _ in range(self.depth):
             self.slots.append({
-                "src": torch.empty((self.B, 224, 224, 3), **u8), "crp": torch.empty((self.B, 256, 256, 3), **u8),
-                "frm": torch.empty((self.B, H, W, 3), **u8), "out": torch.empty((self.B, H, W, 3), **u8),
+                "src": torch.empty((self.S, 224, 224, 3), **u8), "crp": torch.empty((self.B, 256, 256, 3), **u8),
+                "frm": torch.empty((self.F, H, W, 3), **u8), "out": torch.empty((self.F, H, W, 3), **u8),
                 "msk": torch.empty((self.B, 224, 224), dtype=mask_dtype, device=self.dev),
                 "ev_in": torch.cuda.Event(), "ev_frm": torch.cuda.Event(), "ev_done": torch.cuda.Event(), "ev_out": torch.cuda.Event(), "used": False})
         self.s_in = torch.cuda.Stream(device=self.dev)
@@ -682,10 +699,11 @@ class SwapPipeline(object):
         self.ev_enc = torch.cuda.Event()
         self.i = 0
 
-    def submit(self, sources, crops, frames, masks, tfms, face_frame, out):
-        """sources uint8 RGB [B,224,224,3], crops uint8 BGR [B,256,256,3], frames uint8 BGR [B,H,W,3], masks
+    def submit(self, sources, crops, frames, masks, tfms, face_frame, out, face_source=None):
+        """sources uint8 RGB [S,224,224,3], crops uint8 BGR [B,256,256,3], frames uint8 BGR [F,H,W,3], masks
         [B,224,224]: pinned host tensors of one batch; tfms / face_frame as in paste_back (one face per entry);
-        out: pinned host tensor [B,H,W,3] that receives the composited frames (valid after flush())."""
+        face_source: int64 device tensor [B] (source of each crop) when S != B;
+        out: pinned host tensor [F,H,W,3] that receives the composited frames (valid after flush())."""
         slot = self.slots[self.i % self.depth]
         self.i += 1
         main = torch.cuda.current_stream(self.dev)
@@ -712,12 +730,13 @@ class SwapPipeline(object):
             self.h2d_bytes = (nb + sources.numel() + crops.numel() + masks.numel() * masks.element_size())
         main.wait_event(slot["ev_in"])
         if self.sr is None:
-            embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False)
+            embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc, write_u8=False,
+                           face_source=face_source)
             yptr, ydt = self.G.y_nhwc(self.B, self.dev)
             swap_arg = (yptr, ydt, self.B)
         else:
             embed_and_swap(self.G, self.arc, slot["src"], slot["crp"], side=self.s_enc, event=self.ev_enc,
-                           out=self.swapped, write_u8=True)
+                           out=self.swapped, write_u8=True, face_source=face_source)
             for b0 in range(0, self.B, self.sr_batch):
                 self.sr.enhance_u8(self.swapped[b0:b0 + self.sr_batch], out=self.enhanced[b0:b0 + self.sr_batch])
             swap_arg = self.enhanced

@@ -51,24 +51,61 @@ class FrameSharder(object):
         Ranks may own different counts; each sends exactly its own frames."""
         if self.world == 1:
             return local_frames
+        self.gather_async(local_frames, dst)
+        return self.wait()
+
+    def gather_async(self, local_frames, dst=0):
+        """Start the gather of one step's finished frames and return at once: the transfer is ordered after the work
+        already queued on the current stream and runs beside whatever is queued next (NCCL's own stream on the GPUs),
+        so step k's frames travel while step k+1 computes.  At most two gathers are in flight: starting gather k+1
+        first orders the current stream after gather k-1, so the caller may reuse a `local_frames` buffer two steps
+        later (double-buffer it), and rank `dst` alternates between two frame-ordered receive buffers.
+        wait() returns the most recently started gather's result."""
+        if self.world == 1:
+            self._last = local_frames
+            return
         if local_frames.shape[0] != self.local_count:
             raise ValueError("expected %d local frames, got %d" % (self.local_count, local_frames.shape[0]))
+        pending = getattr(self, "_pending", [])
+        while len(pending) > 1:              # keep one older gather in flight, retire the rest
+            self._retire(pending.pop(0))
         tail = tuple(local_frames.shape[1:])
+        works, out = [], None
         if self.rank == dst:
-            out = torch.empty((self.n_frames,) + tail, dtype=local_frames.dtype, device=local_frames.device)
-            reqs = []
+            bufs = getattr(self, "_bufs", None)
+            if bufs is None or bufs[0].shape[1:] != tail or bufs[0].dtype != local_frames.dtype:
+                bufs = self._bufs = [torch.empty((self.n_frames,) + tail, dtype=local_frames.dtype,
+                                                 device=local_frames.device) for _ in range(2)]
+                self._turn = 0
+            out = bufs[self._turn % 2]
+            self._turn += 1
+            ops = []
             for r in range(self.world):
                 lo, hi = shard_range(self.n_frames, r, self.world)
                 if r == dst:
                     out[lo:hi].copy_(local_frames)
                 elif hi > lo:
-                    reqs.append(dist.irecv(out[lo:hi], src=r, group=self.group))
-            for q in reqs:
-                q.wait()
-            return out
-        if self.local_count > 0:
-            dist.send(local_frames.contiguous(), dst=dst, group=self.group)
-        return None
+                    ops.append(dist.P2POp(dist.irecv, out[lo:hi], r, self.group))
+            if ops:
+                works = dist.batch_isend_irecv(ops)      # one grouped launch for all the peers
+        elif self.local_count > 0:
+            works = [dist.isend(local_frames.contiguous(), dst=dst, group=self.group)]
+        pending.append((works, out))
+        self._pending = pending
+
+    def _retire(self, item):
+        works, out = item
+        for w in works:
+            w.wait()        # CUDA: the current stream waits for the transfer; gloo: the host does
+        self._last = out
+
+    def wait(self):
+        """Order the current stream (gloo: the host) after every gather started so far; returns the last one's
+        frame-ordered tensor on the destination rank, None elsewhere."""
+        pending = getattr(self, "_pending", [])
+        while pending:
+            self._retire(pending.pop(0))
+        return getattr(self, "_last", None)
 
 
 def bind_to_gpu_numa(device_index):

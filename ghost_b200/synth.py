@@ -62,7 +62,7 @@ def frame_u8(H, W, seed=0, cell=16):
     return np.ascontiguousarray(np.clip(np.rint(img), 0, 255).astype(np.uint8))
 
 
-def similarity_tfm(H, W, rng, clipped=False, scale=None):
+def similarity_tfm(H, W, rng, clipped=False, scale=None, center=None):
     """2x3 float64 frame->224-crop affine: crop = s*R(theta)*frame + t.  The inverse-mapped 224^2 square lies
     inside the frame, except with clipped=True where its centre sits near the frame border."""
     s_hi = 0.6
@@ -70,7 +70,9 @@ def similarity_tfm(H, W, rng, clipped=False, scale=None):
     s = float(rng.uniform(min(s_lo, s_hi), s_hi)) if scale is None else float(scale)
     th = math.radians(float(rng.uniform(-20.0, 20.0)))
     half = 112.0 * math.sqrt(2.0) / s + 2.0   # half-diagonal of the square in frame pixels
-    if clipped:
+    if center is not None:
+        cx, cy = float(center[0]), float(center[1])
+    elif clipped:
         cx = float(rng.choice([half * 0.3, W - half * 0.3]))
         cy = float(rng.uniform(half * 0.3, H - half * 0.3))
     else:

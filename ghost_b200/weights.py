@@ -169,6 +169,17 @@ def perturb_(sd, seed=1):
     return sd
 
 
+def unit_embedding_(arc_sd, pre_bn_std=281.0):
+    """Synthetic stand-in for what training gives the ArcFace head: with random-init convs the pre-BN embedding of
+    iresnet100 has a per-dimension std of ~280 (|z_id| ~ 6000), while a trained network's `features` BatchNorm1d
+    leaves z_id ~ N(0,1) per dimension (|z_id| ~ 22, what synth.z_ids models and what the generator's id branch is
+    scaled for).  Sets `features.running_var` so that the random-init network does the same.  Used by bench.py and
+    the bench-shape tests; a z_id of magnitude 6000 drives every AAD layer into saturation, where no 16-bit
+    arithmetic (the reference's own G.half() included) tracks the fp32 forward."""
+    arc_sd["features.running_var"] = torch.full_like(arc_sd["features.running_var"], float(pre_bn_std) ** 2)
+    return arc_sd
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # pix2pix super-resolution generator: LIPSPADEGenerator with TestOptions (models/config_sr.py:3-29: ngf=48,
 # norm_G='spectralspadesyncbatch3x3', num_upsampling_layers='normal', semantic_nc=3).  Key names follow

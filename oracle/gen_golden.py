@@ -198,9 +198,60 @@ def gen_sr():
         print(name, "Y mean|.|", float(out["Y_absmean"]))
 
 
+def align_case_tracks(seed=0, n_frames=40):
+    """Synthetic 5-point landmark tracks (float32 [5,2] per frame, as the detector returns them) for two targets:
+    smooth drift + jitter, a scene cut (a jump of ~40 px) at frame 17, a slow pan that crosses the 5 px threshold on
+    the nose only at frame 30, missing detections (empty lists) at frames 9 and 25-26 of target 1, and a
+    one-frame run between two cuts."""
+    rng = np.random.default_rng(seed)
+    base = np.array([[80, 100], [150, 98], [116, 140], [88, 175], [144, 173]], np.float32)
+    tracks = []
+    for q in range(2):
+        tr = []
+        off = np.array([300.0 + 500 * q, 200.0 + 100 * q])
+        for i in range(n_frames):
+            off = off + rng.uniform(-1.5, 1.5, 2)
+            if i == 17:
+                off = off + np.array([40.0, -25.0])
+            if i == 21 and q == 0:
+                off = off + np.array([9.0, 0.0])
+            if i == 22 and q == 0:
+                off = off - np.array([9.0, 0.0])
+            k = (base * (1.0 + 0.2 * q) + off + rng.uniform(-0.7, 0.7, (5, 2))).astype(np.float32)
+            if i == 30:
+                k[2] += np.float32(6.0)
+            tr.append(k)
+        tracks.append(tr)
+    for i in (9, 25, 26):
+        tracks[1][i] = []
+    return tracks
+
+
+def gen_align():
+    """smooth_landmarks of the unmodified reference (utils/inference/video_processing.py:86-108) on the tracks above."""
+    for m in ("matplotlib", "matplotlib.pyplot", "insightface", "insightface.utils", "insightface.utils.face_align",
+              "kornia", "kornia.geometry", "kornia.geometry.transform"):
+        sys.modules.setdefault(m, types.ModuleType(m))
+    sys.modules["insightface"].utils = sys.modules["insightface.utils"]
+    sys.modules["insightface.utils"].face_align = sys.modules["insightface.utils.face_align"]
+    from utils.inference.video_processing import smooth_landmarks
+    tracks = align_case_tracks()
+    out = smooth_landmarks(tracks, n=2)
+    rec = {}
+    for q, row in enumerate(out):
+        present = np.array([len(k) != 0 for k in row])
+        rec["present%d" % q] = present
+        rec["smooth%d" % q] = np.stack([np.asarray(k) for k in row if len(k) != 0])
+        rec["dtype%d" % q] = np.array(str(np.asarray([k for k in row if len(k) != 0][0]).dtype))
+    np.savez_compressed(os.path.join(GOLD, "align_smooth.npz"), **rec)
+    print("align_smooth", {k: v.shape for k, v in rec.items()})
+
+
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["aei", "paste", "sr"]
+    which = sys.argv[1:] or ["aei", "paste", "sr", "align"]
+    if "align" in which:
+        gen_align()
     if "sr" in which:
         gen_sr()
     if "aei" in which:

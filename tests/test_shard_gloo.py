@@ -33,6 +33,16 @@ def _worker(rank, world, port, n_frames, q):
             q.put(bool(ok))
         else:
             assert out is None
+        # pipelined form: three steps in flight two deep, every step's frames arrive in order and intact
+        for step in range(3):
+            loc = (local.to(torch.int32) + step).to(torch.uint8) if sh.local_count else local
+            sh.gather_async(loc, dst=0)     # the caller computes step + 1 while this travels
+        last = sh.wait()
+        if rank == 0:
+            ok2 = all(int(last[i, 0, 0, 0]) == (i % 251 + 2) % 256 for i in range(n_frames))
+            q.put(bool(ok2))
+        else:
+            assert last is None
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -49,6 +59,7 @@ def test_gather_in_frame_order_world2(n_frames):
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
+    assert q.get(timeout=5) is True
     assert q.get(timeout=5) is True
 
 

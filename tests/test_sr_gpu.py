@@ -26,13 +26,13 @@ def build(sd, dtype):
     return G.to(dtype).cuda()
 
 
-@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+@pytest.mark.parametrize("mode", ["fp32", "bf16", "fp16"])
 @pytest.mark.parametrize("case", SR_CASES, ids=[c[0] for c in SR_CASES])
 def test_forward_matches_reference_golden(case, mode, golden_dir):
     name, B, pert, calls = case
     gold = np.load(os.path.join(golden_dir, name + ".npz"))
     sd, crops = sr_case_inputs(name, B, pert)
-    dt = torch.bfloat16 if mode == "bf16" else torch.float32
+    dt = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}[mode]
     G = build(sd, dt)
     x = sr_ref.preprocess_ref(crops).cuda()
     for _ in range(calls):
@@ -50,7 +50,10 @@ def test_forward_matches_reference_golden(case, mode, golden_dir):
         sdn = G.state_dict()
         assert np.abs(sdn["head_0.conv_0.weight_u"].numpy() - gold["u_head0_conv0"]).max() <= 1e-5
         assert np.abs(sdn["ups.3.conv_s.weight_u"].numpy() - gold["u_ups3_convs"]).max() <= 1e-5
-    else:
+    elif mode == "fp16":    # fp16 storage on the tcgen05 path: north_star's bound (1e-2 / 1e-3) as written
+        assert np.isfinite(yc).all()
+        assert d.max() <= 1e-2 and d.mean() <= 1e-3
+    else:                   # bf16 storage: outside north_star's bound, documented
         assert d.max() <= 8e-2 and d.mean() <= 6e-3
 
 
