@@ -18,6 +18,7 @@ F32, BF16, F16, U8 = 0, 1, 2, 3
 # ghost_paste_mode / ghost_crop_kind
 PASTE_EXACT, PASTE_FLOAT = 0, 1
 CROP_U8_BGR, CROP_Y_BF16, CROP_Y_F32, CROP_Y_F16 = 0, 1, 2, 3
+CROP_NOALLOC_MAX_FACES = 32   # GHOST_CROP_NOALLOC_MAX_FACES
 
 
 class GhostError(RuntimeError):
@@ -77,6 +78,7 @@ SIGNATURES = {
     "ghost_copy_boxes": (_i, [_vp, _vp, _i, _i, _i, C.POINTER(_i), C.POINTER(_i), _i, _i, _vp]),
     "ghost_match_identities": (_i, [_vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp, _vp]),
     "ghost_crop_faces": (_i, [_vp, _i, _i, _i, C.POINTER(_d), C.POINTER(_i), _i, _vp, _vp, _vp]),
+    "ghost_crop_faces_noalloc": (_i, [_vp, _i, _i, _i, C.POINTER(_d), C.POINTER(_i), _i, _vp, _vp, _vp]),
     "ghost_face_masks": (_i, [_fp, C.POINTER(_i), _i, _vp, _i, _vp]),
     "ghost_test_conv": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _i, _vp]),
     "ghost_test_aad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f,

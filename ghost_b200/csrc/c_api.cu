@@ -12,6 +12,13 @@
 
 using namespace ghost;
 
+namespace {
+thread_local std::string g_last_error;
+}
+namespace ghost {
+void set_last_error(const char* msg) { g_last_error = msg ? msg : ""; }
+}  // namespace ghost
+
 struct ghost_net {
   Net net;
   std::mutex mu;
@@ -19,8 +26,6 @@ struct ghost_net {
 };
 
 namespace {
-
-thread_local std::string g_last_error;
 
 template <typename F>
 int guarded(F&& f) {

@@ -7,6 +7,11 @@
 #include "crop.cuh"
 
 #include <math.h>
+#include <stdio.h>
+
+#include <mutex>
+
+#include "../../include/ghost_b200.h"
 
 namespace ghost {
 
@@ -128,3 +133,115 @@ const char* crop_faces_launch(const uint8_t* frames, int H, int W, const CropFac
 }
 
 }  // namespace ghost
+
+// ------------------------------------------------------------------------------------------------------------------
+// ghost_crop_faces_noalloc: the same two kernels with every byte of scratch (face table, resize tables, the 224x224
+// intermediate when the caller does not want it) in ONE file-scope device array instead of a stream-ordered
+// allocation - for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid
+// it).  No counterpart in the reference.
+//
+// Layout of the array (per GPU that loads the library, held until exit):
+//   [0, 2048)        CropFace[GHOST_CROP_NOALLOC_MAX_FACES]   rewritten by every call
+//   [2048, 6144)     7 x 256 shorts of cv2.resize 224 -> 256   written once per device at set-up
+//   [6144, ...)      MAX_FACES x 224 x 224 x 3 bytes           intermediate crops when crops224 == NULL
+// Nothing in it has to start at zero: every byte a kernel reads was written earlier in the same call (or at set-up).
+// Every call shares it, so calls that overlap on the GPU (different streams, different threads) race.
+namespace {
+
+constexpr int kNaMaxFaces = GHOST_CROP_NOALLOC_MAX_FACES;
+constexpr size_t kNaTablesOff = 2048, kNa224Off = 6144;
+constexpr size_t kNaBytes = kNa224Off + static_cast<size_t>(kNaMaxFaces) * 224 * 224 * 3;
+static_assert(sizeof(ghost::CropFace) * kNaMaxFaces <= kNaTablesOff, "face table overruns its slot");
+static_assert(7 * 256 * sizeof(short) <= kNa224Off - kNaTablesOff, "resize tables overrun their slot");
+
+static __device__ __align__(256) unsigned char g_crop_noalloc_scratch[kNaBytes];
+
+constexpr int kNaMaxDevices = 64;
+unsigned char* g_na_ptr[kNaMaxDevices];   // device address of the array, per device (NOT the host-side symbol)
+std::mutex g_na_mu;
+
+// once per device, with that device current: resolve the device address of the array and write the constant tables
+const char* noalloc_setup(unsigned char** out, char* msg, size_t cap) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    snprintf(msg, cap, "ghost_crop_faces_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+    return msg;
+  }
+  if (dev < 0 || dev >= kNaMaxDevices) {
+    snprintf(msg, cap, "ghost_crop_faces_noalloc: device index %d out of range", dev);
+    return msg;
+  }
+  std::lock_guard<std::mutex> lk(g_na_mu);
+  if (!g_na_ptr[dev]) {
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_crop_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      snprintf(msg, cap, "ghost_crop_faces_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return msg;
+    }
+    short tables[7 * 256];
+    ghost::crop_resize_tables(tables);
+    e = cudaMemcpy(p + kNaTablesOff, tables, sizeof(tables), cudaMemcpyHostToDevice);   // synchronous, 3.5 KB, once
+    if (e != cudaSuccess) {
+      snprintf(msg, cap, "ghost_crop_faces_noalloc: table upload: %s", cudaGetErrorString(e));
+      return msg;
+    }
+    g_na_ptr[dev] = p;
+  }
+  *out = g_na_ptr[dev];
+  return nullptr;
+}
+
+}  // namespace
+
+extern "C" int ghost_crop_faces_noalloc(const uint8_t* frames, int n_frames, int H, int W, const double* tfm,
+                                        const int* face_frame, int n, uint8_t* crops224, uint8_t* crops256,
+                                        void* stream) {
+  char msg[256];
+  if (!(frames && tfm && face_frame && n > 0 && n_frames > 0 && H > 0 && W > 0)) {
+    ghost::set_last_error("ghost_crop_faces_noalloc: bad argument");
+    return GHOST_ERR_INVALID;
+  }
+  if (!(crops224 || crops256)) {
+    ghost::set_last_error("ghost_crop_faces_noalloc: no output buffer");
+    return GHOST_ERR_INVALID;
+  }
+  if (n > kNaMaxFaces) {
+    snprintf(msg, sizeof(msg), "ghost_crop_faces_noalloc: n = %d exceeds the static scratch limit of %d faces per call "
+                               "(split the batch or use ghost_crop_faces)", n, kNaMaxFaces);
+    ghost::set_last_error(msg);
+    return GHOST_ERR_INVALID;
+  }
+  ghost::CropFace faces[kNaMaxFaces];
+  for (int i = 0; i < n; ++i) {
+    if (face_frame[i] < 0 || face_frame[i] >= n_frames) {
+      ghost::set_last_error("ghost_crop_faces_noalloc: face_frame out of range");
+      return GHOST_ERR_INVALID;
+    }
+    ghost::crop_prepare_face(&faces[i], tfm + 6 * i, face_frame[i]);
+  }
+  unsigned char* scratch = nullptr;
+  if (const char* err = noalloc_setup(&scratch, msg, sizeof(msg))) {
+    ghost::set_last_error(err);
+    return GHOST_ERR_CUDA;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  // pageable source: staged by the time the call returns, ordered on `s` behind the previous call's kernels
+  cudaError_t e = cudaMemcpyAsync(scratch, faces, sizeof(ghost::CropFace) * n, cudaMemcpyHostToDevice, s);
+  if (e != cudaSuccess) {
+    snprintf(msg, sizeof(msg), "ghost_crop_faces_noalloc: face table upload: %s", cudaGetErrorString(e));
+    ghost::set_last_error(msg);
+    return GHOST_ERR_CUDA;
+  }
+  uint8_t* c224 = crops224 ? crops224 : scratch + kNa224Off;
+  const char* err = ghost::crop_faces_launch(frames, H, W, reinterpret_cast<const ghost::CropFace*>(scratch), n,
+                                             reinterpret_cast<const short*>(scratch + kNaTablesOff), c224, crops256, s);
+  if (err) {
+    snprintf(msg, sizeof(msg), "ghost_crop_faces_noalloc: %s", err);
+    ghost::set_last_error(msg);
+    return GHOST_ERR_CUDA;
+  }
+  return GHOST_OK;
+}
+

@@ -19,4 +19,8 @@ void crop_resize_tables(short* t);
 const char* crop_faces_launch(const uint8_t* frames, int H, int W, const CropFace* faces_dev, int n,
                               const short* tables_dev, uint8_t* crops224, uint8_t* crops256, cudaStream_t s);
 
+// message returned by ghost_last_error() on the calling thread (defined in c_api.cu); for entry points that live
+// next to their kernels instead of in c_api.cu
+void set_last_error(const char* msg);
+
 }  // namespace ghost

@@ -208,6 +208,21 @@ int ghost_match_identities(const float* face_embeds, int n_faces, const float* t
 int ghost_crop_faces(const uint8_t* frames, int n_frames, int H, int W, const double* tfm, const int* face_frame, int n,
                      uint8_t* crops224, uint8_t* crops256, void* stream);
 
+/* ---- ghost_crop_faces without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same kernels and bit-identical results as ghost_crop_faces, but the scratch (face
+ * table, resize tables, the 224x224 intermediate when crops224 is NULL) lives in one file-scope
+ * `static __device__` array of GHOST_CROP_NOALLOC_MAX_FACES * 150528 + 6144 bytes (~4.6 MiB, held by every GPU that
+ * loads the library until exit) whose device address is resolved once per device with cudaGetSymbolAddress.  The call
+ * performs no cudaMalloc / cudaMallocAsync / cudaFree and no allocating library routine; the caller passes every input
+ * and output buffer.  n > GHOST_CROP_NOALLOC_MAX_FACES -> GHOST_ERR_INVALID with a message naming the limit.
+ * All calls share the array: calls that overlap on the GPU (different streams or threads) race - issue them on one
+ * stream or order them with events.  Nothing in the array needs to start at zero.  The first call on a device does
+ * the set-up (one synchronous 3.5 KB copy): make it before a graph capture begins. */
+#define GHOST_CROP_NOALLOC_MAX_FACES 32
+int ghost_crop_faces_noalloc(const uint8_t* frames, int n_frames, int H, int W, const double* tfm, const int* face_frame,
+                             int n, uint8_t* crops224, uint8_t* crops256, void* stream);
+
 /* ---- blend-mask synthesis (utils/inference/masks.py:39-108 face_mask_static + erode_and_blur, called at
  * image_processing.py:68 and video_processing.py:221-223), bit-exact against the reference's OpenCV calls:
  *   landmarks [n][106][2] float32 (host): the 106-point landmarks of the swapped 224x224 crop, as
