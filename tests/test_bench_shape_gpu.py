@@ -79,7 +79,8 @@ def test_forward_b64_matches_oracle():
     arc = bench.make_arcface(torch.float16)
     zc = arc.embed_hwc(torch.from_numpy(d["sources"]).cuda(), out_dtype=torch.float32).cpu()
     cos = torch.nn.functional.cosine_similarity(zc, z, dim=1)
-    print("ArcFace B=64 fp16 vs fp32 oracle: min cosine %.6f" % cos.min().item())
+    print("ArcFace B=64 fp16 vs fp32 oracle: min cosine %.6f, max |dz| %.3e at |z| ~ %.1f" % (
+        cos.min().item(), (zc - z).abs().max().item(), z.norm(dim=1).mean().item()))
     assert cos.min().item() >= 0.999
 
 
@@ -147,9 +148,22 @@ def test_config5_b60_sr_pipeline_matches_cpu_port():
                                 aei_ref.transform_target_ref(d["crops"][sl], half=False), z, "linknet", 3)
     ref_sw = aei_ref.postprocess_ref(Yr)
     d1 = np.abs(swapped.astype(int) - ref_sw.astype(int))
-    print("config5 (1) swapped crops vs fp32 port: mean %.3f p99.9 %d max %d grey levels" % (
-        d1.mean(), np.percentile(d1, 99.9), d1.max()))
-    assert d1.mean() <= 0.3 and np.percentile(d1, 99.9) <= 3
+    # yardstick: the reference's own deployment of this stage on this GPU - the same torch ops on half tensors
+    # (G.half(), fp32 netArc -> source_embed.half(); inference.py:30, core.py:66).  linknet/3 with random-init
+    # weights (29 AAD layers) is ill-conditioned at isolated pixels: ANY 16-bit rounding flips them (test_aei_gpu.py)
+    with torch.no_grad():
+        sdh = {k: v.cuda().half() for k, v in W.init_state_dict(W.aei_spec("linknet", 3, 512), seed=0).items()
+               if v.dtype.is_floating_point}
+        Xh = aei_ref.transform_target_ref(d["crops"][sl], half=True).cuda()
+        Yh = aei_ref.generate(sdh, aei_ref.encode(sdh, Xh, "linknet"), z.cuda().half(), 3)
+    dh = np.abs(aei_ref.postprocess_ref_half(Yh.cpu()).astype(int) - ref_sw.astype(int))
+    print("config5 (1) swapped crops vs fp32 port: mean %.3f p99.9 %d max %d grey levels | reference G.half() eager: "
+          "mean %.3f p99.9 %d max %d" % (d1.mean(), np.percentile(d1, 99.9), d1.max(), dh.mean(),
+                                         np.percentile(dh, 99.9), dh.max()))
+    # (the reference keeps netArc in fp32; the device ArcFace runs on fp16 storage, and its 2e-3 relative distance
+    # on z_id moves Y more than the generator's own fp16 arithmetic does - tools/z_diag.py - hence the factor 2)
+    assert d1.mean() <= max(0.2, 2.0 * dh.mean())
+    assert np.percentile(d1, 99.9) <= max(2, 2.0 * np.percentile(dh, 99.9) + 1)
     # (2) face_enhancement on the device's swapped crops: three DataLoader batches of 20, spectral-norm state carried
     with torch.no_grad():
         sr_sd = {k: v.float() for k, v in W.init_state_dict(W.sr_spec(), seed=0).items() if v.dtype.is_floating_point}

@@ -237,12 +237,16 @@ def test_swap_pipeline_boxes_only_matches_full_frames():
 def test_swap_pipeline_with_sr_stage_matches_sequential_calls():
     """SwapPipeline(sr=...): swap -> face_enhancement batches -> paste-back inside the streaming loop gives the frames
     of the calls made one after the other (the SR generator is stateful: a twin with the same seed replays them)."""
-    B, H, W = 3, 240, 320
+    B, H, W = 4, 240, 320
     G = ghost_b200.AEI_Net("unet", 1, 512, seed=3).eval().bfloat16().cuda()
     arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
     sr_a = ghost_b200.LIPSPADEGenerator(seed=1).bfloat16().cuda()
     sr_b = ghost_b200.LIPSPADEGenerator(seed=1).bfloat16().cuda()
     rng = np.random.default_rng(11)
+    # the SR batches must fall where face_enhancement puts them (batch statistics): a pipeline batch that is not a
+    # multiple of sr_batch would restart the batching inside every submit (ADVICE round 1)
+    with pytest.raises(ValueError):
+        ghost_b200.SwapPipeline(G, arc, 3, (H, W), sr=sr_a, sr_batch=2)
     pipe = ghost_b200.SwapPipeline(G, arc, B, (H, W), depth=2, mode="exact", sr=sr_a, sr_batch=2)
     face_frame = np.arange(B, dtype=np.int32)
     batches, outs = [], []
