@@ -84,6 +84,7 @@ SIGNATURES = {
     "ghost_test_aad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f,
                             _vp, _i, _vp]),
     "ghost_test_last_error": (C.c_char_p, []),
+    "ghost_test_last_ms": (_f, []),
     "ghost_test_mask_job": (_i, [_fp, _i, _i, _i, C.POINTER(C.c_uint32), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16),
                                 C.POINTER(_i)]),
     "ghost_test_upsample2x": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -269,7 +269,42 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.n_valid = 2 * aad->c_x;
     if (w.rows_pad < 2 * aad->c_x) return "lower_conv: AAD weights must hold 2*c_x rows";
   } else {
-    int bn_ = bn_hint;
+    int bn_ = bn_hint & 1023;
+    // CTA-pair kernel (igemm.cuh `cta2`): plain linear-mode convs with 64-channel chunks; bits 10-11 of the hint
+    // force it on (1) / off (2) for the kernel tests, GHOST_CTA2=0 turns it off for A/B profiling
+    static const int cta2_mode = [] {
+      const char* e = getenv("GHOST_CTA2");
+      return e ? atoi(e) : 1;
+    }();
+    const int force2 = bn_hint >> 10;
+    const long long tiles_m2 = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
+    bool pair_ok = !win && p.kc == 64 && w.Cout >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
+    if (pair_ok) {
+      // Cost of a K block per SM, measured on B200 (tools/conv_sweep.py, us): one CTA 0.276 / 0.29 / 0.425 at N tiles
+      // of 64 / 128 / 256 (operand delivery: 16 KB + BN*128 B per block), CTA pair 0.237 / 0.258 / 0.38 (16 KB +
+      // BN*64 B; 0.38 us is the tensor-core time of a 128 x 256 x 64 block at the measured 1.63 PFLOP/s).  Both
+      // kernels run rounds of a persistent grid: 148 CTAs / 74 pairs.
+      const int cpad = (w.Cout + 15) / 16 * 16;
+      auto t1 = [](int bn) { return bn <= 128 ? 0.262 + 0.00022 * bn : 0.29 + 0.00105 * (bn - 128); };
+      auto t2 = [](int bn) { return bn <= 128 ? 0.216 + 0.00033 * bn : 0.258 + 0.00095 * (bn - 128); };
+      const int cands[4] = {256, 128, 64, cpad < 256 ? cpad : 256};
+      double best1 = 1e30, best2 = 1e30;
+      int bn2 = 0;
+      for (int i = 0; i < 4; ++i) {
+        const int c = cands[i];
+        if ((c > cpad && c != cands[3]) || (bn_ && c != bn_)) continue;
+        const long long nt = (w.Cout + c - 1) / c;
+        const double c1 = static_cast<double>((tiles_m2 * nt + 147) / 148) * t1(c);
+        const double c2 = static_cast<double>((((tiles_m2 + 1) / 2) * nt + 73) / 74) * t2(c);
+        if (c1 < best1) best1 = c1;
+        if (c2 < best2 || (c2 == best2 && c > bn2)) best2 = c2, bn2 = c;
+      }
+      if (bn_ && !bn2) bn2 = bn_;
+      if (bn2 && (force2 == 1 || best2 < 0.98 * best1)) {
+        p.cta2 = 1;
+        bn_ = bn2;
+      }
+    }
     if (!bn_) {
       // Measured on B200 (tools/conv_sweep.py): with one CTA per SM a K block costs ~0.40 us whatever the N tile
       // (issue-bound: four tcgen05.mma + two TMA boxes per block), ~0.43 us at N = 256.  So pick the N tile that
@@ -299,10 +334,10 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   {
     const uint64_t dims[2] = {static_cast<uint64_t>(w.K), static_cast<uint64_t>(w.rows_pad)};
     const uint64_t str[1] = {static_cast<uint64_t>(w.K) * eb};
-    const uint32_t box[2] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.BN)};
+    const uint32_t box[2] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.cta2 ? p.BN / 2 : p.BN)};
     if (const char* e = encode_tmap(&p.tmB, w.wb, 2, dims, str, box, swz)) return e;
   }
-  int stage_bytes = (128 + p.BN) * p.kc * 2;
+  int stage_bytes = p.cta2 ? (128 + p.BN / 2) * 128 : (128 + p.BN) * p.kc * 2;
   int resident_bytes = 0;
   if (win) {
     const int b_tile = p.BN * 128;
@@ -349,7 +384,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   // bound: bytes in flight / ~1.8 us).
   {
     const int nkb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
-    p.dual = !aad && stages >= 4 && 2 * nkb <= stages;
+    p.dual = !aad && !p.cta2 && stages >= 4 && 2 * nkb <= stages;
   }
   p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
   // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring

@@ -278,6 +278,185 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
           }
 }
 
+// Linear-mode epilogue of one accumulator tile, shared by the one-CTA kernel (igemm_kernel) and the CTA-pair kernel
+// (igemm2_kernel).  All 16 epilogue warps work on every tile: four warps per TMEM lane group split the columns.
+// Staged output (use_stg) for the LAST tile of a CTA, whose epilogue nothing overlaps: once that tile's accumulator
+// is complete the operand ring is idle, so every warp parks its 32 rows x wcols there (rows of P 16-byte pieces,
+// piece q of row r at slot q ^ stg_key(r): bank-conflict free) and moves whole row segments to / from global
+// memory - 4-8 cache lines per instruction instead of 32.
+template <bool F16>
+struct LinEpi {
+  int lane, lg, ew, r, rn, rh, rw, rows_used;
+  int wcols, rowb, P, lgP, rb_row0, rb_piece, rb_step;
+  uint8_t* wst;
+  const float* eparm;
+  bool staged;
+  uint32_t tmem_lanes;  // TMEM address of this warp's lane group, column 0
+  int acc_stride;
+
+  __device__ __forceinline__ void init(const IgemmParams& p, int warp, int lane_, uint8_t* ring, const float* eparm_,
+                                       bool staged_, int rows_used_, uint32_t tmem_base, int acc_stride_) {
+    lane = lane_;
+    lg = warp & 3;                        // TMEM lane group this warp may read
+    ew = (warp - kIgemmEpiWarp0) >> 2;    // 0..3: which of the four warps of that lane group
+    r = lg * 32 + lane;                   // GEMM row inside the tile
+    rn = r / (p.bh * p.bw);
+    rh = (r / p.bw) % p.bh;
+    rw = r % p.bw;
+    rows_used = rows_used_;
+    wcols = p.BN >> 2, rowb = wcols * 2, P = rowb >> 4, lgP = 31 - __clz(P);
+    wst = ring + (warp - kIgemmEpiWarp0) * (32 * rowb);
+    rb_row0 = lane >> lgP, rb_piece = lane & (P - 1), rb_step = 32 >> lgP;
+    eparm = eparm_;
+    staged = staged_;
+    tmem_lanes = tmem_base + (static_cast<uint32_t>(lg * 32) << 16);
+    acc_stride = acc_stride_;
+  }
+  __device__ __forceinline__ int stg_key(int row) const { return ((row * rowb) >> 7) & (P - 1); }
+
+  // REMOTE: the accumulator-empty barrier lives in the leader CTA of the pair (cluster rank 0)
+  template <bool REMOTE>
+  __device__ __forceinline__ void release(uint64_t* tempty) const {
+    if (lane == 0) {
+      if (REMOTE) mbar_arrive_rank0(tempty);
+      else mbar_arrive(tempty);
+    }
+  }
+
+  // returns false when the pipeline was aborted (the caller leaves its tile loop)
+  template <bool REMOTE>
+  __device__ __forceinline__ bool tile(const IgemmParams& p, const TileCoord& t, int as, uint32_t aphase, bool use_stg,
+                                       uint64_t* tfull, uint64_t* tempty, volatile int* abort_flag) const {
+        const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
+        const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
+        const uint32_t t_addr = tmem_lanes + as * acc_stride;
+        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
+        const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
+        const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
+        const int colw = t.nt * p.BN + ew * wcols;  // staged path: first column of this warp
+        const bool cols_on = colw < p.n_valid;      // (n_valid is a multiple of wcols there)
+        if (!__all_sync(0xffffffffu, mbar_wait(tfull, aphase, abort_flag))) return false;
+        tc_fence_after();
+        if (use_stg) {
+          if (p.res != nullptr) {
+            // residual rows of this warp's piece of the tile, as whole row segments
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (i < P) {  // warp-uniform
+                const int row = i * rb_step + rb_row0;
+                const long long rp_row = __shfl_sync(0xffffffffu, r_pix, row);
+                const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
+                if (v_row && cols_on)
+                  *reinterpret_cast<uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4)) =
+                      __ldg(reinterpret_cast<const uint4*>(p.res + rp_row + colw + rb_piece * 8));
+              }
+            }
+            __syncwarp();
+          }
+          uint8_t* my_row = wst + lane * rowb;
+          const int my_key = stg_key(lane);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (c * 16 < wcols) {  // warp-uniform
+              const int j = ew * wcols + c * 16;
+              uint32_t v[16];
+              __syncwarp();
+              tmem_ld16(t_addr + j, v);
+              tmem_ld_wait();
+              if (valid && cols_on) {
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
+                uint4* s0 = reinterpret_cast<uint4*>(my_row + (((2 * c) ^ my_key) << 4));
+                uint4* s1 = reinterpret_cast<uint4*>(my_row + (((2 * c + 1) ^ my_key) << 4));
+                if (p.res) {
+                  const uint4 q0 = *s0, q1 = *s1;
+                  const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    f[2 * i] += lo16<F16>(qq[i]);
+                    f[2 * i + 1] += hi16<F16>(qq[i]);
+                  }
+                }
+                if (p.act2 == kAct2Tanh) {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
+                }
+                uint4 o0, o1;
+                o0.x = pack16<F16>(f[0], f[1]);
+                o0.y = pack16<F16>(f[2], f[3]);
+                o0.z = pack16<F16>(f[4], f[5]);
+                o0.w = pack16<F16>(f[6], f[7]);
+                o1.x = pack16<F16>(f[8], f[9]);
+                o1.y = pack16<F16>(f[10], f[11]);
+                o1.z = pack16<F16>(f[12], f[13]);
+                o1.w = pack16<F16>(f[14], f[15]);
+                *s0 = o0;
+                *s1 = o1;
+              }
+            }
+          }
+          // the accumulator stage goes back to the MMA warp before the global stores
+          tc_fence_before();
+          __syncwarp();
+          release<REMOTE>(tempty);
+          const int jt = ew * wcols + rb_piece * 8;  // tile column of this lane's 8 channels
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (i >= P) break;  // warp-uniform
+            const int row = i * rb_step + rb_row0;
+            const long long op_row = __shfl_sync(0xffffffffu, o_pix, row);
+            const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
+            if (v_row && cols_on) {
+              const uint4 q = *reinterpret_cast<const uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4));
+              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + op_row + colw + rb_piece * 8) = q;
+              if (p.out2) {
+                // second output from the value as stored (rounded to bf16), e.g. the next block's bn1
+                float4 sc0, sc1, sh0, sh1;
+                if (staged) {
+                  sc0 = *reinterpret_cast<const float4*>(eparm + 512 + jt);
+                  sc1 = *reinterpret_cast<const float4*>(eparm + 512 + jt + 4);
+                  sh0 = *reinterpret_cast<const float4*>(eparm + 768 + jt);
+                  sh1 = *reinterpret_cast<const float4*>(eparm + 768 + jt + 4);
+                } else {
+                  const int cg = colw + rb_piece * 8;
+                  sc0 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg));
+                  sc1 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg) + 1);
+                  sh0 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg));
+                  sh1 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg) + 1);
+                }
+                uint4 o2;
+                o2.x = pack16<F16>(fmaf(lo16<F16>(q.x), sc0.x, sh0.x), fmaf(hi16<F16>(q.x), sc0.y, sh0.y));
+                o2.y = pack16<F16>(fmaf(lo16<F16>(q.y), sc0.z, sh0.z), fmaf(hi16<F16>(q.y), sc0.w, sh0.w));
+                o2.z = pack16<F16>(fmaf(lo16<F16>(q.z), sc1.x, sh1.x), fmaf(hi16<F16>(q.z), sc1.y, sh1.y));
+                o2.w = pack16<F16>(fmaf(lo16<F16>(q.w), sc1.z, sh1.z), fmaf(hi16<F16>(q.w), sc1.w, sh1.w));
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out2) + op_row + colw + rb_piece * 8) = o2;
+              }
+            }
+          }
+          return true;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (ch0 + c < ch1) {  // warp-uniform
+            const int j = (ch0 + c) * 16;
+            uint32_t v[16];
+            __syncwarp();
+            tmem_ld16(t_addr + j, v);
+            tmem_ld_wait();
+            const int col0 = t.nt * p.BN + j;
+            if (valid && col0 < p.n_valid) linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
+          }
+        }
+        // hand the accumulator stage back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        release<REMOTE>(tempty);
+        return true;
+  }
+};
+
 }  // namespace
 
 // One MMA issuer warp (converged; one elected lane issues).  `par` is a literal at both call sites so that every
@@ -634,163 +813,16 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     const int rw = r % p.bw;
     if (p.mode == kModeLinear) {
       // all 16 warps share every tile: warp ew takes a quarter of its columns
-      // Staged output (p.stg) for the LAST tile of the CTA, whose epilogue nothing overlaps: once that tile's
-      // accumulator is complete the operand ring is idle, so every warp parks its 32 rows x wcols there (rows of
-      // P 16-byte pieces, piece q of row r at slot q ^ stg_key(r): bank-conflict free) and moves whole row
-      // segments to / from global memory - 4-8 cache lines per instruction instead of 32.
-      const int wcols = p.BN >> 2, rowb = wcols * 2, P = rowb >> 4, lgP = 31 - __clz(P);
-      uint8_t* wst = ring + (warp - kIgemmEpiWarp0) * (32 * rowb);
-      const int rb_row0 = lane >> lgP, rb_piece = lane & (P - 1), rb_step = 32 >> lgP;
-      auto stg_key = [&](int row) { return ((row * rowb) >> 7) & (P - 1); };
+      LinEpi<F16> epi;
+      epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
       int it = 0;
       TileWalk walk;
       walk.init(p, blockIdx.x, gridDim.x);
       for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it, walk.next(p)) {
-        const TileCoord t = walk.t;
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
-        const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
-        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(lg * 32) << 16) + as * acc_stride;
-        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
-        const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
-        const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
-        const int colw = t.nt * p.BN + ew * wcols;  // staged path: first column of this warp
-        const bool cols_on = colw < p.n_valid;      // (n_valid is a multiple of wcols there)
         const bool use_stg = p.stg && tile + static_cast<int>(gridDim.x) >= tiles_total;
-#ifdef GHOST_IGEMM_PROF
-        const long long ew0_ = clock64();
-#endif
-        if (!__all_sync(0xffffffffu, mbar_wait(&tfull_bar[as], aphase, &abort_flag))) break;
-#ifdef GHOST_IGEMM_PROF
-        if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x < 160) {
-          g_igemm_prof[blockIdx.x][6] = (it ? g_igemm_prof[blockIdx.x][6] : 0ull) + (clock64() - ew0_);
-          g_igemm_prof[blockIdx.x][7] = it + 1;
-        }
-#endif
-        tc_fence_after();
-#ifdef GHOST_IGEMM_PROF
-        if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[4] = clock64();
-#endif
-        if (use_stg) {
-          if (p.res != nullptr) {
-            // residual rows of this warp's piece of the tile, as whole row segments
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              if (i < P) {  // warp-uniform
-                const int row = i * rb_step + rb_row0;
-                const long long rp_row = __shfl_sync(0xffffffffu, r_pix, row);
-                const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
-                if (v_row && cols_on)
-                  *reinterpret_cast<uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4)) =
-                      __ldg(reinterpret_cast<const uint4*>(p.res + rp_row + colw + rb_piece * 8));
-              }
-            }
-            __syncwarp();
-          }
-          uint8_t* my_row = wst + lane * rowb;
-          const int my_key = stg_key(lane);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (c * 16 < wcols) {  // warp-uniform
-              const int j = ew * wcols + c * 16;
-              uint32_t v[16];
-              __syncwarp();
-              tmem_ld16(t_addr + j, v);
-              tmem_ld_wait();
-              if (valid && cols_on) {
-                float f[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
-                uint4* s0 = reinterpret_cast<uint4*>(my_row + (((2 * c) ^ my_key) << 4));
-                uint4* s1 = reinterpret_cast<uint4*>(my_row + (((2 * c + 1) ^ my_key) << 4));
-                if (p.res) {
-                  const uint4 q0 = *s0, q1 = *s1;
-                  const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-#pragma unroll
-                  for (int i = 0; i < 8; ++i) {
-                    f[2 * i] += lo16<F16>(qq[i]);
-                    f[2 * i + 1] += hi16<F16>(qq[i]);
-                  }
-                }
-                if (p.act2 == kAct2Tanh) {
-#pragma unroll
-                  for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
-                }
-                uint4 o0, o1;
-                o0.x = pack16<F16>(f[0], f[1]);
-                o0.y = pack16<F16>(f[2], f[3]);
-                o0.z = pack16<F16>(f[4], f[5]);
-                o0.w = pack16<F16>(f[6], f[7]);
-                o1.x = pack16<F16>(f[8], f[9]);
-                o1.y = pack16<F16>(f[10], f[11]);
-                o1.z = pack16<F16>(f[12], f[13]);
-                o1.w = pack16<F16>(f[14], f[15]);
-                *s0 = o0;
-                *s1 = o1;
-              }
-            }
-          }
-          // the accumulator stage goes back to the MMA warp before the global stores
-          tc_fence_before();
-          __syncwarp();
-#ifdef GHOST_IGEMM_PROF
-          if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[5] = clock64();
-#endif
-          if (lane == 0) mbar_arrive(&tempty_bar[as]);
-          const int jt = ew * wcols + rb_piece * 8;  // tile column of this lane's 8 channels
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            if (i >= P) break;  // warp-uniform
-            const int row = i * rb_step + rb_row0;
-            const long long op_row = __shfl_sync(0xffffffffu, o_pix, row);
-            const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
-            if (v_row && cols_on) {
-              const uint4 q = *reinterpret_cast<const uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4));
-              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + op_row + colw + rb_piece * 8) = q;
-              if (p.out2) {
-                // second output from the value as stored (rounded to bf16), e.g. the next block's bn1
-                float4 sc0, sc1, sh0, sh1;
-                if (staged) {
-                  sc0 = *reinterpret_cast<const float4*>(eparm + 512 + jt);
-                  sc1 = *reinterpret_cast<const float4*>(eparm + 512 + jt + 4);
-                  sh0 = *reinterpret_cast<const float4*>(eparm + 768 + jt);
-                  sh1 = *reinterpret_cast<const float4*>(eparm + 768 + jt + 4);
-                } else {
-                  const int cg = colw + rb_piece * 8;
-                  sc0 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg));
-                  sc1 = __ldg(reinterpret_cast<const float4*>(p.scale2 + cg) + 1);
-                  sh0 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg));
-                  sh1 = __ldg(reinterpret_cast<const float4*>(p.shift2 + cg) + 1);
-                }
-                uint4 o2;
-                o2.x = pack16<F16>(fmaf(lo16<F16>(q.x), sc0.x, sh0.x), fmaf(hi16<F16>(q.x), sc0.y, sh0.y));
-                o2.y = pack16<F16>(fmaf(lo16<F16>(q.y), sc0.z, sh0.z), fmaf(hi16<F16>(q.y), sc0.w, sh0.w));
-                o2.z = pack16<F16>(fmaf(lo16<F16>(q.z), sc1.x, sh1.x), fmaf(hi16<F16>(q.z), sc1.y, sh1.y));
-                o2.w = pack16<F16>(fmaf(lo16<F16>(q.w), sc1.z, sh1.z), fmaf(hi16<F16>(q.w), sc1.w, sh1.w));
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out2) + op_row + colw + rb_piece * 8) = o2;
-              }
-            }
-          }
-          continue;
-        }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (ch0 + c < ch1) {  // warp-uniform
-            const int j = (ch0 + c) * 16;
-            uint32_t v[16];
-            __syncwarp();
-            tmem_ld16(t_addr + j, v);
-            tmem_ld_wait();
-            const int col0 = t.nt * p.BN + j;
-            if (valid && col0 < p.n_valid) linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
-          }
-        }
-        // hand the accumulator stage back to the MMA warp
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty_bar[as]);
+        const int as = it & 1;
+        if (!epi.template tile<false>(p, walk.t, as, (it >> 1) & 1, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag))
+          break;
       }
     } else {
       // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
@@ -1109,7 +1141,203 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// CTA-pair kernel (tcgen05 cta_group::2): linear mode, 64-channel K chunks, streaming weights.
+//
+// A one-CTA tile of 128 x BN brings 16 KB of activations + BN*128 B of weights into the SM per K block; at BN = 256
+// that is 48 KB per 4.2 MFLOP = 87 FLOP/B, while one SM takes ~64 B/clk from L2 and retires 8192 dense 16-bit
+// FLOP/clk = 128 FLOP/B: the one-CTA kernel is bound by operand delivery (measured ~0.43 us per K block against
+// 0.26 us of MMA time).  Two CTAs on the SM pair of a TPC run ONE 256 x BN MMA per K step instead: each CTA loads its
+// own 128 pixel rows and HALF of the weight tile, the tensor cores of both SMs read both halves, and each SM keeps
+// the 128 accumulator rows of its own pixels in its own TMEM.  Per SM and K block: 16 KB + BN*64 B.
+//
+// Roles per CTA as in igemm_kernel (warp 0: activation TMA, warp 3: weight TMA, warps 4-19: epilogue of the CTA's own
+// 128 rows); warp 1 of the LEADER CTA (cluster rank 0) issues the MMAs of the pair, warp 2 of both CTAs owns the
+// TMEM allocation.  Barriers: `full` lives in the leader (both CTAs' TMA loads count their bytes there), `empty` and
+// `tfull` are signalled in both CTAs by multicast commits, `tempty` lives in the leader and collects the epilogue
+// warps of both CTAs.
+template <bool F16>
+__global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_constant__ IgemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[8];
+  __shared__ uint64_t empty_bar[8];
+  __shared__ uint64_t tfull_bar[2];
+  __shared__ uint64_t tempty_bar[2];
+  __shared__ __align__(16) float eparm[1024];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ int abort_flag;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* ring = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  constexpr int a_stage_bytes = 128 * 128;
+  const int b_half_bytes = (p.BN >> 1) * 128;
+  const int stage_bytes = a_stage_bytes + b_half_bytes;  // multiple of 1024
+  const int rows_used = p.bw * p.bh * p.bn;
+  const int num_kb = p.ntaps * p.kc_per_tap;
+  const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
+  const int super_total = ((tiles_m + 1) >> 1) * p.tiles_n;  // pairs of M tiles x N tiles
+  const int acc_stride = p.tmem_cols >> 1;
+
+  if (warp == 1) {
+    if (lane == 0) abort_flag = 0;
+    if (lane < 8) mbar_init(&full_bar[lane], 2);  // the leader's two producers (activations, weights)
+    else if (lane < 16) mbar_init(&empty_bar[lane - 8], 1);
+    else if (lane < 18) mbar_init(&tfull_bar[lane - 16], 1);
+    else if (lane < 20) mbar_init(&tempty_bar[lane - 18], 2 * kIgemmEpiWarps);
+    fence_mbar_init();
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tmA);
+    prefetch_tmap(&p.tmB);
+  }
+  const bool staged = p.tiles_n == 1;
+  if (staged && warp >= kIgemmEpiWarp0) {
+    for (int i = threadIdx.x - kIgemmEpiWarp0 * 32; i < p.BN; i += kIgemmEpiWarps * 32) {
+      const bool in = i < p.n_valid;
+      eparm[i] = (in && p.bias) ? __ldg(p.bias + i) : 0.f;
+      eparm[256 + i] = (in && p.act1 == kActPRelu) ? __ldg(p.slope_c + i) : 0.f;
+      eparm[512 + i] = (in && p.out2) ? __ldg(p.scale2 + i) : 0.f;
+      eparm[768 + i] = (in && p.out2) ? __ldg(p.shift2 + i) : 0.f;
+    }
+  }
+  if (warp == 2) tmem2_alloc(&tmem_base_smem, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything signals them
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+  grid_dep_launch();
+
+  // super tile s -> this CTA's own tile: N tile s % tiles_n, M tile 2 * (s / tiles_n) + rank (an odd tile count
+  // leaves the last pair's second CTA with a tile past the batch: its loads are zero-filled, its rows never stored)
+  auto my_tile = [&](int s) {
+    TileCoord t;
+    t.nt = s % p.tiles_n;
+    int m = (s / p.tiles_n) * 2 + static_cast<int>(rank);
+    t.tw = m % p.tiles_w;
+    m /= p.tiles_w;
+    t.th = m % p.tiles_h;
+    t.tn = m / p.tiles_h;
+    return t;
+  };
+
+  if (warp == 0) {
+    // ============================== TMA producer: activations (both CTAs) =====
+    grid_dep_wait();
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t a_tx = 2u * rows_used * 128u;  // both CTAs' boxes
+    for (int s = cluster; s < super_total; s += nclusters) {
+      const TileCoord t = my_tile(s);
+      const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+      int tap = 0, kci = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+        if (elect_one()) {
+          uint8_t* sa = ring + stage * stage_bytes;
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], a_tx);
+          const int c = p.a_c0 + p.tap_c[tap] + kci * 64;
+          if (p.a_rank == 4)
+            tma2_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
+          else
+            tma2_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+        }
+        __syncwarp();
+        if (++kci == p.kc_per_tap) {
+          kci = 0;
+          ++tap;
+        }
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ============================== TMA producer: this CTA's half of the weight tile
+    int stage = 0;
+    uint32_t phase = 0;
+    const int half = p.BN >> 1;
+    for (int s = cluster; s < super_total; s += nclusters) {
+      const int row0 = (s % p.tiles_n) * p.BN + static_cast<int>(rank) * half;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+        if (elect_one()) {
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * b_half_bytes);
+          tma2_load_2d(ring + stage * stage_bytes + a_stage_bytes, &p.tmB, &full_bar[stage], p.b_k0 + kb * 64, row0);
+        }
+        __syncwarp();
+        if (++stage == p.stages) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer of the pair (leader CTA) =======
+    if (rank == 0) {
+      const uint32_t tmem_base_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t idesc = make_idesc_f16(256, p.BN, p.f16 != 0);
+      const uint32_t dhi = smem_desc_hi(1024, false);
+      const uint32_t ring_u = smem_u32(ring);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int s = cluster; s < super_total; s += nclusters, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (it >> 1) & 1;
+        const uint32_t d_tmem = tmem_base_u + as * acc_stride;
+        mbar_wait_nofail(&tempty_bar[as], aphase ^ 1u, &abort_flag);
+        tc_fence_after();
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait_nofail(&full_bar[stage], phase, &abort_flag);
+          tc_fence_after();
+          const uint32_t sa = ring_u + stage * stage_bytes;
+          umma2_bf16_batch4(d_tmem, smem_desc_lo(sa), smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
+          umma2_commit_elect(&empty_bar[stage]);  // frees the slot in both CTAs when these MMAs retire
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        umma2_commit_elect(&tfull_bar[as]);
+      }
+    }
+  } else if (warp >= kIgemmEpiWarp0) {
+    // ============================== epilogue of this CTA's 128 rows ===========
+    grid_dep_wait();
+    LinEpi<F16> epi;
+    epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
+    int it = 0;
+    for (int s = cluster; s < super_total; s += nclusters, ++it) {
+      const TileCoord t = my_tile(s);
+      const int as = it & 1;
+      const bool use_stg = p.stg && s + nclusters >= super_total;
+      if (!epi.template tile<true>(p, t, as, (it >> 1) & 1, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) break;
+    }
+  }
+
+  // ------------------------------ teardown ------------------------------------
+  tc_fence_before();
+  __syncthreads();
+  if (abort_flag && threadIdx.x == 0 && p.err) {
+    *reinterpret_cast<volatile int*>(p.err) = 1;
+    __threadfence_system();
+  }
+  cluster_sync_all();  // neither CTA leaves while the other may still signal its barriers / read its operands
+  if (warp == 2) {
+    tc_fence_after();
+    tmem2_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
 int igemm_smem_bytes(const IgemmParams& p) {
+  if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024;
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
   const int b_tile = p.BN * row_bytes;
@@ -1123,6 +1351,7 @@ namespace {
 // a device property, so both are cached per device ordinal (one process may drive several GPUs).
 struct IgemmDevState {
   int max_dyn_smem = 0;  // opt-in dynamic shared memory limit (227 KB minus the kernel's static part)
+  int max_dyn_smem2 = 0; // the same for the CTA-pair kernel
   int num_sms = 0;
 };
 constexpr int kMaxDevices = 64;
@@ -1145,6 +1374,14 @@ const char* igemm_dev_state(IgemmDevState* out) {
       e = cudaFuncSetAttribute(igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     }
     if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) {
+      cudaFuncAttributes fa2;
+      e = cudaFuncGetAttributes(&fa2, igemm2_kernel<false>);
+      const int lim2 = 227 * 1024 - static_cast<int>(fa2.sharedSizeBytes);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      st.max_dyn_smem2 = lim2;
+    }
     int sms = 0;
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) {
@@ -1159,9 +1396,53 @@ const char* igemm_dev_state(IgemmDevState* out) {
 }
 }  // namespace
 
+namespace {
+const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, cudaStream_t stream) {
+  if (p.mode != kModeLinear || p.kc != 64 || p.a_win || p.b_res || p.splits != 1 || p.dual)
+    return "igemm2: the CTA-pair kernel runs plain linear-mode convs with 64-channel chunks";
+  if (p.BN % 16 || p.BN < 32 || p.BN > 256) return "igemm2: BN must be a multiple of 16 in [32,256]";
+  if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm2: M box must hold 1..128 rows";
+  if (p.stages < 2 || p.stages > 8) return "igemm2: stages must be in [2,8]";
+  if (p.sets != 2 || p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
+    return "igemm2: bad tmem_cols";
+  if (p.ntaps > kIgemmMaxTaps) return "igemm2: too many taps";
+  if (p.stg && (p.out_f32 || (p.BN != 128 && p.BN != 256) || p.n_valid % (p.BN >> 2)))
+    return "igemm2: staged output needs a 16-bit linear epilogue and N tiles of 128 or 256 whole warp quarters";
+  const int smem = igemm_smem_bytes(p);
+  if (smem > max_dyn_smem) return "igemm2: shared memory budget exceeded";
+  const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
+  const int supers = ((tiles_m + 1) / 2) * p.tiles_n;
+  if (supers <= 0) return "igemm2: empty grid";
+  int clusters = num_sms / 2;
+  if (clusters > supers) clusters = supers;
+  static const int pdl = [] {
+    const char* ev = getenv("GHOST_PDL");
+    return ev ? (atoi(ev) != 0) : 1;
+  }();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters, 1, 1);
+  cfg.blockDim = dim3(kIgemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = static_cast<size_t>(smem);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 2 : 1;
+  cudaError_t e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false>, p);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+}  // namespace
+
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   IgemmDevState dev_state;
   if (const char* e = igemm_dev_state(&dev_state)) return e;
+  if (p.cta2) return igemm2_launch(p, dev_state.max_dyn_smem2, dev_state.num_sms, stream);
   const int max_dyn_smem = dev_state.max_dyn_smem;
   if (p.BN % 16 || p.BN < 16 || p.BN > 256) return "igemm: BN must be a multiple of 16 in [16,256]";
   if (p.kc != 64 && p.kc != 32) return "igemm: kc must be 32 or 64";

@@ -103,6 +103,12 @@ struct alignas(64) IgemmParams {
   // cross HBM once for both layers (the second reader hits L2), and every CTA keeps one layer's weights resident.
   int aad_pair;
 
+  // CTA-pair mode (igemm2_kernel, tcgen05 cta_group::2): clusters of two CTAs work on two neighbouring M tiles of the
+  // same N tile as ONE 256 x BN MMA - each CTA loads its own 128 A rows and HALF of the weight tile (tmB boxes of
+  // BN/2 rows), so a K block brings 16 KB + BN*64 B instead of 16 KB + BN*128 B into each SM.  Linear mode, 64-channel
+  // chunks, streaming weights only.
+  int cta2;
+
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
   int* err;  // device word set non-zero when a pipeline wait timed out

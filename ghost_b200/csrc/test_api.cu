@@ -1,5 +1,6 @@
 // Single-op entry points for the kernel-level parity tests.  They run one lowered op
 // synchronously with weights supplied in the reference's own layouts.
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/ghost_b200.h"
@@ -29,6 +30,11 @@ int guarded_t(F&& f) {
 extern "C" {
 
 const char* ghost_test_last_error(void) { return g_err.c_str(); }
+
+// GHOST_TEST_CONV_REPS=n: ghost_test_conv re-launches its (first) op n more times between two CUDA events; the mean
+// duration of those launches is what ghost_test_last_ms returns (tools/conv_sweep.py)
+static float g_last_ms = 0.f;
+float ghost_test_last_ms(void) { return g_last_ms; }
 
 // conv weights: kind 0 -> [Cout][Cin][k][k] (nn.Conv2d), kind 1 -> [Cin][Cout][4][4] (nn.ConvTranspose2d k4 s2 p1)
 int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_host, const float* bias_host, int Cout,
@@ -83,6 +89,24 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
                            dt == kF32, device_err_word(), nullptr, bn_hint),
                 "test conv lower");
       check_msg(op.launch(s), "test conv launch");
+      if (const char* ev = getenv("GHOST_TEST_CONV_REPS")) {
+        const int reps = atoi(ev);
+        if (reps > 0) {
+          cudaEvent_t e0, e1;
+          check_cuda(cudaEventCreate(&e0), "event");
+          check_cuda(cudaEventCreate(&e1), "event");
+          for (int i = 0; i < 3; ++i) check_msg(op.launch(s), "test conv launch");
+          check_cuda(cudaEventRecord(e0, s), "event");
+          for (int i = 0; i < reps; ++i) check_msg(op.launch(s), "test conv launch");
+          check_cuda(cudaEventRecord(e1, s), "event");
+          check_cuda(cudaEventSynchronize(e1), "event");
+          float ms = 0.f;
+          cudaEventElapsedTime(&ms, e0, e1);
+          g_last_ms = ms / reps;
+          cudaEventDestroy(e0);
+          cudaEventDestroy(e1);
+        }
+      }
     } else {
       static const int kk[2][2] = {{1, 3}, {0, 2}};
       Act out;

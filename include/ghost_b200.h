@@ -248,6 +248,8 @@ int ghost_test_aad(const void* h_nhwc, const void* zattr_nhwc, const float* zid_
                    const float* conv2_b, const float* fc1_w, const float* fc1_b, const float* fc2_w,
                    const float* fc2_b, const float* convh_w, float convh_b, void* out_nhwc, int mode, void* stream);
 const char* ghost_test_last_error(void);
+/* mean duration (ms) of the re-launches ghost_test_conv timed when GHOST_TEST_CONV_REPS=n is set (tools/conv_sweep.py) */
+float ghost_test_last_ms(void);
 int ghost_test_upsample2x(const void* x_nhwc, void* y_nhwc, int dtype, int N, int H, int W, int C, void* stream);
 /* Bilinear x2 fused with the InstanceNorm statistics of its output (the next AAD block's input,
  * network/AEI_Net.py:124-138 + network/AADLayer.py:21); mean / biased variance per (n, c) come back on the host. */
