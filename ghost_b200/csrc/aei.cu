@@ -95,6 +95,8 @@ void Net::finalize_aei() {
     expect_shape(w, {Ci, Co, 4, 4}, k + ".deconv.weight");
     std::vector<float> sc, sh;
     bn_fold(W(k + ".bn.weight"), W(k + ".bn.bias"), W(k + ".bn.running_mean"), W(k + ".bn.running_var"), &sc, &sh);
+    // tensor-core modes: the four phase matrices stacked along the rows (one launch, igemm.cuh `nphase`)
+    std::vector<float> all_rows, all_sh;
     for (int r = 0; r < 2; ++r)
       for (int s = 0; s < 2; ++s) {
         std::vector<float> rows(static_cast<size_t>(Co) * 4 * Ci);
@@ -106,8 +108,14 @@ void Net::finalize_aei() {
               for (int ci = 0; ci < Ci; ++ci)
                 dst[ci] = w.data[((static_cast<size_t>(ci) * Co + co) * 4 + kh) * 4 + kw] * sc[co];
             }
-        packed_[S("deconv%d.p%d", i, r * 2 + s)] = pack(rows, Co, 4 * Ci, &sh, !bf, bf);
+        if (bf && Ci % 64 == 0) {
+          all_rows.insert(all_rows.end(), rows.begin(), rows.end());
+          all_sh.insert(all_sh.end(), sh.begin(), sh.end());
+        } else {
+          packed_[S("deconv%d.p%d", i, r * 2 + s)] = pack(rows, Co, 4 * Ci, &sh, !bf, bf);
+        }
       }
+    if (!all_rows.empty()) packed_[S("deconv%d.all", i)] = pack(all_rows, 4 * Co, 4 * Ci, &all_sh, false, true);
   }
 
   // ---- z_id GEMM: up1 (ConvTranspose2d c_id->1024 k2 on a 1x1 map, AEI_Net.py:101,123) and every
@@ -220,12 +228,13 @@ void Net::build_aei(ExecPlan& p) {
     return a;
   };
   auto add_conv = [&](const std::string& name, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
-                      const std::string& wname, const OutView& out, const Epilogue& epi, const AadArgs* aad) {
+                      const std::string& wname, const OutView& out, const Epilogue& epi, const AadArgs* aad,
+                      const DeconvPhases* phases = nullptr) {
     auto it = packed_.find(wname);
     if (it == packed_.end()) fail(-2, "internal: packed weights missing for " + wname);
     LaunchOp lop;
     lop.name = name;
-    check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad), name);
+    check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad, 0, phases), name);
     Op op;
     op.name = name;
     op.flops = lop.flops;
@@ -294,6 +303,26 @@ void Net::build_aei(ExecPlan& p) {
   for (int j = 1; j <= 6; ++j) {
     const Act& in = z[j];
     const Act& out = z[j + 1];
+    if (packed_.count(S("deconv%d.all", j))) {
+      // one launch for the four output phases (24 -> 6 launches, four times the tiles per launch)
+      DeconvPhases dp;
+      Epilogue e = leaky;
+      const Act* sk = unet ? nullptr : featbuf[7 - j];
+      for (int ph = 0; ph < 4; ++ph) {
+        const int r = ph >> 1, s = ph & 1;
+        dp.taps[ph] = Taps::deconv_phase(r, s);
+        dp.o_off[ph] = OutView::deconv_phase(out, r, s, 0).off;
+        if (sk) dp.r_off[ph] = OutView::deconv_phase(*sk, r, s, featoff[7 - j]).off;
+      }
+      if (sk) {  // linknet: x + skip (AEI_Net.py:38-39)
+        const OutView rv = OutView::deconv_phase(*sk, 0, 0, featoff[7 - j]);
+        e.res = sk->p;
+        e.r_sn = rv.sn; e.r_sh = rv.sh; e.r_sw = rv.sw; e.r_off = rv.off;
+      }
+      add_conv(S("enc.deconv%d", j), in, 0, in.C, dp.taps[0], in.H, in.W, S("deconv%d.all", j),
+               OutView::deconv_phase(out, 0, 0, 0), e, nullptr, &dp);
+      continue;
+    }
     for (int ph = 0; ph < 4; ++ph) {
       const int r = ph >> 1, s = ph & 1;
       Epilogue e = leaky;

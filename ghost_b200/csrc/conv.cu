@@ -107,8 +107,12 @@ int pow2_at_least(int v) {
 
 const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
                        const PackedW& w, const OutView& out, const Epilogue& epi, bool force_simt, int* err_word,
-                       const AadArgs* aad, int bn_hint) {
-  if (taps.n > kIgemmMaxTaps) return "lower_conv: too many taps";
+                       const AadArgs* aad, int bn_hint, const DeconvPhases* phases) {
+  if (taps.n * (phases ? 4 : 1) > kIgemmMaxTaps) return "lower_conv: too many taps";
+  if (phases && (aad || force_simt || w.Cout % 4 || !is16(in.dtype) || Cin % 64))
+    return "lower_conv: merged deconv phases need the plain tensor-core path";
+  // per-phase channel count: the N tiling never crosses a phase
+  const int cout_t = phases ? w.Cout / 4 : w.Cout;
   if (w.K != taps.n * Cin) return "lower_conv: weight K does not match taps*Cin";
   op->flops = 2.0 * in.N * Ho * Wo * static_cast<double>(w.Cout) * w.K;
   const bool can_igemm = !force_simt && is16(in.dtype) && (Cin % 32 == 0) && (in.C % 8 == 0) && (c0 % 8 == 0) &&
@@ -150,7 +154,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const char* e = getenv("GHOST_TAPN");  // A/B switch for profiling: GHOST_TAPN=0 keeps these convs on igemm_kernel
     return e ? (atoi(e) != 0) : 1;
   }();
-  bool tapn = tapn_mode != 0 && !aad && w.wt != nullptr && taps.n == 9 && taps.stride == 1 && Wo == in.W &&
+  bool tapn = tapn_mode != 0 && !aad && !phases && w.wt != nullptr && taps.n == 9 && taps.stride == 1 && Wo == in.W &&
               Ho == in.H && w.Cout <= 3 && Cin % 64 == 0 && Cin / 64 <= kTapnMaxChunks && in.H >= kTapnTileH &&
               in.W >= kTapnTileW && epi.act1 == kActNone && !epi.out2 && out.sw >= w.Cout;
   for (int i = 0; tapn && i < 9; ++i) tapn = taps.dh[i] == i / 3 - 1 && taps.dw[i] == i % 3 - 1;
@@ -203,7 +207,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const char* e = getenv("GHOST_AWIN");  // A/B switch for profiling: GHOST_AWIN=0 turns the mode off
     return e ? (atoi(e) != 0) : 1;
   }();
-  bool win = win_mode != 0 && !aad && taps.n == 9 && taps.stride == 1 && p.kc == 64 && Wo == in.W && Ho == in.H &&
+  bool win = win_mode != 0 && !aad && !phases && taps.n == 9 && taps.stride == 1 && p.kc == 64 && Wo == in.W && Ho == in.H &&
              Wo >= 112 && w.Cout <= 128;
   for (int i = 0; win && i < 9; ++i) win = taps.dh[i] == i / 3 - 1 && taps.dw[i] == i % 3 - 1;
   if (win) {
@@ -238,7 +242,17 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       p.tap_p[i] = 0;
       p.tap_h[i] = taps.dh[i];
     }
+    for (int ph = 1; phases && ph < 4; ++ph) {
+      if (phases->taps[ph].n != taps.n || phases->taps[ph].stride != 1) return "lower_conv: deconv phases must share the tap count";
+      for (int i = 0; i < taps.n; ++i) {
+        p.tap_c[ph * taps.n + i] = 0;
+        p.tap_w[ph * taps.n + i] = phases->taps[ph].dw[i];
+        p.tap_p[ph * taps.n + i] = 0;
+        p.tap_h[ph * taps.n + i] = phases->taps[ph].dh[i];
+      }
+    }
   } else {
+    if (phases) return "lower_conv: deconv phases are stride-1 gathers";
     // parity-split view: (2C | W/2 | 2 | H/2 | N); input pixel (2*hh+ph, 2*ww+pw), channel c lives at
     // inner index pw*C + c.
     p.a_rank = 5;
@@ -278,13 +292,14 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     }();
     const int force2 = bn_hint >> 10;
     const long long tiles_m2 = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
-    bool pair_ok = !win && p.kc == 64 && w.Cout >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
+    const int nph = phases ? 4 : 1;
+    bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
     if (pair_ok) {
       // Cost of a K block per SM, measured on B200 (tools/conv_sweep.py, us): one CTA 0.276 / 0.29 / 0.425 at N tiles
       // of 64 / 128 / 256 (operand delivery: 16 KB + BN*128 B per block), CTA pair 0.237 / 0.258 / 0.38 (16 KB +
       // BN*64 B; 0.38 us is the tensor-core time of a 128 x 256 x 64 block at the measured 1.63 PFLOP/s).  Both
       // kernels run rounds of a persistent grid: 148 CTAs / 74 pairs.
-      const int cpad = (w.Cout + 15) / 16 * 16;
+      const int cpad = (cout_t + 15) / 16 * 16;
       auto t1 = [](int bn) { return bn <= 128 ? 0.262 + 0.00022 * bn : 0.29 + 0.00105 * (bn - 128); };
       auto t2 = [](int bn) { return bn <= 128 ? 0.216 + 0.00033 * bn : 0.258 + 0.00095 * (bn - 128); };
       const int cands[4] = {256, 128, 64, cpad < 256 ? cpad : 256};
@@ -293,7 +308,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       for (int i = 0; i < 4; ++i) {
         const int c = cands[i];
         if ((c > cpad && c != cands[3]) || (bn_ && c != bn_)) continue;
-        const long long nt = (w.Cout + c - 1) / c;
+        if (phases && cout_t % c) continue;
+        const long long nt = static_cast<long long>(nph) * ((cout_t + c - 1) / c);
         const double c1 = static_cast<double>((tiles_m2 * nt + 147) / 148) * t1(c);
         const double c2 = static_cast<double>((((tiles_m2 + 1) / 2) * nt + 73) / 74) * t2(c);
         if (c1 < best1) best1 = c1;
@@ -310,7 +326,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       // (issue-bound: four tcgen05.mma + two TMA boxes per block), ~0.43 us at N = 256.  So pick the N tile that
       // minimises (rounds of the persistent grid) x (cost of a K block); ties go to the narrower tile, which
       // spreads the work over more SMs.
-      const int cpad = (w.Cout + 15) / 16 * 16;
+      const int cpad = (cout_t + 15) / 16 * 16;
       const long long tiles_m = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
       double best = 1e30;
       bn_ = cpad < 256 ? cpad : 256;
@@ -318,7 +334,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       for (int i = 0; i < 4; ++i) {
         const int bn_c = cands[i];
         if (bn_c > cpad && bn_c != cands[3]) continue;
-        const long long tiles = tiles_m * ((w.Cout + bn_c - 1) / bn_c);
+        if (phases && cout_t % bn_c) continue;
+        const long long tiles = tiles_m * nph * ((cout_t + bn_c - 1) / bn_c);
         const double cost = static_cast<double>((tiles + 147) / 148) * (bn_c > 128 ? 0.43 : 0.40);
         if (cost < best || (cost == best && bn_c < bn_)) {
           best = cost;
@@ -327,8 +344,13 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       }
     }
     p.BN = bn_;
-    p.tiles_n = (w.Cout + p.BN - 1) / p.BN;
-    p.n_valid = w.Cout;
+    p.tiles_n = nph * ((cout_t + p.BN - 1) / p.BN);
+    p.n_valid = nph * cout_t;
+    if (phases) {
+      if (cout_t % p.BN) return "lower_conv: the N tile must divide the channels of a deconv phase";
+      p.nphase = 4;
+      p.tpn = cout_t / p.BN;
+    }
     if (w.rows_pad < p.tiles_n * p.BN) return "lower_conv: packed weight rows are not padded to the N tile";
   }
   {
@@ -462,6 +484,11 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     }
   } else {
     p.mode = kModeLinear;
+    for (int ph = 0; phases && ph < 4; ++ph) {
+      // relative to phase 0's view, minus the stacked column offset the epilogue adds (ph * channels per phase)
+      p.ph_o[ph] = phases->o_off[ph] - out.off - static_cast<long long>(ph) * cout_t;
+      p.ph_r[ph] = phases->r_off[ph] - epi.r_off - static_cast<long long>(ph) * cout_t;
+    }
     p.act1 = epi.act1; p.slope = epi.slope; p.slope_c = epi.slope_c;
     p.res = reinterpret_cast<const __nv_bfloat16*>(epi.res);
     p.r_sn = epi.r_sn; p.r_sh = epi.r_sh; p.r_sw = epi.r_sw; p.r_off = epi.r_off;

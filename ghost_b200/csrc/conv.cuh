@@ -99,6 +99,15 @@ struct AadArgs {  // only for the fused AAD epilogue
   int pair = 0;  // two layers on the same h / z_attr as the two N tiles (igemm.cuh aad_pair); c_x = 2 * channels of h
 };
 
+// The four output phases of a ConvTranspose2d(k4, s2, p1) as one launch (igemm.cuh `nphase`): `w` passed to lower_conv
+// holds the four phase matrices stacked along the rows (Cout = 4 * Cout_phase, phase-major, bias stacked likewise),
+// `taps` is phase 0's, `out` / `epi.res` the views of phase (0, 0); here: the other phases' taps and view offsets.
+struct DeconvPhases {
+  Taps taps[4];
+  long long o_off[4] = {0, 0, 0, 0};  // OutView::off of each phase
+  long long r_off[4] = {0, 0, 0, 0};  // residual view offset of each phase (ignored without a residual)
+};
+
 // A lowered, launch-ready op.
 struct LaunchOp {
   enum Kind { kIgemm, kSimt, kTapn } kind = kIgemm;
@@ -119,7 +128,7 @@ struct LaunchOp {
 // force_simt selects the CUDA-core kernel (fp32 mode).  Returns nullptr on success.
 const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
                        const PackedW& w, const OutView& out, const Epilogue& epi, bool force_simt, int* err_word,
-                       const AadArgs* aad = nullptr, int bn_hint = 0);
+                       const AadArgs* aad = nullptr, int bn_hint = 0, const DeconvPhases* phases = nullptr);
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
 const char* encode_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,

@@ -330,8 +330,9 @@ struct LinEpi {
         const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
         const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
         const uint32_t t_addr = tmem_lanes + as * acc_stride;
-        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off;
-        const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off;
+        const int ph = p.nphase > 1 ? t.nt / p.tpn : 0;
+        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off + (p.nphase > 1 ? p.ph_o[ph] : 0);
+        const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off + (p.nphase > 1 ? p.ph_r[ph] : 0);
         const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
         const int colw = t.nt * p.BN + ew * wcols;  // staged path: first column of this warp
         const bool cols_on = colw < p.n_valid;      // (n_valid is a multiple of wcols there)
@@ -710,7 +711,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
           hphase ^= 1u;
         }
       }
-      int tap = tap0, kci = kci0;
+      int tap = tap0 + (p.nphase > 1 ? (t.nt / p.tpn) * p.ntaps : 0), kci = kci0;
       const int rg = p.dual ? (hit & 1) : 0;
       int stage_r = st[rg];
       uint32_t phase = ph[rg];
@@ -1235,7 +1236,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     for (int s = cluster; s < super_total; s += nclusters) {
       const TileCoord t = my_tile(s);
       const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
-      int tap = 0, kci = 0;
+      int tap = p.nphase > 1 ? (t.nt / p.tpn) * p.ntaps : 0, kci = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
         if (elect_one()) {
@@ -1405,7 +1406,8 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   if (p.stages < 2 || p.stages > 8) return "igemm2: stages must be in [2,8]";
   if (p.sets != 2 || p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm2: bad tmem_cols";
-  if (p.ntaps > kIgemmMaxTaps) return "igemm2: too many taps";
+  if (p.ntaps * (p.nphase > 1 ? p.nphase : 1) > kIgemmMaxTaps) return "igemm2: too many taps";
+  if (p.nphase > 1 && (p.nphase != 4 || p.tpn < 1 || p.tiles_n != p.nphase * p.tpn)) return "igemm2: bad phase tiling";
   if (p.stg && (p.out_f32 || (p.BN != 128 && p.BN != 256) || p.n_valid % (p.BN >> 2)))
     return "igemm2: staged output needs a 16-bit linear epilogue and N tiles of 128 or 256 whole warp quarters";
   const int smem = igemm_smem_bytes(p);
@@ -1457,7 +1459,10 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.tmem_cols < p.sets * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm: bad tmem_cols";
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
-  if (p.ntaps > kIgemmMaxTaps) return "igemm: too many taps";
+  if (p.ntaps * (p.nphase > 1 ? p.nphase : 1) > kIgemmMaxTaps) return "igemm: too many taps";
+  if (p.nphase > 1 && (p.nphase != 4 || p.mode != kModeLinear || p.a_win || p.b_res || p.splits != 1 || p.tpn < 1 ||
+                       p.tiles_n != p.nphase * p.tpn))
+    return "igemm: output phases need a plain linear-mode launch";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
   if (p.b_res && ((p.tiles_n != 1 && !p.aad_pair) || p.kc != 64 || p.splits != 1))

@@ -109,6 +109,14 @@ struct alignas(64) IgemmParams {
   // chunks, streaming weights only.
   int cta2;
 
+  // Output phases (the four phases of a ConvTranspose2d k4 s2 p1 as ONE launch): the N-tile index runs over
+  // nphase * tpn tiles, tile nt belongs to phase nt / tpn.  The phase weight matrices (and bias vectors) are stacked
+  // along the rows, so weight rows and bias columns follow nt * BN as usual; phase ph uses taps [ph*ntaps,
+  // (ph+1)*ntaps) of the tap tables and adds ph_o[ph] / ph_r[ph] to the output / residual pixel offsets (these
+  // already carry -ph * Cout, so "pixel offset + stacked column" addresses the right channel).  nphase = 1: off.
+  int nphase, tpn;
+  long long ph_o[4], ph_r[4];
+
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
   int* err;  // device word set non-zero when a pipeline wait timed out

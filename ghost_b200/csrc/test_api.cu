@@ -111,6 +111,9 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
       static const int kk[2][2] = {{1, 3}, {0, 2}};
       Act out;
       out.p = y; out.N = N; out.H = 2 * H; out.W = 2 * W; out.C = Cout; out.dtype = dt;
+      const bool merged = dt != kF32 && Cin % 64 == 0 && Cout % 16 == 0;   // as the network plans do
+      std::vector<float> all_rows;
+      DeconvPhases dp;
       for (int ph = 0; ph < 4; ++ph) {
         const int r = ph >> 1, q = ph & 1;
         std::vector<float> rows(static_cast<size_t>(Cout) * 4 * Cin);
@@ -120,12 +123,38 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
               for (int ci = 0; ci < Cin; ++ci)
                 rows[(static_cast<size_t>(co) * 4 + th * 2 + tw) * Cin + ci] =
                     w_host[((static_cast<size_t>(ci) * Cout + co) * 4 + kk[r][th]) * 4 + kk[q][tw]];
+        if (merged) {
+          all_rows.insert(all_rows.end(), rows.begin(), rows.end());
+          dp.taps[ph] = Taps::deconv_phase(r, q);
+          dp.o_off[ph] = OutView::deconv_phase(out, r, q, 0).off;
+          continue;
+        }
         const PackedW pw = make_w(rows, 4 * Cin);
         LaunchOp op;
         check_msg(lower_conv(&op, in, 0, Cin, Taps::deconv_phase(r, q), H, W, pw, OutView::deconv_phase(out, r, q, 0),
                              e, dt == kF32, device_err_word(), nullptr, bn_hint),
                   "test deconv lower");
         check_msg(op.launch(s), "test deconv launch");
+      }
+      if (merged) {
+        // the four phases as one launch: matrices (and bias) stacked along the rows
+        PackedW pw;
+        pw.Cout = 4 * Cout;
+        pw.K = 4 * Cin;
+        pw.rows_pad = (4 * Cout + 255) / 256 * 256;
+        std::vector<float> padded(static_cast<size_t>(pw.rows_pad) * pw.K, 0.f);
+        memcpy(padded.data(), all_rows.data(), all_rows.size() * sizeof(float));
+        pw.wb = pool.upload_16(padded, dt == kF16);
+        if (bias_host) {
+          std::vector<float> b(pw.rows_pad, 0.f);
+          for (int ph = 0; ph < 4; ++ph) memcpy(b.data() + ph * Cout, bias.data(), sizeof(float) * Cout);
+          pw.bias = pool.upload(b);
+        }
+        LaunchOp op;
+        check_msg(lower_conv(&op, in, 0, Cin, dp.taps[0], H, W, pw, OutView::deconv_phase(out, 0, 0, 0), e, false,
+                             device_err_word(), nullptr, bn_hint, &dp),
+                  "test deconv lower (merged phases)");
+        check_msg(op.launch(s), "test deconv launch (merged phases)");
       }
     }
     check_cuda(cudaStreamSynchronize(s), "test conv sync");

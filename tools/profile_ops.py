@@ -9,10 +9,10 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 bb = sys.argv[2] if len(sys.argv) > 2 else "unet"
 nb = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 CLS = ["conv_tc", "aad_tc", "conv_simt", "stats", "upsample", "misc"]
-G = ghost_b200.AEI_Net(bb, nb, 512).eval().bfloat16().cuda()
-arc = ghost_b200.iresnet100().eval().bfloat16().cuda()
+G = ghost_b200.AEI_Net(bb, nb, 512).eval().half().cuda()
+arc = ghost_b200.iresnet100().eval().half().cuda()
 crops = torch.from_numpy(synth.crops_u8(B)).cuda()
-z = arc.embed_hwc(torch.from_numpy(synth.sources_u8(B)).cuda(), out_dtype=torch.bfloat16)
+z = arc.embed_hwc(torch.from_numpy(synth.sources_u8(B)).cuda(), out_dtype=torch.float16)
 G.swap_u8(crops, z)
 torch.cuda.synchronize()
 for name, net in (("AEI_Net %s/%d" % (bb, nb), G), ("iresnet100", arc)):
