@@ -235,6 +235,7 @@ void Net::build_aei(ExecPlan& p) {
     LaunchOp lop;
     lop.name = name;
     check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad, 0, phases), name);
+    if (lop.ws_bytes) lop.set_workspace(p.pool.alloc(lop.ws_bytes));  // split-K partial tiles
     Op op;
     op.name = name;
     op.flops = lop.flops;

@@ -1,7 +1,9 @@
 #include "conv.cuh"
 
 #include <cudaTypedefs.h>
+#include <stdio.h>
 #include <stdlib.h>
+#include <string>
 #include <string.h>
 
 namespace ghost {
@@ -293,33 +295,51 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const int force2 = bn_hint >> 10;
     const long long tiles_m2 = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
     const int nph = phases ? 4 : 1;
-    bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
-    if (pair_ok) {
-      // Cost of a K block per SM, measured on B200 (tools/conv_sweep.py, us): one CTA 0.276 / 0.29 / 0.425 at N tiles
-      // of 64 / 128 / 256 (operand delivery: 16 KB + BN*128 B per block), CTA pair 0.237 / 0.258 / 0.38 (16 KB +
-      // BN*64 B; 0.38 us is the tensor-core time of a 128 x 256 x 64 block at the measured 1.63 PFLOP/s).  Both
-      // kernels run rounds of a persistent grid: 148 CTAs / 74 pairs.
-      const int cpad = (cout_t + 15) / 16 * 16;
-      auto t1 = [](int bn) { return bn <= 128 ? 0.262 + 0.00022 * bn : 0.29 + 0.00105 * (bn - 128); };
-      auto t2 = [](int bn) { return bn <= 128 ? 0.216 + 0.00033 * bn : 0.258 + 0.00095 * (bn - 128); };
-      const int cands[4] = {256, 128, 64, cpad < 256 ? cpad : 256};
-      double best1 = 1e30, best2 = 1e30;
-      int bn2 = 0;
-      for (int i = 0; i < 4; ++i) {
-        const int c = cands[i];
-        if ((c > cpad && c != cands[3]) || (bn_ && c != bn_)) continue;
-        if (phases && cout_t % c) continue;
-        const long long nt = static_cast<long long>(nph) * ((cout_t + c - 1) / c);
-        const double c1 = static_cast<double>((tiles_m2 * nt + 147) / 148) * t1(c);
-        const double c2 = static_cast<double>((((tiles_m2 + 1) / 2) * nt + 73) / 74) * t2(c);
-        if (c1 < best1) best1 = c1;
+    const int nkb_all = taps.n * p.kc_per_tap;
+    auto t1 = [](int bn) { return bn <= 128 ? 0.262 + 0.00022 * bn : 0.29 + 0.00105 * (bn - 128); };
+    auto t2 = [](int bn) { return bn <= 128 ? 0.216 + 0.00033 * bn : 0.258 + 0.00095 * (bn - 128); };
+    // Cost of a K block per SM, measured on B200 (tools/conv_sweep.py, us): one CTA 0.276 / 0.29 / 0.425 at N tiles
+    // of 64 / 128 / 256 (operand delivery: 16 KB + BN*128 B per block), CTA pair 0.237 / 0.258 / 0.38 (16 KB +
+    // BN*64 B; 0.38 us is the tensor-core time of a 128 x 256 x 64 block at the measured 1.63 PFLOP/s).  Both
+    // kernels run rounds of a persistent grid: 148 CTAs / 74 pairs.  Split-K (one-CTA kernel, one round): K blocks
+    // of a tile spread over `s` CTAs + a reduce pass (~3 us + the fp32 partial tiles through L2).
+    const int cpad0 = (cout_t + 15) / 16 * 16;
+    const int cands0[4] = {256, 128, 64, cpad0 < 256 ? cpad0 : 256};
+    double best1 = 1e30, best2 = 1e30, best3 = 1e30;
+    int bn2 = 0, bn3 = 0, s3 = 1;
+    static const int splitk_mode = [] {
+      const char* e = getenv("GHOST_SPLITK");  // A/B switch for profiling: GHOST_SPLITK=0 turns split-K off
+      return e ? atoi(e) : 1;
+    }();
+    const bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
+    const bool split_ok = !win && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
+    for (int i = 0; i < 4; ++i) {
+      const int c = cands0[i];
+      if ((c > cpad0 && c != cands0[3]) || (bn_ && c != bn_)) continue;
+      if (phases && cout_t % c) continue;
+      const long long nt = static_cast<long long>(nph) * ((cout_t + c - 1) / c);
+      const double c1 = static_cast<double>((tiles_m2 * nt + 147) / 148) * nkb_all * t1(c);
+      if (c1 < best1) best1 = c1;
+      if (pair_ok) {
+        const double c2 = static_cast<double>((((tiles_m2 + 1) / 2) * nt + 73) / 74) * nkb_all * t2(c);
         if (c2 < best2 || (c2 == best2 && c > bn2)) best2 = c2, bn2 = c;
       }
-      if (bn_ && !bn2) bn2 = bn_;
-      if (bn2 && (force2 == 1 || best2 < 0.98 * best1)) {
-        p.cta2 = 1;
-        bn_ = bn2;
+      if (split_ok && tiles_m2 * nt <= 74) {
+        for (int sp = 2; sp <= 49; ++sp) {
+          if (nkb_all % sp || nkb_all / sp < 4 || tiles_m2 * nt * sp > 148) continue;
+          const double ws_mb = static_cast<double>(sp) * tiles_m2 * 128 * nt * c * 4.0 / 1e6;
+          const double c3 = (nkb_all / sp) * t1(c) + 3.0 + ws_mb * 2.0 / 4.0;  // written + read at ~4 TB/s (L2)
+          if (c3 < best3) best3 = c3, bn3 = c, s3 = sp;
+        }
       }
+    }
+    if (bn_ && !bn2) bn2 = bn_;
+    if (bn3 && best3 < 0.85 * (best1 < best2 ? best1 : best2)) {
+      p.splits = s3;
+      bn_ = bn3;
+    } else if (pair_ok && bn2 && (force2 == 1 || best2 < 0.98 * best1)) {
+      p.cta2 = 1;
+      bn_ = bn2;
     }
     if (!bn_) {
       // Measured on B200 (tools/conv_sweep.py): with one CTA per SM a K block costs ~0.40 us whatever the N tile
@@ -406,11 +426,11 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   // bound: bytes in flight / ~1.8 us).
   {
     const int nkb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
-    p.dual = !aad && !p.cta2 && stages >= 4 && 2 * nkb <= stages;
+    p.dual = !aad && !p.cta2 && p.splits == 1 && stages >= 4 && 2 * nkb <= stages;
   }
   p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
   // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring
-  if (!aad && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
+  if (!aad && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
       !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&
       (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8))) &&
       256 * p.BN <= stages * stage_bytes) {
@@ -499,6 +519,20 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     if (epi.out2 && (!is16(out.dtype) || w.Cout % 16)) return "lower_conv: the second output needs a 16-bit tensor and Cout % 16 == 0";
     if (is16(out.dtype) && w.Cout % 16 == 0 && ((out.off % 8) || (out.sw % 8) || (out.sh % 8) || (out.sn % 8)))
       return "lower_conv: bf16 output view must be 16-byte aligned";
+    static const int dbg = [] {
+      const char* e = getenv("GHOST_LOWER_DEBUG");  // prints the kernel variant picked for every lowered conv
+      return e ? atoi(e) : 0;
+    }();
+    if (dbg)
+      fprintf(stderr, "lower_conv: N=%d %dx%d Cin=%d Cout=%d taps=%d%s -> %s BN=%d tiles=%dx%d kb=%d stages=%d%s\n", in.N, Ho,
+              Wo, Cin, w.Cout, taps.n, phases ? " x4 phases" : "",
+              p.splits > 1 ? "split-K" : (p.cta2 ? "CTA pair" : (p.a_win ? "row window" : "one CTA")), p.BN,
+              p.tiles_w * p.tiles_h * p.tiles_nb, p.tiles_n, p.ntaps * p.kc_per_tap / p.splits, p.stages,
+              p.splits > 1 ? (std::string(" splits=") + std::to_string(p.splits)).c_str() : "");
+    if (p.splits > 1) {
+      p.ws_cols = p.tiles_n * p.BN;
+      op->ws_bytes = static_cast<size_t>(p.splits) * p.tiles_w * p.tiles_h * p.tiles_nb * 128 * p.ws_cols * sizeof(float);
+    }
   }
   return nullptr;
 }

@@ -118,8 +118,16 @@ struct LaunchOp {
   std::shared_ptr<RgbConvConst> rgb;  // Cin = 3 stems: weights by value in the kernel parameters (simt.cuh)
   std::string name;
   double flops = 0.0;
+  // split-K (ig.splits > 1): bytes of fp32 workspace the caller must provide through set_workspace() before launch
+  size_t ws_bytes = 0;
+  void set_workspace(void* ws) { ig.ws = static_cast<float*>(ws); }
   const char* launch(cudaStream_t s) const {
     if (kind == kSimt && rgb) return rgb_const_launch(sc, *rgb, simt_dtype, s);
+    if (kind == kIgemm && ig.splits > 1) {
+      if (!ig.ws) return "split-K op launched without its workspace";
+      if (const char* e = igemm_launch(ig, s)) return e;
+      return splitk_reduce_launch(ig, s);
+    }
     return kind == kIgemm ? igemm_launch(ig, s) : kind == kTapn ? tapn_launch(tp, s) : simt_conv_launch(sc, simt_dtype, s);
   }
 };

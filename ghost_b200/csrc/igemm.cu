@@ -185,17 +185,18 @@ __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (
           }
 }
 
-template <bool F16>
+// FINAL: called by the split-K reduce kernel with the summed accumulators (p.splits > 1 there too)
+template <bool F16, bool FINAL = false>
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
                                                    long long o_pix, long long r_pix, const float* sp, int j) {
           float f[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.splits > 1) {
-            float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
+          if (!FINAL && p.splits > 1) {
+            // partial tile of this K range: o_pix is the row offset inside the workspace
+            float4* o = reinterpret_cast<float4*>(p.ws + o_pix + col0);
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (col0 + i < p.n_valid) atomicAdd(o + i, f[i]);
+            for (int i = 0; i < 4; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
             return;
           }
           linear_bias_act_16(p, f, col0, sp, j);
@@ -331,7 +332,11 @@ struct LinEpi {
         const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
         const uint32_t t_addr = tmem_lanes + as * acc_stride;
         const int ph = p.nphase > 1 ? t.nt / p.tpn : 0;
-        const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off + (p.nphase > 1 ? p.ph_o[ph] : 0);
+        const long long o_pix =
+            p.splits > 1
+                ? ((static_cast<long long>(blockIdx.y) * p.tiles_nb * p.tiles_h * p.tiles_w +
+                    (static_cast<long long>(t.tn) * p.tiles_h + t.th) * p.tiles_w + t.tw) * 128 + r) * p.ws_cols
+                : n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off + (p.nphase > 1 ? p.ph_o[ph] : 0);
         const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off + (p.nphase > 1 ? p.ph_r[ph] : 0);
         const int nch = p.BN >> 4, ch0 = (nch * ew) >> 2, ch1 = (nch * (ew + 1)) >> 2;
         const int colw = t.nt * p.BN + ew * wcols;  // staged path: first column of this warp
@@ -447,7 +452,8 @@ struct LinEpi {
             tmem_ld16(t_addr + j, v);
             tmem_ld_wait();
             const int col0 = t.nt * p.BN + j;
-            if (valid && col0 < p.n_valid) linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
+            if ((valid || p.splits > 1) && col0 < p.n_valid)
+              linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
           }
         }
         // hand the accumulator stage back to the MMA warp
@@ -1337,6 +1343,58 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Split-K, second pass: one thread per (GEMM row, 16 columns) adds the partial tiles in split order (deterministic)
+// and runs the linear epilogue of the op.
+template <bool F16>
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const __grid_constant__ IgemmParams p) {
+  const int chunks = p.ws_cols >> 4;
+  const long long rows_tot = static_cast<long long>(p.tiles_nb) * p.tiles_h * p.tiles_w * 128;
+  const long long idx = blockIdx.x * 256LL + threadIdx.x;
+  if (idx >= rows_tot * chunks) return;
+  const int ch = static_cast<int>(idx % chunks);
+  const long long row = idx / chunks;
+  const int r = static_cast<int>(row & 127);
+  int m = static_cast<int>(row >> 7);
+  const int tw = m % p.tiles_w;
+  m /= p.tiles_w;
+  const int th = m % p.tiles_h, tn = m / p.tiles_h;
+  const int rn = r / (p.bh * p.bw), rh = (r / p.bw) % p.bh, rw = r % p.bw;
+  const int n = tn * p.bn + rn, oh = th * p.bh + rh, ow = tw * p.bw + rw;
+  const int col0 = ch * 16;
+  if (r >= p.bw * p.bh * p.bn || n >= p.Nimg || oh >= p.Ho || ow >= p.Wo || col0 >= p.n_valid) return;
+  float f[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) f[i] = 0.f;
+  const float4* src = reinterpret_cast<const float4*>(p.ws + row * p.ws_cols + col0);
+  const long long split_stride = rows_tot * p.ws_cols / 4;
+  for (int s = 0; s < p.splits; ++s) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float4 q = src[s * split_stride + i];
+      f[4 * i] += q.x, f[4 * i + 1] += q.y, f[4 * i + 2] += q.z, f[4 * i + 3] += q.w;
+    }
+  }
+  uint32_t v[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(f[i]);
+  const int ph = p.nphase > 1 ? (col0 / p.BN) / p.tpn : 0;
+  const long long o_pix = n * p.o_sn + oh * p.o_sh + ow * p.o_sw + p.o_off + (p.nphase > 1 ? p.ph_o[ph] : 0);
+  const long long r_pix = n * p.r_sn + oh * p.r_sh + ow * p.r_sw + p.r_off + (p.nphase > 1 ? p.ph_r[ph] : 0);
+  linear_epilogue_16<F16, true>(p, v, col0, o_pix, r_pix, nullptr, 0);
+}
+
+const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream) {
+  if (p.splits < 2 || !p.ws || p.ws_cols % 16) return "splitk_reduce: not a split-K op";
+  const long long rows_tot = static_cast<long long>(p.tiles_nb) * p.tiles_h * p.tiles_w * 128;
+  const long long total = rows_tot * (p.ws_cols >> 4);
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  if (p.f16) splitk_reduce_kernel<true><<<blocks, 256, 0, stream>>>(p);
+  else splitk_reduce_kernel<false><<<blocks, 256, 0, stream>>>(p);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
+}
+
 int igemm_smem_bytes(const IgemmParams& p) {
   if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024;
   const int row_bytes = p.kc * 2;
@@ -1460,7 +1518,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
     return "igemm: bad tmem_cols";
   if (p.splits < 1 || (p.ntaps * p.kc_per_tap) % p.splits) return "igemm: splits must divide the K blocks";
   if (p.ntaps * (p.nphase > 1 ? p.nphase : 1) > kIgemmMaxTaps) return "igemm: too many taps";
-  if (p.nphase > 1 && (p.nphase != 4 || p.mode != kModeLinear || p.a_win || p.b_res || p.splits != 1 || p.tpn < 1 ||
+  if (p.nphase > 1 && (p.nphase != 4 || p.mode != kModeLinear || p.a_win || p.b_res || p.tpn < 1 ||
                        p.tiles_n != p.nphase * p.tpn))
     return "igemm: output phases need a plain linear-mode launch";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))

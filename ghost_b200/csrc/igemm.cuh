@@ -37,7 +37,8 @@ struct alignas(64) IgemmParams {
   int ntaps, kc_per_tap;
   int a_c0;                       // first input channel inside the inner dimension
   int b_k0;                       // first K column inside the packed weight matrix
-  int splits;                     // split-K factor (grid.y); >1 => fp32 atomic accumulate
+  int splits;                     // split-K factor (grid.y); > 1: CTA row y handles K blocks [y, y+1) * nkb / splits and
+                                  // stores its fp32 partial tile into ws (below); splitk_reduce_launch finishes the op
   short tap_c[kIgemmMaxTaps];     // added to the channel coordinate (parity * C for 5-D maps)
   short tap_w[kIgemmMaxTaps];     // added to the w coordinate
   short tap_p[kIgemmMaxTaps];     // h-parity coordinate (5-D maps only)
@@ -117,6 +118,12 @@ struct alignas(64) IgemmParams {
   int nphase, tpn;
   long long ph_o[4], ph_r[4];
 
+  // Deterministic split-K for layers with a handful of output tiles and a long K (2x2 .. 8x8 feature maps, the
+  // ArcFace FC): partial accumulators [splits][tiles_m * 128 rows][ws_cols] fp32, plain stores; the reduce kernel adds
+  // them in split order and applies the whole linear epilogue (bias, activation, residual, second output).
+  float* ws;
+  int ws_cols;  // tiles_n * BN
+
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
   int* err;  // device word set non-zero when a pipeline wait timed out
@@ -124,6 +131,8 @@ struct alignas(64) IgemmParams {
 
 // Host side (igemm.cu)
 const char* igemm_launch(const IgemmParams& p, cudaStream_t stream);
+// second pass of a split-K op: `p` is the op's parameter block (real output, epilogue, ws, splits)
+const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream);
 int igemm_smem_bytes(const IgemmParams& p);
 
 }  // namespace ghost

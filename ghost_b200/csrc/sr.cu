@@ -271,6 +271,7 @@ void Net::build_sr(ExecPlan& p) {
     LaunchOp lop;
     lop.name = name;
     check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad), name);
+    if (lop.ws_bytes) lop.set_workspace(p.pool.alloc(lop.ws_bytes));  // split-K partial tiles
     Op op;
     op.name = name;
     op.flops = real_flops;

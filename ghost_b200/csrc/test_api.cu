@@ -88,6 +88,7 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
       check_msg(lower_conv(&op, in, 0, Cin, Taps::square(k, pad, stride), Ho, Wo, pw, OutView::dense(out), e,
                            dt == kF32, device_err_word(), nullptr, bn_hint),
                 "test conv lower");
+      if (op.ws_bytes) op.set_workspace(pool.alloc(op.ws_bytes));
       check_msg(op.launch(s), "test conv launch");
       if (const char* ev = getenv("GHOST_TEST_CONV_REPS")) {
         const int reps = atoi(ev);
@@ -134,6 +135,7 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
         check_msg(lower_conv(&op, in, 0, Cin, Taps::deconv_phase(r, q), H, W, pw, OutView::deconv_phase(out, r, q, 0),
                              e, dt == kF32, device_err_word(), nullptr, bn_hint),
                   "test deconv lower");
+        if (op.ws_bytes) op.set_workspace(pool.alloc(op.ws_bytes));
         check_msg(op.launch(s), "test deconv launch");
       }
       if (merged) {
@@ -154,6 +156,7 @@ int ghost_test_conv(const void* x, int N, int H, int W, int Cin, const float* w_
         check_msg(lower_conv(&op, in, 0, Cin, dp.taps[0], H, W, pw, OutView::deconv_phase(out, 0, 0, 0), e, false,
                              device_err_word(), nullptr, bn_hint, &dp),
                   "test deconv lower (merged phases)");
+        if (op.ws_bytes) op.set_workspace(pool.alloc(op.ws_bytes));
         check_msg(op.launch(s), "test deconv launch (merged phases)");
       }
     }

@@ -124,11 +124,23 @@ def test_forward_matches_oracle_odd_batch(mode, golden_dir):
         tol = {"bf16": 3e-2, "fp16": 4e-3, "fp32": 2e-4}[mode] * max(1.0, r.abs().max().item())
         assert (a.float().cpu() - r).abs().max().item() <= tol
     # per-sample independence: crop 1 alone gives the same result as inside the batch
-    # (tile shapes differ with the batch size, so accumulation order - not the function - may differ)
+    # (tile shapes, split-K factors and with them the accumulation order - not the function - differ with the batch
+    # size; with these ill-conditioned weights every changed fp16 rounding is amplified like the fp16-vs-fp32
+    # distance itself, so the fp16 bound is that distance: the reference's own G.half() vs fp32 on this architecture)
     Y1, _ = G(Xt[1:2].cuda().to(dt), z[1:2].cuda().to(dt))
     d1 = (Y1.float() - Y[1:2].float()).abs()
-    assert d1.mean().item() <= {"bf16": 3e-3, "fp16": 4e-4, "fp32": 1e-6}[mode]
-    assert d1.max().item() <= {"bf16": 1.0, "fp16": 1e-1, "fp32": 2e-5}[mode]
+    dr = (Y1.float().cpu() - Yr[1:2]).abs()
+    if mode == "fp16":
+        rh_max, rh_mean = np.load(os.path.join(golden_dir, "aei_half_ref.npz"))["aei_unet2_perturbed"]
+        assert d1.mean().item() <= rh_mean and dr.mean().item() <= 1.5 * rh_mean and dr.max().item() <= 1.5 * rh_max, (
+            d1.mean().item(), dr.mean().item(), dr.max().item(), rh_mean, rh_max)
+    elif mode == "bf16":   # the batch-size effect is no larger than the bf16 distance to the fp32 forward itself
+        dm = d.mean().item()
+        assert d1.mean().item() <= max(3e-3, dm) and dr.mean().item() <= 1.5 * dm + 2e-4, (d1.mean().item(),
+                                                                                            dr.mean().item(), dm)
+    else:
+        assert d1.mean().item() <= 1e-6 and d1.max().item() <= 2e-5
+        assert dr.max().item() <= 5 * FP32_NOISE["aei_unet2_perturbed"]
 
 
 def test_blocks_match_bf16_emulation():
