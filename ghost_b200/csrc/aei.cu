@@ -229,13 +229,19 @@ void Net::build_aei(ExecPlan& p) {
   };
   auto add_conv = [&](const std::string& name, const Act& in, int c0, int Cin, const Taps& taps, int Ho, int Wo,
                       const std::string& wname, const OutView& out, const Epilogue& epi, const AadArgs* aad,
-                      const DeconvPhases* phases = nullptr) {
+                      const DeconvPhases* phases = nullptr, float** stats_parts = nullptr, int* stats_P = nullptr) {
     auto it = packed_.find(wname);
     if (it == packed_.end()) fail(-2, "internal: packed weights missing for " + wname);
     LaunchOp lop;
     lop.name = name;
     check_msg(lower_conv(&lop, in, c0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, aad, 0, phases), name);
     if (lop.ws_bytes) lop.set_workspace(p.pool.alloc(lop.ws_bytes));  // split-K partial tiles
+    if (lop.st_floats) {                                               // fused InstanceNorm statistics of the output
+      float* parts = p.pool.alloc_n<float>(lop.st_floats);
+      lop.set_stats(parts);
+      if (stats_parts) *stats_parts = parts;
+      if (stats_P) *stats_P = lop.ig.st_P;
+    }
     Op op;
     op.name = name;
     op.flops = lop.flops;
@@ -384,7 +390,7 @@ void Net::build_aei(ExecPlan& p) {
       float4* ncpar;
       float *whf, *bhf, *mask;
     };
-    auto aad_fold = [&](const std::string& lname, const float* sums) {
+    auto aad_fold = [&](const std::string& lname, const float* sums, int sums_P) {
       const AadInfo& info = aad_.at(lname);
       AadPre q;
       q.ncpar = p.pool.alloc_n<float4>(static_cast<size_t>(B) * b.cin);
@@ -398,12 +404,13 @@ void Net::build_aei(ExecPlan& p) {
       float4* ncpar = q.ncpar;
       float *whf = q.whf, *bhf = q.bhf;
       add_op(lname + ".fold", [=](cudaStream_t s) {
-        return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, fsc, s);
+        return aad_fold_launch(sums, sums_P, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncpar, whf, bhf, fsc, s);
       });
       return q;
     };
-    auto aad_layer = [&](const std::string& lname, const Act& h, const float* sums, const AadPre* pre = nullptr) {
-      const AadPre q = pre ? *pre : aad_fold(lname, sums);
+    auto aad_layer = [&](const std::string& lname, const Act& h, const float* sums, int sums_P,
+                         const AadPre* pre = nullptr) {
+      const AadPre q = pre ? *pre : aad_fold(lname, sums, sums_P);
       float4* ncpar = q.ncpar;
       float *whf = q.whf, *bhf = q.bhf;
       const int cx = b.cin;
@@ -468,8 +475,8 @@ void Net::build_aei(ExecPlan& p) {
     AadPre pre_sc{}, pre_0{};
     const bool mask2 = bf && !pair && b.cin != b.cout && b.cin > 128;
     if (mask2) {
-      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m);
-      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m);
+      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m, parts_in);
+      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m, parts_in);
       pre_sc.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       pre_0.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       const Act mm = m;
@@ -481,17 +488,27 @@ void Net::build_aei(ExecPlan& p) {
     }
     if (b.cin != b.cout) {
       sc = new_act(hw, hw, b.cout);
-      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, mask2 ? &pre_sc : nullptr);
+      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, parts_in, mask2 ? &pre_sc : nullptr);
       add_conv(S("blk%d.convsc", k), pair ? a2 : a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
                OutView::dense(sc), Epilogue(), nullptr);
     }
     Act x = m;
     const float* sums_x = sums_m;
+    int sums_xP = parts_in;
     Act y;
+    // tensor-core modes, images of >= 256 pixels: the statistics of a conv output that feeds the next AADLayer come
+    // out of that conv's epilogue (igemm.cuh st_mode) instead of a separate pass over the tensor
+    static const int fuse_stats_env = [] {
+      const char* e = getenv("GHOST_FUSE_STATS");  // A/B switch for profiling: GHOST_FUSE_STATS=0 keeps in_stats_kernel
+      return e ? atoi(e) : 1;
+    }();
+    // (measured: worth it where the conv is K-heavy, blocks 4-6; in the thin-K row-window convs of blocks 7-8 the
+    // epilogue is the bottleneck and the column sums cost more there than the separate pass over the tensor)
+    const bool fuse_stats = bf && HW >= 256 && HW <= 4096 && fuse_stats_env != 0;
     for (int i = 0; i < num_blocks; ++i) {
       const bool last = i == num_blocks - 1;
       const bool from_pair = pair && i == 0;
-      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x, (mask2 && i == 0) ? &pre_0 : nullptr);
+      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x, sums_xP, (mask2 && i == 0) ? &pre_0 : nullptr);
       const int co = last ? b.cout : b.cin;
       Act o = new_act(hw, hw, co);
       Epilogue e;
@@ -502,15 +519,22 @@ void Net::build_aei(ExecPlan& p) {
         e.r_sn = rv.sn; e.r_sh = rv.sh; e.r_sw = rv.sw; e.r_off = rv.off;
         if (k == 8) e.act2 = kAct2Tanh;
       }
+      float* fused_parts = nullptr;
+      int fused_P = 0;
+      e.want_stats = !last && fuse_stats;
       add_conv(S("blk%d.conv%d", k, i), from_pair ? a2 : a, from_pair ? b.cin : 0, b.cin, Taps::square(3, 1, 1), hw, hw,
-               S("blk%d.conv%d", k, i), OutView::dense(o), e, nullptr);
-      if (!last) {
+               S("blk%d.conv%d", k, i), OutView::dense(o), e, nullptr, nullptr, &fused_parts, &fused_P);
+      if (!last && fused_parts) {
+        sums_x = fused_parts;
+        sums_xP = fused_P;
+      } else if (!last) {
         float* sums_o = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * co);  // co == b.cin here
         const Act oo = o;
         add_op(S("blk%d.stats%d", k, i + 1),
                [=](cudaStream_t s) { return in_stats_launch(oo.p, dt, B, HW, oo.C, sums_o, s); }, kOpStats,
                static_cast<double>(B) * HW * oo.C * esz);
         sums_x = sums_o;
+        sums_xP = parts_in;
       }
       x = o;
       y = o;

@@ -312,7 +312,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       return e ? atoi(e) : 1;
     }();
     const bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
-    const bool split_ok = !win && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
+    const bool split_ok = !win && !epi.want_stats && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
     for (int i = 0; i < 4; ++i) {
       const int c = cands0[i];
       if ((c > cpad0 && c != cands0[3]) || (bn_ && c != bn_)) continue;
@@ -381,14 +381,26 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   }
   int stage_bytes = p.cta2 ? (128 + p.BN / 2) * 128 : (128 + p.BN) * p.kc * 2;
   int resident_bytes = 0;
+  // fused output statistics: tiles inside one image, whole 64-column warp quarters, no split-K
+  const bool stats = epi.want_stats && !aad;
+  if (stats) {
+    if (p.bn != 1 || p.BN % 64 || w.Cout % p.BN || p.splits != 1 || phases)
+      return "lower_conv: fused output statistics need tiles inside one image and N tiles of whole 64-column quarters";
+    const long long tpi = static_cast<long long>(p.tiles_w) * p.tiles_h;
+    p.st_mode = (tpi <= 148 || p.tiles_n != 1) ? 1 : 2;
+    p.st_P = p.st_mode == 1 ? static_cast<int>(tpi) : 148;
+    p.st_C = w.Cout;
+    op->st_floats = static_cast<size_t>(in.N) * (2 * p.st_P + 1) * p.st_C;
+  }
+  const int st_bytes = stats ? 8192 : 0;
   if (win) {
     const int b_tile = p.BN * 128;
     const int slab = 9 * p.kc_per_tap * b_tile;
     p.a_win = win_mode;
-    p.b_res = p.tiles_n == 1 && (221 * 1024 - slab) / (17 * 1024) >= 4;
+    p.b_res = p.tiles_n == 1 && (221 * 1024 - st_bytes - slab) / (17 * 1024) >= 4;
     stage_bytes = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
     resident_bytes = p.b_res ? slab : 0;
-    if ((221 * 1024 - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
+    if ((221 * 1024 - st_bytes - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
   }
   p.sets = 2;
   int aad_bytes = 0;
@@ -411,7 +423,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       aad_bytes = p.h_bufs * hbox * 16384;
     }
   }
-  int stages = (221 * 1024 - aad_bytes - resident_bytes) / stage_bytes;
+  int stages = (221 * 1024 - st_bytes - aad_bytes - resident_bytes) / stage_bytes;
   if (stages > 8) stages = 8;
   static const int max_stages = [] {
     const char* e = getenv("GHOST_MAX_STAGES");  // profiling switch: cap the operand ring depth
@@ -429,6 +441,16 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.dual = !aad && !p.cta2 && p.splits == 1 && stages >= 4 && 2 * nkb <= stages;
   }
   p.tmem_cols = aad ? 512 : pow2_at_least(2 * p.BN);
+  // thin-K tiles (a few K blocks): the latency of an epilogue pass (accumulator complete -> all 16 warps done) is a
+  // multiple of the tile's MMA time, so the issuers run up to three tiles ahead on four accumulator stages
+  static const int sets4_mode = [] {
+    const char* e = getenv("GHOST_SETS4");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  if (!aad && !p.cta2 && sets4_mode && 4 * p.BN <= 512) {
+    p.sets = 4;
+    p.tmem_cols = pow2_at_least(4 * p.BN);
+  }
   // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring
   if (!aad && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
       !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&

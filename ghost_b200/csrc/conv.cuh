@@ -55,6 +55,10 @@ struct Epilogue {
   void* out2 = nullptr;
   const float* scale2 = nullptr;
   const float* shift2 = nullptr;
+  // tensor-core path: also produce the InstanceNorm partial statistics of the output (igemm.cuh st_mode); after
+  // lowering, LaunchOp::st_floats says how large the parts buffer must be (set_stats()), LaunchOp::ig.st_P is the P the
+  // fold kernel reads it with
+  bool want_stats = false;
 };
 
 struct OutView {
@@ -121,8 +125,15 @@ struct LaunchOp {
   // split-K (ig.splits > 1): bytes of fp32 workspace the caller must provide through set_workspace() before launch
   size_t ws_bytes = 0;
   void set_workspace(void* ws) { ig.ws = static_cast<float*>(ws); }
+  // fused output statistics (Epilogue::want_stats): floats of the parts buffer [N][2P+1][C]; zeroed at every launch
+  size_t st_floats = 0;
+  void set_stats(float* parts) { ig.st_parts = parts; }
   const char* launch(cudaStream_t s) const {
     if (kind == kSimt && rgb) return rgb_const_launch(sc, *rgb, simt_dtype, s);
+    if (kind == kIgemm && ig.st_mode) {
+      if (!ig.st_parts) return "conv with fused statistics launched without its parts buffer";
+      if (cudaMemsetAsync(ig.st_parts, 0, st_floats * sizeof(float), s) != cudaSuccess) return "stats parts memset failed";
+    }
     if (kind == kIgemm && ig.splits > 1) {
       if (!ig.ws) return "split-K op launched without its workspace";
       if (const char* e = igemm_launch(ig, s)) return e;

@@ -186,9 +186,11 @@ __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (
 }
 
 // FINAL: called by the split-K reduce kernel with the summed accumulators (p.splits > 1 there too)
+// stored (optional): receives the 16 values as they read back from the output tensor (for the fused statistics)
 template <bool F16, bool FINAL = false>
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
-                                                   long long o_pix, long long r_pix, const float* sp, int j) {
+                                                   long long o_pix, long long r_pix, const float* sp, int j,
+                                                   float* stored = nullptr) {
           float f[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
@@ -220,6 +222,10 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
           if (p.act2 == kAct2Tanh) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
+          }
+          if (stored) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) stored[i] = (col0 + i < p.n_valid) ? (p.out_f32 ? f[i] : round16<F16>(f[i])) : 0.f;
           }
           if (p.out_f32) {
             float* o = reinterpret_cast<float*>(p.out) + o_pix + col0;
@@ -285,7 +291,7 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
 // is complete the operand ring is idle, so every warp parks its 32 rows x wcols there (rows of P 16-byte pieces,
 // piece q of row r at slot q ^ stg_key(r): bank-conflict free) and moves whole row segments to / from global
 // memory - 4-8 cache lines per instruction instead of 32.
-template <bool F16>
+template <bool F16, bool STATS>
 struct LinEpi {
   int lane, lg, ew, r, rn, rh, rw, rows_used;
   int wcols, rowb, P, lgP, rb_row0, rb_piece, rb_step;
@@ -294,6 +300,12 @@ struct LinEpi {
   bool staged;
   uint32_t tmem_lanes;  // TMEM address of this warp's lane group, column 0
   int acc_stride;
+  // fused output statistics (igemm.cuh st_mode): per 16-column chunk of this warp, lane L holds the sum (L even) or
+  // the sum of squares (L odd) of column (L >> 1) & 15 over the rows seen so far
+  float st_acc[4];
+  float st_tmp[16];
+  int st_img, st_nt;
+  float* st_x;  // shared exchange [4 ew][4 lg][4 chunks][32 lanes]
 
   __device__ __forceinline__ void init(const IgemmParams& p, int warp, int lane_, uint8_t* ring, const float* eparm_,
                                        bool staged_, int rows_used_, uint32_t tmem_base, int acc_stride_) {
@@ -312,6 +324,75 @@ struct LinEpi {
     staged = staged_;
     tmem_lanes = tmem_base + (static_cast<uint32_t>(lg * 32) << 16);
     acc_stride = acc_stride_;
+    st_acc[0] = st_acc[1] = st_acc[2] = st_acc[3] = 0.f;
+    st_img = -1;
+    st_nt = 0;
+    st_x = reinterpret_cast<float*>(ring + p.stages * st_stage_bytes(p));
+  }
+  __device__ __forceinline__ static int st_stage_bytes(const IgemmParams& p) {
+    if (p.cta2) return 128 * 128 + (p.BN >> 1) * 128;
+    const int b_tile = p.BN * p.kc * 2;
+    return p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_tile) : 128 * p.kc * 2 + (p.b_res ? 0 : b_tile);
+  }
+  // Column sums over the 32 rows of this warp: a = values, b = their squares (16 columns per lane).  Exchanges with
+  // lane ^ 16, 8, 4, 2 halve the columns a lane carries and double the rows they cover; the last exchange leaves the
+  // sum in the even lane and the sum of squares in the odd lane of a pair.  31 shuffles, fixed order.
+  __device__ __forceinline__ float st_colsum(float (&a)[16], float (&b)[16]) const {
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1) {
+      const bool hi = (lane & (2 * w)) != 0;
+#pragma unroll
+      for (int i = 0; i < w; ++i) {
+        const float sa = hi ? a[i] : a[i + w], ka = hi ? a[i + w] : a[i];
+        const float sb = hi ? b[i] : b[i + w], kb = hi ? b[i + w] : b[i];
+        a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, 2 * w);
+        b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, 2 * w);
+      }
+    }
+    const bool odd = (lane & 1) != 0;
+    const float send = odd ? a[0] : b[0], keep = odd ? b[0] : a[0];
+    return keep + __shfl_xor_sync(0xffffffffu, send, 1);
+  }
+  __device__ __forceinline__ void st_zero() {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) st_tmp[i] = 0.f;
+  }
+  __device__ __forceinline__ void st_keep(const float (&f)[16]) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) st_tmp[i] = f[i];
+  }
+  __device__ __forceinline__ void st_add(int c, float (&stored)[16]) {
+    float sq[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sq[i] = stored[i] * stored[i];
+    st_acc[c] += st_colsum(stored, sq);
+  }
+  // the four lane-group warps of this column quarter add up in lane-group order and write one part
+  __device__ __forceinline__ void st_flush(const IgemmParams& p, int part) {
+    const int nchunk = wcols >> 4;
+    float* mine = st_x + ((ew * 4 + lg) * 4) * 32 + lane;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < nchunk) mine[c * 32] = st_acc[c];
+    named_bar_sync(1 + ew, 128);
+    if (lg == 0) {
+      const float* q = st_x + (ew * 4 * 4) * 32 + lane;
+      float* dst = p.st_parts + (static_cast<long long>(st_img) * (2 * p.st_P + 1) + 2 * part + (lane & 1)) * p.st_C +
+                   st_nt * p.BN + ew * wcols + ((lane >> 1) & 15);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c < nchunk) {
+          const float v = ((q[c * 32] + q[(4 + c) * 32]) + q[(8 + c) * 32]) + q[(12 + c) * 32];
+          if (st_nt * p.BN + ew * wcols + c * 16 < p.n_valid) dst[c * 16] = v;
+        }
+      }
+    }
+    named_bar_sync(1 + ew, 128);
+    st_acc[0] = st_acc[1] = st_acc[2] = st_acc[3] = 0.f;
+  }
+  // call after the last tile of the CTA
+  __device__ __forceinline__ void st_finish(const IgemmParams& p) {
+    if (STATS && p.st_mode == 2 && st_img >= 0) st_flush(p, blockIdx.x);
   }
   __device__ __forceinline__ int stg_key(int row) const { return ((row * rowb) >> 7) & (P - 1); }
 
@@ -327,7 +408,12 @@ struct LinEpi {
   // returns false when the pipeline was aborted (the caller leaves its tile loop)
   template <bool REMOTE>
   __device__ __forceinline__ bool tile(const IgemmParams& p, const TileCoord& t, int as, uint32_t aphase, bool use_stg,
-                                       uint64_t* tfull, uint64_t* tempty, volatile int* abort_flag) const {
+                                       uint64_t* tfull, uint64_t* tempty, volatile int* abort_flag) {
+        if (STATS) {  // bn == 1: the tile lies in image t.tn
+          if (p.st_mode == 2 && st_img >= 0 && st_img != t.tn) st_flush(p, blockIdx.x);
+          st_img = t.tn;
+          st_nt = t.nt;
+        }
         const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
         const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
         const uint32_t t_addr = tmem_lanes + as * acc_stride;
@@ -400,13 +486,26 @@ struct LinEpi {
                 o1.w = pack16<F16>(f[14], f[15]);
                 *s0 = o0;
                 *s1 = o1;
+                if (STATS) {
+                  const uint32_t ow_[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    f[2 * i] = lo16<F16>(ow_[i]);
+                    f[2 * i + 1] = hi16<F16>(ow_[i]);
+                  }
+                  st_keep(f);
+                }
+              } else if (STATS) {
+                st_zero();
               }
+              if (STATS) st_add(c, st_tmp);
             }
           }
           // the accumulator stage goes back to the MMA warp before the global stores
           tc_fence_before();
           __syncwarp();
           release<REMOTE>(tempty);
+          if (STATS && p.st_mode == 1) st_flush(p, t.th * p.tiles_w + t.tw);
           const int jt = ew * wcols + rb_piece * 8;  // tile column of this lane's 8 channels
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -453,13 +552,17 @@ struct LinEpi {
             tmem_ld_wait();
             const int col0 = t.nt * p.BN + j;
             if ((valid || p.splits > 1) && col0 < p.n_valid)
-              linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j);
+              linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j, STATS ? st_tmp : nullptr);
+            else if (STATS)
+              st_zero();
+            if (STATS) st_add(c, st_tmp);
           }
         }
         // hand the accumulator stage back to the MMA warp
         tc_fence_before();
         __syncwarp();
         release<REMOTE>(tempty);
+        if (STATS && p.st_mode == 1) st_flush(p, t.th * p.tiles_w + t.tw);
         return true;
   }
 };
@@ -555,7 +658,7 @@ __device__ __forceinline__ void mma_issuer(const IgemmParams& p, const int par, 
 #endif
 }
 
-template <bool F16>
+template <bool F16, bool STATS>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
@@ -820,17 +923,19 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     const int rw = r % p.bw;
     if (p.mode == kModeLinear) {
       // all 16 warps share every tile: warp ew takes a quarter of its columns
-      LinEpi<F16> epi;
+      LinEpi<F16, STATS> epi;
       epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
       int it = 0;
       TileWalk walk;
       walk.init(p, blockIdx.x, gridDim.x);
       for (int tile = blockIdx.x; tile < tiles_total; tile += gridDim.x, ++it, walk.next(p)) {
         const bool use_stg = p.stg && tile + static_cast<int>(gridDim.x) >= tiles_total;
-        const int as = it & 1;
-        if (!epi.template tile<false>(p, walk.t, as, (it >> 1) & 1, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag))
+        const int as = p.sets == 4 ? (it & 3) : (it & 1);
+        const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
+        if (!epi.template tile<false>(p, walk.t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag))
           break;
       }
+      if (!abort_flag) epi.st_finish(p);
     } else {
       // ---------------- AAD blend epilogue (network/AADLayer.py:20-38) ----------------
       // h arrives by TMA in shared memory (SWIZZLE_128B boxes of 64 channels); each warp blends its own 32 rows x
@@ -1163,7 +1268,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 // TMEM allocation.  Barriers: `full` lives in the leader (both CTAs' TMA loads count their bytes there), `empty` and
 // `tfull` are signalled in both CTAs by multicast commits, `tempty` lives in the leader and collects the epilogue
 // warps of both CTAs.
-template <bool F16>
+template <bool F16, bool STATS>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_constant__ IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
@@ -1318,7 +1423,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   } else if (warp >= kIgemmEpiWarp0) {
     // ============================== epilogue of this CTA's 128 rows ===========
     grid_dep_wait();
-    LinEpi<F16> epi;
+    LinEpi<F16, STATS> epi;
     epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
     int it = 0;
     for (int s = cluster; s < super_total; s += nclusters, ++it) {
@@ -1327,6 +1432,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
       const bool use_stg = p.stg && s + nclusters >= super_total;
       if (!epi.template tile<true>(p, t, as, (it >> 1) & 1, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) break;
     }
+    if (!abort_flag) epi.st_finish(p);
   }
 
   // ------------------------------ teardown ------------------------------------
@@ -1396,13 +1502,14 @@ const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream) {
 }
 
 int igemm_smem_bytes(const IgemmParams& p) {
-  if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024;
+  const int st = p.st_mode ? 8192 : 0;  // exchange buffer of the fused statistics, behind the operand ring
+  if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024 + st;
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
   const int b_tile = p.BN * row_bytes;
   const int resident = p.b_res ? p.ntaps * p.kc_per_tap * b_tile : 0;
   const int stage = p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_tile) : 128 * row_bytes + (p.b_res ? 0 : b_tile);
-  return p.stages * stage + resident + aad + 1024;
+  return p.stages * stage + resident + aad + 1024 + st;
 }
 
 namespace {
@@ -1426,19 +1533,23 @@ const char* igemm_dev_state(IgemmDevState* out) {
   IgemmDevState& st = g_dev_state[dev];
   if (!st.max_dyn_smem) {
     cudaFuncAttributes fa;
-    e = cudaFuncGetAttributes(&fa, igemm_kernel<false>);
+    e = cudaFuncGetAttributes(&fa, igemm_kernel<false, false>);
     int lim = 0;
     if (e == cudaSuccess) {
       lim = 227 * 1024 - static_cast<int>(fa.sharedSizeBytes);
-      e = cudaFuncSetAttribute(igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+      e = cudaFuncSetAttribute(igemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     }
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e == cudaSuccess) {
       cudaFuncAttributes fa2;
-      e = cudaFuncGetAttributes(&fa2, igemm2_kernel<false>);
+      e = cudaFuncGetAttributes(&fa2, igemm2_kernel<false, false>);
       const int lim2 = 227 * 1024 - static_cast<int>(fa2.sharedSizeBytes);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
       st.max_dyn_smem2 = lim2;
     }
     int sms = 0;
@@ -1493,7 +1604,11 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 2 : 1;
-  cudaError_t e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false>, p);
+  cudaError_t e;
+  if (p.st_mode)
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, true>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, true>, p);
+  else
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, false>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, false>, p);
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }
@@ -1510,7 +1625,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.stages < 2 || p.stages > 8) return "igemm: stages must be in [2,8]";
   if (p.dual && p.stages < 4) return "igemm: two issuers need at least four ring slots";
   if (p.sets != 2 && p.sets != 4) return "igemm: 2 or 4 accumulator stages";
-  if (p.mode == kModeLinear && p.sets != 2) return "igemm: the linear epilogue works on two accumulator stages";
+  if (p.mode == kModeLinear && p.sets != 2 && p.sets != 4) return "igemm: the linear epilogue works on two or four accumulator stages";
   if (p.mode == kModeAAD &&
       (p.sets * (p.BN >> 7) != 4 || (p.h_bufs != p.sets && p.h_bufs != 2 * p.sets) || p.dual || p.BN % 128))
     return "igemm: bad AAD staging";
@@ -1558,7 +1673,11 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1 : 0;
-  cudaError_t e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm_kernel<true>, p) : cudaLaunchKernelEx(&cfg, igemm_kernel<false>, p);
+  cudaError_t e;
+  if (p.st_mode)
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm_kernel<true, true>, p) : cudaLaunchKernelEx(&cfg, igemm_kernel<false, true>, p);
+  else
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm_kernel<true, false>, p) : cudaLaunchKernelEx(&cfg, igemm_kernel<false, false>, p);
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }

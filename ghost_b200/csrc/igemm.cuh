@@ -124,6 +124,16 @@ struct alignas(64) IgemmParams {
   float* ws;
   int ws_cols;  // tiles_n * BN
 
+  // InstanceNorm statistics of the OUTPUT in the epilogue (the next AADLayer normalises exactly this tensor,
+  // AADLayer.py:21): per-column sum and sum of squares of the values as stored, in the partial-sum layout of
+  // in_stats_kernel (simt.cu) with a zero shift row: st_parts [Nimg][2*st_P + 1][st_C].  Tiles lie inside one image.
+  //   st_mode 1: one part per tile of an image (st_P = tiles per image), every part written by exactly one CTA;
+  //   st_mode 2: one part per CTA (st_P >= grid size, buffer zeroed before the launch): a CTA adds up its
+  //              consecutive tiles of an image in registers and flushes when the image changes (one N tile only).
+  // Either way the fold kernel adds the parts in index order: deterministic.
+  float* st_parts;
+  int st_mode, st_P, st_C;
+
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
   int* err;  // device word set non-zero when a pipeline wait timed out

@@ -1,3 +1,4 @@
+#include <type_traits>
 #include "simt.cuh"
 
 #include <cuda_fp16.h>
@@ -79,6 +80,38 @@ __device__ __forceinline__ void load8<__half>(const __half* p, float (&v)[8]) {
     v[2 * i + 1] = f.y;
   }
 }
+// the same load in two steps, so that several loads can be in flight with only their raw 16 bytes live
+template <typename T>
+struct Raw8 {
+  uint4 q;
+  __device__ __forceinline__ void load(const T* p) { q = __ldg(reinterpret_cast<const uint4*>(p)); }
+  __device__ __forceinline__ void get(float (&v)[8]) const {
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (sizeof(T) == 2 && std::is_same<T, __half>::value) {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+        v[2 * i] = f.x;
+        v[2 * i + 1] = f.y;
+      } else {
+        v[2 * i] = __uint_as_float(w[i] << 16);
+        v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+      }
+    }
+  }
+};
+template <>
+struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = __ldg(reinterpret_cast<const float4*>(p));
+    b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  }
+  __device__ __forceinline__ void get(float (&v)[8]) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+    v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
 template <typename T>
 __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
 template <>
@@ -473,8 +506,9 @@ __device__ __forceinline__ void stats_accumulate8(const float (&v)[8], const flo
     q[i] = qn.x; q[i + 1] = qn.y;
   }
 }
+// (two blocks per SM at 86 registers left the kernel latency-bound at 37 % of the DRAM peak - ncu, round 2)
 template <typename T>
-__global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restrict__ x, int HW, int C,
+__global__ void __launch_bounds__(kStatThreads, 4) in_stats_kernel(const T* __restrict__ x, int HW, int C,
                                                                  int pix_per_block, float* __restrict__ parts,
                                                                  int common_shift) {
   extern __shared__ float sh[];  // [kStatThreads][16]
@@ -496,13 +530,17 @@ __global__ void __launch_bounds__(kStatThreads) in_stats_kernel(const T* __restr
   if (pl < ppi) {
     // four independent 16-byte loads in flight per thread: the kernel is a pure HBM stream
     for (int p = p0 + pl; p < p1; p += 4 * ppi) {
-      float v[4][8];
+      Raw8<T> raw[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (p + u * ppi < p1) load8(base + static_cast<long long>(p + u * ppi) * C, v[u]);
+        if (p + u * ppi < p1) raw[u].load(base + static_cast<long long>(p + u * ppi) * C);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        if (p + u * ppi < p1) stats_accumulate8(v[u], sft, s, q);
+        if (p + u * ppi < p1) {
+          float v[8];
+          raw[u].get(v);
+          stats_accumulate8(v, sft, s, q);
+        }
       }
     }
   }
