@@ -392,11 +392,27 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.st_C = w.Cout;
     op->st_floats = static_cast<size_t>(in.N) * (2 * p.st_P + 1) * p.st_C;
   }
-  const int st_bytes = stats ? 8192 : 0;
+  // TMA-store epilogue (igemm.cuh tst) for thin-K tiles on the one-CTA kernel
+  static const int tst_mode = [] {
+    const char* e = getenv("GHOST_TST");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  bool tst = tst_mode && !aad && !stats && !phases && !p.cta2 && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
+                   (p.BN == 64 || (p.BN == 128 && !win)) && w.Cout % 64 == 0 && p.bw % 32 == 0 && p.bh * p.bw * p.bn == 128 &&
+                   taps.n * p.kc_per_tap <= 18 && out.sw % 8 == 0 && out.off % 8 == 0 &&
+                   out.sh == static_cast<long long>(Wo) * out.sw && out.sn == static_cast<long long>(Ho) * Wo * out.sw &&
+                   (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8)));
+  int st_bytes = stats ? 8192 : (tst ? 2 * 4 * (p.BN >> 6) * 4096 : 0);
   if (win) {
     const int b_tile = p.BN * 128;
     const int slab = 9 * p.kc_per_tap * b_tile;
     p.a_win = win_mode;
+    // resident weights beat the TMA-store epilogue when only one of the two fits (the weight slab would otherwise be
+    // streamed again for every tile: 3 x BN x 128 B per K block on top of the 17 KB window)
+    if (tst && p.tiles_n == 1 && (221 * 1024 - st_bytes - slab) / (17 * 1024) < 4 && (221 * 1024 - slab) / (17 * 1024) >= 4) {
+      tst = false;
+      st_bytes = 0;
+    }
     p.b_res = p.tiles_n == 1 && (221 * 1024 - st_bytes - slab) / (17 * 1024) >= 4;
     stage_bytes = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
     resident_bytes = p.b_res ? slab : 0;
@@ -452,7 +468,16 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.tmem_cols = pow2_at_least(4 * p.BN);
   }
   // coalesced epilogue for the last tile of each CTA (igemm.cuh), staged in the idle operand ring
-  if (!aad && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
+  if (tst) {
+    p.tst = 1;
+    p.tst_c0 = static_cast<int>(out.off);
+    const uint64_t ct = static_cast<uint64_t>(out.sw);
+    const uint64_t dims[4] = {ct, static_cast<uint64_t>(Wo), static_cast<uint64_t>(Ho), static_cast<uint64_t>(in.N)};
+    const uint64_t str[3] = {ct * 2, static_cast<uint64_t>(Wo) * ct * 2, static_cast<uint64_t>(Ho) * Wo * ct * 2};
+    const uint32_t ob[4] = {64u, 32u, 1u, 1u};
+    if (const char* e = encode_tmap(&p.tmO, out.p, 4, dims, str, ob, 128)) return e;
+  }
+  if (!tst && !aad && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
       !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&
       (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8))) &&
       256 * p.BN <= stages * stage_bytes) {

@@ -185,6 +185,30 @@ __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (
           }
 }
 
+// v -> final values of 16 full columns: bias, first activation, residual, second activation (no stores)
+template <bool F16>
+__device__ __forceinline__ void linear_values_16(const IgemmParams& p, const uint32_t (&v)[16], int col0, long long r_pix,
+                                                 const float* sp, int j, float (&f)[16]) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+  linear_bias_act_16(p, f, col0, sp, j);
+  if (p.res) {
+    const __nv_bfloat16* rp = p.res + r_pix + col0;
+    const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
+    const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+    const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      f[2 * i] += lo16<F16>(qq[i]);
+      f[2 * i + 1] += hi16<F16>(qq[i]);
+    }
+  }
+  if (p.act2 == kAct2Tanh) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) f[i] = tanhf(f[i]);
+  }
+}
+
 // FINAL: called by the split-K reduce kernel with the summed accumulators (p.splits > 1 there too)
 // stored (optional): receives the 16 values as they read back from the output tensor (for the fused statistics)
 template <bool F16, bool FINAL = false>
@@ -306,6 +330,8 @@ struct LinEpi {
   float st_tmp[16];
   int st_img, st_nt;
   float* st_x;  // shared exchange [4 ew][4 lg][4 chunks][32 lanes]
+  uint8_t* tst_buf;  // TMA-store epilogue: [2 buffers][4 lane groups][BN/64 boxes][32 rows][128 B]
+  int tst_it;        // tiles this warp has sent through the staging buffers
 
   __device__ __forceinline__ void init(const IgemmParams& p, int warp, int lane_, uint8_t* ring, const float* eparm_,
                                        bool staged_, int rows_used_, uint32_t tmem_base, int acc_stride_) {
@@ -328,6 +354,8 @@ struct LinEpi {
     st_img = -1;
     st_nt = 0;
     st_x = reinterpret_cast<float*>(ring + p.stages * st_stage_bytes(p));
+    tst_buf = ring + p.stages * st_stage_bytes(p);  // (never together with the statistics exchange)
+    tst_it = 0;
   }
   __device__ __forceinline__ static int st_stage_bytes(const IgemmParams& p) {
     if (p.cta2) return 128 * 128 + (p.BN >> 1) * 128;
@@ -393,6 +421,7 @@ struct LinEpi {
   // call after the last tile of the CTA
   __device__ __forceinline__ void st_finish(const IgemmParams& p) {
     if (STATS && p.st_mode == 2 && st_img >= 0) st_flush(p, blockIdx.x);
+    if (p.tst && ew == 0 && lane == 0) bulk_wait<0>();  // outstanding TMA stores
   }
   __device__ __forceinline__ int stg_key(int row) const { return ((row * rowb) >> 7) & (P - 1); }
 
@@ -429,6 +458,55 @@ struct LinEpi {
         const bool cols_on = colw < p.n_valid;      // (n_valid is a multiple of wcols there)
         if (!__all_sync(0xffffffffu, mbar_wait(tfull, aphase, abort_flag))) return false;
         tc_fence_after();
+        if (p.tst) {
+          // this lane group's piece of the tile: hb boxes of [32 rows][128 B], buffer tst_it & 1
+          const int hb = p.BN >> 6;
+          uint8_t* piece = tst_buf + (((tst_it & 1) * 4 + lg) * hb) * 4096;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            if (c * 16 < wcols) {  // warp-uniform
+              const int j = ew * wcols + c * 16;
+              uint32_t v[16];
+              __syncwarp();
+              tmem_ld16(t_addr + j, v);
+              tmem_ld_wait();
+              uint4 o0 = make_uint4(0u, 0u, 0u, 0u), o1 = o0;
+              if (valid) {
+                float f[16];
+                linear_values_16<F16>(p, v, t.nt * p.BN + j, r_pix, staged ? eparm : nullptr, j, f);
+                o0.x = pack16<F16>(f[0], f[1]);
+                o0.y = pack16<F16>(f[2], f[3]);
+                o0.z = pack16<F16>(f[4], f[5]);
+                o0.w = pack16<F16>(f[6], f[7]);
+                o1.x = pack16<F16>(f[8], f[9]);
+                o1.y = pack16<F16>(f[10], f[11]);
+                o1.z = pack16<F16>(f[12], f[13]);
+                o1.w = pack16<F16>(f[14], f[15]);
+              }
+              uint8_t* row = piece + (j >> 6) * 4096 + lane * 128;
+              const int cc = (j & 63) >> 3;  // 16-byte chunk inside the 128-byte row
+              *reinterpret_cast<uint4*>(row + ((cc ^ (lane & 7)) << 4)) = o0;
+              *reinterpret_cast<uint4*>(row + (((cc + 1) ^ (lane & 7)) << 4)) = o1;
+            }
+          }
+          // the accumulator stage goes back to the MMA warp; the piece goes out through the TMA
+          tc_fence_before();
+          fence_proxy_async();
+          __syncwarp();
+          release<REMOTE>(tempty);
+          // the store of the previous tile (other buffer) has read its shared memory before anyone refills it
+          if (ew == 0 && lane == 0) bulk_wait_read<0>();
+          named_bar_sync(5 + lg, 128);
+          if (ew == 0 && lane == 0) {
+            if (r < rows_used && n < p.Nimg && oh < p.Ho && ow < p.Wo) {
+              for (int b = 0; b < hb; ++b)
+                tma_store_4d(&p.tmO, piece + b * 4096, p.tst_c0 + t.nt * p.BN + b * 64, ow, oh, n);
+            }
+            bulk_commit();
+          }
+          ++tst_it;
+          return true;
+        }
         if (use_stg) {
           if (p.res != nullptr) {
             // residual rows of this warp's piece of the tile, as whole row segments
@@ -736,6 +814,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
       prefetch_tmap(&p.tmH);
       prefetch_tmap(&p.tmO);
     }
+    if (p.tst) prefetch_tmap(&p.tmO);
   }
   if (warp == 1) {
     __syncwarp();
@@ -1502,7 +1581,8 @@ const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream) {
 }
 
 int igemm_smem_bytes(const IgemmParams& p) {
-  const int st = p.st_mode ? 8192 : 0;  // exchange buffer of the fused statistics, behind the operand ring
+  // behind the operand ring: exchange buffer of the fused statistics, or the staging of the TMA-store epilogue
+  const int st = p.st_mode ? 8192 : (p.tst ? 2 * 4 * (p.BN >> 6) * 4096 : 0);
   if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024 + st;
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
@@ -1643,6 +1723,9 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.stg && (p.mode != kModeLinear || p.out_f32 || p.splits != 1 || (p.BN != 128 && p.BN != 256) ||
                 p.n_valid % (p.BN >> 2)))
     return "igemm: staged output needs a bf16 linear epilogue and N tiles of 128 or 256 whole warp quarters";
+  if (p.tst && (p.mode != kModeLinear || p.out_f32 || p.splits != 1 || p.st_mode || p.stg || p.out2 || p.nphase > 1 ||
+                (p.BN != 64 && p.BN != 128) || p.bw % 32 || p.n_valid % 64))
+    return "igemm: the TMA-store epilogue needs a plain 16-bit linear tile of 64 / 128 columns and rows of 32 pixels";
   const int smem = igemm_smem_bytes(p);
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;

@@ -134,6 +134,15 @@ struct alignas(64) IgemmParams {
   float* st_parts;
   int st_mode, st_P, st_C;
 
+  // TMA-store epilogue of thin-K linear tiles (tst = 1): the row-per-lane 16-byte stores of the plain epilogue cost 32
+  // LSU wavefronts per instruction (32 lanes, 32 different 128-byte lines) and bound the 3x3 convs of AADBlk7-8
+  // (measured: the MMA issuers wait half of their time for a free accumulator stage).  Instead the four warps of a
+  // TMEM lane group write their 32 rows x BN columns into a double-buffered shared-memory piece (128B swizzle, boxes
+  // of 64 channels) and one lane sends it out through tmO (box 64 channels x 32 pixels).  BN 64 / 128, bw % 32 == 0,
+  // 16-bit output with regular NHWC strides.
+  int tst;
+  int tst_c0;  // first output channel (view offset) inside the tensor tmO describes
+
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
   int* err;  // device word set non-zero when a pipeline wait timed out
