@@ -368,12 +368,14 @@ void Net::build_aei(ExecPlan& p) {
   }
 
   float* sums_next = nullptr;  // statistics of m written by the previous block's fused upsample
+  int parts_next = 0;          // ... and the number of parts per image it writes
   for (int k = 1; k <= 8; ++k) {
     const BlockSpec& b = blocks[k - 1];
     const int hw = 2 << (k - 1);
     const int HW = hw * hw;
     const Act& za = z[k];
-    const int parts_in = in_stats_parts(B, HW, b.cin);
+    const int parts_in = in_stats_parts(B, HW, b.cin);   // parts of in_stats_launch on a tensor of this block
+    const int parts_m = sums_next ? parts_next : parts_in;  // parts of the statistics of the block input m
     float* sums_m = sums_next;
     if (!sums_m) {
       sums_m = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_in + 1) * b.cin);
@@ -462,7 +464,7 @@ void Net::build_aei(ExecPlan& p) {
         float* bhp = bhf2 + L * B;
         const float* sums = sums_m;
         add_op(lname + ".fold", [=](cudaStream_t s) {
-          return aad_fold_launch(sums, parts_in, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncp, whp, bhp, fsc, s, 2 * cx);
+          return aad_fold_launch(sums, parts_m, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncp, whp, bhp, fsc, s, 2 * cx);
         });
       }
       AadArgs args;
@@ -475,8 +477,8 @@ void Net::build_aei(ExecPlan& p) {
     AadPre pre_sc{}, pre_0{};
     const bool mask2 = bf && !pair && b.cin != b.cout && b.cin > 128;
     if (mask2) {
-      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m, parts_in);
-      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m, parts_in);
+      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m, parts_m);
+      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m, parts_m);
       pre_sc.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       pre_0.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       const Act mm = m;
@@ -488,13 +490,13 @@ void Net::build_aei(ExecPlan& p) {
     }
     if (b.cin != b.cout) {
       sc = new_act(hw, hw, b.cout);
-      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, parts_in, mask2 ? &pre_sc : nullptr);
+      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, parts_m, mask2 ? &pre_sc : nullptr);
       add_conv(S("blk%d.convsc", k), pair ? a2 : a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
                OutView::dense(sc), Epilogue(), nullptr);
     }
     Act x = m;
     const float* sums_x = sums_m;
-    int sums_xP = parts_in;
+    int sums_xP = parts_m;
     Act y;
     // tensor-core modes, images of >= 256 pixels: the statistics of a conv output that feeds the next AADLayer come
     // out of that conv's epilogue (igemm.cuh st_mode) instead of a separate pass over the tensor
@@ -545,12 +547,13 @@ void Net::build_aei(ExecPlan& p) {
       // bilinear x2 (AEI_Net.py:124-138) fused with the InstanceNorm statistics of the next block's input
       Act nm = new_act(2 * hw, 2 * hw, b.cout);
       const Act yy = y, nn = nm;
-      const int parts_nx = in_stats_parts(B, 4 * HW, b.cout);
+      const int parts_nx = upsample2x_stats_parts(B, yy.H, yy.W, yy.C);
       float* sums_nx = p.pool.alloc_n<float>(static_cast<size_t>(B) * (2 * parts_nx + 1) * b.cout);
       add_op(S("blk%d.upsample_stats", k), [=](cudaStream_t s) {
         return upsample2x_stats_launch(yy.p, nn.p, dt, B, yy.H, yy.W, yy.C, sums_nx, s);
       }, kOpUpsample, 5.0 * B * yy.H * yy.W * yy.C * esz);
       sums_next = sums_nx;
+      parts_next = parts_nx;
       m = nm;
       p.named[S("m%d", k + 1)] = m;
     } else {

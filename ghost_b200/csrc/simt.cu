@@ -1083,6 +1083,147 @@ __global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const S* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------
+// Bilinear x2, one thread per 2 x 2 OUTPUT block and 8 channels (round 2; ncu of the per-pixel kernels above: issue
+// bound at 70-85 % issue slots, 2.6 TB/s).  The four outputs of a block draw on a 3 x 3 source neighbourhood: 9 loads
+// and conversions instead of 16, the horizontal blends of the middle source row are shared by both output rows
+// (20 instead of 24 packed blends per output), the index arithmetic is paid once per block.  Every output is still
+//   o = (1-lh) * ((1-lw)*a + lw*b) + lh * ((1-lw)*c + lw*d)          (ATen upsample_bilinear2d, align_corners)
+// on the same four neighbours with the same fp32 lambdas, so the result is bit-identical to the per-pixel kernels;
+// blocks whose rows / columns do not form the regular pattern (image borders) take the per-pixel formula.
+// STATS: fused InstanceNorm partial statistics of the output (layout of in_stats_kernel), parts per block.
+__device__ __forceinline__ void quad_axis(int o, float scale, int n, int* i0, int* i1, float* l) {
+  const float f = scale * o;
+  *i0 = static_cast<int>(f);
+  *i1 = *i0 + (*i0 < n - 1 ? 1 : 0);
+  *l = f - *i0;
+}
+// horizontal blends of one source row for the two output columns: tA from (v0, v1), tB from (v1, v2)
+__device__ __forceinline__ void quad_hblend(const float (&v0)[8], const float (&v1)[8], const float (&v2)[8], float lwA,
+                                            float lwB, float (&tA)[8], float (&tB)[8]) {
+  const float2 a0 = make_float2(1.f - lwA, 1.f - lwA), a1 = make_float2(lwA, lwA);
+  const float2 b0 = make_float2(1.f - lwB, 1.f - lwB), b1 = make_float2(lwB, lwB);
+#pragma unroll
+  for (int k = 0; k < 8; k += 2) {
+    const float2 x0 = make_float2(v0[k], v0[k + 1]), x1 = make_float2(v1[k], v1[k + 1]), x2 = make_float2(v2[k], v2[k + 1]);
+    const float2 ta = ptx::fma2(a1, x1, ptx::mul2(a0, x0));
+    const float2 tb = ptx::fma2(b1, x2, ptx::mul2(b0, x1));
+    tA[k] = ta.x; tA[k + 1] = ta.y;
+    tB[k] = tb.x; tB[k + 1] = tb.y;
+  }
+}
+__device__ __forceinline__ void quad_vblend(const float (&t0)[8], const float (&t1)[8], float lh, float (&o)[8]) {
+  const float2 h0 = make_float2(1.f - lh, 1.f - lh), h1 = make_float2(lh, lh);
+#pragma unroll
+  for (int k = 0; k < 8; k += 2) {
+    const float2 r = ptx::fma2(h1, make_float2(t1[k], t1[k + 1]), ptx::mul2(h0, make_float2(t0[k], t0[k + 1])));
+    o[k] = r.x; o[k + 1] = r.y;
+  }
+}
+
+template <typename T, bool STATS>
+__global__ void __launch_bounds__(kStatThreads, 2) upsample2x_quad_kernel(const T* __restrict__ x, T* __restrict__ y, int H,
+                                                                        int W, int C, int oC, int o_c0,
+                                                                        int quads_per_block, float* __restrict__ parts) {
+  extern __shared__ float sh[];  // STATS: [kStatThreads][16]
+  const int n = blockIdx.y;
+  const int P = gridDim.x;
+  const int Ho = 2 * H, Wo = 2 * W, HW = H * W;
+  const int vecs = C >> 3;
+  const int ppi = kStatThreads / vecs;
+  const int cv = threadIdx.x % vecs, pl = threadIdx.x / vecs;
+  const int q0 = blockIdx.x * quads_per_block;
+  const int q1 = min(HW, q0 + quads_per_block);
+  const float shh = Ho > 1 ? static_cast<float>(H - 1) / static_cast<float>(Ho - 1) : 0.f;
+  const float sww = Wo > 1 ? static_cast<float>(W - 1) / static_cast<float>(Wo - 1) : 0.f;
+  float s[8], q[8], sft[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = sft[i] = 0.f;
+  const T* base = x + static_cast<long long>(n) * HW * C + cv * 8;
+  T* obase = y + static_cast<long long>(n) * Ho * Wo * oC + o_c0 + cv * 8;
+  if (STATS) load8(base, sft);
+  if (pl < ppi) {
+    for (int qi = q0 + pl; qi < q1; qi += ppi) {
+      const int qy = qi / W, qx = qi - qy * W;
+      int ha0, ha1, hb0, hb1, wa0, wa1, wb0, wb1;
+      float lha, lhb, lwa, lwb;
+      quad_axis(2 * qy, shh, H, &ha0, &ha1, &lha);
+      quad_axis(2 * qy + 1, shh, H, &hb0, &hb1, &lhb);
+      quad_axis(2 * qx, sww, W, &wa0, &wa1, &lwa);
+      quad_axis(2 * qx + 1, sww, W, &wb0, &wb1, &lwb);
+      float o[4][8];  // (row a, col A), (a, B), (b, A), (b, B)
+      if (ha1 == hb0 && wa1 == wb0) {
+        // regular pattern: rows (ha0, hb0, hb1), columns (wa0, wb0, wb1)
+        const int rr[3] = {ha0, hb0, hb1}, cc[3] = {wa0, wb0, wb1};
+        float tA[3][8], tB[3][8];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          Raw8<T> raw[3];
+#pragma unroll
+          for (int c = 0; c < 3; ++c) raw[c].load(base + static_cast<long long>(rr[r] * W + cc[c]) * C);
+          float v0[8], v1[8], v2[8];
+          raw[0].get(v0);
+          raw[1].get(v1);
+          raw[2].get(v2);
+          quad_hblend(v0, v1, v2, lwa, lwb, tA[r], tB[r]);
+        }
+        quad_vblend(tA[0], tA[1], lha, o[0]);
+        quad_vblend(tB[0], tB[1], lha, o[1]);
+        quad_vblend(tA[1], tA[2], lhb, o[2]);
+        quad_vblend(tB[1], tB[2], lhb, o[3]);
+      } else {
+        // borders: the four outputs one by one
+        const int hh0[2] = {ha0, hb0}, hh1[2] = {ha1, hb1}, ww0[2] = {wa0, wb0}, ww1[2] = {wa1, wb1};
+        const float lh[2] = {lha, lhb}, lw[2] = {lwa, lwb};
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float a[8], b[8], cc_[8], d[8];
+            load8(base + static_cast<long long>(hh0[r] * W + ww0[c]) * C, a);
+            load8(base + static_cast<long long>(hh0[r] * W + ww1[c]) * C, b);
+            load8(base + static_cast<long long>(hh1[r] * W + ww0[c]) * C, cc_);
+            load8(base + static_cast<long long>(hh1[r] * W + ww1[c]) * C, d);
+            bilerp8(a, b, cc_, d, lw[c], lh[r], o[r * 2 + c]);
+          }
+      }
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          T* dst = obase + (static_cast<long long>(2 * qy + r) * Wo + 2 * qx + c) * oC;
+          if (STATS) {
+            float stored[8];
+            store8_rounded(dst, o[r * 2 + c], stored);
+            stats_accumulate8(stored, sft, s, q);
+          } else {
+            store8(dst, o[r * 2 + c]);
+          }
+        }
+    }
+  }
+  if (STATS) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sh[threadIdx.x * 16 + i] = s[i];
+      sh[threadIdx.x * 16 + 8 + i] = q[i];
+    }
+    __syncthreads();
+    float* out = parts + static_cast<long long>(n) * (2 * P + 1) * C;
+    for (int t = threadIdx.x; t < vecs * 16; t += kStatThreads) {
+      const int v = t >> 4, slot = t & 15;
+      float acc = 0.f;
+      for (int l = 0; l < ppi; ++l) acc += sh[(l * vecs + v) * 16 + slot];
+      const int c = v * 8 + (slot & 7);
+      out[(2 * blockIdx.x + (slot >> 3)) * C + c] = acc;
+    }
+    if (blockIdx.x == 0 && pl == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) out[2 * P * C + cv * 8 + i] = sft[i];
+    }
+  }
+}
+
 template <typename T>
 __global__ void zfc_to_act_kernel(const float* __restrict__ zfc, int ldz, int off, int count,
                                   const float* __restrict__ bias, T* __restrict__ dst, int N) {
@@ -1159,10 +1300,48 @@ const char* nhwc_to_nchw_dst(const S* src, int srcC, int src_c0, void* dst, int 
 
 }  // namespace
 
+namespace {
+// quads (2 x 2 output blocks = source pixels) per block: ~16 blocks per SM over the batch, at least 8 iterations
+int quads_per_block(int N, int HW, int C) {
+  const int ppi = kStatThreads / (C / 8);
+  const int blocks_x = (148 * 16 + N - 1) / N;
+  int qpb = (HW + blocks_x - 1) / blocks_x;
+  if (qpb < ppi * 8) qpb = ppi * 8;
+  return qpb;
+}
+static const int g_quad_mode = [] {
+  const char* e = getenv("GHOST_UPSAMPLE_QUAD");  // A/B switch for profiling: 0 = the per-pixel kernels
+  return e ? atoi(e) : 1;
+}();
+template <typename T, bool STATS>
+const char* upsample_quad_launch(const void* x, void* y, int N, int H, int W, int C, int oC, int o_c0, float* parts,
+                                 cudaStream_t s) {
+  const int qpb = quads_per_block(N, H * W, C);
+  dim3 grid((H * W + qpb - 1) / qpb, N);
+  const int smem = STATS ? kStatThreads * 16 * sizeof(float) : 0;
+  upsample2x_quad_kernel<T, STATS><<<grid, kStatThreads, smem, s>>>(reinterpret_cast<const T*>(x), reinterpret_cast<T*>(y),
+                                                                    H, W, C, oC, o_c0, qpb, parts);
+  return last_err();
+}
+}  // namespace
+
+// number of statistic parts upsample2x_stats_launch writes per image
+int upsample2x_stats_parts(int N, int H, int W, int C) {
+  if (!g_quad_mode) return in_stats_parts(N, 4 * H * W, C);
+  const int qpb = quads_per_block(N, H * W, C);
+  return (H * W + qpb - 1) / qpb;
+}
+
 const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, int oC, int o_c0,
                               cudaStream_t s) {
   if (C % 8 || oC % 8 || o_c0 % 8) return "upsample2x: channels must be multiples of 8";
   if (static_cast<long long>(H) * W * C >= (1LL << 31)) return "upsample2x: image too large";
+  if (g_quad_mode && C <= 8 * kStatThreads) {
+    if (dtype == kF32) return upsample_quad_launch<float, false>(x, y, N, H, W, C, oC, o_c0, nullptr, s);
+    if (dtype == kBF16) return upsample_quad_launch<__nv_bfloat16, false>(x, y, N, H, W, C, oC, o_c0, nullptr, s);
+    if (dtype == kF16) return upsample_quad_launch<__half, false>(x, y, N, H, W, C, oC, o_c0, nullptr, s);
+    return "upsample2x: unsupported dtype";
+  }
   const int row_items = 2 * W * (C / 8);
   dim3 grid((row_items + 255) / 256, 2 * H, N);
   if (grid.x > 64) grid.x = 64;
@@ -1184,6 +1363,12 @@ const char* upsample2x_stats_launch(const void* x, void* y, int dtype, int N, in
                                     cudaStream_t s) {
   if (C % 8 || C > 8 * kStatThreads) return "upsample2x_stats: C must be a multiple of 8 and <= 2048";
   if (static_cast<long long>(H) * W * C >= (1LL << 31)) return "upsample2x_stats: image too large";
+  if (g_quad_mode) {
+    if (dtype == kF32) return upsample_quad_launch<float, true>(x, y, N, H, W, C, C, 0, parts, s);
+    if (dtype == kBF16) return upsample_quad_launch<__nv_bfloat16, true>(x, y, N, H, W, C, C, 0, parts, s);
+    if (dtype == kF16) return upsample_quad_launch<__half, true>(x, y, N, H, W, C, C, 0, parts, s);
+    return "upsample2x_stats: unsupported dtype";
+  }
   const int HWo = 4 * H * W;
   const int ppb = stats_pix_per_block(N, HWo, C);
   dim3 grid((HWo + ppb - 1) / ppb, N);

@@ -80,7 +80,9 @@ const char* aad_apply_launch(const void* h, const void* gb, void* out, int dtype
 // The output may be a channel slice of a wider tensor (oC = pixel stride, o_c0 = first channel).
 const char* upsample2x_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, int oC, int o_c0,
                               cudaStream_t s);
-// Same, fused with in_stats of the (dense, oC == C) output: parts as in_stats_launch(y, N, 4*H*W, C).
+// Same, fused with in_stats of the (dense, oC == C) output: parts in the layout of in_stats_launch with
+// P = upsample2x_stats_parts(N, H, W, C) parts per image.
+int upsample2x_stats_parts(int N, int H, int W, int C);
 const char* upsample2x_stats_launch(const void* x, void* y, int dtype, int N, int H, int W, int C, float* parts,
                                     cudaStream_t s);
 

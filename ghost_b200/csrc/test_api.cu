@@ -266,7 +266,7 @@ int ghost_test_upsample2x_stats(const void* x, void* y, int dtype, int N, int H,
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     DevPool pool;
     const int HWo = 4 * H * W;
-    const int P = in_stats_parts(N, HWo, C);
+    const int P = upsample2x_stats_parts(N, H, W, C);
     const size_t nparts = static_cast<size_t>(N) * (2 * P + 1) * C;
     float* parts = pool.alloc_n<float>(nparts);
     check_msg(upsample2x_stats_launch(x, y, dtype == GHOST_F32 ? kF32 : (dtype == GHOST_F16 ? kF16 : kBF16), N, H, W, C, parts, s), "upsample2x_stats");
