@@ -85,8 +85,10 @@ __device__ __forceinline__ double mask_at(const PasteParams& p, int mi, int y, i
                     : static_cast<double>(__ldg(reinterpret_cast<const float*>(p.masks) + i));
 }
 
-// One destination pixel, exact mode.  fin[3] is the float64 running composite.
-__device__ __forceinline__ void paste_exact_px(const PasteParams& p, const PasteFace& f, int x, int y, double (&fin)[3]) {
+// One destination pixel, exact mode.  fin[3] is the float64 running composite; it is loaded from the frame (offset
+// `off`) the first time a face's warped mask is non-zero at this pixel (`touched`).
+__device__ __forceinline__ void paste_exact_px(const PasteParams& p, const PasteFace& f, int x, int y, double (&fin)[3],
+                                               long long off, bool& touched) {
   // cv2.warpAffine fixed-point coordinates (AB_BITS = 10, INTER_BITS = 5)
   const long long adelta = __double2ll_rn(__dmul_rn(__dmul_rn(f.M[0], static_cast<double>(x)), 1024.0));
   const long long bdelta = __double2ll_rn(__dmul_rn(__dmul_rn(f.M[3], static_cast<double>(x)), 1024.0));
@@ -108,6 +110,12 @@ __device__ __forceinline__ void paste_exact_px(const PasteParams& p, const Paste
   m = __dadd_rn(m, __dmul_rn(mask_at(p, f.mask_index, sy + 1, sx), w10 * k));
   m = __dadd_rn(m, __dmul_rn(mask_at(p, f.mask_index, sy + 1, sx + 1), w11 * k));
   if (m == 0.0) return;  // 0*swap + (1-0)*final == final exactly
+  if (!touched) {
+    fin[0] = static_cast<double>(p.frames_in[off]);
+    fin[1] = static_cast<double>(p.frames_in[off + 1]);
+    fin[2] = static_cast<double>(p.frames_in[off + 2]);
+    touched = true;
+  }
   const int x0 = min(max(sx, 0), 223), x1 = min(max(sx + 1, 0), 223);
   const int y0 = min(max(sy, 0), 223), y1 = min(max(sy + 1, 0), 223);
   const uint32_t q00 = rz_px(p, f.crop_index, y0, x0), q01 = rz_px(p, f.crop_index, y0, x1);
@@ -170,17 +178,23 @@ __global__ void __launch_bounds__(256) paste_faces_kernel(const PasteParams p) {
     if (x >= o.x0 && x < o.x1 && y >= o.y0 && y < o.y1) return;  // an earlier box owns this pixel
   }
   const long long off = ((static_cast<long long>(f) * p.H + y) * p.W + x) * 3;
-  const int b0 = p.frames_in[off], b1 = p.frames_in[off + 1], b2 = p.frames_in[off + 2];
   if (p.mode == kPasteExact) {
-    double fd[3] = {static_cast<double>(b0), static_cast<double>(b1), static_cast<double>(b2)};
+    // Most pixels of a face box lie outside the blend mask (the box bounds the rotated 224 x 224 crop, the mask is
+    // an ellipse inside it): there the composite IS the frame pixel, which frames_out already holds (copied, or the
+    // same buffer), so such a pixel costs the two coordinate maps and four mask taps and nothing else.
+    double fd[3] = {0.0, 0.0, 0.0};
+    bool touched = false;
     for (int k = j; k < fe; ++k) {
       const PasteFace& face = p.faces[k];
       if (x < face.x0 || x >= face.x1 || y < face.y0 || y >= face.y1) continue;
-      paste_exact_px(p, face, x, y, fd);
+      paste_exact_px(p, face, x, y, fd, off, touched);
     }
+    if (touched) {
 #pragma unroll
-    for (int c = 0; c < 3; ++c) p.frames_out[off + c] = static_cast<uint8_t>(static_cast<int>(fd[c]));
+      for (int c = 0; c < 3; ++c) p.frames_out[off + c] = static_cast<uint8_t>(static_cast<int>(fd[c]));
+    }
   } else {
+    const int b0 = p.frames_in[off], b1 = p.frames_in[off + 1], b2 = p.frames_in[off + 2];
     float ff[3] = {static_cast<float>(b0), static_cast<float>(b1), static_cast<float>(b2)};
     for (int k = j; k < fe; ++k) {
       const PasteFace& face = p.faces[k];
