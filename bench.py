@@ -455,28 +455,43 @@ def run_ours(args):
     # (ghost_b200.FrameSharder: the gather of step k travels on a side stream while step k+1 computes);
     # device-resident like `value`, one gather per step, the last one inside the timed region.
     ms_gather = 0.0
+    ms_gather_nccl = 0.0
     if world > 1:
-        sharder = ghost_b200.FrameSharder(NF * world, rank, world)
         outs = [out_d, torch.empty_like(out_d)]
-        for i in range(2):
-            step_device(sources_d, crops_d, frames_d, outs[i % 2])
-            sharder.gather_async(outs[i % 2], dst=0)
-        sharder.wait()
-        barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        for i in range(args.steps):
-            step_device(sources_d, crops_d, frames_d, outs[i % 2])
-            sharder.gather_async(outs[i % 2], dst=0)
-        sharder.wait()
-        g1.record()
-        barrier()
-        ms_gather = g0.elapsed_time(g1)
 
-    t = torch.tensor([ms_total, ms_e2e, ms_gather, ms_e2e_full], dtype=torch.float64, device=dev)
+        def time_gather(start, finish, slot=None):
+            def one(i):
+                # the consumer rank composites straight into its slot of the gather buffer (no local copy)
+                dst_t = slot() if slot is not None else None
+                dst_t = outs[i % 2] if dst_t is None else dst_t
+                step_device(sources_d, crops_d, frames_d, dst_t)
+                start(dst_t)
+            for i in range(2):
+                one(i)
+            finish()
+            barrier()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            for i in range(args.steps):
+                one(i)
+            finish()
+            g1.record()
+            barrier()
+            return g0.elapsed_time(g1)
+
+        # (a) peer-mapped buffers: one copy-engine transfer per rank and step into rank 0's IPC-exported buffer
+        peer = ghost_b200.PeerGather(NF * world, tuple(out_d.shape[1:]), dst=0, device=dev)
+        ms_gather = time_gather(peer.gather_async, peer.wait, peer.local_out)
+        peer.close()
+        del peer
+        # (b) the same exchange as NCCL send / recv (a kernel on both ends), for comparison
+        sharder = ghost_b200.FrameSharder(NF * world, rank, world)
+        ms_gather_nccl = time_gather(lambda t: sharder.gather_async(t, dst=0), sharder.wait)
+
+    t = torch.tensor([ms_total, ms_e2e, ms_gather, ms_e2e_full, ms_gather_nccl], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e, ms_gather, ms_e2e_full = float(t[0]), float(t[1]), float(t[2]), float(t[3])
+    ms_total, ms_e2e, ms_gather, ms_e2e_full, ms_gather_nccl = (float(t[i]) for i in range(5))
 
     # ---------------------------------------------------------------- per-kernel-class roofline (rank 0)
     line = None
@@ -573,8 +588,13 @@ def run_ours(args):
                                    "ms_per_step": ms_gather / args.steps,
                                    "bytes_into_rank0_per_step": int((world - 1) * out_d.numel()),
                                    "note": "device-resident step + gather of every rank's finished frames on rank 0 "
-                                           "(frame order; step k's frames travel on a side stream while step k+1 "
-                                           "computes, the last gather is inside the timed region)"}
+                                           "(frame order): ghost_b200.PeerGather - copy-engine transfers into rank "
+                                           "0's IPC-mapped buffer, step k's frames travel while step k+1 computes, "
+                                           "the last gather is inside the timed region",
+                                   "nccl_send_recv": {"value": B * world * args.steps / (ms_gather_nccl * 1e-3),
+                                                      "ms_per_step": ms_gather_nccl / args.steps,
+                                                      "note": "the same exchange through FrameSharder.gather_async "
+                                                              "(NCCL send / recv kernels beside the compute)"}}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

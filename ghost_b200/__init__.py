@@ -8,9 +8,9 @@ from .api import (AEI_Net, IResNet100, iresnet100, faceshifter_batch, transform_
                   normalize_and_torch, normalize_and_torch_batch, get_final_image, get_final_video, paste_back, paste_boxes, SwapPipeline,
                   LIPSPADEGenerator, Pix2PixModel, face_enhancement, crop_faces, match_identities, embed_and_swap)
 from . import masks
-from .shard import shard_range, FrameSharder
+from .shard import shard_range, FrameSharder, PeerGather
 
 __all__ = ["AEI_Net", "IResNet100", "iresnet100", "faceshifter_batch", "transform_target_to_torch",
            "normalize_and_torch", "normalize_and_torch_batch", "get_final_image", "get_final_video", "paste_back",
-           "SwapPipeline", "paste_boxes", "shard_range", "FrameSharder", "LIPSPADEGenerator", "Pix2PixModel", "face_enhancement", "crop_faces", "match_identities", "embed_and_swap", "masks"]
+           "SwapPipeline", "paste_boxes", "shard_range", "FrameSharder", "PeerGather", "LIPSPADEGenerator", "Pix2PixModel", "face_enhancement", "crop_faces", "match_identities", "embed_and_swap", "masks"]
 __version__ = "0.1.0"

@@ -79,6 +79,13 @@ SIGNATURES = {
     "ghost_match_identities": (_i, [_vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp, _vp]),
     "ghost_crop_faces": (_i, [_vp, _i, _i, _i, C.POINTER(_d), C.POINTER(_i), _i, _vp, _vp, _vp]),
     "ghost_crop_faces_noalloc": (_i, [_vp, _i, _i, _i, C.POINTER(_d), C.POINTER(_i), _i, _vp, _vp, _vp]),
+    "ghost_peer_alloc": (_i, [C.c_size_t, C.POINTER(_vp), C.c_char_p]),
+    "ghost_peer_open": (_i, [C.c_char_p, C.POINTER(_vp)]),
+    "ghost_peer_close": (_i, [_vp]),
+    "ghost_peer_free": (_i, [_vp]),
+    "ghost_peer_copy": (_i, [_vp, _vp, C.c_size_t, _vp]),
+    "ghost_peer_signal": (_i, [_vp, C.c_uint32, _vp]),
+    "ghost_peer_wait": (_i, [_vp, C.c_uint32, _vp]),
     "ghost_face_masks": (_i, [_fp, C.POINTER(_i), _i, _vp, _i, _vp]),
     "ghost_test_conv": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _i, _i, _vp]),
     "ghost_test_aad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f,

@@ -22,6 +22,7 @@
 #ifndef GHOST_B200_H_
 #define GHOST_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -222,6 +223,22 @@ int ghost_crop_faces(const uint8_t* frames, int n_frames, int H, int W, const do
 #define GHOST_CROP_NOALLOC_MAX_FACES 32
 int ghost_crop_faces_noalloc(const uint8_t* frames, int n_frames, int H, int W, const double* tfm, const int* face_frame,
                              int n, uint8_t* crops224, uint8_t* crops256, void* stream);
+
+/* ---- peer-mapped gather buffers: the one exchange of the sharded path, the final gather of finished
+ * uint8 frames on the consumer rank, as copy-engine transfers into a buffer the consumer exports through CUDA IPC.
+ * No counterpart in the reference (it has no multi-GPU inference path); ghost_b200/shard.py::PeerGather is the host
+ * side.  ghost_peer_alloc: cudaMalloc (zeroed) + the 64-byte IPC handle of the allocation (consumer rank);
+ * ghost_peer_open / ghost_peer_close: map / unmap it in another process of the same box; ghost_peer_copy: asynchronous
+ * copy (cudaMemcpyDefault) on `stream`; ghost_peer_signal: stores `value` in a 32-bit flag (possibly peer memory)
+ * behind the work queued on `stream`; ghost_peer_wait: makes `stream` wait until *flag >= value (cuStreamWaitValue32,
+ * no kernel). */
+int ghost_peer_alloc(size_t bytes, void** dev_ptr, unsigned char* handle64);
+int ghost_peer_open(const unsigned char* handle64, void** dev_ptr);
+int ghost_peer_close(void* dev_ptr);
+int ghost_peer_free(void* dev_ptr);
+int ghost_peer_copy(void* dst, const void* src, size_t bytes, void* stream);
+int ghost_peer_signal(uint32_t* flag, uint32_t value, void* stream);
+int ghost_peer_wait(uint32_t* flag, uint32_t value, void* stream);
 
 /* ---- blend-mask synthesis (utils/inference/masks.py:39-108 face_mask_static + erode_and_blur, called at
  * image_processing.py:68 and video_processing.py:221-223), bit-exact against the reference's OpenCV calls:

@@ -19,7 +19,7 @@ for nm in ("ghost_prof_aad_read", "ghost_prof_igemm_read"):
     getattr(lib, nm).restype = C.c_int
 g = torch.Generator().manual_seed(0)
 c_id = 512
-shapes = [(64, 256, 64, 64), (64, 128, 128, 64), (64, 64, 256, 128), (64, 32, 512, 256)]
+shapes = [(64, 256, 64, 64), (64, 128, 128, 128), (64, 64, 256, 256), (64, 32, 512, 512), (64, 16, 1024, 1024)]
 for (N, H, c_x, c_attr) in shapes:
     h = torch.randn(N, H, H, c_x, generator=g).cuda().bfloat16()
     za = torch.randn(N, H, H, c_attr, generator=g).cuda().bfloat16()
