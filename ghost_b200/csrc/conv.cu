@@ -363,6 +363,17 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
         }
       }
     }
+    // row-window convs (thin K, N <= 128): measured MMA-pipe bound at ~68 clk per 128 x 64 x 16 MMA, each of which
+    // re-reads its 4 KB A slab from shared memory; the 256-row MMA of a CTA pair halves that per output
+    static const int cta2win_mode = [] {
+      const char* e = getenv("GHOST_CTA2WIN");  // A/B switch for profiling
+      return e ? atoi(e) : 1;
+    }();
+    // (with 64 input channels a tile has only three K blocks and the epilogue bounds it either way: measured
+    // 0.344 ms one CTA vs 0.362 ms as a pair on AADBlk8's 64 -> 64 conv)
+    if (win && !p.cta2 && cta2_mode != 0 && cta2win_mode != 0 && force2 != 2 && tiles_m2 >= 2 && bn_ % 16 == 0 && bn_ >= 32 &&
+        (p.kc_per_tap >= 2 || force2 == 1))
+      p.cta2 = 1;
     p.BN = bn_;
     p.tiles_n = nph * ((cout_t + p.BN - 1) / p.BN);
     p.n_valid = nph * cout_t;
@@ -397,14 +408,14 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const char* e = getenv("GHOST_TST");  // A/B switch for profiling
     return e ? atoi(e) : 1;
   }();
-  bool tst = tst_mode && !aad && !stats && !phases && !p.cta2 && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
+  bool tst = tst_mode && !aad && !stats && !phases && (!p.cta2 || win) && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
                    (p.BN == 64 || (p.BN == 128 && !win)) && w.Cout % 64 == 0 && p.bw % 32 == 0 && p.bh * p.bw * p.bn == 128 &&
                    taps.n * p.kc_per_tap <= 18 && out.sw % 8 == 0 && out.off % 8 == 0 &&
                    out.sh == static_cast<long long>(Wo) * out.sw && out.sn == static_cast<long long>(Ho) * Wo * out.sw &&
                    (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8)));
   int st_bytes = stats ? 8192 : (tst ? 2 * 4 * (p.BN >> 6) * 4096 : 0);
   if (win) {
-    const int b_tile = p.BN * 128;
+    const int b_tile = (p.cta2 ? p.BN / 2 : p.BN) * 128;  // a CTA of a pair holds half of every weight tile
     const int slab = 9 * p.kc_per_tap * b_tile;
     p.a_win = win_mode;
     // resident weights beat the TMA-store epilogue when only one of the two fits (the weight slab would otherwise be
@@ -463,7 +474,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const char* e = getenv("GHOST_SETS4");  // A/B switch for profiling
     return e ? atoi(e) : 1;
   }();
-  if (!aad && !p.cta2 && sets4_mode && 4 * p.BN <= 512) {
+  if (!aad && sets4_mode && 4 * p.BN <= 512) {
     p.sets = 4;
     p.tmem_cols = pow2_at_least(4 * p.BN);
   }

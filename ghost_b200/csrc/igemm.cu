@@ -358,7 +358,10 @@ struct LinEpi {
     tst_it = 0;
   }
   __device__ __forceinline__ static int st_stage_bytes(const IgemmParams& p) {
-    if (p.cta2) return 128 * 128 + (p.BN >> 1) * 128;
+    if (p.cta2) {
+      const int b_half = (p.BN >> 1) * 128;
+      return p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half);
+    }
     const int b_tile = p.BN * p.kc * 2;
     return p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_tile) : 128 * p.kc * 2 + (p.b_res ? 0 : b_tile);
   }
@@ -1352,8 +1355,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
   __shared__ uint64_t empty_bar[8];
-  __shared__ uint64_t tfull_bar[2];
-  __shared__ uint64_t tempty_bar[2];
+  __shared__ uint64_t tfull_bar[4];
+  __shared__ uint64_t tempty_bar[4];
+  __shared__ uint64_t bfull_bar;  // resident-weights mode (leader): both CTAs' halves of the weight slab landed
   __shared__ __align__(16) float eparm[1024];
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
@@ -1363,28 +1367,38 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   const uint32_t rank = cluster_ctarank();
   const int cluster = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
 
+  // Row-window mode (a_win, see igemm_kernel): the A slot holds bw + 2 pixel rows of one image row, the three
+  // horizontal taps are row-shifted views of it; the weight operand is this CTA's HALF of every tile (BN/2 rows),
+  // resident for the whole kernel (b_res) or streamed three taps at a time.
   const uint32_t raw_addr = smem_u32(smem_raw);
-  uint8_t* ring = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  constexpr int a_stage_bytes = 128 * 128;
+  uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
+  const bool win = p.a_win != 0;
   const int b_half_bytes = (p.BN >> 1) * 128;
-  const int stage_bytes = a_stage_bytes + b_half_bytes;  // multiple of 1024
+  const int a_stage_bytes = win ? 17 * 1024 : 128 * 128;
+  const int b_stage_bytes = p.b_res ? 0 : (win ? 3 * b_half_bytes : b_half_bytes);
+  const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
+  const int bres_tiles = p.b_res ? p.ntaps * p.kc_per_tap : 0;
+  uint8_t* bres = smem;
+  uint8_t* ring = smem + bres_tiles * b_half_bytes;
   const int rows_used = p.bw * p.bh * p.bn;
-  const int num_kb = p.ntaps * p.kc_per_tap;
+  const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
   const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
   const int super_total = ((tiles_m + 1) >> 1) * p.tiles_n;  // pairs of M tiles x N tiles
-  const int acc_stride = p.tmem_cols >> 1;
+  const int acc_stride = p.tmem_cols / p.sets;
 
   if (warp == 1) {
     if (lane == 0) abort_flag = 0;
-    if (lane < 8) mbar_init(&full_bar[lane], 2);  // the leader's two producers (activations, weights)
+    if (lane < 8) mbar_init(&full_bar[lane], p.b_res ? 1 : 2);  // the leader's producers (activations, weights)
     else if (lane < 16) mbar_init(&empty_bar[lane - 8], 1);
-    else if (lane < 18) mbar_init(&tfull_bar[lane - 16], 1);
-    else if (lane < 20) mbar_init(&tempty_bar[lane - 18], 2 * kIgemmEpiWarps);
+    else if (lane < 20) mbar_init(&tfull_bar[lane - 16], 1);
+    else if (lane < 24) mbar_init(&tempty_bar[lane - 20], 2 * kIgemmEpiWarps);
+    else if (lane == 24) mbar_init(&bfull_bar, 1);
     fence_mbar_init();
   }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmA);
     prefetch_tmap(&p.tmB);
+    if (p.tst) prefetch_tmap(&p.tmO);
   }
   const bool staged = p.tiles_n == 1;
   if (staged && warp >= kIgemmEpiWarp0) {
@@ -1419,10 +1433,17 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
 
   if (warp == 0) {
     // ============================== TMA producer: activations (both CTAs) =====
+    if (p.b_res && elect_one()) {
+      // this CTA's half (BN/2 rows) of every resident weight tile; the bytes of both CTAs count on the leader
+      if (rank == 0) mbar_expect_tx(&bfull_bar, 2u * bres_tiles * b_half_bytes);
+      for (int i = 0; i < bres_tiles; ++i)
+        tma2_load_2d(bres + i * b_half_bytes, &p.tmB, &bfull_bar, p.b_k0 + i * 64, static_cast<int>(rank) * (p.BN >> 1));
+    }
+    __syncwarp();
     grid_dep_wait();
     int stage = 0;
     uint32_t phase = 0;
-    const uint32_t a_tx = 2u * rows_used * 128u;  // both CTAs' boxes
+    const uint32_t a_tx = win ? 2u * (p.bw + 2) * 128u : 2u * rows_used * 128u;  // both CTAs' boxes
     for (int s = cluster; s < super_total; s += nclusters) {
       const TileCoord t = my_tile(s);
       const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
@@ -1432,11 +1453,16 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
         if (elect_one()) {
           uint8_t* sa = ring + stage * stage_bytes;
           if (rank == 0) mbar_expect_tx(&full_bar[stage], a_tx);
-          const int c = p.a_c0 + p.tap_c[tap] + kci * 64;
-          if (p.a_rank == 4)
-            tma2_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
-          else
-            tma2_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+          if (win) {
+            // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
+            tma2_load_4d(sa, &p.tmA, &full_bar[stage], p.a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
+          } else {
+            const int c = p.a_c0 + p.tap_c[tap] + kci * 64;
+            if (p.a_rank == 4)
+              tma2_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
+            else
+              tma2_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+          }
         }
         __syncwarp();
         if (++kci == p.kc_per_tap) {
@@ -1451,21 +1477,35 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     }
   } else if (warp == 3) {
     // ============================== TMA producer: this CTA's half of the weight tile
-    int stage = 0;
-    uint32_t phase = 0;
-    const int half = p.BN >> 1;
-    for (int s = cluster; s < super_total; s += nclusters) {
-      const int row0 = (s % p.tiles_n) * p.BN + static_cast<int>(rank) * half;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
-        if (elect_one()) {
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * b_half_bytes);
-          tma2_load_2d(ring + stage * stage_bytes + a_stage_bytes, &p.tmB, &full_bar[stage], p.b_k0 + kb * 64, row0);
-        }
-        __syncwarp();
-        if (++stage == p.stages) {
-          stage = 0;
-          phase ^= 1u;
+    if (!p.b_res) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const int half = p.BN >> 1;
+      for (int s = cluster; s < super_total; s += nclusters) {
+        const int row0 = (s % p.tiles_n) * p.BN + static_cast<int>(rank) * half;
+        int tap = 0, kci = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+          if (elect_one()) {
+            uint8_t* sb = ring + stage * stage_bytes + a_stage_bytes;
+            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * b_stage_bytes);
+            if (win) {
+              for (int dwi = 0; dwi < 3; ++dwi)
+                tma2_load_2d(sb + dwi * b_half_bytes, &p.tmB, &full_bar[stage],
+                             p.b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, row0);
+            } else {
+              tma2_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * 64, row0);
+            }
+          }
+          __syncwarp();
+          if (++kci == p.kc_per_tap) {
+            kci = 0;
+            ++tap;
+          }
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
         }
       }
     }
@@ -1476,20 +1516,52 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
       const uint32_t idesc = make_idesc_f16(256, p.BN, p.f16 != 0);
       const uint32_t dhi = smem_desc_hi(1024, false);
       const uint32_t ring_u = smem_u32(ring);
+      const uint32_t bt16 = static_cast<uint32_t>(b_half_bytes) >> 4;  // weight half-tile in descriptor units
+      const uint32_t bres_lo = smem_desc_lo(smem_u32(bres));
+      const uint32_t bstep = p.kc_per_tap * bt16;
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      if (p.b_res) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
       for (int s = cluster; s < super_total; s += nclusters, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
+        if (it != 0 && ++as == p.sets) {
+          as = 0;
+          aphase ^= 1u;
+        }
         const uint32_t d_tmem = tmem_base_u + as * acc_stride;
         mbar_wait_nofail(&tempty_bar[as], aphase ^ 1u, &abort_flag);
         tc_fence_after();
+        uint32_t bq = bres_lo;
+        int kci = 0;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait_nofail(&full_bar[stage], phase, &abort_flag);
           tc_fence_after();
           const uint32_t sa = ring_u + stage * stage_bytes;
-          umma2_bf16_batch4(d_tmem, smem_desc_lo(sa), smem_desc_lo(sa + a_stage_bytes), dhi, idesc, kb != 0);
+          const uint32_t a_lo = smem_desc_lo(sa);
+          if (win) {
+            // the horizontal taps are views of the window shifted by whole pixel rows (128 B = 8 descriptor units)
+            if (p.b_res) {
+              umma2_bf16_batch4(d_tmem, a_lo, bq, dhi, idesc, kb != 0);
+              umma2_bf16_batch4(d_tmem, a_lo + 8, bq + bstep, dhi, idesc, 1);
+              umma2_bf16_batch4(d_tmem, a_lo + 16, bq + 2 * bstep, dhi, idesc, 1);
+              bq += bt16;
+              if (++kci == p.kc_per_tap) {
+                kci = 0;
+                bq += 2 * bstep;
+              }
+            } else {
+              const uint32_t b_lo = smem_desc_lo(sa + a_stage_bytes);
+              umma2_bf16_batch4(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
+              umma2_bf16_batch4(d_tmem, a_lo + 8, b_lo + bt16, dhi, idesc, 1);
+              umma2_bf16_batch4(d_tmem, a_lo + 16, b_lo + 2 * bt16, dhi, idesc, 1);
+            }
+          } else {
+            const uint32_t b_lo = p.b_res ? bq : smem_desc_lo(sa + a_stage_bytes);
+            umma2_bf16_batch4(d_tmem, a_lo, b_lo, dhi, idesc, kb != 0);
+            bq += bt16;
+          }
           umma2_commit_elect(&empty_bar[stage]);  // frees the slot in both CTAs when these MMAs retire
           if (++stage == p.stages) {
             stage = 0;
@@ -1507,9 +1579,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     int it = 0;
     for (int s = cluster; s < super_total; s += nclusters, ++it) {
       const TileCoord t = my_tile(s);
-      const int as = it & 1;
+      const int as = p.sets == 4 ? (it & 3) : (it & 1);
+      const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
       const bool use_stg = p.stg && s + nclusters >= super_total;
-      if (!epi.template tile<true>(p, t, as, (it >> 1) & 1, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) break;
+      if (!epi.template tile<true>(p, t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) break;
     }
     if (!abort_flag) epi.st_finish(p);
   }
@@ -1583,7 +1656,11 @@ const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream) {
 int igemm_smem_bytes(const IgemmParams& p) {
   // behind the operand ring: exchange buffer of the fused statistics, or the staging of the TMA-store epilogue
   const int st = p.st_mode ? 8192 : (p.tst ? 2 * 4 * (p.BN >> 6) * 4096 : 0);
-  if (p.cta2) return p.stages * (128 * 128 + (p.BN >> 1) * 128) + 1024 + st;
+  if (p.cta2) {
+    const int b_half = (p.BN >> 1) * 128;
+    const int stage2 = p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half);
+    return p.stages * stage2 + (p.b_res ? p.ntaps * p.kc_per_tap * b_half : 0) + 1024 + st;
+  }
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
   const int b_tile = p.BN * row_bytes;
@@ -1648,13 +1725,20 @@ const char* igemm_dev_state(IgemmDevState* out) {
 
 namespace {
 const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, cudaStream_t stream) {
-  if (p.mode != kModeLinear || p.kc != 64 || p.a_win || p.b_res || p.splits != 1 || p.dual)
-    return "igemm2: the CTA-pair kernel runs plain linear-mode convs with 64-channel chunks";
+  if (p.mode != kModeLinear || p.kc != 64 || p.splits != 1 || p.dual)
+    return "igemm2: the CTA-pair kernel runs linear-mode convs with 64-channel chunks";
+  if (p.a_win && (p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.a_rank != 4 || p.bw > 128 || p.nphase > 1))
+    return "igemm2: row-window mode needs a 3x3 stride-1 conv and single-row tiles";
+  if (p.b_res && p.tiles_n != 1) return "igemm2: resident weights need one N tile";
   if (p.BN % 16 || p.BN < 32 || p.BN > 256) return "igemm2: BN must be a multiple of 16 in [32,256]";
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm2: M box must hold 1..128 rows";
   if (p.stages < 2 || p.stages > 8) return "igemm2: stages must be in [2,8]";
-  if (p.sets != 2 || p.tmem_cols < 2 * p.BN || p.tmem_cols > 512 || (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
+  if ((p.sets != 2 && p.sets != 4) || p.tmem_cols < p.sets * p.BN || p.tmem_cols > 512 ||
+      (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm2: bad tmem_cols";
+  if (p.tst && (p.out_f32 || p.st_mode || p.stg || p.out2 || p.nphase > 1 || (p.BN != 64 && p.BN != 128) || p.bw % 32 ||
+                p.n_valid % 64))
+    return "igemm2: the TMA-store epilogue needs a plain 16-bit tile of 64 / 128 columns and rows of 32 pixels";
   if (p.ntaps * (p.nphase > 1 ? p.nphase : 1) > kIgemmMaxTaps) return "igemm2: too many taps";
   if (p.nphase > 1 && (p.nphase != 4 || p.tpn < 1 || p.tiles_n != p.nphase * p.tpn)) return "igemm2: bad phase tiling";
   if (p.stg && (p.out_f32 || (p.BN != 128 && p.BN != 256) || p.n_valid % (p.BN >> 2)))
