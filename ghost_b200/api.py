@@ -815,7 +815,12 @@ def get_final_video(final_frames, crop_frames, full_frames, tfm_array, OUT_VIDEO
         crops, mks, tfs, ffr = [], [], [], []
         for i in range(c0, c1):
             for j in range(nJ):
-                if len(crop_frames[j][i]) == 0 or len(final_frames[j][i]) == 0:
+                # the reference resizes the swapped frame first (video_processing.py:212): for a frame without this face
+                # that raises inside its try / except and the iteration ends with params[j] untouched; the reset at
+                # :214-216 is only reached by a swapped frame whose crop is missing
+                if len(final_frames[j][i]) == 0:
+                    continue
+                if len(crop_frames[j][i]) == 0:
                     params[j] = None
                     continue
                 if masks is not None:

@@ -85,25 +85,29 @@ DeviceTables& resize_tables() {
   return t;
 }
 
-// grow-only per-device scratch for the paste-back face table
-struct Scratch {
-  void* p = nullptr;
-  size_t cap = 0;
-};
-void* paste_scratch(size_t bytes) {
-  static std::map<int, Scratch> per_dev;
+// Per-call scratch (face tables, resized crops) comes from the device's stream-ordered pool, so that calls on
+// different streams or threads never share a buffer.  The pool keeps what it has handed out once
+// (release threshold = max): after the first call an allocation is a pointer bump on the stream, not a cudaMalloc.
+void* stream_scratch(size_t bytes, cudaStream_t s) {
+  static std::mutex mu;
+  static bool tuned[64] = {};
   int dev = 0;
   check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
-  Scratch& s = per_dev[dev];
-  if (s.cap < bytes) {
-    if (s.p) {
-      check_cuda(cudaDeviceSynchronize(), "scratch sync");
-      cudaFree(s.p);
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev >= 0 && dev < 64 && !tuned[dev]) {
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+      cudaGetLastError();
+      tuned[dev] = true;
     }
-    s.cap = bytes * 2 + 4096;
-    check_cuda(cudaMalloc(&s.p, s.cap), "paste scratch");
   }
-  return s.p;
+  void* p = nullptr;
+  check_cuda(cudaMallocAsync(&p, bytes, s), "stream-ordered scratch");
+  return p;
 }
 
 }  // namespace
@@ -495,7 +499,7 @@ int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
     const size_t fb = faces.size() * sizeof(PasteFace), sb = start.size() * sizeof(int);
     const size_t fb_al = (fb + 255) / 256 * 256;
     const size_t sb_al = (sb + 255) / 256 * 256;
-    char* scratch = static_cast<char*>(paste_scratch(fb_al + sb_al + paste_rz_bytes(d->n_faces > 0 ? d->n_crops : 0)));
+    char* scratch = static_cast<char*>(stream_scratch(fb_al + sb_al + paste_rz_bytes(d->n_faces > 0 ? d->n_crops : 0), s));
     check_cuda(cudaMemcpyAsync(scratch, faces.data(), fb, cudaMemcpyHostToDevice, s), "faces upload");
     check_cuda(cudaMemcpyAsync(scratch + fb_al, start.data(), sb, cudaMemcpyHostToDevice, s), "face index upload");
     DeviceTables& t = resize_tables();
@@ -515,7 +519,9 @@ int ghost_paste_back(const ghost_paste_desc* d, void* stream) {
     p.n_faces = d->n_faces;
     p.n_crops = d->n_crops;
     p.rz = reinterpret_cast<uint8_t*>(scratch + fb_al + sb_al);
-    check_msg(paste_back_launch(p, faces.data(), s), "paste_back");
+    const char* err = paste_back_launch(p, faces.data(), s);
+    cudaFreeAsync(scratch, s);  // stream-ordered: released behind the kernels that read it
+    check_msg(err, "paste_back");
   });
 }
 

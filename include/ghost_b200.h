@@ -180,6 +180,8 @@ typedef struct {
   int mode;                 /* ghost_paste_mode */
 } ghost_paste_desc;
 
+/* Re-entrant: the per-call tables and the resized crops live in a stream-ordered allocation (cudaMallocAsync on
+ * `stream`, released behind the kernels), so concurrent calls on different streams / threads share nothing. */
 int ghost_paste_back(const ghost_paste_desc* desc, void* stream);
 
 /* The paste-back rewrites only the bounding box of each face (the image of the 224 x 224 crop under the inverse of

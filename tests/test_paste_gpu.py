@@ -270,3 +270,40 @@ def test_swap_pipeline_with_sr_stage_matches_sequential_calls():
             sr_b.enhance_u8(swapped[b0:b0 + 2], out=enh[b0:b0 + 2])
         ref = ghost_b200.paste_back(frm.cuda(), enh, msk.cuda(), tf, face_frame, mode="exact")
         assert torch.equal(out, ref.cpu())
+
+
+def test_get_final_video_handler_keeps_preset_across_a_gap():
+    """Handler path with a frame that has no face in mid-sequence: the reference resizes the (empty) swapped frame
+    first, cv2 raises inside its try / except, and the erode / blur preset chosen on the first face stays in force
+    (video_processing.py:209-216) - the mask after the gap is built with the FIRST frame's preset, not a new one."""
+    from ghost_b200 import masks as M
+
+    class Handler(object):   # landmark "model": the shift of the face is written in the crop's first pixel
+        def get_without_detection_without_transform(self, img):
+            return synth.landmarks106(np.random.default_rng(5), shift=float(int(img[0, 0, 0]) % 16))
+
+    rng = np.random.default_rng(21)
+    H, W = 360, 640
+    frames = [synth.frame_u8(H, W, seed=60 + i) for i in range(3)]
+    tf = [synth.similarity_tfm(H, W, rng, scale=0.8) for _ in range(3)]
+
+    def crop(seed, tag, size):
+        c = synth.frame_u8(size, size, seed=seed, cell=8)
+        c[:16, :16] = tag
+        return c
+    swaps = [crop(70, 3, 256), [], crop(72, 0, 256)]          # frame 0: swapped face shifted by 3 px -> preset [15,15,10]
+    targets = [crop(80, 0, 224), [], crop(82, 0, 224)]        # frame 2 alone would pick the default [5,5,5]
+    out = ghost_b200.get_final_video([swaps], [targets], frames, [[tf[0], [], tf[2]]], None, 30.0, handler=Handler())
+    assert np.array_equal(out[1], frames[1])                  # the gap: frame untouched
+    h = Handler()
+    import cv2
+    lm0 = h.get_without_detection_without_transform(cv2.resize(swaps[0], (224, 224)))
+    lm2 = h.get_without_detection_without_transform(cv2.resize(swaps[2], (224, 224)))
+    assert M.choose_params(lm0, h.get_without_detection_without_transform(targets[0])) == [15, 15, 10]
+    assert M.choose_params(lm2, h.get_without_detection_without_transform(targets[2])) == [5, 5, 5]
+    kept = M.face_masks(lm2[None], [[15, 15, 10]], dtype=torch.float32)[0]
+    fresh = M.face_masks(lm2[None], [[5, 5, 5]], dtype=torch.float32)[0]
+    want = ghost_b200.get_final_video([[swaps[2]]], [[targets[2]]], [frames[2]], [[tf[2]]], None, 30.0, masks=[[kept]])[0]
+    other = ghost_b200.get_final_video([[swaps[2]]], [[targets[2]]], [frames[2]], [[tf[2]]], None, 30.0, masks=[[fresh]])[0]
+    assert np.array_equal(out[2], want)
+    assert not np.array_equal(want, other)                    # the two presets do differ on this face
