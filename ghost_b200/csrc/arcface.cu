@@ -111,6 +111,32 @@ void Net::build_arcface(ExecPlan& p) {
     a.p = p.pool.alloc(a.bytes());
     return a;
   };
+  // Lowered convs wait in `pend` while the next one has the same geometry: the identical-shape 3x3 convs of a stage
+  // (layer 3: 58 launches, layer 2: 24) become ONE chain launch (conv.cuh make_chain) - every cluster keeps whole images,
+  // so a cluster barrier stands where the kernel boundary was.
+  std::vector<LaunchOp> pend;
+  auto push_lop = [&](const LaunchOp& lop) {
+    Op op;
+    op.name = lop.name;
+    op.flops = lop.flops;
+    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : kOpConvTC;
+    op.run = [lop](cudaStream_t s) { return lop.launch(s); };
+    p.ops.push_back(std::move(op));
+  };
+  auto flush = [&]() {
+    if (pend.size() >= 2) {
+      LaunchOp chain;
+      bool fused = false;
+      check_msg(make_chain(&chain, pend, p.pool.alloc(chain_param_bytes(pend.size())), &fused), pend.front().name);
+      if (fused) {
+        push_lop(chain);
+        pend.clear();
+        return;
+      }
+    }
+    for (const LaunchOp& l : pend) push_lop(l);
+    pend.clear();
+  };
   auto add_conv = [&](const std::string& name, const Act& in, int Cin, const Taps& taps, int Ho, int Wo,
                       const std::string& wname, const OutView& out, const Epilogue& epi) {
     auto it = packed_.find(wname);
@@ -119,12 +145,8 @@ void Net::build_arcface(ExecPlan& p) {
     lop.name = name;
     check_msg(lower_conv(&lop, in, 0, Cin, taps, Ho, Wo, it->second, out, epi, !bf, err, nullptr), name);
     if (lop.ws_bytes) lop.set_workspace(p.pool.alloc(lop.ws_bytes));  // split-K partial tiles
-    Op op;
-    op.name = name;
-    op.flops = lop.flops;
-    op.cls = lop.kind == LaunchOp::kSimt ? kOpConvSimt : kOpConvTC;
-    op.run = [lop](cudaStream_t s) { return lop.launch(s); };
-    p.ops.push_back(std::move(op));
+    if (!pend.empty() && !chain_compatible(pend.front(), lop)) flush();
+    pend.push_back(lop);
   };
 
   // Block names in execution order: in bf16 mode the conv that produces a block's input also writes bn1(input)
@@ -171,6 +193,7 @@ void Net::build_arcface(ExecPlan& p) {
         const Act xx = x, tt = t;
         const float* scv = vecs_.at(n + ".bn1.scale");
         const float* shv = vecs_.at(n + ".bn1.shift");
+        flush();
         Op op;
         op.name = n + ".bn1";
         op.run = [=](cudaStream_t s) {
@@ -221,6 +244,7 @@ void Net::build_arcface(ExecPlan& p) {
   } else {
     add_conv("fc", flat, 25088, Taps::point(), 1, 1, "fc", zo, Epilogue());
   }
+  flush();
 }
 
 }  // namespace ghost

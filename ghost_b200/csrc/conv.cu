@@ -595,4 +595,80 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   return nullptr;
 }
 
+// ------------------------------------------------------------------------------------------------ conv chains
+bool chain_compatible(const LaunchOp& first, const LaunchOp& next) {
+  static const int on = [] {
+    const char* e = getenv("GHOST_CHAIN");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  if (!on || first.kind != LaunchOp::kIgemm || next.kind != LaunchOp::kIgemm) return false;
+  const IgemmParams &a = first.ig, &b = next.ig;
+  auto plain = [](const IgemmParams& p) {
+    return p.cta2 && p.mode == kModeLinear && p.splits == 1 && !p.st_mode && !p.tst && !p.b_res && !p.a_win && p.nphase <= 1 &&
+           !p.out_f32 && !p.dual && p.kc == 64 && p.act2 == kAct2None;
+  };
+  if (!plain(a) || !plain(b)) return false;
+  if (a.a_rank != b.a_rank || a.bw != b.bw || a.bh != b.bh || a.bn != b.bn || a.tiles_w != b.tiles_w ||
+      a.tiles_h != b.tiles_h || a.tiles_nb != b.tiles_nb || a.tiles_n != b.tiles_n || a.Nimg != b.Nimg || a.Ho != b.Ho ||
+      a.Wo != b.Wo || a.BN != b.BN || a.n_valid != b.n_valid || a.ntaps != b.ntaps || a.kc_per_tap != b.kc_per_tap ||
+      a.stages != b.stages || a.tmem_cols != b.tmem_cols || a.sets != b.sets || a.stg != b.stg || a.f16 != b.f16 ||
+      a.err != b.err)
+    return false;
+  for (int t = 0; t < a.ntaps; ++t)
+    if (a.tap_c[t] != b.tap_c[t] || a.tap_w[t] != b.tap_w[t] || a.tap_p[t] != b.tap_p[t] || a.tap_h[t] != b.tap_h[t]) return false;
+  return true;
+}
+
+const char* make_chain(LaunchOp* out, const std::vector<LaunchOp>& steps, void* dev_params, bool* fused) {
+  *fused = false;
+  if (steps.size() < 2) return nullptr;
+  for (size_t i = 1; i < steps.size(); ++i)
+    if (!chain_compatible(steps[0], steps[i])) return "make_chain: steps of different geometry";
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+    return "make_chain: no device";
+  const int clusters = sms / 2;
+  IgemmParams g = steps[0].ig;
+  // a group = the M-tile pairs of bn whole images (x all N tiles); an odd tile count per image gets one tile of rows
+  // past the image: its loads are zero-filled and its rows never stored
+  int tiles_h = g.tiles_h;
+  if ((g.tiles_w * tiles_h) & 1) ++tiles_h;
+  const int spg = (g.tiles_w * tiles_h / 2) * g.tiles_n;
+  const int ngroups = g.tiles_nb;
+  const long long rounds_chain = static_cast<long long>((ngroups + clusters - 1) / clusters) * spg;
+  const long long supers_plain = static_cast<long long>((g.tiles_w * g.tiles_h * g.tiles_nb + 1) / 2) * g.tiles_n;
+  const long long rounds_plain = (supers_plain + clusters - 1) / clusters;
+  if (rounds_chain > rounds_plain) return nullptr;  // not worth it: *fused stays false
+  // room for the chain's shared-memory blocks behind the ring
+  int stages = g.stages;
+  {
+    IgemmParams probe = g;
+    probe.chain_n = static_cast<int>(steps.size());
+    const int budget = 221 * 1024;
+    while (stages >= 3 && (probe.stages = stages, igemm_smem_bytes(probe)) > budget) --stages;
+    probe.stages = stages;
+    if (igemm_smem_bytes(probe) > budget) return nullptr;
+    const int stage_bytes = 128 * 128 + (g.BN >> 1) * 128;
+    if (g.stg && 256 * g.BN > stages * stage_bytes) return nullptr;
+  }
+  std::vector<IgemmParams> host(steps.size());
+  for (size_t i = 0; i < steps.size(); ++i) {
+    host[i] = steps[i].ig;
+    host[i].tiles_h = tiles_h;
+    host[i].stages = stages;
+    host[i].chain = static_cast<const IgemmParams*>(dev_params);
+    host[i].chain_n = static_cast<int>(steps.size());
+    host[i].chain_spg = spg;
+  }
+  if (cudaMemcpy(dev_params, host.data(), host.size() * sizeof(IgemmParams), cudaMemcpyHostToDevice) != cudaSuccess)
+    return "make_chain: parameter upload failed";
+  *out = steps[0];
+  out->ig = host[0];
+  out->name = steps.front().name + ".." + steps.back().name;
+  out->flops = 0.0;
+  for (const LaunchOp& s : steps) out->flops += s.flops;
+  *fused = true;
+  return nullptr;
+}
+
 }  // namespace ghost

@@ -149,6 +149,16 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
                        const PackedW& w, const OutView& out, const Epilogue& epi, bool force_simt, int* err_word,
                        const AadArgs* aad = nullptr, int bn_hint = 0, const DeconvPhases* phases = nullptr);
 
+// Conv chains (igemm.cuh `chain`): consecutive lowered convs that feed one another, all on the CTA-pair kernel with
+// identical geometry, as ONE launch.  chain_compatible() says whether `next` may follow `first` in a chain;
+// make_chain() turns steps (>= 2) into one launch-ready op - `dev_params` is device memory for steps.size() parameter
+// blocks (chain_param_bytes(), 128-byte aligned), filled here with a synchronous copy.  Returns nullptr on success and
+// sets *fused = false (leaving `out` untouched) when the chain would cost more rounds of the persistent grid than the
+// separate launches (groups of whole images per cluster do not always divide the tile count as well).
+bool chain_compatible(const LaunchOp& first, const LaunchOp& next);
+inline size_t chain_param_bytes(size_t steps) { return steps * sizeof(IgemmParams); }
+const char* make_chain(LaunchOp* out, const std::vector<LaunchOp>& steps, void* dev_params, bool* fused);
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
 const char* encode_tmap(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                         const uint32_t* box, int swizzle_bytes);

@@ -41,6 +41,7 @@ __device__ unsigned long long g_tl_t0[kTlSlots], g_tl_t1[kTlSlots];
 __device__ int g_tl_meta[kTlSlots][12];
 __device__ long long g_tl_cta0[8];  // CTA 0 of the running launch: entry clock, prologue end, issuer end, epilogue end
 __device__ unsigned int g_tl_seq, g_tl_done;
+#define PROF_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && ew == 0 && lg == 0 && lane == 0) g_tl_cta0[i] = clock64(); } while (0)
 #define PROF_BEGIN() long long pw0_ = 0, pw1_ = 0; const long long pt0_ = clock64()
 #define PROF_WAIT0(stmt) do { const long long a_ = clock64(); stmt; pw0_ += clock64() - a_; } while (0)
 #define PROF_WAIT1(stmt) do { const long long a_ = clock64(); stmt; pw1_ += clock64() - a_; } while (0)
@@ -48,6 +49,7 @@ __device__ unsigned int g_tl_seq, g_tl_done;
     g_igemm_prof[blockIdx.x][slot] = pw0_; g_igemm_prof[blockIdx.x][slot + 1] = pw1_; \
     g_igemm_prof[blockIdx.x][slot + 2] = clock64() - pt0_; } } while (0)
 #else
+#define PROF_STAMP(i) do {} while (0)
 #define PROF_BEGIN() do {} while (0)
 #define PROF_WAIT0(stmt) stmt
 #define PROF_WAIT1(stmt) stmt
@@ -230,8 +232,9 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
           if (p.res) {
             const __nv_bfloat16* rp = p.res + r_pix + col0;
             if (full16) {
-              const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
-              const uint4 q1 = __ldg(reinterpret_cast<const uint4*>(rp) + 1);
+              // (conv chains read residuals written earlier in the same launch: no non-coherent loads there)
+              const uint4 q0 = p.chain_n ? ld_global_cg16(rp) : __ldg(reinterpret_cast<const uint4*>(rp));
+              const uint4 q1 = p.chain_n ? ld_global_cg16(rp + 8) : __ldg(reinterpret_cast<const uint4*>(rp) + 1);
               const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
@@ -511,6 +514,7 @@ struct LinEpi {
           return true;
         }
         if (use_stg) {
+          PROF_STAMP(5);  // accumulator complete
           if (p.res != nullptr) {
             // residual rows of this warp's piece of the tile, as whole row segments
 #pragma unroll
@@ -521,11 +525,13 @@ struct LinEpi {
                 const int v_row = __shfl_sync(0xffffffffu, static_cast<int>(valid), row);
                 if (v_row && cols_on)
                   *reinterpret_cast<uint4*>(wst + row * rowb + ((rb_piece ^ stg_key(row)) << 4)) =
-                      __ldg(reinterpret_cast<const uint4*>(p.res + rp_row + colw + rb_piece * 8));
+                      p.chain_n ? ld_global_cg16(p.res + rp_row + colw + rb_piece * 8)
+                                : __ldg(reinterpret_cast<const uint4*>(p.res + rp_row + colw + rb_piece * 8));
               }
             }
             __syncwarp();
           }
+          PROF_STAMP(6);  // residual rows staged
           uint8_t* my_row = wst + lane * rowb;
           const int my_key = stg_key(lane);
 #pragma unroll
@@ -585,6 +591,7 @@ struct LinEpi {
           // the accumulator stage goes back to the MMA warp before the global stores
           tc_fence_before();
           __syncwarp();
+          PROF_STAMP(7);  // tile converted into the staging rows
           release<REMOTE>(tempty);
           if (STATS && p.st_mode == 1) st_flush(p, t.th * p.tiles_w + t.tw);
           const int jt = ew * wcols + rb_piece * 8;  // tile column of this lane's 8 channels
@@ -1350,7 +1357,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
 // TMEM allocation.  Barriers: `full` lives in the leader (both CTAs' TMA loads count their bytes there), `empty` and
 // `tfull` are signalled in both CTAs by multicast commits, `tempty` lives in the leader and collects the epilogue
 // warps of both CTAs.
-template <bool F16, bool STATS>
+template <bool F16, bool STATS, bool CHAIN>
 __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_constant__ IgemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[8];
@@ -1366,6 +1373,14 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cluster = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+#ifdef GHOST_IGEMM_PROF
+  const long long cta_t0 = clock64();
+  unsigned long long cta_ns0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cta_ns0));
+  const unsigned tl_seq = *reinterpret_cast<volatile unsigned*>(&g_tl_seq) & (kTlSlots - 1);
+  if (threadIdx.x == 0) atomicMin(&g_tl_t0[tl_seq], cta_ns0);
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[0] = cta_t0;
+#endif
 
   // Row-window mode (a_win, see igemm_kernel): the A slot holds bw + 2 pixel rows of one image row, the three
   // horizontal taps are row-shifted views of it; the weight operand is this CTA's HALF of every tile (BN/2 rows),
@@ -1385,6 +1400,12 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
   const int super_total = ((tiles_m + 1) >> 1) * p.tiles_n;  // pairs of M tiles x N tiles
   const int acc_stride = p.tmem_cols / p.sets;
+  // conv chain (igemm.cuh `chain`): nsteps convs of this geometry; a cluster walks whole groups of spg super tiles
+  const int nsteps = CHAIN ? p.chain_n : 1;
+  const int spg = CHAIN ? p.chain_spg : 1;
+  const int ngroups = super_total / spg;
+  IgemmParams* const sp = reinterpret_cast<IgemmParams*>(ring + p.stages * stage_bytes);  // [2], chain launches only
+  float* const eparm2 = reinterpret_cast<float*>(ring + p.stages * stage_bytes + 2 * sizeof(IgemmParams));  // [2][1024]
 
   if (warp == 1) {
     if (lane == 0) abort_flag = 0;
@@ -1402,13 +1423,19 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   }
   const bool staged = p.tiles_n == 1;
   if (staged && warp >= kIgemmEpiWarp0) {
+    float* ep0 = CHAIN ? eparm2 : eparm;
     for (int i = threadIdx.x - kIgemmEpiWarp0 * 32; i < p.BN; i += kIgemmEpiWarps * 32) {
       const bool in = i < p.n_valid;
-      eparm[i] = (in && p.bias) ? __ldg(p.bias + i) : 0.f;
-      eparm[256 + i] = (in && p.act1 == kActPRelu) ? __ldg(p.slope_c + i) : 0.f;
-      eparm[512 + i] = (in && p.out2) ? __ldg(p.scale2 + i) : 0.f;
-      eparm[768 + i] = (in && p.out2) ? __ldg(p.shift2 + i) : 0.f;
+      ep0[i] = (in && p.bias) ? __ldg(p.bias + i) : 0.f;
+      ep0[256 + i] = (in && p.act1 == kActPRelu) ? __ldg(p.slope_c + i) : 0.f;
+      ep0[512 + i] = (in && p.out2) ? __ldg(p.scale2 + i) : 0.f;
+      ep0[768 + i] = (in && p.out2) ? __ldg(p.shift2 + i) : 0.f;
     }
+  }
+  if (CHAIN) {  // step 0's parameter block (= p) into its shared-memory slot
+    const uint4* src = reinterpret_cast<const uint4*>(p.chain);
+    for (int i = threadIdx.x; i < static_cast<int>(sizeof(IgemmParams) / 16); i += kIgemmThreads)
+      reinterpret_cast<uint4*>(sp)[i] = __ldg(src + i);
   }
   if (warp == 2) tmem2_alloc(&tmem_base_smem, p.tmem_cols);
   tc_fence_before();
@@ -1417,6 +1444,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
   grid_dep_launch();
+#ifdef GHOST_IGEMM_PROF
+  if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[1] = clock64();
+#endif
 
   // super tile s -> this CTA's own tile: N tile s % tiles_n, M tile 2 * (s / tiles_n) + rank (an odd tile count
   // leaves the last pair's second CTA with a tile past the batch: its loads are zero-filled, its rows never stored)
@@ -1444,70 +1474,85 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t a_tx = win ? 2u * (p.bw + 2) * 128u : 2u * rows_used * 128u;  // both CTAs' boxes
-    for (int s = cluster; s < super_total; s += nclusters) {
-      const TileCoord t = my_tile(s);
-      const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
-      int tap = p.nphase > 1 ? (t.nt / p.tpn) * p.ntaps : 0, kci = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
-        if (elect_one()) {
-          uint8_t* sa = ring + stage * stage_bytes;
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], a_tx);
-          if (win) {
-            // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
-            tma2_load_4d(sa, &p.tmA, &full_bar[stage], p.a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
-          } else {
-            const int c = p.a_c0 + p.tap_c[tap] + kci * 64;
-            if (p.a_rank == 4)
-              tma2_load_4d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
-            else
-              tma2_load_5d(sa, &p.tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+    for (int step = 0; step < nsteps; ++step) {
+      const CUtensorMap* tmA = CHAIN ? &p.chain[step].tmA : &p.tmA;
+      const int a_c0 = CHAIN ? sp[step & 1].a_c0 : p.a_c0;
+      for (int g = cluster; g < ngroups; g += nclusters) {
+        for (int u = 0; u < spg; ++u) {
+          const TileCoord t = my_tile(g * spg + u);
+          const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+          int tap = p.nphase > 1 ? (t.nt / p.tpn) * p.ntaps : 0, kci = 0;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+            if (elect_one()) {
+              uint8_t* sa = ring + stage * stage_bytes;
+              if (rank == 0) mbar_expect_tx(&full_bar[stage], a_tx);
+              if (win) {
+                // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
+                tma2_load_4d(sa, tmA, &full_bar[stage], a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
+              } else {
+                const int c = a_c0 + p.tap_c[tap] + kci * 64;
+                if (p.a_rank == 4)
+                  tma2_load_4d(sa, tmA, &full_bar[stage], c, w0 + p.tap_w[tap], h0 + p.tap_h[tap], n0);
+                else
+                  tma2_load_5d(sa, tmA, &full_bar[stage], c, w0 + p.tap_w[tap], p.tap_p[tap], h0 + p.tap_h[tap], n0);
+              }
+            }
+            __syncwarp();
+            if (++kci == p.kc_per_tap) {
+              kci = 0;
+              ++tap;
+            }
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
         }
-        __syncwarp();
-        if (++kci == p.kc_per_tap) {
-          kci = 0;
-          ++tap;
-        }
-        if (++stage == p.stages) {
-          stage = 0;
-          phase ^= 1u;
-        }
       }
+      // the next conv of the chain reads what this cluster's epilogue warps are still writing
+      if (CHAIN && step + 1 < nsteps) cluster_sync_all();
     }
   } else if (warp == 3) {
     // ============================== TMA producer: this CTA's half of the weight tile
-    if (!p.b_res) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const int half = p.BN >> 1;
-      for (int s = cluster; s < super_total; s += nclusters) {
-        const int row0 = (s % p.tiles_n) * p.BN + static_cast<int>(rank) * half;
-        int tap = 0, kci = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
-          if (elect_one()) {
-            uint8_t* sb = ring + stage * stage_bytes + a_stage_bytes;
-            if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * b_stage_bytes);
-            if (win) {
-              for (int dwi = 0; dwi < 3; ++dwi)
-                tma2_load_2d(sb + dwi * b_half_bytes, &p.tmB, &full_bar[stage],
-                             p.b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, row0);
-            } else {
-              tma2_load_2d(sb, &p.tmB, &full_bar[stage], p.b_k0 + kb * 64, row0);
+    int stage = 0;
+    uint32_t phase = 0;
+    const int half = p.BN >> 1;
+    for (int step = 0; step < nsteps; ++step) {
+      const CUtensorMap* tmB = CHAIN ? &p.chain[step].tmB : &p.tmB;
+      const int b_k0 = CHAIN ? sp[step & 1].b_k0 : p.b_k0;
+      if (!p.b_res) {
+        for (int g = cluster; g < ngroups; g += nclusters) {
+          for (int u = 0; u < spg; ++u) {
+            const int row0 = ((g * spg + u) % p.tiles_n) * p.BN + static_cast<int>(rank) * half;
+            int tap = 0, kci = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+              mbar_wait_nofail(&empty_bar[stage], phase ^ 1u, &abort_flag);
+              if (elect_one()) {
+                uint8_t* sb = ring + stage * stage_bytes + a_stage_bytes;
+                if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * b_stage_bytes);
+                if (win) {
+                  for (int dwi = 0; dwi < 3; ++dwi)
+                    tma2_load_2d(sb + dwi * b_half_bytes, tmB, &full_bar[stage],
+                                 b_k0 + ((tap * 3 + dwi) * p.kc_per_tap + kci) * 64, row0);
+                } else {
+                  tma2_load_2d(sb, tmB, &full_bar[stage], b_k0 + kb * 64, row0);
+                }
+              }
+              __syncwarp();
+              if (++kci == p.kc_per_tap) {
+                kci = 0;
+                ++tap;
+              }
+              if (++stage == p.stages) {
+                stage = 0;
+                phase ^= 1u;
+              }
             }
-          }
-          __syncwarp();
-          if (++kci == p.kc_per_tap) {
-            kci = 0;
-            ++tap;
-          }
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1u;
           }
         }
       }
+      if (CHAIN && step + 1 < nsteps) cluster_sync_all();
     }
   } else if (warp == 1) {
     // ============================== MMA issuer of the pair (leader CTA) =======
@@ -1525,7 +1570,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
       int as = 0;
       uint32_t aphase = 0;
       if (p.b_res) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
-      for (int s = cluster; s < super_total; s += nclusters, ++it) {
+      for (int step = 0; step < nsteps; ++step) {
+      for (int gu = 0, ng = (ngroups > cluster ? (ngroups - 1 - cluster) / nclusters + 1 : 0) * spg; gu < ng; ++gu, ++it) {
         if (it != 0 && ++as == p.sets) {
           as = 0;
           aphase ^= 1u;
@@ -1570,21 +1616,77 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
         }
         umma2_commit_elect(&tfull_bar[as]);
       }
+      if (CHAIN && step + 1 < nsteps) cluster_sync_all();
+      }
+#ifdef GHOST_IGEMM_PROF
+      if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0) g_tl_cta0[2] = clock64();
+#endif
+    } else if (CHAIN) {
+      for (int step = 0; step + 1 < nsteps; ++step) cluster_sync_all();
+    }
+  } else if (CHAIN && warp == 2) {
+    // ============================== chain: the next step's parameter block and epilogue tables ==========
+    for (int step = 0; step + 1 < nsteps; ++step) {
+      const IgemmParams* nx = p.chain + step + 1;
+      uint4* dst = reinterpret_cast<uint4*>(sp + ((step + 1) & 1));
+      for (int i = lane; i < static_cast<int>(sizeof(IgemmParams) / 16); i += 32)
+        dst[i] = __ldg(reinterpret_cast<const uint4*>(nx) + i);
+      if (staged) {
+        float* ep = eparm2 + ((step + 1) & 1) * 1024;
+        const float* bias = nx->bias;
+        const float* slope_c = nx->act1 == kActPRelu ? nx->slope_c : nullptr;
+        const float* scale2 = nx->out2 ? nx->scale2 : nullptr;
+        const float* shift2 = nx->out2 ? nx->shift2 : nullptr;
+        for (int i = lane; i < p.BN; i += 32) {
+          const bool in = i < p.n_valid;
+          ep[i] = (in && bias) ? __ldg(bias + i) : 0.f;
+          ep[256 + i] = (in && slope_c) ? __ldg(slope_c + i) : 0.f;
+          ep[512 + i] = (in && scale2) ? __ldg(scale2 + i) : 0.f;
+          ep[768 + i] = (in && shift2) ? __ldg(shift2 + i) : 0.f;
+        }
+      }
+      __syncwarp();
+      cluster_sync_all();
     }
   } else if (warp >= kIgemmEpiWarp0) {
     // ============================== epilogue of this CTA's 128 rows ===========
+#ifdef GHOST_IGEMM_PROF
+    const long long gd0_ = clock64();
+#endif
     grid_dep_wait();
+#ifdef GHOST_IGEMM_PROF
+    if (blockIdx.x == 0 && blockIdx.y == 0 && warp == kIgemmEpiWarp0 && lane == 0) g_tl_cta0[4] = g_tl_cta0[0] + (clock64() - gd0_);
+#endif
     LinEpi<F16, STATS> epi;
-    epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
+    epi.init(p, warp, lane, ring, CHAIN ? eparm2 : eparm, staged, rows_used, tmem_base, acc_stride);
     int it = 0;
-    for (int s = cluster; s < super_total; s += nclusters, ++it) {
-      const TileCoord t = my_tile(s);
-      const int as = p.sets == 4 ? (it & 3) : (it & 1);
-      const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
-      const bool use_stg = p.stg && s + nclusters >= super_total;
-      if (!epi.template tile<true>(p, t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) break;
+    for (int step = 0; step < nsteps; ++step) {
+      const IgemmParams& q = CHAIN ? sp[step & 1] : p;
+      if (CHAIN) epi.eparm = eparm2 + (step & 1) * 1024;
+      bool ok = true;
+      for (int g = cluster; ok && g < ngroups; g += nclusters) {
+        for (int u = 0; u < spg; ++u, ++it) {
+          const TileCoord t = my_tile(g * spg + u);
+          const int as = p.sets == 4 ? (it & 3) : (it & 1);
+          const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
+          const bool use_stg = p.stg && g + nclusters >= ngroups && u + 1 == spg;
+          if (!epi.template tile<true>(q, t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) {
+            ok = false;
+            break;
+          }
+        }
+      }
+      if (CHAIN && step + 1 < nsteps) {
+        // this thread's plain stores -> visible to the TMA loads of the next conv, in either CTA of the pair
+        fence_proxy_async_all();
+        __threadfence();
+        cluster_sync_all();
+      }
     }
     if (!abort_flag) epi.st_finish(p);
+#ifdef GHOST_IGEMM_PROF
+    if (warp == kIgemmEpiWarp0 && lane == 0 && blockIdx.x == 0 && blockIdx.y == 0) g_tl_cta0[3] = clock64();
+#endif
   }
 
   // ------------------------------ teardown ------------------------------------
@@ -1594,6 +1696,33 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     *reinterpret_cast<volatile int*>(p.err) = 1;
     __threadfence_system();
   }
+#ifdef GHOST_IGEMM_PROF
+  if (threadIdx.x == 0) {
+    unsigned long long ns1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+    atomicMax(&g_tl_t1[tl_seq], ns1);
+    if (blockIdx.x == 0 && blockIdx.y == 0) {
+      g_tl_meta[tl_seq][0] = 2000 + p.BN;  // "mode 2" = CTA pair
+      g_tl_meta[tl_seq][1] = p.tiles_w * p.tiles_h * p.tiles_nb * p.tiles_n;
+      g_tl_meta[tl_seq][2] = num_kb;
+      g_tl_meta[tl_seq][3] = gridDim.x * 10 + p.a_win;
+      g_tl_meta[tl_seq][4] = static_cast<int>(g_tl_cta0[1] - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][5] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[2]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][6] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[3]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][7] = static_cast<int>(clock64() - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][8] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[4]) - g_tl_cta0[0]);  // griddepcontrol.wait
+      g_tl_meta[tl_seq][9] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[5]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][10] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[6]) - g_tl_cta0[0]);
+      g_tl_meta[tl_seq][11] = static_cast<int>(*reinterpret_cast<volatile long long*>(&g_tl_cta0[7]) - g_tl_cta0[0]);
+    }
+    __threadfence();
+    if (atomicAdd(&g_tl_done, 1u) == gridDim.x * gridDim.y - 1) {
+      g_tl_done = 0;
+      __threadfence();
+      atomicAdd(&g_tl_seq, 1u);
+    }
+  }
+#endif
   cluster_sync_all();  // neither CTA leaves while the other may still signal its barriers / read its operands
   if (warp == 2) {
     tc_fence_after();
@@ -1659,7 +1788,7 @@ int igemm_smem_bytes(const IgemmParams& p) {
   if (p.cta2) {
     const int b_half = (p.BN >> 1) * 128;
     const int stage2 = p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half);
-    return p.stages * stage2 + (p.b_res ? p.ntaps * p.kc_per_tap * b_half : 0) + 1024 + st;
+    return p.stages * stage2 + (p.b_res ? p.ntaps * p.kc_per_tap * b_half : 0) + 1024 + st + (p.chain_n ? kChainSmemBytes : 0);
   }
   const int row_bytes = p.kc * 2;
   const int aad = p.mode == kModeAAD ? p.h_bufs * ((p.BN >> 1) >> 6) * 16384 : 0;
@@ -1701,12 +1830,14 @@ const char* igemm_dev_state(IgemmDevState* out) {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim);
     if (e == cudaSuccess) {
       cudaFuncAttributes fa2;
-      e = cudaFuncGetAttributes(&fa2, igemm2_kernel<false, false>);
+      e = cudaFuncGetAttributes(&fa2, igemm2_kernel<false, false, false>);
       const int lim2 = 227 * 1024 - static_cast<int>(fa2.sharedSizeBytes);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
-      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(igemm2_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim2);
       st.max_dyn_smem2 = lim2;
     }
     int sms = 0;
@@ -1750,6 +1881,13 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   if (supers <= 0) return "igemm2: empty grid";
   int clusters = num_sms / 2;
   if (clusters > supers) clusters = supers;
+  if (p.chain_n) {
+    if (p.chain_n < 2 || !p.chain || p.chain_spg < 1 || supers % p.chain_spg || (tiles_m & 1) || p.st_mode || p.tst || p.b_res ||
+        p.nphase > 1)
+      return "igemm2: a conv chain needs whole groups of super tiles and the plain linear epilogue";
+    clusters = num_sms / 2;
+    if (clusters > supers / p.chain_spg) clusters = supers / p.chain_spg;
+  }
   static const int pdl = [] {
     const char* ev = getenv("GHOST_PDL");
     return ev ? (atoi(ev) != 0) : 1;
@@ -1769,10 +1907,15 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 2 : 1;
   cudaError_t e;
-  if (p.st_mode)
-    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, true>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, true>, p);
+  if (p.chain_n)
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, false, true>, p)
+              : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, false, true>, p);
+  else if (p.st_mode)
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, true, false>, p)
+              : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, true, false>, p);
   else
-    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, false>, p) : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, false>, p);
+    e = p.f16 ? cudaLaunchKernelEx(&cfg, igemm2_kernel<true, false, false>, p)
+              : cudaLaunchKernelEx(&cfg, igemm2_kernel<false, false, false>, p);
   if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? nullptr : cudaGetErrorString(e);
 }

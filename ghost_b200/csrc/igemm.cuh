@@ -145,6 +145,17 @@ struct alignas(64) IgemmParams {
 
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
+  // Conv chain (CTA-pair kernel only): `chain_n` convs of IDENTICAL geometry (tiling, N tile, taps, ring) that feed
+  // one another run as ONE launch.  A 3x3 conv only reads pixels of its own image, so when every cluster owns whole
+  // images - `chain_spg` consecutive super tiles (pairs of M tiles x N tiles) form one group of images, cluster c works
+  // on groups c, c + clusters, ... in every step - step k+1 of a group depends on step k of the SAME cluster only: a
+  // cluster barrier (plus the generic -> async proxy fence for the TMA loads that follow plain stores) replaces the
+  // kernel boundary, and with it the launch gap, the prologue and the teardown (~4 us of every ~20 us iresnet conv).
+  // `chain` points at the device copies of all steps' parameter blocks (tensor maps are read from there); the block
+  // passed to the launch is step 0's.  0 = off.
+  const IgemmParams* chain;
+  int chain_n, chain_spg;
+
   int* err;  // device word set non-zero when a pipeline wait timed out
 };
 
@@ -153,5 +164,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream);
 // second pass of a split-K op: `p` is the op's parameter block (real output, epilogue, ws, splits)
 const char* splitk_reduce_launch(const IgemmParams& p, cudaStream_t stream);
 int igemm_smem_bytes(const IgemmParams& p);
+// bytes behind the operand ring of a chain launch: two parameter blocks + two epilogue parameter tables
+constexpr int kChainSmemBytes = 2 * static_cast<int>(sizeof(IgemmParams)) + 2 * 4096;
 
 }  // namespace ghost

@@ -52,3 +52,25 @@ def test_embed_hwc_matches_oracle(sd, is_u8):
     net = net.eval().cuda()
     z = net.embed_hwc(torch.from_numpy(src).cuda()).cpu()
     assert (z - ref).abs().max().item() <= 2e-4 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("batch", [5, 64])
+def test_conv_chain_is_bit_identical_to_separate_launches(batch, tmp_path):
+    """The 58 identical 3x3 convs of layer 3 and the 24 of layer 2 run as ONE chain launch each (igemm.cuh `chain`:
+    every cluster keeps whole images, a cluster barrier stands where the kernel boundary was).  Same tiles, same
+    summation order: the embedding must be bit-identical to the separate launches (GHOST_CHAIN=0), for an odd batch
+    (odd tile counts, a padded tile per image in layer 2) and at the benchmarked batch."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for chain in ("0", "1"):
+        out = str(tmp_path / ("z%s.npy" % chain))
+        env = dict(os.environ, GHOST_CHAIN=chain)
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "arc_chain_ab.py"), out, str(batch)], env=env,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        outs.append(np.load(out))
+    assert np.isfinite(outs[1]).all()
+    assert np.array_equal(outs[0], outs[1])

@@ -47,17 +47,17 @@ def timeline(label, fn):
     print("   idx  mode  BN  tiles  num_kb  grid win   dur_us  gap_after_us | CTA 0 cycles: prologue, issuer done, epilogue done, exit; last tile: accumulator ready, staged")
     for i in range(n):
         m = meta[i]
-        print("   %3d  %4d %3d %6d %6d %5d %3d %8.2f %8.2f | %6d %7d %7d %7d ; %7d %7d" % (
+        print("   %3d  %4d %3d %6d %6d %5d %3d %8.2f %8.2f | %6d %7d %7d %7d ; %7d %7d %7d %7d" % (
             i, m[0] // 1000, m[0] % 1000, m[1], m[2], m[3] // 10, m[3] % 10, dur[i], gap[i], m[4], m[5], m[6], m[7], m[8],
-            m[9]))
+            m[9], m[10], m[11]))
 
 
-arc = gb.iresnet100().cuda().bfloat16().eval()
+arc = gb.iresnet100().cuda().half().eval()
 arc.enable_graph(True)
 x = torch.randn(B, 3, 112, 112, device="cuda")
 timeline("iresnet100 B=%d" % B, lambda: arc(x))
 
-G = gb.AEI_Net("unet", num_blocks=2, c_id=512).cuda().bfloat16().eval()
+G = gb.AEI_Net("unet", num_blocks=2, c_id=512).cuda().half().eval()
 G.enable_graph(True)
 Xt = torch.randn(B, 3, 256, 256, device="cuda")
 z = torch.nn.functional.normalize(torch.randn(B, 512, device="cuda"))
