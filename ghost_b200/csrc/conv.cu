@@ -498,6 +498,34 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     }();
     p.stg = stg_mode;
   }
+  // ... and through the TMA unit instead of the load/store path when the views are plain NHWC tensors (igemm.cuh tte)
+  if (p.stg && !stats && !phases && epi.act2 == kAct2None && w.Cout % 64 == 0 && out.off >= 0 && out.off < out.sw &&
+      out.sh == static_cast<long long>(Wo) * out.sw && out.sn == static_cast<long long>(Ho) * Wo * out.sw &&
+      (!epi.res || (epi.r_off >= 0 && epi.r_off < epi.r_sw && epi.r_sh == static_cast<long long>(Wo) * epi.r_sw &&
+                    epi.r_sn == static_cast<long long>(Ho) * Wo * epi.r_sw)) &&
+      (epi.out2 ? 2 : 1) * 256 * p.BN <= stages * stage_bytes) {
+    static const int tte_mode = [] {
+      const char* e = getenv("GHOST_TTE");  // A/B switch for profiling
+      return e ? atoi(e) : 1;
+    }();
+    if (tte_mode) {
+      const uint32_t box[4] = {64u, static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
+      auto nhwc_map = [&](CUtensorMap* m, const void* base, long long ct_) {
+        const uint64_t ct = static_cast<uint64_t>(ct_);
+        const uint64_t dims[4] = {ct, static_cast<uint64_t>(Wo), static_cast<uint64_t>(Ho), static_cast<uint64_t>(in.N)};
+        const uint64_t str[3] = {ct * 2, static_cast<uint64_t>(Wo) * ct * 2, static_cast<uint64_t>(Ho) * Wo * ct * 2};
+        return encode_tmap(m, base, 4, dims, str, box, 128);
+      };
+      if (const char* e = nhwc_map(&p.tmO, out.p, out.sw)) return e;
+      if (epi.out2)
+        if (const char* e = nhwc_map(&p.tmO2, epi.out2, out.sw)) return e;
+      if (epi.res)
+        if (const char* e = nhwc_map(&p.tmH, epi.res, epi.r_sw)) return e;
+      p.tte = 1;
+      p.tst_c0 = static_cast<int>(out.off);
+      p.tte_r0 = static_cast<int>(epi.r_off);
+    }
+  }
 
   // ---- epilogue
   p.out = out.p;
@@ -612,6 +640,7 @@ bool chain_compatible(const LaunchOp& first, const LaunchOp& next) {
       a.tiles_h != b.tiles_h || a.tiles_nb != b.tiles_nb || a.tiles_n != b.tiles_n || a.Nimg != b.Nimg || a.Ho != b.Ho ||
       a.Wo != b.Wo || a.BN != b.BN || a.n_valid != b.n_valid || a.ntaps != b.ntaps || a.kc_per_tap != b.kc_per_tap ||
       a.stages != b.stages || a.tmem_cols != b.tmem_cols || a.sets != b.sets || a.stg != b.stg || a.f16 != b.f16 ||
+      a.tte != b.tte ||
       a.err != b.err)
     return false;
   for (int t = 0; t < a.ntaps; ++t)
@@ -649,7 +678,9 @@ const char* make_chain(LaunchOp* out, const std::vector<LaunchOp>& steps, void* 
     probe.stages = stages;
     if (igemm_smem_bytes(probe) > budget) return nullptr;
     const int stage_bytes = 128 * 128 + (g.BN >> 1) * 128;
-    if (g.stg && 256 * g.BN > stages * stage_bytes) return nullptr;
+    bool two = false;
+    for (const LaunchOp& st : steps) two = two || st.ig.out2 != nullptr;
+    if (g.stg && (g.tte && two ? 2 : 1) * 256 * g.BN > stages * stage_bytes) return nullptr;
   }
   std::vector<IgemmParams> host(steps.size());
   for (size_t i = 0; i < steps.size(); ++i) {

@@ -335,9 +335,16 @@ struct LinEpi {
   float* st_x;  // shared exchange [4 ew][4 lg][4 chunks][32 lanes]
   uint8_t* tst_buf;  // TMA-store epilogue: [2 buffers][4 lane groups][BN/64 boxes][32 rows][128 B]
   int tst_it;        // tiles this warp has sent through the staging buffers
+  uint8_t* ring0;    // whole-tile TMA epilogue (tte): staging = the idle operand ring
+  uint64_t* rbar;    // tte: [4] one barrier per 64-column group for the residual box
+  uint32_t rphase;
 
   __device__ __forceinline__ void init(const IgemmParams& p, int warp, int lane_, uint8_t* ring, const float* eparm_,
-                                       bool staged_, int rows_used_, uint32_t tmem_base, int acc_stride_) {
+                                       bool staged_, int rows_used_, uint32_t tmem_base, int acc_stride_,
+                                       uint64_t* rbar_) {
+    ring0 = ring;
+    rbar = rbar_;
+    rphase = 0;
     lane = lane_;
     lg = warp & 3;                        // TMEM lane group this warp may read
     ew = (warp - kIgemmEpiWarp0) >> 2;    // 0..3: which of the four warps of that lane group
@@ -428,6 +435,11 @@ struct LinEpi {
   __device__ __forceinline__ void st_finish(const IgemmParams& p) {
     if (STATS && p.st_mode == 2 && st_img >= 0) st_flush(p, blockIdx.x);
     if (p.tst && ew == 0 && lane == 0) bulk_wait<0>();  // outstanding TMA stores
+    tte_drain(p);
+  }
+  // whole-tile TMA epilogue: the lanes that issued stores wait until they are complete (and the staging is free)
+  __device__ __forceinline__ void tte_drain(const IgemmParams& p) {
+    if (p.tte && lg == 0 && lane == 0) bulk_wait<0>();
   }
   __device__ __forceinline__ int stg_key(int row) const { return ((row * rowb) >> 7) & (P - 1); }
 
@@ -441,9 +453,11 @@ struct LinEpi {
   }
 
   // returns false when the pipeline was aborted (the caller leaves its tile loop)
+  // gp: where the tensor maps of this launch / chain step live (kernel parameter or global memory, never shared)
   template <bool REMOTE>
-  __device__ __forceinline__ bool tile(const IgemmParams& p, const TileCoord& t, int as, uint32_t aphase, bool use_stg,
-                                       uint64_t* tfull, uint64_t* tempty, volatile int* abort_flag) {
+  __device__ __forceinline__ bool tile(const IgemmParams& p, const IgemmParams* gp, const TileCoord& t, int as,
+                                       uint32_t aphase, bool use_stg, uint64_t* tfull, uint64_t* tempty,
+                                       volatile int* abort_flag) {
         if (STATS) {  // bn == 1: the tile lies in image t.tn
           if (p.st_mode == 2 && st_img >= 0 && st_img != t.tn) st_flush(p, blockIdx.x);
           st_img = t.tn;
@@ -506,12 +520,120 @@ struct LinEpi {
           if (ew == 0 && lane == 0) {
             if (r < rows_used && n < p.Nimg && oh < p.Ho && ow < p.Wo) {
               for (int b = 0; b < hb; ++b)
-                tma_store_4d(&p.tmO, piece + b * 4096, p.tst_c0 + t.nt * p.BN + b * 64, ow, oh, n);
+                tma_store_4d(&gp->tmO, piece + b * 4096, p.tst_c0 + t.nt * p.BN + b * 64, ow, oh, n);
             }
             bulk_commit();
           }
           ++tst_it;
           return true;
+        }
+        if (use_stg && p.tte) {
+          // Whole-tile TMA epilogue of the last tile: the residual box of every 64-column group arrives by TMA in the
+          // (idle) operand ring, laid out as the store box [rows][128 B, 128B swizzle]; every lane adds its row in place
+          // and the group leaves through ONE TMA store (a second one for out2) - nothing goes through the LSU path
+          // (measured on a 14x14x256 iresnet conv: residual rows 3800 cycles, out + out2 stores 6000 cycles of a 12600
+          // cycle epilogue that no main loop hides).
+          PROF_STAMP(5);  // accumulator complete
+          const int g = (ew * wcols) >> 6, cg = (ew * wcols) & 63;  // 64-column group of this warp, first column in it
+          const int ngrp = p.BN >> 6;
+          uint8_t* Rg = ring0 + g * 16384;
+          uint8_t* R2g = Rg + ngrp * 16384;
+          const int w0 = t.tw * p.bw, h0 = t.th * p.bh, n0 = t.tn * p.bn;
+          const bool leader = lg == 0 && cg == 0 && lane == 0;
+          const bool gcols_on = t.nt * p.BN + g * 64 < p.n_valid;  // (n_valid is a multiple of 64 here)
+          if (p.res != nullptr && leader && gcols_on) {
+            mbar_expect_tx(&rbar[g], static_cast<uint32_t>(rows_used) * 128u);
+            tma_load_4d(Rg, &gp->tmH, &rbar[g], p.tte_r0 + t.nt * p.BN + g * 64, w0, h0, n0);
+          }
+          uint8_t* my_row = Rg + r * 128;
+          const int key = r & 7;
+          bool tte_ok = true;
+          // (not unrolled: this code runs once per launch, straight from a cold instruction cache - a quarter of the
+          // instructions to fetch; pipelining the TMEM loads over two register buffers measured no gain)
+          const int nchunk = wcols >> 4;
+#pragma unroll 1
+          for (int c = 0; c < nchunk; ++c) {
+            {
+              const int j = ew * wcols + c * 16;
+              uint32_t v[16];
+              __syncwarp();
+              tmem_ld16(t_addr + j, v);
+              tmem_ld_wait();
+              if (c == 0 && p.res != nullptr && gcols_on) {
+                if (!__all_sync(0xffffffffu, mbar_wait(&rbar[g], rphase, abort_flag))) tte_ok = false;  // (aborting)
+                PROF_STAMP(6);  // residual box landed
+              }
+              if (valid && gcols_on) {
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
+                const int ch = (cg >> 3) + 2 * c;  // 16-byte chunk inside the 128-byte row
+                uint4* s0 = reinterpret_cast<uint4*>(my_row + ((ch ^ key) << 4));
+                uint4* s1 = reinterpret_cast<uint4*>(my_row + (((ch + 1) ^ key) << 4));
+                if (p.res) {
+                  const uint4 q0 = *s0, q1 = *s1;
+                  const uint32_t qq[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    f[2 * i] += lo16<F16>(qq[i]);
+                    f[2 * i + 1] += hi16<F16>(qq[i]);
+                  }
+                }
+                uint4 o0, o1;
+                o0.x = pack16<F16>(f[0], f[1]);
+                o0.y = pack16<F16>(f[2], f[3]);
+                o0.z = pack16<F16>(f[4], f[5]);
+                o0.w = pack16<F16>(f[6], f[7]);
+                o1.x = pack16<F16>(f[8], f[9]);
+                o1.y = pack16<F16>(f[10], f[11]);
+                o1.z = pack16<F16>(f[12], f[13]);
+                o1.w = pack16<F16>(f[14], f[15]);
+                *s0 = o0;
+                *s1 = o1;
+                if (p.out2) {
+                  // second output from the value as stored (rounded to 16 bits), e.g. the next block's bn1
+                  const uint32_t ow_[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+                  float t2[16];
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const float4 sc = staged ? *reinterpret_cast<const float4*>(eparm + 512 + j + 4 * i)
+                                             : __ldg(reinterpret_cast<const float4*>(p.scale2 + t.nt * p.BN + j) + i);
+                    const float4 sh = staged ? *reinterpret_cast<const float4*>(eparm + 768 + j + 4 * i)
+                                             : __ldg(reinterpret_cast<const float4*>(p.shift2 + t.nt * p.BN + j) + i);
+                    t2[4 * i] = fmaf(lo16<F16>(ow_[2 * i]), sc.x, sh.x);
+                    t2[4 * i + 1] = fmaf(hi16<F16>(ow_[2 * i]), sc.y, sh.y);
+                    t2[4 * i + 2] = fmaf(lo16<F16>(ow_[2 * i + 1]), sc.z, sh.z);
+                    t2[4 * i + 3] = fmaf(hi16<F16>(ow_[2 * i + 1]), sc.w, sh.w);
+                  }
+                  uint4 u0, u1;
+                  u0.x = pack16<F16>(t2[0], t2[1]);
+                  u0.y = pack16<F16>(t2[2], t2[3]);
+                  u0.z = pack16<F16>(t2[4], t2[5]);
+                  u0.w = pack16<F16>(t2[6], t2[7]);
+                  u1.x = pack16<F16>(t2[8], t2[9]);
+                  u1.y = pack16<F16>(t2[10], t2[11]);
+                  u1.z = pack16<F16>(t2[12], t2[13]);
+                  u1.w = pack16<F16>(t2[14], t2[15]);
+                  *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(s0) + ngrp * 16384) = u0;
+                  *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(s1) + ngrp * 16384) = u1;
+                }
+              }
+            }
+          }
+          if (p.res != nullptr && gcols_on) rphase ^= 1u;
+          tc_fence_before();
+          fence_proxy_async();  // the staged rows -> visible to the TMA store
+          __syncwarp();
+          PROF_STAMP(7);  // tile converted into the staging rows
+          release<REMOTE>(tempty);
+          named_bar_sync(1 + g, (256 / wcols) * 32);  // the warps of this 64-column group
+          if (leader && gcols_on) {
+            tma_store_4d(&gp->tmO, Rg, p.tst_c0 + t.nt * p.BN + g * 64, w0, h0, n0);
+            if (p.out2) tma_store_4d(&gp->tmO2, R2g, p.tst_c0 + t.nt * p.BN + g * 64, w0, h0, n0);
+            bulk_commit();
+          }
+          return tte_ok;
         }
         if (use_stg) {
           PROF_STAMP(5);  // accumulator complete
@@ -534,7 +656,8 @@ struct LinEpi {
           PROF_STAMP(6);  // residual rows staged
           uint8_t* my_row = wst + lane * rowb;
           const int my_key = stg_key(lane);
-#pragma unroll
+          // (unrolled only where the statistics index registers by c: the last-tile code runs from a cold instruction cache)
+#pragma unroll(STATS ? 4 : 1)
           for (int c = 0; c < 4; ++c) {
             if (c * 16 < wcols) {  // warp-uniform
               const int j = ew * wcols + c * 16;
@@ -630,7 +753,7 @@ struct LinEpi {
           }
           return true;
         }
-#pragma unroll
+#pragma unroll(STATS ? 4 : 1)
         for (int c = 0; c < 4; ++c) {
           if (ch0 + c < ch1) {  // warp-uniform
             const int j = (ch0 + c) * 16;
@@ -1013,7 +1136,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
     if (p.mode == kModeLinear) {
       // all 16 warps share every tile: warp ew takes a quarter of its columns
       LinEpi<F16, STATS> epi;
-      epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride);
+      epi.init(p, warp, lane, ring, eparm, staged, rows_used, tmem_base, acc_stride, hfull_bar);  // (free in linear mode)
       int it = 0;
       TileWalk walk;
       walk.init(p, blockIdx.x, gridDim.x);
@@ -1021,7 +1144,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm_kernel(const __grid_co
         const bool use_stg = p.stg && tile + static_cast<int>(gridDim.x) >= tiles_total;
         const int as = p.sets == 4 ? (it & 3) : (it & 1);
         const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
-        if (!epi.template tile<false>(p, walk.t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag))
+        if (!epi.template tile<false>(p, &p, walk.t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag))
           break;
       }
       if (!abort_flag) epi.st_finish(p);
@@ -1365,6 +1488,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   __shared__ uint64_t tfull_bar[4];
   __shared__ uint64_t tempty_bar[4];
   __shared__ uint64_t bfull_bar;  // resident-weights mode (leader): both CTAs' halves of the weight slab landed
+  __shared__ uint64_t rbar[4];    // whole-tile TMA epilogue: residual box of each 64-column group
   __shared__ __align__(16) float eparm[1024];
   __shared__ uint32_t tmem_base_smem;
   __shared__ int abort_flag;
@@ -1414,6 +1538,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     else if (lane < 20) mbar_init(&tfull_bar[lane - 16], 1);
     else if (lane < 24) mbar_init(&tempty_bar[lane - 20], 2 * kIgemmEpiWarps);
     else if (lane == 24) mbar_init(&bfull_bar, 1);
+    else if (lane < 29) mbar_init(&rbar[lane - 25], 1);
     fence_mbar_init();
   }
   if (warp == 0 && lane == 0) {
@@ -1658,10 +1783,11 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     if (blockIdx.x == 0 && blockIdx.y == 0 && warp == kIgemmEpiWarp0 && lane == 0) g_tl_cta0[4] = g_tl_cta0[0] + (clock64() - gd0_);
 #endif
     LinEpi<F16, STATS> epi;
-    epi.init(p, warp, lane, ring, CHAIN ? eparm2 : eparm, staged, rows_used, tmem_base, acc_stride);
+    epi.init(p, warp, lane, ring, CHAIN ? eparm2 : eparm, staged, rows_used, tmem_base, acc_stride, rbar);
     int it = 0;
     for (int step = 0; step < nsteps; ++step) {
       const IgemmParams& q = CHAIN ? sp[step & 1] : p;
+      const IgemmParams* gq = CHAIN ? p.chain + step : &p;  // tensor maps: never from shared memory
       if (CHAIN) epi.eparm = eparm2 + (step & 1) * 1024;
       bool ok = true;
       for (int g = cluster; ok && g < ngroups; g += nclusters) {
@@ -1670,7 +1796,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
           const int as = p.sets == 4 ? (it & 3) : (it & 1);
           const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
           const bool use_stg = p.stg && g + nclusters >= ngroups && u + 1 == spg;
-          if (!epi.template tile<true>(q, t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) {
+          if (!epi.template tile<true>(q, gq, t, as, aph, use_stg, &tfull_bar[as], &tempty_bar[as], &abort_flag)) {
             ok = false;
             break;
           }
@@ -1678,6 +1804,7 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
       }
       if (CHAIN && step + 1 < nsteps) {
         // this thread's plain stores -> visible to the TMA loads of the next conv, in either CTA of the pair
+        epi.tte_drain(q);
         fence_proxy_async_all();
         __threadfence();
         cluster_sync_all();

@@ -142,6 +142,13 @@ struct alignas(64) IgemmParams {
   // 16-bit output with regular NHWC strides.
   int tst;
   int tst_c0;  // first output channel (view offset) inside the tensor tmO describes
+  // Whole-tile TMA epilogue of the staged last tile (tte = 1, with stg): tmH / tmO / tmO2 describe the residual, the
+  // output and the second output as NHWC tensors with boxes of 64 channels x (bw, bh, bn) pixels (128B swizzle); the
+  // residual box lands in the idle operand ring, every lane adds its row in place, one TMA store per 64-column group
+  // (and output) sends the tile out.  tst_c0 / tte_r0: channel offsets of the output / residual views.
+  int tte;
+  int tte_r0;
+  CUtensorMap tmO2;
 
   int f16;   // 16-bit storage type of activations / weights / outputs: 0 = bf16, 1 = IEEE fp16 (same MMA rate)
 
