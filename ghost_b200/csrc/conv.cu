@@ -218,6 +218,48 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     p.bh = 1;
     p.bn = 1;
   }
+  // Tile-window mode (igemm.cuh a_win = 2): the same conv over a NARROW image on the CTA-pair kernel.  A tile = bh whole
+  // image rows; its (bh + 2) x (Wo + 2) pixel patch crosses L2 -> shared once per 64-channel chunk instead of nine
+  // times, the weights stay resident (half of the slab per CTA).  The tap-shifted loads of the plain kernel make these
+  // layers L2-bound (measured 0.26 us per K block of a 128-wide pair tile against 0.135 us of MMA time): iresnet
+  // layers 1-2 (56 x 56 x 64, 28 x 28 x 128).
+  static const int win2_mode = [] {
+    const char* e = getenv("GHOST_AWIN2");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  static const int cta2_env = [] {
+    const char* e = getenv("GHOST_CTA2");
+    return e ? atoi(e) : 1;
+  }();
+  bool win2 = false;
+  int w2_slot = 0, w2_slab = 0;
+  if (!win && win2_mode && cta2_env && !aad && !phases && !epi.want_stats && !force_simt && taps.n == 9 && taps.stride == 1 &&
+      p.kc == 64 && Wo == in.W && Ho == in.H && Wo + 2 <= 64 && w.Cout <= 128 && w.Cout % 32 == 0 && (bn_hint >> 10) != 2 &&
+      ((bn_hint & 1023) == 0 || (bn_hint & 1023) == w.Cout) && is16(out.dtype)) {
+    bool taps_ok = true;
+    for (int i = 0; taps_ok && i < 9; ++i) taps_ok = taps.dh[i] == i / 3 - 1 && taps.dw[i] == i % 3 - 1;
+    const int pitch = Wo + 2;
+    int hmax = 128 / pitch;
+    if (hmax > Ho) hmax = Ho;
+    if (taps_ok && hmax >= 1) {
+      const int tiles_h = (Ho + hmax - 1) / hmax;
+      const int bh = (Ho + tiles_h - 1) / tiles_h;  // the smallest tile height with that many tiles per image
+      const long long tiles_m = static_cast<long long>(tiles_h) * in.N;
+      const double eff = static_cast<double>(Ho) * Wo / (tiles_h * 128.0);
+      int slot = (2 * pitch + 2 + 128) * 128;  // rows the farthest tap view reads (past the patch: junk rows only)
+      if (slot < (bh + 2) * pitch * 128) slot = (bh + 2) * pitch * 128;
+      slot = (slot + 1023) / 1024 * 1024;
+      const int slab = 9 * (Cin / 64) * (w.Cout / 2) * 128;
+      if (tiles_m >= 2 && eff >= 0.7 && slab + 2 * slot + 1024 <= 221 * 1024) {
+        win2 = true;
+        w2_slot = slot;
+        w2_slab = slab;
+        p.bw = Wo;
+        p.bh = bh;
+        p.bn = 1;
+      }
+    }
+  }
   p.tiles_w = (Wo + p.bw - 1) / p.bw;
   p.tiles_h = (Ho + p.bh - 1) / p.bh;
   p.tiles_nb = (in.N + p.bn - 1) / p.bn;
@@ -235,8 +277,8 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
                               static_cast<uint64_t>(in.N)};
     const uint64_t str[3] = {in.C * eb, static_cast<uint64_t>(in.W) * in.C * eb,
                              static_cast<uint64_t>(in.H) * in.W * in.C * eb};
-    const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(win ? p.bw + 2 : p.bw),
-                             static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
+    const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(win || win2 ? p.bw + 2 : p.bw),
+                             static_cast<uint32_t>(win2 ? p.bh + 2 : p.bh), static_cast<uint32_t>(p.bn)};
     if (const char* e = encode_tmap(&p.tmA, in.p, 4, dims, str, box, swz)) return e;
     for (int i = 0; i < taps.n; ++i) {
       p.tap_c[i] = 0;
@@ -374,6 +416,11 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     if (win && !p.cta2 && cta2_mode != 0 && cta2win_mode != 0 && force2 != 2 && tiles_m2 >= 2 && bn_ % 16 == 0 && bn_ >= 32 &&
         (p.kc_per_tap >= 2 || force2 == 1))
       p.cta2 = 1;
+    if (win2) {  // one N tile on the pair kernel, whatever the cost model of the plain kernels says
+      p.cta2 = 1;
+      p.splits = 1;
+      bn_ = w.Cout;
+    }
     p.BN = bn_;
     p.tiles_n = nph * ((cout_t + p.BN - 1) / p.BN);
     p.n_valid = nph * cout_t;
@@ -408,7 +455,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const char* e = getenv("GHOST_TST");  // A/B switch for profiling
     return e ? atoi(e) : 1;
   }();
-  bool tst = tst_mode && !aad && !stats && !phases && (!p.cta2 || win) && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
+  bool tst = tst_mode && !aad && !stats && !phases && !win2 && (!p.cta2 || win) && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
                    (p.BN == 64 || (p.BN == 128 && !win)) && w.Cout % 64 == 0 && p.bw % 32 == 0 && p.bh * p.bw * p.bn == 128 &&
                    taps.n * p.kc_per_tap <= 18 && out.sw % 8 == 0 && out.off % 8 == 0 &&
                    out.sh == static_cast<long long>(Wo) * out.sw && out.sn == static_cast<long long>(Ho) * Wo * out.sw &&
@@ -428,6 +475,13 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     stage_bytes = 17 * 1024 + (p.b_res ? 0 : 3 * b_tile);
     resident_bytes = p.b_res ? slab : 0;
     if ((221 * 1024 - st_bytes - resident_bytes) / stage_bytes < 2) return "lower_conv: row-window stage does not fit (N tile too wide)";
+  }
+  if (win2) {
+    p.a_win = 2;
+    p.a_slot = w2_slot;
+    p.b_res = 1;
+    stage_bytes = w2_slot;
+    resident_bytes = w2_slab;
   }
   p.sets = 2;
   int aad_bytes = 0;
@@ -488,7 +542,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const uint32_t ob[4] = {64u, 32u, 1u, 1u};
     if (const char* e = encode_tmap(&p.tmO, out.p, 4, dims, str, ob, 128)) return e;
   }
-  if (!tst && !aad && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
+  if (!tst && !aad && !win2 && p.splits == 1 && is16(out.dtype) && (p.BN == 128 || p.BN == 256) && w.Cout % (p.BN >> 2) == 0 && !(out.off % 8) &&
       !(out.sw % 8) && !(out.sh % 8) && !(out.sn % 8) &&
       (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8))) &&
       256 * p.BN <= stages * stage_bytes) {

@@ -320,7 +320,7 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
 // memory - 4-8 cache lines per instruction instead of 32.
 template <bool F16, bool STATS>
 struct LinEpi {
-  int lane, lg, ew, r, rn, rh, rw, rows_used;
+  int lane, lg, ew, r, rn, rh, rw, rows_used, box_rows;
   int wcols, rowb, P, lgP, rb_row0, rb_piece, rb_step;
   uint8_t* wst;
   const float* eparm;
@@ -349,10 +349,12 @@ struct LinEpi {
     lg = warp & 3;                        // TMEM lane group this warp may read
     ew = (warp - kIgemmEpiWarp0) >> 2;    // 0..3: which of the four warps of that lane group
     r = lg * 32 + lane;                   // GEMM row inside the tile
-    rn = r / (p.bh * p.bw);
-    rh = (r / p.bw) % p.bh;
-    rw = r % p.bw;
-    rows_used = rows_used_;
+    const int pitch = p.a_win == 2 ? p.bw + 2 : p.bw;  // tile-window mode: rows of bw + 2 GEMM rows, the last two junk
+    rn = r / (p.bh * pitch);
+    rh = (r / pitch) % p.bh;
+    rw = r % pitch;
+    rows_used = (rw < p.bw) ? rows_used_ : 0;  // (a junk row is never valid)
+    box_rows = rows_used_;
     wcols = p.BN >> 2, rowb = wcols * 2, P = rowb >> 4, lgP = 31 - __clz(P);
     wst = ring + (warp - kIgemmEpiWarp0) * (32 * rowb);
     rb_row0 = lane >> lgP, rb_piece = lane & (P - 1), rb_step = 32 >> lgP;
@@ -370,6 +372,7 @@ struct LinEpi {
   __device__ __forceinline__ static int st_stage_bytes(const IgemmParams& p) {
     if (p.cta2) {
       const int b_half = (p.BN >> 1) * 128;
+      if (p.a_win == 2) return p.a_slot;
       return p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half);
     }
     const int b_tile = p.BN * p.kc * 2;
@@ -542,7 +545,7 @@ struct LinEpi {
           const bool leader = lg == 0 && cg == 0 && lane == 0;
           const bool gcols_on = t.nt * p.BN + g * 64 < p.n_valid;  // (n_valid is a multiple of 64 here)
           if (p.res != nullptr && leader && gcols_on) {
-            mbar_expect_tx(&rbar[g], static_cast<uint32_t>(rows_used) * 128u);
+            mbar_expect_tx(&rbar[g], static_cast<uint32_t>(box_rows) * 128u);
             tma_load_4d(Rg, &gp->tmH, &rbar[g], p.tte_r0 + t.nt * p.BN + g * 64, w0, h0, n0);
           }
           uint8_t* my_row = Rg + r * 128;
@@ -1511,16 +1514,21 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   // resident for the whole kernel (b_res) or streamed three taps at a time.
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  const bool win = p.a_win != 0;
+  // Tile-window mode (a_win = 2, narrow images): the A slot holds the (bh + 2) x (bw + 2) pixel patch around a tile of
+  // bh whole image rows, loaded ONCE per 64-channel chunk; all nine taps are views of it shifted by dy * (bw + 2) + dx
+  // pixel rows, so GEMM row m is pixel (m / (bw + 2), m % (bw + 2)) of the tile and the rows with m % (bw + 2) >= bw
+  // are junk that the epilogue skips.  One K block = one chunk = nine MMA batches; the weights are resident.
+  const bool win = p.a_win == 1;
+  const bool win2 = p.a_win == 2;
   const int b_half_bytes = (p.BN >> 1) * 128;
-  const int a_stage_bytes = win ? 17 * 1024 : 128 * 128;
+  const int a_stage_bytes = win2 ? p.a_slot : (win ? 17 * 1024 : 128 * 128);
   const int b_stage_bytes = p.b_res ? 0 : (win ? 3 * b_half_bytes : b_half_bytes);
   const int stage_bytes = a_stage_bytes + b_stage_bytes;  // multiple of 1024
   const int bres_tiles = p.b_res ? p.ntaps * p.kc_per_tap : 0;
   uint8_t* bres = smem;
   uint8_t* ring = smem + bres_tiles * b_half_bytes;
-  const int rows_used = p.bw * p.bh * p.bn;
-  const int num_kb = win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap;
+  const int rows_used = win2 ? p.bh * (p.bw + 2) : p.bw * p.bh * p.bn;  // GEMM rows a tile spans
+  const int num_kb = win2 ? p.kc_per_tap : (win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap);
   const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
   const int super_total = ((tiles_m + 1) >> 1) * p.tiles_n;  // pairs of M tiles x N tiles
   const int acc_stride = p.tmem_cols / p.sets;
@@ -1598,7 +1606,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
     grid_dep_wait();
     int stage = 0;
     uint32_t phase = 0;
-    const uint32_t a_tx = win ? 2u * (p.bw + 2) * 128u : 2u * rows_used * 128u;  // both CTAs' boxes
+    const uint32_t a_tx = win2 ? 2u * (p.bw + 2) * (p.bh + 2) * 128u
+                               : (win ? 2u * (p.bw + 2) * 128u : 2u * rows_used * 128u);  // both CTAs' boxes
     for (int step = 0; step < nsteps; ++step) {
       const CUtensorMap* tmA = CHAIN ? &p.chain[step].tmA : &p.tmA;
       const int a_c0 = CHAIN ? sp[step & 1].a_c0 : p.a_c0;
@@ -1612,7 +1621,10 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
             if (elect_one()) {
               uint8_t* sa = ring + stage * stage_bytes;
               if (rank == 0) mbar_expect_tx(&full_bar[stage], a_tx);
-              if (win) {
+              if (win2) {
+                // kb = chunk: the patch of pixels (h0-1 .. h0+bh, w0-1 .. w0+bw)
+                tma2_load_4d(sa, tmA, &full_bar[stage], a_c0 + kb * 64, w0 - 1, h0 - 1, n0);
+              } else if (win) {
                 // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
                 tma2_load_4d(sa, tmA, &full_bar[stage], a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
               } else {
@@ -1711,7 +1723,18 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
           tc_fence_after();
           const uint32_t sa = ring_u + stage * stage_bytes;
           const uint32_t a_lo = smem_desc_lo(sa);
-          if (win) {
+          if (win2) {
+            // nine taps = nine views of the patch, shifted by dy * (bw + 2) + dx pixel rows (128 B = 8 descriptor units)
+            const uint32_t pitch8 = static_cast<uint32_t>(p.bw + 2) * 8u;
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx)
+                umma2_bf16_batch4(d_tmem, a_lo + dy * pitch8 + dx * 8, bq + (dy * 3 + dx) * bstep, dhi, idesc,
+                                  (kb | dy | dx) != 0);
+            }
+            bq += bt16;
+          } else if (win) {
             // the horizontal taps are views of the window shifted by whole pixel rows (128 B = 8 descriptor units)
             if (p.b_res) {
               umma2_bf16_batch4(d_tmem, a_lo, bq, dhi, idesc, kb != 0);
@@ -1914,7 +1937,8 @@ int igemm_smem_bytes(const IgemmParams& p) {
   const int st = p.st_mode ? 8192 : (p.tst ? 2 * 4 * (p.BN >> 6) * 4096 : 0);
   if (p.cta2) {
     const int b_half = (p.BN >> 1) * 128;
-    const int stage2 = p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half);
+    const int stage2 = p.a_win == 2 ? p.a_slot
+                                    : (p.a_win ? 17 * 1024 + (p.b_res ? 0 : 3 * b_half) : 128 * 128 + (p.b_res ? 0 : b_half));
     return p.stages * stage2 + (p.b_res ? p.ntaps * p.kc_per_tap * b_half : 0) + 1024 + st + (p.chain_n ? kChainSmemBytes : 0);
   }
   const int row_bytes = p.kc * 2;
@@ -1985,8 +2009,13 @@ namespace {
 const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, cudaStream_t stream) {
   if (p.mode != kModeLinear || p.kc != 64 || p.splits != 1 || p.dual)
     return "igemm2: the CTA-pair kernel runs linear-mode convs with 64-channel chunks";
-  if (p.a_win && (p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.a_rank != 4 || p.bw > 128 || p.nphase > 1))
+  if (p.a_win == 1 && (p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.a_rank != 4 || p.bw > 128 || p.nphase > 1))
     return "igemm2: row-window mode needs a 3x3 stride-1 conv and single-row tiles";
+  if (p.a_win == 2 && (p.ntaps != 9 || p.bn != 1 || p.a_rank != 4 || p.nphase > 1 || !p.b_res || p.tiles_w != 1 ||
+                       p.bh * (p.bw + 2) > 128 || p.a_slot % 1024 || p.a_slot < (2 * (p.bw + 2) + 2 + 128) * 128 || p.stg ||
+                       p.tst || p.st_mode || p.chain_n))
+    return "igemm2: tile-window mode needs a 3x3 stride-1 conv, tiles of whole image rows and resident weights";
+  if (p.a_win < 0 || p.a_win > 2) return "igemm2: bad a_win";
   if (p.b_res && p.tiles_n != 1) return "igemm2: resident weights need one N tile";
   if (p.BN % 16 || p.BN < 32 || p.BN > 256) return "igemm2: BN must be a multiple of 16 in [32,256]";
   if (p.bw * p.bh * p.bn > 128 || p.bw * p.bh * p.bn <= 0) return "igemm2: M box must hold 1..128 rows";
@@ -2070,6 +2099,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
   if (p.nphase > 1 && (p.nphase != 4 || p.mode != kModeLinear || p.a_win || p.b_res || p.tpn < 1 ||
                        p.tiles_n != p.nphase * p.tpn))
     return "igemm: output phases need a plain linear-mode launch";
+  if (p.a_win == 2) return "igemm: tile-window mode runs on the CTA-pair kernel";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
   if (p.b_res && ((p.tiles_n != 1 && !p.aad_pair) || p.kc != 64 || p.splits != 1))

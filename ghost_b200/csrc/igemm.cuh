@@ -50,7 +50,11 @@ struct alignas(64) IgemmParams {
   // (kernel row, 64-channel chunk) serves the three horizontal taps as row-shifted UMMA views, so the A operand
   // crosses L2->shared 3x instead of 9x.  b_res: the whole packed weight slab stays resident in shared memory.
   int dual;    // 1: two MMA issuer warps (even / odd tiles), each with its own half of the operand ring
-  int a_win;   // 0 off, 1 on (the UMMA descriptor start address carries the row shift)
+  int a_win;   // 0 off, 1 row window (the UMMA descriptor start address carries the row shift), 2 tile window:
+               // CTA-pair kernel, narrow images - the (bh + 2) x (bw + 2) pixel patch of a tile of bh whole image rows
+               // is loaded once per 64-channel chunk (a_slot bytes per ring slot) and all NINE taps are shifted views
+               // of it; GEMM row m = pixel (m / (bw + 2), m % (bw + 2)), two junk rows per image row; weights resident
+  int a_slot;
   int b_res;
   // Linear mode, bf16 output, BN 128 / 256: 1 = for the last tile of a CTA every epilogue warp stages its 32 rows x
   // BN/4 columns in the (then idle) operand ring and moves whole row segments to / from global memory (residual in,
