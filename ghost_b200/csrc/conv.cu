@@ -456,7 +456,10 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     return e ? atoi(e) : 1;
   }();
   bool tst = tst_mode && !aad && !stats && !phases && !win2 && (!p.cta2 || win) && p.splits == 1 && is16(out.dtype) && !epi.out2 &&
-                   (p.BN == 64 || (p.BN == 128 && !win)) && w.Cout % 64 == 0 && p.bw % 32 == 0 && p.bh * p.bw * p.bn == 128 &&
+                   (p.BN == 64 || (p.BN == 128 && !win)) && w.Cout % 64 == 0 &&
+                   // pieces of 32 pixels of one image row: whole tiles of such pieces, or ONE tile per image row whose
+                   // last piece the TMA store clips at the image edge (iresnet's 112-pixel rows)
+                   ((p.bw % 32 == 0 && p.bh * p.bw * p.bn == 128) || (p.bh == 1 && p.bn == 1 && p.bw == Wo && p.bw > 32)) &&
                    taps.n * p.kc_per_tap <= 18 && out.sw % 8 == 0 && out.off % 8 == 0 &&
                    out.sh == static_cast<long long>(Wo) * out.sw && out.sn == static_cast<long long>(Ho) * Wo * out.sw &&
                    (!epi.res || (!(epi.r_off % 8) && !(epi.r_sw % 8) && !(epi.r_sh % 8) && !(epi.r_sn % 8)));

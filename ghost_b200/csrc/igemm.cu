@@ -2023,8 +2023,8 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   if ((p.sets != 2 && p.sets != 4) || p.tmem_cols < p.sets * p.BN || p.tmem_cols > 512 ||
       (p.tmem_cols & (p.tmem_cols - 1)) || p.tmem_cols < 32)
     return "igemm2: bad tmem_cols";
-  if (p.tst && (p.out_f32 || p.st_mode || p.stg || p.out2 || p.nphase > 1 || (p.BN != 64 && p.BN != 128) || p.bw % 32 ||
-                p.n_valid % 64))
+  if (p.tst && (p.out_f32 || p.st_mode || p.stg || p.out2 || p.nphase > 1 || (p.BN != 64 && p.BN != 128) ||
+                (p.bw % 32 && !(p.bh == 1 && p.bn == 1 && p.tiles_w == 1)) || p.n_valid % 64))
     return "igemm2: the TMA-store epilogue needs a plain 16-bit tile of 64 / 128 columns and rows of 32 pixels";
   if (p.ntaps * (p.nphase > 1 ? p.nphase : 1) > kIgemmMaxTaps) return "igemm2: too many taps";
   if (p.nphase > 1 && (p.nphase != 4 || p.tpn < 1 || p.tiles_n != p.nphase * p.tpn)) return "igemm2: bad phase tiling";
@@ -2108,7 +2108,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
                 p.n_valid % (p.BN >> 2)))
     return "igemm: staged output needs a bf16 linear epilogue and N tiles of 128 or 256 whole warp quarters";
   if (p.tst && (p.mode != kModeLinear || p.out_f32 || p.splits != 1 || p.st_mode || p.stg || p.out2 || p.nphase > 1 ||
-                (p.BN != 64 && p.BN != 128) || p.bw % 32 || p.n_valid % 64))
+                (p.BN != 64 && p.BN != 128) || (p.bw % 32 && !(p.bh == 1 && p.bn == 1 && p.tiles_w == 1)) || p.n_valid % 64))
     return "igemm: the TMA-store epilogue needs a plain 16-bit linear tile of 64 / 128 columns and rows of 32 pixels";
   const int smem = igemm_smem_bytes(p);
   if (smem > max_dyn_smem) return "igemm: shared memory budget exceeded";
