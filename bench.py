@@ -362,13 +362,23 @@ def run_ours(args):
     fsrc_d = torch.from_numpy(d["face_source"]).to(dev) if NS != B else None
 
     side, side_ev = torch.cuda.Stream(device=dev), torch.cuda.Event()
+    copy_st, copy_ev = torch.cuda.Stream(device=dev), torch.cuda.Event()
 
     def step_device(src, crp, frm, out):
+        # The frames of the step go into the output buffer first - a device-to-device copy that depends on nothing the
+        # networks compute, so it runs on its own stream while they work (out-of-place paste-back = this copy + the
+        # in-place composite below; paste_back(frames, ..., out=other) does the same copy on the calling stream).
+        main = torch.cuda.current_stream(dev)
+        copy_st.wait_stream(main)                    # the previous step is done with `out`
+        with torch.cuda.stream(copy_st):
+            out.copy_(frm, non_blocking=True)
+            copy_ev.record(copy_st)
         # ArcFace on the current stream, the attribute encoder (independent of z_id) beside it on `side`, then the
         # AAD generator; the generator output stays on the device
         ghost_b200.embed_and_swap(G, arc, src, crp, side=side, event=side_ev, write_u8=False, face_source=fsrc_d)
         yptr, ydt = G.y_nhwc(B, dev)
-        ghost_b200.paste_back(frm, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out)
+        main.wait_event(copy_ev)
+        ghost_b200.paste_back(out, (yptr, ydt, B), masks_d, tfms, face_frame, mode="exact", out=out)
 
     def barrier():
         torch.cuda.synchronize()
