@@ -530,7 +530,7 @@ def run_ours(args):
         up_ms, _, up_by, up_n = agg(prof_g, (4,))
         all_ms = sum(o["ms"] for o in prof_g + prof_a) + paste_ms
         conv_tf = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
-        roofline = {"kernel": "igemm_kernel (tcgen05 implicit-GEMM conv, %d launches/step incl. the two 64->3 convs of AADBlk8 on tapn_kernel)" % conv_n, "bound": "tensor",
+        roofline = {"kernel": "igemm_kernel / igemm2_kernel (tcgen05 implicit-GEMM conv, one CTA or cta_group::2 pairs; %d launches/step incl. the two 64->3 convs of AADBlk8 on tapn_kernel)" % conv_n, "bound": "tensor",
                     "achieved": conv_tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
                     "frac": conv_tf / pk["tf_sustained"], "traffic": ncu_traffic(),
                     "peak_source": pk["source"] + ", sustained",
