@@ -1647,6 +1647,27 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
           }
         }
       }
+      if (CHAIN && p.b_res && step + 1 < nsteps) {
+        // Resident weights of the NEXT step: as soon as the last MMAs of this step have retired (the accumulator-full
+        // barrier of its last tile) both CTAs refill their halves of the slab - under the epilogue of that tile, which
+        // nothing else overlaps.  The issuer waits for phase (step + 1) & 1 of bfull_bar.
+        const int my_groups = ngroups > cluster ? (ngroups - 1 - cluster) / nclusters + 1 : 0;
+        const int done = (step + 1) * my_groups * spg;  // tiles of this CTA so far
+        if (done > 0) {
+          const int it = done - 1;
+          const int as = p.sets == 4 ? (it & 3) : (it & 1);
+          const uint32_t aph = p.sets == 4 ? (it >> 2) & 1 : (it >> 1) & 1;
+          mbar_wait_nofail(&tfull_bar[as], aph, &abort_flag);
+        }
+        if (elect_one()) {
+          const IgemmParams* nx = p.chain + step + 1;
+          const int b_k0n = nx->b_k0;
+          if (rank == 0) mbar_expect_tx(&bfull_bar, 2u * bres_tiles * b_half_bytes);
+          for (int i = 0; i < bres_tiles; ++i)
+            tma2_load_2d(bres + i * b_half_bytes, &nx->tmB, &bfull_bar, b_k0n + i * 64, static_cast<int>(rank) * (p.BN >> 1));
+        }
+        __syncwarp();
+      }
       // the next conv of the chain reads what this cluster's epilogue warps are still writing
       if (CHAIN && step + 1 < nsteps) cluster_sync_all();
     }
@@ -1706,8 +1727,9 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
       int it = 0;
       int as = 0;
       uint32_t aphase = 0;
-      if (p.b_res) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
+      if (p.b_res && !CHAIN) mbar_wait_nofail(&bfull_bar, 0, &abort_flag);
       for (int step = 0; step < nsteps; ++step) {
+      if (p.b_res && CHAIN) mbar_wait_nofail(&bfull_bar, static_cast<uint32_t>(step & 1), &abort_flag);
       for (int gu = 0, ng = (ngroups > cluster ? (ngroups - 1 - cluster) / nclusters + 1 : 0) * spg; gu < ng; ++gu, ++it) {
         if (it != 0 && ++as == p.sets) {
           as = 0;
@@ -2013,7 +2035,7 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
     return "igemm2: row-window mode needs a 3x3 stride-1 conv and single-row tiles";
   if (p.a_win == 2 && (p.ntaps != 9 || p.bn != 1 || p.a_rank != 4 || p.nphase > 1 || !p.b_res || p.tiles_w != 1 ||
                        p.bh * (p.bw + 2) > 128 || p.a_slot % 1024 || p.a_slot < (2 * (p.bw + 2) + 2 + 128) * 128 || p.stg ||
-                       p.tst || p.st_mode || p.chain_n))
+                       p.tst || p.st_mode))
     return "igemm2: tile-window mode needs a 3x3 stride-1 conv, tiles of whole image rows and resident weights";
   if (p.a_win < 0 || p.a_win > 2) return "igemm2: bad a_win";
   if (p.b_res && p.tiles_n != 1) return "igemm2: resident weights need one N tile";
@@ -2038,8 +2060,8 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   int clusters = num_sms / 2;
   if (clusters > supers) clusters = supers;
   if (p.chain_n) {
-    if (p.chain_n < 2 || !p.chain || p.chain_spg < 1 || supers % p.chain_spg || (tiles_m & 1) || p.st_mode || p.tst || p.b_res ||
-        p.nphase > 1)
+    if (p.chain_n < 2 || !p.chain || p.chain_spg < 1 || supers % p.chain_spg || (tiles_m & 1) || p.st_mode || p.tst ||
+        (p.b_res && p.a_win != 2) || p.nphase > 1)
       return "igemm2: a conv chain needs whole groups of super tiles and the plain linear epilogue";
     clusters = num_sms / 2;
     if (clusters > supers / p.chain_spg) clusters = supers / p.chain_spg;
