@@ -28,8 +28,20 @@ void bn_fold_t(const HostTensor& g, const HostTensor& b, const HostTensor& rm, c
 }
 }  // namespace
 
+namespace {
+// GHOST_FOLD_BN1=0: keep bn1 as the second output of the producing conv (A/B switch for profiling)
+bool fold_bn1_mode() {
+  static const int on = [] {
+    const char* e = getenv("GHOST_FOLD_BN1");
+    return e ? atoi(e) : 1;
+  }();
+  return on != 0;
+}
+}  // namespace
+
 void Net::finalize_arcface() {
   const bool bf = is16(act_dtype);  // tensor-core mode: bf16 or fp16 storage
+  const bool fold_bn1 = fold_bn1_mode();
   auto bn = [&](const std::string& k, std::vector<float>* sc, std::vector<float>* sh) {
     bn_fold_t(W(k + ".weight"), W(k + ".bias"), W(k + ".running_mean"), W(k + ".running_var"), sc, sh);
   };
@@ -63,8 +75,43 @@ void Net::finalize_arcface() {
       bn(k + ".bn1", &sc, &sh);
       vecs_[n + ".bn1.scale"] = wpool_.upload(sc);
       vecs_[n + ".bn1.shift"] = wpool_.upload(sh);
+      const std::vector<float> s1 = sc, t1 = sh;
       bn(k + ".bn2", &sc, &sh);
-      pack_conv(n + ".conv1", k + ".conv1.weight", ci, pl, 3, sc, sh);
+      if (bf && fold_bn1 && ci % 32 == 0) {
+        // Tensor-core mode: bn1 folded into conv1.  conv1 pads bn1(x) = s1*x + t1 with zeros, so the scale goes into
+        // the weights (w * s1[ci]) and the shift reaches an output pixel only through the taps that lie inside the
+        // image: nine bias vectors, one per border class (igemm.cuh bias9).  No bn1 pass, no second output of the
+        // producing conv, one tensor less to write and read per block.
+        const HostTensor& w = W(k + ".conv1.weight");
+        if (w.shape != std::vector<int64_t>({pl, ci, 3, 3})) fail(-2, "unexpected shape for " + k + ".conv1.weight");
+        std::vector<float> rows(static_cast<size_t>(pl) * 9 * ci);
+        std::vector<double> wt(static_cast<size_t>(pl) * 9, 0.0);  // sum over ci of w * t1 per (co, tap)
+        for (int co = 0; co < pl; ++co)
+          for (int c = 0; c < ci; ++c)
+            for (int t = 0; t < 9; ++t) {
+              const float wv = w.data[(static_cast<size_t>(co) * ci + c) * 9 + t];
+              rows[(static_cast<size_t>(co) * 9 + t) * ci + c] = wv * sc[co] * s1[c];
+              wt[static_cast<size_t>(co) * 9 + t] += static_cast<double>(wv) * t1[c];
+            }
+        packed_[n + ".conv1"] = pack(rows, pl, 9 * ci, nullptr, false, true);
+        const int ld = packed_[n + ".conv1"].rows_pad;
+        std::vector<float> b9(static_cast<size_t>(9) * ld, 0.f);
+        for (int cls = 0; cls < 9; ++cls) {
+          const int rc = cls / 3, cc = cls % 3;  // 0 = first row / column, 1 = inner, 2 = last
+          for (int co = 0; co < pl; ++co) {
+            double acc = 0.0;
+            for (int t = 0; t < 9; ++t) {
+              const int dy = t / 3 - 1, dx = t % 3 - 1;
+              if ((rc == 0 && dy < 0) || (rc == 2 && dy > 0) || (cc == 0 && dx < 0) || (cc == 2 && dx > 0)) continue;
+              acc += wt[static_cast<size_t>(co) * 9 + t];
+            }
+            b9[static_cast<size_t>(cls) * ld + co] = sh[co] + sc[co] * static_cast<float>(acc);
+          }
+        }
+        vecs_[n + ".conv1.bias9"] = wpool_.upload(b9);
+      } else {
+        pack_conv(n + ".conv1", k + ".conv1.weight", ci, pl, 3, sc, sh);
+      }
       {
         std::vector<float> pr = W(k + ".prelu.weight").data;
         pr.resize((pl + 255) / 256 * 256, 0.f);
@@ -166,6 +213,7 @@ void Net::build_arcface(ExecPlan& p) {
   auto fuse_bn1 = [&](Epilogue* e, const Act& like, size_t next_blk) {
     t_fused = Act();
     if (!bf || next_blk >= names.size() || like.C % 16) return;
+    if (vecs_.count(names[next_blk] + ".conv1.bias9")) return;  // the next block's bn1 is folded into its conv1
     t_fused = new_act(like.H, like.W, like.C);
     e->out2 = t_fused.p;
     e->scale2 = vecs_.at(names[next_blk] + ".bn1.scale");
@@ -188,7 +236,10 @@ void Net::build_arcface(ExecPlan& p) {
       const int stride = i == 0 ? 2 : 1;
       const int ho = hw / stride;
       Act t = t_fused;
-      if (!t.p) {
+      const auto b9 = vecs_.find(n + ".conv1.bias9");
+      if (b9 != vecs_.end()) {
+        t = x;  // bn1 lives in conv1's weights and border-class biases
+      } else if (!t.p) {
         t = new_act(hw, hw, x.C);
         const Act xx = x, tt = t;
         const float* scv = vecs_.at(n + ".bn1.scale");
@@ -207,6 +258,10 @@ void Net::build_arcface(ExecPlan& p) {
         Epilogue e;
         e.act1 = kActPRelu;
         e.slope_c = vecs_.at(n + ".prelu");
+        if (b9 != vecs_.end()) {
+          e.bias9 = b9->second;
+          e.bias9_ld = packed_.at(n + ".conv1").rows_pad;
+        }
         add_conv(n + ".conv1", t, x.C, Taps::square(3, 1, 1), hw, hw, n + ".conv1", OutView::dense(u), e);
       }
       Act idn = x;

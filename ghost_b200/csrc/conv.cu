@@ -354,7 +354,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       return e ? atoi(e) : 1;
     }();
     const bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
-    const bool split_ok = !win && !epi.want_stats && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
+    const bool split_ok = !win && !epi.want_stats && !epi.bias9 && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
     for (int i = 0; i < 4; ++i) {
       const int c = cands0[i];
       if ((c > cpad0 && c != cands0[3]) || (bn_ && c != bn_)) continue;
@@ -591,6 +591,13 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
   p.f16 = in.dtype == kF16;
   if (!p.out_f32 && out.dtype != in.dtype) return "lower_conv: 16-bit output type must match the input";
   p.bias = w.bias;
+  if (epi.bias9) {
+    if (aad || p.splits != 1 || epi.bias9_ld < p.tiles_n * p.BN || epi.bias9_ld % 4)
+      return "lower_conv: a per-border-class bias needs a plain linear conv and rows padded to the N tiles";
+    p.bias = nullptr;
+    p.bias9 = epi.bias9;
+    p.bias9_ld = epi.bias9_ld;
+  }
   p.err = err_word;
   if (aad) {
     if (!is16(out.dtype)) return "lower_conv: AAD output must be a 16-bit tensor";

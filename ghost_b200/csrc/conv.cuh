@@ -44,6 +44,9 @@ struct PackedW {
 };
 
 struct Epilogue {
+  // tensor-core path: bias per border class of the output pixel, [9][bias9_ld] (igemm.cuh bias9), instead of PackedW::bias
+  const float* bias9 = nullptr;
+  int bias9_ld = 0;
   int act1 = kActNone;
   float slope = 0.f;
   const float* slope_c = nullptr;

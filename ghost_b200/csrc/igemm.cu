@@ -150,9 +150,16 @@ __device__ __forceinline__ uint32_t pack16_slope(float lo, float hi, float slope
 
 // acc + bias, first activation.  `sp` != nullptr: per-channel parameters of this CTA's N tile staged in shared
 // memory ([bias | slope | scale2 | shift2] x 256 floats, column j of the tile at sp[j]).
+// brow (optional): bias row of this pixel's border class (igemm.cuh bias9), used instead of p.bias
 __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (&f)[16], int col0, const float* sp,
-                                                   int j) {
-          if (p.bias) {
+                                                   int j, const float* brow = nullptr) {
+          if (brow) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(brow + col0) + i);
+              f[4 * i] += b.x, f[4 * i + 1] += b.y, f[4 * i + 2] += b.z, f[4 * i + 3] += b.w;
+            }
+          } else if (p.bias) {
             if (sp) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
@@ -190,10 +197,10 @@ __device__ __forceinline__ void linear_bias_act_16(const IgemmParams& p, float (
 // v -> final values of 16 full columns: bias, first activation, residual, second activation (no stores)
 template <bool F16>
 __device__ __forceinline__ void linear_values_16(const IgemmParams& p, const uint32_t (&v)[16], int col0, long long r_pix,
-                                                 const float* sp, int j, float (&f)[16]) {
+                                                 const float* sp, int j, float (&f)[16], const float* brow = nullptr) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-  linear_bias_act_16(p, f, col0, sp, j);
+  linear_bias_act_16(p, f, col0, sp, j, brow);
   if (p.res) {
     const __nv_bfloat16* rp = p.res + r_pix + col0;
     const uint4 q0 = __ldg(reinterpret_cast<const uint4*>(rp));
@@ -216,7 +223,7 @@ __device__ __forceinline__ void linear_values_16(const IgemmParams& p, const uin
 template <bool F16, bool FINAL = false>
 __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const uint32_t (&v)[16], int col0,
                                                    long long o_pix, long long r_pix, const float* sp, int j,
-                                                   float* stored = nullptr) {
+                                                   float* stored = nullptr, const float* brow = nullptr) {
           float f[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
@@ -227,7 +234,7 @@ __device__ __forceinline__ void linear_epilogue_16(const IgemmParams& p, const u
             for (int i = 0; i < 4; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
             return;
           }
-          linear_bias_act_16(p, f, col0, sp, j);
+          linear_bias_act_16(p, f, col0, sp, j, brow);
           const bool full16 = (col0 + 16 <= p.n_valid);
           if (p.res) {
             const __nv_bfloat16* rp = p.res + r_pix + col0;
@@ -468,6 +475,10 @@ struct LinEpi {
         }
         const int n = t.tn * p.bn + rn, oh = t.th * p.bh + rh, ow = t.tw * p.bw + rw;
         const bool valid = (r < rows_used) && (n < p.Nimg) && (oh < p.Ho) && (ow < p.Wo);
+        // bias per border class of the output pixel (igemm.cuh bias9): rows {first, inner, last} x columns likewise
+        const float* brow =
+            p.bias9 ? p.bias9 + ((oh == 0 ? 0 : (oh >= p.Ho - 1 ? 2 : 1)) * 3 + (ow == 0 ? 0 : (ow >= p.Wo - 1 ? 2 : 1))) * p.bias9_ld
+                    : nullptr;
         const uint32_t t_addr = tmem_lanes + as * acc_stride;
         const int ph = p.nphase > 1 ? t.nt / p.tpn : 0;
         const long long o_pix =
@@ -496,7 +507,7 @@ struct LinEpi {
               uint4 o0 = make_uint4(0u, 0u, 0u, 0u), o1 = o0;
               if (valid) {
                 float f[16];
-                linear_values_16<F16>(p, v, t.nt * p.BN + j, r_pix, staged ? eparm : nullptr, j, f);
+                linear_values_16<F16>(p, v, t.nt * p.BN + j, r_pix, staged ? eparm : nullptr, j, f, brow);
                 o0.x = pack16<F16>(f[0], f[1]);
                 o0.y = pack16<F16>(f[2], f[3]);
                 o0.z = pack16<F16>(f[4], f[5]);
@@ -570,7 +581,7 @@ struct LinEpi {
                 float f[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
+                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j, brow);
                 const int ch = (cg >> 3) + 2 * c;  // 16-byte chunk inside the 128-byte row
                 uint4* s0 = reinterpret_cast<uint4*>(my_row + ((ch ^ key) << 4));
                 uint4* s1 = reinterpret_cast<uint4*>(my_row + (((ch + 1) ^ key) << 4));
@@ -672,7 +683,7 @@ struct LinEpi {
                 float f[16];
 #pragma unroll
                 for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
-                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j);
+                linear_bias_act_16(p, f, t.nt * p.BN + j, staged ? eparm : nullptr, j, brow);
                 uint4* s0 = reinterpret_cast<uint4*>(my_row + (((2 * c) ^ my_key) << 4));
                 uint4* s1 = reinterpret_cast<uint4*>(my_row + (((2 * c + 1) ^ my_key) << 4));
                 if (p.res) {
@@ -766,7 +777,7 @@ struct LinEpi {
             tmem_ld_wait();
             const int col0 = t.nt * p.BN + j;
             if ((valid || p.splits > 1) && col0 < p.n_valid)
-              linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j, STATS ? st_tmp : nullptr);
+              linear_epilogue_16<F16>(p, v, col0, o_pix, r_pix, staged ? eparm : nullptr, j, STATS ? st_tmp : nullptr, brow);
             else if (STATS)
               st_zero();
             if (STATS) st_add(c, st_tmp);

@@ -67,6 +67,12 @@ struct alignas(64) IgemmParams {
   long long o_sn, o_sh, o_sw, o_off;  // element strides of the output pixel grid
   int out_f32;                        // 1: fp32 output, else bf16
   const float* bias;                  // [tiles_n*BN] or null
+  // Bias per border class of the output pixel, [9][bias9_ld] with class = 3 * {first row, inner, last row} + {first
+  // column, inner, last column}: what a per-channel affine (BatchNorm) in front of a zero-padded 3x3 conv turns into
+  // when it is folded into the conv - the shift only reaches the output through the taps that lie inside the image
+  // (iresnet bn1 -> conv1).  Replaces `bias` (which must be null); linear mode, no split-K.
+  const float* bias9;
+  int bias9_ld;
   int act1;
   float slope;
   const float* slope_c;  // per-channel PReLU slopes
