@@ -74,3 +74,26 @@ def test_conv_chain_is_bit_identical_to_separate_launches(batch, tmp_path):
         outs.append(np.load(out))
     assert np.isfinite(outs[1]).all()
     assert np.array_equal(outs[0], outs[1])
+
+
+def test_bn1_fold_matches_separate_bn1():
+    """Tensor-core mode folds bn1 into conv1: the scale into the weights, the shift into nine border-class bias
+    vectors (zero padding comes AFTER bn1 in IBasicBlock.forward, so the shift only reaches a pixel through the taps
+    inside the image).  With random BatchNorm statistics the folded forward must sit as close to the fp32 forward
+    (separate bn1 pass) as the unfolded one (GHOST_FOLD_BN1=0) - a wrong border class would not."""
+    import os
+    import re
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    rel = {}
+    for fold in ("0", "1"):
+        env = dict(os.environ, GHOST_FOLD_BN1=fold)
+        r = subprocess.run([sys.executable, os.path.join(root, "tools", "arc_fold_check.py"), "4"], env=env,
+                           capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        m = re.search(r"bf16 vs fp32: rel err max ([0-9.e+-]+)", r.stdout)
+        assert m, r.stdout
+        rel[fold] = float(m.group(1))
+    assert rel["1"] <= 2.5e-2, rel
+    assert abs(rel["1"] - rel["0"]) <= 4e-3, rel
