@@ -410,6 +410,33 @@ void Net::build_aei(ExecPlan& p) {
       });
       return q;
     };
+    // two layers that normalise the same tensor (shortcut + first main layer of a block): one fold launch
+    auto aad_fold_two = [&](const std::string& la, const std::string& lb, const float* sums, int sums_P, AadPre* qa,
+                            AadPre* qb) {
+      AadFoldSet fs[2];
+      AadPre* q[2] = {qa, qb};
+      const std::string* ln[2] = {&la, &lb};
+      for (int L = 0; L < 2; ++L) {
+        const AadInfo& info = aad_.at(*ln[L]);
+        q[L]->ncpar = p.pool.alloc_n<float4>(static_cast<size_t>(B) * b.cin);
+        q[L]->whf = p.pool.alloc_n<float>(static_cast<size_t>(B) * b.cin);
+        q[L]->bhf = p.pool.alloc_n<float>(B);
+        q[L]->mask = nullptr;
+        fs[L].off_gamma = info.off_gamma;
+        fs[L].off_beta = info.off_beta;
+        fs[L].w_h = vecs_.at(*ln[L] + ".wh");
+        fs[L].b_h = scalars_.at(*ln[L] + ".bh");
+        fs[L].ncpar = q[L]->ncpar;
+        fs[L].wh_fold = q[L]->whf;
+        fs[L].bh_fold = q[L]->bhf;
+        fs[L].scratch = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, b.cin));  // zeroed by the pool
+      }
+      const AadFoldSet f0 = fs[0], f1 = fs[1];
+      const int cx = b.cin;
+      add_op(la + "+" + lb.substr(lb.rfind('.') + 1) + ".fold", [=](cudaStream_t s) {
+        return aad_fold2_launch(sums, sums_P, B, HW, cx, zfc, ldz, f0, &f1, s);
+      });
+    };
     auto aad_layer = [&](const std::string& lname, const Act& h, const float* sums, int sums_P,
                          const AadPre* pre = nullptr) {
       const AadPre q = pre ? *pre : aad_fold(lname, sums, sums_P);
@@ -452,19 +479,25 @@ void Net::build_aei(ExecPlan& p) {
       float4* ncpar2 = p.pool.alloc_n<float4>(static_cast<size_t>(B) * 2 * cx);
       float* whf2 = p.pool.alloc_n<float>(static_cast<size_t>(B) * 2 * cx);
       float* bhf2 = p.pool.alloc_n<float>(2 * static_cast<size_t>(B));
+      AadFoldSet fs[2];
       for (int L = 0; L < 2; ++L) {
         const std::string lname = L == 0 ? S("blk%d.aadsc", k) : S("blk%d.aad0", k);
         const AadInfo& info = aad_.at(lname);
-        float* fsc = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, cx));  // zeroed by the pool
-        const float* wh = vecs_.at(lname + ".wh");
-        const float bh = scalars_.at(lname + ".bh");
-        const int og = info.off_gamma, ob = info.off_beta;
-        float4* ncp = ncpar2 + L * cx;
-        float* whp = whf2 + L * cx;
-        float* bhp = bhf2 + L * B;
+        fs[L].off_gamma = info.off_gamma;
+        fs[L].off_beta = info.off_beta;
+        fs[L].w_h = vecs_.at(lname + ".wh");
+        fs[L].b_h = scalars_.at(lname + ".bh");
+        fs[L].ncpar = ncpar2 + L * cx;
+        fs[L].wh_fold = whf2 + L * cx;
+        fs[L].bh_fold = bhf2 + L * B;
+        fs[L].scratch = p.pool.alloc_n<float>(aad_fold_scratch_floats(B, cx));  // zeroed by the pool
+        fs[L].ld_out = 2 * cx;
+      }
+      {
+        const AadFoldSet f0 = fs[0], f1 = fs[1];
         const float* sums = sums_m;
-        add_op(lname + ".fold", [=](cudaStream_t s) {
-          return aad_fold_launch(sums, parts_m, B, HW, cx, zfc, ldz, og, ob, wh, bh, ncp, whp, bhp, fsc, s, 2 * cx);
+        add_op(S("blk%d.aadsc+aad0.fold", k), [=](cudaStream_t s) {
+          return aad_fold2_launch(sums, parts_m, B, HW, cx, zfc, ldz, f0, &f1, s);
         });
       }
       AadArgs args;
@@ -476,9 +509,9 @@ void Net::build_aei(ExecPlan& p) {
     // c_x > 128: the masks of the shortcut layer and of the first main layer in one pass over m
     AadPre pre_sc{}, pre_0{};
     const bool mask2 = bf && !pair && b.cin != b.cout && b.cin > 128;
+    const bool fold2 = !pair && b.cin != b.cout;  // shortcut + first main layer: same statistics, one fold launch
+    if (fold2) aad_fold_two(S("blk%d.aadsc", k), S("blk%d.aad0", k), sums_m, parts_m, &pre_sc, &pre_0);
     if (mask2) {
-      pre_sc = aad_fold(S("blk%d.aadsc", k), sums_m, parts_m);
-      pre_0 = aad_fold(S("blk%d.aad0", k), sums_m, parts_m);
       pre_sc.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       pre_0.mask = p.pool.alloc_n<float>(static_cast<size_t>(B) * HW);
       const Act mm = m;
@@ -490,7 +523,7 @@ void Net::build_aei(ExecPlan& p) {
     }
     if (b.cin != b.cout) {
       sc = new_act(hw, hw, b.cout);
-      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, parts_m, mask2 ? &pre_sc : nullptr);
+      if (!pair) aad_layer(S("blk%d.aadsc", k), m, sums_m, parts_m, fold2 ? &pre_sc : nullptr);
       add_conv(S("blk%d.convsc", k), pair ? a2 : a, 0, b.cin, Taps::square(3, 1, 1), hw, hw, S("blk%d.convsc", k),
                OutView::dense(sc), Epilogue(), nullptr);
     }
@@ -510,7 +543,7 @@ void Net::build_aei(ExecPlan& p) {
     for (int i = 0; i < num_blocks; ++i) {
       const bool last = i == num_blocks - 1;
       const bool from_pair = pair && i == 0;
-      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x, sums_xP, (mask2 && i == 0) ? &pre_0 : nullptr);
+      if (!from_pair) aad_layer(S("blk%d.aad%d", k, i), x, sums_x, sums_xP, (fold2 && i == 0) ? &pre_0 : nullptr);
       const int co = last ? b.cout : b.cin;
       Act o = new_act(hw, hw, co);
       Epilogue e;

@@ -569,11 +569,19 @@ __global__ void __launch_bounds__(kStatThreads, 4) in_stats_kernel(const T* __re
 // order and lane 0 adds the lanes in a fixed order, so the statistics stay deterministic however many parts the
 // producers wrote.  The conv_h bias needs a sum over all channels: each block leaves its partial in
 // scratch[n][by], the last block of image n to finish (self-resetting counter) adds them in index order.
+// blockIdx.z selects the layer: two AADLayers that normalise the SAME tensor (the shortcut layer and the first main
+// layer of an AAD block) fold their parameters in one launch.
 __global__ void __launch_bounds__(256) aad_fold_kernel(const float* __restrict__ parts, int P, int HW, int C,
-                                                        const float* __restrict__ zfc, int ldz, int off_gamma,
-                                                        int off_beta, const float* __restrict__ w_h, float b_h,
-                                                        float4* __restrict__ ncpar, float* __restrict__ wh_fold,
-                                                        float* __restrict__ bh_fold, float* scratch, int ld_out) {
+                                                        const float* __restrict__ zfc, int ldz, const AadFoldSet fa,
+                                                        const AadFoldSet fb) {
+  const AadFoldSet& fs = blockIdx.z ? fb : fa;
+  const int off_gamma = fs.off_gamma, off_beta = fs.off_beta, ld_out = fs.ld_out;
+  const float* __restrict__ w_h = fs.w_h;
+  const float b_h = fs.b_h;
+  float4* __restrict__ ncpar = fs.ncpar;
+  float* __restrict__ wh_fold = fs.wh_fold;
+  float* __restrict__ bh_fold = fs.bh_fold;
+  float* scratch = fs.scratch;
   __shared__ double shs[256], shq[256];
   __shared__ float red[2];
   __shared__ int is_last;
@@ -865,9 +873,19 @@ size_t aad_fold_scratch_floats(int N, int C) { return static_cast<size_t>(N) * (
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
                             float* scratch, cudaStream_t s, int ld_out) {
-  dim3 grid(N, (C + 63) / 64);
-  aad_fold_kernel<<<grid, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, off_gamma, off_beta, w_h, b_h, ncpar, wh_fold,
-                                       bh_fold, scratch, ld_out > 0 ? ld_out : C);
+  AadFoldSet a;
+  a.off_gamma = off_gamma; a.off_beta = off_beta; a.w_h = w_h; a.b_h = b_h; a.ncpar = ncpar; a.wh_fold = wh_fold;
+  a.bh_fold = bh_fold; a.scratch = scratch; a.ld_out = ld_out;
+  return aad_fold2_launch(parts, P, N, HW, C, zfc, ldz, a, nullptr, s);
+}
+
+const char* aad_fold2_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz,
+                             const AadFoldSet& a, const AadFoldSet* b, cudaStream_t s) {
+  AadFoldSet fa = a, fb = b ? *b : a;
+  if (fa.ld_out <= 0) fa.ld_out = C;
+  if (fb.ld_out <= 0) fb.ld_out = C;
+  dim3 grid(N, (C + 63) / 64, b ? 2 : 1);
+  aad_fold_kernel<<<grid, 256, 0, s>>>(parts, P, HW, C, zfc, ldz, fa, fb);
   return last_err();
 }
 

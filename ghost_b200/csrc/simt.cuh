@@ -60,6 +60,19 @@ const char* in_stats_launch(const void* x, int dtype, int N, int HW, int C, floa
 //   ncpar[n][c] = per channel pair: {rstd0, rstd1, -mu0*rstd0, -mu1*rstd1}, {gamma_id0, gamma_id1, beta_id0, beta_id1}; wh_fold[n][c] = w_h[c]*rstd; bh_fold[n] = b_h - sum_c w_h*mu*rstd
 // scratch: aad_fold_scratch_floats(N, C) floats, zero before the first launch (the kernel leaves it zeroed)
 size_t aad_fold_scratch_floats(int N, int C);
+// the per-layer half of a fold (see aad_fold_launch); two layers on the same statistics share one launch
+struct AadFoldSet {
+  int off_gamma = 0, off_beta = 0;
+  const float* w_h = nullptr;
+  float b_h = 0.f;
+  float4* ncpar = nullptr;
+  float* wh_fold = nullptr;
+  float* bh_fold = nullptr;
+  float* scratch = nullptr;  // own scratch per layer
+  int ld_out = 0;
+};
+const char* aad_fold2_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz,
+                             const AadFoldSet& a, const AadFoldSet* b, cudaStream_t s);
 const char* aad_fold_launch(const float* parts, int P, int N, int HW, int C, const float* zfc, int ldz, int off_gamma,
                             int off_beta, const float* w_h, float b_h, float4* ncpar, float* wh_fold, float* bh_fold,
                             float* scratch, cudaStream_t s, int ld_out = 0);  // ld_out: row stride of ncpar / wh_fold (0 = C)
