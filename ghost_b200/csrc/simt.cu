@@ -780,6 +780,99 @@ __global__ void __launch_bounds__(256) aad_mask_kernel(const __nv_bfloat16* __re
   }
 }
 
+// The same mask with LPP lanes per pixel (32 channels per lane, 32 / LPP pixels per warp and iteration): the 27 % of
+// the issue slots that the one-warp-per-pixel kernel spends on the 5-step shuffle reduction, the sigmoid and the
+// bookkeeping of every pixel are shared by 4 (c_x = 256) or 2 (c_x = 512) pixels, and every lane has four
+// independent 16-byte loads in flight (ncu: the one-warp-per-pixel kernel ran at 61 % issue-slot utilisation and
+// 26 % of the DRAM rate on AADBlk6).  C = 32 * LPP; HW and the per-warp runs are multiples of 32 / LPP, so the pixels
+// of one iteration share their image.
+template <int LPP, bool DUAL, bool F16>
+__global__ void __launch_bounds__(256) aad_mask_lpp_kernel(const __nv_bfloat16* __restrict__ h, long long npix, int HW,
+                                                            const float* __restrict__ wh_fold,
+                                                            const float* __restrict__ bh_fold, float* __restrict__ mask,
+                                                            const float* __restrict__ wh_fold2,
+                                                            const float* __restrict__ bh_fold2, float* __restrict__ mask2) {
+  constexpr int G = 32 / LPP;  // pixels per warp and iteration
+  constexpr int C = 32 * LPP;
+  const int lane = threadIdx.x & 31;
+  const int g = lane / LPP, l = lane % LPP;
+  const long long warp0 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = (static_cast<long long>(gridDim.x) * blockDim.x) >> 5;
+  long long chunk = (npix + nwarps - 1) / nwarps;
+  chunk = (chunk + G - 1) / G * G;
+  const long long p0 = warp0 * chunk, pend = min(npix, p0 + chunk);
+  float w[4][8], u[DUAL ? 4 : 1][8];
+  float bh = 0.f, bh2 = 0.f;
+  int cur_n = -1;
+  for (long long base = p0; base < pend; base += G) {
+    const long long pix = base + g;  // (npix is a multiple of G: every lane group has a pixel)
+    uint4 q[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) q[it] = __ldg(reinterpret_cast<const uint4*>(h + pix * C + it * (LPP * 8) + l * 8));
+    const int n = static_cast<int>(base / HW);
+    if (n != cur_n) {
+      cur_n = n;
+      bh = __ldg(bh_fold + n);
+      if (DUAL) bh2 = __ldg(bh_fold2 + n);
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int c = it * (LPP * 8) + l * 8;
+        const float4 a0 = __ldg(reinterpret_cast<const float4*>(wh_fold + static_cast<long long>(n) * C + c));
+        const float4 a1 = __ldg(reinterpret_cast<const float4*>(wh_fold + static_cast<long long>(n) * C + c) + 1);
+        w[it][0] = a0.x; w[it][1] = a0.y; w[it][2] = a0.z; w[it][3] = a0.w;
+        w[it][4] = a1.x; w[it][5] = a1.y; w[it][6] = a1.z; w[it][7] = a1.w;
+        if (DUAL) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(wh_fold2 + static_cast<long long>(n) * C + c));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(wh_fold2 + static_cast<long long>(n) * C + c) + 1);
+          u[it][0] = b0.x; u[it][1] = b0.y; u[it][2] = b0.z; u[it][3] = b0.w;
+          u[it][4] = b1.x; u[it][5] = b1.y; u[it][6] = b1.z; u[it][7] = b1.w;
+        }
+      }
+    }
+    float acc = 0.f, acc2 = 0.f;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const uint32_t q4[4] = {q[it].x, q[it].y, q[it].z, q[it].w};
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (F16) {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&q4[i]));
+          v[2 * i] = f.x;
+          v[2 * i + 1] = f.y;
+        } else {
+          v[2 * i] = __uint_as_float(q4[i] << 16);
+          v[2 * i + 1] = __uint_as_float(q4[i] & 0xffff0000u);
+        }
+      }
+      acc += v[0] * w[it][0] + v[1] * w[it][1] + v[2] * w[it][2] + v[3] * w[it][3] + v[4] * w[it][4] + v[5] * w[it][5] +
+             v[6] * w[it][6] + v[7] * w[it][7];
+      if (DUAL)
+        acc2 += v[0] * u[it][0] + v[1] * u[it][1] + v[2] * u[it][2] + v[3] * u[it][3] + v[4] * u[it][4] + v[5] * u[it][5] +
+                v[6] * u[it][6] + v[7] * u[it][7];
+    }
+#pragma unroll
+    for (int o = LPP / 2; o > 0; o >>= 1) {
+      acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (DUAL) acc2 += __shfl_xor_sync(0xffffffffu, acc2, o);
+    }
+    if (l == 0) {
+      mask[pix] = 1.f / (1.f + __expf(-(acc + bh)));
+      if (DUAL) mask2[pix] = 1.f / (1.f + __expf(-(acc2 + bh2)));
+    }
+  }
+}
+
+template <int LPP, bool F16>
+void aad_mask_lpp_dispatch(unsigned blocks, cudaStream_t s, const __nv_bfloat16* h, long long npix, int HW,
+                           const float* wh_fold, const float* bh_fold, float* mask, const float* wh_fold2,
+                           const float* bh_fold2, float* mask2) {
+  if (wh_fold2)
+    aad_mask_lpp_kernel<LPP, true, F16><<<blocks, 256, 0, s>>>(h, npix, HW, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+  else
+    aad_mask_lpp_kernel<LPP, false, F16><<<blocks, 256, 0, s>>>(h, npix, HW, wh_fold, bh_fold, mask, nullptr, nullptr, nullptr);
+}
+
 template <int NIT, bool F16>
 void aad_mask_dispatch(unsigned blocks, cudaStream_t s, const __nv_bfloat16* h, long long npix, int HW, int C,
                        const float* wh_fold, const float* bh_fold, float* mask, const float* wh_fold2,
@@ -815,6 +908,25 @@ const char* aad_mask2_launch(const void* h, int N, int HW, int C, const float* w
   if (blocks > 148 * 16) blocks = 148 * 16;
   const __nv_bfloat16* hp = reinterpret_cast<const __nv_bfloat16*>(h);
   const unsigned nb = static_cast<unsigned>(blocks);
+  static const int lpp_mode = [] {
+    const char* e = getenv("GHOST_MASK_LPP");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  if (lpp_mode && (C == 256 || C == 512) && HW % (C == 256 ? 4 : 2) == 0) {
+    // several pixels per warp: a block of 8 warps covers 8 * G pixels per iteration
+    const int G = C == 256 ? 4 : 2;
+    long long bl = (npix + 8 * G - 1) / (8 * G);
+    if (bl > 148 * 16) bl = 148 * 16;
+    const unsigned nbl = static_cast<unsigned>(bl);
+    if (C == 256) {
+      if (dtype == kF16) aad_mask_lpp_dispatch<8, true>(nbl, s, hp, npix, HW, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+      else aad_mask_lpp_dispatch<8, false>(nbl, s, hp, npix, HW, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    } else {
+      if (dtype == kF16) aad_mask_lpp_dispatch<16, true>(nbl, s, hp, npix, HW, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+      else aad_mask_lpp_dispatch<16, false>(nbl, s, hp, npix, HW, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
+    }
+    return last_err();
+  }
   if (C <= 256)
     aad_mask_dispatch<1>(nb, s, dtype, hp, npix, HW, C, wh_fold, bh_fold, mask, wh_fold2, bh_fold2, mask2);
   else if (C <= 512)
