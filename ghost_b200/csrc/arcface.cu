@@ -120,8 +120,27 @@ void Net::finalize_arcface() {
       bn(k + ".bn3", &sc, &sh);
       pack_conv(n + ".conv2", k + ".conv2.weight", pl, pl, 3, sc, sh);
       if (i == 0) {
+        const std::vector<float> sc3 = sc, sh3 = sh;
         bn(k + ".downsample.1", &sc, &sh);
         pack_conv(n + ".down", k + ".downsample.0.weight", ci, pl, 1, sc, sh);
+        if (bf && ci % 64 == 0 && pl % 64 == 0) {
+          // Tensor-core mode: bn3(conv2(u)) + bn_d(downsample(x)) as ONE GEMM - the 1x1 stride-2 shortcut conv rides as
+          // extra K blocks behind the 3x3 taps (conv.cuh Epilogue::x2): rows [co] = [conv2 * sc3 | downsample * sc_d],
+          // bias = sh3 + sh_d.  No downsample launch, no residual read.
+          const HostTensor& w2 = W(k + ".conv2.weight");
+          const HostTensor& wd = W(k + ".downsample.0.weight");
+          const int K = 9 * pl + ci;
+          std::vector<float> rows(static_cast<size_t>(pl) * K);
+          std::vector<float> bias(pl);
+          for (int co = 0; co < pl; ++co) {
+            for (int c = 0; c < pl; ++c)
+              for (int t = 0; t < 9; ++t)
+                rows[static_cast<size_t>(co) * K + t * pl + c] = w2.data[(static_cast<size_t>(co) * pl + c) * 9 + t] * sc3[co];
+            for (int c = 0; c < ci; ++c) rows[static_cast<size_t>(co) * K + 9 * pl + c] = wd.data[static_cast<size_t>(co) * ci + c] * sc[co];
+            bias[co] = sh3[co] + sh[co];
+          }
+          packed_[n + ".conv2x"] = pack(rows, pl, K, &bias, false, true);
+        }
       }
     }
     inpl = pl;
@@ -195,6 +214,10 @@ void Net::build_arcface(ExecPlan& p) {
     if (!pend.empty() && !chain_compatible(pend.front(), lop)) flush();
     pend.push_back(lop);
   };
+  static const int fuse_down = [] {
+    const char* ev = getenv("GHOST_FUSE_DOWN");  // A/B switch for profiling
+    return ev ? atoi(ev) : 1;
+  }();
 
   // Block names in execution order: in bf16 mode the conv that produces a block's input also writes bn1(input)
   // as a second output (IBasicBlock.forward applies bn1 before conv1 and keeps x for the shortcut), which saves
@@ -265,14 +288,30 @@ void Net::build_arcface(ExecPlan& p) {
         add_conv(n + ".conv1", t, x.C, Taps::square(3, 1, 1), hw, hw, n + ".conv1", OutView::dense(u), e);
       }
       Act idn = x;
-      if (i == 0) {
+      Act o = new_act(ho, ho, pl);
+      bool fused_down = false;
+      if (i == 0 && bf && fuse_down && packed_.count(n + ".conv2x")) {
+        // conv2 + downsample shortcut as one launch, where the CTA-pair kernel applies at this batch size
+        Epilogue e;
+        e.x2 = x;
+        e.x2_cin = x.C;
+        fuse_bn1(&e, o, blk + 1);
+        LaunchOp lop;
+        lop.name = n + ".conv2+down";
+        if (!lower_conv(&lop, u, 0, pl, Taps::square(3, 1, stride), ho, ho, packed_.at(n + ".conv2x"), OutView::dense(o), e,
+                        false, err, nullptr)) {
+          if (!pend.empty() && !chain_compatible(pend.front(), lop)) flush();
+          pend.push_back(lop);
+          fused_down = true;
+        }
+      }
+      if (i == 0 && !fused_down) {
         idn = new_act(ho, ho, pl);
         Taps tp = Taps::point();
         tp.stride = 2;
         add_conv(n + ".down", x, x.C, tp, ho, ho, n + ".down", OutView::dense(idn), Epilogue());
       }
-      Act o = new_act(ho, ho, pl);
-      {
+      if (!fused_down) {
         Epilogue e;
         const OutView rv = OutView::dense(idn);
         e.res = idn.p;

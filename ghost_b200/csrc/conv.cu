@@ -115,7 +115,10 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     return "lower_conv: merged deconv phases need the plain tensor-core path";
   // per-phase channel count: the N tiling never crosses a phase
   const int cout_t = phases ? w.Cout / 4 : w.Cout;
-  if (w.K != taps.n * Cin) return "lower_conv: weight K does not match taps*Cin";
+  if (w.K != taps.n * Cin + epi.x2_cin) return "lower_conv: weight K does not match taps*Cin";
+  if (epi.x2_cin && (aad || phases || force_simt || Cin % 64 || epi.x2_cin % 64 || !epi.x2.p || epi.x2.N != in.N ||
+                     epi.x2.H != in.H || epi.x2.W != in.W || epi.x2.dtype != in.dtype || epi.x2.C % 8 || epi.want_stats || epi.res))
+    return "lower_conv: a second input tensor needs a plain tensor-core conv and an input-sized 16-bit tensor";
   op->flops = 2.0 * in.N * Ho * Wo * static_cast<double>(w.Cout) * w.K;
   const bool can_igemm = !force_simt && is16(in.dtype) && (Cin % 32 == 0) && (in.C % 8 == 0) && (c0 % 8 == 0) &&
                          w.wb != nullptr && (taps.stride == 1 || (taps.stride == 2 && in.H % 2 == 0 && in.W % 2 == 0));
@@ -317,6 +320,32 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     }
   }
 
+  if (epi.x2_cin) {
+    // the second tensor through tmH: same view, same box as tmA; one 1x1 tap at the conv's stride
+    const Act& x2 = epi.x2;
+    if (taps.stride == 1) {
+      const uint64_t dims[4] = {static_cast<uint64_t>(x2.C), static_cast<uint64_t>(x2.W), static_cast<uint64_t>(x2.H),
+                                static_cast<uint64_t>(x2.N)};
+      const uint64_t str[3] = {x2.C * eb, static_cast<uint64_t>(x2.W) * x2.C * eb,
+                               static_cast<uint64_t>(x2.H) * x2.W * x2.C * eb};
+      const uint32_t box[4] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.bw), static_cast<uint32_t>(p.bh),
+                               static_cast<uint32_t>(p.bn)};
+      if (const char* e = encode_tmap(&p.tmH, x2.p, 4, dims, str, box, swz)) return e;
+    } else {
+      const uint64_t dims[5] = {static_cast<uint64_t>(2 * x2.C), static_cast<uint64_t>(x2.W / 2), 2,
+                                static_cast<uint64_t>(x2.H / 2), static_cast<uint64_t>(x2.N)};
+      const uint64_t str[4] = {2 * x2.C * eb, static_cast<uint64_t>(x2.W) * x2.C * eb,
+                               2 * static_cast<uint64_t>(x2.W) * x2.C * eb,
+                               static_cast<uint64_t>(x2.H) * x2.W * x2.C * eb};
+      const uint32_t box[5] = {static_cast<uint32_t>(p.kc), static_cast<uint32_t>(p.bw), 1,
+                               static_cast<uint32_t>(p.bh), static_cast<uint32_t>(p.bn)};
+      if (const char* e = encode_tmap(&p.tmH, x2.p, 5, dims, str, box, swz)) return e;
+    }
+    p.x_kb = epi.x2_cin / 64;
+    p.x_c0 = 0;
+    p.x_tap_c = p.x_tap_w = p.x_tap_p = p.x_tap_h = 0;  // pixel (stride * o, stride * o): parity 0 of the split view
+  }
+
   // ---- N tiling
   if (aad) {
     const int cn = aad->pair ? aad->c_x / 2 : (aad->c_x < 128 ? aad->c_x : 128);
@@ -337,7 +366,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
     const int force2 = bn_hint >> 10;
     const long long tiles_m2 = static_cast<long long>(p.tiles_w) * p.tiles_h * p.tiles_nb;
     const int nph = phases ? 4 : 1;
-    const int nkb_all = taps.n * p.kc_per_tap;
+    const int nkb_all = taps.n * p.kc_per_tap + epi.x2_cin / 64;
     auto t1 = [](int bn) { return bn <= 128 ? 0.262 + 0.00022 * bn : 0.29 + 0.00105 * (bn - 128); };
     auto t2 = [](int bn) { return bn <= 128 ? 0.216 + 0.00033 * bn : 0.258 + 0.00095 * (bn - 128); };
     // Cost of a K block per SM, measured on B200 (tools/conv_sweep.py, us): one CTA 0.276 / 0.29 / 0.425 at N tiles
@@ -354,7 +383,7 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       return e ? atoi(e) : 1;
     }();
     const bool pair_ok = !win && p.kc == 64 && cout_t >= 32 && tiles_m2 >= 2 && cta2_mode != 0 && force2 != 2;
-    const bool split_ok = !win && !epi.want_stats && !epi.bias9 && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
+    const bool split_ok = !win && !epi.want_stats && !epi.bias9 && !epi.x2_cin && splitk_mode != 0 && force2 == 0 && !bn_ && nkb_all >= 16 && cout_t % 16 == 0;
     for (int i = 0; i < 4; ++i) {
       const int c = cands0[i];
       if ((c > cpad0 && c != cands0[3]) || (bn_ && c != bn_)) continue;
@@ -420,6 +449,12 @@ const char* lower_conv(LaunchOp* op, const Act& in, int c0, int Cin, const Taps&
       p.cta2 = 1;
       p.splits = 1;
       bn_ = w.Cout;
+    }
+    if (epi.x2_cin) {  // the extra K blocks exist on the pair kernel only
+      if (win || win2 || !pair_ok || !bn2) return "lower_conv: a second input tensor needs the CTA-pair kernel";
+      p.cta2 = 1;
+      p.splits = 1;
+      bn_ = bn2;
     }
     p.BN = bn_;
     p.tiles_n = nph * ((cout_t + p.BN - 1) / p.BN);

@@ -62,6 +62,12 @@ struct Epilogue {
   // lowering, LaunchOp::st_floats says how large the parts buffer must be (set_stats()), LaunchOp::ig.st_P is the P the
   // fold kernel reads it with
   bool want_stats = false;
+  // tensor-core path (CTA-pair kernel): a second input tensor whose x2_cin channels (a multiple of 64) follow the conv's
+  // own K columns in the packed weight matrix, read at the conv's stride with a 1x1 tap: out = conv(in) + pointwise(x2)
+  // in one accumulator (igemm.cuh x_kb).  x2 has the spatial size of `in`.  lower_conv fails when the CTA-pair kernel
+  // does not apply (the caller keeps the two-launch form for that shape).
+  Act x2;
+  int x2_cin = 0;
 };
 
 struct OutView {

@@ -1539,7 +1539,8 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
   uint8_t* bres = smem;
   uint8_t* ring = smem + bres_tiles * b_half_bytes;
   const int rows_used = win2 ? p.bh * (p.bw + 2) : p.bw * p.bh * p.bn;  // GEMM rows a tile spans
-  const int num_kb = win2 ? p.kc_per_tap : (win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap);
+  const int num_kb = win2 ? p.kc_per_tap : (win ? 3 * p.kc_per_tap : p.ntaps * p.kc_per_tap + p.x_kb);
+  const int main_kb = p.ntaps * p.kc_per_tap;  // (plain mode) blocks of the conv itself; the rest come from tmH
   const int tiles_m = p.tiles_w * p.tiles_h * p.tiles_nb;
   const int super_total = ((tiles_m + 1) >> 1) * p.tiles_n;  // pairs of M tiles x N tiles
   const int acc_stride = p.tmem_cols / p.sets;
@@ -1638,6 +1639,13 @@ __global__ void __launch_bounds__(kIgemmThreads, 1) igemm2_kernel(const __grid_c
               } else if (win) {
                 // kb = (kernel row `tap`, chunk kci): pixels w0-1 .. w0+bw of input row h0+tap-1
                 tma2_load_4d(sa, tmA, &full_bar[stage], a_c0 + kci * 64, w0 - 1, h0 + tap - 1, n0);
+              } else if (kb >= main_kb) {
+                // extra K blocks: 64-channel chunks of the second tensor (igemm.cuh x_kb)
+                const int c = p.x_c0 + p.x_tap_c + (kb - main_kb) * 64;
+                if (p.a_rank == 4)
+                  tma2_load_4d(sa, &p.tmH, &full_bar[stage], c, w0 + p.x_tap_w, h0 + p.x_tap_h, n0);
+                else
+                  tma2_load_5d(sa, &p.tmH, &full_bar[stage], c, w0 + p.x_tap_w, p.x_tap_p, h0 + p.x_tap_h, n0);
               } else {
                 const int c = a_c0 + p.tap_c[tap] + kci * 64;
                 if (p.a_rank == 4)
@@ -2070,6 +2078,8 @@ const char* igemm2_launch(const IgemmParams& p, int max_dyn_smem, int num_sms, c
   if (supers <= 0) return "igemm2: empty grid";
   int clusters = num_sms / 2;
   if (clusters > supers) clusters = supers;
+  if (p.x_kb && (p.a_win || p.b_res || p.chain_n || p.nphase > 1 || p.x_kb < 0))
+    return "igemm2: extra K blocks from a second tensor need the plain tap-shifted mode";
   if (p.chain_n) {
     if (p.chain_n < 2 || !p.chain || p.chain_spg < 1 || supers % p.chain_spg || (tiles_m & 1) || p.st_mode || p.tst ||
         (p.b_res && p.a_win != 2) || p.nphase > 1)
@@ -2133,6 +2143,7 @@ const char* igemm_launch(const IgemmParams& p, cudaStream_t stream) {
                        p.tiles_n != p.nphase * p.tpn))
     return "igemm: output phases need a plain linear-mode launch";
   if (p.a_win == 2) return "igemm: tile-window mode runs on the CTA-pair kernel";
+  if (p.x_kb) return "igemm: extra K blocks from a second tensor run on the CTA-pair kernel";
   if (p.a_win && (p.kc != 64 || p.ntaps != 9 || p.bh != 1 || p.bn != 1 || p.splits != 1 || p.a_rank != 4 || p.bw > 128))
     return "igemm: row-window mode needs a 3x3 stride-1 conv, 64-channel chunks and single-row tiles";
   if (p.b_res && ((p.tiles_n != 1 && !p.aad_pair) || p.kc != 64 || p.splits != 1))

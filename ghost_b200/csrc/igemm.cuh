@@ -173,6 +173,14 @@ struct alignas(64) IgemmParams {
   const IgemmParams* chain;
   int chain_n, chain_spg;
 
+  // Second activation tensor as extra K blocks (CTA-pair kernel, plain tap-shifted loads): after the ntaps * kc_per_tap
+  // blocks of the conv, x_kb more blocks load 64-channel chunks of ANOTHER tensor through tmH (same box, same rank as
+  // tmA, tap coordinates x_tap_*) against the K columns that follow in the packed weight matrix: out = conv(A) + 1x1
+  // conv(X) in one accumulator - iresnet's stride-2 blocks, conv2(u) + downsample(x), without the downsample launch
+  // and without a residual read.
+  int x_kb, x_c0;
+  short x_tap_c, x_tap_w, x_tap_p, x_tap_h;
+
   int* err;  // device word set non-zero when a pipeline wait timed out
 };
 
