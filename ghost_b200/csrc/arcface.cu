@@ -63,21 +63,71 @@ void Net::finalize_arcface() {
   bn("bn1", &sc, &sh);
   pack_conv("stem", "conv1.weight", 3, 64, 3, sc, sh);
   vecs_["stem.prelu"] = wpool_.upload(W("prelu.weight").data);
+  // Tensor-core mode, blocks 1..48: the residual stream is stored SHIFTED, x' = x + c with c = t1 / s1 of the block that
+  // reads it.  Then bn1(x) = s1 * x' exactly, zero padding included (pad(s1 * x') = s1 * pad(x')), so bn1 is nothing but
+  // a scale in conv1's weights - no border-class biases - and the constants move into biases: the conv2 that writes
+  // x'_{b+1} adds c_{b+1} and, where it reads x'_b as its residual, subtracts c_b; a downsample conv reading x'_b
+  // subtracts W_d c_b.  Block 0 reads the stem's PReLU output, which cannot carry a constant: it keeps the nine
+  // border-class biases (igemm.cuh bias9), as does any block whose bn1 scale is too small to divide by.
+  static const int xshift_mode = [] {
+    const char* e = getenv("GHOST_XSHIFT");  // A/B switch for profiling
+    return e ? atoi(e) : 1;
+  }();
+  std::vector<std::vector<float>> cshift;  // per block: c (empty = not shifted)
+  {
+    int ip = 64;
+    for (int l = 0; l < 4; ++l)
+      for (int i = 0; i < kLayers[l]; ++i) {
+        char kb[64];
+        snprintf(kb, sizeof(kb), "layer%d.%d", l + 1, i);
+        const int ci = i == 0 ? ip : kPlanes[l];
+        std::vector<float> c;
+        if (bf && fold_bn1 && xshift_mode && !cshift.empty() && ci % 32 == 0) {
+          std::vector<float> s1v, t1v;
+          bn(std::string(kb) + ".bn1", &s1v, &t1v);
+          c.resize(ci);
+          bool ok = true;
+          for (int ch = 0; ch < ci && ok; ++ch) {
+            if (fabsf(s1v[ch]) < 1e-3f) ok = false;
+            else c[ch] = t1v[ch] / s1v[ch];
+            if (ok && fabsf(c[ch]) > 8.f) ok = false;
+          }
+          if (!ok) c.clear();
+        }
+        cshift.push_back(c);
+        if (i == kLayers[l] - 1) ip = kPlanes[l];
+      }
+    cshift.push_back(std::vector<float>());  // the head reads the plain stream
+  }
+  size_t blk_i = 0;
   int inpl = 64;
   for (int l = 0; l < 4; ++l) {
     const int pl = kPlanes[l];
-    for (int i = 0; i < kLayers[l]; ++i) {
+    for (int i = 0; i < kLayers[l]; ++i, ++blk_i) {
       char kb[64], nb[64];
       snprintf(kb, sizeof(kb), "layer%d.%d", l + 1, i);
       snprintf(nb, sizeof(nb), "l%d.%d", l + 1, i);
       const std::string k = kb, n = nb;
       const int ci = i == 0 ? inpl : pl;
+      const std::vector<float>& ck = cshift[blk_i];      // shift of the stream this block reads (ci channels) or empty
+      const std::vector<float>& cn = cshift[blk_i + 1];  // shift of the stream this block writes (pl channels) or empty
       bn(k + ".bn1", &sc, &sh);
       vecs_[n + ".bn1.scale"] = wpool_.upload(sc);
       vecs_[n + ".bn1.shift"] = wpool_.upload(sh);
       const std::vector<float> s1 = sc, t1 = sh;
       bn(k + ".bn2", &sc, &sh);
-      if (bf && fold_bn1 && ci % 32 == 0) {
+      if (!ck.empty()) {
+        // shifted input stream: bn1 is the scale s1 in the weights, nothing else
+        const HostTensor& w = W(k + ".conv1.weight");
+        if (w.shape != std::vector<int64_t>({pl, ci, 3, 3})) fail(-2, "unexpected shape for " + k + ".conv1.weight");
+        std::vector<float> rows(static_cast<size_t>(pl) * 9 * ci);
+        for (int co = 0; co < pl; ++co)
+          for (int c = 0; c < ci; ++c)
+            for (int t = 0; t < 9; ++t)
+              rows[(static_cast<size_t>(co) * 9 + t) * ci + c] = w.data[(static_cast<size_t>(co) * ci + c) * 9 + t] * sc[co] * s1[c];
+        packed_[n + ".conv1"] = pack(rows, pl, 9 * ci, &sh, false, true);
+        scalars_[n + ".conv1.folded"] = 1.f;  // marks "reads the (shifted) stream directly" for build_arcface
+      } else if (bf && fold_bn1 && ci % 32 == 0) {
         // Tensor-core mode: bn1 folded into conv1.  conv1 pads bn1(x) = s1*x + t1 with zeros, so the scale goes into
         // the weights (w * s1[ci]) and the shift reaches an output pixel only through the taps that lie inside the
         // image: nine bias vectors, one per border class (igemm.cuh bias9).  No bn1 pass, no second output of the
@@ -118,10 +168,23 @@ void Net::finalize_arcface() {
         vecs_[n + ".prelu"] = wpool_.upload(pr);
       }
       bn(k + ".bn3", &sc, &sh);
+      // shifted streams: + c of the stream written; - c of the stream read back as the residual (stride-1 blocks)
+      for (int co = 0; co < pl; ++co) {
+        if (!cn.empty()) sh[co] += cn[co];
+        if (i != 0 && !ck.empty()) sh[co] -= ck[co];
+      }
       pack_conv(n + ".conv2", k + ".conv2.weight", pl, pl, 3, sc, sh);
       if (i == 0) {
         const std::vector<float> sc3 = sc, sh3 = sh;
         bn(k + ".downsample.1", &sc, &sh);
+        if (!ck.empty()) {  // the downsample conv reads x' = x + c: take W_d c back out
+          const HostTensor& wd0 = W(k + ".downsample.0.weight");
+          for (int co = 0; co < pl; ++co) {
+            double acc = 0.0;
+            for (int c = 0; c < ci; ++c) acc += static_cast<double>(wd0.data[static_cast<size_t>(co) * ci + c]) * ck[c];
+            sh[co] -= sc[co] * static_cast<float>(acc);
+          }
+        }
         pack_conv(n + ".down", k + ".downsample.0.weight", ci, pl, 1, sc, sh);
         if (bf && ci % 64 == 0 && pl % 64 == 0) {
           // Tensor-core mode: bn3(conv2(u)) + bn_d(downsample(x)) as ONE GEMM - the 1x1 stride-2 shortcut conv rides as
@@ -236,7 +299,8 @@ void Net::build_arcface(ExecPlan& p) {
   auto fuse_bn1 = [&](Epilogue* e, const Act& like, size_t next_blk) {
     t_fused = Act();
     if (!bf || next_blk >= names.size() || like.C % 16) return;
-    if (vecs_.count(names[next_blk] + ".conv1.bias9")) return;  // the next block's bn1 is folded into its conv1
+    if (vecs_.count(names[next_blk] + ".conv1.bias9") || scalars_.count(names[next_blk] + ".conv1.folded"))
+      return;  // the next block's bn1 is folded into its conv1
     t_fused = new_act(like.H, like.W, like.C);
     e->out2 = t_fused.p;
     e->scale2 = vecs_.at(names[next_blk] + ".bn1.scale");
@@ -260,8 +324,8 @@ void Net::build_arcface(ExecPlan& p) {
       const int ho = hw / stride;
       Act t = t_fused;
       const auto b9 = vecs_.find(n + ".conv1.bias9");
-      if (b9 != vecs_.end()) {
-        t = x;  // bn1 lives in conv1's weights and border-class biases
+      if (b9 != vecs_.end() || scalars_.count(n + ".conv1.folded")) {
+        t = x;  // bn1 lives in conv1's weights (and border-class biases, or the shift of the stream)
       } else if (!t.p) {
         t = new_act(hw, hw, x.C);
         const Act xx = x, tt = t;
